@@ -1,0 +1,264 @@
+/*
+ * hppb200.h — C ABI of the B200-native batched validation engine.
+ *
+ * This is the drop-in boundary for hpp-core's data-parallel hot path
+ * (SURVEY.md §8b).  Every entry point takes plain pointers and sizes, returns
+ * a status code (no exceptions cross the ABI) and is what a hpp-core adapter
+ *  binds in place of the reference virtuals:
+ *
+ *   hppb200_validate_configs   <- hpp::core::ConfigValidations::validate /
+ *                                 CollisionValidation::validate /
+ *                                 JointBoundValidation::validate
+ *                                 (reference src/config-validations.cc:40-49,
+ *                                  src/collision-validation.cc:48-95,
+ *                                  src/joint-bound-validation.cc:45-80)
+ *   hppb200_validate_edges     <- PathValidation::validate for
+ *                                 pathValidation::Discretized
+ *                                 (src/path-validation/discretized.cc:55-107),
+ *                                 continuousValidation::Progressive
+ *                                 (src/continuous-validation/progressive.cc:78-129),
+ *                                 continuousValidation::Dichotomy
+ *                                 (src/continuous-validation/dichotomy.cc:68-132)
+ *   hppb200_straight_lengths   <- steeringMethod::Straight::impl_compute
+ *                                 (src/steering-method/straight.cc:38-51) /
+ *                                 WeighedDistance::impl_distance
+ *                                 (src/weighed-distance.cc:272-289)
+ *   hppb200_knn_*              <- nearestNeighbor::Basic::{search,KnearestSearch,
+ *                                 withinBall} (src/nearest-neighbor/basic.cc:52-181)
+ *   hppb200_model_*            <- ObstacleUser::{addRobotCollisionPairs,addObstacle,
+ *                                 setSecurityMargins} (src/obstacle-user.cc:53-241),
+ *                                 ContinuousValidation::{Initialize,AddObstacle}
+ *                                 (src/continuous-validation.cc:63-118),
+ *                                 SolidSolidCollision ctor
+ *                                 (src/continuous-validation/solid-solid-collision.cc:162-299)
+ *
+ * All floating-point data is IEEE-754 binary64 (hpp::core::value_type,
+ * reference include/hpp/core/fwd.hh:174).  Matrices are row-major.
+ * A rigid placement is 12 doubles: R (9, row-major) then t (3).
+ *
+ * There is no CPU fallback behind this ABI: every compute entry point needs a
+ * CUDA device and fails with HPPB200_ERR_CUDA otherwise.
+ */
+#ifndef HPPB200_H
+#define HPPB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HPPB200_ABI_VERSION 1
+
+/* ---- status codes ------------------------------------------------------ */
+enum {
+  HPPB200_OK = 0,
+  HPPB200_ERR_INVALID_ARGUMENT = 1, /* std::invalid_argument in the reference */
+  HPPB200_ERR_RUNTIME = 2,          /* std::runtime_error in the reference    */
+  HPPB200_ERR_CUDA = 3,             /* no device / CUDA failure               */
+  HPPB200_ERR_UNSUPPORTED = 4
+};
+
+/* ---- joint types (pinocchio joint models reachable from hpp-pinocchio) -- */
+enum {
+  HPPB200_JOINT_REVOLUTE_X = 0, /* bounded revolute, nq = nv = 1 (R^1, rotation) */
+  HPPB200_JOINT_REVOLUTE_Y = 1,
+  HPPB200_JOINT_REVOLUTE_Z = 2,
+  HPPB200_JOINT_PRISMATIC_X = 3, /* nq = nv = 1 (R^1, translation) */
+  HPPB200_JOINT_PRISMATIC_Y = 4,
+  HPPB200_JOINT_PRISMATIC_Z = 5,
+  HPPB200_JOINT_FREEFLYER = 6 /* R^3 x SO(3): nq = 7 (x y z qx qy qz qw), nv = 6 */
+};
+
+/* ---- shape types (coal::ShapeBase subclasses used by the path) ---------- */
+enum {
+  HPPB200_SHAPE_SPHERE = 0,  /* params: radius                                 */
+  HPPB200_SHAPE_CAPSULE = 1, /* params: radius, halfLength (axis = local z)    */
+  HPPB200_SHAPE_BOX = 2,     /* params: half extents hx, hy, hz                */
+  HPPB200_SHAPE_CONVEX = 3   /* vertices [vert_begin, vert_begin+vert_count)   */
+};
+
+/* ---- edge validation methods ------------------------------------------- */
+enum {
+  HPPB200_METHOD_DISCRETIZED = 0, /* param = step size (> 0)  */
+  HPPB200_METHOD_PROGRESSIVE = 1, /* param = tolerance (> 0)  */
+  HPPB200_METHOD_DICHOTOMY = 2    /* param = tolerance (== 0) */
+};
+
+/* ---- per-item result codes written to `status`/`reason` arrays ---------- */
+enum {
+  HPPB200_REASON_VALID = 0,
+  HPPB200_REASON_COLLISION = 1,   /* CollisionValidationReport        */
+  HPPB200_REASON_JOINT_BOUND = 2, /* JointBoundValidationReport       */
+  HPPB200_REASON_ITER_CAP = 3     /* continuous validation hit max_iterations
+                                     (the reference has no cap; flagged, never
+                                     silently accepted)                        */
+};
+
+/*
+ * Robot + environment description, the flattened form of what hpp-core reads
+ * from pinocchio::Model / GeomModel (robot) and from the obstacle GeomModel
+ * (ProblemSolver::addObstacle, reference src/problem-solver.cc:863-901).
+ * Joint indices are pinocchio's: 0 is the universe, moving joints are
+ * 1..njoints and parent[i] < i.  Arrays indexed by joint have njoints entries,
+ * entry k describing joint k+1.
+ */
+typedef struct hppb200_model_desc {
+  int32_t njoints;
+  const int32_t* joint_parent;    /* [njoints] parent joint index (0 = universe)   */
+  const int32_t* joint_type;      /* [njoints] HPPB200_JOINT_*                     */
+  const double* joint_placement;  /* [njoints][12] placement in the parent frame   */
+  const double* q_lower;          /* [nq] lower configuration bounds               */
+  const double* q_upper;          /* [nq] upper configuration bounds               */
+
+  int32_t ngeoms;                 /* robot collision geometries (pinocchio order)  */
+  const int32_t* geom_joint;      /* [ngeoms] parent joint (0 = fixed to universe) */
+  const double* geom_placement;   /* [ngeoms][12] placement in the joint frame     */
+  const int32_t* geom_shape;      /* [ngeoms] HPPB200_SHAPE_*                      */
+  const double* geom_params;      /* [ngeoms][4]                                   */
+  const int32_t* geom_vert_begin; /* [ngeoms] (convex only, else 0)                */
+  const int32_t* geom_vert_count; /* [ngeoms]                                      */
+
+  int32_t nself_pairs;            /* active GeomModel::collisionPairs, in order    */
+  const int32_t* self_pairs;      /* [nself_pairs][2] geometry indices             */
+
+  int32_t nobstacles;             /* obstacles in addObstacle() call order         */
+  const double* obst_placement;   /* [nobstacles][12] world placement              */
+  const int32_t* obst_shape;      /* [nobstacles]                                  */
+  const double* obst_params;      /* [nobstacles][4]                               */
+  const int32_t* obst_vert_begin; /* [nobstacles]                                  */
+  const int32_t* obst_vert_count; /* [nobstacles]                                  */
+
+  int32_t nvertices;
+  const double* vertices;         /* [nvertices][3] shared convex vertex pool      */
+
+  /* (njoints+1)x(njoints+1) security-margin matrix indexed by joint index
+     (ObstacleUser::setSecurityMargins, reference src/obstacle-user.cc:166-196);
+     NULL = all zero.  Obstacles use row/column 0. */
+  const double* security_margins;
+
+  double break_distance;          /* ContinuousValidation::breakDistance, default 1e-2
+                                     (reference src/continuous-validation.cc:411);
+                                     only affects BVH pairs in coal, kept for API
+                                     fidelity */
+  const double* weights;          /* [njoints] WeighedDistance::weights(); NULL = 1 */
+} hppb200_model_desc;
+
+typedef struct hppb200_model hppb200_model;         /* immutable compiled tables   */
+typedef struct hppb200_workspace hppb200_workspace; /* one CUDA stream + scratch   */
+typedef struct hppb200_knn hppb200_knn;             /* device mirror of roadmap nodes */
+
+typedef struct hppb200_stats {
+  uint64_t configs;          /* configurations run through FK                  */
+  uint64_t pair_tests;       /* narrow-phase calls actually executed           */
+  uint64_t gjk_iterations;   /* summed GJK iterations                          */
+  uint64_t edge_samples;     /* path samples evaluated by edge validation      */
+  uint64_t kernel_launches;  /* CUDA kernels launched by this workspace        */
+  uint64_t iter_cap_hits;    /* edges that ended with HPPB200_REASON_ITER_CAP  */
+  double last_kernel_ms;     /* device time of the last validate_* call        */
+} hppb200_stats;
+
+/* ---- library ----------------------------------------------------------- */
+int hppb200_abi_version(void);
+const char* hppb200_last_error(void); /* thread-local message of the last failure */
+int hppb200_device_count(void);       /* 0 when no CUDA device is visible        */
+
+/* ---- model ------------------------------------------------------------- */
+int hppb200_model_create(const hppb200_model_desc* desc, hppb200_model** out);
+void hppb200_model_destroy(hppb200_model* m);
+int hppb200_model_nq(const hppb200_model* m);
+int hppb200_model_nv(const hppb200_model* m);
+/* Configuration-validation pair table in cPairs_ order:
+   geomA is a robot geometry, geomB >= 0 a robot geometry or -(k+1) for obstacle k. */
+int hppb200_model_num_config_pairs(const hppb200_model* m);
+int hppb200_model_get_config_pairs(const hppb200_model* m, int32_t* geomA,
+                                   int32_t* geomB, double* margin);
+/* Continuous-validation body pairs in intervalValidations_ order. */
+int hppb200_model_num_body_pairs(const hppb200_model* m);
+/* joint_a/joint_b [nbp]; geom-pair range [pair_begin[i], pair_begin[i+1]) into
+   (pairA, pairB); coefficient range [coef_begin[i], coef_begin[i+1]) a->b and
+   [rcoef_begin[i], rcoef_begin[i+1]) b->a.  Any output pointer may be NULL. */
+int hppb200_model_get_body_pairs(const hppb200_model* m, int32_t* joint_a,
+                                 int32_t* joint_b, int32_t* pair_begin,
+                                 int32_t* coef_begin, int32_t* rcoef_begin);
+int hppb200_model_num_body_geom_pairs(const hppb200_model* m);
+int hppb200_model_get_body_geom_pairs(const hppb200_model* m, int32_t* geomA,
+                                      int32_t* geomB, double* margin);
+int hppb200_model_num_coefficients(const hppb200_model* m, int reverse);
+int hppb200_model_get_coefficients(const hppb200_model* m, int reverse,
+                                   int32_t* joint, double* value);
+/* Body::radius() per joint index 0..njoints (pinocchio GeomData::radius). */
+int hppb200_model_get_body_radii(const hppb200_model* m, double* radius);
+
+/* ---- workspace --------------------------------------------------------- */
+int hppb200_workspace_create(const hppb200_model* m, int device,
+                             hppb200_workspace** out);
+void hppb200_workspace_destroy(hppb200_workspace* ws);
+int hppb200_get_stats(const hppb200_workspace* ws, hppb200_stats* out);
+/* Use an externally owned cudaStream_t (e.g. torch's current stream). */
+int hppb200_workspace_set_stream(hppb200_workspace* ws, void* cuda_stream);
+
+/* ---- configuration validation ----------------------------------------- */
+#define HPPB200_CHECK_JOINT_BOUNDS 1u /* JointBoundValidation first, as in the default
+                                         Problem (reference src/problem.cc)          */
+#define HPPB200_DEVICE_POINTERS 2u    /* in/out arrays already live on the device    */
+
+/* q [n][nq]; valid [n] (1 valid / 0 invalid); first_pair [n] index of the first
+   colliding pair in cPairs_ order, or the violated configuration rank for a joint
+   bound, -1 when valid; reason [n] HPPB200_REASON_* (may be NULL). */
+int hppb200_validate_configs(hppb200_workspace* ws, const double* q, size_t n,
+                             uint32_t flags, uint8_t* valid, int32_t* first_pair,
+                             uint8_t* reason);
+
+/* Forward kinematics only: oMg [n][ngeoms][12] robot geometry world placements
+   (pinocchio::forwardKinematics + updateGeometryPlacements). Test/diagnostic. */
+int hppb200_geometry_placements(hppb200_workspace* ws, const double* q, size_t n,
+                                uint32_t flags, double* oMg);
+
+/* Signed distance minus security margin (coal distance_lower_bound semantics for
+   shape pairs) of every configuration-validation pair: dist [n][npairs].
+   Test/diagnostic; mirrors DistanceBetweenObjects (src/distance-between-objects.cc). */
+int hppb200_pair_distances(hppb200_workspace* ws, const double* q, size_t n,
+                           uint32_t flags, double* dist);
+
+/* ---- edge (StraightPath) validation ------------------------------------ */
+/* L[i] = WeighedDistance(q1[i], q2[i]) (steeringMethod::Straight). */
+int hppb200_straight_lengths(hppb200_workspace* ws, const double* q1,
+                             const double* q2, size_t n, uint32_t flags, double* L);
+
+/* Edge i is the StraightPath from q1[i] to q2[i] over [0, L[i]].
+   valid [n]; t_fail [n] report->parameter (NaN when valid); t_last_valid [n] end of
+   the valid part (forward: validPart = extract(0, t_last_valid); reverse:
+   extract(t_last_valid, L)); pair [n] colliding pair (cPairs_ index for Discretized,
+   body-pair geometry-pair index for continuous methods; configuration rank for a
+   joint bound), -1 when valid; reason [n] HPPB200_REASON_*. */
+int hppb200_validate_edges(hppb200_workspace* ws, int method, double param,
+                           int reverse, const double* q1, const double* q2,
+                           const double* L, size_t n, uint32_t flags,
+                           uint8_t* valid, double* t_fail, double* t_last_valid,
+                           int32_t* pair, uint8_t* reason);
+/* Iteration cap per edge for continuous methods (default 1<<20). */
+int hppb200_workspace_set_max_iterations(hppb200_workspace* ws, uint32_t max_iter);
+
+/* ---- nearest neighbour (WeighedDistance brute force) ------------------- */
+int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out);
+void hppb200_knn_destroy(hppb200_knn* nn);
+/* Append nodes (roadmap insertion order = scan order); cc [n] connected-component
+   label per node (may be NULL = 0). */
+int hppb200_knn_append(hppb200_knn* nn, const double* q, const int32_t* cc, size_t n);
+int hppb200_knn_relabel(hppb200_knn* nn, int32_t from_cc, int32_t to_cc);
+size_t hppb200_knn_size(const hppb200_knn* nn);
+/* queries [nqueries][nq]; cc < 0 searches the whole roadmap.  idx [nqueries][k]
+   nearest first (-1 padded), dist [nqueries][k]. */
+int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries,
+                      int k, int32_t cc, uint32_t flags, int64_t* idx, double* dist);
+/* count [nqueries]; idx [nqueries][cap] in scan order (strict d < radius). */
+int hppb200_knn_within_ball(hppb200_knn* nn, const double* queries, size_t nqueries,
+                            double radius, int32_t cc, size_t cap, int64_t* idx,
+                            int64_t* count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HPPB200_H */
