@@ -1,0 +1,229 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_math.hpp header).
+//
+// CPU restatement of hpp-core's configuration validation (one configuration at a
+// time, first-hit semantics), StraightPath, and the discretized path validation.
+// Each function cites the reference file:line it follows (paths relative to
+// /root/reference).  PARITY UNPINNED for numeric outputs (reference tests assert only
+// cross-method invariants); the invariants are re-asserted in tests/.
+#pragma once
+#include <algorithm>
+#include <cstring>
+
+#include "oracle_model.hpp"
+
+namespace oracle {
+
+// include/hpp/core/collision-pair.hh:45-81 — (first, second) objects + request margin.
+// second < 0 encodes obstacle -(second+1).
+struct CollisionPair {
+  int first = 0, second = 0;
+  double margin = 0;
+};
+
+struct PairResult {
+  bool collision = false;
+  double distanceLowerBound = kInf;
+};
+
+// CollisionPair::collide -> coal::ComputeCollision (Appendix A.4)
+inline PairResult collidePair(const Device& dev, const DeviceData& data, const CollisionPair& p, GjkStats* st) {
+  const Geometry& A = dev.geoms[p.first];
+  const SE3& TA = data.oMg[p.first];
+  const Geometry& B = p.second >= 0 ? dev.geoms[p.second] : dev.obstacles[-(p.second + 1)];
+  const SE3& TB = p.second >= 0 ? data.oMg[p.second] : B.placement;
+  double d = shapeDistance(A.shape, TA, B.shape, TB, st);
+  PairResult r;
+  r.distanceLowerBound = d - p.margin;
+  r.collision = r.distanceLowerBound <= kCollisionThreshold;
+  return r;
+}
+
+// src/obstacle-user.cc:53-76 (addObstacle: joint-major, inner objects of each body),
+// :222-235 (addRobotCollisionPairs: active self pairs first), :166-196 (margins).
+struct ObstacleUser {
+  const Device* dev;
+  std::vector<CollisionPair> cPairs;
+
+  explicit ObstacleUser(const Device& d) : dev(&d) {
+    for (auto& sp : d.selfPairs) cPairs.push_back({sp.first, sp.second, 0.0});  // addRobotCollisionPairs
+    for (size_t o = 0; o < d.obstacles.size(); ++o) addObstacle((int)o);
+    setSecurityMargins();
+  }
+  void addObstacle(int o) {
+    // robot_->nbJoints()/jointAt(j): moving joints only, model joint j+1 (Appendix A.3)
+    for (int j = 1; j <= dev->njoints(); ++j)
+      for (size_t g = 0; g < dev->geoms.size(); ++g)
+        if (dev->geoms[g].joint == j) cPairs.push_back({(int)g, -(o + 1), 0.0});
+  }
+  void setSecurityMargins() {
+    for (auto& p : cPairs) {
+      int j1 = dev->geoms[p.first].joint;
+      int j2 = p.second >= 0 ? dev->geoms[p.second].joint : 0;
+      p.margin = dev->margin(j1, j2);
+    }
+  }
+  // src/obstacle-user.cc:42-51 — sequential loop, stop at first hit.
+  bool collide(const DeviceData& data, size_t& i, GjkStats* st) const {
+    for (i = 0; i < cPairs.size(); ++i)
+      if (collidePair(*dev, data, cPairs[i], st).collision) return true;
+    return false;
+  }
+};
+
+struct ConfigReport {
+  int reason = HPPB200_REASON_VALID;
+  int index = -1;  // first colliding pair / violated configuration rank
+};
+
+// src/collision-validation.cc:48-95
+struct CollisionValidation : ObstacleUser {
+  explicit CollisionValidation(const Device& d) : ObstacleUser(d) {}
+  bool validate(const double* q, ConfigReport& rep, GjkStats* st = nullptr) const {
+    DeviceData data;
+    dev->forwardKinematics(q, data);
+    size_t i = 0;
+    if (collide(data, i, st)) {
+      rep.reason = HPPB200_REASON_COLLISION;
+      rep.index = (int)i;
+      return false;
+    }
+    rep = ConfigReport();
+    return true;
+  }
+};
+
+// src/joint-bound-validation.cc:45-80 — first violated rank wins.
+struct JointBoundValidation {
+  const Device* dev;
+  explicit JointBoundValidation(const Device& d) : dev(&d) {}
+  bool validate(const double* q, ConfigReport& rep) const {
+    for (int i = 0; i < dev->nq; ++i) {
+      // free-flyer quaternion ranks carry no bounds (lower > upper in pinocchio => skipped)
+      if (dev->lower[i] > dev->upper[i]) continue;
+      if (q[i] < dev->lower[i] || dev->upper[i] < q[i]) {
+        rep.reason = HPPB200_REASON_JOINT_BOUND;
+        rep.index = i;
+        return false;
+      }
+    }
+    rep = ConfigReport();
+    return true;
+  }
+};
+
+// src/config-validations.cc:40-49 — AND, first failure's report.
+struct ConfigValidations {
+  JointBoundValidation jb;
+  CollisionValidation cv;
+  bool checkBounds;
+  ConfigValidations(const Device& d, bool bounds) : jb(d), cv(d), checkBounds(bounds) {}
+  bool validate(const double* q, ConfigReport& rep, GjkStats* st = nullptr) const {
+    if (checkBounds && !jb.validate(q, rep)) return false;
+    return cv.validate(q, rep, st);
+  }
+};
+
+// ---- Lie-group pieces (hpp-pinocchio LiegroupSpace, Appendix A.3) -------------
+// q1 (-) q0, size nv.  R^n joints: plain difference.
+inline void lieDifference(const Device& dev, const double* q1, const double* q0, double* v) {
+  for (int i = 1; i <= dev.njoints(); ++i) {
+    const Joint& J = dev.joints[i];
+    if (J.type == HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("free-flyer Lie ops not in the oracle yet");
+    v[J.idx_v] = q1[J.idx_q] - q0[J.idx_q];
+  }
+}
+// interpolate(q0,q1,u) = q0 (+) u*(q1 (-) q0); R^n: fma(u, q1-q0, q0)
+inline void lieInterpolate(const Device& dev, const double* q0, const double* q1, double u, double* q) {
+  for (int i = 1; i <= dev.njoints(); ++i) {
+    const Joint& J = dev.joints[i];
+    if (J.type == HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("free-flyer Lie ops not in the oracle yet");
+    q[J.idx_q] = std::fma(u, q1[J.idx_q] - q0[J.idx_q], q0[J.idx_q]);
+  }
+}
+
+// src/weighed-distance.cc:272-289 — sqrt(sum_j squaredDistance_j(q1,q2,w_j^2)).
+// Vector-space rotation joints: w^2 * dq^2; translations unweighted (Appendix A.3).
+inline double weighedDistance(const Device& dev, const double* q1, const double* q2) {
+  double res = 0;
+  for (int i = 1; i <= dev.njoints(); ++i) {
+    const Joint& J = dev.joints[i];
+    double w2 = dev.weights[i - 1] * dev.weights[i - 1];
+    double dq = q2[J.idx_q] - q1[J.idx_q];
+    double d;
+    if (J.type <= HPPB200_JOINT_REVOLUTE_Z) d = w2 * (dq * dq);
+    else if (J.type <= HPPB200_JOINT_PRISMATIC_Z) d = dq * dq;
+    else throw std::invalid_argument("free-flyer Lie ops not in the oracle yet");
+    res += d;
+  }
+  return std::sqrt(res);
+}
+
+// src/straight-path.cc:91-158, src/steering-method/straight.cc:38-51
+struct StraightPath {
+  const Device* dev;
+  std::vector<double> initial, end;
+  double t0 = 0, t1 = 0;  // paramRange == timeRange (no time parameterization)
+  StraightPath(const Device& d, const double* q1, const double* q2, double L)
+      : dev(&d), initial(q1, q1 + d.nq), end(q2, q2 + d.nq), t0(0), t1(L) {}
+  double length() const { return t1 - t0; }
+  // impl_compute :91-110 — endpoints returned bit-exactly
+  void eval(double* q, double param) const {
+    const double L = t1 - t0;
+    if (param == t0 || L == 0) { std::memcpy(q, initial.data(), sizeof(double) * dev->nq); return; }
+    if (param == t1) { std::memcpy(q, end.data(), sizeof(double) * dev->nq); return; }
+    double u = (param - t0) / L;
+    lieInterpolate(*dev, initial.data(), end.data(), u, q);
+  }
+  // impl_velocityBound :132-140 — |end (-) initial| / L, zero for zero-length paths
+  void velocityBound(double* vb) const {
+    if (t0 == t1) { for (int i = 0; i < dev->nv; ++i) vb[i] = 0; return; }
+    lieDifference(*dev, end.data(), initial.data(), vb);
+    const double L = t1 - t0;
+    for (int i = 0; i < dev->nv; ++i) vb[i] = std::fabs(vb[i]) / L;
+  }
+};
+
+struct PathReport {
+  bool valid = true;
+  double parameter = std::numeric_limits<double>::quiet_NaN();  // report->parameter
+  double lastValid = 0;  // forward: validPart = extract(tmin,lastValid); reverse: extract(lastValid,tmax)
+  int reason = HPPB200_REASON_VALID;
+  int index = -1;
+  uint64_t samples = 0;
+};
+
+// src/path-validation/discretized.cc:55-107
+struct Discretized {
+  ConfigValidations cfg;
+  double stepSize;
+  Discretized(const Device& d, double step, bool bounds) : cfg(d, bounds), stepSize(step) {}
+  PathReport validate(const StraightPath& path, bool reverse, GjkStats* st = nullptr) const {
+    PathReport R;
+    const double tmin = path.t0, tmax = path.t1;
+    unsigned finished = 0;
+    std::vector<double> q(path.dev->nq);
+    double T1, step, lastValidTime;
+    if (reverse) { lastValidTime = tmax; T1 = tmin; step = -stepSize; }
+    else { lastValidTime = tmin; T1 = tmax; step = stepSize; }
+    double t = lastValidTime;
+    bool valid = true;
+    while (finished < 2 && valid) {
+      path.eval(q.data(), t);
+      ConfigReport cr;
+      R.samples++;
+      if (!cfg.validate(q.data(), cr, st)) {
+        R.parameter = t; R.reason = cr.reason; R.index = cr.index;
+        valid = false;
+      } else {
+        lastValidTime = t;
+        t += step;
+      }
+      if ((reverse && t < T1) || (!reverse && t > T1)) { t = T1; finished++; }
+    }
+    R.valid = valid;
+    R.lastValid = valid ? (reverse ? tmin : tmax) : lastValidTime;
+    return R;
+  }
+};
+
+}  // namespace oracle
