@@ -1,0 +1,230 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY (see oracle_math.hpp header).
+// extern "C" surface of the oracle for ctypes (tests/, smoke(), bench.py cpu_baseline).
+// Batch drivers use OpenMP over independent configurations / edges, one working copy of
+// the body-pair state per thread, as the reference does with its pools
+// (src/continuous-validation.cc:193-205, tests/test-continuous-validation.cc:324).
+#include <omp.h>
+
+#include <memory>
+
+#include "oracle_continuous.hpp"
+#include "oracle_nn.hpp"
+
+using namespace oracle;
+
+struct OracleHandle {
+  std::unique_ptr<Device> dev;
+  std::unique_ptr<Roadmap> roadmap;
+  GjkStats stats;
+  uint64_t pairEvals = 0, samples = 0;
+};
+
+static thread_local std::string g_err;
+
+extern "C" {
+
+const char* oracle_last_error() { return g_err.c_str(); }
+
+int oracle_create(const hppb200_model_desc* desc, OracleHandle** out) {
+  try {
+    auto h = new OracleHandle;
+    h->dev.reset(new Device(*desc));
+    h->roadmap.reset(new Roadmap(*h->dev));
+    *out = h;
+    return 0;
+  } catch (std::exception& e) { g_err = e.what(); return 1; }
+}
+void oracle_destroy(OracleHandle* h) { delete h; }
+int oracle_nq(OracleHandle* h) { return h->dev->nq; }
+int oracle_nv(OracleHandle* h) { return h->dev->nv; }
+
+void oracle_sincos(const double* x, size_t n, double* s, double* c) {
+  for (size_t i = 0; i < n; ++i) sincos_portable(x[i], s + i, c + i);
+}
+
+// ---- tables -----------------------------------------------------------------
+int oracle_num_config_pairs(OracleHandle* h) { return (int)ObstacleUser(*h->dev).cPairs.size(); }
+void oracle_get_config_pairs(OracleHandle* h, int32_t* a, int32_t* b, double* margin) {
+  ObstacleUser ou(*h->dev);
+  for (size_t i = 0; i < ou.cPairs.size(); ++i) { a[i] = ou.cPairs[i].first; b[i] = ou.cPairs[i].second; margin[i] = ou.cPairs[i].margin; }
+}
+int oracle_num_body_pairs(OracleHandle* h) { return (int)ContinuousValidation(*h->dev, 0).intervalValidations_.size(); }
+int oracle_num_body_geom_pairs(OracleHandle* h) { return (int)ContinuousValidation(*h->dev, 0).allGeomPairs.size(); }
+int oracle_num_coefficients(OracleHandle* h, int reverse) {
+  ContinuousValidation cv(*h->dev, 0);
+  size_t n = 0;
+  for (auto& s : cv.intervalValidations_) n += reverse ? s.coefficientsReverse.size() : s.coefficients.size();
+  return (int)n;
+}
+void oracle_get_body_pairs(OracleHandle* h, int32_t* ja, int32_t* jb, int32_t* pair_begin, int32_t* coef_begin, int32_t* rcoef_begin) {
+  ContinuousValidation cv(*h->dev, 0);
+  int pb = 0, cb = 0, rb = 0;
+  size_t i = 0;
+  for (auto& s : cv.intervalValidations_) {
+    ja[i] = s.joint_a; jb[i] = s.joint_b; pair_begin[i] = pb; coef_begin[i] = cb; rcoef_begin[i] = rb;
+    pb += (int)s.pairs.size(); cb += (int)s.coefficients.size(); rb += (int)s.coefficientsReverse.size();
+    ++i;
+  }
+  pair_begin[i] = pb; coef_begin[i] = cb; rcoef_begin[i] = rb;
+}
+void oracle_get_body_geom_pairs(OracleHandle* h, int32_t* a, int32_t* b, double* margin) {
+  ContinuousValidation cv(*h->dev, 0);
+  for (size_t i = 0; i < cv.allGeomPairs.size(); ++i) { a[i] = cv.allGeomPairs[i].first; b[i] = cv.allGeomPairs[i].second; margin[i] = cv.allGeomPairs[i].margin; }
+}
+void oracle_get_coefficients(OracleHandle* h, int reverse, int32_t* joint, double* value) {
+  ContinuousValidation cv(*h->dev, 0);
+  size_t k = 0;
+  for (auto& s : cv.intervalValidations_)
+    for (auto& c : (reverse ? s.coefficientsReverse : s.coefficients)) { joint[k] = c.joint; value[k] = c.value; ++k; }
+}
+void oracle_get_body_radii(OracleHandle* h, double* r) {
+  std::vector<double> v = h->dev->bodyRadii();
+  for (size_t i = 0; i < v.size(); ++i) r[i] = v[i];
+}
+
+// ---- FK / distances ------------------------------------------------------------
+void oracle_geometry_placements(OracleHandle* h, const double* q, size_t n, double* oMg) {
+  const Device& d = *h->dev;
+  DeviceData data;
+  for (size_t i = 0; i < n; ++i) {
+    d.forwardKinematics(q + i * d.nq, data);
+    for (size_t g = 0; g < d.geoms.size(); ++g) data.oMg[g].to12(oMg + (i * d.geoms.size() + g) * 12);
+  }
+}
+void oracle_pair_distances(OracleHandle* h, const double* q, size_t n, double* dist) {
+  const Device& d = *h->dev;
+  ObstacleUser ou(d);
+  DeviceData data;
+  for (size_t i = 0; i < n; ++i) {
+    d.forwardKinematics(q + i * d.nq, data);
+    for (size_t p = 0; p < ou.cPairs.size(); ++p)
+      dist[i * ou.cPairs.size() + p] = collidePair(d, data, ou.cPairs[p], nullptr).distanceLowerBound;
+  }
+}
+// distance between two shapes given as (type, params[4], placement[12]); convex verts optional
+double oracle_shape_distance(int ta, const double* pa, const double* Ta, const double* va, int na, int tb,
+                             const double* pb, const double* Tb, const double* vb, int nb) {
+  Shape A, B;
+  A.type = ta; B.type = tb;
+  for (int k = 0; k < 4; ++k) { A.p[k] = pa[k]; B.p[k] = pb[k]; }
+  A.verts = va; A.nverts = na; B.verts = vb; B.nverts = nb;
+  return shapeDistance(A, SE3::from12(Ta), B, SE3::from12(Tb), nullptr);
+}
+
+// ---- configuration validation ----------------------------------------------------
+int oracle_validate_configs(OracleHandle* h, const double* q, size_t n, uint32_t flags, uint8_t* valid,
+                            int32_t* first_pair, uint8_t* reason, int nthreads) {
+  const Device& d = *h->dev;
+  ConfigValidations cv(d, flags & HPPB200_CHECK_JOINT_BOUNDS);
+  uint64_t calls = 0, iters = 0;
+  if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 256) num_threads(nthreads) reduction(+ : calls, iters)
+  for (long i = 0; i < (long)n; ++i) {
+    ConfigReport rep;
+    GjkStats st;
+    bool ok = cv.validate(q + (size_t)i * d.nq, rep, &st);
+    valid[i] = ok ? 1 : 0;
+    if (first_pair) first_pair[i] = rep.index;
+    if (reason) reason[i] = (uint8_t)rep.reason;
+    calls += st.calls; iters += st.iterations;
+  }
+  h->stats.calls += calls; h->stats.iterations += iters;
+  return 0;
+}
+
+// ---- edges -----------------------------------------------------------------------
+void oracle_straight_lengths(OracleHandle* h, const double* q1, const double* q2, size_t n, double* L) {
+  const Device& d = *h->dev;
+  for (size_t i = 0; i < n; ++i) L[i] = weighedDistance(d, q1 + i * d.nq, q2 + i * d.nq);
+}
+
+int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse, const double* q1, const double* q2,
+                          const double* L, size_t n, uint32_t flags, uint8_t* valid, double* t_fail, double* t_last_valid,
+                          int32_t* pair, uint8_t* reason, uint64_t* samples, int order_mode, uint64_t max_iter, int nthreads) {
+  const Device& d = *h->dev;
+  if (nthreads <= 0) nthreads = omp_get_max_threads();
+  if (order_mode == ORDER_PERSISTENT) nthreads = 1;  // history-dependent: sequential like one reference thread
+  int err = 0;
+  uint64_t evals = 0, nsamples = 0;
+#pragma omp parallel num_threads(nthreads) reduction(+ : evals, nsamples)
+  {
+    try {
+      std::unique_ptr<Discretized> disc;
+      std::unique_ptr<Progressive> prog;
+      std::unique_ptr<Dichotomy> dich;
+      if (method == HPPB200_METHOD_DISCRETIZED) disc.reset(new Discretized(d, param, flags & HPPB200_CHECK_JOINT_BOUNDS));
+      else if (method == HPPB200_METHOD_PROGRESSIVE) { prog.reset(new Progressive(d, param)); prog->orderMode = order_mode; if (max_iter) prog->maxIterations = max_iter; }
+      else { dich.reset(new Dichotomy(d, param)); dich->orderMode = order_mode; if (max_iter) dich->maxIterations = max_iter; }
+#pragma omp for schedule(dynamic, 16)
+      for (long i = 0; i < (long)n; ++i) {
+        StraightPath path(d, q1 + (size_t)i * d.nq, q2 + (size_t)i * d.nq, L[i]);
+        PathReport R;
+        uint64_t ev = 0;
+        if (disc) R = disc->validate(path, reverse != 0);
+        else if (prog) R = prog->validate(path, reverse != 0, nullptr, &ev);
+        else R = dich->validate(path, reverse != 0, nullptr, &ev);
+        valid[i] = R.valid ? 1 : 0;
+        if (t_fail) t_fail[i] = R.parameter;
+        if (t_last_valid) t_last_valid[i] = R.lastValid;
+        if (pair) pair[i] = R.index;
+        if (reason) reason[i] = (uint8_t)R.reason;
+        if (samples) samples[i] = R.samples;
+        evals += ev; nsamples += R.samples;
+      }
+    } catch (std::exception& e) {
+#pragma omp critical
+      { g_err = e.what(); err = 2; }
+    }
+  }
+  h->pairEvals += evals; h->samples += nsamples;
+  return err;
+}
+
+void oracle_get_counters(OracleHandle* h, uint64_t* out4) {
+  out4[0] = h->stats.calls; out4[1] = h->stats.iterations; out4[2] = h->pairEvals; out4[3] = h->samples;
+}
+
+// ---- intervals (pinned against oracle/_ref) ----------------------------------------
+// Applies n unions, writes the resulting list (max cap intervals) and returns its size.
+int oracle_intervals_union(const double* lo, const double* hi, size_t n, double* out_lo, double* out_hi, int cap) {
+  Intervals I;
+  for (size_t i = 0; i < n; ++i) I.unionInterval(interval_t(lo[i], hi[i]));
+  int k = 0;
+  for (auto& s : I.list()) { if (k < cap) { out_lo[k] = s.first; out_hi[k] = s.second; } ++k; }
+  return k;
+}
+
+// ---- nearest neighbour -----------------------------------------------------------
+void oracle_knn_append(OracleHandle* h, const double* q, const int32_t* cc, size_t n) {
+  for (size_t i = 0; i < n; ++i) h->roadmap->addNode(q + i * h->dev->nq, cc ? cc[i] : 0);
+}
+void oracle_knn_relabel(OracleHandle* h, int from, int to) {
+  for (auto& c : h->roadmap->cc) if (c == from) c = to;
+}
+void oracle_knn_query(OracleHandle* h, const double* queries, size_t nqueries, int k, int cc, int64_t* idx, double* dist, int nthreads) {
+  const Roadmap& rm = *h->roadmap;
+  if (nthreads <= 0) nthreads = omp_get_max_threads();
+#pragma omp parallel for schedule(dynamic, 1) num_threads(nthreads)
+  for (long i = 0; i < (long)nqueries; ++i) {
+    double dk;
+    const double* q = queries + (size_t)i * h->dev->nq;
+    if (k == 1) {
+      double d;
+      long r = nnSearch(rm, q, cc, d);
+      idx[i] = r; dist[i] = d;
+    } else {
+      auto res = nnKnearest(rm, q, cc, (size_t)k, dk);
+      for (int j = 0; j < k; ++j) {
+        idx[(size_t)i * k + j] = j < (int)res.size() ? res[j].second : -1;
+        dist[(size_t)i * k + j] = j < (int)res.size() ? res[j].first : kInf;
+      }
+    }
+  }
+}
+int64_t oracle_knn_within_ball(OracleHandle* h, const double* q, double radius, int cc, int64_t* idx, size_t cap) {
+  auto r = nnWithinBall(*h->roadmap, q, cc, radius);
+  for (size_t i = 0; i < r.size() && i < cap; ++i) idx[i] = r[i];
+  return (int64_t)r.size();
+}
+
+}  // extern "C"
