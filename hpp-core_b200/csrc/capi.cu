@@ -1,0 +1,323 @@
+// C ABI of the engine (include/hppb200.h).  Status codes only; exceptions are caught here
+// and turned into HPPB200_ERR_* + a thread-local message, mirroring the exception types
+// the reference throws (std::invalid_argument / std::runtime_error).
+// There is no CPU fallback: compute entry points require a CUDA device.
+#include <cmath>
+#include <cstring>
+
+#include "engine.hpp"
+
+struct hppb200_model {
+  hppb200::Model impl;
+  explicit hppb200_model(const hppb200_model_desc& d) : impl(d) {}
+};
+struct hppb200_workspace {
+  hppb200::Workspace impl;
+  hppb200_workspace(const hppb200::Model* m, int dev) : impl(m, dev) {}
+};
+
+namespace hppb200 {
+
+static thread_local std::string g_last_error;
+void setLastError(const std::string& s) { g_last_error = s; }
+
+Workspace::Workspace(const Model* m, int dev) : model(m), device(dev) {
+  int count = 0;
+  if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0)
+    throw std::runtime_error("no CUDA device visible: the engine has no CPU fallback");
+  if (dev < 0 || dev >= count) throw std::invalid_argument("device index out of range");
+  HPPB200_CUDA_CHECK(cudaSetDevice(dev));
+  cudaDeviceProp prop;
+  HPPB200_CUDA_CHECK(cudaGetDeviceProperties(&prop, dev));
+  num_sms = prop.multiProcessorCount;
+  HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+  HPPB200_CUDA_CHECK(cudaEventCreate(&ev0));
+  HPPB200_CUDA_CHECK(cudaEventCreate(&ev1));
+  HPPB200_CUDA_CHECK(cudaMalloc((void**)&d_stats, sizeof(DeviceStats)));
+  HPPB200_CUDA_CHECK(cudaMemset(d_stats, 0, sizeof(DeviceStats)));
+  view = m->deviceView(dev);
+}
+
+Workspace::~Workspace() {
+  cudaSetDevice(device);
+  if (own_stream && stream) cudaStreamDestroy(stream);
+  if (ev0) cudaEventDestroy(ev0);
+  if (ev1) cudaEventDestroy(ev1);
+  if (d_stats) cudaFree(d_stats);
+}
+
+void Workspace::syncStats() {
+  DeviceStats h;
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h, d_stats, sizeof(h), cudaMemcpyDeviceToHost, stream));
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(stream));
+  stats.pair_tests = h.pair_tests;
+  stats.gjk_iterations = h.gjk_iterations;
+  stats.edge_samples = h.edge_samples;
+  stats.iter_cap_hits = h.iter_cap_hits;
+}
+
+template <typename F>
+static int guarded(F&& f) {
+  try {
+    f();
+    return HPPB200_OK;
+  } catch (const std::invalid_argument& e) {
+    setLastError(e.what());
+    return HPPB200_ERR_INVALID_ARGUMENT;
+  } catch (const std::runtime_error& e) {
+    setLastError(e.what());
+    return std::strncmp(e.what(), "CUDA", 4) == 0 || std::strncmp(e.what(), "no CUDA", 7) == 0 ? HPPB200_ERR_CUDA
+                                                                                            : HPPB200_ERR_RUNTIME;
+  } catch (const std::exception& e) {
+    setLastError(e.what());
+    return HPPB200_ERR_RUNTIME;
+  }
+}
+
+struct Timed {
+  Workspace* ws;
+  explicit Timed(Workspace* w) : ws(w) { cudaEventRecord(ws->ev0, ws->stream); }
+  void stop() {
+    cudaEventRecord(ws->ev1, ws->stream);
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, ws->ev0, ws->ev1);
+    ws->stats.last_kernel_ms = ms;
+  }
+};
+
+}  // namespace hppb200
+
+using namespace hppb200;
+
+extern "C" {
+
+int hppb200_abi_version(void) { return HPPB200_ABI_VERSION; }
+const char* hppb200_last_error(void) { return g_last_error.c_str(); }
+int hppb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+  return n;
+}
+
+int hppb200_model_create(const hppb200_model_desc* desc, hppb200_model** out) {
+  return guarded([&] {
+    if (!desc || !out) throw std::invalid_argument("null argument");
+    *out = new hppb200_model(*desc);
+  });
+}
+void hppb200_model_destroy(hppb200_model* m) { delete m; }
+int hppb200_model_nq(const hppb200_model* m) { return m->impl.nq; }
+int hppb200_model_nv(const hppb200_model* m) { return m->impl.nv; }
+int hppb200_model_num_config_pairs(const hppb200_model* m) { return (int)m->impl.cPairs.size(); }
+int hppb200_model_get_config_pairs(const hppb200_model* m, int32_t* a, int32_t* b, double* margin) {
+  for (size_t i = 0; i < m->impl.cPairs.size(); ++i) {
+    if (a) a[i] = m->impl.cPairs[i].a;
+    if (b) b[i] = m->impl.cPairs[i].b;
+    if (margin) margin[i] = m->impl.cPairs[i].margin;
+  }
+  return HPPB200_OK;
+}
+int hppb200_model_num_body_pairs(const hppb200_model* m) { return (int)m->impl.bodyPairs.size(); }
+int hppb200_model_get_body_pairs(const hppb200_model* m, int32_t* ja, int32_t* jb, int32_t* pair_begin,
+                                 int32_t* coef_begin, int32_t* rcoef_begin) {
+  int pb = 0, cb = 0, rb = 0;
+  size_t i = 0;
+  for (const BodyPairHost& b : m->impl.bodyPairs) {
+    if (ja) ja[i] = b.joint_a;
+    if (jb) jb[i] = b.joint_b;
+    if (pair_begin) pair_begin[i] = pb;
+    if (coef_begin) coef_begin[i] = cb;
+    if (rcoef_begin) rcoef_begin[i] = rb;
+    pb += (int)b.pairs.size();
+    cb += (int)b.coefs.size();
+    rb += (int)b.rcoefs.size();
+    ++i;
+  }
+  if (pair_begin) pair_begin[i] = pb;
+  if (coef_begin) coef_begin[i] = cb;
+  if (rcoef_begin) rcoef_begin[i] = rb;
+  return HPPB200_OK;
+}
+int hppb200_model_num_body_geom_pairs(const hppb200_model* m) {
+  size_t n = 0;
+  for (const BodyPairHost& b : m->impl.bodyPairs) n += b.pairs.size();
+  return (int)n;
+}
+int hppb200_model_get_body_geom_pairs(const hppb200_model* m, int32_t* a, int32_t* b, double* margin) {
+  size_t k = 0;
+  for (const BodyPairHost& bp : m->impl.bodyPairs)
+    for (const DevPair& p : bp.pairs) {
+      if (a) a[k] = p.a;
+      if (b) b[k] = p.b;
+      if (margin) margin[k] = p.margin;
+      ++k;
+    }
+  return HPPB200_OK;
+}
+int hppb200_model_num_coefficients(const hppb200_model* m, int reverse) {
+  size_t n = 0;
+  for (const BodyPairHost& b : m->impl.bodyPairs) n += reverse ? b.rcoefs.size() : b.coefs.size();
+  return (int)n;
+}
+int hppb200_model_get_coefficients(const hppb200_model* m, int reverse, int32_t* joint, double* value) {
+  size_t k = 0;
+  for (const BodyPairHost& b : m->impl.bodyPairs)
+    for (auto& c : (reverse ? b.rcoefs : b.coefs)) {
+      if (joint) joint[k] = c.first;
+      if (value) value[k] = c.second;
+      ++k;
+    }
+  return HPPB200_OK;
+}
+int hppb200_model_get_body_radii(const hppb200_model* m, double* radius) {
+  for (size_t i = 0; i < m->impl.radii.size(); ++i) radius[i] = m->impl.radii[i];
+  return HPPB200_OK;
+}
+
+int hppb200_workspace_create(const hppb200_model* m, int device, hppb200_workspace** out) {
+  return guarded([&] {
+    if (!m || !out) throw std::invalid_argument("null argument");
+    *out = new hppb200_workspace(&m->impl, device);
+  });
+}
+void hppb200_workspace_destroy(hppb200_workspace* ws) { delete ws; }
+int hppb200_get_stats(const hppb200_workspace* ws, hppb200_stats* out) {
+  return guarded([&] {
+    const_cast<hppb200_workspace*>(ws)->impl.syncStats();
+    *out = ws->impl.stats;
+  });
+}
+int hppb200_workspace_set_stream(hppb200_workspace* ws, void* cuda_stream) {
+  return guarded([&] {
+    Workspace& w = ws->impl;
+    if (w.own_stream && w.stream) cudaStreamDestroy(w.stream);
+    w.stream = (cudaStream_t)cuda_stream;
+    w.own_stream = false;
+  });
+}
+int hppb200_workspace_set_max_iterations(hppb200_workspace* ws, uint32_t max_iter) {
+  ws->impl.max_iterations = max_iter ? max_iter : 1u;
+  return HPPB200_OK;
+}
+
+int hppb200_validate_configs(hppb200_workspace* wsp, const double* q, size_t n, uint32_t flags, uint8_t* valid,
+                             int32_t* first_pair, uint8_t* reason) {
+  return guarded([&] {
+    if (!wsp || (n && (!q || !valid))) throw std::invalid_argument("null argument");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq;
+    if (flags & HPPB200_DEVICE_POINTERS) {
+      Timed tm(ws);
+      launchValidateConfigs(ws, q, n, flags, valid, first_pair, reason);
+      tm.stop();
+      return;
+    }
+    ws->d_q.reserve(n * nq);
+    ws->d_valid.reserve(n);
+    ws->d_pair.reserve(n);
+    ws->d_reason.reserve(n);
+    Timed tm(ws);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchValidateConfigs(ws, ws->d_q.p, n, flags, ws->d_valid.p, ws->d_pair.p, ws->d_reason.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_valid.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    if (first_pair) HPPB200_CUDA_CHECK(cudaMemcpyAsync(first_pair, ws->d_pair.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    if (reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(reason, ws->d_reason.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    tm.stop();
+  });
+}
+
+int hppb200_geometry_placements(hppb200_workspace* wsp, const double* q, size_t n, uint32_t flags, double* oMg) {
+  return guarded([&] {
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq, per = (size_t)ws->model->geoms.size() * 12;
+    if (flags & HPPB200_DEVICE_POINTERS) { launchGeometryPlacements(ws, q, n, oMg); HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream)); return; }
+    ws->d_q.reserve(n * nq);
+    ws->d_scratch.reserve(n * per);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchGeometryPlacements(ws, ws->d_q.p, n, ws->d_scratch.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(oMg, ws->d_scratch.p, n * per * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  });
+}
+
+int hppb200_pair_distances(hppb200_workspace* wsp, const double* q, size_t n, uint32_t flags, double* dist) {
+  return guarded([&] {
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq, per = ws->model->cPairs.size();
+    if (flags & HPPB200_DEVICE_POINTERS) { launchPairDistances(ws, q, n, dist); HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream)); return; }
+    ws->d_q.reserve(n * nq);
+    ws->d_scratch.reserve(n * per);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchPairDistances(ws, ws->d_q.p, n, ws->d_scratch.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(dist, ws->d_scratch.p, n * per * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  });
+}
+
+int hppb200_straight_lengths(hppb200_workspace* wsp, const double* q1, const double* q2, size_t n, uint32_t flags,
+                             double* L) {
+  return guarded([&] {
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq;
+    if (flags & HPPB200_DEVICE_POINTERS) { launchStraightLengths(ws, q1, q2, n, L); HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream)); return; }
+    ws->d_q.reserve(n * nq);
+    ws->d_q2.reserve(n * nq);
+    ws->d_L.reserve(n);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q1, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q2.p, q2, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchStraightLengths(ws, ws->d_q.p, ws->d_q2.p, n, ws->d_L.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(L, ws->d_L.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  });
+}
+
+int hppb200_validate_edges(hppb200_workspace* wsp, int method, double param, int reverse, const double* q1,
+                           const double* q2, const double* L, size_t n, uint32_t flags, uint8_t* valid, double* t_fail,
+                           double* t_last_valid, int32_t* pair, uint8_t* reason) {
+  return guarded([&] {
+    if (!wsp || (n && (!q1 || !q2 || !L || !valid))) throw std::invalid_argument("null argument");
+    // constructor checks of the reference validators
+    if (method == HPPB200_METHOD_PROGRESSIVE && !(param > 0))
+      throw std::runtime_error("tolerance should be positive for progressive continuous validation.");  // progressive.cc:138-145
+    if (method == HPPB200_METHOD_DICHOTOMY && param != 0)
+      throw std::runtime_error("Dichotomy path validation method does not support penetration.");  // dichotomy.cc:139-148
+    if (method == HPPB200_METHOD_DISCRETIZED && !(param > 0)) throw std::invalid_argument("step size must be positive");
+    if (method < HPPB200_METHOD_DISCRETIZED || method > HPPB200_METHOD_DICHOTOMY) throw std::invalid_argument("unknown method");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq;
+    if (flags & HPPB200_DEVICE_POINTERS) {
+      Timed tm(ws);
+      launchValidateEdges(ws, method, param, reverse, q1, q2, L, n, flags, valid, t_fail, t_last_valid, pair, reason);
+      tm.stop();
+      return;
+    }
+    ws->d_q.reserve(n * nq);
+    ws->d_q2.reserve(n * nq);
+    ws->d_L.reserve(n);
+    ws->d_valid.reserve(n);
+    ws->d_reason.reserve(n);
+    ws->d_pair.reserve(n);
+    ws->d_tfail.reserve(n);
+    ws->d_tlast.reserve(n);
+    Timed tm(ws);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q1, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q2.p, q2, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_L.p, L, n * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchValidateEdges(ws, method, param, reverse, ws->d_q.p, ws->d_q2.p, ws->d_L.p, n, flags, ws->d_valid.p,
+                        ws->d_tfail.p, ws->d_tlast.p, ws->d_pair.p, ws->d_reason.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_valid.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    if (t_fail) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_fail, ws->d_tfail.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    if (t_last_valid) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_last_valid, ws->d_tlast.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    if (pair) HPPB200_CUDA_CHECK(cudaMemcpyAsync(pair, ws->d_pair.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    if (reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(reason, ws->d_reason.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    tm.stop();
+  });
+}
+
+}  // extern "C"

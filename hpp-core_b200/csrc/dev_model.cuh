@@ -1,0 +1,93 @@
+// Device view of the compiled model blob + TMA staging into shared memory.
+// Table layouts are defined in engine.hpp (host) and mirrored here.
+#pragma once
+#include "dev_narrow.cuh"
+#include "engine.hpp"
+
+namespace hppb200 {
+
+static_assert(sizeof(DevShape) == sizeof(DevShapeH), "shape record mismatch");
+
+// Typed pointers into a staged (shared-memory) or global copy of the blob.
+struct Tables {
+  const DevJoint* joints;
+  const DevGeom* geoms;
+  const DevObstacle* obstacles;
+  const DevPair* cpairs;
+  const DevBodyPair* bodypairs;
+  const DevPair* bgpairs;
+  const DevCoef* coefs;
+  const DevCoef* rcoefs;
+  const double* lower;
+  const double* upper;
+  const double* weights;
+};
+
+__device__ __forceinline__ Tables makeTables(const unsigned char* base, const ModelView& mv) {
+  Tables t;
+  t.joints = (const DevJoint*)(base + mv.off_joints);
+  t.geoms = (const DevGeom*)(base + mv.off_geoms);
+  t.obstacles = (const DevObstacle*)(base + mv.off_obstacles);
+  t.cpairs = (const DevPair*)(base + mv.off_cpairs);
+  t.bodypairs = (const DevBodyPair*)(base + mv.off_bodypairs);
+  t.bgpairs = (const DevPair*)(base + mv.off_bgpairs);
+  t.coefs = (const DevCoef*)(base + mv.off_coefs);
+  t.rcoefs = (const DevCoef*)(base + mv.off_rcoefs);
+  t.lower = (const double*)(base + mv.off_lower);
+  t.upper = (const double*)(base + mv.off_upper);
+  t.weights = (const double*)(base + mv.off_weights);
+  return t;
+}
+
+// Stage `bytes` (multiple of 16, both pointers 16-byte aligned) from global to shared memory
+// with one TMA bulk copy (cp.async.bulk, SASS UBLKCP) completed through an mbarrier.
+// Must be called by every thread of the CTA; returns when the data is visible to all.
+__device__ __forceinline__ void stageBlobTMA(unsigned char* sdst, const unsigned char* gsrc, uint32_t bytes,
+                                             uint64_t* bar) {
+  const uint32_t bar_s = (uint32_t)__cvta_generic_to_shared(bar);
+  const uint32_t dst_s = (uint32_t)__cvta_generic_to_shared(sdst);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(bytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s),
+        "l"(gsrc), "r"(bytes), "r"(bar_s)
+        : "memory");
+  }
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar_s), "r"(0u)
+        : "memory");
+  }
+}
+
+// pinocchio joint transform composed with the joint placement: liMi = P * M_joint(q)
+__device__ __forceinline__ T3 jointLocal(const DevJoint& J, const double* __restrict__ q) {
+  T3 P = load12(J.P);
+  T3 M = identityT();
+  if (J.type <= HPPB200_JOINT_REVOLUTE_Z) {
+    double s, c;
+    sincos_portable(q[J.idx_q], &s, &c);
+    // static indices only (keeps M in registers)
+    if (J.type == HPPB200_JOINT_REVOLUTE_X) { M.r[4] = c; M.r[5] = -s; M.r[7] = s; M.r[8] = c; }
+    else if (J.type == HPPB200_JOINT_REVOLUTE_Y) { M.r[8] = c; M.r[6] = -s; M.r[2] = s; M.r[0] = c; }
+    else { M.r[0] = c; M.r[1] = -s; M.r[3] = s; M.r[4] = c; }
+  } else {
+    const int a = J.type - HPPB200_JOINT_PRISMATIC_X;
+    double v = q[J.idx_q];
+    M.t = mk(a == 0 ? v : 0.0, a == 1 ? v : 0.0, a == 2 ? v : 0.0);
+  }
+  return compose(P, M);
+}
+
+}  // namespace hppb200

@@ -1,0 +1,238 @@
+// Device narrow phase: closed forms for sphere/capsule/box pairs and GJK on the core
+// shapes for everything else.  Replaces coal::ComputeCollision as called through
+// hpp::core::CollisionPair::collide (reference include/hpp/core/collision-pair.hh:67-80,
+// src/obstacle-user.cc:42-51, src/continuous-validation/body-pair-collision.cc:175-198).
+//
+// Semantics: d = separation of the two convex shapes (cores
+// overlapping => 0 - radii), distance_lower_bound = d - security_margin,
+// collision <=> d - security_margin <= 1e-12.  EPA is not needed: hpp-core's validators never
+// read a penetration depth.
+#pragma once
+#include "dev_math.cuh"
+
+namespace hppb200 {
+
+enum { SH_SPHERE = 0, SH_CAPSULE = 1, SH_BOX = 2, SH_CONVEX = 3 };
+// pair kinds after canonical ordering (shape type of first <= type of second)
+enum { PK_SPHERE_SPHERE = 0, PK_SPHERE_CAPSULE = 1, PK_CAPSULE_CAPSULE = 2, PK_SPHERE_BOX = 3, PK_GJK = 4 };
+
+#define HPPB200_COLLISION_THRESHOLD 1e-12
+#define HPPB200_GJK_EPS_REL 1e-10
+#define HPPB200_GJK_EPS_ABS2 1e-28
+#define HPPB200_GJK_MAX_ITER 64
+
+// 48-byte shape record (lives in the model blob, staged in shared memory)
+struct DevShape {
+  double p[4];      // sphere: r | capsule: r, halfLength | box: hx hy hz
+  int32_t type;
+  int32_t vbegin;   // convex: first vertex in the pool
+  int32_t vcount;
+  int32_t pad;
+};
+
+__device__ __forceinline__ double inflation(const DevShape& s) { return s.type <= SH_CAPSULE ? s.p[0] : 0.0; }
+
+// support of the core shape, local frame; ties -> positive side / first maximal vertex
+__device__ __forceinline__ V3 supportLocal(const DevShape& s, const double* __restrict__ verts, V3 d) {
+  switch (s.type) {
+    case SH_SPHERE: return mk(0, 0, 0);
+    case SH_CAPSULE: return mk(0, 0, d.z >= 0 ? s.p[1] : -s.p[1]);
+    case SH_BOX: return mk(d.x >= 0 ? s.p[0] : -s.p[0], d.y >= 0 ? s.p[1] : -s.p[1], d.z >= 0 ? s.p[2] : -s.p[2]);
+    default: {
+      int best = 0;
+      double bv = -CUDART_INF;
+      const double* vp = verts + 3 * (size_t)s.vbegin;
+      for (int i = 0; i < s.vcount; ++i) {
+        double h = dot(mk(vp[3 * i], vp[3 * i + 1], vp[3 * i + 2]), d);
+        if (h > bv) { bv = h; best = i; }
+      }
+      return mk(vp[3 * best], vp[3 * best + 1], vp[3 * best + 2]);
+    }
+  }
+}
+
+// ---- simplex sub-algorithms (closest point to the origin) -------------------------
+// Ericson, Real-Time Collision Detection §5.1.5: Voronoi-region tests with p = origin.
+// Outputs the supporting sub-simplex (o0..o2, n) and the closest point v.
+__device__ __forceinline__ void closestTriangle(V3 A, V3 B, V3 C, V3& o0, V3& o1, V3& o2, int& n, V3& v) {
+  V3 ab = B - A, ac = C - A;
+  double d1 = -dot(ab, A), d2 = -dot(ac, A);
+  if (d1 <= 0 && d2 <= 0) { o0 = A; n = 1; v = A; return; }
+  double d3 = -dot(ab, B), d4 = -dot(ac, B);
+  if (d3 >= 0 && d4 <= d3) { o0 = B; n = 1; v = B; return; }
+  double vc = fma(d1, d4, -(d3 * d2));
+  if (vc <= 0 && d1 >= 0 && d3 <= 0) {
+    double r = d1 / (d1 - d3);
+    o0 = A; o1 = B; n = 2; v = axpy(r, ab, A); return;
+  }
+  double d5 = -dot(ab, C), d6 = -dot(ac, C);
+  if (d6 >= 0 && d5 <= d6) { o0 = C; n = 1; v = C; return; }
+  double vb = fma(d5, d2, -(d1 * d6));
+  if (vb <= 0 && d2 >= 0 && d6 <= 0) {
+    double r = d2 / (d2 - d6);
+    o0 = A; o1 = C; n = 2; v = axpy(r, ac, A); return;
+  }
+  double va = fma(d3, d6, -(d5 * d4));
+  double e1 = d4 - d3, e2 = d5 - d6;
+  if (va <= 0 && e1 >= 0 && e2 >= 0) {
+    double r = e1 / (e1 + e2);
+    o0 = B; o1 = C; n = 2; v = axpy(r, C - B, B); return;
+  }
+  V3 nn = cross(ab, ac);
+  double k = dot(A, nn) / dot(nn, nn);
+  o0 = A; o1 = B; o2 = C; n = 3;
+  v = k * nn;
+}
+
+struct GjkCounters {
+  unsigned calls, iterations, cap_hits;
+};
+
+// Distance between core shapes; `rel` = placement of B in A's frame.  0 when cores intersect.
+__device__ __noinline__ double gjkCoreDistance(const DevShape& A, const DevShape& B, const T3& rel,
+                                               const double* __restrict__ verts, GjkCounters& cnt) {
+  V3 w0 = mk(0, 0, 0), w1 = w0, w2 = w0, w3 = w0;
+  int n = 0;
+  V3 v = -rel.t;
+  double vv = dot(v, v);
+  if (vv == 0) { v = mk(1, 0, 0); vv = 1; }
+  int it = 0;
+  double result = -1.0;
+  for (; it < HPPB200_GJK_MAX_ITER; ++it) {
+    V3 sa = supportLocal(A, verts, -v);
+    V3 sbl = supportLocal(B, verts, rtmul(rel, v));
+    V3 sb = rmul(rel, sbl) + rel.t;
+    V3 w = sa - sb;
+    double vw = dot(v, w);
+    if (n > 0 && (vv - vw) <= HPPB200_GJK_EPS_REL * vv) break;
+    bool dup = false;
+    if (n > 0 && w0.x == w.x && w0.y == w.y && w0.z == w.z) dup = true;
+    if (n > 1 && w1.x == w.x && w1.y == w.y && w1.z == w.z) dup = true;
+    if (n > 2 && w2.x == w.x && w2.y == w.y && w2.z == w.z) dup = true;
+    if (dup) break;
+    // tentative simplex T = S + {w}
+    V3 t0 = w0, t1 = w1, t2 = w2;
+    int tn;
+    V3 nv;
+    bool inside = false;
+    if (n == 0) { t0 = w; tn = 1; nv = w; }
+    else if (n == 1) {
+      // segment A = w0 (old), B = w (new)
+      V3 d = w - w0;
+      double dd = dot(d, d);
+      double s = -dot(w0, d);
+      if (dd == 0 || s >= dd) { t0 = w; tn = 1; nv = w; }
+      else if (s <= 0) { tn = 1; nv = w0; }
+      else { double r = s / dd; t1 = w; tn = 2; nv = axpy(r, d, w0); }
+    } else if (n == 2) {
+      closestTriangle(w0, w1, w, t0, t1, t2, tn, nv);
+    } else {
+      // tetrahedron (w0,w1,w2,w): Ericson §5.1.6, all four faces
+      double best = CUDART_INF;
+      bool any = false;
+      tn = 0; nv = v;
+#pragma unroll
+      for (int f = 0; f < 4; ++f) {
+        V3 a, b, c, d;
+        if (f == 0) { a = w0; b = w1; c = w2; d = w; }
+        else if (f == 1) { a = w0; b = w1; c = w; d = w2; }
+        else if (f == 2) { a = w0; b = w2; c = w; d = w1; }
+        else { a = w1; b = w2; c = w; d = w0; }
+        V3 nn = cross(b - a, c - a);
+        double sp = -dot(a, nn);
+        double sd = dot(d - a, nn);
+        if (sd == 0 || sp * sd < 0) {
+          V3 q0, q1, q2, qv;
+          q0 = q1 = q2 = a;
+          int qn;
+          closestTriangle(a, b, c, q0, q1, q2, qn, qv);
+          double qq = dot(qv, qv);
+          if (qq < best) { best = qq; t0 = q0; t1 = q1; t2 = q2; tn = qn; nv = qv; }
+          any = true;
+        }
+      }
+      inside = !any;
+    }
+    if (inside) { result = 0.0; break; }
+    double nvv = dot(nv, nv);
+    if (nvv <= HPPB200_GJK_EPS_ABS2) { result = 0.0; break; }
+    if (n > 0 && nvv >= vv) break;  // no progress: keep previous closest point
+    w0 = t0; w1 = t1; w2 = t2; n = tn; v = nv; vv = nvv;
+  }
+  cnt.calls += 1;
+  cnt.iterations += it + 1;
+  if (it == HPPB200_GJK_MAX_ITER) cnt.cap_hits += 1;
+  if (result == 0.0) return 0.0;
+  return sqrt(vv);
+}
+
+__device__ __forceinline__ double clamp01(double x) { return x < 0 ? 0 : (x > 1 ? 1 : x); }
+
+__device__ __forceinline__ double pointSegmentDist2(V3 c, V3 p, V3 u, double h) {
+  V3 d = c - p;
+  double s = dot(d, u);
+  s = s < -h ? -h : (s > h ? h : s);
+  V3 e = axpy(-s, u, d);
+  return dot(e, e);
+}
+
+// Ericson §5.1.9
+__device__ __forceinline__ double segmentSegmentDist2(V3 p1, V3 q1, V3 p2, V3 q2) {
+  const double EPS = 1e-300;
+  V3 d1 = q1 - p1, d2 = q2 - p2, r = p1 - p2;
+  double a = dot(d1, d1), e = dot(d2, d2), f = dot(d2, r);
+  double s, t;
+  if (a <= EPS && e <= EPS) return dot(r, r);
+  if (a <= EPS) { s = 0; t = clamp01(f / e); }
+  else {
+    double c = dot(d1, r);
+    if (e <= EPS) { t = 0; s = clamp01(-c / a); }
+    else {
+      double b = dot(d1, d2);
+      double denom = fma(a, e, -(b * b));
+      if (denom > 0) s = clamp01(fma(b, f, -(c * e)) / denom); else s = 0;
+      double tnom = fma(b, s, f);
+      if (tnom < 0) { t = 0; s = clamp01(-c / a); }
+      else if (tnom > e) { t = 1; s = clamp01((b - c) / a); }
+      else t = tnom / e;
+    }
+  }
+  V3 c1 = axpy(s, d1, p1), c2 = axpy(t, d2, p2);
+  V3 dd = c1 - c2;
+  return dot(dd, dd);
+}
+
+// Signed distance (no margin) of a canonically ordered pair.
+__device__ __forceinline__ double shapeDistance(int kind, const DevShape& A, const T3& TA, const DevShape& B,
+                                                const T3& TB, const double* __restrict__ verts, GjkCounters& cnt) {
+  switch (kind) {
+    case PK_SPHERE_SPHERE: {
+      V3 d = TA.t - TB.t;
+      return sqrt(dot(d, d)) - A.p[0] - B.p[0];
+    }
+    case PK_SPHERE_CAPSULE:
+      return sqrt(pointSegmentDist2(TA.t, TB.t, rcol(TB, 2), B.p[1])) - A.p[0] - B.p[0];
+    case PK_CAPSULE_CAPSULE: {
+      V3 ua = rcol(TA, 2), ub = rcol(TB, 2);
+      V3 p1 = axpy(-A.p[1], ua, TA.t), q1 = axpy(A.p[1], ua, TA.t);
+      V3 p2 = axpy(-B.p[1], ub, TB.t), q2 = axpy(B.p[1], ub, TB.t);
+      return sqrt(segmentSegmentDist2(p1, q1, p2, q2)) - A.p[0] - B.p[0];
+    }
+    case PK_SPHERE_BOX: {
+      V3 c = rtmul(TB, TA.t - TB.t);
+      double ex = fabs(c.x) - B.p[0], ey = fabs(c.y) - B.p[1], ez = fabs(c.z) - B.p[2];
+      double ox = ex > 0 ? ex : 0, oy = ey > 0 ? ey : 0, oz = ez > 0 ? ez : 0;
+      double out2 = fma(oz, oz, fma(oy, oy, ox * ox));
+      if (out2 > 0) return sqrt(out2) - A.p[0];
+      double m = ex > ey ? ex : ey;
+      m = m > ez ? m : ez;
+      return m - A.p[0];
+    }
+    default: {
+      T3 rel = composeInv(TA, TB);
+      return gjkCoreDistance(A, B, rel, verts, cnt) - inflation(A) - inflation(B);
+    }
+  }
+}
+
+}  // namespace hppb200

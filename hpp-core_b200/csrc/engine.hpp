@@ -1,0 +1,156 @@
+// Host side of the engine: the model compiler (flattened robot/scene tables in the
+// reference's pair ORDER), the device blob layout shared with the kernels, and the
+// workspace (one CUDA stream + scratch).  See DESIGN.md §2-§3.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <map>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/hppb200.h"
+
+namespace hppb200 {
+
+// ---- records inside the device blob (all 8-byte aligned, blob 16-byte padded) ----------
+struct DevShapeH {  // mirrors DevShape in dev_narrow.cuh
+  double p[4];
+  int32_t type, vbegin, vcount, pad;
+};
+struct DevJoint {
+  int32_t parent, type, idx_q, idx_v;
+  double P[12];
+};
+struct DevGeom {
+  int32_t joint, pad;
+  double P[12];
+  DevShapeH shape;
+};
+struct DevObstacle {
+  double P[12];
+  DevShapeH shape;
+};
+// a/b: >= 0 robot geometry index, < 0 obstacle -(k+1); already canonically ordered
+// (shape type of a <= shape type of b) so that the kernel can dispatch on `kind` directly.
+struct DevPair {
+  int32_t a, b, kind, pad;
+  double margin;
+};
+struct DevBodyPair {
+  int32_t joint_a, joint_b;
+  int32_t pair_begin, pair_end;    // into bodyGeomPairs
+  int32_t coef_begin, coef_end;    // a -> b
+  int32_t rcoef_begin, rcoef_end;  // b -> a (empty when joint_b == 0)
+};
+struct DevCoef {
+  int32_t idx_v, nv;
+  double value;
+};
+
+// Offsets (bytes) of each table in the blob + counts; passed to kernels by value.
+struct ModelView {
+  const unsigned char* blob;  // global memory
+  const double* vertices;     // global memory convex vertex pool (not staged)
+  uint32_t blob_bytes;
+  uint32_t off_joints, off_geoms, off_obstacles, off_cpairs, off_bodypairs, off_bgpairs, off_coefs, off_rcoefs,
+      off_lower, off_upper, off_weights;
+  int32_t njoints, ngeoms, nobstacles, ncpairs, nbodypairs, nbgpairs, ncoefs, nrcoefs, nq, nv;
+};
+
+struct BodyPairHost {
+  int joint_a, joint_b;
+  std::vector<DevPair> pairs;      // reference order (first = robot geometry)
+  std::vector<std::pair<int, double>> coefs, rcoefs;  // (child joint, value)
+};
+
+struct Model {
+  explicit Model(const hppb200_model_desc& d);
+  ~Model();
+  int njoints = 0, nq = 0, nv = 0;
+  std::vector<DevJoint> joints;       // index 0 = joint 1
+  std::vector<int> joint_nq, joint_nv;
+  std::vector<DevGeom> geoms;
+  std::vector<DevObstacle> obstacles;
+  std::vector<double> lower, upper, weights, margins, vertices, radii;
+  double break_distance = 1e-2;
+  // reference-order tables (for the query API and reports)
+  std::vector<DevPair> cPairs;        // first/second as in cPairs_ (NOT canonicalised)
+  std::vector<BodyPairHost> bodyPairs;
+  // device
+  std::vector<unsigned char> blob;
+  ModelView view{};                   // blob/vertices pointers are filled per device
+  ModelView deviceView(int device) const;  // uploads on first use
+
+ private:
+  void buildConfigPairs(const hppb200_model_desc& d);
+  void buildBodyPairs(const hppb200_model_desc& d);
+  void buildBlob();
+  double margin(int j1, int j2) const { return margins.empty() ? 0.0 : margins[(size_t)j1 * (njoints + 1) + j2]; }
+  mutable std::mutex mu_;
+  mutable std::map<int, std::pair<void*, void*>> dev_;  // device -> (blob, vertices)
+};
+
+struct DeviceStats {  // accumulated by kernels with atomics
+  unsigned long long configs, pair_tests, gjk_iterations, edge_samples, iter_cap_hits, gjk_cap_hits, overflow;
+};
+
+template <typename T>
+struct DeviceBuffer {
+  T* p = nullptr;
+  size_t cap = 0;
+  void reserve(size_t n) {
+    if (n <= cap) return;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = n + n / 8 + 64;
+    if (cudaMalloc((void**)&p, want * sizeof(T)) != cudaSuccess) throw std::runtime_error("cudaMalloc failed");
+    cap = want;
+  }
+  ~DeviceBuffer() { if (p) cudaFree(p); }
+};
+
+struct Workspace {
+  Workspace(const Model* m, int device);
+  ~Workspace();
+  const Model* model;
+  int device;
+  int num_sms = 148;
+  cudaStream_t stream = nullptr;
+  bool own_stream = true;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  ModelView view;
+  DeviceStats* d_stats = nullptr;
+  hppb200_stats stats{};
+  uint32_t max_iterations = 1u << 20;
+  // staging for host-pointer calls
+  DeviceBuffer<double> d_q, d_q2, d_L, d_tfail, d_tlast, d_scratch;
+  DeviceBuffer<uint8_t> d_valid, d_reason;
+  DeviceBuffer<int32_t> d_pair;
+  DeviceBuffer<unsigned char> d_state;
+  void syncStats();
+};
+
+void setLastError(const std::string& s);
+
+// kernel launchers (kernels_config.cu / kernels_edges.cu), all asynchronous on ws->stream
+void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
+                           int32_t* d_first, uint8_t* d_reason);
+void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg);
+void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_dist);
+void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2, size_t n, double* d_L);
+void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1,
+                         const double* d_q2, const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid,
+                         double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason);
+
+#define HPPB200_CUDA_CHECK(expr)                                                                      \
+  do {                                                                                                \
+    cudaError_t _e = (expr);                                                                          \
+    if (_e != cudaSuccess)                                                                            \
+      throw std::runtime_error(std::string("CUDA error: ") + cudaGetErrorString(_e) + " at " #expr); \
+  } while (0)
+
+}  // namespace hppb200

@@ -1,0 +1,300 @@
+// Model compiler: flattens a robot + obstacle description into the device tables, in the
+// exact pair ORDER hpp-core would use.  Host-side restatement of
+//   ObstacleUser::addRobotCollisionPairs / addObstacle / setSecurityMargins
+//       (reference src/obstacle-user.cc:222-235, :53-76, :166-196)
+//   ContinuousValidation::Initialize::doExecute / AddObstacle::doExecute
+//       (reference src/continuous-validation.cc:63-98, :103-118)
+//   SolidSolidCollision::Model::{computeSequenceOfJoints,computeCoefficients,setCoefficients}
+//       (reference src/continuous-validation/solid-solid-collision.cc:162-244)
+//   hpp-pinocchio Body::radius / Joint::{maximalDistanceToParent,upperBound*Velocity}
+//       
+// Setup-time integer/FP64 work; runs once per model on the host.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "engine.hpp"
+
+namespace hppb200 {
+
+static int pairKind(int ta, int tb) {  // ta <= tb
+  if (ta == HPPB200_SHAPE_SPHERE && tb == HPPB200_SHAPE_SPHERE) return 0;
+  if (ta == HPPB200_SHAPE_SPHERE && tb == HPPB200_SHAPE_CAPSULE) return 1;
+  if (ta == HPPB200_SHAPE_CAPSULE && tb == HPPB200_SHAPE_CAPSULE) return 2;
+  if (ta == HPPB200_SHAPE_SPHERE && tb == HPPB200_SHAPE_BOX) return 3;
+  return 4;
+}
+
+static DevShapeH makeShape(int type, const double* p, int vb, int vc) {
+  DevShapeH s{};
+  if (type < HPPB200_SHAPE_SPHERE || type > HPPB200_SHAPE_CONVEX) throw std::invalid_argument("unknown shape type");
+  s.type = type;
+  for (int k = 0; k < 4; ++k) s.p[k] = p[k];
+  s.vbegin = type == HPPB200_SHAPE_CONVEX ? vb : 0;
+  s.vcount = type == HPPB200_SHAPE_CONVEX ? vc : 0;
+  return s;
+}
+
+static double norm3(double x, double y, double z) { return std::sqrt(std::fma(z, z, std::fma(y, y, x * x))); }
+// |R p + t| with the engine's dot convention
+static double actNorm(const double* P, double x, double y, double z) {
+  double w[3];
+  for (int i = 0; i < 3; ++i) w[i] = std::fma(P[3 * i + 2], z, std::fma(P[3 * i + 1], y, P[3 * i] * x)) + P[9 + i];
+  return norm3(w[0], w[1], w[2]);
+}
+
+Model::Model(const hppb200_model_desc& d) {
+  if (d.njoints <= 0 || !d.joint_parent || !d.joint_type || !d.joint_placement || !d.q_lower || !d.q_upper)
+    throw std::invalid_argument("model description: missing joint arrays");
+  njoints = d.njoints;
+  joints.resize(njoints);
+  joint_nq.resize(njoints);
+  joint_nv.resize(njoints);
+  for (int k = 0; k < njoints; ++k) {
+    DevJoint& J = joints[k];
+    J.parent = d.joint_parent[k];
+    if (J.parent < 0 || J.parent > k) throw std::invalid_argument("joint parent must precede its child");
+    J.type = d.joint_type[k];
+    if (J.type < HPPB200_JOINT_REVOLUTE_X || J.type > HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("unknown joint type");
+    if (J.type == HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("free-flyer joints are not supported yet (HPPB200_ERR_UNSUPPORTED)");
+    std::memcpy(J.P, d.joint_placement + 12 * k, sizeof(J.P));
+    joint_nq[k] = J.type == HPPB200_JOINT_FREEFLYER ? 7 : 1;
+    joint_nv[k] = J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1;
+    J.idx_q = nq;
+    J.idx_v = nv;
+    nq += joint_nq[k];
+    nv += joint_nv[k];
+  }
+  lower.assign(d.q_lower, d.q_lower + nq);
+  upper.assign(d.q_upper, d.q_upper + nq);
+  if (d.nvertices > 0 && d.vertices) vertices.assign(d.vertices, d.vertices + 3 * (size_t)d.nvertices);
+  for (int g = 0; g < d.ngeoms; ++g) {
+    DevGeom G{};
+    G.joint = d.geom_joint[g];
+    if (G.joint < 0 || G.joint > njoints) throw std::invalid_argument("geometry parent joint out of range");
+    std::memcpy(G.P, d.geom_placement + 12 * g, sizeof(G.P));
+    G.shape = makeShape(d.geom_shape[g], d.geom_params + 4 * g, d.geom_vert_begin ? d.geom_vert_begin[g] : 0,
+                        d.geom_vert_count ? d.geom_vert_count[g] : 0);
+    geoms.push_back(G);
+  }
+  for (int o = 0; o < d.nobstacles; ++o) {
+    DevObstacle O{};
+    std::memcpy(O.P, d.obst_placement + 12 * o, sizeof(O.P));
+    O.shape = makeShape(d.obst_shape[o], d.obst_params + 4 * o, d.obst_vert_begin ? d.obst_vert_begin[o] : 0,
+                        d.obst_vert_count ? d.obst_vert_count[o] : 0);
+    obstacles.push_back(O);
+  }
+  if (d.security_margins) {
+    size_t n = (size_t)(njoints + 1);
+    margins.assign(d.security_margins, d.security_margins + n * n);
+  }
+  weights.assign(njoints, 1.0);
+  if (d.weights) weights.assign(d.weights, d.weights + njoints);
+  break_distance = d.break_distance;
+
+  // Body::radius per joint (pinocchio computeBodyRadius): farthest corner of each geometry's
+  // local AABB mapped by its placement.
+  radii.assign(njoints + 1, 0.0);
+  for (const DevGeom& G : geoms) {
+    double lo[3], hi[3];
+    const DevShapeH& s = G.shape;
+    if (s.type == HPPB200_SHAPE_SPHERE) { for (int k = 0; k < 3; ++k) { lo[k] = -s.p[0]; hi[k] = s.p[0]; } }
+    else if (s.type == HPPB200_SHAPE_CAPSULE) { lo[0] = lo[1] = -s.p[0]; hi[0] = hi[1] = s.p[0]; lo[2] = -(s.p[1] + s.p[0]); hi[2] = s.p[1] + s.p[0]; }
+    else if (s.type == HPPB200_SHAPE_BOX) { for (int k = 0; k < 3; ++k) { lo[k] = -s.p[k]; hi[k] = s.p[k]; } }
+    else {
+      for (int k = 0; k < 3; ++k) { lo[k] = INFINITY; hi[k] = -INFINITY; }
+      for (int i = 0; i < s.vcount; ++i)
+        for (int k = 0; k < 3; ++k) {
+          double c = vertices[3 * (size_t)(s.vbegin + i) + k];
+          lo[k] = std::min(lo[k], c);
+          hi[k] = std::max(hi[k], c);
+        }
+    }
+    for (int c = 0; c < 8; ++c) {
+      double n = actNorm(G.P, (c & 1) ? hi[0] : lo[0], (c & 2) ? hi[1] : lo[1], (c & 4) ? hi[2] : lo[2]);
+      if (n > radii[G.joint]) radii[G.joint] = n;
+    }
+  }
+  buildConfigPairs(d);
+  buildBodyPairs(d);
+  buildBlob();
+}
+
+// cPairs_ order: active self pairs, then for every obstacle (call order) every moving joint
+// (index order) every inner object of its body.  Geometry on the universe gets no obstacle pair.
+void Model::buildConfigPairs(const hppb200_model_desc& d) {
+  for (int p = 0; p < d.nself_pairs; ++p) {
+    int a = d.self_pairs[2 * p], b = d.self_pairs[2 * p + 1];
+    if (a < 0 || b < 0 || a >= (int)geoms.size() || b >= (int)geoms.size()) throw std::invalid_argument("self pair index out of range");
+    cPairs.push_back(DevPair{a, b, 0, 0, margin(geoms[a].joint, geoms[b].joint)});
+  }
+  for (int o = 0; o < (int)obstacles.size(); ++o)
+    for (int j = 1; j <= njoints; ++j)
+      for (int g = 0; g < (int)geoms.size(); ++g)
+        if (geoms[g].joint == j) cPairs.push_back(DevPair{g, -(o + 1), 0, 0, margin(j, 0)});
+}
+
+void Model::buildBodyPairs(const hppb200_model_desc& d) {
+  auto parentOf = [&](int j) { return joints[j - 1].parent; };
+  auto linVel = [&](int j) { int t = joints[j - 1].type; return (t >= HPPB200_JOINT_PRISMATIC_X) ? 1.0 : 0.0; };
+  auto angVel = [&](int j) { int t = joints[j - 1].type; return (t <= HPPB200_JOINT_REVOLUTE_Z || t == HPPB200_JOINT_FREEFLYER) ? 1.0 : 0.0; };
+  auto maxDistToParent = [&](int j) {
+    const DevJoint& J = joints[j - 1];
+    if (J.type <= HPPB200_JOINT_REVOLUTE_Z) return norm3(J.P[9], J.P[10], J.P[11]);
+    int a = J.type - HPPB200_JOINT_PRISMATIC_X;  // prismatic: farthest end of the stroke
+    double best = 0;
+    for (double s : {lower[J.idx_q], upper[J.idx_q]}) {
+      double n = norm3(std::fma(s, J.P[a], J.P[9]), std::fma(s, J.P[3 + a], J.P[10]), std::fma(s, J.P[6 + a], J.P[11]));
+      best = std::max(best, n);
+    }
+    return best;
+  };
+  auto coefficients = [&](const std::vector<int>& seq, int joint_a) {
+    std::vector<std::pair<int, double>> out;
+    double cumulative = radii[joint_a];  // radius of body a for both directions, as the reference does
+    for (size_t i = 0; i + 1 < seq.size(); ++i) {
+      int child;
+      if (seq[i] != 0 && parentOf(seq[i]) == seq[i + 1]) child = seq[i];
+      else if (seq[i + 1] != 0 && parentOf(seq[i + 1]) == seq[i]) child = seq[i + 1];
+      else throw std::runtime_error("joint sequence is not a kinematic chain");
+      out.push_back({child, linVel(child) + cumulative * angVel(child)});
+      cumulative += maxDistToParent(child);
+    }
+    return out;
+  };
+  auto finish = [&](BodyPairHost& bp) {
+    std::vector<int> up, down;  // climb from the larger index until both meet
+    int ia = bp.joint_a, ib = bp.joint_b;
+    while (ia != ib) {
+      if (ia > ib) { up.push_back(ia); ia = parentOf(ia); }
+      else { down.push_back(ib); ib = parentOf(ib); }
+    }
+    up.push_back(ia);
+    std::vector<int> seq(up);
+    seq.insert(seq.end(), down.rbegin(), down.rend());
+    bp.coefs = coefficients(seq, bp.joint_a);
+    if (bp.joint_b != 0) {
+      std::reverse(seq.begin(), seq.end());
+      bp.rcoefs = coefficients(seq, bp.joint_a);
+    }
+  };
+  // self pairs: one body pair per ordered joint pair, in order of first appearance
+  std::map<std::pair<int, int>, size_t> seen;
+  for (int p = 0; p < d.nself_pairs; ++p) {
+    int ga = d.self_pairs[2 * p], gb = d.self_pairs[2 * p + 1];
+    std::pair<int, int> jp(geoms[ga].joint, geoms[gb].joint);
+    if (jp.first == jp.second) continue;
+    auto it = seen.find(jp);
+    if (it == seen.end()) {
+      BodyPairHost bp;
+      int j1 = jp.first, j2 = jp.second;
+      if (j2 == 0) std::swap(j1, j2);
+      bp.joint_a = j2;
+      bp.joint_b = j1;
+      finish(bp);
+      bodyPairs.push_back(bp);
+      it = seen.insert({jp, bodyPairs.size() - 1}).first;
+    }
+    bodyPairs[it->second].pairs.push_back(DevPair{ga, gb, 0, 0, margin(jp.first, jp.second)});
+  }
+  // obstacles: one body pair per (joint carrying a body, obstacle)
+  for (int o = 0; o < (int)obstacles.size(); ++o)
+    for (int j = 1; j <= njoints; ++j) {
+      BodyPairHost bp;
+      bp.joint_a = j;
+      bp.joint_b = 0;
+      for (int g = 0; g < (int)geoms.size(); ++g)
+        if (geoms[g].joint == j) bp.pairs.push_back(DevPair{g, -(o + 1), 0, 0, margin(j, 0)});
+      if (bp.pairs.empty()) continue;
+      finish(bp);
+      bodyPairs.push_back(bp);
+    }
+}
+
+void Model::buildBlob() {
+  auto shapeOf = [&](int ref) -> const DevShapeH& { return ref >= 0 ? geoms[ref].shape : obstacles[-(ref + 1)].shape; };
+  auto canonical = [&](DevPair p) {
+    if (shapeOf(p.a).type > shapeOf(p.b).type) std::swap(p.a, p.b);
+    p.kind = pairKind(shapeOf(p.a).type, shapeOf(p.b).type);
+    return p;
+  };
+  auto append = [&](const void* src, size_t bytes) {
+    size_t off = blob.size();
+    blob.resize(off + ((bytes + 15) & ~size_t(15)), 0);
+    if (bytes) std::memcpy(blob.data() + off, src, bytes);
+    return (uint32_t)off;
+  };
+  std::vector<DevPair> cp, bg;
+  std::vector<DevBodyPair> bps;
+  std::vector<DevCoef> cf, rcf;
+  for (const DevPair& p : cPairs) cp.push_back(canonical(p));
+  for (const BodyPairHost& b : bodyPairs) {
+    DevBodyPair B{};
+    B.joint_a = b.joint_a;
+    B.joint_b = b.joint_b;
+    B.pair_begin = (int)bg.size();
+    for (const DevPair& p : b.pairs) bg.push_back(canonical(p));
+    B.pair_end = (int)bg.size();
+    B.coef_begin = (int)cf.size();
+    for (auto& c : b.coefs) cf.push_back(DevCoef{joints[c.first - 1].idx_v, joint_nv[c.first - 1], c.second});
+    B.coef_end = (int)cf.size();
+    B.rcoef_begin = (int)rcf.size();
+    for (auto& c : b.rcoefs) rcf.push_back(DevCoef{joints[c.first - 1].idx_v, joint_nv[c.first - 1], c.second});
+    B.rcoef_end = (int)rcf.size();
+    bps.push_back(B);
+  }
+  view = ModelView{};
+  view.off_joints = append(joints.data(), joints.size() * sizeof(DevJoint));
+  view.off_geoms = append(geoms.data(), geoms.size() * sizeof(DevGeom));
+  view.off_obstacles = append(obstacles.data(), obstacles.size() * sizeof(DevObstacle));
+  view.off_cpairs = append(cp.data(), cp.size() * sizeof(DevPair));
+  view.off_bodypairs = append(bps.data(), bps.size() * sizeof(DevBodyPair));
+  view.off_bgpairs = append(bg.data(), bg.size() * sizeof(DevPair));
+  view.off_coefs = append(cf.data(), cf.size() * sizeof(DevCoef));
+  view.off_rcoefs = append(rcf.data(), rcf.size() * sizeof(DevCoef));
+  view.off_lower = append(lower.data(), lower.size() * sizeof(double));
+  view.off_upper = append(upper.data(), upper.size() * sizeof(double));
+  view.off_weights = append(weights.data(), weights.size() * sizeof(double));
+  view.blob_bytes = (uint32_t)blob.size();
+  view.njoints = njoints;
+  view.ngeoms = (int)geoms.size();
+  view.nobstacles = (int)obstacles.size();
+  view.ncpairs = (int)cp.size();
+  view.nbodypairs = (int)bps.size();
+  view.nbgpairs = (int)bg.size();
+  view.ncoefs = (int)cf.size();
+  view.nrcoefs = (int)rcf.size();
+  view.nq = nq;
+  view.nv = nv;
+}
+
+ModelView Model::deviceView(int device) const {
+  std::lock_guard<std::mutex> lock(mu_);
+  auto it = dev_.find(device);
+  if (it == dev_.end()) {
+    HPPB200_CUDA_CHECK(cudaSetDevice(device));
+    void* dblob = nullptr;
+    void* dverts = nullptr;
+    HPPB200_CUDA_CHECK(cudaMalloc(&dblob, blob.size()));
+    HPPB200_CUDA_CHECK(cudaMemcpy(dblob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+    if (!vertices.empty()) {
+      HPPB200_CUDA_CHECK(cudaMalloc(&dverts, vertices.size() * sizeof(double)));
+      HPPB200_CUDA_CHECK(cudaMemcpy(dverts, vertices.data(), vertices.size() * sizeof(double), cudaMemcpyHostToDevice));
+    }
+    it = dev_.insert({device, {dblob, dverts}}).first;
+  }
+  ModelView v = view;
+  v.blob = (const unsigned char*)it->second.first;
+  v.vertices = (const double*)it->second.second;
+  return v;
+}
+
+Model::~Model() {
+  for (auto& kv : dev_) {
+    cudaSetDevice(kv.first);
+    if (kv.second.first) cudaFree(kv.second.first);
+    if (kv.second.second) cudaFree(kv.second.second);
+  }
+}
+
+}  // namespace hppb200
