@@ -1,0 +1,274 @@
+"""hpp-core_b200 — B200-native batched validation engine for hpp-core's hot path.
+
+Thin ctypes binding of the C ABI (include/hppb200.h, built into hpp-core_b200/libhppb200.so)
+plus a Python mirror of the reference's operator interface for this path (same names and
+argument meaning as hpp::core::{CollisionValidation, JointBoundValidation, ConfigValidations,
+pathValidation::Discretized, continuousValidation::{Progressive, Dichotomy},
+nearestNeighbor::Basic}), extended with batch entry points.
+
+The directory name contains a hyphen, so import it through `load()` in __graft_entry__.py
+(importlib) under the module name `hpp_core_b200`.
+
+There is NO CPU fallback: every compute call goes to the CUDA library and raises if the
+library or a GPU is missing.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from .model_io import ModelDescription, hppb200_model_desc, uniform_configs  # noqa: F401
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libhppb200.so")
+
+OK, ERR_INVALID_ARGUMENT, ERR_RUNTIME, ERR_CUDA, ERR_UNSUPPORTED = range(5)
+METHOD_DISCRETIZED, METHOD_PROGRESSIVE, METHOD_DICHOTOMY = 0, 1, 2
+REASON_VALID, REASON_COLLISION, REASON_JOINT_BOUND, REASON_ITER_CAP = 0, 1, 2, 3
+CHECK_JOINT_BOUNDS, DEVICE_POINTERS = 1, 2
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+_u8p = C.POINTER(C.c_uint8)
+_i64p = C.POINTER(C.c_int64)
+
+
+class hppb200_stats(C.Structure):
+    _fields_ = [("configs", C.c_uint64), ("pair_tests", C.c_uint64), ("gjk_iterations", C.c_uint64),
+                ("edge_samples", C.c_uint64), ("kernel_launches", C.c_uint64), ("iter_cap_hits", C.c_uint64),
+                ("last_kernel_ms", C.c_double)]
+
+
+# every symbol include/hppb200.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "hppb200_abi_version", "hppb200_last_error", "hppb200_device_count",
+    "hppb200_model_create", "hppb200_model_destroy", "hppb200_model_nq", "hppb200_model_nv",
+    "hppb200_model_num_config_pairs", "hppb200_model_get_config_pairs", "hppb200_model_num_body_pairs",
+    "hppb200_model_get_body_pairs", "hppb200_model_num_body_geom_pairs", "hppb200_model_get_body_geom_pairs",
+    "hppb200_model_num_coefficients", "hppb200_model_get_coefficients", "hppb200_model_get_body_radii",
+    "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
+    "hppb200_validate_configs", "hppb200_geometry_placements", "hppb200_pair_distances",
+    "hppb200_straight_lengths", "hppb200_validate_edges", "hppb200_workspace_set_max_iterations",
+    "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_size",
+    "hppb200_knn_query", "hppb200_knn_within_ball",
+]
+
+_LIB = None
+
+
+def build(verbose=False):
+    """Compile the CUDA extension in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    out = subprocess.run(["make", "-C", os.path.join(HERE, "csrc")], capture_output=True, text=True)
+    if verbose or out.returncode != 0:
+        print(out.stdout[-4000:], out.stderr[-4000:])
+    if out.returncode != 0:
+        raise RuntimeError("building libhppb200.so failed")
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError("CUDA extension %s is missing: run __graft_entry__.build() "
+                               "(there is no CPU fallback)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.hppb200_last_error.restype = C.c_char_p
+        L.hppb200_knn_size.restype = C.c_size_t
+        _LIB = L
+    return _LIB
+
+
+class EngineError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc == OK:
+        return
+    msg = lib().hppb200_last_error().decode()
+    if rc == ERR_INVALID_ARGUMENT:
+        raise ValueError(msg)  # std::invalid_argument in the reference
+    raise EngineError(msg)  # std::runtime_error in the reference
+
+
+def _p(a, t):
+    return None if a is None else a.ctypes.data_as(t)
+
+
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+class Model:
+    """Compiled robot + obstacle tables (immutable, shareable between workspaces)."""
+
+    def __init__(self, desc):
+        self.desc = desc if isinstance(desc, ModelDescription) else ModelDescription.load(desc)
+        self._struct = self.desc.struct()
+        self.h = C.c_void_p()
+        _check(lib().hppb200_model_create(C.byref(self._struct), C.byref(self.h)))
+        self.nq = lib().hppb200_model_nq(self.h)
+        self.nv = lib().hppb200_model_nv(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hppb200_model_destroy(self.h)
+            self.h = None
+
+    def config_pairs(self):
+        n = lib().hppb200_model_num_config_pairs(self.h)
+        a, b, m = np.zeros(n, np.int32), np.zeros(n, np.int32), np.zeros(n)
+        lib().hppb200_model_get_config_pairs(self.h, _p(a, _ip), _p(b, _ip), _p(m, _dp))
+        return a, b, m
+
+    def body_pairs(self):
+        n = lib().hppb200_model_num_body_pairs(self.h)
+        ja, jb = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        pb, cb, rb = (np.zeros(n + 1, np.int32) for _ in range(3))
+        lib().hppb200_model_get_body_pairs(self.h, _p(ja, _ip), _p(jb, _ip), _p(pb, _ip), _p(cb, _ip), _p(rb, _ip))
+        ng = lib().hppb200_model_num_body_geom_pairs(self.h)
+        ga, gb, gm = np.zeros(ng, np.int32), np.zeros(ng, np.int32), np.zeros(ng)
+        lib().hppb200_model_get_body_geom_pairs(self.h, _p(ga, _ip), _p(gb, _ip), _p(gm, _dp))
+        out = dict(joint_a=ja, joint_b=jb, pair_begin=pb, coef_begin=cb, rcoef_begin=rb, geomA=ga, geomB=gb, margin=gm)
+        for rev, key in ((0, "coef"), (1, "rcoef")):
+            nc = lib().hppb200_model_num_coefficients(self.h, rev)
+            j, v = np.zeros(nc, np.int32), np.zeros(nc)
+            lib().hppb200_model_get_coefficients(self.h, rev, _p(j, _ip), _p(v, _dp))
+            out[key + "_joint"], out[key + "_value"] = j, v
+        return out
+
+    def body_radii(self):
+        r = np.zeros(self.desc.njoints + 1)
+        lib().hppb200_model_get_body_radii(self.h, _p(r, _dp))
+        return r
+
+
+class Workspace:
+    """One CUDA stream + scratch on one device.  Accepts numpy arrays (host pointers, the
+    library stages them) or CUDA torch tensors (device pointers, zero copy)."""
+
+    def __init__(self, model, device=0):
+        self.model = model
+        self.device = device
+        self.h = C.c_void_p()
+        _check(lib().hppb200_workspace_create(model.h, C.c_int(device), C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hppb200_workspace_destroy(self.h)
+            self.h = None
+
+    def set_stream(self, cuda_stream_ptr):
+        _check(lib().hppb200_workspace_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
+
+    def set_max_iterations(self, n):
+        _check(lib().hppb200_workspace_set_max_iterations(self.h, C.c_uint32(n)))
+
+    def stats(self):
+        s = hppb200_stats()
+        _check(lib().hppb200_get_stats(self.h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in s._fields_}
+
+    # -- raw pointer forms (host or device pointers, as ints) -----------------------------
+    def validate_configs_ptr(self, q_ptr, n, valid_ptr, first_ptr=0, reason_ptr=0, flags=0):
+        _check(lib().hppb200_validate_configs(self.h, C.c_void_p(q_ptr), C.c_size_t(n), C.c_uint32(flags),
+                                              C.c_void_p(valid_ptr), C.c_void_p(first_ptr or None),
+                                              C.c_void_p(reason_ptr or None)))
+
+    def validate_edges_ptr(self, method, param, reverse, q1_ptr, q2_ptr, L_ptr, n, valid_ptr, tfail_ptr=0,
+                           tlast_ptr=0, pair_ptr=0, reason_ptr=0, flags=0):
+        _check(lib().hppb200_validate_edges(self.h, C.c_int(method), C.c_double(param), C.c_int(1 if reverse else 0),
+                                            C.c_void_p(q1_ptr), C.c_void_p(q2_ptr), C.c_void_p(L_ptr), C.c_size_t(n),
+                                            C.c_uint32(flags), C.c_void_p(valid_ptr), C.c_void_p(tfail_ptr or None),
+                                            C.c_void_p(tlast_ptr or None), C.c_void_p(pair_ptr or None),
+                                            C.c_void_p(reason_ptr or None)))
+
+    # -- numpy forms ------------------------------------------------------------------------
+    def validate_configs(self, q, check_bounds=False):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.model.nq)
+        n = q.shape[0]
+        valid, first, reason = np.zeros(n, np.uint8), np.full(n, -1, np.int32), np.zeros(n, np.uint8)
+        self.validate_configs_ptr(q.ctypes.data, n, valid.ctypes.data, first.ctypes.data, reason.ctypes.data,
+                                  CHECK_JOINT_BOUNDS if check_bounds else 0)
+        return valid, first, reason
+
+    def geometry_placements(self, q):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.model.nq)
+        out = np.zeros((q.shape[0], self.model.desc.ngeoms, 12))
+        _check(lib().hppb200_geometry_placements(self.h, _p(q, _dp), C.c_size_t(q.shape[0]), C.c_uint32(0), _p(out, _dp)))
+        return out
+
+    def pair_distances(self, q):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.model.nq)
+        npairs = lib().hppb200_model_num_config_pairs(self.model.h)
+        out = np.zeros((q.shape[0], npairs))
+        _check(lib().hppb200_pair_distances(self.h, _p(q, _dp), C.c_size_t(q.shape[0]), C.c_uint32(0), _p(out, _dp)))
+        return out
+
+    def straight_lengths(self, q1, q2):
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.model.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.model.nq)
+        L = np.zeros(q1.shape[0])
+        _check(lib().hppb200_straight_lengths(self.h, _p(q1, _dp), _p(q2, _dp), C.c_size_t(q1.shape[0]), C.c_uint32(0),
+                                              _p(L, _dp)))
+        return L
+
+    def validate_edges(self, method, param, q1, q2, L, reverse=False, check_bounds=False):
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.model.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.model.nq)
+        L = np.ascontiguousarray(L, np.float64)
+        n = q1.shape[0]
+        valid, reason = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        t_fail, t_last = np.zeros(n), np.zeros(n)
+        pair = np.full(n, -1, np.int32)
+        self.validate_edges_ptr(method, param, reverse, q1.ctypes.data, q2.ctypes.data, L.ctypes.data, n,
+                                valid.ctypes.data, t_fail.ctypes.data, t_last.ctypes.data, pair.ctypes.data,
+                                reason.ctypes.data, CHECK_JOINT_BOUNDS if check_bounds else 0)
+        return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason)
+
+
+class NearestNeighbor:
+    """Device mirror of the roadmap nodes + brute-force WeighedDistance search
+    (nearestNeighbor::Basic, reference src/nearest-neighbor/basic.cc)."""
+
+    def __init__(self, model, device=0):
+        self.model = model
+        self.h = C.c_void_p()
+        _check(lib().hppb200_knn_create(model.h, C.c_int(device), C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().hppb200_knn_destroy(self.h)
+            self.h = None
+
+    def __len__(self):
+        return int(lib().hppb200_knn_size(self.h))
+
+    def append(self, q, cc=None):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.model.nq)
+        cc = None if cc is None else np.ascontiguousarray(cc, np.int32)
+        _check(lib().hppb200_knn_append(self.h, _p(q, _dp), _p(cc, _ip), C.c_size_t(q.shape[0])))
+
+    def relabel(self, from_cc, to_cc):
+        _check(lib().hppb200_knn_relabel(self.h, C.c_int32(from_cc), C.c_int32(to_cc)))
+
+    def query(self, queries, k=1, cc=-1):
+        queries = np.ascontiguousarray(queries, np.float64).reshape(-1, self.model.nq)
+        n = queries.shape[0]
+        idx, dist = np.zeros((n, k), np.int64), np.zeros((n, k))
+        _check(lib().hppb200_knn_query(self.h, _p(queries, _dp), C.c_size_t(n), C.c_int(k), C.c_int32(cc),
+                                       C.c_uint32(0), _p(idx, _i64p), _p(dist, _dp)))
+        return idx, dist
+
+    def within_ball(self, queries, radius, cc=-1, cap=4096):
+        queries = np.ascontiguousarray(queries, np.float64).reshape(-1, self.model.nq)
+        n = queries.shape[0]
+        idx, count = np.full((n, cap), -1, np.int64), np.zeros(n, np.int64)
+        _check(lib().hppb200_knn_within_ball(self.h, _p(queries, _dp), C.c_size_t(n), C.c_double(radius),
+                                             C.c_int32(cc), C.c_size_t(cap), _p(idx, _i64p), _p(count, _i64p)))
+        return [idx[i, :min(count[i], cap)].copy() for i in range(n)], count
+
+
+from .validators import (CollisionValidation, ConfigValidations, Dichotomy, Discretized,  # noqa: E402,F401
+                         JointBoundValidation, Progressive, StraightPath, ValidationReport)

@@ -7,15 +7,6 @@
 
 #include "engine.hpp"
 
-struct hppb200_model {
-  hppb200::Model impl;
-  explicit hppb200_model(const hppb200_model_desc& d) : impl(d) {}
-};
-struct hppb200_workspace {
-  hppb200::Workspace impl;
-  hppb200_workspace(const hppb200::Model* m, int dev) : impl(m, dev) {}
-};
-
 namespace hppb200 {
 
 static thread_local std::string g_last_error;

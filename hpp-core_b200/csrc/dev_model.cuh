@@ -72,22 +72,65 @@ __device__ __forceinline__ void stageBlobTMA(unsigned char* sdst, const unsigned
 }
 
 // pinocchio joint transform composed with the joint placement: liMi = P * M_joint(q)
-__device__ __forceinline__ T3 jointLocal(const DevJoint& J, const double* __restrict__ q) {
+template <class Q>
+__device__ __forceinline__ T3 jointLocal(const DevJoint& J, const Q& q) {
   T3 P = load12(J.P);
   T3 M = identityT();
   if (J.type <= HPPB200_JOINT_REVOLUTE_Z) {
     double s, c;
-    sincos_portable(q[J.idx_q], &s, &c);
+    sincos_portable(q(J.idx_q), &s, &c);
     // static indices only (keeps M in registers)
     if (J.type == HPPB200_JOINT_REVOLUTE_X) { M.r[4] = c; M.r[5] = -s; M.r[7] = s; M.r[8] = c; }
     else if (J.type == HPPB200_JOINT_REVOLUTE_Y) { M.r[8] = c; M.r[6] = -s; M.r[2] = s; M.r[0] = c; }
     else { M.r[0] = c; M.r[1] = -s; M.r[3] = s; M.r[4] = c; }
   } else {
     const int a = J.type - HPPB200_JOINT_PRISMATIC_X;
-    double v = q[J.idx_q];
+    double v = q(J.idx_q);
     M.t = mk(a == 0 ? v : 0.0, a == 1 ? v : 0.0, a == 2 ? v : 0.0);
   }
   return compose(P, M);
+}
+
+// FK for one configuration (pinocchio::forwardKinematics + updateGeometryPlacements):
+//   liMi = placement * M_joint(q); oMi = oMi[parent] * liMi; oMg = oMi[joint] * placement_g.
+// `store` is SoA: element k of slot s for this thread at store[(s*12+k)*stride].
+// Geometry g uses slot g; for tree-shaped robots joint j (1-based) uses slot ngeoms + j - 1.
+// `q(k)` returns configuration entry k.
+template <bool TREE, class Q>
+__device__ __forceinline__ void forwardKinematics(const Tables& T, const ModelView& mv, const Q& q, double* store,
+                                                  size_t stride) {
+  for (int g = 0; g < mv.ngeoms; ++g)
+    if (T.geoms[g].joint == 0) store12s(store + (size_t)g * 12 * stride, stride, load12(T.geoms[g].P));
+  T3 cur = identityT();
+  for (int j = 1; j <= mv.njoints; ++j) {
+    const DevJoint& J = T.joints[j - 1];
+    T3 li = jointLocal(J, q);
+    if (J.parent == 0) cur = li;
+    else if (!TREE || J.parent == j - 1) cur = compose(cur, li);
+    else cur = compose(load12s(store + (size_t)(mv.ngeoms + J.parent - 1) * 12 * stride, stride), li);
+    if (TREE) store12s(store + (size_t)(mv.ngeoms + j - 1) * 12 * stride, stride, cur);
+    for (int g = 0; g < mv.ngeoms; ++g)
+      if (T.geoms[g].joint == j) store12s(store + (size_t)g * 12 * stride, stride, compose(cur, load12(T.geoms[g].P)));
+  }
+}
+
+// distance_lower_bound (distance - security margin) of one canonically ordered pair
+__device__ __forceinline__ double pairLowerBound(const Tables& T, const DevPair& pr, const double* store, size_t stride,
+                                                 const double* __restrict__ verts, GjkCounters& cnt) {
+  const DevShape* sa;
+  const DevShape* sb;
+  T3 TA, TB;
+  if (pr.a >= 0) { sa = (const DevShape*)&T.geoms[pr.a].shape; TA = load12s(store + (size_t)pr.a * 12 * stride, stride); }
+  else { const DevObstacle& O = T.obstacles[-(pr.a + 1)]; sa = (const DevShape*)&O.shape; TA = load12(O.P); }
+  if (pr.b >= 0) { sb = (const DevShape*)&T.geoms[pr.b].shape; TB = load12s(store + (size_t)pr.b * 12 * stride, stride); }
+  else { const DevObstacle& O = T.obstacles[-(pr.b + 1)]; sb = (const DevShape*)&O.shape; TB = load12(O.P); }
+  return shapeDistance(pr.kind, *sa, TA, *sb, TB, verts, cnt) - pr.margin;
+}
+
+static inline bool modelIsTree(const Model* m) {
+  for (int k = 0; k < m->njoints; ++k)
+    if (m->joints[k].parent != k) return true;  // joint k+1 whose parent is not joint k
+  return false;
 }
 
 }  // namespace hppb200

@@ -89,7 +89,7 @@ struct GjkCounters {
 };
 
 // Distance between core shapes; `rel` = placement of B in A's frame.  0 when cores intersect.
-__device__ __noinline__ double gjkCoreDistance(const DevShape& A, const DevShape& B, const T3& rel,
+static __device__ __noinline__ double gjkCoreDistance(const DevShape& A, const DevShape& B, const T3& rel,
                                                const double* __restrict__ verts, GjkCounters& cnt) {
   V3 w0 = mk(0, 0, 0), w1 = w0, w2 = w0, w3 = w0;
   int n = 0;

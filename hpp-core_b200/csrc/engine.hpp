@@ -154,3 +154,13 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   } while (0)
 
 }  // namespace hppb200
+
+// opaque C handles (include/hppb200.h)
+struct hppb200_model {
+  hppb200::Model impl;
+  explicit hppb200_model(const hppb200_model_desc& d) : impl(d) {}
+};
+struct hppb200_workspace {
+  hppb200::Workspace impl;
+  hppb200_workspace(const hppb200::Model* m, int dev) : impl(m, dev) {}
+};

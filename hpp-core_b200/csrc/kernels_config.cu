@@ -44,41 +44,6 @@ static ConfigSmemLayout configSmemLayout(const ModelView& mv, bool tree) {
   return L;
 }
 
-// FK for one configuration (pinocchio::forwardKinematics + updateGeometryPlacements):
-//   liMi = placement * M_joint(q); oMi = oMi[parent] * liMi; oMg = oMi[joint] * placement_g.
-// `store` is SoA: element k of slot s for configuration c at store[(s*12+k)*stride + c].
-// Geometry g uses slot g; for tree-shaped robots joint j (1-based) uses slot ngeoms + j - 1.
-template <bool TREE>
-__device__ __forceinline__ void forwardKinematics(const Tables& T, const ModelView& mv, const double* __restrict__ q,
-                                                  double* store, size_t stride) {
-  for (int g = 0; g < mv.ngeoms; ++g)
-    if (T.geoms[g].joint == 0) store12s(store + (size_t)g * 12 * stride, stride, load12(T.geoms[g].P));
-  T3 cur = identityT();
-  for (int j = 1; j <= mv.njoints; ++j) {
-    const DevJoint& J = T.joints[j - 1];
-    T3 li = jointLocal(J, q);
-    if (J.parent == 0) cur = li;
-    else if (!TREE || J.parent == j - 1) cur = compose(cur, li);
-    else cur = compose(load12s(store + (size_t)(mv.ngeoms + J.parent - 1) * 12 * stride, stride), li);
-    if (TREE) store12s(store + (size_t)(mv.ngeoms + j - 1) * 12 * stride, stride, cur);
-    for (int g = 0; g < mv.ngeoms; ++g)
-      if (T.geoms[g].joint == j) store12s(store + (size_t)g * 12 * stride, stride, compose(cur, load12(T.geoms[g].P)));
-  }
-}
-
-// distance_lower_bound of one (canonically ordered) pair for configuration column c
-__device__ __forceinline__ double pairLowerBound(const Tables& T, const DevPair& pr, const double* store, size_t stride,
-                                                 const double* __restrict__ verts, GjkCounters& cnt) {
-  const DevShape* sa;
-  const DevShape* sb;
-  T3 TA, TB;
-  if (pr.a >= 0) { sa = (const DevShape*)&T.geoms[pr.a].shape; TA = load12s(store + (size_t)pr.a * 12 * stride, stride); }
-  else { const DevObstacle& O = T.obstacles[-(pr.a + 1)]; sa = (const DevShape*)&O.shape; TA = load12(O.P); }
-  if (pr.b >= 0) { sb = (const DevShape*)&T.geoms[pr.b].shape; TB = load12s(store + (size_t)pr.b * 12 * stride, stride); }
-  else { const DevObstacle& O = T.obstacles[-(pr.b + 1)]; sb = (const DevShape*)&O.shape; TB = load12(O.P); }
-  return shapeDistance(pr.kind, *sa, TA, *sb, TB, verts, cnt) - pr.margin;
-}
-
 template <bool TREE>
 __global__ void __launch_bounds__(CFG_THREADS)
 validateConfigsKernel(ModelView mv, ConfigSmemLayout L, const double* __restrict__ q, size_t n, uint32_t flags, int mode,
@@ -112,7 +77,7 @@ validateConfigsKernel(ModelView mv, ConfigSmemLayout L, const double* __restrict
           if (qc[k] < lo || hi < qc[k]) { boundHit[tid] = k; break; }
         }
       }
-      if (boundHit[tid] < 0) forwardKinematics<TREE>(T, mv, qc, store + tid, CFG_PER_BLOCK);
+      if (boundHit[tid] < 0) forwardKinematics<TREE>(T, mv, [qc](int k) { return qc[k]; }, store + tid, CFG_PER_BLOCK);
     }
   }
   __syncthreads();
@@ -171,16 +136,10 @@ validateConfigsKernel(ModelView mv, ConfigSmemLayout L, const double* __restrict
   }
 }
 
-static bool isTree(const Model* m) {
-  for (int k = 0; k < m->njoints; ++k)
-    if (m->joints[k].parent != k) return true;  // joint k+1 whose parent is not joint k
-  return false;
-}
-
 static void launchConfigKernel(Workspace* ws, const double* d_q, size_t n, uint32_t flags, int mode, uint8_t* d_valid,
                                int32_t* d_first, uint8_t* d_reason, double* d_aux) {
   if (n == 0) return;
-  const bool tree = isTree(ws->model);
+  const bool tree = modelIsTree(ws->model);
   ConfigSmemLayout L = configSmemLayout(ws->view, tree);
   if (L.total > 227u * 1024u)
     throw std::runtime_error("model too large for the shared-memory configuration kernel (" + std::to_string(L.total) + " B)");

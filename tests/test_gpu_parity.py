@@ -1,0 +1,245 @@
+"""GPU parity tests (-m gpu): the CUDA path, called through the C ABI, against the CPU oracle on
+the same inputs.  Bar: bit-exact flags, pair indices, edge parameters and distances (both sides
+follow the same numerics contract); any deviation must sit within 1e-9 of contact."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def eng(pkg, ur5):
+    m = pkg.Model(ur5)
+    return m, pkg.Workspace(m, 0)
+
+
+def test_fk_bit_exact(pkg, eng, ur5, ur5_oracle, golden_configs):
+    _, ws = eng
+    q = np.concatenate([golden_configs, pkg.uniform_configs(ur5, 5000, seed=3), np.zeros((1, 6))])
+    assert np.array_equal(ws.geometry_placements(q), ur5_oracle.geometry_placements(q))
+
+
+def test_pair_distances_bit_exact(pkg, eng, ur5, ur5_oracle, golden_configs):
+    _, ws = eng
+    q = np.concatenate([golden_configs, pkg.uniform_configs(ur5, 3000, seed=4)])
+    d, o = ws.pair_distances(q), ur5_oracle.pair_distances(q)
+    assert np.array_equal(d, o)
+
+
+def _check_flags(valid, first, ov, op, dist):
+    """flags/pair identical; a mismatch is tolerated only within 1e-9 of contact (north_star)."""
+    bad = np.nonzero((valid != ov) | (first != op))[0]
+    for i in bad:
+        assert np.abs(dist[i]).min() < 1e-9, i
+    return len(bad)
+
+
+def test_config_validation_golden_and_random(pkg, eng, ur5, ur5_oracle, golden_configs):
+    _, ws = eng
+    q = np.concatenate([golden_configs, pkg.uniform_configs(ur5, 200000, seed=12345)])
+    valid, first, reason = ws.validate_configs(q)
+    ov, op, orr = ur5_oracle.validate_configs(q)
+    assert np.array_equal(valid, ov)
+    assert np.array_equal(first, op)
+    assert np.array_equal(reason, orr)
+    assert 0.2 < valid.mean() < 0.9
+
+
+def test_config_validation_joint_bounds_and_ragged(pkg, eng, ur5, ur5_oracle):
+    _, ws = eng
+    q = pkg.uniform_configs(ur5, 1000 + 37, seed=8) * 1.2  # some out of bounds; ragged last block
+    for cb in (False, True):
+        got = ws.validate_configs(q, check_bounds=cb)
+        exp = ur5_oracle.validate_configs(q, check_bounds=cb)
+        for a, b in zip(got, exp):
+            assert np.array_equal(a, b)
+    assert (ws.validate_configs(q, check_bounds=True)[2] == 2).any()
+    v, f, r = ws.validate_configs(np.zeros((0, 6)))
+    assert v.shape == (0,)
+    v, f, r = ws.validate_configs(np.zeros((1, 6)))
+    assert v[0] == 1 and f[0] == -1
+
+
+@pytest.mark.parametrize("name", ["ur5_boxes0.json", "ur5_boxes1.json", "ur5_boxes32.json"])
+def test_config_validation_other_scenes(pkg, ob, name):
+    desc = pkg.ModelDescription.load(name)
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    o = ob.Oracle(desc)
+    q = pkg.uniform_configs(desc, 20000, seed=21)
+    for a, b in zip(ws.validate_configs(q), o.validate_configs(q)):
+        assert np.array_equal(a, b)
+
+
+def test_security_margins(pkg, ob):
+    desc = pkg.ModelDescription.load("ur5_boxes8.json")
+    desc.security_margins = np.full((7, 7), 0.02)
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    o = ob.Oracle(desc)
+    q = pkg.uniform_configs(desc, 20000, seed=22)
+    got, exp = ws.validate_configs(q), o.validate_configs(q)
+    for a, b in zip(got, exp):
+        assert np.array_equal(a, b)
+    base = ob.Oracle(pkg.ModelDescription.load("ur5_boxes8.json")).validate_configs(q)[0]
+    assert got[0].sum() < base.sum()  # margins only remove valid configurations
+
+
+def test_straight_lengths(pkg, eng, ur5, ur5_oracle):
+    _, ws = eng
+    q = pkg.uniform_configs(ur5, 20000, seed=6)
+    assert np.array_equal(ws.straight_lengths(q[0::2], q[1::2]), ur5_oracle.straight_lengths(q[0::2], q[1::2]))
+
+
+def _edges(pkg, ur5, o, n, seed, short=False):
+    q = pkg.uniform_configs(ur5, 2 * n, seed=seed)
+    q1, q2 = q[0::2].copy(), q[1::2].copy()
+    if short:
+        d = q2 - q1
+        q2 = np.clip(q1 + 0.3 * d / np.linalg.norm(d, axis=1, keepdims=True), -np.pi, np.pi)
+    return q1, q2, o.straight_lengths(q1, q2)
+
+
+@pytest.mark.parametrize("method,param", [(0, 0.05), (1, 1e-3), (2, 0.0)])
+@pytest.mark.parametrize("reverse", [False, True])
+def test_edge_validation_parity(pkg, eng, ur5, ur5_oracle, golden_configs, method, param, reverse):
+    """C1-style edges (q1 = conf[2i], q2 = conf[2i+1], tests/test-continuous-validation.cc:165-176):
+    the 100 golden edges + random long and short edges."""
+    _, ws = eng
+    o = ur5_oracle
+    g1, g2 = golden_configs[0:200:2], golden_configs[1:200:2]
+    a1, a2, _ = _edges(pkg, ur5, o, 4000, 31)
+    b1, b2, _ = _edges(pkg, ur5, o, 4000, 32, short=True)
+    q1, q2 = np.concatenate([g1, a1, b1]), np.concatenate([g2, a2, b2])
+    L = o.straight_lengths(q1, q2)
+    r = ws.validate_edges(method, param, q1, q2, L, reverse=reverse)
+    e = o.validate_edges(method, param, q1, q2, L, reverse=reverse)
+    st = ws.stats()
+    assert st["iter_cap_hits"] == 0
+    assert np.array_equal(r["valid"], e["valid"])
+    assert np.array_equal(r["reason"], e["reason"])
+    assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+    assert np.array_equal(r["t_last_valid"], e["t_last_valid"])
+    assert np.array_equal(r["pair"], e["pair"])
+    assert 0.02 < r["valid"].mean() < 0.98
+
+
+def test_edge_zero_length_and_endpoints(pkg, eng, ur5, ur5_oracle):
+    """PathValidation::validate(q) == zero-length StraightPath (src/path-validation.cc:36-49): I1."""
+    _, ws = eng
+    q = pkg.uniform_configs(ur5, 3000, seed=41)
+    v = ws.validate_configs(q)[0]
+    z = np.zeros(len(q))
+    for method, param in ((0, 0.05), (1, 1e-3), (2, 0.0)):
+        r = ws.validate_edges(method, param, q, q, z)
+        assert np.array_equal(r["valid"], v)
+        assert np.all(r["t_fail"][v == 0] == 0.0)
+
+
+def test_edge_invariants_on_gpu(pkg, eng, ur5, ur5_oracle):
+    """I2: Discretized(0.05) invalid => Progressive(1e-3) and Dichotomy(0) invalid."""
+    _, ws = eng
+    q1, q2, L = _edges(pkg, ur5, ur5_oracle, 20000, 51)
+    for rev in (False, True):
+        d = ws.validate_edges(0, 0.05, q1, q2, L, reverse=rev)["valid"]
+        p = ws.validate_edges(1, 1e-3, q1, q2, L, reverse=rev)["valid"]
+        c = ws.validate_edges(2, 0.0, q1, q2, L, reverse=rev)["valid"]
+        assert not np.any((d == 0) & (p == 1))
+        assert not np.any((d == 0) & (c == 1))
+
+
+def test_edge_iteration_cap_is_flagged(pkg, eng, ur5, ur5_oracle):
+    m, _ = eng
+    ws = pkg.Workspace(m, 0)
+    ws.set_max_iterations(3)
+    q1, q2, L = _edges(pkg, ur5, ur5_oracle, 500, 61)
+    r = ws.validate_edges(1, 1e-3, q1, q2, L)
+    e = ur5_oracle.validate_edges(1, 1e-3, q1, q2, L, max_iter=3)
+    assert np.array_equal(r["reason"], e["reason"])
+    assert (r["reason"] == 3).any() and np.all(r["valid"][r["reason"] == 3] == 0)
+
+
+def test_error_codes(pkg, eng):
+    _, ws = eng
+    q = np.zeros((1, 6))
+    with pytest.raises(pkg.EngineError):   # std::runtime_error in the reference constructors
+        ws.validate_edges(1, 0.0, q, q, np.zeros(1))
+    with pytest.raises(pkg.EngineError):
+        ws.validate_edges(2, 1e-3, q, q, np.zeros(1))
+    with pytest.raises(ValueError):
+        ws.validate_edges(7, 1e-3, q, q, np.zeros(1))
+
+
+def test_validator_mirror_classes(pkg, eng, ur5, ur5_oracle):
+    """The reference-shaped interface: validate(q) / validate(path, reverse)."""
+    _, ws = eng
+    cv = pkg.CollisionValidation.create(ws)
+    prog = pkg.Progressive.create(ws, 1e-3)
+    q = pkg.uniform_configs(ur5, 40, seed=71)
+    ov = ur5_oracle.validate_configs(q)
+    for i in range(20):
+        ok, rep = cv.validate(q[i])
+        assert ok == bool(ov[0][i])
+        if not ok:
+            assert rep.reason == 1 and rep.index == ov[1][i]
+        ok5, _ = prog.validate_config(q[i])
+        assert ok5 == ok
+    L = ur5_oracle.straight_lengths(q[:20], q[20:])
+    e = ur5_oracle.validate_edges(1, 1e-3, q[:20], q[20:], L)
+    for i in range(20):
+        path = pkg.StraightPath(q[i], q[20 + i], L[i])
+        ok, part, rep = prog.validate(path, False)
+        assert ok == bool(e["valid"][i])
+        if ok:
+            assert part is path
+        else:
+            assert rep.parameter == e["t_fail"][i] and part.length == e["t_last_valid"][i]
+
+
+def test_knn_parity(pkg, eng, ur5, ob):
+    m, _ = eng
+    o = ob.Oracle(ur5)
+    nn = pkg.NearestNeighbor(m, 0)
+    nodes = pkg.uniform_configs(ur5, 30000, seed=81)
+    nodes[20000] = nodes[123]  # exact duplicate
+    cc = (np.arange(len(nodes)) % 4).astype(np.int32)
+    for lo in range(0, len(nodes), 7000):  # incremental appends, as a growing roadmap
+        nn.append(nodes[lo:lo + 7000], cc[lo:lo + 7000])
+        o.knn_append(nodes[lo:lo + 7000], cc[lo:lo + 7000])
+    assert len(nn) == len(nodes)
+    qs = pkg.uniform_configs(ur5, 64, seed=82)
+    qs[0] = nodes[123]
+    for k, c in ((1, -1), (1, 2), (10, -1), (7, 3)):
+        gi, gd = nn.query(qs, k, c)
+        oi, od = o.knn_query(qs, k, c)
+        assert np.array_equal(gi, oi), (k, c)
+        assert np.array_equal(gd, od)
+    assert nn.query(qs[:1], 1)[0][0, 0] == 123
+    nn.relabel(3, 0)
+    o.knn_relabel(3, 0)
+    assert np.array_equal(nn.query(qs, 5, 0)[0], o.knn_query(qs, 5, 0)[0])
+    balls, count = nn.within_ball(qs[:8], 0.9)
+    for i in range(8):
+        assert np.array_equal(balls[i], o.knn_within_ball(qs[i], 0.9))
+    # k larger than the component: padded with -1
+    small = pkg.NearestNeighbor(m, 0)
+    small.append(nodes[:3])
+    gi, gd = small.query(qs[:2], 5)
+    assert np.all(gi[:, 3:] == -1) and np.all(np.isinf(gd[:, 3:]))
+
+
+def test_full_size_properties(pkg, eng, ur5, ur5_oracle):
+    """BASELINE config[1] size (1M configurations): size-independent properties —
+    idempotence (same batch twice -> same flags), permutation equivariance, consistency of a
+    random 20k subsample with the oracle, and flag/pair coherence."""
+    _, ws = eng
+    n = 1 << 20
+    q = pkg.uniform_configs(ur5, n, seed=12345)
+    v1, f1, r1 = ws.validate_configs(q)
+    v2, f2, _ = ws.validate_configs(q)
+    assert np.array_equal(v1, v2) and np.array_equal(f1, f2)
+    perm = np.random.default_rng(0).permutation(n)
+    v3, f3, _ = ws.validate_configs(q[perm])
+    assert np.array_equal(v3, v1[perm]) and np.array_equal(f3, f1[perm])
+    assert np.all((f1 >= 0) == (v1 == 0)) and np.all((r1 == 1) == (v1 == 0))
+    sub = np.random.default_rng(1).choice(n, 20000, replace=False)
+    ov, op, _ = ur5_oracle.validate_configs(q[sub])
+    assert np.array_equal(v1[sub], ov) and np.array_equal(f1[sub], op)

@@ -1,0 +1,261 @@
+"""CPU tests (-m "not gpu"): the oracle against the reference's own fixtures/invariants, and
+oracle self-checks."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+# ---- Intervals: pinned against the reference --------------------------------------------
+def test_intervals_known_answers(ob):
+    """tests/test-intervals.cc:55-233 known answers."""
+    cases = json.load(open(os.path.join(ROOT, "tests", "golden", "intervals_known_answers.json")))
+    assert len(cases) == 5
+    for c in cases:
+        u = np.array(c["unions"])
+        got = ob.intervals_union(u[:, 0], u[:, 1])
+        assert np.array_equal(got, np.array(c["expected"])), c["name"]
+
+
+def test_intervals_touching_merge(ob):
+    """tests/test-intervals.cc interval_6: [0,1] u [2,3] u [1,2] -> one interval."""
+    got = ob.intervals_union(np.array([0., 2., 1.]), np.array([1., 3., 2.]))
+    assert np.array_equal(got, np.array([[0., 3.]]))
+
+
+def test_intervals_vs_reference_build(ob):
+    """oracle::Intervals == the reference's own class (oracle/_ref) on random sequences,
+    including exact ties (grid-valued end points) and zero-length intervals."""
+    if ob.ref_intervals() is None:
+        pytest.skip("oracle/_ref not built (reference absent)")
+    rng = np.random.default_rng(3)
+    for trial in range(400):
+        n = int(rng.integers(1, 40))
+        if trial % 2:
+            lo = rng.integers(0, 30, n).astype(float)
+            hi = lo + rng.integers(0, 5, n)
+        else:
+            t = rng.uniform(0, 1, n)
+            l = rng.uniform(0, .05, n)
+            lo, hi = t - l, t + l
+        a = ob.intervals_union(lo, hi, "oracle")
+        b = ob.intervals_union(lo, hi, "ref")
+        assert np.array_equal(a, b), (trial, lo, hi, a, b)
+        assert np.all(a[1:, 0] > a[:-1, 1])  # sorted, disjoint (test-intervals.cc checkIntervals)
+
+
+# ---- numerics self-checks ----------------------------------------------------------------
+def test_portable_sincos(ob):
+    x = np.concatenate([np.random.default_rng(0).uniform(-20, 20, 200000), np.linspace(-np.pi, np.pi, 10001),
+                        [0.0, np.pi / 2, -np.pi / 2, np.pi, 1e-300, 1e4]])
+    s, c = ob.sincos(x)
+    assert np.abs(s - np.sin(x)).max() < 2.3e-16
+    assert np.abs(c - np.cos(x)).max() < 2.3e-16
+
+
+def test_fk_vs_dh_end_effector(ob, ur5, ur5_oracle):
+    """FK against an independent numpy chain product (the URDF chain of Appendix A.1)."""
+    q = np.random.default_rng(1).uniform(-np.pi, np.pi, (50, 6))
+    oMg = ur5_oracle.geometry_placements(q)
+
+    def rot(axis, a):
+        c, s = np.cos(a), np.sin(a)
+        return {0: np.array([[1, 0, 0], [0, c, -s], [0, s, c]]), 1: np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]]),
+                2: np.array([[c, -s, 0], [s, c, 0], [0, 0, 1]])}[axis]
+    for i in range(q.shape[0]):
+        R, t = np.eye(3), np.zeros(3)
+        for j in range(6):
+            P = ur5.joint_placement[j]
+            Rp, tp = P[:9].reshape(3, 3), P[9:]
+            t = R @ tp + t
+            R = R @ Rp @ rot(int(ur5.joint_type[j]), q[i, j])
+        g = ur5.ngeoms - 1  # tool box on wrist_3
+        Pg = ur5.geom_placement[g]
+        assert np.allclose(oMg[i, g, :9].reshape(3, 3), R @ Pg[:9].reshape(3, 3), atol=1e-13)
+        assert np.allclose(oMg[i, g, 9:], R @ Pg[9:] + t, atol=1e-13)
+
+
+def _rand_T(rng, scale=1.0):
+    q = rng.normal(size=4)
+    q /= np.linalg.norm(q)
+    x, y, z, w = q
+    R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                  [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                  [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+    return np.concatenate([R.reshape(-1), rng.uniform(-scale, scale, 3)])
+
+
+def _box_verts(h):
+    return np.array([[sx * h[0], sy * h[1], sz * h[2]] for sx in (-1, 1) for sy in (-1, 1) for sz in (-1, 1)])
+
+
+def test_gjk_vs_closed_forms(ob):
+    """GJK (via convex point sets) agrees with the closed forms on sphere/capsule cases."""
+    rng = np.random.default_rng(5)
+    for _ in range(300):
+        Ta, Tb = _rand_T(rng), _rand_T(rng)
+        ra, rb, ha, hb = rng.uniform(.05, .3, 4)
+        # capsule-capsule closed form vs GJK on 2-vertex convex cores
+        d_closed = ob.shape_distance(1, [ra, ha], Ta, 1, [rb, hb], Tb)
+        va = np.array([[0, 0, -ha], [0, 0, ha]])
+        vb = np.array([[0, 0, -hb], [0, 0, hb]])
+        d_gjk = ob.shape_distance(3, [0], Ta, 3, [0], Tb, va, vb) - ra - rb
+        if d_closed > -ra - rb + 1e-9:  # cores separated
+            assert abs(d_closed - d_gjk) <= 1e-9 * max(1.0, abs(d_closed)), (d_closed, d_gjk)
+        # sphere-box closed form vs GJK(point, box vertices)
+        hbx = rng.uniform(.05, .4, 3)
+        d_sb = ob.shape_distance(0, [ra], Ta, 2, list(hbx), Tb)
+        d_sb_gjk = ob.shape_distance(3, [0], Ta, 3, [0], Tb, np.zeros((1, 3)), _box_verts(hbx)) - ra
+        if d_sb > -ra + 1e-9:
+            assert abs(d_sb - d_sb_gjk) <= 1e-9 * max(1.0, abs(d_sb)), (d_sb, d_sb_gjk)
+        # box primitive support == box as convex hull
+        hax = rng.uniform(.05, .4, 3)
+        d_bb = ob.shape_distance(2, list(hax), Ta, 2, list(hbx), Tb)
+        d_bb_c = ob.shape_distance(3, [0], Ta, 3, [0], Tb, _box_verts(hax), _box_verts(hbx))
+        assert abs(d_bb - d_bb_c) <= 1e-9 * max(1.0, d_bb), (d_bb, d_bb_c)
+
+
+def test_gjk_box_box_vs_sampling(ob):
+    """Box-box / capsule-box distance vs brute-force optimisation (scipy) on separated cases."""
+    from scipy.optimize import minimize
+    rng = np.random.default_rng(11)
+    for _ in range(40):
+        Ta, Tb = _rand_T(rng, 0.8), _rand_T(rng, 0.8)
+        ha, hb = rng.uniform(.05, .3, 3), rng.uniform(.05, .3, 3)
+        d = ob.shape_distance(2, list(ha), Ta, 2, list(hb), Tb)
+        Ra, ta, Rb, tb = Ta[:9].reshape(3, 3), Ta[9:], Tb[:9].reshape(3, 3), Tb[9:]
+
+        def f(x):
+            pa = Ra @ (np.clip(x[:3], -1, 1) * ha) + ta
+            pb = Rb @ (np.clip(x[3:], -1, 1) * hb) + tb
+            return np.sum((pa - pb) ** 2)
+        best = min(minimize(f, rng.uniform(-1, 1, 6), bounds=[(-1, 1)] * 6, method="L-BFGS-B",
+                            options=dict(ftol=1e-16, gtol=1e-12)).fun for _ in range(6))
+        ref = np.sqrt(max(best, 0))
+        if ref > 1e-3:
+            assert abs(d - ref) < 2e-6 * max(1, ref), (d, ref)
+        else:
+            assert d < 2e-3
+
+
+# ---- model tables ---------------------------------------------------------------------------
+def test_pair_order(ur5, ur5_oracle):
+    """cPairs_ order: self pairs first, then obstacle-major / joint-major / inner object
+    (src/obstacle-user.cc:53-76,222-235); universe geometry gets no obstacle pair."""
+    a, b, m = ur5_oracle.config_pairs()
+    ns = ur5.self_pairs.shape[0]
+    assert np.array_equal(np.stack([a[:ns], b[:ns]], 1), ur5.self_pairs)
+    moving = [g for g in range(ur5.ngeoms) if ur5.geom_joint[g] != 0]
+    exp = [(g, -(o + 1)) for o in range(ur5.nobstacles) for g in sorted(moving, key=lambda g: (ur5.geom_joint[g], g))]
+    assert list(zip(a[ns:], b[ns:])) == exp
+    assert len(a) == ns + ur5.nobstacles * len(moving)
+
+
+def test_body_pairs_and_coefficients(ur5, ur5_oracle):
+    bp = ur5_oracle.body_pairs()
+    # 15 self body pairs (non-adjacent link pairs) + 8 obstacles x 6 joints with a body
+    assert len(bp["joint_a"]) == 15 + 8 * 6
+    # Initialize::doExecute swaps so that joint_a is the moving joint of the second geometry
+    assert bp["joint_a"][0] == 2 and bp["joint_b"][0] == 0
+    # obstacle pair of joint 6: chain 6->...->0, coefficient_i = cumulative length (revolute)
+    last = len(bp["joint_a"]) - 1
+    c0, c1 = bp["coef_begin"][last], bp["coef_begin"][last + 1]
+    assert list(bp["coef_joint"][c0:c1]) == [6, 5, 4, 3, 2, 1]
+    radii = ur5_oracle.body_radii()
+    dists = [np.linalg.norm(ur5.joint_placement[j - 1][9:]) for j in (6, 5, 4, 3, 2, 1)]
+    exp = radii[6] + np.concatenate([[0], np.cumsum(dists[:-1])])
+    assert np.allclose(bp["coef_value"][c0:c1], exp, rtol=1e-15)
+    # obstacle pairs have no reverse coefficients
+    assert bp["rcoef_begin"][last] == bp["rcoef_begin"][last + 1]
+
+
+# ---- the reference's invariants (tests/test-continuous-validation.cc) ---------------------
+def _edges_from(configs):
+    return configs[0::2], configs[1::2]
+
+
+@pytest.mark.parametrize("source", ["golden", "random"])
+def test_reference_invariants(pkg, ur5, ur5_oracle, golden_configs, source):
+    """I1: PathValidation::validate(q) == CollisionValidation::validate(q) (:200-202,242-244)
+       I2: Discretized(0.05) invalid => Progressive(1e-3) and Dichotomy(0) invalid (:203-205,251-253)
+       I3: forward, Discretized valid => both continuous valid is NOT guaranteed in general; the
+           reference asserts the converse direction only where it holds (:217-219): continuous
+           valid => discretized valid."""
+    o = ur5_oracle
+    cfg = golden_configs[:200] if source == "golden" else pkg.uniform_configs(ur5, 600, seed=99)
+    q1, q2 = _edges_from(cfg)
+    L = o.straight_lengths(q1, q2)
+    v, _, _ = o.validate_configs(q1)
+    zero = np.zeros(len(q1))
+    for meth, par in ((0, 0.05), (1, 1e-3), (2, 0.0)):
+        r = o.validate_edges(meth, par, q1, q1, zero)
+        assert np.array_equal(r["valid"], v), "I1 method %d" % meth
+    for rev in (False, True):
+        d = o.validate_edges(0, 0.05, q1, q2, L, reverse=rev)
+        p = o.validate_edges(1, 1e-3, q1, q2, L, reverse=rev)
+        c = o.validate_edges(2, 0.0, q1, q2, L, reverse=rev)
+        assert not np.any((d["valid"] == 0) & (p["valid"] == 1)), "I2 progressive"
+        assert not np.any((d["valid"] == 0) & (c["valid"] == 1)), "I2 dichotomy"
+        assert np.all(d["valid"][c["valid"] == 1] == 1)
+        assert np.all(d["valid"][p["valid"] == 1] == 1)
+        # valid part ends before (forward) / after (reverse) the reported collision parameter
+        bad = p["valid"] == 0
+        if rev:
+            assert np.all(p["t_last_valid"][bad] >= p["t_fail"][bad])
+        else:
+            assert np.all(p["t_last_valid"][bad] <= p["t_fail"][bad])
+
+
+def test_progressive_single_interval_property(ur5, ur5_oracle, pkg):
+    """Persistent pair order (the reference's pooled vector) vs per-edge reset: flags may differ
+    only inside the tolerance band; measured here on random edges."""
+    cfg = pkg.uniform_configs(ur5, 400, seed=5)
+    q1, q2 = _edges_from(cfg)
+    L = ur5_oracle.straight_lengths(q1, q2)
+    a = ur5_oracle.validate_edges(1, 1e-3, q1, q2, L, order_mode=0)
+    b = ur5_oracle.validate_edges(1, 1e-3, q1, q2, L, order_mode=1)
+    assert np.mean(a["valid"] != b["valid"]) < 0.02
+
+
+def test_edge_cases(ur5, ur5_oracle):
+    o = ur5_oracle
+    q = np.zeros((1, 6))
+    # zero-length edge: exactly one sample for Progressive (progressive.cc:100), two for Discretized
+    assert o.validate_edges(1, 1e-3, q, q, np.zeros(1))["samples"][0] == 1
+    assert o.validate_edges(0, 0.05, q, q, np.zeros(1))["samples"][0] == 2
+    # constructor checks
+    with pytest.raises(RuntimeError):
+        o.validate_edges(1, 0.0, q, q, np.zeros(1))
+    with pytest.raises(RuntimeError):
+        o.validate_edges(2, 1e-3, q, q, np.zeros(1))
+    # joint bounds: first violated rank
+    qq = np.array([[0, 4.0, 0, -5.0, 0, 0]])
+    v, idx, reason = o.validate_configs(qq, check_bounds=True)
+    assert v[0] == 0 and idx[0] == 1 and reason[0] == 2
+    # empty batch
+    v, _, _ = o.validate_configs(np.zeros((0, 6)))
+    assert v.shape == (0,)
+
+
+def test_nn_basic(ur5, ob, pkg):
+    o = ob.Oracle(ur5)
+    nodes = pkg.uniform_configs(ur5, 500, seed=1)
+    nodes[100] = nodes[50]  # exact duplicate: the earlier index must win (strict '<')
+    cc = (np.arange(500) % 3).astype(np.int32)
+    o.knn_append(nodes, cc)
+    w = np.array(ur5.weights)
+    qs = pkg.uniform_configs(ur5, 20, seed=2)
+    qs[0] = nodes[50]
+    idx, dist = o.knn_query(qs, 1)
+    assert idx[0, 0] == 50 and dist[0, 0] == 0
+    d = np.sqrt((((nodes[None] - qs[:, None]) * w) ** 2).sum(-1))
+    assert np.array_equal(idx[:, 0], d.argmin(1))
+    idx5, dist5 = o.knn_query(qs, 5, cc=1)
+    dm = np.where(cc[None] == 1, d, np.inf)
+    assert np.array_equal(idx5[1:], np.argsort(dm, 1, kind="stable")[1:, :5])
+    assert np.allclose(dist5, np.sort(dm, 1)[:, :5], rtol=1e-14)
+    ball = o.knn_within_ball(qs[3], 1.0)
+    assert np.array_equal(ball, np.nonzero(d[3] < 1.0)[0])
