@@ -44,7 +44,7 @@ void Workspace::syncStats() {
   stats.pair_tests = h.pair_tests;
   stats.gjk_iterations = h.gjk_iterations;
   stats.edge_samples = h.edge_samples;
-  stats.iter_cap_hits = h.iter_cap_hits;
+  stats.iter_cap_hits = h.iter_cap_hits;  // (second-pass overflows are counted here by the kernel)
 }
 
 template <typename F>
@@ -89,6 +89,14 @@ int hppb200_device_count(void) {
   int n = 0;
   if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
   return n;
+}
+
+int hppb200_measure_fp64_peak(int device, double* tflops) {
+  return guarded([&] {
+    if (!tflops) throw std::invalid_argument("null argument");
+    if (hppb200_device_count() == 0) throw std::runtime_error("no CUDA device visible: the engine has no CPU fallback");
+    *tflops = measureFp64Peak(device);
+  });
 }
 
 int hppb200_model_create(const hppb200_model_desc* desc, hppb200_model** out) {

@@ -128,13 +128,16 @@ struct Workspace {
   uint32_t max_iterations = 1u << 20;
   // staging for host-pointer calls
   DeviceBuffer<double> d_q, d_q2, d_L, d_tfail, d_tlast, d_scratch;
-  DeviceBuffer<uint8_t> d_valid, d_reason;
+  DeviceBuffer<uint8_t> d_valid, d_reason, d_reason_int;
+  DeviceBuffer<uint32_t> d_list;
+  DeviceBuffer<unsigned long long> d_count;
   DeviceBuffer<int32_t> d_pair;
   DeviceBuffer<unsigned char> d_state;
   void syncStats();
 };
 
 void setLastError(const std::string& s);
+double measureFp64Peak(int device);
 
 // kernel launchers (kernels_config.cu / kernels_edges.cu), all asynchronous on ws->stream
 void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,

@@ -164,4 +164,42 @@ void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_d
   launchConfigKernel(ws, d_q, n, 0, MODE_DISTANCES, nullptr, nullptr, nullptr, d_dist);
 }
 
+
+// FP64 FMA peak: 8 independent DFMA chains per thread, 4096 steps, enough CTAs to fill the chip.
+__global__ void __launch_bounds__(256) fp64PeakKernel(double* out, double a, double b, int iters) {
+  double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;
+  for (int i = 0; i < iters; ++i) {
+    x0 = fma(x0, a, b); x1 = fma(x1, a, b); x2 = fma(x2, a, b); x3 = fma(x3, a, b);
+    x4 = fma(x4, a, b); x5 = fma(x5, a, b); x6 = fma(x6, a, b); x7 = fma(x7, a, b);
+  }
+  out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+}
+
+double measureFp64Peak(int device) {
+  HPPB200_CUDA_CHECK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  HPPB200_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+  const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 1 << 14;
+  double* out = nullptr;
+  HPPB200_CUDA_CHECK(cudaMalloc((void**)&out, (size_t)blocks * threads * sizeof(double)));
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  double best = 0;
+  for (int rep = 0; rep < 6; ++rep) {
+    cudaEventRecord(e0);
+    fp64PeakKernel<<<blocks, threads>>>(out, 0.999999, 1e-7, iters);
+    cudaEventRecord(e1);
+    HPPB200_CUDA_CHECK(cudaEventSynchronize(e1));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    const double flops = 2.0 * 8 * (double)iters * blocks * threads;
+    if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  return best;
+}
+
 }  // namespace hppb200

@@ -56,6 +56,8 @@ struct EdgeArgs {
   int32_t* pair;
   uint8_t* reason;
   unsigned long long* counter;  // next edge to hand out
+  const uint32_t* edge_list;    // optional indirection (second pass over overflowed edges)
+  int overflow_reason;          // reason written when an interval list overflows
 };
 
 // Sorted disjoint closed-interval list with capacity cap, SoA-strided.  Same observable
@@ -194,7 +196,7 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
         b = __shfl_sync(m, b, leader);
         const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
         if (idx >= A.n) { phase = PH_RETIRED; break; }
-        e = (size_t)idx;
+        e = A.edge_list ? (size_t)A.edge_list[idx] : (size_t)idx;
         q1 = A.q1 + e * (size_t)mv.nq;
         q2 = A.q2 + e * (size_t)mv.nq;
         L = A.L[e];
@@ -286,8 +288,8 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
             else finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
           } else {
             if (!ivUnion(S.sublo + slot, S.subhi + slot, NS, subCnt, S.KS, ilo, ihi)) {
-              ++overflows;
-              finishEdge(false, HPPB200_REASON_ITER_CAP, t, reverse ? S.sublo[(size_t)(subCnt - 1) * NS + slot] : S.subhi[slot], -1);
+              if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
+              finishEdge(false, A.overflow_reason, t, reverse ? S.sublo[(size_t)(subCnt - 1) * NS + slot] : S.subhi[slot], -1);
               continue;
             }
             if (ivContains(S.sublo + slot, S.subhi + slot, NS, subCnt, 0.0, L)) {
@@ -340,10 +342,10 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
           const size_t o = ((size_t)curId * S.K) * NS + slot;
           int c = S.ivcnt[curId * NS + slot];
           if (!ivUnion(S.ivlo + o, S.ivhi + o, NS, c, S.K, a, b)) {
-            ++overflows;
+            if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
             double tl = lastValid;
             if (DICH) tl = reverse ? S.sublo[(size_t)(subCnt - 1) * NS + slot] : S.subhi[slot];
-            finishEdge(false, HPPB200_REASON_ITER_CAP, t, tl, -1);
+            finishEdge(false, A.overflow_reason, t, tl, -1);
           } else {
             S.ivcnt[curId * NS + slot] = (uint8_t)c;
             if (ivContains(S.ivlo + o, S.ivhi + o, NS, c, 0.0, L)) S.ivvalid[curId * NS + slot] = 1;
@@ -405,8 +407,16 @@ void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2
   ws->stats.kernel_launches += 1;
 }
 
+constexpr int REASON_OVERFLOW_INTERNAL = 4;  // never leaves the library
+
+__global__ void collectOverflowKernel(const uint8_t* __restrict__ reason, size_t n, uint32_t* __restrict__ list,
+                                      unsigned long long* __restrict__ count) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n && reason[i] == REASON_OVERFLOW_INTERNAL) list[atomicAdd(count, 1ull)] = (uint32_t)i;
+}
+
 template <int METHOD>
-static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS) {
+static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS, size_t maxSlots) {
   const bool tree = modelIsTree(ws->model);
   auto kern = tree ? edgeWalkerKernel<METHOD, true> : edgeWalkerKernel<METHOD, false>;
   const ModelView& mv = ws->view;
@@ -418,6 +428,7 @@ static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS) {
   size_t grid = (size_t)ws->num_sms * perSM;
   const size_t needed = (A0.n + EDGE_THREADS - 1) / EDGE_THREADS;
   if (grid > needed) grid = needed;
+  if (grid * EDGE_THREADS > maxSlots) grid = std::max<size_t>(1, maxSlots / EDGE_THREADS);
   const size_t NS = grid * EDGE_THREADS;
 
   // carve the scratch (8-byte aligned fields)
@@ -450,6 +461,7 @@ static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS) {
   S.KS = KS;
   EdgeArgs A = A0;
   A.counter = (unsigned long long*)(base + o_counter);
+
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.counter, 0, sizeof(unsigned long long), ws->stream));
   kern<<<(unsigned)grid, EDGE_THREADS, smemBytes, ws->stream>>>(mv, A, S, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
@@ -460,17 +472,45 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
                          const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                          int32_t* d_pair, uint8_t* d_reason) {
   if (n == 0) return;
+  if (n > 0xffffffffull) throw std::invalid_argument("at most 2^32-1 edges per call");
   if (ws->view.nbodypairs > 65535) throw std::runtime_error("too many body pairs");
+  if (!d_reason) {  // the overflow protocol needs a reason array
+    ws->d_reason_int.reserve(n);
+    d_reason = ws->d_reason_int.p;
+  }
   EdgeArgs A{};
   A.q1 = d_q1; A.q2 = d_q2; A.L = d_L; A.n = n; A.flags = flags; A.reverse = reverse; A.param = param;
   A.max_iter = ws->max_iterations;
   A.valid = d_valid; A.t_fail = d_tfail; A.t_last = d_tlast; A.pair = d_pair; A.reason = d_reason;
+  A.edge_list = nullptr;
+  A.overflow_reason = REASON_OVERFLOW_INTERNAL;
   // Interval-set capacities.  Progressive provably keeps ONE connected validated interval per
-  // body pair; Dichotomy keeps short lists.  Overflow is detected, counted in
-  // stats.overflow and reported as HPPB200_REASON_ITER_CAP, never silently dropped.
-  if (method == HPPB200_METHOD_DISCRETIZED) launchEdgeWalker<HPPB200_METHOD_DISCRETIZED>(ws, A, 1, 1);
-  else if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, A, 2, 1);
-  else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, A, 12, 96);
+  // body pair; Dichotomy keeps short lists.  An edge whose lists overflow the
+  // fast-path capacity is re-run ON THE DEVICE with large lists (second pass); if even that
+  // overflows it is reported as HPPB200_REASON_ITER_CAP, never silently accepted.
+  DeviceStats before, after;
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
+  const size_t allSlots = ~size_t(0);
+  if (method == HPPB200_METHOD_DISCRETIZED) { launchEdgeWalker<HPPB200_METHOD_DISCRETIZED>(ws, A, 1, 1, allSlots); return; }
+  if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, A, 2, 1, allSlots);
+  else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, A, 12, 96, allSlots);
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&after, ws->d_stats, sizeof(after), cudaMemcpyDeviceToHost, ws->stream));
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  const unsigned long long nover = after.overflow - before.overflow;
+  if (nover == 0) return;
+  // second pass: gather the overflowed edges and walk them with large interval lists
+  ws->d_list.reserve(nover + 1);
+  ws->d_count.reserve(1);
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(ws->d_count.p, 0, sizeof(unsigned long long), ws->stream));
+  collectOverflowKernel<<<(unsigned)((n + 255) / 256), 256, 0, ws->stream>>>(d_reason, n, ws->d_list.p, ws->d_count.p);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 1;
+  A.edge_list = ws->d_list.p;
+  A.n = (size_t)nover;
+  A.overflow_reason = HPPB200_REASON_ITER_CAP;
+  const size_t slots2 = 2048;  // 255-entry lists: ~4 KB per body pair per slot
+  if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, A, 255, 1, slots2);
+  else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, A, 255, 2048, slots2);
 }
 
 }  // namespace hppb200

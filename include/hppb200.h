@@ -163,6 +163,9 @@ typedef struct hppb200_stats {
 int hppb200_abi_version(void);
 const char* hppb200_last_error(void); /* thread-local message of the last failure */
 int hppb200_device_count(void);       /* 0 when no CUDA device is visible        */
+/* Measured FP64 FMA throughput of `device` in TFLOP/s (independent DFMA chains, CUDA events):
+   the roofline denominator for the narrow-phase kernels. */
+int hppb200_measure_fp64_peak(int device, double* tflops);
 
 /* ---- model ------------------------------------------------------------- */
 int hppb200_model_create(const hppb200_model_desc* desc, hppb200_model** out);

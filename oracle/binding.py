@@ -145,9 +145,10 @@ class Oracle:
         return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, samples=samples)
 
     def counters(self):
-        c = np.zeros(4, np.uint64)
+        c = np.zeros(5, np.uint64)
         lib().oracle_get_counters(self.h, _p(c, u64p))
-        return dict(gjk_calls=int(c[0]), gjk_iterations=int(c[1]), pair_evals=int(c[2]), samples=int(c[3]))
+        return dict(gjk_calls=int(c[0]), gjk_iterations=int(c[1]), pair_evals=int(c[2]), samples=int(c[3]),
+                    closed_form_calls=int(c[4]))
 
     # nearest neighbour
     def knn_append(self, q, cc=None):

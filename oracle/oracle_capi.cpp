@@ -116,9 +116,9 @@ int oracle_validate_configs(OracleHandle* h, const double* q, size_t n, uint32_t
                             int32_t* first_pair, uint8_t* reason, int nthreads) {
   const Device& d = *h->dev;
   ConfigValidations cv(d, flags & HPPB200_CHECK_JOINT_BOUNDS);
-  uint64_t calls = 0, iters = 0;
+  uint64_t calls = 0, iters = 0, closed = 0;
   if (nthreads <= 0) nthreads = omp_get_max_threads();
-#pragma omp parallel for schedule(dynamic, 256) num_threads(nthreads) reduction(+ : calls, iters)
+#pragma omp parallel for schedule(dynamic, 256) num_threads(nthreads) reduction(+ : calls, iters, closed)
   for (long i = 0; i < (long)n; ++i) {
     ConfigReport rep;
     GjkStats st;
@@ -126,9 +126,9 @@ int oracle_validate_configs(OracleHandle* h, const double* q, size_t n, uint32_t
     valid[i] = ok ? 1 : 0;
     if (first_pair) first_pair[i] = rep.index;
     if (reason) reason[i] = (uint8_t)rep.reason;
-    calls += st.calls; iters += st.iterations;
+    calls += st.calls; iters += st.iterations; closed += st.closed;
   }
-  h->stats.calls += calls; h->stats.iterations += iters;
+  h->stats.calls += calls; h->stats.iterations += iters; h->stats.closed += closed;
   return 0;
 }
 
@@ -180,8 +180,8 @@ int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse
   return err;
 }
 
-void oracle_get_counters(OracleHandle* h, uint64_t* out4) {
-  out4[0] = h->stats.calls; out4[1] = h->stats.iterations; out4[2] = h->pairEvals; out4[3] = h->samples;
+void oracle_get_counters(OracleHandle* h, uint64_t* out5) {
+  out5[0] = h->stats.calls; out5[1] = h->stats.iterations; out5[2] = h->pairEvals; out5[3] = h->samples; out5[4] = h->stats.closed;
 }
 
 // ---- intervals (pinned against oracle/_ref) ----------------------------------------

@@ -37,7 +37,7 @@ constexpr double kGjkEpsAbs2 = 1e-28;          // |v|^2 below this = cores inter
 constexpr int kGjkMaxIter = 64;
 
 struct GjkStats {
-  uint64_t calls = 0, iterations = 0, cap_hits = 0;
+  uint64_t calls = 0, iterations = 0, cap_hits = 0, closed = 0;
 };
 
 // Support point of the core shape in its own frame, direction d.
@@ -219,6 +219,7 @@ inline double segmentSegmentDist2(const Vec3& p1, const Vec3& q1, const Vec3& p2
 // Signed distance of two shapes given world placements (no margin).
 inline double shapeDistance(const Shape& A, const SE3& TA, const Shape& B, const SE3& TB, GjkStats* st) {
   if (A.type > B.type) return shapeDistance(B, TB, A, TA, st);
+  if (st && !(B.type > CAPSULE && !(A.type == SPHERE && B.type == BOX))) st->closed++;
   if (A.type == SPHERE && B.type == SPHERE) {
     Vec3 d = TA.t - TB.t;
     return std::sqrt(dot(d, d)) - A.p[0] - B.p[0];
