@@ -1,0 +1,359 @@
+#!/usr/bin/env python3
+"""Headline benchmark: validated configs/sec (+ edges/sec) on UR5 + 8 box obstacles.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload at N=1 (BASELINE.json configs[1]): 1 M uniform random UR5 configurations through
+CollisionValidation (FK + narrow phase) per step, synthetic inputs from the counter-based RNG
+(seed 12345).  N>1 (torchrun, one rank per GPU): every rank validates its own 1 M-configuration
+shard (weak scaling) and the validity masks are all-gathered over NCCL — the only collective on
+the path.  One JSON line on rank 0 (contract in the task statement):
+  value      whole-job configs/s, inputs resident in HBM, CUDA events on the launching stream
+  e2e        same metric through the C ABI with pinned HOST buffers (H2D + D2H inside the timing)
+  roofline   FP64 pipe (the kernel is compute bound: 53 algorithmic bytes vs ~5e4 flops per
+             configuration); achieved = oracle-counted algorithmic flops / kernel time, peak =
+             DFMA peak measured live by hppb200_measure_fp64_peak; the HBM view is reported beside it
+  cpu_baseline  the oracle (CPU restatement of the reference algorithm) on a bounded sample
+  edges      secondary metric: Progressive(1e-3) StraightPath edges/s on the same scene
+`--impl reference` times the reference algorithm's CPU implementation (oracle port: the reference
+binary cannot be built here) on all host threads.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_CONFIGS = 1 << 20          # configurations per GPU per step (BASELINE configs[1])
+N_EDGES = 1 << 17            # edges per GPU for the secondary metric
+SEED = 12345
+MODEL = "ur5_boxes8.json"
+# Algorithmic flop model (FMA = 2): FK = 126*njoints + 63*ngeoms + 40*njoints (sincos);
+# closed-form pair ~110; GJK call = 70 (relative placement + sqrt) + 110 per iteration.
+FLOPS_FK = 126 * 6 + 63 * 8 + 40 * 6
+FLOPS_CLOSED = 110
+FLOPS_GJK_CALL = 70
+FLOPS_GJK_ITER = 110
+BYTES_PER_CONFIG = 48 + 1 + 4  # q in, flag + first-pair index out
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-edges", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows = []
+        self.proc = None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for ts, r in self.rows if t0 <= ts <= t1 + 0.2] or [r for _, r in self.rows]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[3 + k].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
+                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows)}
+
+
+def oracle_counts(orc, q):
+    """Algorithmic work of the REFERENCE algorithm (sequential pair loop with early exit) on q."""
+    c0 = orc.counters()
+    orc.validate_configs(q)
+    c1 = orc.counters()
+    n = q.shape[0]
+    gj = c1["gjk_calls"] - c0["gjk_calls"]
+    it = c1["gjk_iterations"] - c0["gjk_iterations"]
+    cl = c1["closed_form_calls"] - c0["closed_form_calls"]
+    flops = n * FLOPS_FK + cl * FLOPS_CLOSED + gj * FLOPS_GJK_CALL + it * FLOPS_GJK_ITER
+    return dict(flops_per_config=flops / n, gjk_calls_per_config=gj / n, gjk_iters_per_config=it / n,
+                closed_per_config=cl / n)
+
+
+def cpu_rate_configs(orc, desc, mio, threads, budget_s=12.0):
+    """oracle configs/s on a bounded sample of the same workload (first configurations of rank 0's batch)."""
+    q = mio.uniform_configs(desc, 20000, seed=SEED)
+    t = time.perf_counter()
+    orc.validate_configs(q, nthreads=threads)
+    rate = 20000 / (time.perf_counter() - t)
+    n = int(min(N_CONFIGS, max(20000, rate * budget_s)))
+    q = mio.uniform_configs(desc, n, seed=SEED)
+    t = time.perf_counter()
+    orc.validate_configs(q, nthreads=threads)
+    dt = time.perf_counter() - t
+    return n / dt, n, dt
+
+
+def cpu_rate_edges(orc, q1, q2, L, threads, budget_s=10.0):
+    n0 = min(2000, len(L))
+    t = time.perf_counter()
+    orc.validate_edges(1, 1e-3, q1[:n0], q2[:n0], L[:n0], nthreads=threads)
+    rate = n0 / (time.perf_counter() - t)
+    n = int(min(len(L), max(n0, rate * budget_s)))
+    t = time.perf_counter()
+    orc.validate_edges(1, 1e-3, q1[:n], q2[:n], L[:n], nthreads=threads)
+    dt = time.perf_counter() - t
+    return n / dt, n, dt
+
+
+def run_reference(args):
+    """The reference algorithm's own CPU path (oracle port), all host threads, rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import __graft_entry__ as ge
+    pkg = ge.load()          # model_io only; no CUDA call is made on this arm
+    from oracle import binding as ob
+    desc = pkg.ModelDescription.load(MODEL)
+    orc = ob.Oracle(desc)
+    threads = os.cpu_count() or 1
+    per_step = max(1.0, min(10.0, 150.0 / max(1, args.steps + args.warmup)))
+    q = pkg.uniform_configs(desc, 20000, seed=SEED)
+    t = time.perf_counter()
+    orc.validate_configs(q, nthreads=threads)
+    rate = 20000 / (time.perf_counter() - t)
+    n = int(min(N_CONFIGS, max(20000, rate * per_step)))
+    q = pkg.uniform_configs(desc, n, seed=SEED)
+    for _ in range(args.warmup):
+        orc.validate_configs(q, nthreads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        orc.validate_configs(q, nthreads=threads)
+    dt = time.perf_counter() - t0
+    value = n * args.steps / dt
+    sample = "first %d of the %d configurations of rank 0's step batch (seed %d), every step" % (n, N_CONFIGS, SEED)
+    line = {
+        "impl": "reference", "metric": "validated configs/sec", "value": value, "unit": "configs/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "UR5 + 8 boxes: uniform random configurations through CollisionValidation "
+                               "(FK + narrow phase), CPU reference algorithm", "model": MODEL,
+                   "configs_per_step": n, "seed": SEED},
+        "cpu_baseline": {"value": value, "unit": "configs/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "configs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import __graft_entry__ as ge
+    pkg = ge.load()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    desc = pkg.ModelDescription.load(MODEL)
+    model = pkg.Model(desc)
+    ws = pkg.Workspace(model, local_rank)
+    stream = torch.cuda.current_stream()
+    ws.set_stream(stream.cuda_stream)
+    FLAGS_DEV = pkg.DEVICE_POINTERS
+    n, nq = N_CONFIGS, model.nq
+
+    # this rank's shard: configurations [rank*n, (rank+1)*n) of the global synthetic stream
+    q_host = torch.from_numpy(pkg.uniform_configs(desc, n, seed=SEED, offset=rank * n)).pin_memory()
+    q_dev = q_host.to(dev, non_blocking=False)
+    valid_d = torch.empty(n, dtype=torch.uint8, device=dev)
+    first_d = torch.empty(n, dtype=torch.int32, device=dev)
+    reason_d = torch.empty(n, dtype=torch.uint8, device=dev)
+    valid_all = torch.empty(n * world, dtype=torch.uint8, device=dev) if world > 1 else None
+    valid_h = torch.empty(n, dtype=torch.uint8).pin_memory()
+    first_h = torch.empty(n, dtype=torch.int32).pin_memory()
+    reason_h = torch.empty(n, dtype=torch.uint8).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def step_device():
+        ws.validate_configs_ptr(q_dev.data_ptr(), n, valid_d.data_ptr(), first_d.data_ptr(), reason_d.data_ptr(), FLAGS_DEV)
+        if world > 1:  # the path's only exchange: gather of the validity masks (1 B per configuration)
+            dist.all_gather_into_tensor(valid_all, valid_d)
+
+    def step_e2e():
+        ws.validate_configs_ptr(q_host.data_ptr(), n, valid_h.data_ptr(), first_h.data_ptr(), reason_h.data_ptr(), 0)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        evs = []
+        w0 = time.time()
+        for _ in range(steps):
+            flush.zero_()  # evict inputs/outputs from L2 between timed iterations (not timed)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            fn()
+            e1.record(stream)
+            evs.append((e0, e1))
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        w1 = time.time()
+        ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), w0, w1
+
+    st0 = ws.stats()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    total_ms, w0, w1 = timed(step_device, args.steps, args.warmup)
+    clocks = sampler.stop(w0, w1) if sampler else None
+    st1 = ws.stats()
+    kernel_ms = st1["last_kernel_ms"]  # device time of the last validate call (events inside the C ABI)
+    launches = st1["kernel_launches"] - st0["kernel_launches"] - args.warmup  # kernels inside the timed region
+    e2e_ms, _, _ = timed(step_e2e, args.steps, max(3, args.warmup))
+    value = world * n * args.steps / (total_ms * 1e-3)
+    e2e_value = world * n * args.steps / (e2e_ms * 1e-3)
+    # identical results on both paths
+    assert torch.equal(valid_h, valid_d.cpu()) and torch.equal(first_h, first_d.cpu())
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0: roofline, CPU baseline, secondary edge metric -------------------------------------
+    from oracle import binding as ob
+    orc = ob.Oracle(desc)
+    threads = os.cpu_count() or 1
+    sub = q_host.numpy()[:50000]
+    work = oracle_counts(orc, sub)
+    ov, op, _ = orc.validate_configs(sub)
+    parity_ok = bool(np.array_equal(ov, valid_h.numpy()[:50000]) and np.array_equal(op, first_h.numpy()[:50000]))
+    peak = pkg.measure_fp64_peak(local_rank)
+    per_launch_s = (total_ms * 1e-3) / args.steps if world == 1 else kernel_ms * 1e-3
+    achieved = work["flops_per_config"] * n / per_launch_s / 1e12
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    roofline = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "traffic": None, "peak_source": "hppb200_measure_fp64_peak (DFMA chains, measured live)",
+                "kernel": "validateConfigsKernel", "algorithmic_flops_per_config": work["flops_per_config"],
+                "hbm": {"achieved": BYTES_PER_CONFIG * n / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                        "frac": BYTES_PER_CONFIG * n / per_launch_s / 1e9 / hbm_peak,
+                        "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+                "device_pair_tests_per_config": (st1["pair_tests"] - st0["pair_tests"]) / (n * (args.steps + args.warmup)),
+                "reference_pair_tests_per_config": work["gjk_calls_per_config"] + work["closed_per_config"]}
+    cpu = None
+    if not args.no_cpu:
+        rate, ns, dt = cpu_rate_configs(orc, desc, pkg, threads)
+        cpu = {"value": rate, "unit": "configs/s", "cores": threads, "kind": "port",
+               "sample": "first %d of the %d configurations of the step batch, %.1f s" % (ns, n, dt)}
+    edges = None
+    if not args.no_edges:
+        ne = N_EDGES
+        cfg = pkg.uniform_configs(desc, 2 * ne, seed=SEED + 1, offset=0)
+        e1h = torch.from_numpy(np.ascontiguousarray(cfg[0::2])).pin_memory()
+        e2h = torch.from_numpy(np.ascontiguousarray(cfg[1::2])).pin_memory()
+        L_h = torch.from_numpy(ws.straight_lengths(e1h.numpy(), e2h.numpy())).pin_memory()
+        e1d, e2d, Ld = e1h.to(dev), e2h.to(dev), L_h.to(dev)
+        ev_d = torch.empty(ne, dtype=torch.uint8, device=dev)
+        tf_d = torch.empty(ne, dtype=torch.float64, device=dev)
+        tl_d = torch.empty(ne, dtype=torch.float64, device=dev)
+        pr_d = torch.empty(ne, dtype=torch.int32, device=dev)
+        rs_d = torch.empty(ne, dtype=torch.uint8, device=dev)
+        ev_h = torch.empty(ne, dtype=torch.uint8).pin_memory()
+        tf_h = torch.empty(ne, dtype=torch.float64).pin_memory()
+        res = {}
+        for name, meth, par in (("progressive", pkg.METHOD_PROGRESSIVE, 1e-3), ("discretized", pkg.METHOD_DISCRETIZED, 0.05),
+                                ("dichotomy", pkg.METHOD_DICHOTOMY, 0.0)):
+            def dev_call():
+                ws.validate_edges_ptr(meth, par, False, e1d.data_ptr(), e2d.data_ptr(), Ld.data_ptr(), ne, ev_d.data_ptr(),
+                                      tf_d.data_ptr(), tl_d.data_ptr(), pr_d.data_ptr(), rs_d.data_ptr(), FLAGS_DEV)
+
+            def host_call():
+                ws.validate_edges_ptr(meth, par, False, e1h.data_ptr(), e2h.data_ptr(), L_h.data_ptr(), ne, ev_h.data_ptr(),
+                                      tf_h.data_ptr(), 0, 0, 0, 0)
+            s0 = ws.stats()
+            ms_d, _, _ = timed(dev_call, 3, 1)
+            s1 = ws.stats()
+            ms_h, _, _ = timed(host_call, 3, 1)
+            res[name] = {"value": ne * 3 / (ms_d * 1e-3), "e2e": ne * 3 / (ms_h * 1e-3), "unit": "edges/s", "n_edges": ne,
+                         "param": par, "valid_frac": float(ev_h.numpy().mean()),
+                         "samples_per_edge": (s1["edge_samples"] - s0["edge_samples"]) / (4 * ne),
+                         "pair_tests_per_edge": (s1["pair_tests"] - s0["pair_tests"]) / (4 * ne)}
+        if not args.no_cpu:
+            rate, ns, dt = cpu_rate_edges(orc, e1h.numpy(), e2h.numpy(), L_h.numpy(), threads)
+            res["progressive"]["cpu_baseline"] = {"value": rate, "unit": "edges/s", "cores": threads, "kind": "port",
+                                                  "sample": "first %d of the %d edges, %.1f s" % (ns, ne, dt)}
+        edges = res
+
+    line = {
+        "metric": "validated configs/sec", "value": value, "unit": "configs/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "UR5 + 8 boxes: 1M uniform random configurations through CollisionValidation "
+                               "(FK + narrow phase) per GPU per step (BASELINE configs[1])",
+                   "model": MODEL, "configs_per_gpu_per_step": n, "seed": SEED, "pairs": int(len(model.config_pairs()[0])),
+                   "l2": "flushed between timed steps (256 MiB memset, untimed)",
+                   "collective": "all_gather of uint8 validity masks (NCCL)" if world > 1 else "none"},
+        "e2e": {"value": e2e_value, "unit": "configs/s", "h2d_bytes_per_step": n * nq * 8, "d2h_bytes_per_step": n * 6,
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": roofline,
+        "cpu_baseline": cpu,
+        "edges": edges,
+        "parity_vs_oracle_50k": parity_ok,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

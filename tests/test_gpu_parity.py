@@ -135,15 +135,21 @@ def test_edge_zero_length_and_endpoints(pkg, eng, ur5, ur5_oracle):
 
 
 def test_edge_invariants_on_gpu(pkg, eng, ur5, ur5_oracle):
-    """I2: Discretized(0.05) invalid => Progressive(1e-3) and Dichotomy(0) invalid."""
+    """I2: Discretized(0.05) invalid => Dichotomy(0) invalid, strictly.  Progressive(tol > 0)
+    tolerates penetrations up to its tolerance, so a discretized sample may catch a graze it
+    accepts: rare, and then the GPU must still agree with the oracle."""
     _, ws = eng
     q1, q2, L = _edges(pkg, ur5, ur5_oracle, 20000, 51)
     for rev in (False, True):
         d = ws.validate_edges(0, 0.05, q1, q2, L, reverse=rev)["valid"]
         p = ws.validate_edges(1, 1e-3, q1, q2, L, reverse=rev)["valid"]
         c = ws.validate_edges(2, 0.0, q1, q2, L, reverse=rev)["valid"]
-        assert not np.any((d == 0) & (p == 1))
         assert not np.any((d == 0) & (c == 1))
+        odd = np.nonzero((d == 0) & (p == 1))[0]
+        assert len(odd) < 0.002 * len(L)
+        if len(odd):
+            e = ur5_oracle.validate_edges(1, 1e-3, q1[odd], q2[odd], L[odd], reverse=rev)
+            assert np.all(e["valid"] == 1)
 
 
 def test_edge_iteration_cap_is_flagged(pkg, eng, ur5, ur5_oracle):
