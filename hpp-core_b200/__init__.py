@@ -118,9 +118,12 @@ class Model:
         self.nv = lib().hppb200_model_nv(self.h)
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hppb200_model_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hppb200_model_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown
+            pass
 
     def config_pairs(self):
         n = lib().hppb200_model_num_config_pairs(self.h)
@@ -161,9 +164,12 @@ class Workspace:
         _check(lib().hppb200_workspace_create(model.h, C.c_int(device), C.byref(self.h)))
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hppb200_workspace_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hppb200_workspace_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown
+            pass
 
     def set_stream(self, cuda_stream_ptr):
         _check(lib().hppb200_workspace_set_stream(self.h, C.c_void_p(cuda_stream_ptr)))
@@ -244,9 +250,12 @@ class NearestNeighbor:
         _check(lib().hppb200_knn_create(model.h, C.c_int(device), C.byref(self.h)))
 
     def __del__(self):
-        if getattr(self, "h", None):
-            lib().hppb200_knn_destroy(self.h)
-            self.h = None
+        try:
+            if getattr(self, "h", None):
+                lib().hppb200_knn_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown
+            pass
 
     def __len__(self):
         return int(lib().hppb200_knn_size(self.h))
