@@ -24,20 +24,32 @@ struct DevJoint {
   int32_t parent, type, idx_q, idx_v;
   double P[12];
 };
+// Bounding core used by the conservative cull test: a point (or, for a
+// capsule, its axis segment) at local offset bc, inflated by br.  br is rounded UP.
+struct DevBound {
+  double bc[3];
+  double br;
+};
 struct DevGeom {
   int32_t joint, pad;
   double P[12];
   DevShapeH shape;
+  DevBound bound;
 };
 struct DevObstacle {
   double P[12];
   DevShapeH shape;
+  DevBound bound;
+  double wc[3];  // world position of the bounding core (R bc + t), fixed
+  double pad;
 };
 // a/b: >= 0 robot geometry index, < 0 obstacle -(k+1); already canonically ordered
 // (shape type of a <= shape type of b) so that the kernel can dispatch on `kind` directly.
 struct DevPair {
-  int32_t a, b, kind, pad;
+  int32_t a, b, kind;
+  int32_t bound;   // 0: point-point, 1: segment(a)-point(b) cull test
   double margin;
+  double cull2;    // squared core distance above which the pair provably does not collide
 };
 struct DevBodyPair {
   int32_t joint_a, joint_b;
@@ -131,7 +143,9 @@ struct Workspace {
   DeviceBuffer<uint8_t> d_valid, d_reason, d_reason_int;
   DeviceBuffer<uint32_t> d_list;
   DeviceBuffer<unsigned long long> d_count;
-  DeviceBuffer<int32_t> d_pair;
+  DeviceBuffer<int32_t> d_pair, d_pair_int;
+  DeviceBuffer<unsigned long long> d_jobs;
+  unsigned long long last_jobs = 0;
   DeviceBuffer<unsigned char> d_state;
   void syncStats();
 };

@@ -136,6 +136,263 @@ validateConfigsKernel(ModelView mv, ConfigSmemLayout L, const double* __restrict
   }
 }
 
+// =====================================================================================
+// Production path for MODE_VALIDATE: two kernels.
+//
+//  K1 configPassKernel — one THREAD per configuration, uniform work:
+//       joint bounds, FK in registers (sparse joint transform), geometry placements written
+//       once to a global scratch (SoA over configurations, coalesced; read back only by the
+//       rare GJK jobs) and, per geometry, the 6 doubles the cheap tests need (core centre +
+//       capsule axis) kept in shared memory.  Then the pair loop IN REFERENCE ORDER with the
+//       reference's early exit: closed-form kinds (sphere/capsule) are decided exactly;
+//       GJK kinds first get a conservative cull test (squared core distance vs. inflation
+//       radii + margin + 1e-9 slack, then a box-face separating-axis bound): a culled pair
+//       provably does not collide, so flags stay identical to the reference; a pair that
+//       survives is queued as a job (configuration, pair).  ~99 % of the reference's GJK
+//       calls are culled on the UR5 + boxes workload.
+//  K2 gjkJobsKernel — one thread per surviving job, full warps of GJK; a colliding job does
+//       atomicMin on the configuration's first-hit index (unsigned: -1 = none = max).
+// The minimum colliding index over exact tests equals the reference's first hit.
+// =====================================================================================
+constexpr int K1_THREADS = 128;
+constexpr int K1_JOBS_PER_BLOCK = 4 * K1_THREADS;  // smem staging; overflow goes straight to global
+
+struct ValidateArgs {
+  const double* q;
+  size_t n;
+  uint32_t flags;
+  uint8_t* valid;
+  uint32_t* first;  // int32 viewed as unsigned (0xffffffff = -1)
+  uint8_t* reason;
+  double* oMg;             // [ngeoms*12][n] scratch
+  unsigned long long* jobs;  // (config << 32 | pair)
+  unsigned long long* njobs;
+  unsigned long long jobs_cap;
+};
+
+// Sparse pinocchio joint transform: liMi = P * M_joint(q), exploiting the zeros/ones of M.
+// Bit-identical to the dense product up to the sign of zeros.
+__device__ __forceinline__ T3 jointLocalSparse(const DevJoint& J, double qv) {
+  T3 P = load12(J.P);
+  T3 R = P;
+  if (J.type <= HPPB200_JOINT_REVOLUTE_Z) {
+    double s, c;
+    sincos_portable(qv, &s, &c);
+    const double ms = -s;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const double p0 = P.r[3 * i], p1 = P.r[3 * i + 1], p2 = P.r[3 * i + 2];
+      if (J.type == HPPB200_JOINT_REVOLUTE_Z) { R.r[3 * i] = fma(p1, s, p0 * c); R.r[3 * i + 1] = fma(p1, c, p0 * ms); }
+      else if (J.type == HPPB200_JOINT_REVOLUTE_Y) { R.r[3 * i] = fma(p2, ms, p0 * c); R.r[3 * i + 2] = fma(p2, c, p0 * s); }
+      else { R.r[3 * i + 1] = fma(p2, s, p1 * c); R.r[3 * i + 2] = fma(p2, c, p1 * ms); }
+    }
+  } else {
+    const int a = J.type - HPPB200_JOINT_PRISMATIC_X;
+    // R unchanged; t = P.R[:,a] * q + P.t  (dense form: dot(row, (..q..)) + t)
+    R.t = mk(P.r[a] * qv + P.t.x, P.r[3 + a] * qv + P.t.y, P.r[6 + a] * qv + P.t.z);
+  }
+  return R;
+}
+
+__device__ __forceinline__ void pushJob(unsigned long long job, unsigned long long* sjobs, int* scount, const ValidateArgs& A) {
+  const int slot = atomicAdd(scount, 1);
+  if (slot < K1_JOBS_PER_BLOCK) { sjobs[slot] = job; return; }
+  const unsigned long long g = atomicAdd(A.njobs, 1ull);  // staging full (rare): straight to global
+  if (g < A.jobs_cap) A.jobs[g] = job;
+}
+
+template <bool TREE>
+__global__ void __launch_bounds__(K1_THREADS)
+configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* bar = (uint64_t*)smem;
+  int* scount = (int*)(smem + 8);
+  unsigned char* sblob = smem + 16;
+  double* cstore = (double*)(sblob + mv.blob_bytes);                         // [ngeoms*6][K1_THREADS]
+  unsigned long long* sjobs = (unsigned long long*)(cstore + (size_t)mv.ngeoms * 6 * K1_THREADS);
+  __shared__ unsigned long long sbase;
+  stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+  const int tid = threadIdx.x;
+  if (tid == 0) *scount = 0;
+  __syncthreads();
+  const size_t i = (size_t)blockIdx.x * K1_THREADS + tid;
+  unsigned tests = 0;
+  if (i < A.n) {
+    const double* qc = A.q + i * (size_t)mv.nq;
+    int bad = -1;
+    if (A.flags & HPPB200_CHECK_JOINT_BOUNDS) {
+      for (int k = 0; k < mv.nq && bad < 0; ++k) {
+        const double lo = T.lower[k], hi = T.upper[k];
+        if (lo > hi) continue;
+        if (qc[k] < lo || hi < qc[k]) bad = k;
+      }
+    }
+    if (bad >= 0) {
+      A.valid[i] = 0; A.first[i] = (uint32_t)bad; A.reason[i] = HPPB200_REASON_JOINT_BOUND;
+    } else {
+      // ---- FK: placements to global scratch, compact cores to shared memory ----
+      double* cs = cstore + tid;
+      auto emit = [&](int g, const T3& M) {
+        store12s(A.oMg + (size_t)g * 12 * A.n + i, A.n, M);
+        const DevGeom& G = T.geoms[g];
+        V3 c = M.t;
+        if (G.shape.type >= SH_BOX) c = rmul(M, mk(G.bound.bc[0], G.bound.bc[1], G.bound.bc[2])) + M.t;
+        cs[(g * 6 + 0) * K1_THREADS] = c.x; cs[(g * 6 + 1) * K1_THREADS] = c.y; cs[(g * 6 + 2) * K1_THREADS] = c.z;
+        cs[(g * 6 + 3) * K1_THREADS] = M.r[2]; cs[(g * 6 + 4) * K1_THREADS] = M.r[5]; cs[(g * 6 + 5) * K1_THREADS] = M.r[8];
+      };
+      for (int g = 0; g < mv.ngeoms; ++g)
+        if (T.geoms[g].joint == 0) emit(g, load12(T.geoms[g].P));
+      T3 cur = identityT();
+      for (int j = 1; j <= mv.njoints; ++j) {
+        const DevJoint& J = T.joints[j - 1];
+        T3 li = jointLocalSparse(J, qc[J.idx_q]);
+        if (J.parent == 0) cur = li;
+        else if (!TREE || J.parent == j - 1) cur = compose(cur, li);
+        else cur = compose(load12s(A.oMg + (size_t)(mv.ngeoms + J.parent - 1) * 12 * A.n + i, A.n), li);
+        if (TREE) store12s(A.oMg + (size_t)(mv.ngeoms + j - 1) * 12 * A.n + i, A.n, cur);
+        for (int g = 0; g < mv.ngeoms; ++g)
+          if (T.geoms[g].joint == j) emit(g, compose(cur, load12(T.geoms[g].P)));
+      }
+      // ---- pair loop in reference order, early exit at the first definite hit ----
+      auto core = [&](int ref, V3& c, V3& u) {
+        if (ref >= 0) {
+          c = mk(cs[(ref * 6 + 0) * K1_THREADS], cs[(ref * 6 + 1) * K1_THREADS], cs[(ref * 6 + 2) * K1_THREADS]);
+          u = mk(cs[(ref * 6 + 3) * K1_THREADS], cs[(ref * 6 + 4) * K1_THREADS], cs[(ref * 6 + 5) * K1_THREADS]);
+        } else {
+          const DevObstacle& O = T.obstacles[-(ref + 1)];
+          c = mk(O.wc[0], O.wc[1], O.wc[2]);
+          u = mk(O.P[2], O.P[5], O.P[8]);
+        }
+      };
+      int hit = -1;
+      for (int p = 0; p < mv.ncpairs; ++p) {
+        const DevPair pr = T.cpairs[p];
+        const DevShape& sa = *(const DevShape*)(pr.a >= 0 ? &T.geoms[pr.a].shape : &T.obstacles[-(pr.a + 1)].shape);
+        const DevShape& sb = *(const DevShape*)(pr.b >= 0 ? &T.geoms[pr.b].shape : &T.obstacles[-(pr.b + 1)].shape);
+        V3 ca, ua, cb, ub;
+        core(pr.a, ca, ua);
+        core(pr.b, cb, ub);
+        if (pr.kind <= PK_CAPSULE_CAPSULE) {
+          double d;
+          if (pr.kind == PK_SPHERE_SPHERE) { V3 dd = ca - cb; d = sqrt(dot(dd, dd)) - sa.p[0] - sb.p[0]; }
+          else if (pr.kind == PK_SPHERE_CAPSULE) d = sqrt(pointSegmentDist2(ca, cb, ub, sb.p[1])) - sa.p[0] - sb.p[0];
+          else {
+            V3 p1 = axpy(-sa.p[1], ua, ca), q1 = axpy(sa.p[1], ua, ca);
+            V3 p2 = axpy(-sb.p[1], ub, cb), q2 = axpy(sb.p[1], ub, cb);
+            d = sqrt(segmentSegmentDist2(p1, q1, p2, q2)) - sa.p[0] - sb.p[0];
+          }
+          ++tests;
+          if (d - pr.margin <= HPPB200_COLLISION_THRESHOLD) { hit = p; break; }
+          continue;
+        }
+        // GJK kinds: conservative cull on the bounding cores
+        double d2;
+        if (pr.bound == 1) d2 = pointSegmentDist2(cb, ca, ua, sa.p[1]);
+        else { V3 dd = ca - cb; d2 = dot(dd, dd); }
+        if (d2 > pr.cull2) continue;
+        if (pr.b < 0 && sb.type == SH_BOX) {
+          // box-face separating axes: a lower bound of the distance to the obstacle box
+          const DevObstacle& O = T.obstacles[-(pr.b + 1)];
+          const T3 TB = load12(O.P);
+          const double h = pr.bound == 1 ? sa.p[1] : 0.0;
+          const V3 e0 = rtmul(TB, axpy(-h, ua, ca) - TB.t), e1 = rtmul(TB, axpy(h, ua, ca) - TB.t);
+          const double sx = fmax(fmin(e0.x, e1.x) - sb.p[0], -fmax(e0.x, e1.x) - sb.p[0]);
+          const double sy = fmax(fmin(e0.y, e1.y) - sb.p[1], -fmax(e0.y, e1.y) - sb.p[1]);
+          const double sz = fmax(fmin(e0.z, e1.z) - sb.p[2], -fmax(e0.z, e1.z) - sb.p[2]);
+          const double ra = pr.a >= 0 ? T.geoms[pr.a].bound.br : T.obstacles[-(pr.a + 1)].bound.br;
+          if (fmax(sx, fmax(sy, sz)) - ra - pr.margin > 1e-9) continue;
+        }
+        pushJob(((unsigned long long)i << 32) | (unsigned)p, sjobs, scount, A);
+      }
+      A.valid[i] = hit < 0 ? 1 : 0;
+      A.first[i] = (uint32_t)hit;
+      A.reason[i] = hit < 0 ? HPPB200_REASON_VALID : HPPB200_REASON_COLLISION;
+    }
+  }
+  // ---- flush this block's jobs with ONE global atomic ----
+  __syncthreads();
+  const int nj = min(*scount, K1_JOBS_PER_BLOCK);
+  if (tid == 0 && nj > 0) sbase = atomicAdd(A.njobs, (unsigned long long)nj);
+  __syncthreads();
+  for (int k = tid; k < nj; k += K1_THREADS)
+    if (sbase + k < A.jobs_cap) A.jobs[sbase + k] = sjobs[k];
+  const unsigned ts = __reduce_add_sync(0xffffffffu, tests);
+  if ((tid & 31) == 0 && stats && ts) atomicAdd(&stats->pair_tests, (unsigned long long)ts);
+}
+
+__global__ void __launch_bounds__(256)
+gjkJobsKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned char* sblob = smem + 16;
+  stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+  unsigned long long total = *A.njobs;
+  if (total > A.jobs_cap) total = A.jobs_cap;
+  GjkCounters cnt = {0u, 0u, 0u};
+  unsigned tests = 0;
+  for (unsigned long long j = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; j < total;
+       j += (unsigned long long)gridDim.x * blockDim.x) {
+    const unsigned long long job = A.jobs[j];
+    const size_t i = (size_t)(job >> 32);
+    const unsigned p = (unsigned)job;
+    if (*(volatile uint32_t*)&A.first[i] < p) continue;  // a smaller colliding index is already known
+    const DevPair pr = T.cpairs[p];
+    const double d = pairLowerBound(T, pr, A.oMg + i, A.n, mv.vertices, cnt);
+    ++tests;
+    if (d <= HPPB200_COLLISION_THRESHOLD) {
+      atomicMin(&A.first[i], p);
+      A.valid[i] = 0;
+      A.reason[i] = HPPB200_REASON_COLLISION;
+    }
+  }
+  const unsigned ts = __reduce_add_sync(0xffffffffu, tests);
+  const unsigned gi = __reduce_add_sync(0xffffffffu, cnt.iterations);
+  const unsigned gc = __reduce_add_sync(0xffffffffu, cnt.cap_hits);
+  if ((threadIdx.x & 31) == 0 && stats) {
+    if (ts) atomicAdd(&stats->pair_tests, (unsigned long long)ts);
+    if (gi) atomicAdd(&stats->gjk_iterations, (unsigned long long)gi);
+    if (gc) atomicAdd(&stats->gjk_cap_hits, (unsigned long long)gc);
+  }
+}
+
+// Jobs that did not fit the queue (pathological scenes): detected on the host, which re-runs the
+// batch through the single-kernel path below (still on the device).
+static void launchValidateTwoKernel(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
+                                    int32_t* d_first, uint8_t* d_reason) {
+  const bool tree = modelIsTree(ws->model);
+  const ModelView& mv = ws->view;
+  if (n > 0xffffffffull) throw std::invalid_argument("at most 2^32-1 configurations per call");
+  if (!d_first) { ws->d_pair_int.reserve(n); d_first = ws->d_pair_int.p; }
+  if (!d_reason) { ws->d_reason_int.reserve(n); d_reason = ws->d_reason_int.p; }
+  const size_t slots = (size_t)mv.ngeoms + (tree ? mv.njoints : 0);
+  ws->d_scratch.reserve(slots * 12 * n);
+  const size_t cap = 2 * n + 4096;
+  ws->d_jobs.reserve(cap + 1);
+  ValidateArgs A{};
+  A.q = d_q; A.n = n; A.flags = flags; A.valid = d_valid; A.first = (uint32_t*)d_first; A.reason = d_reason;
+  A.oMg = ws->d_scratch.p;
+  A.njobs = ws->d_jobs.p;
+  A.jobs = ws->d_jobs.p + 1;
+  A.jobs_cap = cap;
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), ws->stream));
+  const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
+                       (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
+  if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
+  auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+  k1<<<(unsigned)((n + K1_THREADS - 1) / K1_THREADS), K1_THREADS, smem1, ws->stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  const size_t smem2 = 16 + mv.blob_bytes;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  size_t grid2 = (size_t)ws->num_sms * 4;
+  gjkJobsKernel<<<(unsigned)grid2, 256, smem2, ws->stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 2;
+  ws->stats.configs += n;
+}
+
 static void launchConfigKernel(Workspace* ws, const double* d_q, size_t n, uint32_t flags, int mode, uint8_t* d_valid,
                                int32_t* d_first, uint8_t* d_reason, double* d_aux) {
   if (n == 0) return;
@@ -155,7 +412,15 @@ static void launchConfigKernel(Workspace* ws, const double* d_q, size_t n, uint3
 
 void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
                            int32_t* d_first, uint8_t* d_reason) {
-  launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
+  if (n == 0) return;
+  launchValidateTwoKernel(ws, d_q, n, flags, d_valid, d_first, d_reason);
+  // queue overflow (more than ~2 surviving GJK pairs per configuration on average): fall back to the
+  // single fused kernel, which needs no queue.  Checked after the fact; costs one 8-byte read.
+  unsigned long long njobs = 0;
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&njobs, ws->d_jobs.p, sizeof(njobs), cudaMemcpyDeviceToHost, ws->stream));
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  ws->last_jobs = njobs;
+  if (njobs > 2 * n + 4096) launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
 }
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg) {
   launchConfigKernel(ws, d_q, n, 0, MODE_PLACEMENTS, nullptr, nullptr, nullptr, d_oMg);

@@ -35,6 +35,33 @@ static DevShapeH makeShape(int type, const double* p, int vb, int vc) {
   return s;
 }
 
+static const double kCullSlack = 1e-9;  // >> FP64 rounding of the bound, << anything physical
+
+static DevBound makeBound(const DevShapeH& s, const std::vector<double>& verts) {
+  DevBound b{};
+  const double up = 1.0 + 1e-12;  // round radii up
+  if (s.type == HPPB200_SHAPE_SPHERE || s.type == HPPB200_SHAPE_CAPSULE) b.br = s.p[0];
+  else if (s.type == HPPB200_SHAPE_BOX) b.br = std::sqrt(s.p[0] * s.p[0] + s.p[1] * s.p[1] + s.p[2] * s.p[2]) * up;
+  else {
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < s.vcount; ++i)
+      for (int k = 0; k < 3; ++k) {
+        double c = verts[3 * (size_t)(s.vbegin + i) + k];
+        lo[k] = std::min(lo[k], c);
+        hi[k] = std::max(hi[k], c);
+      }
+    for (int k = 0; k < 3; ++k) b.bc[k] = s.vcount ? 0.5 * (lo[k] + hi[k]) : 0.0;
+    double r2 = 0;
+    for (int i = 0; i < s.vcount; ++i) {
+      double d2 = 0;
+      for (int k = 0; k < 3; ++k) { double d = verts[3 * (size_t)(s.vbegin + i) + k] - b.bc[k]; d2 += d * d; }
+      r2 = std::max(r2, d2);
+    }
+    b.br = std::sqrt(r2) * up;
+  }
+  return b;
+}
+
 static double norm3(double x, double y, double z) { return std::sqrt(std::fma(z, z, std::fma(y, y, x * x))); }
 // |R p + t| with the engine's dot convention
 static double actNorm(const double* P, double x, double y, double z) {
@@ -75,6 +102,7 @@ Model::Model(const hppb200_model_desc& d) {
     std::memcpy(G.P, d.geom_placement + 12 * g, sizeof(G.P));
     G.shape = makeShape(d.geom_shape[g], d.geom_params + 4 * g, d.geom_vert_begin ? d.geom_vert_begin[g] : 0,
                         d.geom_vert_count ? d.geom_vert_count[g] : 0);
+    G.bound = makeBound(G.shape, vertices);
     geoms.push_back(G);
   }
   for (int o = 0; o < d.nobstacles; ++o) {
@@ -82,6 +110,9 @@ Model::Model(const hppb200_model_desc& d) {
     std::memcpy(O.P, d.obst_placement + 12 * o, sizeof(O.P));
     O.shape = makeShape(d.obst_shape[o], d.obst_params + 4 * o, d.obst_vert_begin ? d.obst_vert_begin[o] : 0,
                         d.obst_vert_count ? d.obst_vert_count[o] : 0);
+    O.bound = makeBound(O.shape, vertices);
+    for (int i = 0; i < 3; ++i)
+      O.wc[i] = std::fma(O.P[3 * i + 2], O.bound.bc[2], std::fma(O.P[3 * i + 1], O.bound.bc[1], O.P[3 * i] * O.bound.bc[0])) + O.P[9 + i];
     obstacles.push_back(O);
   }
   if (d.security_margins) {
@@ -126,12 +157,12 @@ void Model::buildConfigPairs(const hppb200_model_desc& d) {
   for (int p = 0; p < d.nself_pairs; ++p) {
     int a = d.self_pairs[2 * p], b = d.self_pairs[2 * p + 1];
     if (a < 0 || b < 0 || a >= (int)geoms.size() || b >= (int)geoms.size()) throw std::invalid_argument("self pair index out of range");
-    cPairs.push_back(DevPair{a, b, 0, 0, margin(geoms[a].joint, geoms[b].joint)});
+    cPairs.push_back(DevPair{a, b, 0, 0, margin(geoms[a].joint, geoms[b].joint), 0.0});
   }
   for (int o = 0; o < (int)obstacles.size(); ++o)
     for (int j = 1; j <= njoints; ++j)
       for (int g = 0; g < (int)geoms.size(); ++g)
-        if (geoms[g].joint == j) cPairs.push_back(DevPair{g, -(o + 1), 0, 0, margin(j, 0)});
+        if (geoms[g].joint == j) cPairs.push_back(DevPair{g, -(o + 1), 0, 0, margin(j, 0), 0.0});
 }
 
 void Model::buildBodyPairs(const hppb200_model_desc& d) {
@@ -195,7 +226,7 @@ void Model::buildBodyPairs(const hppb200_model_desc& d) {
       bodyPairs.push_back(bp);
       it = seen.insert({jp, bodyPairs.size() - 1}).first;
     }
-    bodyPairs[it->second].pairs.push_back(DevPair{ga, gb, 0, 0, margin(jp.first, jp.second)});
+    bodyPairs[it->second].pairs.push_back(DevPair{ga, gb, 0, 0, margin(jp.first, jp.second), 0.0});
   }
   // obstacles: one body pair per (joint carrying a body, obstacle)
   for (int o = 0; o < (int)obstacles.size(); ++o)
@@ -204,7 +235,7 @@ void Model::buildBodyPairs(const hppb200_model_desc& d) {
       bp.joint_a = j;
       bp.joint_b = 0;
       for (int g = 0; g < (int)geoms.size(); ++g)
-        if (geoms[g].joint == j) bp.pairs.push_back(DevPair{g, -(o + 1), 0, 0, margin(j, 0)});
+        if (geoms[g].joint == j) bp.pairs.push_back(DevPair{g, -(o + 1), 0, 0, margin(j, 0), 0.0});
       if (bp.pairs.empty()) continue;
       finish(bp);
       bodyPairs.push_back(bp);
@@ -216,6 +247,12 @@ void Model::buildBlob() {
   auto canonical = [&](DevPair p) {
     if (shapeOf(p.a).type > shapeOf(p.b).type) std::swap(p.a, p.b);
     p.kind = pairKind(shapeOf(p.a).type, shapeOf(p.b).type);
+    // conservative cull: cores farther apart than the inflation radii + margin (+ slack) cannot collide
+    p.bound = shapeOf(p.a).type == HPPB200_SHAPE_CAPSULE ? 1 : 0;
+    const double ra = p.a >= 0 ? geoms[p.a].bound.br : obstacles[-(p.a + 1)].bound.br;
+    const double rb = p.b >= 0 ? geoms[p.b].bound.br : obstacles[-(p.b + 1)].bound.br;
+    const double reach = std::max(0.0, ra + rb + p.margin + kCullSlack);
+    p.cull2 = reach * reach * (1.0 + 1e-12);
     return p;
   };
   auto append = [&](const void* src, size_t bytes) {
