@@ -141,7 +141,10 @@ struct Workspace {
   // staging for host-pointer calls
   DeviceBuffer<double> d_q, d_q2, d_L, d_tfail, d_tlast, d_scratch;
   DeviceBuffer<uint8_t> d_valid, d_reason, d_reason_int;
-  DeviceBuffer<uint32_t> d_list;
+  DeviceBuffer<uint32_t> d_list, d_cont;
+  DeviceBuffer<double> d_sv_dbl;
+  DeviceBuffer<uint16_t> d_sv_order;
+  DeviceBuffer<uint8_t> d_sv_flags;
   DeviceBuffer<unsigned long long> d_count;
   DeviceBuffer<int32_t> d_pair, d_pair_int;
   DeviceBuffer<unsigned long long> d_jobs;

@@ -13,14 +13,17 @@
 // walks its samples exactly like the reference's sequential loop, so skip rules and the
 // smallest-interval-first reordering are reproduced per edge (canonical behaviour: pair order
 // is reset to construction order at the start of every edge).
-// Lanes of a warp stay in lock-step on the expensive step only: in every trip of the main loop
-// each lane that has a pending geometry pair evaluates exactly ONE narrow-phase test; the cheap
-// skip tests (interval containment) are fast-forwarded per lane in between.  When an edge ends
-// the lane pulls the next edge from a global counter (warp-aggregated atomic: ballot + popc
-// prefix), i.e. finished edges are compacted out and new work is queued without leaving the
-// kernel.  Per-lane state that does not fit registers (geometry placements, per-body-pair
-// validated interval sets, pair order) lives in global scratch laid out SoA over lanes
-// (coalesced, L2-resident).
+// The warp is phase-synchronous: (A) lanes whose edge ended pull the next edges from a global
+// counter (warp-aggregated atomic: ballot + popc prefix), i.e. finished edges are compacted out
+// and new work is queued without leaving the kernel; (B) every lane sets up its next sample and
+// runs FK, all in step; (C) rounds in which each lane fast-forwards over the pairs the reference
+// would skip (cheap interval containment tests) and then every lane that has a pending geometry
+// pair evaluates exactly ONE narrow-phase test, in step; (D) per-lane end-of-sample update.
+// Discretized samples reuse the configuration kernel's exact culling (closed forms + conservative
+// bounds decided in a uniform scan, surviving GJK pairs drained in lock-step rounds).
+// Per-lane interval sets and pair order live in shared memory when they fit (Progressive:
+// one interval per body pair), else in global scratch laid out SoA over lanes; geometry
+// placements always live in that scratch (coalesced, L2-resident).
 #include "dev_model.cuh"
 
 namespace hppb200 {
@@ -39,6 +42,7 @@ struct EdgeScratch {
   double* subhi;
   size_t nslots;
   int K, KS;
+  int smem_state;     // per-lane interval sets live in shared memory (fast path) instead of scratch
 };
 
 struct EdgeArgs {
@@ -58,6 +62,17 @@ struct EdgeArgs {
   unsigned long long* counter;  // next edge to hand out
   const uint32_t* edge_list;    // optional indirection (second pass over overflowed edges)
   int overflow_reason;          // reason written when an interval list overflows
+  // Two-pass execution of the continuous methods:
+  //   mode 1: every lane runs ONLY the first sample of its edge (all body pairs are evaluated there,
+  //           so the warp is uniform), saves the per-edge state and appends the edge to cont_list;
+  //   mode 2: the walker resumes the saved edges from their second sample;  mode 0: walk from scratch.
+  int mode;
+  double* sv_dbl;               // [2 + 2*NP + 2][n]: t, lastValid, lo[NP], hi[NP], sublo0, subhi0
+  uint16_t* sv_order;           // [NP][n]
+  uint8_t* sv_flags;            // [1 + 2*NP][n]: finished, cnt[NP], valid[NP]
+  uint32_t* cont_list;
+  unsigned long long* cont_count;
+  size_t n_total;               // stride of the sv_* arrays (edges in the call)
 };
 
 // Sorted disjoint closed-interval list with capacity cap, SoA-strided.  Same observable
@@ -101,8 +116,6 @@ __device__ __forceinline__ bool ivContains(const double* lo, const double* hi, s
   return false;
 }
 
-enum { PH_NEED_EDGE = 0, PH_SAMPLE = 1, PH_PAIRS = 2, PH_RETIRED = 3 };
-
 template <int METHOD, bool TREE>
 __global__ void __launch_bounds__(EDGE_THREADS)
 edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
@@ -124,8 +137,27 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
   const int NP = DISC ? mv.ncpairs : mv.nbodypairs;
   const double INF = CUDART_INF;
 
+  // ---- per-lane interval-set state: shared memory when it fits, else global scratch ----
+  double* ivlo; double* ivhi; uint8_t* ivcnt; uint8_t* ivvalid; uint16_t* order;
+  size_t SS;  // stride between consecutive entries of one lane
+  if (S.smem_state) {
+    unsigned char* st = sblob + mv.blob_bytes;
+    const size_t nb = (size_t)mv.nbodypairs;
+    ivlo = (double*)st + threadIdx.x;
+    ivhi = (double*)st + nb * S.K * EDGE_THREADS + threadIdx.x;
+    order = (uint16_t*)(st + 2 * nb * S.K * EDGE_THREADS * sizeof(double)) + threadIdx.x;
+    ivcnt = (uint8_t*)(order - threadIdx.x + nb * EDGE_THREADS) + threadIdx.x;
+    ivvalid = ivcnt + nb * EDGE_THREADS;
+    SS = EDGE_THREADS;
+  } else {
+    ivlo = S.ivlo + slot; ivhi = S.ivhi + slot; ivcnt = S.ivcnt + slot; ivvalid = S.ivvalid + slot; order = S.order + slot;
+    SS = NS;
+  }
+  double* sublo = S.sublo + slot;
+  double* subhi = S.subhi + slot;
+
   // ---- lane state -----------------------------------------------------------------
-  int phase = PH_NEED_EDGE;
+  bool active = false, retired = false;
   size_t e = 0;
   const double* q1 = nullptr;
   const double* q2 = nullptr;
@@ -133,9 +165,7 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
   int qmode = 0;  // 0: initial config, 1: end config, 2: interpolate
   int finished = 0;
   unsigned iters = 0;
-  int pos = 0, gp = -1, gpEnd = 0, curId = 0, smallest = 0, subCnt = 0;
-  double ilo = 0, ihi = 0, dlb = 0;
-  bool pending = false;
+  int subCnt = 0;
   GjkCounters cnt = {0u, 0u, 0u};
   unsigned tests = 0, samples = 0, caps = 0, overflows = 0;
 
@@ -152,9 +182,9 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
     if (A.t_last) A.t_last[e] = tl;
     if (A.pair) A.pair[e] = pr;
     if (A.reason) A.reason[e] = (uint8_t)rs;
-    phase = PH_NEED_EDGE;
-    pending = false;
+    active = false;
   };
+  auto dichLast = [&]() -> double { return reverse ? sublo[(size_t)(subCnt - 1) * NS] : subhi[0]; };
   // SolidSolidCollision::computeMaximalVelocity on Vb = |q2 - q1| / L (StraightPath::impl_velocityBound)
   auto maximalVelocity = [&](const DevBodyPair& B) -> double {
     if (L == 0) return INF;  // BodyPairCollision::setupPath, zero-length path
@@ -177,185 +207,297 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
     }
     return ab;
   };
-  // validateIntervals: fold one body pair's interval into the running intersection
-  auto applyInterval = [&](double tlo, double thi) {
-    if (ihi > thi) smallest = pos;
-    ilo = (ilo < tlo) ? tlo : ilo;
-    ihi = (thi < ihi) ? thi : ihi;
-  };
 
   for (;;) {
-    // ================= advance the lane until it has one pending narrow-phase test ========
-    for (int round = 0; round < 3 && !pending && phase != PH_RETIRED; ++round) {
-      if (phase == PH_NEED_EDGE) {
-        // warp-aggregated fetch of the next edges (ballot + popc prefix)
-        const unsigned m = __activemask();
+    // ================= A. refill: finished lanes pull the next edges (ballot + popc prefix) ==========
+    {
+      const bool want = !active && !retired;
+      const unsigned m = __ballot_sync(FULL, want);
+      if (m) {
         const int leader = __ffs(m) - 1;
         unsigned long long b = 0;
         if (lane == leader) b = atomicAdd(A.counter, (unsigned long long)__popc(m));
-        b = __shfl_sync(m, b, leader);
-        const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
-        if (idx >= A.n) { phase = PH_RETIRED; break; }
-        e = A.edge_list ? (size_t)A.edge_list[idx] : (size_t)idx;
-        q1 = A.q1 + e * (size_t)mv.nq;
-        q2 = A.q2 + e * (size_t)mv.nq;
-        L = A.L[e];
-        iters = 0;
-        finished = 0;
-        lastValid = reverse ? L : 0.0;
-        t = lastValid;
-        if (PROG) { if (reverse ? t <= 0.0 : t >= L) finished++; }
-        if (!DISC) {
-          for (int id = 0; id < NP; ++id) {
-            S.ivcnt[id * NS + slot] = 0;
-            S.ivvalid[id * NS + slot] = 0;
-            S.order[id * NS + slot] = (uint16_t)id;
+        b = __shfl_sync(FULL, b, leader);
+        if (want) {
+          const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
+          if (idx >= A.n) retired = true;
+          else {
+            e = A.edge_list ? (size_t)A.edge_list[idx] : (size_t)idx;
+            q1 = A.q1 + e * (size_t)mv.nq;
+            q2 = A.q2 + e * (size_t)mv.nq;
+            L = A.L[e];
+            if (!DISC && A.mode == 2) {
+              // resume after the first sample
+              const size_t NT = A.n_total;
+              iters = 1;
+              t = A.sv_dbl[e];
+              lastValid = A.sv_dbl[NT + e];
+              finished = A.sv_flags[e];
+              for (int id = 0; id < NP; ++id) {
+                order[id * SS] = A.sv_order[(size_t)id * NT + e];
+                ivcnt[id * SS] = A.sv_flags[(size_t)(1 + id) * NT + e];
+                ivvalid[id * SS] = A.sv_flags[(size_t)(1 + NP + id) * NT + e];
+                const size_t o = ((size_t)id * S.K) * SS;
+                ivlo[o] = A.sv_dbl[(size_t)(2 + id) * NT + e];
+                ivhi[o] = A.sv_dbl[(size_t)(2 + NP + id) * NT + e];
+              }
+              if (DICH) { sublo[0] = A.sv_dbl[(size_t)(2 + 2 * NP) * NT + e]; subhi[0] = A.sv_dbl[(size_t)(3 + 2 * NP) * NT + e]; subCnt = 1; }
+            } else {
+              iters = 0;
+              finished = 0;
+              lastValid = reverse ? L : 0.0;
+              t = lastValid;
+              if (PROG) { if (reverse ? t <= 0.0 : t >= L) finished++; }
+              if (!DISC) {
+                for (int id = 0; id < NP; ++id) { ivcnt[id * SS] = 0; ivvalid[id * SS] = 0; order[id * SS] = (uint16_t)id; }
+              }
+              if (DICH) { sublo[0] = t; subhi[0] = t; subCnt = 1; }
+            }
+            active = true;
           }
         }
-        if (DICH) { S.sublo[slot] = t; S.subhi[slot] = t; subCnt = 1; }
-        phase = PH_SAMPLE;
       }
-      if (phase == PH_SAMPLE) {
-        if (iters >= A.max_iter) {
-          ++caps;
-          double tl = lastValid;
-          if (DICH) tl = reverse ? S.sublo[(size_t)(subCnt - 1) * NS + slot] : S.subhi[slot];
-          finishEdge(false, HPPB200_REASON_ITER_CAP, t, tl, -1);
-          continue;
-        }
+      if (!__any_sync(FULL, active)) break;
+    }
+
+    // ================= B. sample set-up: q(t), joint bounds, FK — all lanes in step ================
+    bool work = false;  // this lane has a sample whose pairs must be processed
+    if (active) {
+      if (iters >= A.max_iter) {
+        ++caps;
+        finishEdge(false, HPPB200_REASON_ITER_CAP, t, DICH ? dichLast() : lastValid, -1);
+      } else {
         ++iters;
         ++samples;
         // Path::eval -> StraightPath::impl_compute: stored end points are returned bit-exactly
         if (t == 0.0 || L == 0.0) qmode = 0;
         else if (t == L) qmode = 1;
         else { qmode = 2; u = (t - 0.0) / L; }
+        int bad = -1;
         if (DISC && (A.flags & HPPB200_CHECK_JOINT_BOUNDS)) {
-          int bad = -1;
           for (int k = 0; k < mv.nq && bad < 0; ++k) {
             const double lo = T.lower[k], hi = T.upper[k];
             if (lo > hi) continue;
             const double v = qAt(k);
             if (v < lo || hi < v) bad = k;
           }
-          if (bad >= 0) { finishEdge(false, HPPB200_REASON_JOINT_BOUND, t, lastValid, bad); continue; }
         }
-        forwardKinematics<TREE>(T, mv, qAt, store, NS);
-        pos = 0;
-        gp = -1;
-        smallest = 0;
-        ilo = -INF;
-        ihi = INF;
-        phase = PH_PAIRS;
+        if (bad >= 0) finishEdge(false, HPPB200_REASON_JOINT_BOUND, t, lastValid, bad);
+        else work = true;
       }
-      if (phase == PH_PAIRS) {
-        if (DISC) {
-          if (pos < NP) { pending = true; break; }
-        } else {
-          // fast-forward over body pairs the reference would skip (body-pair-collision.cc:51-63)
+    }
+    if (work) forwardKinematics<TREE>(T, mv, qAt, store, NS);
+
+    // ================= C. pairs ======================================================================
+    if (DISC) {
+      // C1: uniform scan in reference order.  Closed forms are decided exactly; GJK kinds are culled
+      // with the conservative bounds of the configuration kernel; survivors wait in a 4-entry list.
+      // C2 (drain): one GJK per lane per round, all lanes in step.
+      int hit = INT_MAX;
+      int pd0 = -1, pd1 = -1, pd2 = -1, pd3 = -1, npend = 0;
+      auto drain = [&]() {
+        for (;;) {
+          const bool has = npend > 0;
+          if (!__any_sync(FULL, has)) break;
+          if (has) {
+            const int p = pd0;
+            pd0 = pd1; pd1 = pd2; pd2 = pd3; pd3 = -1; --npend;
+            if (p < hit) {
+              const DevPair pr = T.cpairs[p];
+              const double d = pairLowerBound(T, pr, store, NS, mv.vertices, cnt);
+              ++tests;
+              if (d <= HPPB200_COLLISION_THRESHOLD) { hit = p; npend = 0; }
+            }
+          }
+        }
+      };
+      for (int p = 0; p < NP; ++p) {
+        if (work && p < hit) {
+          const DevPair pr = T.cpairs[p];
+          const DevShape& sa = *(const DevShape*)(pr.a >= 0 ? &T.geoms[pr.a].shape : &T.obstacles[-(pr.a + 1)].shape);
+          const DevShape& sb = *(const DevShape*)(pr.b >= 0 ? &T.geoms[pr.b].shape : &T.obstacles[-(pr.b + 1)].shape);
+          V3 ca, ua, cb, ub;
+          if (pr.a >= 0) {
+            const double* M = store + (size_t)pr.a * 12 * NS;
+            ua = mk(M[2 * NS], M[5 * NS], M[8 * NS]);
+            ca = mk(M[9 * NS], M[10 * NS], M[11 * NS]);
+            if (sa.type >= SH_BOX) { const DevBound& B = T.geoms[pr.a].bound; ca = rmul(load12s(M, NS), mk(B.bc[0], B.bc[1], B.bc[2])) + ca; }
+          } else { const DevObstacle& O = T.obstacles[-(pr.a + 1)]; ca = mk(O.wc[0], O.wc[1], O.wc[2]); ua = mk(O.P[2], O.P[5], O.P[8]); }
+          if (pr.b >= 0) {
+            const double* M = store + (size_t)pr.b * 12 * NS;
+            ub = mk(M[2 * NS], M[5 * NS], M[8 * NS]);
+            cb = mk(M[9 * NS], M[10 * NS], M[11 * NS]);
+            if (sb.type >= SH_BOX) { const DevBound& B = T.geoms[pr.b].bound; cb = rmul(load12s(M, NS), mk(B.bc[0], B.bc[1], B.bc[2])) + cb; }
+          } else { const DevObstacle& O = T.obstacles[-(pr.b + 1)]; cb = mk(O.wc[0], O.wc[1], O.wc[2]); ub = mk(O.P[2], O.P[5], O.P[8]); }
+          if (pr.kind <= PK_CAPSULE_CAPSULE) {
+            double d;
+            if (pr.kind == PK_SPHERE_SPHERE) { V3 dd = ca - cb; d = sqrt(dot(dd, dd)) - sa.p[0] - sb.p[0]; }
+            else if (pr.kind == PK_SPHERE_CAPSULE) d = sqrt(pointSegmentDist2(ca, cb, ub, sb.p[1])) - sa.p[0] - sb.p[0];
+            else {
+              V3 p1 = axpy(-sa.p[1], ua, ca), q1s = axpy(sa.p[1], ua, ca);
+              V3 p2 = axpy(-sb.p[1], ub, cb), q2s = axpy(sb.p[1], ub, cb);
+              d = sqrt(segmentSegmentDist2(p1, q1s, p2, q2s)) - sa.p[0] - sb.p[0];
+            }
+            ++tests;
+            if (d - pr.margin <= HPPB200_COLLISION_THRESHOLD) hit = p;
+          } else {
+            double d2;
+            if (pr.bound == 1) d2 = pointSegmentDist2(cb, ca, ua, sa.p[1]);
+            else { V3 dd = ca - cb; d2 = dot(dd, dd); }
+            bool survive = !(d2 > pr.cull2);
+            if (survive && pr.b < 0 && sb.type == SH_BOX) {
+              const DevObstacle& O = T.obstacles[-(pr.b + 1)];
+              const T3 TB = load12(O.P);
+              const double h = pr.bound == 1 ? sa.p[1] : 0.0;
+              const V3 e0 = rtmul(TB, axpy(-h, ua, ca) - TB.t), e1 = rtmul(TB, axpy(h, ua, ca) - TB.t);
+              const double sx = fmax(fmin(e0.x, e1.x) - sb.p[0], -fmax(e0.x, e1.x) - sb.p[0]);
+              const double sy = fmax(fmin(e0.y, e1.y) - sb.p[1], -fmax(e0.y, e1.y) - sb.p[1]);
+              const double sz = fmax(fmin(e0.z, e1.z) - sb.p[2], -fmax(e0.z, e1.z) - sb.p[2]);
+              const double ra = pr.a >= 0 ? T.geoms[pr.a].bound.br : T.obstacles[-(pr.a + 1)].bound.br;
+              if (fmax(sx, fmax(sy, sz)) - ra - pr.margin > 1e-9) survive = false;
+            }
+            if (survive) {
+              if (npend == 0) pd0 = p; else if (npend == 1) pd1 = p; else if (npend == 2) pd2 = p; else pd3 = p;
+              ++npend;
+            }
+          }
+        }
+        if (__any_sync(FULL, npend == 4)) drain();
+      }
+      drain();
+      if (work) {
+        if (hit != INT_MAX) finishEdge(false, HPPB200_REASON_COLLISION, t, lastValid, hit);
+        else {
+          lastValid = t;
+          t += reverse ? -A.param : A.param;
+          if ((reverse && t < 0.0) || (!reverse && t > L)) { t = reverse ? 0.0 : L; finished++; }
+          if (finished >= 2) finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+        }
+      }
+    } else {
+      int pos = 0, gp = -1, gpEnd = 0, curId = 0, smallest = 0;
+      double ilo = -INF, ihi = INF, dlb = INF;
+      for (;;) {
+        // fast-forward over the body pairs the reference would skip (body-pair-collision.cc:51-63)
+        if (work && gp < 0) {
           while (pos < NP) {
-            const int id = S.order[pos * NS + slot];
-            if (S.ivvalid[id * NS + slot]) { applyInterval(0.0, L); ++pos; continue; }
-            const size_t o = ((size_t)id * S.K) * NS + slot;
-            if (ivContains(S.ivlo + o, S.ivhi + o, NS, S.ivcnt[id * NS + slot], ilo, ihi)) { ++pos; continue; }
+            const int id = order[pos * SS];
+            if (ivvalid[id * SS]) {  // valid_ on the whole path: interval = timeRange
+              if (ihi > L) smallest = pos;
+              ilo = (ilo < 0.0) ? 0.0 : ilo;
+              ihi = (L < ihi) ? L : ihi;
+              ++pos;
+              continue;
+            }
+            const size_t o = ((size_t)id * S.K) * SS;
+            if (ivContains(ivlo + o, ivhi + o, SS, ivcnt[id * SS], ilo, ihi)) { ++pos; continue; }
             curId = id;
             gp = T.bodypairs[id].pair_begin;
             gpEnd = T.bodypairs[id].pair_end;
             dlb = INF;
             break;
           }
-          if (pos < NP) { pending = true; break; }
         }
-        // ---- end of a collision-free sample ----
-        if (DISC) {
-          lastValid = t;
-          t += reverse ? -A.param : A.param;
-          if ((reverse && t < 0.0) || (!reverse && t > L)) { t = reverse ? 0.0 : L; finished++; }
-          if (finished < 2) phase = PH_SAMPLE;
-          else finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
-        } else {
-          // src/continuous-validation.cc:144-146: smallest interval first
-          if (NP > 1 && smallest != 0) {
-            const uint16_t a0 = S.order[slot], as = S.order[smallest * NS + slot];
-            S.order[slot] = as;
-            S.order[smallest * NS + slot] = a0;
-          }
-          if (PROG) {
-            const double tprev = t;
-            t = reverse ? ilo : ihi;
-            lastValid = tprev;
-            if (reverse ? t <= 0.0 : t >= L) { t = reverse ? 0.0 : L; finished++; }
-            if (finished < 2) phase = PH_SAMPLE;
-            else finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+        const bool pending = work && gp >= 0;
+        if (!__any_sync(FULL, pending)) break;
+        if (pending) {
+          // one narrow-phase test per lane, warp in step
+          const DevPair pr = T.bgpairs[gp];
+          const double d = pairLowerBound(T, pr, store, NS, mv.vertices, cnt);
+          ++tests;
+          if (d <= HPPB200_COLLISION_THRESHOLD) {
+            finishEdge(false, HPPB200_REASON_COLLISION, t, DICH ? dichLast() : lastValid, gp);
+            work = false;
           } else {
-            if (!ivUnion(S.sublo + slot, S.subhi + slot, NS, subCnt, S.KS, ilo, ihi)) {
-              if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
-              finishEdge(false, A.overflow_reason, t, reverse ? S.sublo[(size_t)(subCnt - 1) * NS + slot] : S.subhi[slot], -1);
-              continue;
-            }
-            if (ivContains(S.sublo + slot, S.subhi + slot, NS, subCnt, 0.0, L)) {
-              finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
-            } else {
-              // middle of the first non-validated gap (dichotomy.cc:103-109)
-              double t0, t1;
-              if (!reverse) {
-                t0 = S.subhi[slot];
-                t1 = subCnt > 1 ? S.sublo[NS + slot] : L;
-              } else {
-                t0 = S.sublo[(size_t)(subCnt - 1) * NS + slot];
-                t1 = subCnt > 1 ? S.subhi[(size_t)(subCnt - 2) * NS + slot] : 0.0;
+            if (d < dlb) dlb = d;
+            ++gp;
+            if (gp >= gpEnd) {
+              // BodyPairCollision::validateConfiguration :72-96
+              const DevBodyPair& B = T.bodypairs[curId];
+              double hd, ht;
+              if (dlb == INF) { hd = INF; ht = 0; }
+              else {
+                const double Vm = maximalVelocity(B);
+                hd = dlb / Vm;
+                ht = (Vm != 0) ? 2 * A.param / Vm : INF;
               }
-              t = .5 * (t0 + t1);
-              phase = PH_SAMPLE;
+              const double a = t - (hd + ht), b = t + (hd + ht);
+              const size_t o = ((size_t)curId * S.K) * SS;
+              int c = ivcnt[curId * SS];
+              if (!ivUnion(ivlo + o, ivhi + o, SS, c, S.K, a, b)) {
+                if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
+                finishEdge(false, A.overflow_reason, t, DICH ? dichLast() : lastValid, -1);
+                work = false;
+              } else {
+                ivcnt[curId * SS] = (uint8_t)c;
+                if (ivContains(ivlo + o, ivhi + o, SS, c, 0.0, L)) ivvalid[curId * SS] = 1;
+                // validateIntervals: fold into the running intersection
+                if (ihi > b) smallest = pos;
+                ilo = (ilo < a) ? a : ilo;
+                ihi = (b < ihi) ? b : ihi;
+                ++pos;
+                gp = -1;
+              }
             }
           }
         }
       }
-    }
-    if (__all_sync(FULL, phase == PH_RETIRED)) break;
-
-    // ================= one narrow-phase test per lane, warp in lock-step ==================
-    if (pending) {
-      const DevPair pr = DISC ? T.cpairs[pos] : T.bgpairs[gp];
-      const double d = pairLowerBound(T, pr, store, NS, mv.vertices, cnt);
-      ++tests;
-      if (d <= HPPB200_COLLISION_THRESHOLD) {
-        double tl = lastValid;
-        if (DICH) tl = reverse ? S.sublo[(size_t)(subCnt - 1) * NS + slot] : S.subhi[slot];
-        finishEdge(false, HPPB200_REASON_COLLISION, t, tl, DISC ? pos : gp);
-      } else if (DISC) {
-        ++pos;
-        pending = false;
-      } else {
-        if (d < dlb) dlb = d;
-        ++gp;
-        if (gp >= gpEnd) {
-          // BodyPairCollision::validateConfiguration :72-96
-          const DevBodyPair& B = T.bodypairs[curId];
-          double hd, ht;
-          if (dlb == INF) { hd = INF; ht = 0; }
-          else {
-            const double Vm = maximalVelocity(B);
-            hd = dlb / Vm;
-            ht = (Vm != 0) ? 2 * A.param / Vm : INF;
-          }
-          const double a = t - (hd + ht), b = t + (hd + ht);
-          const size_t o = ((size_t)curId * S.K) * NS + slot;
-          int c = S.ivcnt[curId * NS + slot];
-          if (!ivUnion(S.ivlo + o, S.ivhi + o, NS, c, S.K, a, b)) {
+      // ================= D. end of a collision-free sample =========================================
+      if (work) {
+        // src/continuous-validation.cc:144-146: smallest interval first
+        if (NP > 1 && smallest != 0) {
+          const uint16_t a0 = order[0], as = order[smallest * SS];
+          order[0] = as;
+          order[smallest * SS] = a0;
+        }
+        if (PROG) {
+          const double tprev = t;
+          t = reverse ? ilo : ihi;
+          lastValid = tprev;
+          if (reverse ? t <= 0.0 : t >= L) { t = reverse ? 0.0 : L; finished++; }
+          if (finished >= 2) finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+        } else {
+          if (!ivUnion(sublo, subhi, NS, subCnt, S.KS, ilo, ihi)) {
             if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
-            double tl = lastValid;
-            if (DICH) tl = reverse ? S.sublo[(size_t)(subCnt - 1) * NS + slot] : S.subhi[slot];
-            finishEdge(false, A.overflow_reason, t, tl, -1);
+            finishEdge(false, A.overflow_reason, t, dichLast(), -1);
+          } else if (ivContains(sublo, subhi, NS, subCnt, 0.0, L)) {
+            finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
           } else {
-            S.ivcnt[curId * NS + slot] = (uint8_t)c;
-            if (ivContains(S.ivlo + o, S.ivhi + o, NS, c, 0.0, L)) S.ivvalid[curId * NS + slot] = 1;
-            applyInterval(a, b);
-            ++pos;
-            gp = -1;
-            pending = false;
+            // middle of the first non-validated gap (dichotomy.cc:103-109)
+            double t0, t1;
+            if (!reverse) { t0 = subhi[0]; t1 = subCnt > 1 ? sublo[NS] : L; }
+            else { t0 = sublo[(size_t)(subCnt - 1) * NS]; t1 = subCnt > 1 ? subhi[(size_t)(subCnt - 2) * NS] : 0.0; }
+            t = .5 * (t0 + t1);
           }
         }
-        // else: same body pair, next geometry pair stays pending
+      }
+      // ---- mode 1: first sample done; park the edge for the resume pass ----
+      if (A.mode == 1) {
+        const bool cont = active;
+        const unsigned m = __ballot_sync(FULL, cont);
+        if (m) {
+          const int leader = __ffs(m) - 1;
+          unsigned long long b = 0;
+          if (lane == leader) b = atomicAdd(A.cont_count, (unsigned long long)__popc(m));
+          b = __shfl_sync(FULL, b, leader);
+          if (cont) {
+            const size_t NT = A.n_total;
+            A.cont_list[b + __popc(m & ((1u << lane) - 1u))] = (uint32_t)e;
+            A.sv_dbl[e] = t;
+            A.sv_dbl[NT + e] = lastValid;
+            A.sv_flags[e] = (uint8_t)finished;
+            for (int id = 0; id < NP; ++id) {
+              A.sv_order[(size_t)id * NT + e] = order[id * SS];
+              A.sv_flags[(size_t)(1 + id) * NT + e] = ivcnt[id * SS];
+              A.sv_flags[(size_t)(1 + NP + id) * NT + e] = ivvalid[id * SS];
+              const size_t o = ((size_t)id * S.K) * SS;
+              A.sv_dbl[(size_t)(2 + id) * NT + e] = ivlo[o];
+              A.sv_dbl[(size_t)(2 + NP + id) * NT + e] = ivhi[o];
+            }
+            if (DICH) { A.sv_dbl[(size_t)(2 + 2 * NP) * NT + e] = sublo[0]; A.sv_dbl[(size_t)(3 + 2 * NP) * NT + e] = subhi[0]; }
+            active = false;
+          }
+        }
       }
     }
   }
@@ -420,7 +562,11 @@ static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS, s
   const bool tree = modelIsTree(ws->model);
   auto kern = tree ? edgeWalkerKernel<METHOD, true> : edgeWalkerKernel<METHOD, false>;
   const ModelView& mv = ws->view;
-  const size_t smemBytes = 16 + mv.blob_bytes;
+  size_t smemBytes = 16 + mv.blob_bytes;
+  const size_t nbp0 = METHOD == HPPB200_METHOD_DISCRETIZED ? 0 : (size_t)mv.nbodypairs;
+  const size_t stateBytes = nbp0 * EDGE_THREADS * ((size_t)K * 16 + 4);
+  const bool smemState = nbp0 > 0 && smemBytes + stateBytes <= 200u * 1024u;
+  if (smemState) smemBytes += stateBytes;
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
   int perSM = 0;
   HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, EDGE_THREADS, smemBytes));
@@ -433,7 +579,7 @@ static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS, s
 
   // carve the scratch (8-byte aligned fields)
   const size_t fkSlots = (size_t)mv.ngeoms + (tree ? mv.njoints : 0);
-  const size_t nbp = METHOD == HPPB200_METHOD_DISCRETIZED ? 0 : (size_t)mv.nbodypairs;
+  const size_t nbp = (METHOD == HPPB200_METHOD_DISCRETIZED || smemState) ? 0 : (size_t)mv.nbodypairs;
   auto al = [](size_t x) { return (x + 255) & ~size_t(255); };
   size_t off = 0;
   const size_t o_counter = off; off += 256;
@@ -459,6 +605,7 @@ static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS, s
   S.nslots = NS;
   S.K = K;
   S.KS = KS;
+  S.smem_state = smemState ? 1 : 0;
   EdgeArgs A = A0;
   A.counter = (unsigned long long*)(base + o_counter);
 
@@ -492,8 +639,31 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
   const size_t allSlots = ~size_t(0);
   if (method == HPPB200_METHOD_DISCRETIZED) { launchEdgeWalker<HPPB200_METHOD_DISCRETIZED>(ws, A, 1, 1, allSlots); return; }
-  if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, A, 2, 1, allSlots);
-  else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, A, 12, 96, allSlots);
+  // pass 1: first sample of every edge (uniform warps); pass 2: resume the survivors
+  const size_t NPb = (size_t)ws->view.nbodypairs;
+  ws->d_sv_dbl.reserve((2 + 2 * NPb + 2) * n);
+  ws->d_sv_order.reserve(NPb * n);
+  ws->d_sv_flags.reserve((1 + 2 * NPb) * n);
+  ws->d_cont.reserve(n);
+  ws->d_count.reserve(2);
+  A.sv_dbl = ws->d_sv_dbl.p; A.sv_order = ws->d_sv_order.p; A.sv_flags = ws->d_sv_flags.p;
+  A.cont_list = ws->d_cont.p; A.cont_count = ws->d_count.p + 1; A.n_total = n;
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(A.cont_count, 0, sizeof(unsigned long long), ws->stream));
+  A.mode = 1;
+  if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, A, 1, 1, allSlots);
+  else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, A, 1, 1, allSlots);
+  unsigned long long ncont = 0;
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&ncont, A.cont_count, sizeof(ncont), cudaMemcpyDeviceToHost, ws->stream));
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  if (ncont) {
+    EdgeArgs B = A;
+    B.mode = 2;
+    B.edge_list = ws->d_cont.p;
+    B.n = (size_t)ncont;
+    if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, B, 1, 1, allSlots);
+    else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, B, 12, 96, allSlots);
+  }
+  A.mode = 0;
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&after, ws->d_stats, sizeof(after), cudaMemcpyDeviceToHost, ws->stream));
   HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
   const unsigned long long nover = after.overflow - before.overflow;
