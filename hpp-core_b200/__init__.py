@@ -37,7 +37,7 @@ _i64p = C.POINTER(C.c_int64)
 class hppb200_stats(C.Structure):
     _fields_ = [("configs", C.c_uint64), ("pair_tests", C.c_uint64), ("gjk_iterations", C.c_uint64),
                 ("edge_samples", C.c_uint64), ("kernel_launches", C.c_uint64), ("iter_cap_hits", C.c_uint64),
-                ("last_kernel_ms", C.c_double)]
+                ("last_kernel_ms", C.c_double), ("engine_ticks", C.c_uint64), ("discarded_tests", C.c_uint64)]
 
 
 # every symbol include/hppb200.h declares (checked by tests/test_abi.py)

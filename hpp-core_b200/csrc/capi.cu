@@ -3,6 +3,7 @@
 // the reference throws (std::invalid_argument / std::runtime_error).
 // There is no CPU fallback: compute entry points require a CUDA device.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "engine.hpp"
@@ -27,6 +28,9 @@ Workspace::Workspace(const Model* m, int dev) : model(m), device(dev) {
   HPPB200_CUDA_CHECK(cudaMalloc((void**)&d_stats, sizeof(DeviceStats)));
   HPPB200_CUDA_CHECK(cudaMemset(d_stats, 0, sizeof(DeviceStats)));
   view = m->deviceView(dev);
+  if (const char* v = std::getenv("HPPB200_ENGINE")) use_engine = std::atoi(v) != 0;
+  if (const char* v = std::getenv("HPPB200_ENGINE_ALPHA")) engine_alpha = std::atof(v);
+  if (const char* v = std::getenv("HPPB200_ENGINE_THREADS")) engine_threads = std::atoi(v);
 }
 
 Workspace::~Workspace() {
@@ -45,6 +49,8 @@ void Workspace::syncStats() {
   stats.gjk_iterations = h.gjk_iterations;
   stats.edge_samples = h.edge_samples;
   stats.iter_cap_hits = h.iter_cap_hits;  // (second-pass overflows are counted here by the kernel)
+  stats.engine_ticks = h.engine_ticks;
+  stats.discarded_tests = h.discarded_tests;
 }
 
 template <typename F>

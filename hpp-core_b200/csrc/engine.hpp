@@ -56,6 +56,7 @@ struct DevBodyPair {
   int32_t pair_begin, pair_end;    // into bodyGeomPairs
   int32_t coef_begin, coef_end;    // a -> b
   int32_t rcoef_begin, rcoef_end;  // b -> a (empty when joint_b == 0)
+  int32_t has_gjk;                 // some geometry pair of this body pair goes through GJK
 };
 struct DevCoef {
   int32_t idx_v, nv;
@@ -67,6 +68,7 @@ struct ModelView {
   const unsigned char* blob;  // global memory
   const double* vertices;     // global memory convex vertex pool (not staged)
   uint32_t blob_bytes;
+  uint32_t edge_blob_bytes;  // prefix without the configuration pair table (continuous validation)
   uint32_t off_joints, off_geoms, off_obstacles, off_cpairs, off_bodypairs, off_bgpairs, off_coefs, off_rcoefs,
       off_lower, off_upper, off_weights;
   int32_t njoints, ngeoms, nobstacles, ncpairs, nbodypairs, nbgpairs, ncoefs, nrcoefs, nq, nv;
@@ -107,6 +109,7 @@ struct Model {
 
 struct DeviceStats {  // accumulated by kernels with atomics
   unsigned long long configs, pair_tests, gjk_iterations, edge_samples, iter_cap_hits, gjk_cap_hits, overflow;
+  unsigned long long engine_ticks, discarded_tests;  // continuous engine: CTA ticks, speculative tests thrown away
 };
 
 template <typename T>
@@ -138,6 +141,9 @@ struct Workspace {
   DeviceStats* d_stats = nullptr;
   hppb200_stats stats{};
   uint32_t max_iterations = 1u << 20;
+  bool use_engine = true;      // Progressive: control/narrow-phase engine (HPPB200_ENGINE=0 forces the walker)
+  int engine_threads = 128;    // CTA size of the engine (HPPB200_ENGINE_THREADS: 64 | 96 | 128)
+  double engine_alpha = 2.0;   // candidate prediction: alpha x previous step (HPPB200_ENGINE_ALPHA)
   // staging for host-pointer calls
   DeviceBuffer<double> d_q, d_q2, d_L, d_tfail, d_tlast, d_scratch;
   DeviceBuffer<uint8_t> d_valid, d_reason, d_reason_int;
@@ -162,6 +168,9 @@ void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t 
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg);
 void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_dist);
 void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2, size_t n, double* d_L);
+bool launchProgressiveEngine(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
+                             const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
+                             int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
 void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1,
                          const double* d_q2, const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid,
                          double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason);

@@ -639,6 +639,13 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
   const size_t allSlots = ~size_t(0);
   if (method == HPPB200_METHOD_DISCRETIZED) { launchEdgeWalker<HPPB200_METHOD_DISCRETIZED>(ws, A, 1, 1, allSlots); return; }
+  // Progressive on models whose per-edge state fits in shared memory: the control/narrow-phase
+  // engine of kernels_continuous.cu.  Anything else: the generic walker below.
+  bool engineDone = false;
+  if (method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine)
+    engineDone = launchProgressiveEngine(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,
+                                         REASON_OVERFLOW_INTERNAL);
+  if (!engineDone) {
   // pass 1: first sample of every edge (uniform warps); pass 2: resume the survivors
   const size_t NPb = (size_t)ws->view.nbodypairs;
   ws->d_sv_dbl.reserve((2 + 2 * NPb + 2) * n);
@@ -662,6 +669,7 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
     B.n = (size_t)ncont;
     if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, B, 1, 1, allSlots);
     else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, B, 12, 96, allSlots);
+  }
   }
   A.mode = 0;
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&after, ws->d_stats, sizeof(after), cudaMemcpyDeviceToHost, ws->stream));

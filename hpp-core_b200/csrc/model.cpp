@@ -270,7 +270,10 @@ void Model::buildBlob() {
     B.joint_a = b.joint_a;
     B.joint_b = b.joint_b;
     B.pair_begin = (int)bg.size();
-    for (const DevPair& p : b.pairs) bg.push_back(canonical(p));
+    for (const DevPair& p : b.pairs) {
+      bg.push_back(canonical(p));
+      if (bg.back().kind == 4 /* PK_GJK */) B.has_gjk = 1;
+    }
     B.pair_end = (int)bg.size();
     B.coef_begin = (int)cf.size();
     for (auto& c : b.coefs) cf.push_back(DevCoef{joints[c.first - 1].idx_v, joint_nv[c.first - 1], c.second});
@@ -284,7 +287,6 @@ void Model::buildBlob() {
   view.off_joints = append(joints.data(), joints.size() * sizeof(DevJoint));
   view.off_geoms = append(geoms.data(), geoms.size() * sizeof(DevGeom));
   view.off_obstacles = append(obstacles.data(), obstacles.size() * sizeof(DevObstacle));
-  view.off_cpairs = append(cp.data(), cp.size() * sizeof(DevPair));
   view.off_bodypairs = append(bps.data(), bps.size() * sizeof(DevBodyPair));
   view.off_bgpairs = append(bg.data(), bg.size() * sizeof(DevPair));
   view.off_coefs = append(cf.data(), cf.size() * sizeof(DevCoef));
@@ -292,6 +294,9 @@ void Model::buildBlob() {
   view.off_lower = append(lower.data(), lower.size() * sizeof(double));
   view.off_upper = append(upper.data(), upper.size() * sizeof(double));
   view.off_weights = append(weights.data(), weights.size() * sizeof(double));
+  // the configuration pair table comes last: the edge engine stages only the prefix before it
+  view.edge_blob_bytes = (uint32_t)blob.size();
+  view.off_cpairs = append(cp.data(), cp.size() * sizeof(DevPair));
   view.blob_bytes = (uint32_t)blob.size();
   view.njoints = njoints;
   view.ngeoms = (int)geoms.size();

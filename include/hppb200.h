@@ -157,6 +157,9 @@ typedef struct hppb200_stats {
   uint64_t kernel_launches;  /* CUDA kernels launched by this workspace        */
   uint64_t iter_cap_hits;    /* edges that ended with HPPB200_REASON_ITER_CAP  */
   double last_kernel_ms;     /* device time of the last validate_* call        */
+  uint64_t engine_ticks;     /* continuous engine: control/narrow-phase rounds  */
+  uint64_t discarded_tests;  /* speculative pair tests whose result the reference
+                                order did not need (counted in pair_tests too)  */
 } hppb200_stats;
 
 /* ---- library ----------------------------------------------------------- */
