@@ -92,7 +92,7 @@ static PELayout peLayout(const ModelView& mv) {
 template <bool TREE, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(16) unsigned char smem[];  // @region setup
   uint64_t* bar = (uint64_t*)smem;
   PECtl* ctl = (PECtl*)(smem + 16);
   unsigned char* sblob = smem + SL.off_blob;
@@ -153,76 +153,76 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
     sampleOpen = false;
   };
 
-  // Replay of validateIntervals over the pairs from `pos` on, with the results queued last round
-  // (result k belongs to the k-th queued position).  Called by the whole control warp; `on` lanes take
-  // part.  The warp alternates a cheap per-lane scan over the pairs the reference skips with a step
-  // in which every lane that reached a pair whose result is there folds it in, all together.
-  // Leaves pos == NP when the sample is complete, else pos at the first pair whose result is missing.
-  auto replay = [&](bool on) {
-    int cursor = 0;
-    bool run = on;
-    for (;;) {
-      bool consume = false;
-      int id = 0, k = 0;
-      // warp-uniform trip count (vote) keeps the lanes converged; one position per lane per trip
-      bool scanning = run;
-      while (__any_sync(FULL, scanning)) {
-        if (scanning) {
-          if (pos >= NP) scanning = false;
-          else {
-            id = sOrder[pos * PE_SLOTS];
-            const bool have = cursor < nEm && sEmPos[cursor * PE_SLOTS] == pos;
-            if (have) { k = cursor; ++cursor; }
-            const bool vb = validBit(id);  // valid_ on the whole path: interval = timeRange (body-pair-collision.cc:51-55)
-            const double l = sLo[id * PE_SLOTS], h = sHi[id * PE_SLOTS];
-            const bool contained = l <= ilo && ihi <= h;  // validInterval_ contains the running interval (:56-63)
-            if (vb) {
-              if (ihi > L) smallest = pos;
-              ilo = (ilo < 0.0) ? 0.0 : ilo;
-              ihi = (L < ihi) ? L : ihi;
-            }
-            if (vb || contained) {
-              if (have) ++discarded;
-              ++pos;
+  // One pass of the control warp over the pair positions, all lanes in step (one position per trip, trip
+  // count decided by a vote, so the warp stays converged).  A lane starts in REPLAY mode: it follows
+  // validateIntervals from `pos` on with the results queued last round (result k belongs to the k-th
+  // queued position).  At the first pair the reference evaluates whose result is not there, the lane
+  // switches to EMIT mode: that pair and the predicted candidates after it are recorded for the next
+  // narrow phase.  A lane that reaches the end in REPLAY mode has completed the sample.
+  int nGl = 0, nCl = 0;
+  unsigned gmask = 0;
+  auto scanPass = [&](bool on) {  // @region replay
+    int cursor = 0, p = pos, newEm = 0;
+    bool emit = false, more = on && p < NP;
+    double ql = 0, qh = 0;
+    if (on) { nGl = 0; nCl = 0; gmask = 0; }
+    while (__any_sync(FULL, more)) {
+      if (more) {
+        const int id = sOrder[p * PE_SLOTS];
+        const bool vb = validBit(id);
+        const double l = sLo[id * PE_SLOTS], h = sHi[id * PE_SLOTS];
+        if (!emit) {
+          const bool have = cursor < nEm && sEmPos[cursor * PE_SLOTS] == p;
+          const int k = cursor;
+          if (have) ++cursor;
+          if (vb) {  // valid_ on the whole path: interval = timeRange (body-pair-collision.cc:51-55)
+            if (ihi > L) smallest = p;
+            ilo = (ilo < 0.0) ? 0.0 : ilo;
+            ihi = (L < ihi) ? L : ihi;
+            if (have) ++discarded;
+          } else if (l <= ilo && ihi <= h) {  // validInterval_ contains the running interval (:56-63)
+            if (have) ++discarded;
+          } else if (have) {
+            const double a = sResAAll[k * PE_SLOTS + lane], b = sResBAll[k * PE_SLOTS + lane];
+            if (b == -INF) {  // collision: a carries the geometry pair (computeDistanceLowerBound :186-189)
+              finishEdge(false, HPPB200_REASON_COLLISION, t, lastValid, (int)a);
+              more = false;
+            } else if (!(l > h) && (h < a || b < l)) {
+              // validInterval_.insert (:90) would open a second interval: hand the edge to the walker
+              ++overflows;
+              finishEdge(false, A.overflow_reason, t, lastValid, -1);
+              more = false;
             } else {
-              consume = have;  // else: the reference evaluates this pair now and its result is not there yet
-              scanning = false;
+              double nl = a, nh = b;
+              if (!(l > h)) { nl = (a < l) ? a : l; nh = (h > b) ? h : b; }
+              sLo[id * PE_SLOTS] = nl;
+              sHi[id * PE_SLOTS] = nh;
+              if (nl <= 0.0 && L <= nh) sValid[(id >> 5) * PE_SLOTS] |= 1u << (id & 31);  // :92-96
+              // validateIntervals: fold into the running intersection
+              if (ihi > b) smallest = p;
+              ilo = (ilo < a) ? a : ilo;
+              ihi = (b < ihi) ? b : ihi;
             }
-          }
-        }
-      }
-      if (!consume) run = false;
-      if (!__any_sync(FULL, consume)) break;
-      if (consume) {
-        const double a = sResAAll[k * PE_SLOTS + lane], b = sResBAll[k * PE_SLOTS + lane];
-        if (b == -INF) {  // collision: a carries the geometry pair (computeDistanceLowerBound :186-189)
-          finishEdge(false, HPPB200_REASON_COLLISION, t, lastValid, (int)a);
-          run = false;
-        } else {
-          // validInterval_.insert (:90): the set stays one closed interval, else hand the edge over
-          const double l = sLo[id * PE_SLOTS], h = sHi[id * PE_SLOTS];
-          if (!(l > h) && (h < a || b < l)) {  // a second, disjoint interval
-            ++overflows;
-            finishEdge(false, A.overflow_reason, t, lastValid, -1);
-            run = false;
           } else {
-            double nl = a, nh = b;
-            if (!(l > h)) { nl = (a < l) ? a : l; nh = (h > b) ? h : b; }
-            sLo[id * PE_SLOTS] = nl;
-            sHi[id * PE_SLOTS] = nh;
-            if (nl <= 0.0 && L <= nh) sValid[(id >> 5) * PE_SLOTS] |= 1u << (id & 31);  // :92-96
-            // validateIntervals: fold into the running intersection
-            if (ihi > b) smallest = pos;
-            ilo = (ilo < a) ? a : ilo;
-            ihi = (b < ihi) ? b : ihi;
-            ++pos;
+            // the reference evaluates this pair now and its result is not there yet
+            emit = true;
+            pos = p;
+            ql = fmax(ilo, t - hp);
+            qh = fmin(ihi, t + hp);
           }
         }
+        if (emit && !vb && (p == pos || !(l <= ql && qh <= h))) {
+          sEmPos[newEm * PE_SLOTS] = (uint8_t)p;
+          if (T.bodypairs[id].has_gjk) { gmask |= 1u << newEm; ++nGl; } else ++nCl;
+          ++newEm;
+        }
+        ++p;
+        more = more && p < NP && newEm < PE_RMAX;
       }
     }
-    if (on) nEm = 0;
-    if (on && active && pos == NP) {
-      // src/continuous-validation.cc:144-146: smallest interval first
+    if (on) nEm = newEm;
+    if (on && active && !emit) {
+      // sample complete.  src/continuous-validation.cc:144-146: smallest interval first
       if (NP > 1 && smallest != 0) {
         const uint8_t a0 = sOrder[0], as = sOrder[smallest * PE_SLOTS];
         sOrder[0] = as;
@@ -239,13 +239,14 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
     }
   };
 
-  for (;;) {
+  for (;;) {  // @region mainloop
     if (warp == 0) {
       // =============================== control phase ===============================================
       ++ticks;
-      replay(active && sampleOpen);
+      bool on = active && sampleOpen;
       for (;;) {
-        // refill: finished lanes pull the next edges (ballot + popc prefix, one atomic per warp)
+        scanPass(on);
+        // refill: finished lanes pull the next edges (ballot + popc prefix, one atomic per warp)  @region refill
         const bool want = !active && !retired;
         const unsigned m = __ballot_sync(FULL, want);
         if (m) {
@@ -287,13 +288,14 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
             }
           }
         }
-        bool adv = active && !sampleOpen;
-        if (!__any_sync(FULL, adv)) break;
-        if (adv) {
+        // next sample of every lane that completed one (or just got an edge)
+        on = active && !sampleOpen;
+        if (!__any_sync(FULL, on)) break;
+        if (on) {
           if (iters >= A.max_iter) {
             ++caps;
             finishEdge(false, HPPB200_REASON_ITER_CAP, t, lastValid, -1);
-            adv = false;
+            on = false;
           } else {
             ++iters;
             ++samples;
@@ -302,9 +304,8 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
             fkDone = false;
           }
         }
-        replay(adv);  // nothing queued yet: completes the sample or stops at the first pair to evaluate
       }
-      // every active lane now waits for the result of the pair at `pos`
+      // every active lane now waits for the result of the pair at `pos`  @region fk
       if (active && !fkDone) {
         // Path::eval -> StraightPath::impl_compute: stored end points are returned bit-exactly
         if (t == 0.0 || L == 0.0) qmode = 0;
@@ -314,29 +315,8 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
         sTAll[lane] = t;
         fkDone = true;
       }
-      // queue the needed pair and the predicted candidates after it, in order: scan, then one warp
-      // prefix sum assigns queue slots (GJK pairs from the front, closed-form pairs from the back)
-      int nGl = 0, nCl = 0;
-      unsigned gmask = 0;
-      {
-        const double ql = fmax(ilo, t - hp), qh = fmin(ihi, t + hp);
-        int p = pos;
-        bool more = active && p < NP;
-        while (__any_sync(FULL, more)) {
-          if (more) {
-            const int id = sOrder[p * PE_SLOTS];
-            const double l = sLo[id * PE_SLOTS], h = sHi[id * PE_SLOTS];
-            const bool skip = validBit(id) || (p != pos && l <= ql && qh <= h);
-            if (!skip) {
-              sEmPos[nEm * PE_SLOTS] = (uint8_t)p;
-              if (T.bodypairs[id].has_gjk) { gmask |= 1u << nEm; ++nGl; } else ++nCl;
-              ++nEm;
-            }
-            ++p;
-            more = p < NP && nEm < PE_RMAX;
-          }
-        }
-      }
+      // one warp prefix sum assigns queue slots: GJK pairs from the front, closed-form pairs from the back  @region emit
+      if (!active) { nEm = 0; nGl = 0; nCl = 0; }
       int gOff = nGl, cOff = nCl;  // inclusive scans
       for (int o = 1; o < 32; o <<= 1) {
         const int g2 = __shfl_up_sync(FULL, gOff, o), c2 = __shfl_up_sync(FULL, cOff, o);
@@ -358,7 +338,7 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
     }
     __syncthreads();
     if (ctl->done) break;
-    // ================================= narrow phase ================================================
+    // ================================= narrow phase ================================================  // @region narrow
     // One body pair per thread: BodyPairCollision::validateConfiguration :65-89 up to the interval
     // [t - (hd + ht), t + (hd + ht)]; a collision is reported as (geometry pair, -inf).
     {
@@ -419,7 +399,7 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
     __syncthreads();
   }
 
-  unsigned ts = __reduce_add_sync(FULL, tests);
+  unsigned ts = __reduce_add_sync(FULL, tests);  // @region stats
   unsigned gi = __reduce_add_sync(FULL, cnt.iterations);
   unsigned gc = __reduce_add_sync(FULL, cnt.cap_hits);
   unsigned sm = __reduce_add_sync(FULL, samples);

@@ -28,3 +28,25 @@ for l in sorted(lines, key=lambda x: -x[0])[:top]:
 print("by stall samples:")
 for l in sorted(lines, key=lambda x: -x[2])[:top]:
     print("%5.1f%% smp %5.1f%% inst  lanes %4.1f  %s:%d  %s" % (100*l[2]/max(tot_s,1), 100*l[0]/max(tot_i,1), l[1]/max(l[0],1), l[3], l[4], l[5]))
+# ---- aggregate by file / line range (kernels_continuous.cu regions) ----
+import collections
+agg = collections.Counter(); aggt = collections.Counter()
+def region(f, ln):
+    if f == "kernels_continuous.cu":
+        for name, a, b in REGIONS:
+            if a <= ln <= b: return name
+        return "kc:other"
+    return f
+REGIONS = []
+try:
+    src = open("/root/repo/hpp-core_b200/csrc/kernels_continuous.cu").read().split("\n")
+    marks = [(i + 1, l.split("@region")[1].strip()) for i, l in enumerate(src) if "@region" in l]
+    for j, (ln, name) in enumerate(marks):
+        REGIONS.append((name, ln, marks[j + 1][0] - 1 if j + 1 < len(marks) else 10**9))
+except Exception:
+    pass
+for l in lines:
+    r = region(l[3], l[4]); agg[r] += l[0]; aggt[r] += l[1]
+print("by region:")
+for r, v in agg.most_common(20):
+    print("%5.1f%% inst  lanes %4.1f  %s" % (100 * v / max(tot_i, 1), aggt[r] / max(v, 1), r))
