@@ -1,0 +1,93 @@
+"""Multi-GPU plumbing for the batched validation path.
+
+One process per GPU (torch.distributed; NCCL on the GPU box, gloo in the CPU tests).  Configurations
+and edges are independent units, so the path shards by contiguous index ranges with the model tables
+replicated; the only exchange is the gather of the per-unit results (validity masks, 1 B per unit, and
+optionally pair indices / parameters).  k-NN shards the NODE matrix by node index and replicates the
+queries: every rank returns its local top-k as (distance, GLOBAL node index) and the candidates are
+merged with the reference's tie rule -- strict `<` in nearestNeighbor::Basic keeps the EARLIER node on
+equal distance (reference src/nearest-neighbor/basic.cc:66,106), i.e. the key is (distance, index).
+
+Nothing here computes a distance or a validity flag: those come from the C ABI on each rank.
+"""
+import numpy as np
+
+
+def shard_range(n, rank, world):
+    """Contiguous index range [begin, end) of `rank`: floor(rank*n/world) .. floor((rank+1)*n/world)."""
+    return (rank * n) // world, ((rank + 1) * n) // world
+
+
+def shard_sizes(n, world):
+    return [shard_range(n, r, world)[1] - shard_range(n, r, world)[0] for r in range(world)]
+
+
+def node_owner_ranges(n_nodes, world):
+    """Node-matrix shards for k-NN: rank r owns global node indices [begin_r, end_r)."""
+    return [shard_range(n_nodes, r, world) for r in range(world)]
+
+
+def all_gather_ragged(local, n_total, group=None):
+    """All-gather per-unit results of a contiguous shard into the full array (every rank gets it).
+
+    `local` is a 1-D or 2-D torch tensor holding this rank's shard (rows = units).  Shards may differ in
+    size by one unit, so they are padded to the largest shard for the collective and trimmed afterwards.
+    """
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    sizes = shard_sizes(n_total, world)
+    assert local.shape[0] == sizes[dist.get_rank(group)], "shard size does not match shard_range()"
+    mx = max(sizes)
+    pad_shape = (mx,) + tuple(local.shape[1:])
+    buf = torch.zeros(pad_shape, dtype=local.dtype, device=local.device)
+    buf[: local.shape[0]] = local
+    out = torch.empty((world * mx,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, buf, group=group)
+    parts = [out[r * mx: r * mx + sizes[r]] for r in range(world)]
+    return torch.cat(parts, dim=0)
+
+
+def merge_topk(dist_parts, idx_parts, k):
+    """k-way merge of per-rank candidates with the reference tie rule.
+
+    dist_parts / idx_parts: lists (one per rank) of arrays [nqueries][k_r]; idx are GLOBAL node indices,
+    -1 marks padding.  Returns (idx [nqueries][k] int64, dist [nqueries][k] float64), nearest first,
+    ordered by the key (distance, node index); padded with -1 / +inf when fewer than k candidates exist.
+    """
+    d = np.concatenate([np.asarray(x, dtype=np.float64) for x in dist_parts], axis=1)
+    i = np.concatenate([np.asarray(x, dtype=np.int64) for x in idx_parts], axis=1)
+    d = np.where(i < 0, np.inf, d)
+    big = np.iinfo(np.int64).max
+    ikey = np.where(i < 0, big, i)
+    order = np.lexsort((ikey, d), axis=1)[:, :k]  # primary distance, secondary node index
+    out_i = np.take_along_axis(i, order, axis=1)
+    out_d = np.take_along_axis(d, order, axis=1)
+    if out_i.shape[1] < k:
+        pad = k - out_i.shape[1]
+        out_i = np.concatenate([out_i, -np.ones((out_i.shape[0], pad), dtype=np.int64)], axis=1)
+        out_d = np.concatenate([out_d, np.full((out_d.shape[0], pad), np.inf)], axis=1)
+    out_d = np.where(out_i < 0, np.inf, out_d)
+    return out_i, out_d
+
+
+def all_gather_topk(local_idx, local_dist, node_offset, k, group=None):
+    """Gather every rank's local top-k (local node indices + distances) and merge.
+
+    local_idx [nqueries][k] int64 are indices into THIS rank's node shard (-1 padded); `node_offset` is
+    the global index of the shard's first node.  Returns the global (idx, dist) on every rank.
+    """
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    li = torch.as_tensor(local_idx, dtype=torch.int64).clone()
+    li[li >= 0] += int(node_offset)
+    ld = torch.as_tensor(local_dist, dtype=torch.float64).clone()
+    nq = li.shape[0]
+    gi = torch.empty((world * nq,) + tuple(li.shape[1:]), dtype=torch.int64, device=li.device)
+    gd = torch.empty((world * nq,) + tuple(ld.shape[1:]), dtype=torch.float64, device=ld.device)
+    dist.all_gather_into_tensor(gi, li.contiguous(), group=group)  # rank-major concatenation along dim 0
+    dist.all_gather_into_tensor(gd, ld.contiguous(), group=group)
+    gi = gi.view((world, nq) + tuple(li.shape[1:])).cpu().numpy()
+    gd = gd.view((world, nq) + tuple(ld.shape[1:])).cpu().numpy()
+    return merge_topk([gd[r] for r in range(world)], [gi[r] for r in range(world)], k)
