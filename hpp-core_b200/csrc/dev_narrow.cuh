@@ -88,82 +88,107 @@ struct GjkCounters {
   unsigned calls, iterations, cap_hits;
 };
 
+// GJK as an explicit state + one-iteration step, so that a kernel can either run it to completion
+// (gjkCoreDistance) or interleave iterations of many jobs and refill finished lanes (kernels_wavefront.cu).
+// The arithmetic is the same expression sequence either way.
+struct GjkState {
+  V3 w0, w1, w2, v;
+  double vv;
+  int n, it;
+};
+
+__device__ __forceinline__ void gjkBegin(GjkState& s, const T3& rel) {
+  s.w0 = mk(0, 0, 0); s.w1 = s.w0; s.w2 = s.w0;
+  s.n = 0;
+  s.it = 0;
+  s.v = -rel.t;
+  s.vv = dot(s.v, s.v);
+  if (s.vv == 0) { s.v = mk(1, 0, 0); s.vv = 1; }
+}
+
+// One iteration.  Returns true when the algorithm has terminated; `out` is then the distance between
+// the core shapes (0 when they intersect) and s.it the number of iterations minus one.
+__device__ __forceinline__ bool gjkStep(GjkState& s, const DevShape& A, const DevShape& B, const T3& rel,
+                                        const double* __restrict__ verts, double& out) {
+  const V3 v = s.v;
+  const double vv = s.vv;
+  const int n = s.n;
+  const V3 w0 = s.w0, w1 = s.w1, w2 = s.w2;
+  V3 sa = supportLocal(A, verts, -v);
+  V3 sbl = supportLocal(B, verts, rtmul(rel, v));
+  V3 sb = rmul(rel, sbl) + rel.t;
+  V3 w = sa - sb;
+  double vw = dot(v, w);
+  bool stop = (n > 0 && (vv - vw) <= HPPB200_GJK_EPS_REL * vv);
+  bool dup = false;
+  if (n > 0 && w0.x == w.x && w0.y == w.y && w0.z == w.z) dup = true;
+  if (n > 1 && w1.x == w.x && w1.y == w.y && w1.z == w.z) dup = true;
+  if (n > 2 && w2.x == w.x && w2.y == w.y && w2.z == w.z) dup = true;
+  if (stop || dup) { out = sqrt(vv); return true; }
+  // tentative simplex T = S + {w}
+  V3 t0 = w0, t1 = w1, t2 = w2;
+  int tn;
+  V3 nv;
+  bool inside = false;
+  if (n == 0) { t0 = w; tn = 1; nv = w; }
+  else if (n == 1) {
+    // segment A = w0 (old), B = w (new)
+    V3 d = w - w0;
+    double dd = dot(d, d);
+    double sp = -dot(w0, d);
+    if (dd == 0 || sp >= dd) { t0 = w; tn = 1; nv = w; }
+    else if (sp <= 0) { tn = 1; nv = w0; }
+    else { double r = sp / dd; t1 = w; tn = 2; nv = axpy(r, d, w0); }
+  } else if (n == 2) {
+    closestTriangle(w0, w1, w, t0, t1, t2, tn, nv);
+  } else {
+    // tetrahedron (w0,w1,w2,w): Ericson §5.1.6, all four faces
+    double best = CUDART_INF;
+    bool any = false;
+    tn = 0; nv = v;
+#pragma unroll
+    for (int f = 0; f < 4; ++f) {
+      V3 a, b, c, d;
+      if (f == 0) { a = w0; b = w1; c = w2; d = w; }
+      else if (f == 1) { a = w0; b = w1; c = w; d = w2; }
+      else if (f == 2) { a = w0; b = w2; c = w; d = w1; }
+      else { a = w1; b = w2; c = w; d = w0; }
+      V3 nn = cross(b - a, c - a);
+      double sp = -dot(a, nn);
+      double sd = dot(d - a, nn);
+      if (sd == 0 || sp * sd < 0) {
+        V3 q0, q1, q2, qv;
+        q0 = q1 = q2 = a;
+        int qn;
+        closestTriangle(a, b, c, q0, q1, q2, qn, qv);
+        double qq = dot(qv, qv);
+        if (qq < best) { best = qq; t0 = q0; t1 = q1; t2 = q2; tn = qn; nv = qv; }
+        any = true;
+      }
+    }
+    inside = !any;
+  }
+  if (inside) { out = 0.0; return true; }
+  double nvv = dot(nv, nv);
+  if (nvv <= HPPB200_GJK_EPS_ABS2) { out = 0.0; return true; }
+  if (n > 0 && nvv >= vv) { out = sqrt(vv); return true; }  // no progress: keep previous closest point
+  s.w0 = t0; s.w1 = t1; s.w2 = t2; s.n = tn; s.v = nv; s.vv = nvv;
+  s.it += 1;
+  if (s.it == HPPB200_GJK_MAX_ITER) { out = sqrt(nvv); return true; }
+  return false;
+}
+
 // Distance between core shapes; `rel` = placement of B in A's frame.  0 when cores intersect.
 static __device__ __noinline__ double gjkCoreDistance(const DevShape& A, const DevShape& B, const T3& rel,
                                                const double* __restrict__ verts, GjkCounters& cnt) {
-  V3 w0 = mk(0, 0, 0), w1 = w0, w2 = w0, w3 = w0;
-  int n = 0;
-  V3 v = -rel.t;
-  double vv = dot(v, v);
-  if (vv == 0) { v = mk(1, 0, 0); vv = 1; }
-  int it = 0;
-  double result = -1.0;
-  for (; it < HPPB200_GJK_MAX_ITER; ++it) {
-    V3 sa = supportLocal(A, verts, -v);
-    V3 sbl = supportLocal(B, verts, rtmul(rel, v));
-    V3 sb = rmul(rel, sbl) + rel.t;
-    V3 w = sa - sb;
-    double vw = dot(v, w);
-    if (n > 0 && (vv - vw) <= HPPB200_GJK_EPS_REL * vv) break;
-    bool dup = false;
-    if (n > 0 && w0.x == w.x && w0.y == w.y && w0.z == w.z) dup = true;
-    if (n > 1 && w1.x == w.x && w1.y == w.y && w1.z == w.z) dup = true;
-    if (n > 2 && w2.x == w.x && w2.y == w.y && w2.z == w.z) dup = true;
-    if (dup) break;
-    // tentative simplex T = S + {w}
-    V3 t0 = w0, t1 = w1, t2 = w2;
-    int tn;
-    V3 nv;
-    bool inside = false;
-    if (n == 0) { t0 = w; tn = 1; nv = w; }
-    else if (n == 1) {
-      // segment A = w0 (old), B = w (new)
-      V3 d = w - w0;
-      double dd = dot(d, d);
-      double s = -dot(w0, d);
-      if (dd == 0 || s >= dd) { t0 = w; tn = 1; nv = w; }
-      else if (s <= 0) { tn = 1; nv = w0; }
-      else { double r = s / dd; t1 = w; tn = 2; nv = axpy(r, d, w0); }
-    } else if (n == 2) {
-      closestTriangle(w0, w1, w, t0, t1, t2, tn, nv);
-    } else {
-      // tetrahedron (w0,w1,w2,w): Ericson §5.1.6, all four faces
-      double best = CUDART_INF;
-      bool any = false;
-      tn = 0; nv = v;
-#pragma unroll
-      for (int f = 0; f < 4; ++f) {
-        V3 a, b, c, d;
-        if (f == 0) { a = w0; b = w1; c = w2; d = w; }
-        else if (f == 1) { a = w0; b = w1; c = w; d = w2; }
-        else if (f == 2) { a = w0; b = w2; c = w; d = w1; }
-        else { a = w1; b = w2; c = w; d = w0; }
-        V3 nn = cross(b - a, c - a);
-        double sp = -dot(a, nn);
-        double sd = dot(d - a, nn);
-        if (sd == 0 || sp * sd < 0) {
-          V3 q0, q1, q2, qv;
-          q0 = q1 = q2 = a;
-          int qn;
-          closestTriangle(a, b, c, q0, q1, q2, qn, qv);
-          double qq = dot(qv, qv);
-          if (qq < best) { best = qq; t0 = q0; t1 = q1; t2 = q2; tn = qn; nv = qv; }
-          any = true;
-        }
-      }
-      inside = !any;
-    }
-    if (inside) { result = 0.0; break; }
-    double nvv = dot(nv, nv);
-    if (nvv <= HPPB200_GJK_EPS_ABS2) { result = 0.0; break; }
-    if (n > 0 && nvv >= vv) break;  // no progress: keep previous closest point
-    w0 = t0; w1 = t1; w2 = t2; n = tn; v = nv; vv = nvv;
-  }
+  GjkState s;
+  gjkBegin(s, rel);
+  double out;
+  while (!gjkStep(s, A, B, rel, verts, out)) {}
   cnt.calls += 1;
-  cnt.iterations += it + 1;
-  if (it == HPPB200_GJK_MAX_ITER) cnt.cap_hits += 1;
-  if (result == 0.0) return 0.0;
-  return sqrt(vv);
+  cnt.iterations += s.it + 1;
+  if (s.it == HPPB200_GJK_MAX_ITER) cnt.cap_hits += 1;
+  return out;
 }
 
 __device__ __forceinline__ double clamp01(double x) { return x < 0 ? 0 : (x > 1 ? 1 : x); }

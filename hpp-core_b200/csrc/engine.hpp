@@ -143,7 +143,9 @@ struct Workspace {
   uint32_t max_iterations = 1u << 20;
   bool use_engine = true;      // Progressive: control/narrow-phase engine (HPPB200_ENGINE=0 forces the walker)
   int engine_threads = 128;    // CTA size of the engine (HPPB200_ENGINE_THREADS: 64 | 96 | 128)
-  double engine_alpha = 2.0;   // candidate prediction: alpha x previous step (HPPB200_ENGINE_ALPHA)
+  int engine_kind = 2;         // Progressive: 2 wavefront rounds (kernels_wavefront.cu), 1 CTA engine (HPPB200_ENGINE)
+  size_t wavefront_slots = 0;  // resident edge slots of the wavefront engine (0: 2048 per SM; HPPB200_WF_SLOTS)
+  double engine_alpha = 1.2;   // candidate prediction: alpha x previous step (HPPB200_ENGINE_ALPHA; 1.2 measured best)
   // staging for host-pointer calls
   DeviceBuffer<double> d_q, d_q2, d_L, d_tfail, d_tlast, d_scratch;
   DeviceBuffer<uint8_t> d_valid, d_reason, d_reason_int;
@@ -171,6 +173,9 @@ void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2
 bool launchProgressiveEngine(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
                              const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                              int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
+bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
+                                const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
+                                int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
 void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1,
                          const double* d_q2, const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid,
                          double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason);

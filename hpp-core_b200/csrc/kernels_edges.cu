@@ -642,7 +642,10 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   // Progressive on models whose per-edge state fits in shared memory: the control/narrow-phase
   // engine of kernels_continuous.cu.  Anything else: the generic walker below.
   bool engineDone = false;
-  if (method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine)
+  if (method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine && ws->engine_kind >= 2)
+    engineDone = launchWavefrontProgressive(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair,
+                                            d_reason, REASON_OVERFLOW_INTERNAL);
+  if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine)
     engineDone = launchProgressiveEngine(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,
                                          REASON_OVERFLOW_INTERNAL);
   if (!engineDone) {

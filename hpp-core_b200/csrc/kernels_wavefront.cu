@@ -1,0 +1,879 @@
+// Wavefront engine for continuousValidation::Progressive over many StraightPath edges
+// (reference src/continuous-validation/progressive.cc:78-129): the production path for large batches.
+//
+// The sequential algorithm per edge is: sample t -> FK -> walk the body pairs in the current order,
+// skipping those whose validated interval already covers the running interval, evaluating the others
+// (narrow phase + velocity bound => validated interval) -> t = end of the intersection -> next sample.
+// One sample of one edge is little work, samples of one edge are strictly ordered, but edges are
+// independent.  So the engine advances ALL resident edges by (at most) one sample per ROUND, and every
+// round is two uniform kernels with their own register budget and occupancy:
+//
+//   wfControlKernel  one thread per edge slot.  REPLAY: follows validateIntervals
+//       (include/hpp/core/continuous-validation.hh:267-298) and BodyPairCollision::validateConfiguration
+//       (src/continuous-validation/body-pair-collision.cc:45-99) over the pair positions, consuming the
+//       distances computed last round.  If every pair the reference evaluates had its distance, the sample
+//       is complete: smallest-interval-first swap (src/continuous-validation.cc:144-146), t advances
+//       (progressive.cc:104-117), the edge finishes (slot refilled from the global edge counter, ballot +
+//       prefix sums) or FK runs for the next sample.  EMIT: the pair the reference evaluates next plus the
+//       predicted candidates after it are appended to the job lists (one job per GEOMETRY pair).
+//   wfNarrowKernel   one thread per job.  GJK jobs run one iteration per loop trip and finished lanes are
+//       refilled from the job list (iteration-level refill keeps warps full although iteration counts
+//       differ); closed-form jobs are one thread each.  Result = distance_lower_bound of the pair, 8 bytes.
+//
+// Which tests to queue is a PREDICTION; what the results mean is decided by the replay, which follows the
+// reference order exactly: a pair the reference skips is skipped even if its distance was
+// computed, a pair it evaluates whose distance is missing stops the replay until next round.  The distance
+// of (edge, t, pair) is a pure function, so flags, parameters and intervals are bit-identical to the
+// sequential algorithm whatever was predicted.
+//
+// State lives in global memory, position-major SoA over the slots (coalesced for the thread-per-slot scan):
+// the validated interval and pair id are stored BY ORDER POSITION and swapped together, so the scan reads
+// lohi[p][slot] without an indirection.  valid_ (whole path validated) is encoded as lo = -inf.
+// Progressive keeps each pair's validated set connected, so one closed interval per pair;
+// an insert that would open a second interval hands the edge to the walker (never silently accepted).
+// Placements: AoS per slot (96 contiguous bytes per geometry, read by the jobs).
+#include <cstdio>
+#include <cstdlib>
+#include <vector>
+
+#include "dev_model.cuh"
+
+namespace hppb200 {
+
+constexpr int WF_RB = 12;       // body pairs emitted per slot per round
+constexpr int WF_RG = 16;       // geometry-pair jobs (= result slots) per slot per round
+constexpr int WF_CTHREADS = 128;
+constexpr int WF_NTHREADS = 128;
+constexpr int WF_CHUNK = 128;   // jobs a warp takes from the list per atomic
+
+struct WFRoundCtl {
+  unsigned nG, nC, headG, headC;
+};
+
+struct WFArgs {
+  const double* q1;
+  const double* q2;
+  const double* L;
+  size_t n;
+  int reverse;
+  double tol;
+  uint32_t max_iter;
+  uint8_t* valid;
+  double* t_fail;
+  double* t_last;
+  int32_t* pair;
+  uint8_t* reason;
+  int overflow_reason;
+  double alpha;
+  unsigned long long* counter;  // next edge to hand out
+  uint32_t E;                   // edge slots
+  int fkSlots;
+  double2* lohi;       // [NP][E] by order position
+  uint16_t* ord;       // [E][ordStride] pair id at order position, one record per slot (its reads stay in L1)
+  uint32_t ordStride;  // NP rounded up to 16 entries (32 bytes)
+  double* vmax;        // [NP][E] by pair id: SolidSolidCollision::computeMaximalVelocity, fixed per edge
+  double* sv;          // [nv][E] per-joint velocity norms (refill scratch)
+  double* st_t;        // [E] ...
+  double* st_last;
+  double* st_hp;
+  double* st_ilo;
+  double* st_ihi;
+  double* st_L;
+  uint32_t* st_edge;
+  uint32_t* st_iters;
+  uint32_t* st_pos;    // pos | smallest << 16
+  uint8_t* st_flags;   // bit0 active, bit1 retired, bits 2-3 `finished`
+  uint8_t* st_nEm;
+  unsigned long long* st_vmask;  // [W][E] valid_ bits by order position
+  uint16_t* emPos;     // [WF_RB][E] order position of the k-th emitted body pair
+  uint8_t* emRes;      // [WF_RB][E] its first result slot
+  double2* fold;       // [WF_RB][E] its folded result: validated interval (a, b), or (geometry pair, -inf)
+  double* res;         // [WF_RG][E]
+  double* plc;         // [E][fkSlots*12]
+  unsigned long long* jobsG;  // [E*WF_RG]
+  unsigned long long* jobsC;
+  WFRoundCtl* ctl;     // [2], by round parity
+  unsigned* alive;     // [rounds per batch]
+  int round;           // global round number
+  int aliveIdx;
+  int refill_min;      // idle lanes in a warp before new GJK jobs are fetched (32 = whole-warp batches)
+};
+
+// ------------------------------------------------------------------------------------------------
+// Control kernel: one thread per edge slot.  ONE scan over the pair positions per round:
+//   REPLAY mode  folds the distances computed last round exactly like validateIntervals and, position by
+//                position, marks the candidates of the NEXT sample (predicted from the running intersection);
+//   EMIT mode    (after the first pair the reference evaluates whose distance is missing) marks the
+//                candidates of the CURRENT sample from that pair on.
+// The interval stream lohi[p][slot] is moved global -> shared with cp.async, two chunks of WF_CH positions
+// in flight per thread, so a scan exposes NP / WF_CH memory latencies instead of NP.
+// shared memory: [0,8) mbarrier | [16,48) block counters | chunk ring | model blob prefix
+constexpr int WF_CH = 4;
+constexpr uint32_t WF_RING_BYTES = 2u * WF_CH * WF_CTHREADS * 16u;
+
+__device__ __forceinline__ void cpAsync16(void* sdst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(sdst)), "l"(gsrc)
+               : "memory");
+}
+__device__ __forceinline__ void cpAsyncCommit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cpAsyncWait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// position bit masks, W 64-bit words (W = 1 covers UR5-class models: one shift per update)
+typedef unsigned long long u64;
+template <int W>
+__device__ __forceinline__ bool maskGet(const u64 (&m)[W], int p) {
+  if (W == 1) return (m[0] >> p) & 1ull;
+  bool r = false;
+#pragma unroll
+  for (int w = 0; w < W; ++w)
+    if ((p >> 6) == w) r = (m[w] >> (p & 63)) & 1ull;
+  return r;
+}
+template <int W>
+__device__ __forceinline__ void maskSet(u64 (&m)[W], int p, bool v) {  // OR the bit in
+  if (W == 1) { m[0] |= (u64)(v ? 1 : 0) << p; return; }
+#pragma unroll
+  for (int w = 0; w < W; ++w)
+    if ((p >> 6) == w) m[w] |= (u64)(v ? 1 : 0) << (p & 63);
+}
+template <int W>
+__device__ __forceinline__ void maskPut(u64 (&m)[W], int p, bool v) {  // overwrite the bit
+  if (W == 1) { m[0] = (m[0] & ~(1ull << p)) | ((u64)(v ? 1 : 0) << p); return; }
+#pragma unroll
+  for (int w = 0; w < W; ++w)
+    if ((p >> 6) == w) m[w] = (m[w] & ~(1ull << (p & 63))) | ((u64)(v ? 1 : 0) << (p & 63));
+}
+
+template <int W>
+__global__ void __launch_bounds__(WF_CTHREADS)
+wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
+  extern __shared__ __align__(16) unsigned char smem[];  // @region setup
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned* sCnt = (unsigned*)(smem + 16);  // 0 nG, 1 nC, 2 baseG, 3 baseC, 4 samples, 5 discarded, 6 caps, 7 overflows
+  double2* ring = (double2*)(smem + 48) + threadIdx.x;  // entry (buffer b, k) at ring[(b * WF_CH + k) * WF_CTHREADS]
+  unsigned char* sblob = smem + 48 + WF_RING_BYTES;
+  if (threadIdx.x < 8) sCnt[threadIdx.x] = 0u;
+  stageBlobTMA(sblob, mv.blob, mv.edge_blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+
+  const unsigned FULL = 0xffffffffu;
+  const uint32_t E = A.E;
+  const uint32_t e = blockIdx.x * WF_CTHREADS + threadIdx.x;  // E is a multiple of the CTA size
+  const int lane = threadIdx.x & 31;
+  const int NP = mv.nbodypairs;
+  const double INF = CUDART_INF;
+  const bool reverse = A.reverse != 0;
+  WFRoundCtl* ctl = A.ctl + (A.round & 1);
+  if (e == 0) {  // the other parity was consumed by the previous round's narrow phase
+    WFRoundCtl* nx = A.ctl + ((A.round + 1) & 1);
+    nx->nG = 0; nx->nC = 0; nx->headG = 0; nx->headC = 0;
+  }
+
+  const uint8_t flags0 = A.st_flags[e];
+  bool active = (flags0 & 1) != 0, retired = (flags0 & 2) != 0;
+  int finished = (flags0 >> 2) & 3;
+  double t = 0, lastValid = 0, hp = INF, ilo = -INF, ihi = INF, L = 0;
+  uint32_t edge = 0, iters = 0;
+  int pos = 0, smallest = 0, nEm = 0;
+  if (active) {
+    t = A.st_t[e]; lastValid = A.st_last[e]; hp = A.st_hp[e]; ilo = A.st_ilo[e]; ihi = A.st_ihi[e]; L = A.st_L[e];
+    edge = A.st_edge[e]; iters = A.st_iters[e];
+    const uint32_t ps = A.st_pos[e];
+    pos = (int)(ps & 0xffffu); smallest = (int)(ps >> 16);
+    nEm = A.st_nEm[e];
+  }
+  unsigned samples = 0, caps = 0, overflows = 0, discarded = 0;
+  bool needSample = false, needFK = false;
+  u64 cand[W], vmask[W];  // by order position: candidate for the next narrow phase / valid_
+#pragma unroll
+  for (int w = 0; w < W; ++w) { cand[w] = 0ull; vmask[w] = active ? A.st_vmask[(size_t)w * E + e] : 0ull; }
+
+  auto finishEdge = [&](bool ok, int rs, double tf, double tl, int pr) {
+    A.valid[edge] = ok ? 1 : 0;
+    if (A.t_fail) A.t_fail[edge] = tf;
+    if (A.t_last) A.t_last[edge] = tl;
+    if (A.pair) A.pair[edge] = pr;
+    if (A.reason) A.reason[edge] = (uint8_t)rs;
+    active = false;
+  };
+
+  // ---- the scan ---------------------------------------------------------------------------------  @region scan
+  if (active) {
+    int cursor = 0;
+    int nextP = nEm > 0 ? (int)A.emPos[e] : -1;
+    bool emit = false, stop = false;
+    double ql = 0, qh = 0;
+    const double2* src = A.lohi + e;
+    auto issue = [&](int c0, int b) {  // chunk starting at position c0 into ring buffer b (valid_ positions need no data)
+#pragma unroll
+      for (int k = 0; k < WF_CH; ++k)
+        if (c0 + k < NP && !maskGet<W>(vmask, c0 + k)) cpAsync16(ring + (b * WF_CH + k) * WF_CTHREADS, src + (size_t)(c0 + k) * E);
+      cpAsyncCommit();
+    };
+    issue(pos, 0);
+    int b = 0;
+    for (int c0 = pos; c0 < NP && !stop; c0 += WF_CH, b ^= 1) {
+      issue(c0 + WF_CH, b ^ 1);  // (an empty group past the end)
+      cpAsyncWait<1>();
+      const int cend = (c0 + WF_CH < NP) ? c0 + WF_CH : NP;
+      for (int p = c0; p < cend; ++p) {
+        if (maskGet<W>(vmask, p)) {
+          // valid_ on the whole path: interval = timeRange (body-pair-collision.cc:51-55).  Never a candidate,
+          // so never has a queued result.
+          if (!emit) {
+            if (ihi > L) smallest = p;
+            ilo = (ilo < 0.0) ? 0.0 : ilo;
+            ihi = (L < ihi) ? L : ihi;
+          }
+          continue;
+        }
+        const double2 lh = ring[(b * WF_CH + (p - c0)) * WF_CTHREADS];
+        if (emit) {
+          maskSet<W>(cand, p, !(lh.x <= ql && qh <= lh.y));
+          continue;
+        }
+        const bool have = nextP == p;
+        const int k = cursor;
+        if (have) {
+          ++cursor;
+          nextP = cursor < nEm ? (int)A.emPos[(size_t)cursor * E + e] : -1;
+        }
+        double nl = lh.x, nh = lh.y;  // this pair's validated interval after this position
+        if (lh.x <= ilo && ihi <= lh.y) {  // validInterval_ contains the running interval (:56-63)
+          if (have) ++discarded;
+        } else if (have) {
+          const double2 rr = A.fold[(size_t)k * E + e];
+          const double a = rr.x, bb = rr.y;
+          if (bb == -INF) {  // collision: a carries the geometry pair
+            finishEdge(false, HPPB200_REASON_COLLISION, t, lastValid, (int)a);
+            stop = true;
+            break;
+          }
+          const double l = lh.x, h = lh.y;
+          if (!(l > h) && (h < a || bb < l)) {
+            // validInterval_.insert (:90) would open a second interval: hand the edge to the walker
+            ++overflows;
+            finishEdge(false, A.overflow_reason, t, lastValid, -1);
+            stop = true;
+            break;
+          }
+          nl = a; nh = bb;
+          if (!(l > h)) { nl = (a < l) ? a : l; nh = (h > bb) ? h : bb; }
+          if (nl <= 0.0 && L <= nh) { nl = -INF; nh = INF; maskSet<W>(vmask, p, true); }  // valid_ (:92-96)
+          A.lohi[(size_t)p * E + e] = make_double2(nl, nh);
+          if (ihi > bb) smallest = p;  // validateIntervals: fold into the running intersection
+          ilo = (ilo < a) ? a : ilo;
+          ihi = (bb < ihi) ? bb : ihi;
+        } else {
+          // the reference evaluates this pair now and its distance is not there yet
+          emit = true;
+          pos = p;
+          ql = fmax(ilo, t - hp);
+          qh = fmin(ihi, t + hp);
+#pragma unroll
+          for (int w = 0; w < W; ++w) cand[w] = 0ull;
+          maskSet<W>(cand, p, true);
+          continue;
+        }
+        // candidate of the NEXT sample: predicted t' = end of the running intersection, window alpha x step
+        const double tn = reverse ? ilo : ihi;
+        const double hn = A.alpha * fabs(tn - t);
+        maskSet<W>(cand, p, !(nl <= tn - hn && tn + hn <= nh));
+      }
+    }
+    cpAsyncWait<0>();
+    if (active && !emit) {
+      // sample complete.  src/continuous-validation.cc:144-146: smallest interval first
+      if (NP > 1 && smallest != 0) {
+        const size_t i0 = e, is = (size_t)smallest * E + e;
+        const double2 x0 = A.lohi[i0], xs = A.lohi[is];
+        uint16_t* od = A.ord + (size_t)e * A.ordStride;
+        const uint16_t o0 = od[0], os = od[smallest];
+        A.lohi[i0] = xs; A.lohi[is] = x0;
+        od[0] = os; od[smallest] = o0;
+        const bool c0 = maskGet<W>(cand, 0), cs = maskGet<W>(cand, smallest);
+        maskPut<W>(cand, 0, cs); maskPut<W>(cand, smallest, c0);
+        const bool v0 = maskGet<W>(vmask, 0), vs = maskGet<W>(vmask, smallest);
+        maskPut<W>(vmask, 0, vs); maskPut<W>(vmask, smallest, v0);
+      }
+      // progressive.cc:104-117
+      const double tprev = t;
+      t = reverse ? ilo : ihi;
+      lastValid = tprev;
+      hp = A.alpha * fabs(t - tprev);
+      if (reverse ? t <= 0.0 : t >= L) { t = reverse ? 0.0 : L; finished++; }
+      if (finished >= 2) finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+      else {
+        needSample = true;
+        // the first non-valid pair of the new order is evaluated by the reference for sure
+        int first = -1;
+#pragma unroll
+        for (int w = W - 1; w >= 0; --w) {
+          const u64 nv = ~vmask[w];
+          if (nv) first = w * 64 + __ffsll((long long)nv) - 1;
+        }
+        if (first >= 0 && first < NP) maskPut<W>(cand, first, true);
+#pragma unroll
+        for (int w = 0; w < W; ++w) cand[w] &= ~vmask[w];
+      }
+    }
+  }
+
+  // ---- REFILL: free slots pull the next edges (ballot + popc prefix, one atomic per warp) --------  @region refill
+  {
+    const bool want = !active && !retired;
+    const unsigned m = __ballot_sync(FULL, want);
+    if (m) {
+      const int leader = __ffs(m) - 1;
+      unsigned long long b = 0;
+      if (lane == leader) b = atomicAdd(A.counter, (unsigned long long)__popc(m));
+      b = __shfl_sync(FULL, b, leader);
+      bool got = false;
+      if (want) {
+        const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
+        if (idx >= A.n) retired = true;
+        else {
+          edge = (uint32_t)idx;
+          const double* q1 = A.q1 + (size_t)edge * mv.nq;
+          const double* q2 = A.q2 + (size_t)edge * mv.nq;
+          L = A.L[edge];
+          iters = 0;
+          finished = 0;
+          lastValid = reverse ? L : 0.0;
+          t = lastValid;
+          hp = INF;
+          if (reverse ? t <= 0.0 : t >= L) finished++;
+#pragma unroll
+          for (int w = 0; w < W; ++w) {
+            vmask[w] = 0ull;
+            const int left = NP - 64 * w;
+            cand[w] = left >= 64 ? ~0ull : (left > 0 ? (1ull << left) - 1ull : 0ull);
+          }
+          active = true;
+          needSample = true;
+          got = true;
+        }
+      }
+      // per-edge tables of the new edges, the whole warp working on one new edge at a time (lane = joint, then
+      // lane = body pair): intervals empty, order = construction order, velocity norms, maximal velocities
+      unsigned gm = __ballot_sync(FULL, got);
+      while (gm) {
+        const int srcLane = __ffs(gm) - 1;
+        gm &= gm - 1u;
+        const uint32_t es = e - (uint32_t)lane + (uint32_t)srcLane;
+        const uint32_t ed = __shfl_sync(FULL, edge, srcLane);
+        const double Ls = __shfl_sync(FULL, L, srcLane);
+        const double* q1 = A.q1 + (size_t)ed * mv.nq;
+        const double* q2 = A.q2 + (size_t)ed * mv.nq;
+        if (Ls != 0) {
+          // per-joint norms of Vb = |q2 - q1| / L (StraightPath::impl_velocityBound, straight-path.cc:132-140)
+          for (int j = lane; j < mv.njoints; j += 32) {
+            const DevJoint& J = T.joints[j];
+            const int nvj = J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1;
+            double sj = 0;
+            for (int k = 0; k < nvj; ++k) {
+              const double vb = fabs(q2[J.idx_v + k] - q1[J.idx_v + k]) / Ls;
+              sj = fma(vb, vb, sj);
+            }
+            A.sv[(size_t)J.idx_v * E + es] = sqrt(sj);
+          }
+        }
+        __syncwarp();
+        // SolidSolidCollision::computeMaximalVelocity (solid-solid-collision.cc:76-99), fixed per edge and pair
+        for (int id = lane; id < NP; id += 32) {
+          const DevBodyPair& B = T.bodypairs[id];
+          double Vm;
+          if (Ls == 0) Vm = INF;  // BodyPairCollision::setupPath, zero-length path
+          else {
+            double ab = 0;
+            for (int c = B.coef_begin; c < B.coef_end; ++c) ab += T.coefs[c].value * __ldcg(A.sv + (size_t)T.coefs[c].idx_v * E + es);
+            Vm = ab;
+            if (B.joint_b != 0) {
+              double ba = 0;
+              for (int c = B.rcoef_begin; c < B.rcoef_end; ++c) ba += T.rcoefs[c].value * __ldcg(A.sv + (size_t)T.rcoefs[c].idx_v * E + es);
+              if (ba < ab) Vm = ba;
+            }
+          }
+          A.vmax[(size_t)id * E + es] = Vm;
+          A.lohi[(size_t)id * E + es] = make_double2(INF, -INF);
+          A.ord[(size_t)es * A.ordStride + id] = (uint16_t)id;
+        }
+      }
+      __syncwarp();
+    }
+  }
+
+  // ---- next sample ---------------------------------------------------------------------------------  @region sample
+  if (needSample) {
+    if (iters >= A.max_iter) {
+      ++caps;
+      finishEdge(false, HPPB200_REASON_ITER_CAP, t, lastValid, -1);
+    } else {
+      ++iters;
+      ++samples;
+      pos = 0; smallest = 0; ilo = -INF; ihi = INF; nEm = 0;
+      needFK = true;  // wfFkKernel computes the placements at t
+    }
+  }
+
+  // ---- EMIT: one job per geometry pair of every candidate, in position order -------------------------  @region emit
+  uint32_t jl[WF_RG];  // geometry pair | GJK flag << 31, in result order
+  int nr = 0, nGl = 0, nCl = 0;
+  if (active) {
+    int nb = 0;
+    bool full = false;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      u64 mw = cand[w];
+      while (mw && !full) {
+        const int p = w * 64 + __ffsll((long long)mw) - 1;
+        mw &= mw - 1ull;
+        const int id = A.ord[(size_t)e * A.ordStride + p];
+        const DevBodyPair& B = T.bodypairs[id];
+        const int ng = B.pair_end - B.pair_begin;
+        if (nb >= WF_RB || nr + ng > WF_RG) { full = true; break; }
+        A.emPos[(size_t)nb * E + e] = (uint16_t)p;
+        A.emRes[(size_t)nb * E + e] = (uint8_t)nr;
+        for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
+          const bool g = T.bgpairs[gp].kind == PK_GJK;
+          jl[nr++] = (uint32_t)gp | (g ? 0x80000000u : 0u);
+          if (g) ++nGl; else ++nCl;
+        }
+        ++nb;
+      }
+    }
+    nEm = nb;
+  }
+  // job list slots: warp prefix sums, one shared-memory atomic per warp, one global atomic per CTA
+  {
+    int gOff = nGl, cOff = nCl;  // inclusive scans
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int g2 = __shfl_up_sync(FULL, gOff, o), c2 = __shfl_up_sync(FULL, cOff, o);
+      if (lane >= o) { gOff += g2; cOff += c2; }
+    }
+    unsigned wG = 0, wC = 0;
+    if (lane == 31) {
+      wG = gOff ? atomicAdd(&sCnt[0], (unsigned)gOff) : 0u;
+      wC = cOff ? atomicAdd(&sCnt[1], (unsigned)cOff) : 0u;
+    }
+    wG = __shfl_sync(FULL, wG, 31);
+    wC = __shfl_sync(FULL, wC, 31);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      sCnt[2] = sCnt[0] ? atomicAdd(&ctl->nG, sCnt[0]) : 0u;
+      sCnt[3] = sCnt[1] ? atomicAdd(&ctl->nC, sCnt[1]) : 0u;
+    }
+    __syncthreads();
+    size_t gi = (size_t)sCnt[2] + wG + (unsigned)(gOff - nGl);
+    size_t ci = (size_t)sCnt[3] + wC + (unsigned)(cOff - nCl);
+    for (int i = 0; i < nr; ++i) {
+      const uint32_t j = jl[i];
+      const unsigned long long job =
+          (unsigned long long)e | ((unsigned long long)(j & 0x00ffffffu) << 32) | ((unsigned long long)i << 56);
+      if (j & 0x80000000u) A.jobsG[gi++] = job;
+      else A.jobsC[ci++] = job;
+    }
+  }
+
+  // ---- store the slot state -------------------------------------------------------------------------  @region store
+  A.st_flags[e] = (uint8_t)((active ? 1 : 0) | (retired ? 2 : 0) | (finished << 2) | ((active && needFK) ? 16 : 0));
+  if (active) {
+    A.st_t[e] = t; A.st_last[e] = lastValid; A.st_hp[e] = hp; A.st_ilo[e] = ilo; A.st_ihi[e] = ihi; A.st_L[e] = L;
+    A.st_edge[e] = edge; A.st_iters[e] = iters;
+    A.st_pos[e] = (uint32_t)pos | ((uint32_t)smallest << 16);
+    A.st_nEm[e] = (uint8_t)nEm;
+#pragma unroll
+    for (int w = 0; w < W; ++w) A.st_vmask[(size_t)w * E + e] = vmask[w];
+  }
+  const int nAlive = __syncthreads_count(!retired);  // a free slot retires only after a failed refill
+  const unsigned sm = __reduce_add_sync(FULL, samples), dc = __reduce_add_sync(FULL, discarded);
+  const unsigned cp = __reduce_add_sync(FULL, caps), ov = __reduce_add_sync(FULL, overflows);
+  if (lane == 0) {
+    if (sm) atomicAdd(&sCnt[4], sm);
+    if (dc) atomicAdd(&sCnt[5], dc);
+    if (cp) atomicAdd(&sCnt[6], cp);
+    if (ov) atomicAdd(&sCnt[7], ov);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (nAlive) atomicAdd(A.alive + A.aliveIdx, (unsigned)nAlive);
+    if (stats) {
+      if (sCnt[4]) atomicAdd(&stats->edge_samples, (unsigned long long)sCnt[4]);
+      if (sCnt[5]) atomicAdd(&stats->discarded_tests, (unsigned long long)sCnt[5]);
+      if (sCnt[6]) atomicAdd(&stats->iter_cap_hits, (unsigned long long)sCnt[6]);
+      if (sCnt[7]) atomicAdd(&stats->overflow, (unsigned long long)sCnt[7]);
+      if (blockIdx.x == 0) atomicAdd(&stats->engine_ticks, 1ull);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fold kernel: one thread per (slot, emitted body pair).  BodyPairCollision::validateConfiguration :65-89 on
+// last round's distances, up to the interval [t - (hd + ht), t + (hd + ht)]; a collision is kept as
+// (geometry pair, -inf).  Whether the interval is USED is decided by the control kernel's scan.
+__global__ void __launch_bounds__(256)
+wfFoldKernel(ModelView mv, WFArgs A) {
+  const Tables T = makeTables(mv.blob, mv);  // global copy (read-only, L1 resident)
+  const uint32_t E = A.E;
+  const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
+  if (idx >= (size_t)E * WF_RB) return;
+  const uint32_t e = (uint32_t)(idx % E);
+  const int k = (int)(idx / E);
+  if (!(A.st_flags[e] & 1) || k >= (int)A.st_nEm[e]) return;
+  const double INF = CUDART_INF;
+  const int p = A.emPos[(size_t)k * E + e];
+  const int id = A.ord[(size_t)e * A.ordStride + p];
+  const int r0 = A.emRes[(size_t)k * E + e];
+  const DevBodyPair B = T.bodypairs[id];
+  double dlb = INF;  // computeDistanceLowerBound (:175-198): pairs in order, first collision reports
+  int hit = -1;
+  for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
+    const double d = A.res[(size_t)(r0 + gp - B.pair_begin) * E + e];
+    if (d <= HPPB200_COLLISION_THRESHOLD) { hit = gp; break; }
+    if (d < dlb) dlb = d;
+  }
+  double ra, rb;
+  if (hit >= 0) { ra = (double)hit; rb = -INF; }
+  else {
+    const double t = A.st_t[e];
+    double hd, ht;  // :72-85
+    if (dlb == INF) { hd = INF; ht = 0; }
+    else {
+      const double Vm = A.vmax[(size_t)id * E + e];
+      hd = dlb / Vm;
+      ht = (Vm != 0) ? 2 * A.tol / Vm : INF;
+    }
+    ra = t - (hd + ht);
+    rb = t + (hd + ht);
+  }
+  A.fold[(size_t)k * E + e] = make_double2(ra, rb);
+}
+
+// ------------------------------------------------------------------------------------------------
+// FK kernel: one thread per slot that starts a sample this round: Path::eval + forward kinematics +
+// geometry placements (ContinuousValidation::validateConfiguration, src/continuous-validation.cc:134-137).
+// shared memory: [0,8) mbarrier | [16, ...) model blob prefix
+// Placements leave through a per-warp shared-memory tile: every lane drops its 96-byte record, then the warp
+// writes the 32 records as 16-byte pieces in record order, i.e. whole 32-byte sectors (a lane-per-record
+// store would touch 32 sectors with 8 useful bytes each).
+// shared memory: [0,8) mbarrier | [16, 16 + warps * 3072) tiles | model blob prefix
+constexpr uint32_t WF_FK_TILE = 32u * 96u;
+
+template <bool TREE>
+__global__ void __launch_bounds__(WF_CTHREADS)
+wfFkKernel(ModelView mv, WFArgs A) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned char* sblob = smem + 16 + (WF_CTHREADS / 32) * WF_FK_TILE;
+  stageBlobTMA(sblob, mv.blob, mv.edge_blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t e = blockIdx.x * WF_CTHREADS + threadIdx.x;
+  const bool on = (A.st_flags[e] & 16) != 0;
+  const unsigned onMask = __ballot_sync(FULL, on);
+  if (!onMask) return;
+  const uint32_t edge = on ? A.st_edge[e] : 0u;
+  const double t = on ? A.st_t[e] : 0.0, L = on ? A.st_L[e] : 0.0;
+  const double* q1 = A.q1 + (size_t)edge * mv.nq;
+  const double* q2 = A.q2 + (size_t)edge * mv.nq;
+  // StraightPath::impl_compute: stored end points are returned bit-exactly
+  int qmode;
+  double u = 0;
+  if (t == 0.0 || L == 0.0) qmode = 0;
+  else if (t == L) qmode = 1;
+  else { qmode = 2; u = (t - 0.0) / L; }
+  auto qAt = [&](int k) -> double {
+    const double a = q1[k];
+    if (qmode == 0) return a;
+    const double b = q2[k];
+    if (qmode == 1) return b;
+    return fma(u, b - a, a);  // LiegroupSpace::interpolate on R^n
+  };
+  if (TREE) {  // tree-shaped robots read parent placements back: lane-per-record stores
+    if (on) forwardKinematics<true>(T, mv, qAt, A.plc + (size_t)e * A.fkSlots * 12, 1);
+    return;
+  }
+  double2* tile = (double2*)(smem + 16 + warp * WF_FK_TILE);
+  double2* gdst = (double2*)(A.plc + (size_t)(e - lane) * A.fkSlots * 12);  // the warp's 32 records are contiguous
+  const size_t recStride = (size_t)A.fkSlots * 6;                           // in double2
+  auto put = [&](int g, const T3& X) {  // all lanes call this in step
+    double2* mine = tile + lane * 6;
+    mine[0] = make_double2(X.r[0], X.r[1]); mine[1] = make_double2(X.r[2], X.r[3]); mine[2] = make_double2(X.r[4], X.r[5]);
+    mine[3] = make_double2(X.r[6], X.r[7]); mine[4] = make_double2(X.r[8], X.t.x); mine[5] = make_double2(X.t.y, X.t.z);
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 6; ++r) {
+      const int j = r * 32 + lane, rec = j / 6, part = j - rec * 6;
+      if ((onMask >> rec) & 1u) gdst[(size_t)rec * recStride + (size_t)g * 6 + part] = tile[j];
+    }
+    __syncwarp();
+  };
+  // same operation sequence as forwardKinematics<false> (dev_model.cuh): a chain, joint j's parent is j - 1
+  for (int g = 0; g < mv.ngeoms; ++g)
+    if (T.geoms[g].joint == 0) put(g, load12(T.geoms[g].P));
+  T3 cur = identityT();
+  for (int j = 1; j <= mv.njoints; ++j) {
+    const DevJoint& J = T.joints[j - 1];
+    const T3 li = jointLocal(J, qAt);
+    if (J.parent == 0) cur = li;
+    else cur = compose(cur, li);
+    for (int g = 0; g < mv.ngeoms; ++g)
+      if (T.geoms[g].joint == j) put(g, compose(cur, load12(T.geoms[g].P)));
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Narrow-phase kernel: persistent grid over this round's job lists.
+// shared memory: [0,8) mbarrier | [16, ...) model blob prefix
+#ifndef WF_NMINB
+#define WF_NMINB 3
+#endif
+constexpr int WF_REFILL_MIN = 32;  // idle lanes in a warp before new GJK jobs are fetched
+
+__global__ void __launch_bounds__(WF_NTHREADS, WF_NMINB)
+wfNarrowKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
+  extern __shared__ __align__(16) unsigned char smem[];  // @region setup
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned char* sblob = smem + 16;
+  stageBlobTMA(sblob, mv.blob, mv.edge_blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  WFRoundCtl* ctl = A.ctl + (A.round & 1);
+  const unsigned nG = ctl->nG, nC = ctl->nC;
+  const size_t slotStride = (size_t)A.fkSlots * 12;
+  const uint32_t E = A.E;
+  unsigned tests = 0, iterations = 0, capHits = 0;
+
+  // ---- GJK jobs: one iteration per trip, finished lanes refilled from the list -------------------  @region gjk
+  if (nG) {
+    unsigned wcur = 0, wend = 0;
+    bool exhausted = false, have = false;
+    GjkState s;
+    T3 rel;
+    const DevShape* sa = nullptr;
+    const DevShape* sb = nullptr;
+    double sub0 = 0, sub1 = 0, margin = 0;
+    double* out = nullptr;
+    for (;;) {
+      const unsigned idle = __ballot_sync(FULL, !have);
+      if (!exhausted && __popc(idle) >= A.refill_min) {
+        bool need = !have;
+        for (;;) {
+          const unsigned m = __ballot_sync(FULL, need);
+          if (!m) break;
+          if (wcur >= wend) {
+            unsigned b = 0;
+            if (lane == 0) b = atomicAdd(&ctl->headG, (unsigned)WF_CHUNK);
+            b = __shfl_sync(FULL, b, 0);
+            if (b >= nG) { exhausted = true; break; }
+            wcur = b;
+            wend = (b + WF_CHUNK < nG) ? b + WF_CHUNK : nG;
+          }
+          const unsigned idx = wcur + __popc(m & ((1u << lane) - 1u));
+          if (need && idx < wend) {
+            const unsigned long long job = A.jobsG[idx];
+            const uint32_t e = (uint32_t)job;
+            const int gp = (int)((job >> 32) & 0x00ffffffu), ri = (int)(job >> 56);
+            const DevPair pr = T.bgpairs[gp];
+            const double* store = A.plc + (size_t)e * slotStride;
+            T3 TA, TB;
+            if (pr.a >= 0) { sa = (const DevShape*)&T.geoms[pr.a].shape; TA = load12(store + (size_t)pr.a * 12); }
+            else { const DevObstacle& O = T.obstacles[-(pr.a + 1)]; sa = (const DevShape*)&O.shape; TA = load12(O.P); }
+            if (pr.b >= 0) { sb = (const DevShape*)&T.geoms[pr.b].shape; TB = load12(store + (size_t)pr.b * 12); }
+            else { const DevObstacle& O = T.obstacles[-(pr.b + 1)]; sb = (const DevShape*)&O.shape; TB = load12(O.P); }
+            rel = composeInv(TA, TB);
+            gjkBegin(s, rel);
+            sub0 = inflation(*sa); sub1 = inflation(*sb); margin = pr.margin;
+            out = A.res + (size_t)ri * E + e;
+            have = true;
+            need = false;
+            ++tests;
+          }
+          const unsigned c = (unsigned)__popc(m);
+          wcur = (wcur + c < wend) ? wcur + c : wend;
+        }
+      }
+      if (!__any_sync(FULL, have)) break;  // nothing running and nothing left to fetch
+      if (have) {
+        double core;
+        if (gjkStep(s, *sa, *sb, rel, mv.vertices, core)) {
+          // shapeDistance (GJK kinds) - margin, same operation order as pairLowerBound
+          *out = ((core - sub0) - sub1) - margin;
+          iterations += (unsigned)s.it + 1u;
+          if (s.it == HPPB200_GJK_MAX_ITER) ++capHits;
+          have = false;
+        }
+      }
+    }
+  }
+
+  // ---- closed-form jobs: one thread each ----------------------------------------------------------  @region closed
+  {
+    GjkCounters cnt = {0u, 0u, 0u};
+    for (size_t i = (size_t)blockIdx.x * WF_NTHREADS + threadIdx.x; i < nC; i += (size_t)gridDim.x * WF_NTHREADS) {
+      const unsigned long long job = A.jobsC[i];
+      const uint32_t e = (uint32_t)job;
+      const int gp = (int)((job >> 32) & 0x00ffffffu), ri = (int)(job >> 56);
+      const DevPair pr = T.bgpairs[gp];
+      A.res[(size_t)ri * E + e] = pairLowerBound(T, pr, A.plc + (size_t)e * slotStride, 1, mv.vertices, cnt);
+      ++tests;
+    }
+    iterations += cnt.iterations;
+  }
+
+  const unsigned ts = __reduce_add_sync(FULL, tests), gi = __reduce_add_sync(FULL, iterations);  // @region stats
+  const unsigned gc = __reduce_add_sync(FULL, capHits);
+  if (lane == 0 && stats) {
+    if (ts) atomicAdd(&stats->pair_tests, (unsigned long long)ts);
+    if (gi) atomicAdd(&stats->gjk_iterations, (unsigned long long)gi);
+    if (gc) atomicAdd(&stats->gjk_cap_hits, (unsigned long long)gc);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void wfInitKernel(WFArgs A) {
+  const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e < A.E) A.st_flags[e] = 0;
+  if (e == 0) {
+    *A.counter = 0ull;
+    for (int k = 0; k < 2; ++k) { A.ctl[k].nG = 0; A.ctl[k].nC = 0; A.ctl[k].headG = 0; A.ctl[k].headC = 0; }
+  }
+}
+
+namespace {
+struct Carver {
+  size_t off = 0;
+  template <class T>
+  size_t take(size_t count) {
+    off = (off + 255) & ~size_t(255);
+    const size_t o = off;
+    off += count * sizeof(T);
+    return o;
+  }
+};
+}  // namespace
+
+// Returns false when the model does not fit this engine (the caller then uses another path).
+bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
+                                const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
+                                int32_t* d_pair, uint8_t* d_reason, int overflow_reason) {
+  const ModelView& mv = ws->view;
+  const Model* m = ws->model;
+  const int NP = mv.nbodypairs;
+  if (NP < 1 || NP > 65535 || mv.nbgpairs >= (1 << 24)) return false;
+  for (const BodyPairHost& b : m->bodyPairs)
+    if ((int)b.pairs.size() > WF_RG) return false;
+  if (NP > 256) return false;
+  const int W = NP <= 64 ? 1 : 4;
+  const size_t smemC = 48 + WF_RING_BYTES + mv.edge_blob_bytes, smemN = 16 + mv.edge_blob_bytes;
+  if (smemC > 200u * 1024u) return false;
+  const bool tree = modelIsTree(m);
+
+  WFArgs A{};
+  A.q1 = d_q1; A.q2 = d_q2; A.L = d_L; A.n = n; A.reverse = reverse; A.tol = tol; A.max_iter = ws->max_iterations;
+  A.valid = d_valid; A.t_fail = d_tfail; A.t_last = d_tlast; A.pair = d_pair; A.reason = d_reason;
+  A.overflow_reason = overflow_reason;
+  A.alpha = ws->engine_alpha;
+  A.refill_min = WF_REFILL_MIN;
+  if (const char* v = std::getenv("HPPB200_WF_REFILL")) A.refill_min = std::atoi(v);
+  A.fkSlots = mv.ngeoms + (tree ? mv.njoints : 0);
+  size_t E = ws->wavefront_slots ? ws->wavefront_slots : (size_t)ws->num_sms * 2048;
+  if (E > n) E = n;
+  E = (E + WF_CTHREADS - 1) / WF_CTHREADS * WF_CTHREADS;
+  A.E = (uint32_t)E;
+  const int BATCH = 16;  // rounds between two host checks of the alive counter
+
+  Carver c;
+  const size_t o_counter = c.take<unsigned long long>(1), o_ctl = c.take<WFRoundCtl>(2), o_alive = c.take<unsigned>(BATCH);
+  const size_t o_lohi = c.take<double2>((size_t)NP * E), o_ord = c.take<uint16_t>((size_t)((NP + 15) / 16 * 16) * E);
+  const size_t o_vmax = c.take<double>((size_t)NP * E), o_sv = c.take<double>((size_t)mv.nv * E);
+  const size_t o_t = c.take<double>(E), o_last = c.take<double>(E), o_hp = c.take<double>(E), o_ilo = c.take<double>(E);
+  const size_t o_ihi = c.take<double>(E), o_L = c.take<double>(E);
+  const size_t o_edge = c.take<uint32_t>(E), o_iters = c.take<uint32_t>(E), o_pos = c.take<uint32_t>(E);
+  const size_t o_flags = c.take<uint8_t>(E), o_nEm = c.take<uint8_t>(E), o_vmask = c.take<unsigned long long>((size_t)W * E);
+  const size_t o_emPos = c.take<uint16_t>((size_t)WF_RB * E), o_emRes = c.take<uint8_t>((size_t)WF_RB * E);
+  const size_t o_fold = c.take<double2>((size_t)WF_RB * E);
+  const size_t o_res = c.take<double>((size_t)WF_RG * E), o_plc = c.take<double>(E * (size_t)A.fkSlots * 12);
+  const size_t o_jG = c.take<unsigned long long>(E * (size_t)WF_RG), o_jC = c.take<unsigned long long>(E * (size_t)WF_RG);
+  ws->d_state.reserve(c.off + 256);
+  unsigned char* base = ws->d_state.p;
+  A.counter = (unsigned long long*)(base + o_counter);
+  A.ctl = (WFRoundCtl*)(base + o_ctl);
+  A.alive = (unsigned*)(base + o_alive);
+  A.lohi = (double2*)(base + o_lohi); A.ord = (uint16_t*)(base + o_ord); A.ordStride = (uint32_t)((NP + 15) / 16 * 16);
+  A.vmax = (double*)(base + o_vmax); A.sv = (double*)(base + o_sv);
+  A.st_t = (double*)(base + o_t); A.st_last = (double*)(base + o_last); A.st_hp = (double*)(base + o_hp);
+  A.st_ilo = (double*)(base + o_ilo); A.st_ihi = (double*)(base + o_ihi); A.st_L = (double*)(base + o_L);
+  A.st_edge = (uint32_t*)(base + o_edge); A.st_iters = (uint32_t*)(base + o_iters); A.st_pos = (uint32_t*)(base + o_pos);
+  A.st_flags = base + o_flags; A.st_nEm = base + o_nEm; A.st_vmask = (unsigned long long*)(base + o_vmask);
+  A.emPos = (uint16_t*)(base + o_emPos); A.emRes = base + o_emRes; A.fold = (double2*)(base + o_fold);
+  A.res = (double*)(base + o_res); A.plc = (double*)(base + o_plc);
+  A.jobsG = (unsigned long long*)(base + o_jG); A.jobsC = (unsigned long long*)(base + o_jC);
+
+  auto kc = W == 1 ? wfControlKernel<1> : wfControlKernel<4>;
+  auto kf = tree ? wfFkKernel<true> : wfFkKernel<false>;
+  const size_t smemF = 16 + (WF_CTHREADS / 32) * WF_FK_TILE + mv.edge_blob_bytes;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
+  const unsigned gridF = (unsigned)((E * (size_t)WF_RB + 255) / 256);
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemC));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(wfNarrowKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemN));
+  int perSM = 0;
+  HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, wfNarrowKernel, WF_NTHREADS, smemN));
+  if (perSM < 1) return false;
+  const unsigned gridN = (unsigned)(ws->num_sms * perSM), gridC = (unsigned)(E / WF_CTHREADS);
+
+  wfInitKernel<<<(unsigned)((E + 255) / 256), 256, 0, ws->stream>>>(A);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 1;
+  int round = 0;
+  unsigned h_alive = 1;
+  const bool trace = std::getenv("HPPB200_WF_TRACE") != nullptr;  // per-round kernel times on stderr (debug)
+  std::vector<cudaEvent_t> evs;
+  while (h_alive) {
+    HPPB200_CUDA_CHECK(cudaMemsetAsync(A.alive, 0, BATCH * sizeof(unsigned), ws->stream));
+    for (int k = 0; k < BATCH; ++k, ++round) {
+      A.round = round;
+      A.aliveIdx = k;
+      auto mark = [&]() {
+        if (!trace) return;
+        cudaEvent_t ev;
+        cudaEventCreate(&ev);
+        cudaEventRecord(ev, ws->stream);
+        evs.push_back(ev);
+      };
+      mark();
+      if (round > 0) wfFoldKernel<<<gridF, 256, 0, ws->stream>>>(mv, A);
+      mark();
+      kc<<<gridC, WF_CTHREADS, smemC, ws->stream>>>(mv, A, ws->d_stats);
+      mark();
+      kf<<<gridC, WF_CTHREADS, smemF, ws->stream>>>(mv, A);
+      mark();
+      wfNarrowKernel<<<gridN, WF_NTHREADS, smemN, ws->stream>>>(mv, A, ws->d_stats);
+      mark();
+    }
+    HPPB200_CUDA_CHECK(cudaGetLastError());
+    ws->stats.kernel_launches += 4 * BATCH;
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h_alive, A.alive + (BATCH - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  }
+  if (trace) {
+    double tt[4] = {0, 0, 0, 0};
+    for (size_t r = 0; r + 4 < evs.size(); r += 5) {
+      float d[4];
+      for (int j = 0; j < 4; ++j) { cudaEventElapsedTime(&d[j], evs[r + j], evs[r + j + 1]); tt[j] += d[j]; }
+      const size_t k = r / 5;
+      if (k < 4 || k % 64 == 0)
+        std::fprintf(stderr, "[wf] round %zu fold %.1f control %.1f fk %.1f narrow %.1f us\n", k, d[0] * 1e3, d[1] * 1e3, d[2] * 1e3, d[3] * 1e3);
+    }
+    std::fprintf(stderr, "[wf] E=%u gridC=%u gridN=%u rounds=%d fold %.2f control %.2f fk %.2f narrow %.2f ms\n", A.E, gridC, gridN, round,
+                 tt[0], tt[1], tt[2], tt[3]);
+    for (cudaEvent_t ev : evs) cudaEventDestroy(ev);
+  }
+  return true;
+}
+
+}  // namespace hppb200

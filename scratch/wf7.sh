@@ -1,0 +1,4 @@
+cd /root/repo
+HPPB200_WF_REFILL=32 timeout 800 ncu --set full --clock-control none --import-source on -k regex:wfControl --launch-skip 100 --launch-count 1 -o gpurun_out/wf7c -f python tools/wf_run.py 1048576 0 > gpurun_out/wf7.log 2>&1
+HPPB200_WF_REFILL=32 timeout 800 ncu --set full --clock-control none --import-source on -k regex:wfNarrow --launch-skip 100 --launch-count 1 -o gpurun_out/wf7n -f python tools/wf_run.py 1048576 0 >> gpurun_out/wf7.log 2>&1
+ls -la gpurun_out/wf7*
