@@ -144,6 +144,7 @@ struct Workspace {
   bool use_engine = true;      // Progressive: control/narrow-phase engine (HPPB200_ENGINE=0 forces the walker)
   int engine_threads = 128;    // CTA size of the engine (HPPB200_ENGINE_THREADS: 64 | 96 | 128)
   int engine_kind = 2;         // Progressive: 2 wavefront rounds (kernels_wavefront.cu), 1 CTA engine (HPPB200_ENGINE)
+  size_t wavefront_min = 100000;  // smallest batch that takes the wavefront engine (HPPB200_WF_MIN)
   size_t wavefront_slots = 0;  // resident edge slots of the wavefront engine (0: 2048 per SM; HPPB200_WF_SLOTS)
   double engine_alpha = 1.2;   // candidate prediction: alpha x previous step (HPPB200_ENGINE_ALPHA; 1.2 measured best)
   // staging for host-pointer calls

@@ -642,7 +642,9 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   // Progressive on models whose per-edge state fits in shared memory: the control/narrow-phase
   // engine of kernels_continuous.cu.  Anything else: the generic walker below.
   bool engineDone = false;
-  if (method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine && ws->engine_kind >= 2)
+  // Large batches: round-synchronous wavefront engine (kernels_wavefront.cu); its ~600 rounds of a few kernels
+  // each are a fixed latency that small batches do not amortise, those go to the CTA engine.
+  if (method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine && ws->engine_kind >= 2 && n >= ws->wavefront_min)
     engineDone = launchWavefrontProgressive(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair,
                                             d_reason, REASON_OVERFLOW_INTERNAL);
   if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine)

@@ -145,6 +145,22 @@ __device__ __forceinline__ void maskPut(u64 (&m)[W], int p, bool v) {  // overwr
     if ((p >> 6) == w) m[w] = (m[w] & ~(1ull << (p & 63))) | ((u64)(v ? 1 : 0) << (p & 63));
 }
 
+// bits c0 .. c0 + WF_CH - 1 of a position mask, and OR-ing such a chunk back (one shift per chunk for W = 1)
+template <int W>
+__device__ __forceinline__ unsigned chunkBits(const u64 (&m)[W], int c0) {
+  if (W == 1) return c0 < 64 ? (unsigned)(m[0] >> c0) & ((1u << WF_CH) - 1u) : 0u;
+  unsigned r = 0;
+#pragma unroll
+  for (int k = 0; k < WF_CH; ++k) r |= (maskGet<W>(m, c0 + k) ? 1u : 0u) << k;
+  return r;
+}
+template <int W>
+__device__ __forceinline__ void chunkOr(u64 (&m)[W], int c0, unsigned bits) {
+  if (W == 1) { m[0] |= (u64)bits << c0; return; }
+#pragma unroll
+  for (int k = 0; k < WF_CH; ++k) maskSet<W>(m, c0 + k, (bits >> k) & 1u);
+}
+
 template <int W>
 __global__ void __launch_bounds__(WF_CTHREADS)
 wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
@@ -206,9 +222,11 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     double ql = 0, qh = 0;
     const double2* src = A.lohi + e;
     auto issue = [&](int c0, int b) {  // chunk starting at position c0 into ring buffer b (valid_ positions need no data)
+      const unsigned vch = chunkBits<W>(vmask, c0);
+      const double2* g = src + (size_t)c0 * E;
 #pragma unroll
-      for (int k = 0; k < WF_CH; ++k)
-        if (c0 + k < NP && !maskGet<W>(vmask, c0 + k)) cpAsync16(ring + (b * WF_CH + k) * WF_CTHREADS, src + (size_t)(c0 + k) * E);
+      for (int k = 0; k < WF_CH; ++k, g += E)
+        if (c0 + k < NP && !((vch >> k) & 1u)) cpAsync16(ring + (b * WF_CH + k) * WF_CTHREADS, g);
       cpAsyncCommit();
     };
     issue(pos, 0);
@@ -216,9 +234,13 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     for (int c0 = pos; c0 < NP && !stop; c0 += WF_CH, b ^= 1) {
       issue(c0 + WF_CH, b ^ 1);  // (an empty group past the end)
       cpAsyncWait<1>();
-      const int cend = (c0 + WF_CH < NP) ? c0 + WF_CH : NP;
-      for (int p = c0; p < cend; ++p) {
-        if (maskGet<W>(vmask, p)) {
+      const unsigned vch = chunkBits<W>(vmask, c0);
+      unsigned cbits = 0u, vbits = 0u;  // candidates / newly valid_ pairs of this chunk
+#pragma unroll
+      for (int k = 0; k < WF_CH; ++k) {
+        const int p = c0 + k;
+        if (p >= NP || stop) break;
+        if ((vch >> k) & 1u) {
           // valid_ on the whole path: interval = timeRange (body-pair-collision.cc:51-55).  Never a candidate,
           // so never has a queued result.
           if (!emit) {
@@ -228,13 +250,13 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
           }
           continue;
         }
-        const double2 lh = ring[(b * WF_CH + (p - c0)) * WF_CTHREADS];
+        const double2 lh = ring[(b * WF_CH + k) * WF_CTHREADS];
         if (emit) {
-          maskSet<W>(cand, p, !(lh.x <= ql && qh <= lh.y));
+          cbits |= (!(lh.x <= ql && qh <= lh.y) ? 1u : 0u) << k;
           continue;
         }
         const bool have = nextP == p;
-        const int k = cursor;
+        const int kk = cursor;
         if (have) {
           ++cursor;
           nextP = cursor < nEm ? (int)A.emPos[(size_t)cursor * E + e] : -1;
@@ -243,12 +265,12 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
         if (lh.x <= ilo && ihi <= lh.y) {  // validInterval_ contains the running interval (:56-63)
           if (have) ++discarded;
         } else if (have) {
-          const double2 rr = A.fold[(size_t)k * E + e];
+          const double2 rr = A.fold[(size_t)kk * E + e];
           const double a = rr.x, bb = rr.y;
           if (bb == -INF) {  // collision: a carries the geometry pair
             finishEdge(false, HPPB200_REASON_COLLISION, t, lastValid, (int)a);
             stop = true;
-            break;
+            continue;
           }
           const double l = lh.x, h = lh.y;
           if (!(l > h) && (h < a || bb < l)) {
@@ -256,11 +278,11 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
             ++overflows;
             finishEdge(false, A.overflow_reason, t, lastValid, -1);
             stop = true;
-            break;
+            continue;
           }
           nl = a; nh = bb;
           if (!(l > h)) { nl = (a < l) ? a : l; nh = (h > bb) ? h : bb; }
-          if (nl <= 0.0 && L <= nh) { nl = -INF; nh = INF; maskSet<W>(vmask, p, true); }  // valid_ (:92-96)
+          if (nl <= 0.0 && L <= nh) { nl = -INF; nh = INF; vbits |= 1u << k; }  // valid_ (:92-96), lo = -inf
           A.lohi[(size_t)p * E + e] = make_double2(nl, nh);
           if (ihi > bb) smallest = p;  // validateIntervals: fold into the running intersection
           ilo = (ilo < a) ? a : ilo;
@@ -273,14 +295,16 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
           qh = fmin(ihi, t + hp);
 #pragma unroll
           for (int w = 0; w < W; ++w) cand[w] = 0ull;
-          maskSet<W>(cand, p, true);
+          cbits = 1u << k;
           continue;
         }
         // candidate of the NEXT sample: predicted t' = end of the running intersection, window alpha x step
         const double tn = reverse ? ilo : ihi;
         const double hn = A.alpha * fabs(tn - t);
-        maskSet<W>(cand, p, !(nl <= tn - hn && tn + hn <= nh));
+        cbits |= (!(nl <= tn - hn && tn + hn <= nh) ? 1u : 0u) << k;
       }
+      chunkOr<W>(cand, c0, cbits);
+      if (vbits) chunkOr<W>(vmask, c0, vbits);
     }
     cpAsyncWait<0>();
     if (active && !emit) {

@@ -249,3 +249,42 @@ def test_full_size_properties(pkg, eng, ur5, ur5_oracle):
     sub = np.random.default_rng(1).choice(n, 20000, replace=False)
     ov, op, _ = ur5_oracle.validate_configs(q[sub])
     assert np.array_equal(v1[sub], ov) and np.array_equal(f1[sub], op)
+
+
+@pytest.mark.parametrize("reverse", [False, True])
+@pytest.mark.parametrize("slots", [0, 1024])
+def test_wavefront_engine_parity(pkg, eng, ur5, ur5_oracle, golden_configs, monkeypatch, reverse, slots):
+    """Progressive through the round-synchronous wavefront engine (kernels_wavefront.cu), forced for a small
+    batch; slots=1024 < n exercises the refill of finished slots.  Same bar as the other engines: bit-exact."""
+    m, _ = eng
+    monkeypatch.setenv("HPPB200_WF_MIN", "1")
+    monkeypatch.setenv("HPPB200_WF_SLOTS", str(slots))
+    ws = pkg.Workspace(m, 0)
+    o = ur5_oracle
+    g1, g2 = golden_configs[0:200:2], golden_configs[1:200:2]
+    a1, a2, _ = _edges(pkg, ur5, o, 3000, 33)
+    b1, b2, _ = _edges(pkg, ur5, o, 2000, 34, short=True)
+    z = pkg.uniform_configs(ur5, 300, seed=35)  # zero-length paths
+    q1, q2 = np.concatenate([g1, a1, b1, z]), np.concatenate([g2, a2, b2, z])
+    L = o.straight_lengths(q1, q2)
+    s0 = ws.stats()
+    r = ws.validate_edges(1, 1e-3, q1, q2, L, reverse=reverse)
+    s1 = ws.stats()
+    e = o.validate_edges(1, 1e-3, q1, q2, L, reverse=reverse)
+    assert s1["engine_ticks"] - s0["engine_ticks"] < 2000  # rounds, not CTA ticks: the wavefront engine ran
+    assert s1["iter_cap_hits"] == 0
+    for k in ("valid", "reason", "pair", "t_last_valid"):
+        assert np.array_equal(r[k], e[k]), k
+    assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+
+
+def test_wavefront_engine_iteration_cap(pkg, eng, ur5, ur5_oracle, monkeypatch):
+    m, _ = eng
+    monkeypatch.setenv("HPPB200_WF_MIN", "1")
+    ws = pkg.Workspace(m, 0)
+    ws.set_max_iterations(3)
+    q1, q2, L = _edges(pkg, ur5, ur5_oracle, 500, 62)
+    r = ws.validate_edges(1, 1e-3, q1, q2, L)
+    e = ur5_oracle.validate_edges(1, 1e-3, q1, q2, L, max_iter=3)
+    assert np.array_equal(r["reason"], e["reason"]) and np.array_equal(r["valid"], e["valid"])
+    assert (r["reason"] == 3).any()
