@@ -288,3 +288,21 @@ def test_wavefront_engine_iteration_cap(pkg, eng, ur5, ur5_oracle, monkeypatch):
     e = ur5_oracle.validate_edges(1, 1e-3, q1, q2, L, max_iter=3)
     assert np.array_equal(r["reason"], e["reason"]) and np.array_equal(r["valid"], e["valid"])
     assert (r["reason"] == 3).any()
+
+
+@pytest.mark.parametrize("name", ["ur5_boxes0.json", "ur5_boxes1.json", "ur5_boxes32.json"])
+def test_wavefront_engine_other_scenes(pkg, ob, monkeypatch, name):
+    """15, 21 and 207 body pairs: the last one takes the multi-word position masks (more than 64 pairs)."""
+    monkeypatch.setenv("HPPB200_WF_MIN", "1")
+    desc = pkg.ModelDescription.load(name)
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    o = ob.Oracle(desc)
+    q1, q2, L = _edges(pkg, desc, o, 3000, 36)
+    for rev in (False, True):
+        s0 = ws.stats()
+        r = ws.validate_edges(1, 1e-3, q1, q2, L, reverse=rev)
+        assert ws.stats()["engine_ticks"] - s0["engine_ticks"] < 4000
+        e = o.validate_edges(1, 1e-3, q1, q2, L, reverse=rev)
+        for k in ("valid", "reason", "pair", "t_last_valid"):
+            assert np.array_equal(r[k], e[k]), (name, rev, k)
+        assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
