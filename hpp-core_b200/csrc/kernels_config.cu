@@ -20,7 +20,6 @@
 
 namespace hppb200 {
 
-constexpr int CFG_PER_BLOCK = 64;
 constexpr int CFG_THREADS = 256;
 constexpr int MODE_VALIDATE = 0, MODE_DISTANCES = 1, MODE_PLACEMENTS = 2;
 
@@ -28,7 +27,7 @@ struct ConfigSmemLayout {
   uint32_t off_blob, off_store, off_first, off_bound, total;
 };
 
-static ConfigSmemLayout configSmemLayout(const ModelView& mv, bool tree) {
+static ConfigSmemLayout configSmemLayout(const ModelView& mv, bool tree, uint32_t CFG_PER_BLOCK) {
   ConfigSmemLayout L;
   uint32_t o = 16;  // [0,8) mbarrier, [8,12) work counter
   L.off_blob = o;
@@ -44,7 +43,8 @@ static ConfigSmemLayout configSmemLayout(const ModelView& mv, bool tree) {
   return L;
 }
 
-template <bool TREE>
+// CFG_PER_BLOCK configurations per CTA: 64, or 32 when the placements of a larger model would not fit
+template <bool TREE, int CFG_PER_BLOCK>
 __global__ void __launch_bounds__(CFG_THREADS)
 validateConfigsKernel(ModelView mv, ConfigSmemLayout L, const double* __restrict__ q, size_t n, uint32_t flags, int mode,
                       uint8_t* __restrict__ valid, int32_t* __restrict__ first, uint8_t* __restrict__ reason,
@@ -397,11 +397,14 @@ static void launchConfigKernel(Workspace* ws, const double* d_q, size_t n, uint3
                                int32_t* d_first, uint8_t* d_reason, double* d_aux) {
   if (n == 0) return;
   const bool tree = modelIsTree(ws->model);
-  ConfigSmemLayout L = configSmemLayout(ws->view, tree);
+  uint32_t cpb = 64;
+  ConfigSmemLayout L = configSmemLayout(ws->view, tree, cpb);
+  if (L.total > 227u * 1024u) { cpb = 32; L = configSmemLayout(ws->view, tree, cpb); }
   if (L.total > 227u * 1024u)
     throw std::runtime_error("model too large for the shared-memory configuration kernel (" + std::to_string(L.total) + " B)");
-  const unsigned grid = (unsigned)((n + CFG_PER_BLOCK - 1) / CFG_PER_BLOCK);
-  auto kern = tree ? validateConfigsKernel<true> : validateConfigsKernel<false>;
+  const unsigned grid = (unsigned)((n + cpb - 1) / cpb);
+  auto kern = cpb == 64 ? (tree ? validateConfigsKernel<true, 64> : validateConfigsKernel<false, 64>)
+                        : (tree ? validateConfigsKernel<true, 32> : validateConfigsKernel<false, 32>);
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.total));
   kern<<<grid, CFG_THREADS, L.total, ws->stream>>>(ws->view, L, d_q, n, flags, mode, d_valid, d_first, d_reason, d_aux,
                                                   ws->d_stats);

@@ -115,6 +115,129 @@ def boxes(n, seed=20240607):
     return out
 
 
+def ellipsoid_hull(n, a, b, c):
+    """n points on an ellipsoid (Fibonacci lattice): every point is a vertex of the convex hull."""
+    k = np.arange(n) + 0.5
+    phi = np.arccos(1 - 2 * k / n)
+    th = np.pi * (1 + 5 ** 0.5) * k
+    return np.stack([a * np.cos(th) * np.sin(phi), b * np.sin(th) * np.sin(phi), c * np.cos(phi)], axis=1)
+
+
+def humanoid():
+    """Fixed-pelvis humanoid-like TREE: waist (2) + neck (2) + 2 arms (7 each) + 2 legs (6 each) = 30 revolute
+    joints, capsule / sphere / box / convex-mesh bodies (BASELINE configs[3] without the free-flyer, which the
+    engine does not support yet).  Dimensions are made up (roughly 1.6 m tall); the point is the structure:
+    joint parents that are not the previous joint, convex meshes through GJK, hundreds of body pairs."""
+    J = []  # name, parent, type, xyz
+    def add(name, parent, typ, xyz):
+        J.append((name, parent, typ, xyz))
+        return len(J)
+    waist_y = add("waist_yaw", 0, REV_Z, (0, 0, 0.10))
+    waist_p = add("waist_pitch", waist_y, REV_Y, (0, 0, 0.05))
+    neck_y = add("neck_yaw", waist_p, REV_Z, (0, 0, 0.45))
+    neck_p = add("neck_pitch", neck_y, REV_Y, (0, 0, 0.05))
+    limbs = {}
+    for side, sy in (("l", 1.0), ("r", -1.0)):
+        a = add(side + "_shoulder_pitch", waist_p, REV_Y, (0, sy * 0.20, 0.38))
+        a = add(side + "_shoulder_roll", a, REV_X, (0, sy * 0.03, 0))
+        a = add(side + "_shoulder_yaw", a, REV_Z, (0, 0, -0.05))
+        ua = a
+        a = add(side + "_elbow", a, REV_Y, (0, 0, -0.25))
+        a = add(side + "_wrist_yaw", a, REV_Z, (0, 0, -0.12))
+        fa = a
+        a = add(side + "_wrist_pitch", a, REV_Y, (0, 0, -0.12))
+        a = add(side + "_wrist_roll", a, REV_X, (0, 0, -0.02))
+        limbs[side + "arm"] = (ua, fa, a)
+    for side, sy in (("l", 1.0), ("r", -1.0)):
+        a = add(side + "_hip_yaw", 0, REV_Z, (0, sy * 0.09, -0.05))
+        a = add(side + "_hip_roll", a, REV_X, (0, 0, -0.03))
+        a = add(side + "_hip_pitch", a, REV_Y, (0, 0, -0.03))
+        th = a
+        a = add(side + "_knee", a, REV_Y, (0, 0, -0.38))
+        sh = a
+        a = add(side + "_ankle_pitch", a, REV_Y, (0, 0, -0.38))
+        a = add(side + "_ankle_roll", a, REV_X, (0, 0, -0.02))
+        limbs[side + "leg"] = (th, sh, a)
+    verts = []
+    def mesh(n, a, b, c):
+        begin = len(verts)
+        verts.extend(ellipsoid_hull(n, a, b, c).tolist())
+        return begin, n
+    G = []  # name, joint, shape, params, placement, vbegin, vcount
+    G.append(("pelvis", 0, BOX, (0.10, 0.14, 0.07), se3(t=(0, 0, 0.0)), 0, 0))
+    vb, vc = mesh(24, 0.11, 0.17, 0.22)
+    G.append(("torso", waist_p, CONVEX, (0, 0, 0), se3(t=(0, 0, 0.22)), vb, vc))
+    G.append(("head", neck_p, SPHERE, (0.10,), se3(t=(0, 0, 0.10)), 0, 0))
+    for side in ("l", "r"):
+        ua, fa, hand = limbs[side + "arm"]
+        G.append((side + "_upper_arm", ua, CAPSULE, (0.045, 0.10), se3(t=(0, 0, -0.125)), 0, 0))
+        G.append((side + "_forearm", fa, CAPSULE, (0.04, 0.09), se3(t=(0, 0, 0.0)), 0, 0))
+        vb, vc = mesh(16, 0.035, 0.05, 0.08)
+        G.append((side + "_hand", hand, CONVEX, (0, 0, 0), se3(t=(0, 0, -0.08)), vb, vc))
+    for side in ("l", "r"):
+        th, sh, foot = limbs[side + "leg"]
+        G.append((side + "_thigh", th, CAPSULE, (0.07, 0.15), se3(t=(0, 0, -0.19)), 0, 0))
+        G.append((side + "_shin", sh, CAPSULE, (0.055, 0.15), se3(t=(0, 0, -0.19)), 0, 0))
+        G.append((side + "_foot", foot, BOX, (0.11, 0.05, 0.025), se3(t=(0.03, 0, -0.055)), 0, 0))
+        vb, vc = mesh(12, 0.04, 0.045, 0.03)
+        G.append((side + "_toe_cap", foot, CONVEX, (0, 0, 0), se3(t=(0.13, 0, -0.05)), vb, vc))
+    name_to = {g[0]: i for i, g in enumerate(G)}
+    def prs(a_names, b_names):
+        return [[name_to[a], name_to[b]] for a in a_names for b in b_names if a != b]
+    arms_l, arms_r = ["l_upper_arm", "l_forearm", "l_hand"], ["r_upper_arm", "r_forearm", "r_hand"]
+    legs_l, legs_r = ["l_thigh", "l_shin", "l_foot", "l_toe_cap"], ["r_thigh", "r_shin", "r_foot", "r_toe_cap"]
+    pairs = (prs(["l_forearm", "l_hand", "r_forearm", "r_hand"], ["torso", "head", "pelvis"]) +
+             prs(arms_l[1:], arms_r) + prs(["l_upper_arm"], arms_r[1:]) +
+             prs(["l_forearm", "l_hand"], legs_l[:2] + legs_r[:2]) + prs(["r_forearm", "r_hand"], legs_l[:2] + legs_r[:2]) +
+             prs(legs_l, legs_r) + prs(["l_shin", "l_foot", "l_toe_cap", "r_shin", "r_foot", "r_toe_cap"], ["pelvis"]))
+    n = len(J)
+    lim = {REV_X: 0.8, REV_Y: 1.4, REV_Z: 1.2}
+    return {
+        "name": "humanoid_fixed_pelvis",
+        "joint_names": [j[0] for j in J],
+        "joint_parent": [j[1] for j in J],
+        "joint_type": [j[2] for j in J],
+        "joint_placement": [se3(None, j[3]) for j in J],
+        "q_lower": [-lim[j[2]] for j in J],
+        "q_upper": [lim[j[2]] for j in J],
+        "geom_names": [g[0] for g in G],
+        "geom_joint": [g[1] for g in G],
+        "geom_shape": [g[2] for g in G],
+        "geom_params": [list(g[3]) + [0.0] * (4 - len(g[3])) for g in G],
+        "geom_placement": [g[4] for g in G],
+        "geom_vert_begin": [g[5] for g in G],
+        "geom_vert_count": [g[6] for g in G],
+        "self_pairs": pairs,
+        "vertices": verts,
+        "break_distance": 1e-2,
+    }
+
+
+def humanoid_obstacles(n, verts, seed=77):
+    """n obstacles around the humanoid: boxes and (every third one) a convex mesh appended to `verts`."""
+    rng = np.random.default_rng(seed)
+    out = {"obst_names": [], "obst_placement": [], "obst_shape": [], "obst_params": [],
+           "obst_vert_begin": [], "obst_vert_count": []}
+    for k in range(n):
+        rad, ang = rng.uniform(0.35, 0.9), rng.uniform(-np.pi, np.pi)
+        c = (rad * np.cos(ang), rad * np.sin(ang), rng.uniform(-0.7, 0.9))
+        out["obst_names"].append("obst_%d" % k)
+        out["obst_placement"].append(se3(random_rotation(rng), c))
+        if k % 3 == 2:
+            begin = len(verts)
+            verts.extend(ellipsoid_hull(20, *rng.uniform(0.08, 0.2, size=3)).tolist())
+            out["obst_shape"].append(CONVEX)
+            out["obst_params"].append([0.0] * 4)
+            out["obst_vert_begin"].append(begin)
+            out["obst_vert_count"].append(20)
+        else:
+            out["obst_shape"].append(BOX)
+            out["obst_params"].append([float(x) / 2 for x in rng.uniform(0.1, 0.35, size=3)] + [0.0])
+            out["obst_vert_begin"].append(0)
+            out["obst_vert_count"].append(0)
+    return out
+
+
 def fk_neutral(model):
     """oMi at q = 0 for vector-space models (plain numpy; data preparation only)."""
     n = len(model["joint_parent"])
@@ -137,6 +260,9 @@ def body_radii(model):
             h = np.array([p[0]] * 3)
         elif s == CAPSULE:
             h = np.array([p[0], p[0], p[0] + p[1]])
+        elif s == CONVEX:
+            vb, vc = model["geom_vert_begin"][g], model["geom_vert_count"][g]
+            h = np.abs(np.array(model["vertices"][vb:vb + vc])).max(axis=0)
         else:
             h = np.array(p[:3])
         P = np.array(model["geom_placement"][g])
@@ -193,6 +319,16 @@ def main():
         with open(os.path.join(HERE, "ur5_boxes%d.json" % nb), "w") as f:
             json.dump(m, f, indent=1)
     print("wrote ur5_boxes{0,1,8,32}.json; weights =", robot["weights"])
+    for nb in (6, 16):
+        h = humanoid()
+        h["vertices"] = list(h["vertices"])
+        h.update(humanoid_obstacles(nb, h["vertices"]))
+        h["weights"] = weighed_distance_weights(h)
+        h["name"] = "humanoid_obst%d" % nb
+        with open(os.path.join(HERE, "humanoid_obst%d.json" % nb), "w") as f:
+            json.dump(h, f, indent=1)
+    print("wrote humanoid_obst{6,16}.json: %d joints, %d geometries, %d self pairs" % (
+        len(h["joint_parent"]), len(h["geom_joint"]), len(h["self_pairs"])))
 
 
 if __name__ == "__main__":

@@ -306,3 +306,44 @@ def test_wavefront_engine_other_scenes(pkg, ob, monkeypatch, name):
         for k in ("valid", "reason", "pair", "t_last_valid"):
             assert np.array_equal(r[k], e[k]), (name, rev, k)
         assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+
+
+def _local_edges(pkg, desc, n, seed, step):
+    """Edges from a random configuration to a nearby one (|dq|_2 = step), inside the joint limits."""
+    q1 = pkg.uniform_configs(desc, n, seed=seed)
+    d = np.random.default_rng(seed).normal(size=q1.shape)
+    q2 = np.clip(q1 + step * d / np.linalg.norm(d, axis=1, keepdims=True), desc.q_lower, desc.q_upper)
+    return q1, q2
+
+
+@pytest.mark.parametrize("name", ["humanoid_obst6.json", "humanoid_obst16.json"])
+def test_humanoid_tree_convex_parity(pkg, ob, monkeypatch, name):
+    """BASELINE configs[3]-like model (fixed pelvis): 30 revolute joints in a TREE, convex meshes through GJK,
+    133 / 273 body pairs.  FK, pair distances, configuration validation and the three path validations
+    (Progressive through the wavefront engine when the model fits it, else CTA engine / walker) against the
+    oracle, bit-exact."""
+    monkeypatch.setenv("HPPB200_WF_MIN", "1")
+    desc = pkg.ModelDescription.load(name)
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    o = ob.Oracle(desc)
+    q = pkg.uniform_configs(desc, 20000, seed=81)
+    assert np.array_equal(ws.geometry_placements(q[:2000]), o.geometry_placements(q[:2000]))
+    assert np.array_equal(ws.pair_distances(q[:2000]), o.pair_distances(q[:2000]))
+    got, exp = ws.validate_configs(q), o.validate_configs(q)
+    for a, b in zip(got, exp):
+        assert np.array_equal(a, b)
+    assert 0.02 < got[0].mean() < 0.9
+    a1, a2 = _local_edges(pkg, desc, 3000, 82, 0.4)
+    b1, b2, _ = _edges(pkg, desc, o, 1000, 83)
+    q1, q2 = np.concatenate([a1, b1]), np.concatenate([a2, b2])
+    L = o.straight_lengths(q1, q2)
+    assert np.array_equal(ws.straight_lengths(q1, q2), L)
+    for method, param in ((0, 0.05), (1, 1e-3), (2, 0.0)):
+        for rev in (False, True):
+            r = ws.validate_edges(method, param, q1, q2, L, reverse=rev)
+            e = o.validate_edges(method, param, q1, q2, L, reverse=rev)
+            assert ws.stats()["iter_cap_hits"] == 0
+            for k in ("valid", "reason", "pair", "t_last_valid"):
+                assert np.array_equal(r[k], e[k]), (name, method, rev, k)
+            assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+            assert 0.02 < r["valid"].mean() < 0.98
