@@ -331,6 +331,36 @@ def run_b200(args):
             res["progressive"]["cpu_baseline"] = {"value": rate, "unit": "edges/s", "cores": threads, "kind": "port",
                                                   "sample": "first %d of the %d edges, %.1f s" % (ns, N_EDGES_PROG, dt)}
         edges = res
+    knn = None
+    if not args.no_edges:
+        # secondary metric: nearestNeighbor::Basic over a 1M-node roadmap mirror (BASELINE configs[2]); wall clock
+        # through the C ABI with host pointers (query upload + result download inside), median of 20 calls
+        nn = pkg.NearestNeighbor(model, local_rank)
+        n_nodes = 1 << 20
+        nn.append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
+        knn = {"nodes": n_nodes, "unit": "queries/s", "bytes_per_node": 8 * nq}
+        for label, nqr, kk, reps in (("q1_k1", 1, 1, 20), ("q1_k10", 1, 10, 20), ("q1024_k1", 1024, 1, 5), ("q1024_k10", 1024, 10, 3)):
+            qs = pkg.uniform_configs(desc, nqr, seed=SEED + 3)
+            nn.query(qs, kk)
+            ts = []
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                idx, dd = nn.query(qs, kk)
+                ts.append(time.perf_counter() - t0)
+            tm = sorted(ts)[len(ts) // 2]
+            knn[label] = {"value": nqr / tm, "ms_per_call": tm * 1e3,
+                          "scan_passes": 1 if kk <= 32 else kk,
+                          "node_stream_gbs": n_nodes * 8 * nq * (1 if kk <= 32 else kk) * ((nqr + 3) // 4) / tm / 1e9}
+        if not args.no_cpu:
+            orc.knn_append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
+            qs = pkg.uniform_configs(desc, 64, seed=SEED + 3)
+            t0 = time.perf_counter()
+            oi, od = orc.knn_query(qs, 10, nthreads=threads)
+            dt = time.perf_counter() - t0
+            gi, gd = nn.query(qs, 10)
+            knn["cpu_baseline"] = {"value": 64 / dt, "unit": "queries/s", "cores": threads, "kind": "port",
+                                   "sample": "64 queries, k = 10, %.2f s" % dt}
+            knn["parity_64_queries_k10"] = bool(np.array_equal(oi, gi) and np.array_equal(od, gd))
 
     line = {
         "metric": "validated configs/sec", "value": value, "unit": "configs/s", "n_gpus": world, "steps": args.steps,
@@ -348,6 +378,7 @@ def run_b200(args):
         "roofline": roofline,
         "cpu_baseline": cpu,
         "edges": edges,
+        "knn": knn,
         "parity_vs_oracle_50k": parity_ok,
     }
     print(json.dumps(line), flush=True)

@@ -7,6 +7,7 @@
 // scan with strict '<' keeps: on equal distances the earlier node wins
 // (basic.cc:66,106).  k-NN is k selection passes (k is small: 1 for BiRRT, O(log N) for
 // kPRM*); every pass keeps the best key strictly greater than the previous one.
+#include <algorithm>
 #include <climits>
 #include <cstring>
 
@@ -22,6 +23,8 @@ struct hppb200_knn {
   size_t n = 0, cap = 0;
   hppb200::DeviceBuffer<double> d_queries, d_dist;
   hppb200::DeviceBuffer<long long> d_idx, d_count;
+  hppb200::DeviceBuffer<unsigned char> d_keys;  // previous keys [Q] + per-tile partial keys [tiles][Q]
+  int num_sms = 148;
 };
 
 namespace hppb200 {
@@ -93,6 +96,204 @@ knnQueryKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __
   }
 }
 
+// ---- tiled scan: the whole GPU works on every query -------------------------------------------------
+// Grid (node tiles, query groups): a CTA scans ITS contiguous slice of the node stream once per selection
+// pass and evaluates KNN_QB queries against every node it loads (the node stream is read from HBM once per
+// query group and pass; the array stays L2 resident across groups and passes when it fits).  Per pass r every
+// (tile, query) yields the smallest key strictly greater than the query's previous key; knnReduceKernel
+// merges the tiles, appends result r and publishes the new previous key.  Keys are (distance, node index),
+// i.e. the reference's strict '<' scan (basic.cc:66,106).  A single query over 1 M nodes is HBM-bound
+// (48 B per node at nq = 6); one-CTA-per-query scanning (knnQueryKernel) leaves all but one SM idle there.
+constexpr int KNN_QB = 4;
+
+__global__ void __launch_bounds__(KNN_THREADS)
+knnTileKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
+              const double* __restrict__ queries, int nqueries, int32_t ccFilter, const Key* __restrict__ prev,
+              Key* __restrict__ partial) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned char* sblob = smem + 16;
+  stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+  __shared__ Key red[KNN_QB][KNN_THREADS / 32];
+  const int q0 = blockIdx.y * KNN_QB;
+  const size_t lo = (size_t)((unsigned long long)n * blockIdx.x / gridDim.x);
+  const size_t hi = (size_t)((unsigned long long)n * (blockIdx.x + 1) / gridDim.x);
+  Key best[KNN_QB], pv[KNN_QB];
+  const double* qp[KNN_QB];
+#pragma unroll
+  for (int j = 0; j < KNN_QB; ++j) {
+    const int q = (q0 + j < nqueries) ? q0 + j : nqueries - 1;  // padding lanes repeat the last query
+    qp[j] = queries + (size_t)q * mv.nq;
+    pv[j] = prev[q];
+    best[j].d = CUDART_INF; best[j].i = LLONG_MAX;
+  }
+  for (size_t i = lo + threadIdx.x; i < hi; i += KNN_THREADS) {
+    if (ccFilter >= 0 && cc[i] != ccFilter) continue;
+    const double* node = nodes + i * (size_t)mv.nq;
+#pragma unroll
+    for (int j = 0; j < KNN_QB; ++j) {
+      const Key c = {weighedDistanceDev(T, mv, node, qp[j]), (long long)i};
+      if (keyLess(pv[j], c) && keyLess(c, best[j])) best[j] = c;
+    }
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int j = 0; j < KNN_QB; ++j) {
+    Key b = best[j];
+    for (int o = 16; o > 0; o >>= 1) {
+      const Key other = {__shfl_xor_sync(0xffffffffu, b.d, o), __shfl_xor_sync(0xffffffffu, b.i, o)};
+      if (keyLess(other, b)) b = other;
+    }
+    if (lane == 0) red[j][warp] = b;
+  }
+  __syncthreads();
+  if (threadIdx.x < KNN_QB && q0 + (int)threadIdx.x < nqueries) {
+    Key b = red[threadIdx.x][0];
+    for (int w = 1; w < KNN_THREADS / 32; ++w)
+      if (keyLess(red[threadIdx.x][w], b)) b = red[threadIdx.x][w];
+    partial[(size_t)blockIdx.x * nqueries + q0 + threadIdx.x] = b;
+  }
+}
+
+// one warp per query: merge the tiles of pass r
+__global__ void knnReduceKernel(const Key* __restrict__ partial, int ntiles, int nqueries, int k, int r, Key* __restrict__ prev,
+                                long long* __restrict__ idx, double* __restrict__ dist) {
+  const int q = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (q >= nqueries) return;
+  Key b = {CUDART_INF, LLONG_MAX};
+  for (int t = lane; t < ntiles; t += 32) {
+    const Key c = partial[(size_t)t * nqueries + q];
+    if (keyLess(c, b)) b = c;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const Key other = {__shfl_xor_sync(0xffffffffu, b.d, o), __shfl_xor_sync(0xffffffffu, b.i, o)};
+    if (keyLess(other, b)) b = other;
+  }
+  if (lane == 0) {
+    const bool found = b.i != LLONG_MAX;
+    idx[(size_t)q * k + r] = found ? b.i : -1;
+    dist[(size_t)q * k + r] = b.d;  // +inf when fewer than k candidates exist
+    prev[q] = b;                    // (inf, LLONG_MAX) admits nothing in later passes
+  }
+}
+
+__global__ void knnInitPrevKernel(Key* prev, int nqueries) {
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < nqueries) { prev[q].d = -1.0; prev[q].i = -1; }
+}
+
+// ---- single-pass k selection (k <= 32) ------------------------------------------------------------------
+// Every warp keeps, per query, its k smallest keys sorted across the lanes (lane j = j-th smallest, in
+// registers).  A node is looked at again only if its key beats the current k-th key (rare after the first few
+// hundred nodes); it is then inserted with one ballot + one shuffle.  Warps of a CTA are merged through shared
+// memory, CTAs (tiles) by knnMergeTopkKernel.  Keys are (distance, node index), so the result is the reference's
+// K-nearest SET (strict '>' against the heap top keeps the earlier node, basic.cc:106) in the engine's
+// documented order (ties by node index).
+__device__ __forceinline__ void topkInsert(Key& mine, Key& kth, const Key x, int k, int lane) {
+  const unsigned FULL = 0xffffffffu;
+  const bool gt = keyLess(x, mine);  // monotone over the lanes: true from the insertion point on
+  const unsigned g = __ballot_sync(FULL, gt);
+  const Key up = {__shfl_up_sync(FULL, mine.d, 1), __shfl_up_sync(FULL, mine.i, 1)};
+  if (gt) mine = (lane > 0 && ((g >> (lane - 1)) & 1u)) ? up : x;
+  kth.d = __shfl_sync(FULL, mine.d, k - 1);
+  kth.i = __shfl_sync(FULL, mine.i, k - 1);
+}
+
+__global__ void __launch_bounds__(KNN_THREADS)
+knnTileTopkKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
+                  const double* __restrict__ queries, int nqueries, int32_t ccFilter, int k, Key* __restrict__ partial) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned char* sblob = smem + 16;
+  stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+  constexpr int WARPS = KNN_THREADS / 32;
+  __shared__ Key lists[WARPS][KNN_QB][32];
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int q0 = blockIdx.y * KNN_QB;
+  const size_t lo = (size_t)((unsigned long long)n * blockIdx.x / gridDim.x);
+  const size_t hi = (size_t)((unsigned long long)n * (blockIdx.x + 1) / gridDim.x);
+  Key mine[KNN_QB], kth[KNN_QB];
+  const double* qp[KNN_QB];
+#pragma unroll
+  for (int j = 0; j < KNN_QB; ++j) {
+    const int q = (q0 + j < nqueries) ? q0 + j : nqueries - 1;  // padding repeats the last query
+    qp[j] = queries + (size_t)q * mv.nq;
+    mine[j].d = CUDART_INF; mine[j].i = LLONG_MAX;
+    kth[j] = mine[j];
+  }
+  for (size_t base = lo + (size_t)warp * 32; base < hi; base += (size_t)WARPS * 32) {
+    const size_t i = base + lane;
+    const bool ok = i < hi && (ccFilter < 0 || cc[i] == ccFilter);
+    const double* node = nodes + (ok ? i : lo) * (size_t)mv.nq;
+#pragma unroll
+    for (int j = 0; j < KNN_QB; ++j) {
+      const Key c = {weighedDistanceDev(T, mv, node, qp[j]), (long long)i};
+      unsigned m = __ballot_sync(FULL, ok && keyLess(c, kth[j]));
+      while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1u;
+        const Key x = {__shfl_sync(FULL, c.d, src), __shfl_sync(FULL, c.i, src)};
+        if (keyLess(x, kth[j])) topkInsert(mine[j], kth[j], x, k, lane);  // (warp-uniform condition)
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < KNN_QB; ++j) lists[warp][j][lane] = mine[j];
+  __syncthreads();
+  if (warp < KNN_QB && q0 + warp < nqueries) {  // warp j merges query j's lists of the other warps into its own
+    Key acc = lists[0][warp][lane];
+    Key ak = {__shfl_sync(FULL, acc.d, k - 1), __shfl_sync(FULL, acc.i, k - 1)};
+    for (int w = 1; w < WARPS; ++w) {
+      const Key c = lists[w][warp][lane];
+      unsigned m = __ballot_sync(FULL, lane < k && keyLess(c, ak));
+      while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1u;
+        const Key x = {__shfl_sync(FULL, c.d, src), __shfl_sync(FULL, c.i, src)};
+        if (keyLess(x, ak)) topkInsert(acc, ak, x, k, lane);
+      }
+    }
+    if (lane < k) partial[((size_t)blockIdx.x * nqueries + q0 + warp) * k + lane] = acc;
+  }
+}
+
+// one warp per query: merge the tiles' sorted lists, write the k results nearest first
+__global__ void knnMergeTopkKernel(const Key* __restrict__ partial, int ntiles, int nqueries, int k, long long* __restrict__ idx,
+                                   double* __restrict__ dist) {
+  const unsigned FULL = 0xffffffffu;
+  const int q = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (q >= nqueries) return;
+  Key acc = {CUDART_INF, LLONG_MAX}, ak = acc;
+  // the tiles' lists are one flat stream of ntiles * k keys: 32 keys per trip, 4 trips of loads in flight
+  const int total = ntiles * k;
+  for (int f0 = 0; f0 < total; f0 += 128) {
+    Key c[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int f = f0 + u * 32 + lane;
+      c[u].d = CUDART_INF; c[u].i = LLONG_MAX;
+      if (f < total) c[u] = partial[((size_t)(f / k) * nqueries + q) * k + (f % k)];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      unsigned m = __ballot_sync(FULL, keyLess(c[u], ak));
+      while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1u;
+        const Key x = {__shfl_sync(FULL, c[u].d, src), __shfl_sync(FULL, c[u].i, src)};
+        if (keyLess(x, ak)) topkInsert(acc, ak, x, k, lane);
+      }
+    }
+  }
+  if (lane < k) {
+    idx[(size_t)q * k + lane] = acc.i != LLONG_MAX ? acc.i : -1;
+    dist[(size_t)q * k + lane] = acc.d;
+  }
+}
+
 // withinBall: strict d < radius, output in scan order (basic.cc:170-181)
 __global__ void __launch_bounds__(KNN_THREADS)
 withinBallKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
@@ -155,6 +356,7 @@ int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out) {
     HPPB200_CUDA_CHECK(cudaSetDevice(device));
     nn->view = nn->model->deviceView(device);
     HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&nn->stream, cudaStreamNonBlocking));
+    HPPB200_CUDA_CHECK(cudaDeviceGetAttribute(&nn->num_sms, cudaDevAttrMultiProcessorCount, device));
     *out = nn;
   });
 }
@@ -213,12 +415,37 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
     if (nqueries == 0) return;
     HPPB200_CUDA_CHECK(cudaSetDevice(nn->device));
     const size_t nq = (size_t)nn->model->nq;
+    if (nqueries > 0x7fffffffull / 4) throw std::invalid_argument("too many queries in one call");
     const size_t smemBytes = 16 + nn->view.blob_bytes;
-    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnQueryKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-    if (flags & HPPB200_DEVICE_POINTERS) {
-      knnQueryKernel<<<(unsigned)nqueries, KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, queries, k, cc,
-                                                                               (long long*)idx, dist);
+    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+    auto run = [&](const double* d_q, long long* d_i, double* d_d) {
+      // k selection passes, each = tiled scan on the whole GPU + merge of the tiles (see knnTileKernel)
+      const unsigned groups = (unsigned)((nqueries + KNN_QB - 1) / KNN_QB);
+      size_t tiles = std::max<size_t>(1, std::min<size_t>((size_t)nn->num_sms * 4, (nn->n + KNN_THREADS - 1) / KNN_THREADS));
+      if (groups > 64) tiles = std::max<size_t>(1, std::min<size_t>(tiles, (size_t)nn->num_sms / 2));  // many groups fill the GPU anyway
+      if (k > 1 && k <= 32) {  // single pass (k = 1 is one selection pass anyway, without the insertion logic)
+        nn->d_keys.reserve(tiles * nqueries * (size_t)k * sizeof(Key) + 256);
+        Key* d_part = (Key*)nn->d_keys.p;
+        HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTileTopkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+        knnTileTopkKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
+                                                                                            (int)nqueries, cc, k, d_part);
+        knnMergeTopkKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, d_i, d_d);
+        HPPB200_CUDA_CHECK(cudaGetLastError());
+        return;
+      }
+      nn->d_keys.reserve((nqueries + tiles * nqueries) * sizeof(Key) + 256);
+      Key* d_prev = (Key*)nn->d_keys.p;
+      Key* d_part = d_prev + nqueries;
+      knnInitPrevKernel<<<(unsigned)((nqueries + 255) / 256), 256, 0, nn->stream>>>(d_prev, (int)nqueries);
+      for (int r = 0; r < k; ++r) {
+        knnTileKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
+                                                                                        (int)nqueries, cc, d_prev, d_part);
+        knnReduceKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, r, d_prev, d_i, d_d);
+      }
       HPPB200_CUDA_CHECK(cudaGetLastError());
+    };
+    if (flags & HPPB200_DEVICE_POINTERS) {
+      run(queries, (long long*)idx, dist);
       HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
       return;
     }
@@ -226,9 +453,7 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
     nn->d_idx.reserve(nqueries * k);
     nn->d_dist.reserve(nqueries * k);
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(nn->d_queries.p, queries, nqueries * nq * sizeof(double), cudaMemcpyHostToDevice, nn->stream));
-    knnQueryKernel<<<(unsigned)nqueries, KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, nn->d_queries.p, k,
-                                                                             cc, nn->d_idx.p, nn->d_dist.p);
-    HPPB200_CUDA_CHECK(cudaGetLastError());
+    run(nn->d_queries.p, nn->d_idx.p, nn->d_dist.p);
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(idx, nn->d_idx.p, nqueries * k * sizeof(int64_t), cudaMemcpyDeviceToHost, nn->stream));
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(dist, nn->d_dist.p, nqueries * k * sizeof(double), cudaMemcpyDeviceToHost, nn->stream));
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));

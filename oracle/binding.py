@@ -64,7 +64,10 @@ class Oracle:
 
     def __del__(self):
         if getattr(self, "h", None):
-            lib().oracle_destroy(self.h)
+            try:
+                lib().oracle_destroy(self.h)
+            except TypeError:  # interpreter shutdown: module globals are already gone
+                pass
             self.h = None
 
     # tables
