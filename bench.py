@@ -254,6 +254,31 @@ def run_b200(args):
     # identical results on both paths
     assert torch.equal(valid_h, valid_d.cpu()) and torch.equal(first_h, first_d.cpu())
 
+    # ---- N > 1: every rank validates its own shard of edges (Progressive), validity masks all-gathered ----
+    edges_sharded = None
+    if world > 1 and not args.no_edges:
+        ne = N_EDGES_PROG
+        cfg = pkg.uniform_configs(desc, 2 * ne, seed=SEED + 1, offset=rank * 2 * ne)
+        s1d = torch.from_numpy(np.ascontiguousarray(cfg[0::2])).to(dev)
+        s2d = torch.from_numpy(np.ascontiguousarray(cfg[1::2])).to(dev)
+        sLd = torch.from_numpy(ws.straight_lengths(cfg[0::2], cfg[1::2])).to(dev)
+        sv = torch.empty(ne, dtype=torch.uint8, device=dev)
+        stf = torch.empty(ne, dtype=torch.float64, device=dev)
+        stl = torch.empty(ne, dtype=torch.float64, device=dev)
+        spr = torch.empty(ne, dtype=torch.int32, device=dev)
+        srs = torch.empty(ne, dtype=torch.uint8, device=dev)
+        sv_all = torch.empty(ne * world, dtype=torch.uint8, device=dev)
+
+        def shard_call():
+            ws.validate_edges_ptr(pkg.METHOD_PROGRESSIVE, 1e-3, False, s1d.data_ptr(), s2d.data_ptr(), sLd.data_ptr(), ne,
+                                  sv.data_ptr(), stf.data_ptr(), stl.data_ptr(), spr.data_ptr(), srs.data_ptr(), FLAGS_DEV)
+            dist.all_gather_into_tensor(sv_all, sv)
+        ms_s, _, _ = timed(shard_call, 3, 1)
+        edges_sharded = {"value": world * ne * 3 / (ms_s * 1e-3), "unit": "edges/s", "edges_per_gpu": ne, "param": 1e-3,
+                         "method": "progressive", "collective": "all_gather of uint8 validity masks (NCCL)",
+                         "valid_frac_all_ranks": float(sv_all.float().mean().item())}
+        del s1d, s2d, sLd, sv, stf, stl, spr, srs, sv_all
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -378,6 +403,7 @@ def run_b200(args):
         "roofline": roofline,
         "cpu_baseline": cpu,
         "edges": edges,
+        "edges_sharded": edges_sharded,
         "knn": knn,
         "parity_vs_oracle_50k": parity_ok,
     }

@@ -1,12 +1,11 @@
 // Brute-force WeighedDistance nearest neighbour over roadmap nodes mirrored on the device
 // (reference src/nearest-neighbor/basic.cc:52-181, src/weighed-distance.cc:272-289).
 //
-// Exact FP64 path: one CTA per query scans all nodes (coalesced, 8*nq bytes per node: the
-// kernel is HBM/L2-bound on the node stream) and selects the k smallest by the
-// lexicographic key (distance, node index), which is exactly what the reference's linear
-// scan with strict '<' keeps: on equal distances the earlier node wins
-// (basic.cc:66,106).  k-NN is k selection passes (k is small: 1 for BiRRT, O(log N) for
-// kPRM*); every pass keeps the best key strictly greater than the previous one.
+// Exact FP64 path: the node stream (8*nq bytes per node, coalesced) is scanned by the whole GPU in
+// tiles and the k smallest are selected by the lexicographic key (distance, node index), which is
+// exactly what the reference's linear scan with strict '<' keeps: on equal distances the earlier node
+// wins (basic.cc:66,106).  1 < k <= 32: one pass with warp-register top-k lists; k = 1 or k > 32:
+// selection passes, each keeping the best key strictly greater than the previous one.
 #include <algorithm>
 #include <climits>
 #include <cstring>
@@ -50,52 +49,6 @@ struct Key {
 };
 __device__ __forceinline__ bool keyLess(const Key& a, const Key& b) { return a.d < b.d || (a.d == b.d && a.i < b.i); }
 
-__global__ void __launch_bounds__(KNN_THREADS)
-knnQueryKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
-               const double* __restrict__ queries, int k, int32_t ccFilter, long long* __restrict__ idx,
-               double* __restrict__ dist) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  uint64_t* bar = (uint64_t*)smem;
-  unsigned char* sblob = smem + 16;
-  stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
-  const Tables T = makeTables(sblob, mv);
-  __shared__ Key red[KNN_THREADS / 32];
-  __shared__ Key prevS;
-  const double* q = queries + (size_t)blockIdx.x * mv.nq;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  Key prev = {-1.0, -1};
-  for (int r = 0; r < k; ++r) {
-    Key best = {CUDART_INF, LLONG_MAX};
-    for (size_t i = threadIdx.x; i < n; i += KNN_THREADS) {
-      if (ccFilter >= 0 && cc[i] != ccFilter) continue;
-      Key c = {weighedDistanceDev(T, mv, nodes + i * (size_t)mv.nq, q), (long long)i};
-      if (keyLess(prev, c) && keyLess(c, best)) best = c;
-    }
-    for (int o = 16; o > 0; o >>= 1) {
-      Key other = {__shfl_xor_sync(0xffffffffu, best.d, o), __shfl_xor_sync(0xffffffffu, best.i, o)};
-      if (keyLess(other, best)) best = other;
-    }
-    if (lane == 0) red[warp] = best;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      Key b = red[0];
-      for (int w = 1; w < KNN_THREADS / 32; ++w)
-        if (keyLess(red[w], b)) b = red[w];
-      prevS = b;
-      const bool found = b.i != LLONG_MAX;
-      idx[(size_t)blockIdx.x * k + r] = found ? b.i : -1;
-      dist[(size_t)blockIdx.x * k + r] = b.d;
-    }
-    __syncthreads();
-    prev = prevS;
-    if (prev.i == LLONG_MAX) {  // fewer than k candidates: pad the rest
-      if (threadIdx.x == 0)
-        for (int s = r + 1; s < k; ++s) { idx[(size_t)blockIdx.x * k + s] = -1; dist[(size_t)blockIdx.x * k + s] = CUDART_INF; }
-      break;
-    }
-  }
-}
-
 // ---- tiled scan: the whole GPU works on every query -------------------------------------------------
 // Grid (node tiles, query groups): a CTA scans ITS contiguous slice of the node stream once per selection
 // pass and evaluates KNN_QB queries against every node it loads (the node stream is read from HBM once per
@@ -103,7 +56,7 @@ knnQueryKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __
 // (tile, query) yields the smallest key strictly greater than the query's previous key; knnReduceKernel
 // merges the tiles, appends result r and publishes the new previous key.  Keys are (distance, node index),
 // i.e. the reference's strict '<' scan (basic.cc:66,106).  A single query over 1 M nodes is HBM-bound
-// (48 B per node at nq = 6); one-CTA-per-query scanning (knnQueryKernel) leaves all but one SM idle there.
+// (48 B per node at nq = 6); one CTA per query would leave all but one SM idle there.
 constexpr int KNN_QB = 4;
 
 __global__ void __launch_bounds__(KNN_THREADS)

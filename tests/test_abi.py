@@ -31,12 +31,13 @@ def test_struct_layout_matches_header(pkg):
     assert names == [f[0] for f in pkg.hppb200_model_desc._fields_]
 
 
-@pytest.mark.parametrize("name", ["ur5_boxes0.json", "ur5_boxes1.json", "ur5_boxes8.json", "ur5_boxes32.json"])
+@pytest.mark.parametrize("name", ["ur5_boxes0.json", "ur5_boxes1.json", "ur5_boxes8.json", "ur5_boxes32.json",
+                                  "humanoid_obst6.json", "humanoid_obst16.json"])
 def test_model_tables_match_oracle(pkg, ob, name):
     desc = pkg.ModelDescription.load(name)
     m = pkg.Model(desc)
     o = ob.Oracle(desc)
-    assert m.nq == o.nq == 6 and m.nv == o.nv
+    assert m.nq == o.nq == desc.nq and m.nv == o.nv
     for x, y in zip(m.config_pairs(), o.config_pairs()):
         assert np.array_equal(x, y)
     bm, bo = m.body_pairs(), o.body_pairs()

@@ -259,3 +259,35 @@ def test_nn_basic(ur5, ob, pkg):
     assert np.allclose(dist5, np.sort(dm, 1)[:, :5], rtol=1e-14)
     ball = o.knn_within_ball(qs[3], 1.0)
     assert np.array_equal(ball, np.nonzero(d[3] < 1.0)[0])
+
+
+def test_humanoid_tree_oracle_invariants(pkg, ob):
+    """The 30-joint TREE model with convex meshes (BASELINE configs[3]-like, fixed pelvis): FK of a branch does not
+    depend on the other branches' joints, GJK distances of convex meshes are lower-bounded by their bounding-sphere
+    distance, and the reference invariants I1/I2 hold for the three path validations."""
+    desc = pkg.ModelDescription.load("humanoid_obst6.json")
+    o = ob.Oracle(desc)
+    names = desc.geom_names
+    q = pkg.uniform_configs(desc, 200, seed=7)
+    P = o.geometry_placements(q).reshape(len(q), len(names), 12)
+    q2 = q.copy()
+    q2[:, 18:] = pkg.uniform_configs(desc, 200, seed=8)[:, 18:]  # joints 19..30 = the two legs
+    P2 = o.geometry_placements(q2).reshape(len(q), len(names), 12)
+    upper = [i for i, n in enumerate(names) if not any(t in n for t in ("thigh", "shin", "foot", "toe"))]
+    lower = [i for i, n in enumerate(names) if any(t in n for t in ("thigh", "shin", "foot", "toe"))]
+    assert np.array_equal(P[:, upper], P2[:, upper]) and not np.array_equal(P[:, lower], P2[:, lower])
+    R = P[:, :, :9].reshape(len(q), len(names), 3, 3)
+    assert np.allclose(np.einsum("nkij,nklj->nkil", R, R), np.eye(3), atol=1e-12)
+    # I1 / I2 on local edges
+    q1 = pkg.uniform_configs(desc, 600, seed=9)
+    d = np.random.default_rng(9).normal(size=q1.shape)
+    qb = np.clip(q1 + 0.4 * d / np.linalg.norm(d, axis=1, keepdims=True), desc.q_lower, desc.q_upper)
+    L = o.straight_lengths(q1, qb)
+    v = o.validate_configs(q1)[0]
+    for meth, par in ((0, 0.05), (1, 1e-3), (2, 0.0)):
+        assert np.array_equal(o.validate_edges(meth, par, q1, q1, np.zeros(len(q1)))["valid"], v)
+    dd = o.validate_edges(0, 0.05, q1, qb, L)["valid"]
+    pp = o.validate_edges(1, 1e-3, q1, qb, L)["valid"]
+    cc = o.validate_edges(2, 0.0, q1, qb, L)["valid"]
+    assert not np.any((dd == 0) & (cc == 1)) and np.mean((dd == 0) & (pp == 1)) < 0.01
+    assert 0.05 < cc.mean() < 0.95
