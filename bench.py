@@ -186,7 +186,7 @@ def run_b200(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["NCCL_DEBUG"] = os.environ.get("HPPB200_NCCL_DEBUG", "WARN")  # keep stdout to the one JSON line
+        os.environ["NCCL_DEBUG"] = os.environ.get("HPPB200_NCCL_DEBUG", "NONE")  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     desc = pkg.ModelDescription.load(MODEL)
@@ -217,10 +217,13 @@ def run_b200(args):
     def step_e2e():
         ws.validate_configs_ptr(q_host.data_ptr(), n, valid_h.data_ptr(), first_h.data_ptr(), reason_h.data_ptr(), 0)
 
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, all_ranks=True):
+        """CUDA-event time of `steps` calls; all_ranks: barrier on both sides and MAX over ranks (every rank must
+        call it); all_ranks=False is for the rank-0-only secondary metrics."""
+        multi = world > 1 and all_ranks
         for _ in range(warmup):
             fn()
-        if world > 1:
+        if multi:
             dist.barrier()
         torch.cuda.synchronize()
         evs = []
@@ -233,11 +236,11 @@ def run_b200(args):
             e1.record(stream)
             evs.append((e0, e1))
         torch.cuda.synchronize()
-        if world > 1:
+        if multi:
             dist.barrier()
         w1 = time.time()
         ms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device=dev)
-        if world > 1:
+        if multi:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item()), w0, w1
 
@@ -344,9 +347,9 @@ def run_b200(args):
                 ws.validate_edges_ptr(meth, par, False, e1h.data_ptr(), e2h.data_ptr(), L_h.data_ptr(), ne, ev_h.data_ptr(),
                                       tf_h.data_ptr(), 0, 0, 0, 0)
             s0 = ws.stats()
-            ms_d, _, _ = timed(dev_call, 3, 1)
+            ms_d, _, _ = timed(dev_call, 3, 1, all_ranks=False)
             s1 = ws.stats()
-            ms_h, _, _ = timed(host_call, 3, 1)
+            ms_h, _, _ = timed(host_call, 3, 1, all_ranks=False)
             res[name] = {"value": ne * 3 / (ms_d * 1e-3), "e2e": ne * 3 / (ms_h * 1e-3), "unit": "edges/s", "n_edges": ne,
                          "param": par, "valid_frac": float(ev_h.numpy()[:ne].mean()),
                          "samples_per_edge": (s1["edge_samples"] - s0["edge_samples"]) / (4 * ne),
