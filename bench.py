@@ -32,8 +32,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_CONFIGS = 1 << 20          # configurations per GPU per step (BASELINE configs[1])
-N_EDGES = 1 << 17            # edges per GPU for the secondary metric (Discretized, Dichotomy)
-N_EDGES_PROG = 1 << 20       # Progressive: 1M edges per GPU (BASELINE configs[4]: 10M edges over 8 GPUs)
+N_EDGES = 1 << 17            # edges per GPU for the secondary metric (Discretized)
+N_EDGES_PROG = 1 << 20       # Progressive, Dichotomy: 1M edges per GPU (BASELINE configs[4]: 10M edges over 8 GPUs)
 SEED = 12345
 MODEL = "ur5_boxes8.json"
 # Algorithmic flop model (FMA = 2): FK = 126*njoints + 63*ngeoms + 40*njoints (sincos);
@@ -337,7 +337,7 @@ def run_b200(args):
         res = {}
         for name, meth, par in (("progressive", pkg.METHOD_PROGRESSIVE, 1e-3), ("discretized", pkg.METHOD_DISCRETIZED, 0.05),
                                 ("dichotomy", pkg.METHOD_DICHOTOMY, 0.0)):
-            ne = N_EDGES_PROG if name == "progressive" else N_EDGES  # leading `ne` edges of the same stream
+            ne = N_EDGES if name == "discretized" else N_EDGES_PROG  # leading `ne` edges of the same stream
 
             def dev_call():
                 ws.validate_edges_ptr(meth, par, False, e1d.data_ptr(), e2d.data_ptr(), Ld.data_ptr(), ne, ev_d.data_ptr(),

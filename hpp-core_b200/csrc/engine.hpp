@@ -145,6 +145,7 @@ struct Workspace {
   int engine_threads = 128;    // CTA size of the engine (HPPB200_ENGINE_THREADS: 64 | 96 | 128)
   int engine_kind = 2;         // Progressive: 2 wavefront rounds (kernels_wavefront.cu), 1 CTA engine (HPPB200_ENGINE)
   size_t wavefront_min = 100000;  // smallest batch that takes the wavefront engine (HPPB200_WF_MIN)
+  long wavefront_tail = -1;    // slots left when the wavefront hands the tail to the walker (-1: min(2048, n/64); HPPB200_WF_TAIL)
   size_t wavefront_slots = 0;  // resident edge slots of the wavefront engine (0: 2048 per SM; HPPB200_WF_SLOTS)
   double engine_alpha = 1.2;   // candidate prediction: alpha x previous step (HPPB200_ENGINE_ALPHA; 1.2 measured best)
   // staging for host-pointer calls
@@ -174,7 +175,7 @@ void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2
 bool launchProgressiveEngine(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
                              const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                              int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
-bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
+bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const double* d_q1, const double* d_q2,
                                 const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                                 int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
 void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1,

@@ -644,8 +644,10 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   bool engineDone = false;
   // Large batches: round-synchronous wavefront engine (kernels_wavefront.cu); its ~600 rounds of a few kernels
   // each are a fixed latency that small batches do not amortise, those go to the CTA engine.
-  if (method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine && ws->engine_kind >= 2 && n >= ws->wavefront_min)
-    engineDone = launchWavefrontProgressive(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair,
+  // (Dichotomy's rounds are heavier and its tail longer: the break-even batch is about four times larger)
+  const size_t wfMin = method == HPPB200_METHOD_DICHOTOMY ? 4 * ws->wavefront_min : ws->wavefront_min;
+  if (method != HPPB200_METHOD_DISCRETIZED && ws->use_engine && ws->engine_kind >= 2 && n >= wfMin)
+    engineDone = launchWavefront(ws, method, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair,
                                             d_reason, REASON_OVERFLOW_INTERNAL);
   if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine)
     engineDone = launchProgressiveEngine(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,

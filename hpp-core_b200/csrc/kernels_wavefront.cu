@@ -32,6 +32,7 @@
 // Progressive keeps each pair's validated set connected, so one closed interval per pair;
 // an insert that would open a second interval hands the edge to the walker (never silently accepted).
 // Placements: AoS per slot (96 contiguous bytes per geometry, read by the jobs).
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -85,6 +86,10 @@ struct WFArgs {
   uint8_t* st_flags;   // bit0 active, bit1 retired, bits 2-3 `finished`
   uint8_t* st_nEm;
   unsigned long long* st_vmask;  // [W][E] valid_ bits by order position
+  unsigned long long* st_cbits;  // Dichotomy: [4 * W][E] bit planes of the pairs' list lengths
+  double2* ivl;        // Dichotomy: [NP * WD_K][E] validated intervals by order position
+  double2* sub;        // Dichotomy: [WD_KS][E] valid subset of the edge
+  uint8_t* st_subCnt;  // Dichotomy: [E]
   uint16_t* emPos;     // [WF_RB][E] order position of the k-th emitted body pair
   uint8_t* emRes;      // [WF_RB][E] its first result slot
   double2* fold;       // [WF_RB][E] its folded result: validated interval (a, b), or (geometry pair, -inf)
@@ -145,6 +150,152 @@ __device__ __forceinline__ void maskPut(u64 (&m)[W], int p, bool v) {  // overwr
     if ((p >> 6) == w) m[w] = (m[w] & ~(1ull << (p & 63))) | ((u64)(v ? 1 : 0) << (p & 63));
 }
 
+// ---- pieces shared by the Progressive and Dichotomy control kernels ---------------------------------------
+// Per-edge tables of the edges that just entered a slot, the whole warp working on one new edge at a time
+// (lane = joint, then lane = body pair): intervals empty, order = construction order, velocity norms, maximal
+// velocities.  Called by all lanes; `got` marks the lanes whose slot received an edge.
+__device__ __forceinline__ void wfNewEdgeTables(const ModelView& mv, const WFArgs& A, const Tables& T, uint32_t e, int lane, bool got,
+                                                uint32_t edge, double L) {
+  const unsigned FULL = 0xffffffffu;
+  const uint32_t E = A.E;
+  const int NP = mv.nbodypairs;
+  const double INF = CUDART_INF;
+  unsigned gm = __ballot_sync(FULL, got);
+  while (gm) {
+    const int srcLane = __ffs(gm) - 1;
+    gm &= gm - 1u;
+    const uint32_t es = e - (uint32_t)lane + (uint32_t)srcLane;
+    const uint32_t ed = __shfl_sync(FULL, edge, srcLane);
+    const double Ls = __shfl_sync(FULL, L, srcLane);
+    const double* q1 = A.q1 + (size_t)ed * mv.nq;
+    const double* q2 = A.q2 + (size_t)ed * mv.nq;
+    if (Ls != 0) {
+      // per-joint norms of Vb = |q2 - q1| / L (StraightPath::impl_velocityBound, straight-path.cc:132-140)
+      for (int j = lane; j < mv.njoints; j += 32) {
+        const DevJoint& J = T.joints[j];
+        const int nvj = J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1;
+        double sj = 0;
+        for (int k = 0; k < nvj; ++k) {
+          const double vb = fabs(q2[J.idx_v + k] - q1[J.idx_v + k]) / Ls;
+          sj = fma(vb, vb, sj);
+        }
+        A.sv[(size_t)J.idx_v * E + es] = sqrt(sj);
+      }
+    }
+    __syncwarp();
+    // SolidSolidCollision::computeMaximalVelocity (solid-solid-collision.cc:76-99), fixed per edge and pair
+    for (int id = lane; id < NP; id += 32) {
+      const DevBodyPair& B = T.bodypairs[id];
+      double Vm;
+      if (Ls == 0) Vm = INF;  // BodyPairCollision::setupPath, zero-length path
+      else {
+        double ab = 0;
+        for (int c = B.coef_begin; c < B.coef_end; ++c) ab += T.coefs[c].value * __ldcg(A.sv + (size_t)T.coefs[c].idx_v * E + es);
+        Vm = ab;
+        if (B.joint_b != 0) {
+          double ba = 0;
+          for (int c = B.rcoef_begin; c < B.rcoef_end; ++c) ba += T.rcoefs[c].value * __ldcg(A.sv + (size_t)T.rcoefs[c].idx_v * E + es);
+          if (ba < ab) Vm = ba;
+        }
+      }
+      A.vmax[(size_t)id * E + es] = Vm;
+      if (A.lohi) A.lohi[(size_t)id * E + es] = make_double2(INF, -INF);
+      A.ord[(size_t)es * A.ordStride + id] = (uint16_t)id;
+    }
+  }
+  __syncwarp();
+}
+
+// One job per geometry pair of every candidate body pair, in position order; job list slots by warp prefix
+// sums, one shared-memory atomic per warp, one global atomic per CTA and list.  Called by all threads of the CTA.
+template <int W>
+__device__ __forceinline__ void wfEmitJobs(const WFArgs& A, const Tables& T, uint32_t e, int lane, bool active, const u64 (&cand)[W],
+                                           int& nEm, unsigned* sCnt, WFRoundCtl* ctl) {
+  const unsigned FULL = 0xffffffffu;
+  const uint32_t E = A.E;
+  uint32_t jl[WF_RG];  // geometry pair | GJK flag << 31, in result order
+  int nr = 0, nGl = 0, nCl = 0;
+  if (active) {
+    int nb = 0;
+    bool full = false;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      u64 mw = cand[w];
+      while (mw && !full) {
+        const int p = w * 64 + __ffsll((long long)mw) - 1;
+        mw &= mw - 1ull;
+        const int id = A.ord[(size_t)e * A.ordStride + p];
+        const DevBodyPair& B = T.bodypairs[id];
+        const int ng = B.pair_end - B.pair_begin;
+        if (nb >= WF_RB || nr + ng > WF_RG) { full = true; break; }
+        A.emPos[(size_t)nb * E + e] = (uint16_t)p;
+        A.emRes[(size_t)nb * E + e] = (uint8_t)nr;
+        for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
+          const bool g = T.bgpairs[gp].kind == PK_GJK;
+          jl[nr++] = (uint32_t)gp | (g ? 0x80000000u : 0u);
+          if (g) ++nGl; else ++nCl;
+        }
+        ++nb;
+      }
+    }
+    nEm = nb;
+  }
+  int gOff = nGl, cOff = nCl;  // inclusive scans
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int g2 = __shfl_up_sync(FULL, gOff, o), c2 = __shfl_up_sync(FULL, cOff, o);
+    if (lane >= o) { gOff += g2; cOff += c2; }
+  }
+  unsigned wG = 0, wC = 0;
+  if (lane == 31) {
+    wG = gOff ? atomicAdd(&sCnt[0], (unsigned)gOff) : 0u;
+    wC = cOff ? atomicAdd(&sCnt[1], (unsigned)cOff) : 0u;
+  }
+  wG = __shfl_sync(FULL, wG, 31);
+  wC = __shfl_sync(FULL, wC, 31);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    sCnt[2] = sCnt[0] ? atomicAdd(&ctl->nG, sCnt[0]) : 0u;
+    sCnt[3] = sCnt[1] ? atomicAdd(&ctl->nC, sCnt[1]) : 0u;
+  }
+  __syncthreads();
+  size_t gi = (size_t)sCnt[2] + wG + (unsigned)(gOff - nGl);
+  size_t ci = (size_t)sCnt[3] + wC + (unsigned)(cOff - nCl);
+  for (int i = 0; i < nr; ++i) {
+    const uint32_t j = jl[i];
+    const unsigned long long job =
+        (unsigned long long)e | ((unsigned long long)(j & 0x00ffffffu) << 32) | ((unsigned long long)i << 56);
+    if (j & 0x80000000u) A.jobsG[gi++] = job;
+    else A.jobsC[ci++] = job;
+  }
+}
+
+// alive counter of the round + statistics: warp reduce, shared-memory atomics, one global atomic per CTA
+__device__ __forceinline__ void wfPublish(const WFArgs& A, DeviceStats* stats, unsigned* sCnt, int lane, bool retired, unsigned samples,
+                                          unsigned discarded, unsigned caps, unsigned overflows) {
+  const unsigned FULL = 0xffffffffu;
+  const int nAlive = __syncthreads_count(!retired);  // a free slot retires only after a failed refill
+  const unsigned sm = __reduce_add_sync(FULL, samples), dc = __reduce_add_sync(FULL, discarded);
+  const unsigned cp = __reduce_add_sync(FULL, caps), ov = __reduce_add_sync(FULL, overflows);
+  if (lane == 0) {
+    if (sm) atomicAdd(&sCnt[4], sm);
+    if (dc) atomicAdd(&sCnt[5], dc);
+    if (cp) atomicAdd(&sCnt[6], cp);
+    if (ov) atomicAdd(&sCnt[7], ov);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    if (nAlive) atomicAdd(A.alive + A.aliveIdx, (unsigned)nAlive);
+    if (stats) {
+      if (sCnt[4]) atomicAdd(&stats->edge_samples, (unsigned long long)sCnt[4]);
+      if (sCnt[5]) atomicAdd(&stats->discarded_tests, (unsigned long long)sCnt[5]);
+      if (sCnt[6]) atomicAdd(&stats->iter_cap_hits, (unsigned long long)sCnt[6]);
+      if (sCnt[7]) atomicAdd(&stats->overflow, (unsigned long long)sCnt[7]);
+      if (blockIdx.x == 0) atomicAdd(&stats->engine_ticks, 1ull);
+    }
+  }
+}
+
 // bits c0 .. c0 + WF_CH - 1 of a position mask, and OR-ing such a chunk back (one shift per chunk for W = 1)
 template <int W>
 __device__ __forceinline__ unsigned chunkBits(const u64 (&m)[W], int c0) {
@@ -152,6 +303,14 @@ __device__ __forceinline__ unsigned chunkBits(const u64 (&m)[W], int c0) {
   unsigned r = 0;
 #pragma unroll
   for (int k = 0; k < WF_CH; ++k) r |= (maskGet<W>(m, c0 + k) ? 1u : 0u) << k;
+  return r;
+}
+template <int W, int N>
+__device__ __forceinline__ unsigned chunkBitsN(const u64 (&m)[W], int c0) {  // bits c0 .. c0 + N - 1
+  if (W == 1) return c0 < 64 ? (unsigned)(m[0] >> c0) & ((1u << N) - 1u) : 0u;
+  unsigned r = 0;
+#pragma unroll
+  for (int k = 0; k < N; ++k) r |= (maskGet<W>(m, c0 + k) ? 1u : 0u) << k;
   return r;
 }
 template <int W>
@@ -379,51 +538,7 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
           got = true;
         }
       }
-      // per-edge tables of the new edges, the whole warp working on one new edge at a time (lane = joint, then
-      // lane = body pair): intervals empty, order = construction order, velocity norms, maximal velocities
-      unsigned gm = __ballot_sync(FULL, got);
-      while (gm) {
-        const int srcLane = __ffs(gm) - 1;
-        gm &= gm - 1u;
-        const uint32_t es = e - (uint32_t)lane + (uint32_t)srcLane;
-        const uint32_t ed = __shfl_sync(FULL, edge, srcLane);
-        const double Ls = __shfl_sync(FULL, L, srcLane);
-        const double* q1 = A.q1 + (size_t)ed * mv.nq;
-        const double* q2 = A.q2 + (size_t)ed * mv.nq;
-        if (Ls != 0) {
-          // per-joint norms of Vb = |q2 - q1| / L (StraightPath::impl_velocityBound, straight-path.cc:132-140)
-          for (int j = lane; j < mv.njoints; j += 32) {
-            const DevJoint& J = T.joints[j];
-            const int nvj = J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1;
-            double sj = 0;
-            for (int k = 0; k < nvj; ++k) {
-              const double vb = fabs(q2[J.idx_v + k] - q1[J.idx_v + k]) / Ls;
-              sj = fma(vb, vb, sj);
-            }
-            A.sv[(size_t)J.idx_v * E + es] = sqrt(sj);
-          }
-        }
-        __syncwarp();
-        // SolidSolidCollision::computeMaximalVelocity (solid-solid-collision.cc:76-99), fixed per edge and pair
-        for (int id = lane; id < NP; id += 32) {
-          const DevBodyPair& B = T.bodypairs[id];
-          double Vm;
-          if (Ls == 0) Vm = INF;  // BodyPairCollision::setupPath, zero-length path
-          else {
-            double ab = 0;
-            for (int c = B.coef_begin; c < B.coef_end; ++c) ab += T.coefs[c].value * __ldcg(A.sv + (size_t)T.coefs[c].idx_v * E + es);
-            Vm = ab;
-            if (B.joint_b != 0) {
-              double ba = 0;
-              for (int c = B.rcoef_begin; c < B.rcoef_end; ++c) ba += T.rcoefs[c].value * __ldcg(A.sv + (size_t)T.rcoefs[c].idx_v * E + es);
-              if (ba < ab) Vm = ba;
-            }
-          }
-          A.vmax[(size_t)id * E + es] = Vm;
-          A.lohi[(size_t)id * E + es] = make_double2(INF, -INF);
-          A.ord[(size_t)es * A.ordStride + id] = (uint16_t)id;
-        }
-      }
+      wfNewEdgeTables(mv, A, T, e, lane, got, edge, L);
       __syncwarp();
     }
   }
@@ -442,64 +557,7 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
   }
 
   // ---- EMIT: one job per geometry pair of every candidate, in position order -------------------------  @region emit
-  uint32_t jl[WF_RG];  // geometry pair | GJK flag << 31, in result order
-  int nr = 0, nGl = 0, nCl = 0;
-  if (active) {
-    int nb = 0;
-    bool full = false;
-#pragma unroll
-    for (int w = 0; w < W; ++w) {
-      u64 mw = cand[w];
-      while (mw && !full) {
-        const int p = w * 64 + __ffsll((long long)mw) - 1;
-        mw &= mw - 1ull;
-        const int id = A.ord[(size_t)e * A.ordStride + p];
-        const DevBodyPair& B = T.bodypairs[id];
-        const int ng = B.pair_end - B.pair_begin;
-        if (nb >= WF_RB || nr + ng > WF_RG) { full = true; break; }
-        A.emPos[(size_t)nb * E + e] = (uint16_t)p;
-        A.emRes[(size_t)nb * E + e] = (uint8_t)nr;
-        for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
-          const bool g = T.bgpairs[gp].kind == PK_GJK;
-          jl[nr++] = (uint32_t)gp | (g ? 0x80000000u : 0u);
-          if (g) ++nGl; else ++nCl;
-        }
-        ++nb;
-      }
-    }
-    nEm = nb;
-  }
-  // job list slots: warp prefix sums, one shared-memory atomic per warp, one global atomic per CTA
-  {
-    int gOff = nGl, cOff = nCl;  // inclusive scans
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int g2 = __shfl_up_sync(FULL, gOff, o), c2 = __shfl_up_sync(FULL, cOff, o);
-      if (lane >= o) { gOff += g2; cOff += c2; }
-    }
-    unsigned wG = 0, wC = 0;
-    if (lane == 31) {
-      wG = gOff ? atomicAdd(&sCnt[0], (unsigned)gOff) : 0u;
-      wC = cOff ? atomicAdd(&sCnt[1], (unsigned)cOff) : 0u;
-    }
-    wG = __shfl_sync(FULL, wG, 31);
-    wC = __shfl_sync(FULL, wC, 31);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      sCnt[2] = sCnt[0] ? atomicAdd(&ctl->nG, sCnt[0]) : 0u;
-      sCnt[3] = sCnt[1] ? atomicAdd(&ctl->nC, sCnt[1]) : 0u;
-    }
-    __syncthreads();
-    size_t gi = (size_t)sCnt[2] + wG + (unsigned)(gOff - nGl);
-    size_t ci = (size_t)sCnt[3] + wC + (unsigned)(cOff - nCl);
-    for (int i = 0; i < nr; ++i) {
-      const uint32_t j = jl[i];
-      const unsigned long long job =
-          (unsigned long long)e | ((unsigned long long)(j & 0x00ffffffu) << 32) | ((unsigned long long)i << 56);
-      if (j & 0x80000000u) A.jobsG[gi++] = job;
-      else A.jobsC[ci++] = job;
-    }
-  }
+  wfEmitJobs<W>(A, T, e, lane, active, cand, nEm, sCnt, ctl);
 
   // ---- store the slot state -------------------------------------------------------------------------  @region store
   A.st_flags[e] = (uint8_t)((active ? 1 : 0) | (retired ? 2 : 0) | (finished << 2) | ((active && needFK) ? 16 : 0));
@@ -511,26 +569,331 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
 #pragma unroll
     for (int w = 0; w < W; ++w) A.st_vmask[(size_t)w * E + e] = vmask[w];
   }
-  const int nAlive = __syncthreads_count(!retired);  // a free slot retires only after a failed refill
-  const unsigned sm = __reduce_add_sync(FULL, samples), dc = __reduce_add_sync(FULL, discarded);
-  const unsigned cp = __reduce_add_sync(FULL, caps), ov = __reduce_add_sync(FULL, overflows);
-  if (lane == 0) {
-    if (sm) atomicAdd(&sCnt[4], sm);
-    if (dc) atomicAdd(&sCnt[5], dc);
-    if (cp) atomicAdd(&sCnt[6], cp);
-    if (ov) atomicAdd(&sCnt[7], ov);
+  wfPublish(A, stats, sCnt, lane, retired, samples, discarded, caps, overflows);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Control kernel for continuousValidation::Dichotomy (reference src/continuous-validation/dichotomy.cc:68-132).
+// Same round structure as Progressive; what differs:
+//  * t jumps (middle of the first non-validated gap), so a body pair's validated set is a LIST of disjoint closed
+//    intervals (boost::icl::interval_set in the reference): up to WD_K per pair, position-major like `lohi`.
+//    Bisection towards the validated start leaves about log2(L / interval width) disjoint intervals on the
+//    binding pairs before they merge (6-8 on random UR5 edges, although 99 % of the FINAL lists have <= 4); an
+//    insert that needs more than WD_K hands the edge to the walker, which has 255-entry lists.  List lengths
+//    are 4 bit planes kept in registers, so the scan knows which intervals to load without loading a count.
+//  * the edge's valid subset (Intervals::unionInterval, src/continuous-validation/intervals.hh) is a list of up to
+//    WD_KS intervals per slot.
+//  * the next parameter is known only after the scan, so the candidates of the next sample come from a second,
+//    emit-only scan in the same round (window = alpha x the half-width just validated).
+constexpr int WD_K = 12;
+constexpr int WD_KS = 16;
+constexpr int WD_CH = 8;  // first intervals of this many positions are loaded ahead of their use
+
+// Sorted disjoint closed-interval list, element j at v[j * stride]: same observable behaviour as the reference
+// Intervals::unionInterval and as interval_set<closed>::insert (touching intervals merge).  False on overflow.
+__device__ __forceinline__ bool wdUnion(double2* v, size_t stride, int& cnt, int cap, double a, double b) {
+  int i = 0;
+  while (i < cnt && v[i * stride].y < a) ++i;
+  if (i == cnt) {
+    if (cnt == cap) return false;
+    v[i * stride] = make_double2(a, b);
+    ++cnt;
+    return true;
   }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    if (nAlive) atomicAdd(A.alive + A.aliveIdx, (unsigned)nAlive);
-    if (stats) {
-      if (sCnt[4]) atomicAdd(&stats->edge_samples, (unsigned long long)sCnt[4]);
-      if (sCnt[5]) atomicAdd(&stats->discarded_tests, (unsigned long long)sCnt[5]);
-      if (sCnt[6]) atomicAdd(&stats->iter_cap_hits, (unsigned long long)sCnt[6]);
-      if (sCnt[7]) atomicAdd(&stats->overflow, (unsigned long long)sCnt[7]);
-      if (blockIdx.x == 0) atomicAdd(&stats->engine_ticks, 1ull);
+  if (b < v[i * stride].x) {
+    if (cnt == cap) return false;
+    for (int k = cnt; k > i; --k) v[k * stride] = v[(k - 1) * stride];
+    v[i * stride] = make_double2(a, b);
+    ++cnt;
+    return true;
+  }
+  double nlo = v[i * stride].x;
+  if (a < nlo) nlo = a;
+  double nhi = b;
+  int j = i;
+  while (j < cnt && v[j * stride].x <= b) {
+    const double h = v[j * stride].y;
+    if (h > nhi) nhi = h;
+    ++j;
+  }
+  v[i * stride] = make_double2(nlo, nhi);
+  const int removed = j - i - 1;
+  if (removed > 0) {
+    for (int k = i + 1; k + removed < cnt; ++k) v[k * stride] = v[(k + removed) * stride];
+    cnt -= removed;
+  }
+  return true;
+}
+__device__ __forceinline__ bool wdContains(const double2* v, size_t stride, int cnt, double a, double b) {
+  for (int i = 0; i < cnt; ++i) {
+    const double2 x = v[i * stride];
+    if (x.x <= a && b <= x.y) return true;
+  }
+  return false;
+}
+
+template <int W>
+__global__ void __launch_bounds__(WF_CTHREADS)
+wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
+  extern __shared__ __align__(16) unsigned char smem[];  // @region setup
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned* sCnt = (unsigned*)(smem + 16);
+  unsigned char* sblob = smem + 48;
+  if (threadIdx.x < 8) sCnt[threadIdx.x] = 0u;
+  stageBlobTMA(sblob, mv.blob, mv.edge_blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+
+  const unsigned FULL = 0xffffffffu;
+  const uint32_t E = A.E;
+  const uint32_t e = blockIdx.x * WF_CTHREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int NP = mv.nbodypairs;
+  const double INF = CUDART_INF;
+  const bool reverse = A.reverse != 0;
+  WFRoundCtl* ctl = A.ctl + (A.round & 1);
+  if (e == 0) {
+    WFRoundCtl* nx = A.ctl + ((A.round + 1) & 1);
+    nx->nG = 0; nx->nC = 0; nx->headG = 0; nx->headC = 0;
+  }
+
+  const uint8_t flags0 = A.st_flags[e];
+  bool active = (flags0 & 1) != 0, retired = (flags0 & 2) != 0;
+  double t = 0, hp = INF, ilo = -INF, ihi = INF, L = 0;
+  uint32_t edge = 0, iters = 0;
+  int pos = 0, smallest = 0, nEm = 0, subCnt = 0;
+  u64 cand[W], vmask[W], c0[W], c1[W], c2[W], c3[W];  // candidates, valid_, list length bit planes (by order position)
+#pragma unroll
+  for (int w = 0; w < W; ++w) { cand[w] = 0ull; vmask[w] = 0ull; c0[w] = 0ull; c1[w] = 0ull; c2[w] = 0ull; c3[w] = 0ull; }
+  if (active) {
+    t = A.st_t[e]; hp = A.st_hp[e]; ilo = A.st_ilo[e]; ihi = A.st_ihi[e]; L = A.st_L[e];
+    edge = A.st_edge[e]; iters = A.st_iters[e];
+    const uint32_t ps = A.st_pos[e];
+    pos = (int)(ps & 0xffffu); smallest = (int)(ps >> 16);
+    nEm = A.st_nEm[e];
+    subCnt = A.st_subCnt[e];
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      vmask[w] = A.st_vmask[(size_t)w * E + e];
+      c0[w] = A.st_cbits[(size_t)(0 * W + w) * E + e];
+      c1[w] = A.st_cbits[(size_t)(1 * W + w) * E + e];
+      c2[w] = A.st_cbits[(size_t)(2 * W + w) * E + e];
+      c3[w] = A.st_cbits[(size_t)(3 * W + w) * E + e];
     }
   }
+  unsigned samples = 0, caps = 0, overflows = 0, discarded = 0;
+  bool needSample = false, needFK = false;
+  double2* sub = A.sub + e;  // valid subset, element j at sub[j * E]
+
+  auto getCnt = [&](int p) -> int {
+    return (maskGet<W>(c0, p) ? 1 : 0) + (maskGet<W>(c1, p) ? 2 : 0) + (maskGet<W>(c2, p) ? 4 : 0) + (maskGet<W>(c3, p) ? 8 : 0);
+  };
+  auto setCnt = [&](int p, int v) {
+    maskPut<W>(c0, p, (v & 1) != 0); maskPut<W>(c1, p, (v & 2) != 0); maskPut<W>(c2, p, (v & 4) != 0); maskPut<W>(c3, p, (v & 8) != 0);
+  };
+  auto listOf = [&](int p) -> double2* { return A.ivl + (size_t)p * WD_K * E + e; };  // element j at [j * E]
+  // dichotomy.cc:113-121: the valid part ends where the first (last, if reverse) validated interval ends
+  auto dichLast = [&]() -> double { return reverse ? sub[(size_t)(subCnt - 1) * E].x : sub[0].y; };
+  auto finishEdge = [&](bool ok, int rs, double tf, double tl, int pr) {
+    A.valid[edge] = ok ? 1 : 0;
+    if (A.t_fail) A.t_fail[edge] = tf;
+    if (A.t_last) A.t_last[edge] = tl;
+    if (A.pair) A.pair[edge] = pr;
+    if (A.reason) A.reason[edge] = (uint8_t)rs;
+    active = false;
+  };
+
+  // One scan over the pair positions from `start`.  emitOnly = false: REPLAY of validateIntervals with last
+  // round's results, switching to EMIT at the first pair the reference evaluates whose result is missing.
+  // emitOnly = true: candidates of a sample that has no results yet.  Returns true when the sample completed.
+  auto scan = [&](int start, bool emitOnly) -> bool {  // @region scan
+    int cursor = 0;
+    int nextP = (!emitOnly && nEm > 0) ? (int)A.emPos[e] : -1;
+    bool emit = emitOnly, force = emitOnly, stop = false;
+    double ql = t - hp, qh = t + hp;
+    for (int b0 = start; b0 < NP && !stop; b0 += WD_CH) {
+      double2 first[WD_CH];
+      const unsigned vch = chunkBitsN<W, WD_CH>(vmask, b0);
+      const unsigned k0 = chunkBitsN<W, WD_CH>(c0, b0), k1 = chunkBitsN<W, WD_CH>(c1, b0);
+      const unsigned k2 = chunkBitsN<W, WD_CH>(c2, b0), k3 = chunkBitsN<W, WD_CH>(c3, b0);
+      const unsigned anyc = (k0 | k1 | k2 | k3) & ~vch;  // non-valid positions with a non-empty list
+#pragma unroll
+      for (int k = 0; k < WD_CH; ++k) {
+        first[k] = make_double2(INF, -INF);
+        if (b0 + k < NP && ((anyc >> k) & 1u)) first[k] = listOf(b0 + k)[0];
+      }
+#pragma unroll
+      for (int k = 0; k < WD_CH; ++k) {
+        const int p = b0 + k;
+        if (p >= NP || stop) break;
+        if ((vch >> k) & 1u) {  // valid_ on the whole path: interval = timeRange (body-pair-collision.cc:51-55)
+          if (!emit) {
+            if (ihi > L) smallest = p;
+            ilo = (ilo < 0.0) ? 0.0 : ilo;
+            ihi = (L < ihi) ? L : ihi;
+          }
+          continue;
+        }
+        int cnt = (int)(((k0 >> k) & 1u) + 2u * ((k1 >> k) & 1u) + 4u * ((k2 >> k) & 1u) + 8u * ((k3 >> k) & 1u));
+        double2* lst = listOf(p);
+        const double x0 = emit ? ql : ilo, x1 = emit ? qh : ihi;
+        bool cont = first[k].x <= x0 && x1 <= first[k].y;  // icl::contains(validInterval_, [x0, x1]) (:56-63)
+        for (int j = 1; j < cnt && !cont; ++j) {
+          const double2 v = lst[(size_t)j * E];
+          cont = v.x <= x0 && x1 <= v.y;
+        }
+        if (emit) {
+          maskSet<W>(cand, p, force || !cont);
+          force = false;
+          continue;
+        }
+        const bool have = nextP == p;
+        const int kk = cursor;
+        if (have) {
+          ++cursor;
+          nextP = cursor < nEm ? (int)A.emPos[(size_t)cursor * E + e] : -1;
+        }
+        if (cont) {
+          if (have) ++discarded;
+        } else if (have) {
+          const double2 rr = A.fold[(size_t)kk * E + e];
+          const double a = rr.x, bb = rr.y;
+          if (bb == -INF) {  // collision: a carries the geometry pair
+            finishEdge(false, HPPB200_REASON_COLLISION, t, dichLast(), (int)a);
+            stop = true;
+            continue;
+          }
+          if (!wdUnion(lst, E, cnt, WD_K, a, bb)) {  // validInterval_.insert (:90) needs a longer list: walker
+            ++overflows;
+            finishEdge(false, A.overflow_reason, t, dichLast(), -1);
+            stop = true;
+            continue;
+          }
+          setCnt(p, cnt);
+          if (wdContains(lst, E, cnt, 0.0, L)) maskSet<W>(vmask, p, true);  // valid_ (:92-96)
+          if (ihi > bb) smallest = p;  // validateIntervals: fold into the running intersection
+          ilo = (ilo < a) ? a : ilo;
+          ihi = (bb < ihi) ? bb : ihi;
+        } else {
+          // the reference evaluates this pair now and its distance is not there yet
+          emit = true;
+          pos = p;
+          ql = fmax(ilo, t - hp);
+          qh = fmin(ihi, t + hp);
+#pragma unroll
+          for (int w = 0; w < W; ++w) cand[w] = 0ull;
+          maskSet<W>(cand, p, true);
+        }
+      }
+    }
+    return !emit && !stop;
+  };
+
+  if (active) {
+    const bool complete = scan(pos, false);
+    if (active && complete) {
+      // src/continuous-validation.cc:144-146: smallest interval first
+      if (NP > 1 && smallest != 0) {
+        const int n0 = getCnt(0), ns = getCnt(smallest);
+        double2* l0 = listOf(0);
+        double2* ls = listOf(smallest);
+        const int nm = n0 > ns ? n0 : ns;
+        for (int j = 0; j < nm; ++j) {
+          const double2 x0 = l0[(size_t)j * E], xs = ls[(size_t)j * E];
+          l0[(size_t)j * E] = xs; ls[(size_t)j * E] = x0;
+        }
+        setCnt(0, ns); setCnt(smallest, n0);
+        uint16_t* od = A.ord + (size_t)e * A.ordStride;
+        const uint16_t o0 = od[0], os = od[smallest];
+        od[0] = os; od[smallest] = o0;
+        const bool v0 = maskGet<W>(vmask, 0), vs = maskGet<W>(vmask, smallest);
+        maskPut<W>(vmask, 0, vs); maskPut<W>(vmask, smallest, v0);
+      }
+      // dichotomy.cc:96-109
+      hp = A.alpha * (0.5 * (ihi - ilo));
+      if (!wdUnion(sub, E, subCnt, WD_KS, ilo, ihi)) {
+        ++overflows;
+        finishEdge(false, A.overflow_reason, t, dichLast(), -1);
+      } else if (wdContains(sub, E, subCnt, 0.0, L)) {
+        finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+      } else {
+        double t0, t1;  // middle of the first non-validated gap
+        if (!reverse) { t0 = sub[0].y; t1 = subCnt > 1 ? sub[E].x : L; }
+        else { t0 = sub[(size_t)(subCnt - 1) * E].x; t1 = subCnt > 1 ? sub[(size_t)(subCnt - 2) * E].y : 0.0; }
+        t = .5 * (t0 + t1);
+        needSample = true;
+      }
+    }
+  }
+
+  // ---- REFILL ---------------------------------------------------------------------------------------  @region refill
+  {
+    const bool want = !active && !retired;
+    const unsigned m = __ballot_sync(FULL, want);
+    if (m) {
+      const int leader = __ffs(m) - 1;
+      unsigned long long b = 0;
+      if (lane == leader) b = atomicAdd(A.counter, (unsigned long long)__popc(m));
+      b = __shfl_sync(FULL, b, leader);
+      bool got = false;
+      if (want) {
+        const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
+        if (idx >= A.n) retired = true;
+        else {
+          edge = (uint32_t)idx;
+          L = A.L[edge];
+          iters = 0;
+          t = reverse ? L : 0.0;
+          hp = INF;
+          sub[0] = make_double2(t, t);  // validSubset.unionInterval((t, t)) (dichotomy.cc:84)
+          subCnt = 1;
+#pragma unroll
+          for (int w = 0; w < W; ++w) { vmask[w] = 0ull; c0[w] = 0ull; c1[w] = 0ull; c2[w] = 0ull; c3[w] = 0ull; }
+          active = true;
+          needSample = true;
+          got = true;
+        }
+      }
+      wfNewEdgeTables(mv, A, T, e, lane, got, edge, L);
+    }
+  }
+
+  // ---- next sample: iteration cap, then the candidates of a sample without results -----------------  @region sample
+  if (needSample) {
+    if (iters >= A.max_iter) {
+      ++caps;
+      finishEdge(false, HPPB200_REASON_ITER_CAP, t, dichLast(), -1);
+    } else {
+      ++iters;
+      ++samples;
+      pos = 0; smallest = 0; ilo = -INF; ihi = INF; nEm = 0;
+      needFK = true;  // wfFkKernel computes the placements at t
+#pragma unroll
+      for (int w = 0; w < W; ++w) cand[w] = 0ull;
+      scan(0, true);
+    }
+  }
+
+  // ---- EMIT ------------------------------------------------------------------------------------------  @region emit
+  wfEmitJobs<W>(A, T, e, lane, active, cand, nEm, sCnt, ctl);
+
+  // ---- store the slot state ---------------------------------------------------------------------------  @region store
+  A.st_flags[e] = (uint8_t)((active ? 1 : 0) | (retired ? 2 : 0) | ((active && needFK) ? 16 : 0));
+  if (active) {
+    A.st_t[e] = t; A.st_hp[e] = hp; A.st_ilo[e] = ilo; A.st_ihi[e] = ihi; A.st_L[e] = L;
+    A.st_edge[e] = edge; A.st_iters[e] = iters;
+    A.st_pos[e] = (uint32_t)pos | ((uint32_t)smallest << 16);
+    A.st_nEm[e] = (uint8_t)nEm;
+    A.st_subCnt[e] = (uint8_t)subCnt;
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      A.st_vmask[(size_t)w * E + e] = vmask[w];
+      A.st_cbits[(size_t)(0 * W + w) * E + e] = c0[w];
+      A.st_cbits[(size_t)(1 * W + w) * E + e] = c1[w];
+      A.st_cbits[(size_t)(2 * W + w) * E + e] = c2[w];
+      A.st_cbits[(size_t)(3 * W + w) * E + e] = c3[w];
+    }
+  }
+  wfPublish(A, stats, sCnt, lane, retired, samples, discarded, caps, overflows);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -768,6 +1131,19 @@ __global__ void wfInitKernel(WFArgs A) {
   }
 }
 
+// The last few edges of a batch can need hundreds of samples more than the rest; a round of four launches
+// for a handful of slots is latency, not throughput.  The host stops the rounds when few slots are left and
+// this kernel hands their edges to the walker through the overflow protocol (they restart from t = 0).
+__global__ void wfAbandonKernel(WFArgs A, DeviceStats* stats) {
+  const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= A.E || !(A.st_flags[e] & 1)) return;
+  const uint32_t edge = A.st_edge[e];
+  A.valid[edge] = 0;
+  if (A.reason) A.reason[edge] = (uint8_t)A.overflow_reason;
+  A.st_flags[e] = 2;
+  atomicAdd(&stats->overflow, 1ull);
+}
+
 namespace {
 struct Carver {
   size_t off = 0;
@@ -782,7 +1158,7 @@ struct Carver {
 }  // namespace
 
 // Returns false when the model does not fit this engine (the caller then uses another path).
-bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
+bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const double* d_q1, const double* d_q2,
                                 const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                                 int32_t* d_pair, uint8_t* d_reason, int overflow_reason) {
   const ModelView& mv = ws->view;
@@ -805,20 +1181,27 @@ bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const do
   A.refill_min = WF_REFILL_MIN;
   if (const char* v = std::getenv("HPPB200_WF_REFILL")) A.refill_min = std::atoi(v);
   A.fkSlots = mv.ngeoms + (tree ? mv.njoints : 0);
-  size_t E = ws->wavefront_slots ? ws->wavefront_slots : (size_t)ws->num_sms * 2048;
+  size_t E = ws->wavefront_slots ? ws->wavefront_slots : (size_t)ws->num_sms * (method == HPPB200_METHOD_DICHOTOMY ? 1024 : 2048);
   if (E > n) E = n;
   E = (E + WF_CTHREADS - 1) / WF_CTHREADS * WF_CTHREADS;
   A.E = (uint32_t)E;
   const int BATCH = 16;  // rounds between two host checks of the alive counter
+  // tail: at most one wave of the walker's second pass, and never more than 1/64 of the batch
+  // (Progressive: measured slower with the hand-off, its tail rounds are cheap next to the walker's restart)
+  const unsigned tailSlots = ws->wavefront_tail >= 0 ? (unsigned)ws->wavefront_tail
+                             : (method == HPPB200_METHOD_DICHOTOMY ? (unsigned)std::min<size_t>(2048, n / 64) : 0u);
 
   Carver c;
   const size_t o_counter = c.take<unsigned long long>(1), o_ctl = c.take<WFRoundCtl>(2), o_alive = c.take<unsigned>(BATCH);
-  const size_t o_lohi = c.take<double2>((size_t)NP * E), o_ord = c.take<uint16_t>((size_t)((NP + 15) / 16 * 16) * E);
+  const bool dich = method == HPPB200_METHOD_DICHOTOMY;
+  const size_t o_lohi = c.take<double2>(dich ? 0 : (size_t)NP * E), o_ord = c.take<uint16_t>((size_t)((NP + 15) / 16 * 16) * E);
   const size_t o_vmax = c.take<double>((size_t)NP * E), o_sv = c.take<double>((size_t)mv.nv * E);
   const size_t o_t = c.take<double>(E), o_last = c.take<double>(E), o_hp = c.take<double>(E), o_ilo = c.take<double>(E);
   const size_t o_ihi = c.take<double>(E), o_L = c.take<double>(E);
   const size_t o_edge = c.take<uint32_t>(E), o_iters = c.take<uint32_t>(E), o_pos = c.take<uint32_t>(E);
   const size_t o_flags = c.take<uint8_t>(E), o_nEm = c.take<uint8_t>(E), o_vmask = c.take<unsigned long long>((size_t)W * E);
+  const size_t o_cbits = c.take<unsigned long long>(dich ? (size_t)4 * W * E : 0), o_ivl = c.take<double2>(dich ? (size_t)NP * WD_K * E : 0);
+  const size_t o_sub = c.take<double2>(dich ? (size_t)WD_KS * E : 0), o_subCnt = c.take<uint8_t>(dich ? E : 0);
   const size_t o_emPos = c.take<uint16_t>((size_t)WF_RB * E), o_emRes = c.take<uint8_t>((size_t)WF_RB * E);
   const size_t o_fold = c.take<double2>((size_t)WF_RB * E);
   const size_t o_res = c.take<double>((size_t)WF_RG * E), o_plc = c.take<double>(E * (size_t)A.fkSlots * 12);
@@ -828,22 +1211,25 @@ bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const do
   A.counter = (unsigned long long*)(base + o_counter);
   A.ctl = (WFRoundCtl*)(base + o_ctl);
   A.alive = (unsigned*)(base + o_alive);
-  A.lohi = (double2*)(base + o_lohi); A.ord = (uint16_t*)(base + o_ord); A.ordStride = (uint32_t)((NP + 15) / 16 * 16);
+  A.lohi = dich ? nullptr : (double2*)(base + o_lohi); A.ord = (uint16_t*)(base + o_ord); A.ordStride = (uint32_t)((NP + 15) / 16 * 16);
   A.vmax = (double*)(base + o_vmax); A.sv = (double*)(base + o_sv);
   A.st_t = (double*)(base + o_t); A.st_last = (double*)(base + o_last); A.st_hp = (double*)(base + o_hp);
   A.st_ilo = (double*)(base + o_ilo); A.st_ihi = (double*)(base + o_ihi); A.st_L = (double*)(base + o_L);
   A.st_edge = (uint32_t*)(base + o_edge); A.st_iters = (uint32_t*)(base + o_iters); A.st_pos = (uint32_t*)(base + o_pos);
   A.st_flags = base + o_flags; A.st_nEm = base + o_nEm; A.st_vmask = (unsigned long long*)(base + o_vmask);
+  A.st_cbits = (unsigned long long*)(base + o_cbits); A.ivl = (double2*)(base + o_ivl); A.sub = (double2*)(base + o_sub);
+  A.st_subCnt = base + o_subCnt;
   A.emPos = (uint16_t*)(base + o_emPos); A.emRes = base + o_emRes; A.fold = (double2*)(base + o_fold);
   A.res = (double*)(base + o_res); A.plc = (double*)(base + o_plc);
   A.jobsG = (unsigned long long*)(base + o_jG); A.jobsC = (unsigned long long*)(base + o_jC);
 
-  auto kc = W == 1 ? wfControlKernel<1> : wfControlKernel<4>;
+  const size_t smemCtl = dich ? 48 + mv.edge_blob_bytes : smemC;
+  auto kc = dich ? (W == 1 ? wfDichControlKernel<1> : wfDichControlKernel<4>) : (W == 1 ? wfControlKernel<1> : wfControlKernel<4>);
   auto kf = tree ? wfFkKernel<true> : wfFkKernel<false>;
   const size_t smemF = 16 + (WF_CTHREADS / 32) * WF_FK_TILE + mv.edge_blob_bytes;
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
   const unsigned gridF = (unsigned)((E * (size_t)WF_RB + 255) / 256);
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemC));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemCtl));
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(wfNarrowKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemN));
   int perSM = 0;
   HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, wfNarrowKernel, WF_NTHREADS, smemN));
@@ -872,7 +1258,7 @@ bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const do
       mark();
       if (round > 0) wfFoldKernel<<<gridF, 256, 0, ws->stream>>>(mv, A);
       mark();
-      kc<<<gridC, WF_CTHREADS, smemC, ws->stream>>>(mv, A, ws->d_stats);
+      kc<<<gridC, WF_CTHREADS, smemCtl, ws->stream>>>(mv, A, ws->d_stats);
       mark();
       kf<<<gridC, WF_CTHREADS, smemF, ws->stream>>>(mv, A);
       mark();
@@ -883,6 +1269,12 @@ bool launchWavefrontProgressive(Workspace* ws, double tol, int reverse, const do
     ws->stats.kernel_launches += 4 * BATCH;
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h_alive, A.alive + (BATCH - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream));
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    if (h_alive && h_alive <= tailSlots) {  // (slots hold edges only: the edge counter is exhausted long before)
+      wfAbandonKernel<<<(unsigned)((E + 255) / 256), 256, 0, ws->stream>>>(A, ws->d_stats);
+      HPPB200_CUDA_CHECK(cudaGetLastError());
+      ws->stats.kernel_launches += 1;
+      break;
+    }
   }
   if (trace) {
     double tt[4] = {0, 0, 0, 0};

@@ -352,3 +352,47 @@ def test_humanoid_tree_convex_parity(pkg, ob, monkeypatch, name):
                 assert np.array_equal(r[k], e[k]), (name, method, rev, k)
             assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
             assert 0.02 < r["valid"].mean() < 0.98
+
+
+@pytest.mark.parametrize("reverse", [False, True])
+@pytest.mark.parametrize("slots,tail", [(0, -1), (1024, 0), (1024, 64)])
+def test_wavefront_dichotomy_parity(pkg, eng, ur5, ur5_oracle, golden_configs, monkeypatch, reverse, slots, tail):
+    """Dichotomy through the wavefront engine (interval LISTS per body pair, valid subset per edge), forced for a
+    small batch: slot refill, tail hand-off to the walker (tail = 64 slots) and list overflow -> walker are all on
+    the path.  Bit-exact against the oracle."""
+    m, _ = eng
+    monkeypatch.setenv("HPPB200_WF_MIN", "1")
+    monkeypatch.setenv("HPPB200_WF_SLOTS", str(slots))
+    monkeypatch.setenv("HPPB200_WF_TAIL", str(tail))
+    ws = pkg.Workspace(m, 0)
+    o = ur5_oracle
+    g1, g2 = golden_configs[0:200:2], golden_configs[1:200:2]
+    a1, a2, _ = _edges(pkg, ur5, o, 3000, 37)
+    b1, b2, _ = _edges(pkg, ur5, o, 2000, 38, short=True)
+    z = pkg.uniform_configs(ur5, 300, seed=39)
+    q1, q2 = np.concatenate([g1, a1, b1, z]), np.concatenate([g2, a2, b2, z])
+    L = o.straight_lengths(q1, q2)
+    s0 = ws.stats()
+    r = ws.validate_edges(2, 0.0, q1, q2, L, reverse=reverse)
+    s1 = ws.stats()
+    e = o.validate_edges(2, 0.0, q1, q2, L, reverse=reverse)
+    assert 0 < s1["engine_ticks"] - s0["engine_ticks"] < 20000  # wavefront rounds were run
+    assert s1["iter_cap_hits"] == 0
+    for k in ("valid", "reason", "pair", "t_last_valid"):
+        assert np.array_equal(r[k], e[k]), k
+    assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+
+
+@pytest.mark.parametrize("name", ["ur5_boxes1.json", "ur5_boxes32.json"])
+def test_wavefront_dichotomy_other_scenes(pkg, ob, monkeypatch, name):
+    monkeypatch.setenv("HPPB200_WF_MIN", "1")
+    desc = pkg.ModelDescription.load(name)
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    o = ob.Oracle(desc)
+    q1, q2, L = _edges(pkg, desc, o, 2500, 40)
+    for rev in (False, True):
+        r = ws.validate_edges(2, 0.0, q1, q2, L, reverse=rev)
+        e = o.validate_edges(2, 0.0, q1, q2, L, reverse=rev)
+        for k in ("valid", "reason", "pair", "t_last_valid"):
+            assert np.array_equal(r[k], e[k]), (name, rev, k)
+        assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)

@@ -11,6 +11,8 @@ pkg = ge.load()
 from oracle import binding as ob
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1 << 17
 npar = int(sys.argv[2]) if len(sys.argv) > 2 else 20000
+meth = int(sys.argv[3]) if len(sys.argv) > 3 else 1   # 1 Progressive(1e-3), 2 Dichotomy(0)
+par = 1e-3 if meth == 1 else 0.0
 desc = pkg.ModelDescription.load("ur5_boxes8.json")
 model = pkg.Model(desc)
 ws = pkg.Workspace(model, 0)
@@ -21,8 +23,8 @@ L = ws.straight_lengths(q1, q2)
 if npar:
     o = ob.Oracle(desc)
     for rev in (False, True):
-        r = ws.validate_edges(1, 1e-3, q1[:npar], q2[:npar], L[:npar], reverse=rev)
-        e = o.validate_edges(1, 1e-3, q1[:npar], q2[:npar], L[:npar], reverse=rev)
+        r = ws.validate_edges(meth, par, q1[:npar], q2[:npar], L[:npar], reverse=rev)
+        e = o.validate_edges(meth, par, q1[:npar], q2[:npar], L[:npar], reverse=rev)
         ok = all(np.array_equal(r[k], e[k], equal_nan=True) for k in ("valid", "reason", "t_fail", "t_last_valid", "pair"))
         print("parity reverse=%d: %s (valid %.3f)" % (rev, ok, r["valid"].mean()), flush=True)
         if not ok:
@@ -35,7 +37,7 @@ pr = torch.empty(n, dtype=torch.int32, device=dev); rs = torch.empty(n, dtype=to
 for it in range(3):
     s0 = ws.stats()
     t0 = time.perf_counter()
-    ws.validate_edges_ptr(1, 1e-3, False, a.data_ptr(), b.data_ptr(), l.data_ptr(), n, v.data_ptr(), tf.data_ptr(), tl.data_ptr(), pr.data_ptr(), rs.data_ptr(), pkg.DEVICE_POINTERS)
+    ws.validate_edges_ptr(meth, par, False, a.data_ptr(), b.data_ptr(), l.data_ptr(), n, v.data_ptr(), tf.data_ptr(), tl.data_ptr(), pr.data_ptr(), rs.data_ptr(), pkg.DEVICE_POINTERS)
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
     st = ws.stats()
