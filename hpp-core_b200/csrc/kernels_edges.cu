@@ -24,6 +24,9 @@
 // Per-lane interval sets and pair order live in shared memory when they fit (Progressive:
 // one interval per body pair), else in global scratch laid out SoA over lanes; geometry
 // placements always live in that scratch (coalesced, L2-resident).
+#include <cstdio>
+#include <cstdlib>
+
 #include "dev_model.cuh"
 
 namespace hppb200 {
@@ -682,6 +685,7 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&after, ws->d_stats, sizeof(after), cudaMemcpyDeviceToHost, ws->stream));
   HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
   const unsigned long long nover = after.overflow - before.overflow;
+  if (std::getenv("HPPB200_WF_TRACE")) std::fprintf(stderr, "[edges] %llu of %zu edges go to the large-list walker pass\n", nover, n);
   if (nover == 0) return;
   // second pass: gather the overflowed edges and walk them with large interval lists
   ws->d_list.reserve(nover + 1);

@@ -1187,9 +1187,12 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   A.E = (uint32_t)E;
   const int BATCH = 16;  // rounds between two host checks of the alive counter
   // tail: at most one wave of the walker's second pass, and never more than 1/64 of the batch
-  // (Progressive: measured slower with the hand-off, its tail rounds are cheap next to the walker's restart)
   const unsigned tailSlots = ws->wavefront_tail >= 0 ? (unsigned)ws->wavefront_tail
                              : (method == HPPB200_METHOD_DICHOTOMY ? (unsigned)std::min<size_t>(2048, n / 64) : 0u);
+  // Progressive: measured slower with the hand-off (262 -> 407 ms per 1M edges).  Dichotomy: a few edges in a
+  // million need thousands of samples and lists beyond any fixed capacity; they end in the walker's
+  // large-list pass either way (its latency, ~0.4 s for the longest edge, is the floor of a 1M batch), so the
+  // thin rounds before it are cut short (886 ms with the hand-off, 1008 ms without).
 
   Carver c;
   const size_t o_counter = c.take<unsigned long long>(1), o_ctl = c.take<WFRoundCtl>(2), o_alive = c.take<unsigned>(BATCH);
