@@ -41,8 +41,10 @@
 
 namespace hppb200 {
 
-constexpr int WF_RB = 12;       // body pairs emitted per slot per round
-constexpr int WF_RG = 16;       // geometry-pair jobs (= result slots) per slot per round
+constexpr int WF_RB = 12;       // body pairs emitted per slot per round (UR5-class models; WFArgs::rb is the run's value)
+constexpr int WF_RG = 16;       // geometry-pair jobs (= result slots) per slot per round (WFArgs::rg)
+constexpr int WF_RB_BIG = 32;   // models with more than 64 body pairs: the first samples of an edge evaluate most pairs
+constexpr int WF_RG_BIG = 48;
 constexpr int WF_CTHREADS = 128;
 constexpr int WF_NTHREADS = 128;
 constexpr int WF_CHUNK = 128;   // jobs a warp takes from the list per atomic
@@ -101,6 +103,7 @@ struct WFArgs {
   unsigned* alive;     // [rounds per batch]
   int round;           // global round number
   int aliveIdx;
+  int rb, rg;          // per-round caps: body pairs / geometry-pair jobs per slot
   int refill_min;      // idle lanes in a warp before new GJK jobs are fetched (32 = whole-warp batches)
 };
 
@@ -213,7 +216,7 @@ __device__ __forceinline__ void wfEmitJobs(const WFArgs& A, const Tables& T, uin
                                            int& nEm, unsigned* sCnt, WFRoundCtl* ctl) {
   const unsigned FULL = 0xffffffffu;
   const uint32_t E = A.E;
-  uint32_t jl[WF_RG];  // geometry pair | GJK flag << 31, in result order
+  uint32_t jl[WF_RG_BIG];  // geometry pair | GJK flag << 31, in result order
   int nr = 0, nGl = 0, nCl = 0;
   if (active) {
     int nb = 0;
@@ -227,7 +230,7 @@ __device__ __forceinline__ void wfEmitJobs(const WFArgs& A, const Tables& T, uin
         const int id = A.ord[(size_t)e * A.ordStride + p];
         const DevBodyPair& B = T.bodypairs[id];
         const int ng = B.pair_end - B.pair_begin;
-        if (nb >= WF_RB || nr + ng > WF_RG) { full = true; break; }
+        if (nb >= A.rb || nr + ng > A.rg) { full = true; break; }
         A.emPos[(size_t)nb * E + e] = (uint16_t)p;
         A.emRes[(size_t)nb * E + e] = (uint8_t)nr;
         for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
@@ -737,7 +740,7 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
         double2* lst = listOf(p);
         const double x0 = emit ? ql : ilo, x1 = emit ? qh : ihi;
         bool cont = first[k].x <= x0 && x1 <= first[k].y;  // icl::contains(validInterval_, [x0, x1]) (:56-63)
-        for (int j = 1; j < cnt && !cont; ++j) {
+        for (int j = 1; j < cnt && !cont; ++j) {  // (loading entries 1..4 together was measured slower: 654 -> 777 us)
           const double2 v = lst[(size_t)j * E];
           cont = v.x <= x0 && x1 <= v.y;
         }
@@ -905,7 +908,7 @@ wfFoldKernel(ModelView mv, WFArgs A) {
   const Tables T = makeTables(mv.blob, mv);  // global copy (read-only, L1 resident)
   const uint32_t E = A.E;
   const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (idx >= (size_t)E * WF_RB) return;
+  if (idx >= (size_t)E * A.rb) return;
   const uint32_t e = (uint32_t)(idx % E);
   const int k = (int)(idx / E);
   if (!(A.st_flags[e] & 1) || k >= (int)A.st_nEm[e]) return;
@@ -1166,7 +1169,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   const int NP = mv.nbodypairs;
   if (NP < 1 || NP > 65535 || mv.nbgpairs >= (1 << 24)) return false;
   for (const BodyPairHost& b : m->bodyPairs)
-    if ((int)b.pairs.size() > WF_RG) return false;
+    if ((int)b.pairs.size() > WF_RG) return false;  // (a body pair must fit one round's job cap)
   if (NP > 256) return false;
   const int W = NP <= 64 ? 1 : 4;
   const size_t smemC = 48 + WF_RING_BYTES + mv.edge_blob_bytes, smemN = 16 + mv.edge_blob_bytes;
@@ -1205,10 +1208,13 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   const size_t o_flags = c.take<uint8_t>(E), o_nEm = c.take<uint8_t>(E), o_vmask = c.take<unsigned long long>((size_t)W * E);
   const size_t o_cbits = c.take<unsigned long long>(dich ? (size_t)4 * W * E : 0), o_ivl = c.take<double2>(dich ? (size_t)NP * WD_K * E : 0);
   const size_t o_sub = c.take<double2>(dich ? (size_t)WD_KS * E : 0), o_subCnt = c.take<uint8_t>(dich ? E : 0);
-  const size_t o_emPos = c.take<uint16_t>((size_t)WF_RB * E), o_emRes = c.take<uint8_t>((size_t)WF_RB * E);
-  const size_t o_fold = c.take<double2>((size_t)WF_RB * E);
-  const size_t o_res = c.take<double>((size_t)WF_RG * E), o_plc = c.take<double>(E * (size_t)A.fkSlots * 12);
-  const size_t o_jG = c.take<unsigned long long>(E * (size_t)WF_RG), o_jC = c.take<unsigned long long>(E * (size_t)WF_RG);
+  A.rb = NP > 64 ? WF_RB_BIG : WF_RB;
+  A.rg = NP > 64 ? WF_RG_BIG : WF_RG;
+  const size_t RB = (size_t)A.rb, RG = (size_t)A.rg;
+  const size_t o_emPos = c.take<uint16_t>(RB * E), o_emRes = c.take<uint8_t>(RB * E);
+  const size_t o_fold = c.take<double2>(RB * E);
+  const size_t o_res = c.take<double>(RG * E), o_plc = c.take<double>(E * (size_t)A.fkSlots * 12);
+  const size_t o_jG = c.take<unsigned long long>(E * RG), o_jC = c.take<unsigned long long>(E * RG);
   ws->d_state.reserve(c.off + 256);
   unsigned char* base = ws->d_state.p;
   A.counter = (unsigned long long*)(base + o_counter);
@@ -1231,7 +1237,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   auto kf = tree ? wfFkKernel<true> : wfFkKernel<false>;
   const size_t smemF = 16 + (WF_CTHREADS / 32) * WF_FK_TILE + mv.edge_blob_bytes;
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
-  const unsigned gridF = (unsigned)((E * (size_t)WF_RB + 255) / 256);
+  const unsigned gridF = (unsigned)((E * RB + 255) / 256);
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemCtl));
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(wfNarrowKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemN));
   int perSM = 0;
