@@ -43,6 +43,29 @@ __device__ __forceinline__ double weighedDistanceDev(const Tables& T, const Mode
   return sqrt(res);
 }
 
+// WeighedDistance of one node to KNN_QB queries at once: the node entry, the joint record and w^2 are loaded once
+// per joint; per query the operation sequence is the one of weighedDistanceDev (same bits).  `sq` holds the
+// queries in shared memory, `sw2` the per-joint w * w.
+template <int QB>
+__device__ __forceinline__ void weighedDistanceBatch(const Tables& T, const ModelView& mv, const double* __restrict__ node,
+                                                     const double* sq, const double* sw2, double (&d)[QB]) {
+#pragma unroll
+  for (int q = 0; q < QB; ++q) d[q] = 0;
+  for (int j = 0; j < mv.njoints; ++j) {
+    const DevJoint& J = T.joints[j];
+    const double a = node[J.idx_q];
+    const double w2 = sw2[j];
+    const bool rev = J.type <= HPPB200_JOINT_REVOLUTE_Z;
+#pragma unroll
+    for (int q = 0; q < QB; ++q) {
+      const double dq = sq[q * mv.nq + J.idx_q] - a;
+      d[q] += rev ? w2 * (dq * dq) : dq * dq;
+    }
+  }
+#pragma unroll
+  for (int q = 0; q < QB; ++q) d[q] = sqrt(d[q]);
+}
+
 struct Key {
   double d;
   long long i;
@@ -57,7 +80,10 @@ __device__ __forceinline__ bool keyLess(const Key& a, const Key& b) { return a.d
 // merges the tiles, appends result r and publishes the new previous key.  Keys are (distance, node index),
 // i.e. the reference's strict '<' scan (basic.cc:66,106).  A single query over 1 M nodes is HBM-bound
 // (48 B per node at nq = 6); one CTA per query would leave all but one SM idle there.
-constexpr int KNN_QB = 4;
+#ifndef HPPB200_KNN_QB
+#define HPPB200_KNN_QB 4
+#endif
+constexpr int KNN_QB = HPPB200_KNN_QB;
 
 __global__ void __launch_bounds__(KNN_THREADS)
 knnTileKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
@@ -68,25 +94,33 @@ knnTileKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __r
   unsigned char* sblob = smem + 16;
   stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
   const Tables T = makeTables(sblob, mv);
+  double* sq = (double*)(sblob + mv.blob_bytes);  // the CTA's queries and the per-joint w * w
+  double* sw2 = sq + KNN_QB * mv.nq;
+  for (int x = threadIdx.x; x < KNN_QB * mv.nq; x += KNN_THREADS) {
+    const int qq = blockIdx.y * KNN_QB + x / mv.nq;
+    sq[x] = queries[(size_t)(qq < nqueries ? qq : nqueries - 1) * mv.nq + x % mv.nq];  // padding repeats the last query
+  }
+  for (int j = threadIdx.x; j < mv.njoints; j += KNN_THREADS) { const double w = T.weights[j]; sw2[j] = w * w; }
+  __syncthreads();
   __shared__ Key red[KNN_QB][KNN_THREADS / 32];
   const int q0 = blockIdx.y * KNN_QB;
   const size_t lo = (size_t)((unsigned long long)n * blockIdx.x / gridDim.x);
   const size_t hi = (size_t)((unsigned long long)n * (blockIdx.x + 1) / gridDim.x);
   Key best[KNN_QB], pv[KNN_QB];
-  const double* qp[KNN_QB];
 #pragma unroll
   for (int j = 0; j < KNN_QB; ++j) {
     const int q = (q0 + j < nqueries) ? q0 + j : nqueries - 1;  // padding lanes repeat the last query
-    qp[j] = queries + (size_t)q * mv.nq;
     pv[j] = prev[q];
     best[j].d = CUDART_INF; best[j].i = LLONG_MAX;
   }
   for (size_t i = lo + threadIdx.x; i < hi; i += KNN_THREADS) {
     if (ccFilter >= 0 && cc[i] != ccFilter) continue;
     const double* node = nodes + i * (size_t)mv.nq;
+    double dd[KNN_QB];
+    weighedDistanceBatch<KNN_QB>(T, mv, node, sq, sw2, dd);
 #pragma unroll
     for (int j = 0; j < KNN_QB; ++j) {
-      const Key c = {weighedDistanceDev(T, mv, node, qp[j]), (long long)i};
+      const Key c = {dd[j], (long long)i};
       if (keyLess(pv[j], c) && keyLess(c, best[j])) best[j] = c;
     }
   }
@@ -161,6 +195,14 @@ knnTileTopkKernel(ModelView mv, const double* __restrict__ nodes, const int32_t*
   unsigned char* sblob = smem + 16;
   stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
   const Tables T = makeTables(sblob, mv);
+  double* sq = (double*)(sblob + mv.blob_bytes);  // the CTA's queries and the per-joint w * w
+  double* sw2 = sq + KNN_QB * mv.nq;
+  for (int x = threadIdx.x; x < KNN_QB * mv.nq; x += KNN_THREADS) {
+    const int qq = blockIdx.y * KNN_QB + x / mv.nq;
+    sq[x] = queries[(size_t)(qq < nqueries ? qq : nqueries - 1) * mv.nq + x % mv.nq];  // padding repeats the last query
+  }
+  for (int j = threadIdx.x; j < mv.njoints; j += KNN_THREADS) { const double w = T.weights[j]; sw2[j] = w * w; }
+  __syncthreads();
   constexpr int WARPS = KNN_THREADS / 32;
   __shared__ Key lists[WARPS][KNN_QB][32];
   const unsigned FULL = 0xffffffffu;
@@ -169,11 +211,9 @@ knnTileTopkKernel(ModelView mv, const double* __restrict__ nodes, const int32_t*
   const size_t lo = (size_t)((unsigned long long)n * blockIdx.x / gridDim.x);
   const size_t hi = (size_t)((unsigned long long)n * (blockIdx.x + 1) / gridDim.x);
   Key mine[KNN_QB], kth[KNN_QB];
-  const double* qp[KNN_QB];
 #pragma unroll
   for (int j = 0; j < KNN_QB; ++j) {
     const int q = (q0 + j < nqueries) ? q0 + j : nqueries - 1;  // padding repeats the last query
-    qp[j] = queries + (size_t)q * mv.nq;
     mine[j].d = CUDART_INF; mine[j].i = LLONG_MAX;
     kth[j] = mine[j];
   }
@@ -181,9 +221,11 @@ knnTileTopkKernel(ModelView mv, const double* __restrict__ nodes, const int32_t*
     const size_t i = base + lane;
     const bool ok = i < hi && (ccFilter < 0 || cc[i] == ccFilter);
     const double* node = nodes + (ok ? i : lo) * (size_t)mv.nq;
+    double dd[KNN_QB];
+    weighedDistanceBatch<KNN_QB>(T, mv, node, sq, sw2, dd);
 #pragma unroll
     for (int j = 0; j < KNN_QB; ++j) {
-      const Key c = {weighedDistanceDev(T, mv, node, qp[j]), (long long)i};
+      const Key c = {dd[j], (long long)i};
       unsigned m = __ballot_sync(FULL, ok && keyLess(c, kth[j]));
       while (m) {
         const int src = __ffs(m) - 1;
@@ -369,7 +411,7 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
     HPPB200_CUDA_CHECK(cudaSetDevice(nn->device));
     const size_t nq = (size_t)nn->model->nq;
     if (nqueries > 0x7fffffffull / 4) throw std::invalid_argument("too many queries in one call");
-    const size_t smemBytes = 16 + nn->view.blob_bytes;
+    const size_t smemBytes = 16 + nn->view.blob_bytes + ((size_t)KNN_QB * nq + (size_t)nn->model->njoints) * sizeof(double);
     HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
     auto run = [&](const double* d_q, long long* d_i, double* d_d) {
       // k selection passes, each = tiled scan on the whole GPU + merge of the tiles (see knnTileKernel)
