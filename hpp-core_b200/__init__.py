@@ -18,7 +18,8 @@ import subprocess
 
 import numpy as np
 
-from .model_io import ModelDescription, hppb200_model_desc, uniform_configs  # noqa: F401
+from .model_io import (ModelDescription, freeflyer_ranks, hppb200_model_desc, normalize_quaternions,  # noqa: F401
+                       uniform_configs)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libhppb200.so")

@@ -71,6 +71,63 @@ __device__ __forceinline__ void stageBlobTMA(unsigned char* sdst, const unsigned
   }
 }
 
+// Configuration accessors handed to the FK: entry k of a vector-space joint, or the 7 entries of a free-flyer.
+struct ConfigQ {  // a stored configuration
+  const double* q;
+  __device__ __forceinline__ double operator()(int k) const { return q[k]; }
+  __device__ __forceinline__ void freeflyer(int idx_q, double* out) const {
+#pragma unroll
+    for (int k = 0; k < 7; ++k) out[k] = q[idx_q + k];
+  }
+};
+// Path::eval -> StraightPath::impl_compute (src/straight-path.cc:91-110): qmode 0 / 1 return the stored end
+// points bit-exactly, 2 is LiegroupSpace::interpolate(q1, q2, u)
+struct EdgeQ {
+  const double* q1;
+  const double* q2;
+  int qmode;
+  double u;
+  __device__ __forceinline__ double operator()(int k) const {
+    const double a = q1[k];
+    if (qmode == 0) return a;
+    const double b = q2[k];
+    if (qmode == 1) return b;
+    return fma(u, b - a, a);  // R^n
+  }
+  __device__ __forceinline__ void freeflyer(int idx_q, double* out) const {
+    if (qmode == 2) { ffInterpolate(q1 + idx_q, q2 + idx_q, u, out); return; }
+    const double* s = (qmode == 0 ? q1 : q2) + idx_q;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) out[k] = s[k];
+  }
+};
+__device__ __forceinline__ EdgeQ edgeQ(const double* q1, const double* q2, double t, double L) {
+  EdgeQ e;
+  e.q1 = q1; e.q2 = q2; e.u = 0;
+  if (t == 0.0 || L == 0.0) e.qmode = 0;
+  else if (t == L) e.qmode = 1;
+  else { e.qmode = 2; e.u = (t - 0.0) / L; }
+  return e;
+}
+
+// |Vb| over the velocity segment of one joint, Vb = |q2 (-) q1| / L (StraightPath::impl_velocityBound,
+// src/straight-path.cc:132-140; the segment norm of SolidSolidCollision::computeMaximalVelocity :76-99)
+__device__ __forceinline__ double jointVelocityNorm(const double* q1, const double* q2, int idx_q, int nvj, double L) {
+  if (nvj == 1) {
+    const double vb = fabs(q2[idx_q] - q1[idx_q]) / L;
+    return sqrt(fma(vb, vb, 0.0));
+  }
+  double v[6];
+  ffDifference(q1 + idx_q, q2 + idx_q, v);
+  double s = 0;
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    const double vb = fabs(v[k]) / L;
+    s = fma(vb, vb, s);
+  }
+  return sqrt(s);
+}
+
 // pinocchio joint transform composed with the joint placement: liMi = P * M_joint(q)
 template <class Q>
 __device__ __forceinline__ T3 jointLocal(const DevJoint& J, const Q& q) {
@@ -83,13 +140,26 @@ __device__ __forceinline__ T3 jointLocal(const DevJoint& J, const Q& q) {
     if (J.type == HPPB200_JOINT_REVOLUTE_X) { M.r[4] = c; M.r[5] = -s; M.r[7] = s; M.r[8] = c; }
     else if (J.type == HPPB200_JOINT_REVOLUTE_Y) { M.r[8] = c; M.r[6] = -s; M.r[2] = s; M.r[0] = c; }
     else { M.r[0] = c; M.r[1] = -s; M.r[3] = s; M.r[4] = c; }
-  } else {
+  } else if (J.type <= HPPB200_JOINT_PRISMATIC_Z) {
     const int a = J.type - HPPB200_JOINT_PRISMATIC_X;
     double v = q(J.idx_q);
     M.t = mk(a == 0 ? v : 0.0, a == 1 ? v : 0.0, a == 2 ? v : 0.0);
+  } else {  // free-flyer: translation + unit quaternion (x y z w), Eigen toRotationMatrix operation order
+    double f[7];
+    q.freeflyer(J.idx_q, f);
+    M.t = mk(f[0], f[1], f[2]);
+    const double x = f[3], y = f[4], z = f[5], w = f[6];
+    const double tx = 2 * x, ty = 2 * y, tz = 2 * z;
+    const double twx = tx * w, twy = ty * w, twz = tz * w;
+    const double txx = tx * x, txy = ty * x, txz = tz * x;
+    const double tyy = ty * y, tyz = tz * y, tzz = tz * z;
+    M.r[0] = 1 - (tyy + tzz); M.r[1] = txy - twz; M.r[2] = txz + twy;
+    M.r[3] = txy + twz; M.r[4] = 1 - (txx + tzz); M.r[5] = tyz - twx;
+    M.r[6] = txz - twy; M.r[7] = tyz + twx; M.r[8] = 1 - (txx + tyy);
   }
   return compose(P, M);
 }
+
 
 // FK for one configuration (pinocchio::forwardKinematics + updateGeometryPlacements):
 //   liMi = placement * M_joint(q); oMi = oMi[parent] * liMi; oMg = oMi[joint] * placement_g.

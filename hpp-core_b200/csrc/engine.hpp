@@ -59,7 +59,8 @@ struct DevBodyPair {
   int32_t has_gjk;                 // some geometry pair of this body pair goes through GJK
 };
 struct DevCoef {
-  int32_t idx_v, nv;
+  int32_t idx_v;
+  int16_t nv, idx_q;  // velocity segment of the joint and where its configuration entries start
   double value;
 };
 

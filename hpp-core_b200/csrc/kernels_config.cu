@@ -77,7 +77,7 @@ validateConfigsKernel(ModelView mv, ConfigSmemLayout L, const double* __restrict
           if (qc[k] < lo || hi < qc[k]) { boundHit[tid] = k; break; }
         }
       }
-      if (boundHit[tid] < 0) forwardKinematics<TREE>(T, mv, [qc](int k) { return qc[k]; }, store + tid, CFG_PER_BLOCK);
+      if (boundHit[tid] < 0) forwardKinematics<TREE>(T, mv, ConfigQ{qc}, store + tid, CFG_PER_BLOCK);
     }
   }
   __syncthreads();
@@ -246,7 +246,7 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
       T3 cur = identityT();
       for (int j = 1; j <= mv.njoints; ++j) {
         const DevJoint& J = T.joints[j - 1];
-        T3 li = jointLocalSparse(J, qc[J.idx_q]);
+        T3 li = J.type == HPPB200_JOINT_FREEFLYER ? jointLocal(J, ConfigQ{qc}) : jointLocalSparse(J, qc[J.idx_q]);
         if (J.parent == 0) cur = li;
         else if (!TREE || J.parent == j - 1) cur = compose(cur, li);
         else cur = compose(load12s(A.oMg + (size_t)(mv.ngeoms + J.parent - 1) * 12 * A.n + i, A.n), li);

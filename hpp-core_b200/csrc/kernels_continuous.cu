@@ -136,13 +136,6 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
   unsigned tests = 0;
 
   auto validBit = [&](int id) -> bool { return (sValid[(id >> 5) * PE_SLOTS] >> (id & 31)) & 1u; };
-  auto qAt = [&](int k) -> double {
-    const double a = q1[k];
-    if (qmode == 0) return a;
-    const double b = q2[k];
-    if (qmode == 1) return b;
-    return fma(u, b - a, a);  // LiegroupSpace::interpolate on R^n
-  };
   auto finishEdge = [&](bool ok, int rs, double tf, double tl, int pr) {
     A.valid[e] = ok ? 1 : 0;
     if (A.t_fail) A.t_fail[e] = tf;
@@ -275,12 +268,7 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
                 for (int j = 0; j < mv.njoints; ++j) {
                   const DevJoint& J = T.joints[j];
                   const int nvj = J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1;
-                  double s = 0;
-                  for (int k = 0; k < nvj; ++k) {
-                    const double vb = fabs(q2[J.idx_v + k] - q1[J.idx_v + k]) / L;
-                    s = fma(vb, vb, s);
-                  }
-                  sS[J.idx_v * PE_SLOTS] = sqrt(s);
+                  sS[J.idx_v * PE_SLOTS] = jointVelocityNorm(q1, q2, J.idx_q, nvj, L);
                 }
               }
               active = true;
@@ -311,7 +299,7 @@ progressiveEngineKernel(ModelView mv, PEArgs A, PELayout SL, DeviceStats* stats)
         if (t == 0.0 || L == 0.0) qmode = 0;
         else if (t == L) qmode = 1;
         else { qmode = 2; u = (t - 0.0) / L; }
-        forwardKinematics<TREE>(T, mv, qAt, scratchCTA + (size_t)lane * slotStride, 1);
+        forwardKinematics<TREE>(T, mv, EdgeQ{q1, q2, qmode, u}, scratchCTA + (size_t)lane * slotStride, 1);
         sTAll[lane] = t;
         fkDone = true;
       }

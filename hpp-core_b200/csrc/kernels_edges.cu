@@ -172,13 +172,6 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
   GjkCounters cnt = {0u, 0u, 0u};
   unsigned tests = 0, samples = 0, caps = 0, overflows = 0;
 
-  auto qAt = [&](int k) -> double {
-    const double a = q1[k];
-    if (qmode == 0) return a;
-    const double b = q2[k];
-    if (qmode == 1) return b;
-    return fma(u, b - a, a);  // LiegroupSpace::interpolate on R^n
-  };
   auto finishEdge = [&](bool ok, int rs, double tf, double tl, int pr) {
     A.valid[e] = ok ? 1 : 0;
     if (A.t_fail) A.t_fail[e] = tf;
@@ -194,12 +187,7 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
     auto sum = [&](const DevCoef* c, int b, int en) {
       double acc = 0;
       for (int i = b; i < en; ++i) {
-        double s = 0;
-        for (int k = 0; k < c[i].nv; ++k) {
-          const double vb = fabs(q2[c[i].idx_v + k] - q1[c[i].idx_v + k]) / L;
-          s = fma(vb, vb, s);
-        }
-        acc += c[i].value * sqrt(s);
+        acc += c[i].value * jointVelocityNorm(q1, q2, c[i].idx_q, c[i].nv, L);
       }
       return acc;
     };
@@ -281,7 +269,7 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
           for (int k = 0; k < mv.nq && bad < 0; ++k) {
             const double lo = T.lower[k], hi = T.upper[k];
             if (lo > hi) continue;
-            const double v = qAt(k);
+            const double v = EdgeQ{q1, q2, qmode, u}(k);
             if (v < lo || hi < v) bad = k;
           }
         }
@@ -289,7 +277,7 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
         else work = true;
       }
     }
-    if (work) forwardKinematics<TREE>(T, mv, qAt, store, NS);
+    if (work) forwardKinematics<TREE>(T, mv, EdgeQ{q1, q2, qmode, u}, store, NS);
 
     // ================= C. pairs ======================================================================
     if (DISC) {
@@ -535,10 +523,12 @@ __global__ void straightLengthsKernel(ModelView mv, const double* __restrict__ q
     const DevJoint& J = T.joints[j];
     const double w = T.weights[j];
     const double w2 = w * w;
-    const double dq = b[J.idx_q] - a[J.idx_q];
     double d;
-    if (J.type <= HPPB200_JOINT_REVOLUTE_Z) d = w2 * (dq * dq);
-    else d = dq * dq;
+    if (J.type == HPPB200_JOINT_FREEFLYER) d = ffSquaredDistance(a + J.idx_q, b + J.idx_q, w2);
+    else {
+      const double dq = b[J.idx_q] - a[J.idx_q];
+      d = (J.type <= HPPB200_JOINT_REVOLUTE_Z) ? w2 * (dq * dq) : dq * dq;
+    }
     res += d;
   }
   L[i] = sqrt(res);

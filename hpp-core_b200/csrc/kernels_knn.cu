@@ -37,6 +37,7 @@ __device__ __forceinline__ double weighedDistanceDev(const Tables& T, const Mode
     const DevJoint& J = T.joints[j];
     const double w = T.weights[j];
     const double w2 = w * w;
+    if (J.type == HPPB200_JOINT_FREEFLYER) { res += ffSquaredDistance(a + J.idx_q, b + J.idx_q, w2); continue; }
     const double dq = b[J.idx_q] - a[J.idx_q];
     res += (J.type <= HPPB200_JOINT_REVOLUTE_Z) ? w2 * (dq * dq) : dq * dq;
   }
@@ -46,15 +47,20 @@ __device__ __forceinline__ double weighedDistanceDev(const Tables& T, const Mode
 // WeighedDistance of one node to KNN_QB queries at once: the node entry, the joint record and w^2 are loaded once
 // per joint; per query the operation sequence is the one of weighedDistanceDev (same bits).  `sq` holds the
 // queries in shared memory, `sw2` the per-joint w * w.
-template <int QB>
+template <int QB, bool FF>
 __device__ __forceinline__ void weighedDistanceBatch(const Tables& T, const ModelView& mv, const double* __restrict__ node,
                                                      const double* sq, const double* sw2, double (&d)[QB]) {
 #pragma unroll
   for (int q = 0; q < QB; ++q) d[q] = 0;
   for (int j = 0; j < mv.njoints; ++j) {
     const DevJoint& J = T.joints[j];
-    const double a = node[J.idx_q];
     const double w2 = sw2[j];
+    if (FF && J.type == HPPB200_JOINT_FREEFLYER) {  // distance(node, query): the argument order of nearestNeighbor::Basic
+#pragma unroll
+      for (int q = 0; q < QB; ++q) d[q] += ffSquaredDistance(node + J.idx_q, sq + q * mv.nq + J.idx_q, w2);
+      continue;
+    }
+    const double a = node[J.idx_q];
     const bool rev = J.type <= HPPB200_JOINT_REVOLUTE_Z;
 #pragma unroll
     for (int q = 0; q < QB; ++q) {
@@ -85,6 +91,8 @@ __device__ __forceinline__ bool keyLess(const Key& a, const Key& b) { return a.d
 #endif
 constexpr int KNN_QB = HPPB200_KNN_QB;
 
+// FF: the model has free-flyer joints (the SO(3) logarithm stays out of the vector-space instantiation)
+template <bool FF>
 __global__ void __launch_bounds__(KNN_THREADS)
 knnTileKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
               const double* __restrict__ queries, int nqueries, int32_t ccFilter, const Key* __restrict__ prev,
@@ -117,7 +125,7 @@ knnTileKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __r
     if (ccFilter >= 0 && cc[i] != ccFilter) continue;
     const double* node = nodes + i * (size_t)mv.nq;
     double dd[KNN_QB];
-    weighedDistanceBatch<KNN_QB>(T, mv, node, sq, sw2, dd);
+    weighedDistanceBatch<KNN_QB, FF>(T, mv, node, sq, sw2, dd);
 #pragma unroll
     for (int j = 0; j < KNN_QB; ++j) {
       const Key c = {dd[j], (long long)i};
@@ -187,6 +195,7 @@ __device__ __forceinline__ void topkInsert(Key& mine, Key& kth, const Key x, int
   kth.i = __shfl_sync(FULL, mine.i, k - 1);
 }
 
+template <bool FF>
 __global__ void __launch_bounds__(KNN_THREADS)
 knnTileTopkKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
                   const double* __restrict__ queries, int nqueries, int32_t ccFilter, int k, Key* __restrict__ partial) {
@@ -222,7 +231,7 @@ knnTileTopkKernel(ModelView mv, const double* __restrict__ nodes, const int32_t*
     const bool ok = i < hi && (ccFilter < 0 || cc[i] == ccFilter);
     const double* node = nodes + (ok ? i : lo) * (size_t)mv.nq;
     double dd[KNN_QB];
-    weighedDistanceBatch<KNN_QB>(T, mv, node, sq, sw2, dd);
+    weighedDistanceBatch<KNN_QB, FF>(T, mv, node, sq, sw2, dd);
 #pragma unroll
     for (int j = 0; j < KNN_QB; ++j) {
       const Key c = {dd[j], (long long)i};
@@ -412,7 +421,11 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
     const size_t nq = (size_t)nn->model->nq;
     if (nqueries > 0x7fffffffull / 4) throw std::invalid_argument("too many queries in one call");
     const size_t smemBytes = 16 + nn->view.blob_bytes + ((size_t)KNN_QB * nq + (size_t)nn->model->njoints) * sizeof(double);
-    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+    bool ff = false;
+    for (const DevJoint& J : nn->model->joints) ff = ff || J.type == HPPB200_JOINT_FREEFLYER;
+    auto tileKernel = ff ? knnTileKernel<true> : knnTileKernel<false>;
+    auto topkKernel = ff ? knnTileTopkKernel<true> : knnTileTopkKernel<false>;
+    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(tileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
     auto run = [&](const double* d_q, long long* d_i, double* d_d) {
       // k selection passes, each = tiled scan on the whole GPU + merge of the tiles (see knnTileKernel)
       const unsigned groups = (unsigned)((nqueries + KNN_QB - 1) / KNN_QB);
@@ -421,8 +434,8 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
       if (k > 1 && k <= 32) {  // single pass (k = 1 is one selection pass anyway, without the insertion logic)
         nn->d_keys.reserve(tiles * nqueries * (size_t)k * sizeof(Key) + 256);
         Key* d_part = (Key*)nn->d_keys.p;
-        HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTileTopkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-        knnTileTopkKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
+        HPPB200_CUDA_CHECK(cudaFuncSetAttribute(topkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+        topkKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
                                                                                             (int)nqueries, cc, k, d_part);
         knnMergeTopkKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, d_i, d_d);
         HPPB200_CUDA_CHECK(cudaGetLastError());
@@ -433,7 +446,7 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
       Key* d_part = d_prev + nqueries;
       knnInitPrevKernel<<<(unsigned)((nqueries + 255) / 256), 256, 0, nn->stream>>>(d_prev, (int)nqueries);
       for (int r = 0; r < k; ++r) {
-        knnTileKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
+        tileKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
                                                                                         (int)nqueries, cc, d_prev, d_part);
         knnReduceKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, r, d_prev, d_i, d_d);
       }

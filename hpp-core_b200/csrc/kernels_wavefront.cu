@@ -177,12 +177,7 @@ __device__ __forceinline__ void wfNewEdgeTables(const ModelView& mv, const WFArg
       for (int j = lane; j < mv.njoints; j += 32) {
         const DevJoint& J = T.joints[j];
         const int nvj = J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1;
-        double sj = 0;
-        for (int k = 0; k < nvj; ++k) {
-          const double vb = fabs(q2[J.idx_v + k] - q1[J.idx_v + k]) / Ls;
-          sj = fma(vb, vb, sj);
-        }
-        A.sv[(size_t)J.idx_v * E + es] = sqrt(sj);
+        A.sv[(size_t)J.idx_v * E + es] = jointVelocityNorm(q1, q2, J.idx_q, nvj, Ls);
       }
     }
     __syncwarp();
@@ -975,13 +970,7 @@ wfFkKernel(ModelView mv, WFArgs A) {
   if (t == 0.0 || L == 0.0) qmode = 0;
   else if (t == L) qmode = 1;
   else { qmode = 2; u = (t - 0.0) / L; }
-  auto qAt = [&](int k) -> double {
-    const double a = q1[k];
-    if (qmode == 0) return a;
-    const double b = q2[k];
-    if (qmode == 1) return b;
-    return fma(u, b - a, a);  // LiegroupSpace::interpolate on R^n
-  };
+  const EdgeQ qAt{q1, q2, qmode, u};
   if (TREE) {  // tree-shaped robots read parent placements back: lane-per-record stores
     if (on) forwardKinematics<true>(T, mv, qAt, A.plc + (size_t)e * A.fkSlots * 12, 1);
     return;

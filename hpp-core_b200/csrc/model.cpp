@@ -83,7 +83,6 @@ Model::Model(const hppb200_model_desc& d) {
     if (J.parent < 0 || J.parent > k) throw std::invalid_argument("joint parent must precede its child");
     J.type = d.joint_type[k];
     if (J.type < HPPB200_JOINT_REVOLUTE_X || J.type > HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("unknown joint type");
-    if (J.type == HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("free-flyer joints are not supported yet (HPPB200_ERR_UNSUPPORTED)");
     std::memcpy(J.P, d.joint_placement + 12 * k, sizeof(J.P));
     joint_nq[k] = J.type == HPPB200_JOINT_FREEFLYER ? 7 : 1;
     joint_nv[k] = J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1;
@@ -172,6 +171,17 @@ void Model::buildBodyPairs(const hppb200_model_desc& d) {
   auto maxDistToParent = [&](int j) {
     const DevJoint& J = joints[j - 1];
     if (J.type <= HPPB200_JOINT_REVOLUTE_Z) return norm3(J.P[9], J.P[10], J.P[11]);
+    if (J.type == HPPB200_JOINT_FREEFLYER) {  // farthest corner of the translation bounds (inf if unbounded)
+      double best = 0;
+      for (int c = 0; c < 8; ++c) {
+        const double p[3] = {(c & 1) ? upper[J.idx_q] : lower[J.idx_q], (c & 2) ? upper[J.idx_q + 1] : lower[J.idx_q + 1],
+                             (c & 4) ? upper[J.idx_q + 2] : lower[J.idx_q + 2]};
+        auto row = [&](int i) { return std::fma(J.P[3 * i + 2], p[2], std::fma(J.P[3 * i + 1], p[1], J.P[3 * i] * p[0])); };
+        const double n = norm3(row(0) + J.P[9], row(1) + J.P[10], row(2) + J.P[11]);
+        if (!(n <= best)) best = n;
+      }
+      return best;
+    }
     int a = J.type - HPPB200_JOINT_PRISMATIC_X;  // prismatic: farthest end of the stroke
     double best = 0;
     for (double s : {lower[J.idx_q], upper[J.idx_q]}) {
@@ -276,10 +286,10 @@ void Model::buildBlob() {
     }
     B.pair_end = (int)bg.size();
     B.coef_begin = (int)cf.size();
-    for (auto& c : b.coefs) cf.push_back(DevCoef{joints[c.first - 1].idx_v, joint_nv[c.first - 1], c.second});
+    for (auto& c : b.coefs) cf.push_back(DevCoef{joints[c.first - 1].idx_v, (int16_t)joint_nv[c.first - 1], (int16_t)joints[c.first - 1].idx_q, c.second});
     B.coef_end = (int)cf.size();
     B.rcoef_begin = (int)rcf.size();
-    for (auto& c : b.rcoefs) rcf.push_back(DevCoef{joints[c.first - 1].idx_v, joint_nv[c.first - 1], c.second});
+    for (auto& c : b.rcoefs) rcf.push_back(DevCoef{joints[c.first - 1].idx_v, (int16_t)joint_nv[c.first - 1], (int16_t)joints[c.first - 1].idx_q, c.second});
     B.rcoef_end = (int)rcf.size();
     bps.push_back(B);
   }

@@ -148,4 +148,22 @@ def uniform_configs(model, n, seed=12345, offset=0):
         bits = splitmix64(idx)
     u = (bits >> np.uint64(11)).astype(np.float64) * (2.0 ** -53)
     u = u.reshape(n, nq)
-    return model.q_lower[None, :] + u * (model.q_upper - model.q_lower)[None, :]
+    return normalize_quaternions(model, model.q_lower[None, :] + u * (model.q_upper - model.q_lower)[None, :])
+
+
+def freeflyer_ranks(model):
+    """Configuration rank of every free-flyer joint (7 entries each: x y z, qx qy qz qw)."""
+    ranks, r = [], 0
+    for t in model.joint_type:
+        if int(t) == 6:
+            ranks.append(r)
+        r += 7 if int(t) == 6 else 1
+    return ranks
+
+
+def normalize_quaternions(model, q):
+    """Scales the quaternion entries of free-flyer joints to unit norm (input data preparation)."""
+    q = np.array(q, dtype=np.float64, copy=True)
+    for r in freeflyer_ranks(model):
+        q[..., r + 3:r + 7] /= np.linalg.norm(q[..., r + 3:r + 7], axis=-1, keepdims=True)
+    return q

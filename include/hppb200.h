@@ -68,7 +68,7 @@ enum {
   HPPB200_JOINT_PRISMATIC_X = 3, /* nq = nv = 1 (R^1, translation) */
   HPPB200_JOINT_PRISMATIC_Y = 4,
   HPPB200_JOINT_PRISMATIC_Z = 5,
-  HPPB200_JOINT_FREEFLYER = 6 /* R^3 x SO(3): nq = 7 (x y z qx qy qz qw), nv = 6 */
+  HPPB200_JOINT_FREEFLYER = 6 /* R^3 x SO(3): nq = 7 (x y z qx qy qz qw, unit quaternion), nv = 6 (dt, log3) */
 };
 
 /* ---- shape types (coal::ShapeBase subclasses used by the path) ---------- */

@@ -123,16 +123,18 @@ def ellipsoid_hull(n, a, b, c):
     return np.stack([a * np.cos(th) * np.sin(phi), b * np.sin(th) * np.sin(phi), c * np.cos(phi)], axis=1)
 
 
-def humanoid():
-    """Fixed-pelvis humanoid-like TREE: waist (2) + neck (2) + 2 arms (7 each) + 2 legs (6 each) = 30 revolute
-    joints, capsule / sphere / box / convex-mesh bodies (BASELINE configs[3] without the free-flyer, which the
-    engine does not support yet).  Dimensions are made up (roughly 1.6 m tall); the point is the structure:
-    joint parents that are not the previous joint, convex meshes through GJK, hundreds of body pairs."""
+def humanoid(freeflyer=False):
+    """Humanoid-like TREE: waist (2) + neck (2) + 2 arms (7 each) + 2 legs (6 each) = 30 revolute joints,
+    capsule / sphere / box / convex-mesh bodies (BASELINE configs[3]); with `freeflyer` the pelvis hangs on a
+    free-flyer root joint (R^3 x SO(3), nq = 37, nv = 36), otherwise it is fixed to the world.  Dimensions are
+    made up (roughly 1.6 m tall); the point is the structure: joint parents that are not the previous joint,
+    convex meshes through GJK, hundreds of body pairs."""
     J = []  # name, parent, type, xyz
     def add(name, parent, typ, xyz):
         J.append((name, parent, typ, xyz))
         return len(J)
-    waist_y = add("waist_yaw", 0, REV_Z, (0, 0, 0.10))
+    root = add("root_joint", 0, FREEFLYER, (0, 0, 0)) if freeflyer else 0
+    waist_y = add("waist_yaw", root, REV_Z, (0, 0, 0.10))
     waist_p = add("waist_pitch", waist_y, REV_Y, (0, 0, 0.05))
     neck_y = add("neck_yaw", waist_p, REV_Z, (0, 0, 0.45))
     neck_p = add("neck_pitch", neck_y, REV_Y, (0, 0, 0.05))
@@ -149,7 +151,7 @@ def humanoid():
         a = add(side + "_wrist_roll", a, REV_X, (0, 0, -0.02))
         limbs[side + "arm"] = (ua, fa, a)
     for side, sy in (("l", 1.0), ("r", -1.0)):
-        a = add(side + "_hip_yaw", 0, REV_Z, (0, sy * 0.09, -0.05))
+        a = add(side + "_hip_yaw", root, REV_Z, (0, sy * 0.09, -0.05))
         a = add(side + "_hip_roll", a, REV_X, (0, 0, -0.03))
         a = add(side + "_hip_pitch", a, REV_Y, (0, 0, -0.03))
         th = a
@@ -164,7 +166,7 @@ def humanoid():
         verts.extend(ellipsoid_hull(n, a, b, c).tolist())
         return begin, n
     G = []  # name, joint, shape, params, placement, vbegin, vcount
-    G.append(("pelvis", 0, BOX, (0.10, 0.14, 0.07), se3(t=(0, 0, 0.0)), 0, 0))
+    G.append(("pelvis", root, BOX, (0.10, 0.14, 0.07), se3(t=(0, 0, 0.0)), 0, 0))
     vb, vc = mesh(24, 0.11, 0.17, 0.22)
     G.append(("torso", waist_p, CONVEX, (0, 0, 0), se3(t=(0, 0, 0.22)), vb, vc))
     G.append(("head", neck_p, SPHERE, (0.10,), se3(t=(0, 0, 0.10)), 0, 0))
@@ -190,16 +192,23 @@ def humanoid():
              prs(arms_l[1:], arms_r) + prs(["l_upper_arm"], arms_r[1:]) +
              prs(["l_forearm", "l_hand"], legs_l[:2] + legs_r[:2]) + prs(["r_forearm", "r_hand"], legs_l[:2] + legs_r[:2]) +
              prs(legs_l, legs_r) + prs(["l_shin", "l_foot", "l_toe_cap", "r_shin", "r_foot", "r_toe_cap"], ["pelvis"]))
-    n = len(J)
     lim = {REV_X: 0.8, REV_Y: 1.4, REV_Z: 1.2}
+    q_lower, q_upper = [], []
+    for j in J:
+        if j[2] == FREEFLYER:  # translation box; quaternion ranks bounded by +-1.01 as hpp-pinocchio sets them
+            q_lower += [-0.4, -0.4, -0.2] + [-1.01] * 4
+            q_upper += [0.4, 0.4, 0.3] + [1.01] * 4
+        else:
+            q_lower.append(-lim[j[2]])
+            q_upper.append(lim[j[2]])
     return {
-        "name": "humanoid_fixed_pelvis",
+        "name": "humanoid_freeflyer" if freeflyer else "humanoid_fixed_pelvis",
         "joint_names": [j[0] for j in J],
         "joint_parent": [j[1] for j in J],
         "joint_type": [j[2] for j in J],
         "joint_placement": [se3(None, j[3]) for j in J],
-        "q_lower": [-lim[j[2]] for j in J],
-        "q_upper": [lim[j[2]] for j in J],
+        "q_lower": q_lower,
+        "q_upper": q_upper,
         "geom_names": [g[0] for g in G],
         "geom_joint": [g[1] for g in G],
         "geom_shape": [g[2] for g in G],
@@ -294,7 +303,9 @@ def weighed_distance_weights(model):
             if k != i:
                 continue
             dt = oMi[j][1] - oMi[i][1]
-            if jt <= REV_Z:
+            if jt == FREEFLYER:  # rotation sub-Jacobian of R^3 x SO(3): singular values of [dt]x and of R
+                lin, ang = np.linalg.norm(dt), 1.0
+            elif jt <= REV_Z:
                 lin, ang = np.linalg.norm(np.cross(axis, dt)), 1.0
             else:
                 lin, ang = 1.0, 0.0
@@ -329,6 +340,14 @@ def main():
             json.dump(h, f, indent=1)
     print("wrote humanoid_obst{6,16}.json: %d joints, %d geometries, %d self pairs" % (
         len(h["joint_parent"]), len(h["geom_joint"]), len(h["self_pairs"])))
+    h = humanoid(freeflyer=True)
+    h["vertices"] = list(h["vertices"])
+    h.update(humanoid_obstacles(6, h["vertices"]))
+    h["weights"] = weighed_distance_weights(h)
+    h["name"] = "humanoid_ff_obst6"
+    with open(os.path.join(HERE, "humanoid_ff_obst6.json"), "w") as f:
+        json.dump(h, f, indent=1)
+    print("wrote humanoid_ff_obst6.json: %d joints (free-flyer root), nq = %d" % (len(h["joint_parent"]), len(h["q_lower"])))
 
 
 if __name__ == "__main__":

@@ -128,6 +128,22 @@ class Oracle:
         lib().oracle_straight_lengths(self.h, _p(q1, dp), _p(q2, dp), C.c_size_t(q1.shape[0]), _p(L, dp))
         return L
 
+    def interpolate(self, q1, q2, L, t):
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.nq)
+        L, t = np.ascontiguousarray(L, np.float64), np.ascontiguousarray(t, np.float64)
+        q = np.zeros_like(q1)
+        lib().oracle_interpolate(self.h, _p(q1, dp), _p(q2, dp), _p(L, dp), _p(t, dp), C.c_size_t(q1.shape[0]), _p(q, dp))
+        return q
+
+    def difference(self, q1, q2):
+        """q2 (-) q1, [n][nv]"""
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.nq)
+        v = np.zeros((q1.shape[0], self.nv))
+        lib().oracle_difference(self.h, _p(q1, dp), _p(q2, dp), C.c_size_t(q1.shape[0]), _p(v, dp))
+        return v
+
     def validate_edges(self, method, param, q1, q2, L, reverse=False, check_bounds=False, order_mode=0,
                        max_iter=0, nthreads=0):
         q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.nq)
@@ -183,6 +199,13 @@ def sincos(x):
     s, c = np.zeros_like(x), np.zeros_like(x)
     lib().oracle_sincos(_p(x, dp), C.c_size_t(x.size), _p(s, dp), _p(c, dp))
     return s, c
+
+
+def atan(x):
+    x = np.ascontiguousarray(x, np.float64)
+    y = np.zeros_like(x)
+    lib().oracle_atan(_p(x, dp), C.c_size_t(x.size), _p(y, dp))
+    return y
 
 
 def shape_distance(ta, pa, Ta, tb, pb, Tb, va=None, vb=None):

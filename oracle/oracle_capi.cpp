@@ -42,6 +42,19 @@ void oracle_sincos(const double* x, size_t n, double* s, double* c) {
   for (size_t i = 0; i < n; ++i) sincos_portable(x[i], s + i, c + i);
 }
 
+void oracle_atan(const double* x, size_t n, double* y) {
+  for (size_t i = 0; i < n; ++i) y[i] = atan_portable(x[i]);
+}
+// StraightPath::eval at parameter t of the edge (q1, q2, L), and q2 (-) q1
+void oracle_interpolate(OracleHandle* h, const double* q1, const double* q2, const double* L, const double* t, size_t n, double* q) {
+  const Device& d = *h->dev;
+  for (size_t i = 0; i < n; ++i) StraightPath(d, q1 + i * d.nq, q2 + i * d.nq, L[i]).eval(q + i * d.nq, t[i]);
+}
+void oracle_difference(OracleHandle* h, const double* q1, const double* q2, size_t n, double* v) {
+  const Device& d = *h->dev;
+  for (size_t i = 0; i < n; ++i) lieDifference(d, q2 + i * d.nq, q1 + i * d.nq, v + i * d.nv);
+}
+
 // ---- tables -----------------------------------------------------------------
 int oracle_num_config_pairs(OracleHandle* h) { return (int)ObstacleUser(*h->dev).cPairs.size(); }
 void oracle_get_config_pairs(OracleHandle* h, int32_t* a, int32_t* b, double* margin) {

@@ -139,6 +139,108 @@ inline void sincos_portable(double x, double* s, double* c) {
   }
 }
 
+// Portable arctangent (published fdlibm s_atan.c algorithm and coefficients: reduction at
+// 7/16, 11/16, 19/16, 39/16 + odd minimax polynomial; Horner steps written with fma).
+// Used by the SO(3) logarithm so that Lie-group interpolation is bit-reproducible on host
+// and device (only +,-,*,/,fma).  x >= 0 (inf allowed); the callers fold the sign.
+inline double atan_portable(double x) {
+  const double hi[4] = {4.63647609000806093515e-01, 7.85398163397448278999e-01, 9.82793723247329054082e-01,
+                        1.57079632679489655800e+00};
+  const double lo[4] = {2.26987774529616870924e-17, 3.06161699786838301793e-17, 1.39033110312309984516e-17,
+                        6.12323399573676603587e-17};
+  const double a0 = 3.33333333333329318027e-01, a1 = -1.99999999998764832476e-01, a2 = 1.42857142725034663711e-01,
+               a3 = -1.11111104054623557880e-01, a4 = 9.09088713343650656196e-02, a5 = -7.69187620504482999495e-02,
+               a6 = 6.66107313738753120669e-02, a7 = -5.83357013379057348645e-02, a8 = 4.97687799461593236017e-02,
+               a9 = -3.65315727442169155270e-02, a10 = 1.62858201153657823623e-02;
+  int id;
+  if (x >= 7.378697629483821e19) return hi[3] + lo[3];  // 2^66 and above (and inf)
+  if (x < 0.4375) {
+    if (x < 7.450580596923828e-09) return x;  // 2^-27
+    id = -1;
+  } else if (x < 1.1875) {
+    if (x < 0.6875) { id = 0; x = (2.0 * x - 1.0) / (2.0 + x); }
+    else { id = 1; x = (x - 1.0) / (x + 1.0); }
+  } else if (x < 2.4375) { id = 2; x = (x - 1.5) / std::fma(1.5, x, 1.0); }
+  else { id = 3; x = -1.0 / x; }
+  const double z = x * x, w = z * z;
+  const double s1 = z * std::fma(w, std::fma(w, std::fma(w, std::fma(w, std::fma(w, a10, a8), a6), a4), a2), a0);
+  const double s2 = w * std::fma(w, std::fma(w, std::fma(w, std::fma(w, a9, a7), a5), a3), a1);
+  if (id < 0) return x - x * (s1 + s2);
+  return hi[id] - ((x * (s1 + s2) - lo[id]) - x);
+}
+
+// ---- unit quaternions (x, y, z, w), Eigen coefficient order ----------------------------
+// a * b (Hamilton product)
+inline void quatMul(const double* a, const double* b, double* r) {
+  const double ax = a[0], ay = a[1], az = a[2], aw = a[3], bx = b[0], by = b[1], bz = b[2], bw = b[3];
+  r[0] = std::fma(-az, by, std::fma(ay, bz, std::fma(ax, bw, aw * bx)));
+  r[1] = std::fma(-ax, bz, std::fma(az, bx, std::fma(ay, bw, aw * by)));
+  r[2] = std::fma(-ay, bx, std::fma(ax, by, std::fma(az, bw, aw * bz)));
+  r[3] = std::fma(-az, bz, std::fma(-ay, by, std::fma(-ax, bx, aw * bw)));
+}
+// SO(3) logarithm of a unit quaternion: theta / |vec| * vec with theta = 2 atan(|vec| / w) folded into
+// (-pi, pi] (pinocchio quaternion::log3 as published; series below |vec|^2 = 2^-40).
+inline void so3Log(const double* q, double* v) {
+  const double x = q[0], y = q[1], z = q[2], w = q[3];
+  const double n2 = std::fma(z, z, std::fma(y, y, x * x));
+  double scale;
+  if (n2 < 9.094947017729282e-13) {
+    const double r2 = n2 / (w * w);
+    scale = std::fma(-2.0 / 3.0, r2, 2.0) / w;
+  } else {
+    const double n = std::sqrt(n2);
+    const double half = (w >= 0) ? atan_portable(n / w) : -atan_portable(n / -w);
+    scale = (2.0 * half) / n;
+  }
+  v[0] = scale * x; v[1] = scale * y; v[2] = scale * z;
+}
+// SO(3) exponential as a unit quaternion (pinocchio quaternion::exp3 as published)
+inline void so3Exp(const double* v, double* q) {
+  const double t2 = std::fma(v[2], v[2], std::fma(v[1], v[1], v[0] * v[0]));
+  double s, c;
+  if (t2 < 9.094947017729282e-13) {
+    s = std::fma(-1.0 / 48.0, t2, 0.5);
+    c = std::fma(-0.125, t2, 1.0);
+  } else {
+    const double t = std::sqrt(t2);
+    double sn;
+    sincos_portable(0.5 * t, &sn, &c);
+    s = sn / t;
+  }
+  q[0] = s * v[0]; q[1] = s * v[1]; q[2] = s * v[2]; q[3] = c;
+}
+// log3(q0^-1 * q1)
+inline void so3Difference(const double* q0, const double* q1, double* v) {
+  const double c[4] = {-q0[0], -q0[1], -q0[2], q0[3]};
+  double r[4];
+  quatMul(c, q1, r);
+  so3Log(r, v);
+}
+// Free-flyer in hpp-pinocchio = R^3 x SO(3) (Appendix A.3): q = [x y z, qx qy qz qw], v = [dt, log3].
+inline void ffDifference(const double* q0, const double* q1, double* v) {
+  v[0] = q1[0] - q0[0]; v[1] = q1[1] - q0[1]; v[2] = q1[2] - q0[2];
+  so3Difference(q0 + 3, q1 + 3, v + 3);
+}
+// q0 (+) u * (q1 (-) q0); the quaternion is renormalised to first order as pinocchio's integrate does
+inline void ffInterpolate(const double* q0, const double* q1, double u, double* q) {
+  for (int k = 0; k < 3; ++k) q[k] = std::fma(u, q1[k] - q0[k], q0[k]);
+  double d[3], e[4], r[4];
+  so3Difference(q0 + 3, q1 + 3, d);
+  d[0] = u * d[0]; d[1] = u * d[1]; d[2] = u * d[2];
+  so3Exp(d, e);
+  quatMul(q0 + 3, e, r);
+  const double n2 = std::fma(r[3], r[3], std::fma(r[2], r[2], std::fma(r[1], r[1], r[0] * r[0])));
+  const double alpha = 0.5 * (3.0 - n2);
+  for (int k = 0; k < 4; ++k) q[3 + k] = alpha * r[k];
+}
+// squaredDistance: translation unweighted, rotation w^2 * |log3|^2
+inline double ffSquaredDistance(const double* q0, const double* q1, double w2) {
+  const double dx = q1[0] - q0[0], dy = q1[1] - q0[1], dz = q1[2] - q0[2];
+  double l[3];
+  so3Difference(q0 + 3, q1 + 3, l);
+  return std::fma(dz, dz, std::fma(dy, dy, dx * dx)) + w2 * std::fma(l[2], l[2], std::fma(l[1], l[1], l[0] * l[0]));
+}
+
 constexpr double kInf = std::numeric_limits<double>::infinity();
 
 }  // namespace oracle

@@ -124,20 +124,20 @@ struct ConfigValidations {
 };
 
 // ---- Lie-group pieces (hpp-pinocchio LiegroupSpace, Appendix A.3) -------------
-// q1 (-) q0, size nv.  R^n joints: plain difference.
+// q1 (-) q0, size nv.  R^n joints: plain difference; free-flyer: R^3 x SO(3) (oracle_math.hpp).
 inline void lieDifference(const Device& dev, const double* q1, const double* q0, double* v) {
   for (int i = 1; i <= dev.njoints(); ++i) {
     const Joint& J = dev.joints[i];
-    if (J.type == HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("free-flyer Lie ops not in the oracle yet");
-    v[J.idx_v] = q1[J.idx_q] - q0[J.idx_q];
+    if (J.type == HPPB200_JOINT_FREEFLYER) ffDifference(q0 + J.idx_q, q1 + J.idx_q, v + J.idx_v);
+    else v[J.idx_v] = q1[J.idx_q] - q0[J.idx_q];
   }
 }
 // interpolate(q0,q1,u) = q0 (+) u*(q1 (-) q0); R^n: fma(u, q1-q0, q0)
 inline void lieInterpolate(const Device& dev, const double* q0, const double* q1, double u, double* q) {
   for (int i = 1; i <= dev.njoints(); ++i) {
     const Joint& J = dev.joints[i];
-    if (J.type == HPPB200_JOINT_FREEFLYER) throw std::invalid_argument("free-flyer Lie ops not in the oracle yet");
-    q[J.idx_q] = std::fma(u, q1[J.idx_q] - q0[J.idx_q], q0[J.idx_q]);
+    if (J.type == HPPB200_JOINT_FREEFLYER) ffInterpolate(q0 + J.idx_q, q1 + J.idx_q, u, q + J.idx_q);
+    else q[J.idx_q] = std::fma(u, q1[J.idx_q] - q0[J.idx_q], q0[J.idx_q]);
   }
 }
 
@@ -148,11 +148,12 @@ inline double weighedDistance(const Device& dev, const double* q1, const double*
   for (int i = 1; i <= dev.njoints(); ++i) {
     const Joint& J = dev.joints[i];
     double w2 = dev.weights[i - 1] * dev.weights[i - 1];
-    double dq = q2[J.idx_q] - q1[J.idx_q];
     double d;
-    if (J.type <= HPPB200_JOINT_REVOLUTE_Z) d = w2 * (dq * dq);
-    else if (J.type <= HPPB200_JOINT_PRISMATIC_Z) d = dq * dq;
-    else throw std::invalid_argument("free-flyer Lie ops not in the oracle yet");
+    if (J.type == HPPB200_JOINT_FREEFLYER) d = ffSquaredDistance(q1 + J.idx_q, q2 + J.idx_q, w2);
+    else {
+      double dq = q2[J.idx_q] - q1[J.idx_q];
+      d = (J.type <= HPPB200_JOINT_REVOLUTE_Z) ? w2 * (dq * dq) : dq * dq;
+    }
     res += d;
   }
   return std::sqrt(res);

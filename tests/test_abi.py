@@ -32,7 +32,7 @@ def test_struct_layout_matches_header(pkg):
 
 
 @pytest.mark.parametrize("name", ["ur5_boxes0.json", "ur5_boxes1.json", "ur5_boxes8.json", "ur5_boxes32.json",
-                                  "humanoid_obst6.json", "humanoid_obst16.json"])
+                                  "humanoid_obst6.json", "humanoid_obst16.json", "humanoid_ff_obst6.json"])
 def test_model_tables_match_oracle(pkg, ob, name):
     desc = pkg.ModelDescription.load(name)
     m = pkg.Model(desc)

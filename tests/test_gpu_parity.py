@@ -318,7 +318,7 @@ def _local_edges(pkg, desc, n, seed, step):
     q1 = pkg.uniform_configs(desc, n, seed=seed)
     d = np.random.default_rng(seed).normal(size=q1.shape)
     q2 = np.clip(q1 + step * d / np.linalg.norm(d, axis=1, keepdims=True), desc.q_lower, desc.q_upper)
-    return q1, q2
+    return q1, pkg.normalize_quaternions(desc, q2)
 
 
 @pytest.mark.parametrize("name", ["humanoid_obst6.json", "humanoid_obst16.json"])
@@ -352,6 +352,64 @@ def test_humanoid_tree_convex_parity(pkg, ob, monkeypatch, name):
                 assert np.array_equal(r[k], e[k]), (name, method, rev, k)
             assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
             assert 0.02 < r["valid"].mean() < 0.98
+
+
+@pytest.mark.parametrize("wf_min", ["1", "100000000"])
+def test_freeflyer_humanoid_parity(pkg, ob, monkeypatch, wf_min):
+    """BASELINE configs[3] model WITH its free-flyer root (R^3 x SO(3), nq = 37, nv = 36): FK from the quaternion,
+    Lie-group interpolation along the edge (SO(3) log / exp), velocity bounds from q2 (-) q1, WeighedDistance with
+    the rotation logarithm.  Through the wavefront engine (wf_min = 1) and through the CTA engine / walker
+    (wavefront off).  Bit-exact against the oracle; quaternions of either sign."""
+    monkeypatch.setenv("HPPB200_WF_MIN", wf_min)
+    desc = pkg.ModelDescription.load("humanoid_ff_obst6.json")
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    o = ob.Oracle(desc)
+    q = pkg.uniform_configs(desc, 20000, seed=91)
+    assert np.array_equal(ws.geometry_placements(q[:2000]), o.geometry_placements(q[:2000]))
+    assert np.array_equal(ws.pair_distances(q[:2000]), o.pair_distances(q[:2000]))
+    got, exp = ws.validate_configs(q, check_bounds=True), o.validate_configs(q, check_bounds=True)
+    for a, b in zip(got, exp):
+        assert np.array_equal(a, b)
+    assert 0.02 < got[0].mean() < 0.9
+    a1, a2 = _local_edges(pkg, desc, 3000, 92, 0.4)
+    b1, b2, _ = _edges(pkg, desc, o, 1000, 93)
+    z = pkg.uniform_configs(desc, 100, seed=94)  # zero-length edges
+    q1, q2 = np.concatenate([a1, b1, z]), np.concatenate([a2, b2, z])
+    L = o.straight_lengths(q1, q2)
+    assert np.array_equal(ws.straight_lengths(q1, q2), L)
+    for method, param in ((0, 0.05), (1, 1e-3), (2, 0.0)):
+        for rev in (False, True):
+            r = ws.validate_edges(method, param, q1, q2, L, reverse=rev)
+            e = o.validate_edges(method, param, q1, q2, L, reverse=rev)
+            assert ws.stats()["iter_cap_hits"] == 0
+            for k in ("valid", "reason", "pair", "t_last_valid"):
+                assert np.array_equal(r[k], e[k]), (method, rev, k)
+            assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+            assert 0.02 < r["valid"].mean() < 0.98
+
+
+def test_freeflyer_knn_parity(pkg, ob):
+    """WeighedDistance k-NN over free-flyer configurations: translation unweighted + w^2 |log3(q_node^-1 q)|^2."""
+    desc = pkg.ModelDescription.load("humanoid_ff_obst6.json")
+    m, o = pkg.Model(desc), ob.Oracle(desc)
+    nn = pkg.NearestNeighbor(m, 0)
+    nodes = pkg.uniform_configs(desc, 20000, seed=95)
+    nodes[5000] = nodes[77]
+    cc = (np.arange(len(nodes)) % 3).astype(np.int32)
+    nn.append(nodes, cc)
+    o.knn_append(nodes, cc)
+    qs = pkg.uniform_configs(desc, 37, seed=96)
+    qs[0] = nodes[77]
+    for k, c in ((1, -1), (1, 2), (10, -1), (7, 1), (33, -1)):
+        gi, gd = nn.query(qs, k, c)
+        oi, od = o.knn_query(qs, k, c)
+        srt = np.lexsort((oi, od), axis=1)
+        oi, od = np.take_along_axis(oi, srt, axis=1), np.take_along_axis(od, srt, axis=1)
+        assert np.array_equal(gi, oi), (k, c)
+        assert np.array_equal(gd, od)
+    balls, _ = nn.within_ball(qs[:4], 2.0)
+    for i in range(4):
+        assert np.array_equal(balls[i], o.knn_within_ball(qs[i], 2.0))
 
 
 @pytest.mark.parametrize("reverse", [False, True])

@@ -291,3 +291,77 @@ def test_humanoid_tree_oracle_invariants(pkg, ob):
     cc = o.validate_edges(2, 0.0, q1, qb, L)["valid"]
     assert not np.any((dd == 0) & (cc == 1)) and np.mean((dd == 0) & (pp == 1)) < 0.01
     assert 0.05 < cc.mean() < 0.95
+
+
+def test_portable_atan_accuracy(ob):
+    """The arctangent behind the SO(3) logarithm stays within 1 ulp of libm over its whole domain."""
+    rng = np.random.default_rng(1)
+    x = np.concatenate([rng.uniform(0, 4, 100000), 10.0 ** rng.uniform(-12, 25, 100000),
+                        [0.0, np.inf, 0.4375, 0.6875, 1.1875, 2.4375, 2.0 ** -27, 2.0 ** 66]])
+    y, r = ob.atan(x), np.arctan(x)
+    assert np.all(np.abs(y - r) <= np.spacing(np.maximum(r, 1e-300)))
+
+
+def test_freeflyer_lie_group_ops(pkg, ob):
+    """Free-flyer = R^3 x SO(3): interpolation returns the stored end points exactly,
+    stays on the unit sphere, is a geodesic of WeighedDistance (d(q1,q) + d(q,q2) = L), the difference has the
+    rotation angle of the relative quaternion (shorter arc), and -q2 describes the same path end."""
+    desc = pkg.ModelDescription.load("humanoid_ff_obst6.json")
+    o = ob.Oracle(desc)
+    assert (o.nq, o.nv) == (37, 36) and pkg.freeflyer_ranks(desc) == [0]
+    q1, q2 = pkg.uniform_configs(desc, 2000, seed=3), pkg.uniform_configs(desc, 2000, seed=4)
+    L = o.straight_lengths(q1, q2)
+    assert np.array_equal(o.interpolate(q1, q2, L, 0 * L), q1) and np.array_equal(o.interpolate(q1, q2, L, L), q2)
+    v = o.difference(q1, q2)
+    assert np.array_equal(v[:, :3], q2[:, :3] - q1[:, :3]) and np.array_equal(v[:, 6:], q2[:, 7:] - q1[:, 7:])
+    dots = np.abs(np.sum(q1[:, 3:7] * q2[:, 3:7], axis=1))
+    assert np.allclose(np.linalg.norm(v[:, 3:6], axis=1), 2 * np.arccos(np.clip(dots, 0, 1)), atol=1e-12)
+    for u in (1e-9, 0.25, 0.5, 0.9, 1 - 1e-9):
+        q = o.interpolate(q1, q2, L, u * L)
+        assert np.abs(np.linalg.norm(q[:, 3:7], axis=1) - 1).max() < 1e-15
+        assert np.abs(o.straight_lengths(q1, q) + o.straight_lengths(q, q2) - L).max() < 1e-13
+        assert np.allclose(o.straight_lengths(q1, q), u * L, rtol=1e-9, atol=1e-13)
+    flipped = q2.copy()
+    flipped[:, 3:7] *= -1
+    assert np.allclose(o.straight_lengths(q1, flipped), L, rtol=1e-14)
+    assert np.allclose(o.geometry_placements(q2[:50]), o.geometry_placements(flipped[:50]), atol=1e-15)
+    # zero rotation: the difference vanishes (to rounding), interpolation keeps the quaternion
+    same = q2.copy()
+    same[:, 3:7] = q1[:, 3:7]
+    assert np.abs(o.difference(q1, same)[:, 3:6]).max() < 1e-15
+    assert np.abs(o.interpolate(q1, same, o.straight_lengths(q1, same), 0.3 * o.straight_lengths(q1, same))[:, 3:7]
+                  - q1[:, 3:7]).max() < 1e-15
+
+
+def test_freeflyer_humanoid_oracle_invariants(pkg, ob):
+    """Reference invariants I1 / I2 (tests/test-continuous-validation.cc:200-205,251-253) on the free-flyer
+    humanoid, and FK of the floating base: every geometry placement moves rigidly with the root joint."""
+    desc = pkg.ModelDescription.load("humanoid_ff_obst6.json")
+    o = ob.Oracle(desc)
+    q = pkg.uniform_configs(desc, 300, seed=5)
+    ng = len(desc.geom_names)
+    nrobot = ng  # obstacles are not in geometry_placements
+    P = o.geometry_placements(q).reshape(len(q), nrobot, 12)
+    base = q.copy()
+    base[:, :3] = 0
+    base[:, 3:7] = [0, 0, 0, 1]
+    P0 = o.geometry_placements(base).reshape(len(q), nrobot, 12)
+    x, y, z, w = q[:, 3], q[:, 4], q[:, 5], q[:, 6]
+    R = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                  2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                  2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], axis=1).reshape(-1, 3, 3)
+    t_exp = np.einsum("nij,nkj->nki", R, P0[:, :, 9:]) + q[:, None, :3]
+    assert np.allclose(P[:, :, 9:], t_exp, atol=1e-12)
+    q1 = pkg.uniform_configs(desc, 500, seed=6)
+    d = np.random.default_rng(6).normal(size=q1.shape)
+    qb = pkg.normalize_quaternions(desc, np.clip(q1 + 0.4 * d / np.linalg.norm(d, axis=1, keepdims=True),
+                                                 desc.q_lower, desc.q_upper))
+    L = o.straight_lengths(q1, qb)
+    v = o.validate_configs(q1)[0]
+    for meth, par in ((0, 0.05), (1, 1e-3), (2, 0.0)):
+        assert np.array_equal(o.validate_edges(meth, par, q1, q1, np.zeros(len(q1)))["valid"], v)
+    dd = o.validate_edges(0, 0.05, q1, qb, L)["valid"]
+    pp = o.validate_edges(1, 1e-3, q1, qb, L)["valid"]
+    cc = o.validate_edges(2, 0.0, q1, qb, L)["valid"]
+    assert not np.any((dd == 0) & (cc == 1)) and np.mean((dd == 0) & (pp == 1)) < 0.01
+    assert 0.05 < cc.mean() < 0.95
