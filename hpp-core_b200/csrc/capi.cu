@@ -31,6 +31,9 @@ Workspace::Workspace(const Model* m, int dev) : model(m), device(dev) {
   if (const char* v = std::getenv("HPPB200_ENGINE")) { use_engine = std::atoi(v) != 0; if (use_engine) engine_kind = std::atoi(v); }
   if (const char* v = std::getenv("HPPB200_WF_MIN")) wavefront_min = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_WF_TAIL")) wavefront_tail = std::atol(v);
+  if (const char* v = std::getenv("HPPB200_TAIL")) use_tail = std::atoi(v) != 0;
+  if (const char* v = std::getenv("HPPB200_TAIL_SMEM")) tail_smem = std::atoi(v) != 0;
+  if (const char* v = std::getenv("HPPB200_TAIL_MAX")) tail_max = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_WF_SLOTS")) wavefront_slots = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_ENGINE_ALPHA")) engine_alpha = std::atof(v);
   if (const char* v = std::getenv("HPPB200_ENGINE_THREADS")) engine_threads = std::atoi(v);

@@ -160,7 +160,10 @@ struct Workspace {
   DeviceBuffer<int32_t> d_pair, d_pair_int;
   DeviceBuffer<unsigned long long> d_jobs;
   unsigned long long last_jobs = 0;
-  DeviceBuffer<unsigned char> d_state;
+  DeviceBuffer<unsigned char> d_state, d_tail;
+  bool use_tail = true;        // Dichotomy: CTA-per-edge pass for handed-over edges (HPPB200_TAIL=0: walker large-list pass only)
+  bool tail_smem = true;       // first CTA-per-edge pass keeps the per-pair lists in shared memory (HPPB200_TAIL_SMEM)
+  size_t tail_max = 8192;      // Dichotomy batches up to this size go to the CTA-per-edge kernel directly (HPPB200_TAIL_MAX)
   void syncStats();
 };
 
@@ -179,6 +182,9 @@ bool launchProgressiveEngine(Workspace* ws, double tol, int reverse, const doubl
 bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const double* d_q1, const double* d_q2,
                                 const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                                 int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
+bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
+                         const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
+                         uint8_t* d_reason, int overflow_reason, bool smemLists);
 void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1,
                          const double* d_q2, const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid,
                          double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason);

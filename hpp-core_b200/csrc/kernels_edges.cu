@@ -645,6 +645,19 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine)
     engineDone = launchProgressiveEngine(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,
                                          REASON_OVERFLOW_INTERNAL);
+  // Dichotomy, one CTA per edge (kernels_tail.cu): level 1 keeps the per-pair interval lists in shared memory,
+  // level 2 (64-entry lists in global memory) takes what outgrows level 1; small batches start there directly
+  const int smemK = std::min(64, (int)(65536 / (16 * std::max(1, (int)ws->view.nbodypairs))));
+  auto tailPass = [&](const uint32_t* list, size_t cnt, int level) {
+    if (level == 1 && (!ws->tail_smem || smemK < 8)) return false;
+    return launchDichotomyTail(ws, param, reverse, d_q1, d_q2, d_L, list, cnt, d_valid, d_tfail, d_tlast, d_pair, d_reason,
+                               REASON_OVERFLOW_INTERNAL, level == 1);
+  };
+  int tailLevel = 0;
+  if (!engineDone && method == HPPB200_METHOD_DICHOTOMY && ws->use_tail && n <= ws->tail_max) {
+    for (int level = 1; level <= 2 && !engineDone; ++level)
+      if (tailPass(nullptr, n, level)) { engineDone = true; tailLevel = level; }
+  }
   if (!engineDone) {
   // pass 1: first sample of every edge (uniform warps); pass 2: resume the survivors
   const size_t NPb = (size_t)ws->view.nbodypairs;
@@ -686,6 +699,28 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   ws->stats.kernel_launches += 1;
   A.edge_list = ws->d_list.p;
   A.n = (size_t)nover;
+  if (method == HPPB200_METHOD_DICHOTOMY && ws->use_tail) {
+    unsigned long long cur = nover;
+    DeviceStats last = after;
+    for (int level = tailLevel + 1; level <= 2; ++level) {
+      if (level == 2 && tailLevel == 1 && smemK >= 64) continue;  // same capacity as the pass that overflowed
+      if (!tailPass(ws->d_list.p, (size_t)cur, level)) continue;
+      tailLevel = level;
+      DeviceStats now;
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(&now, ws->d_stats, sizeof(now), cudaMemcpyDeviceToHost, ws->stream));
+      HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+      const unsigned long long left = now.overflow - last.overflow;
+      last = now;
+      if (std::getenv("HPPB200_WF_TRACE")) std::fprintf(stderr, "[edges] CTA-per-edge pass %d: %llu of %llu edges go on\n", level, left, cur);
+      if (left == 0) return;
+      HPPB200_CUDA_CHECK(cudaMemsetAsync(ws->d_count.p, 0, sizeof(unsigned long long), ws->stream));
+      collectOverflowKernel<<<(unsigned)((n + 255) / 256), 256, 0, ws->stream>>>(d_reason, n, ws->d_list.p, ws->d_count.p);
+      HPPB200_CUDA_CHECK(cudaGetLastError());
+      ws->stats.kernel_launches += 1;
+      cur = left;
+    }
+    A.n = (size_t)cur;
+  }
   A.overflow_reason = HPPB200_REASON_ITER_CAP;
   const size_t slots2 = 2048;  // 255-entry lists: ~4 KB per body pair per slot
   if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, A, 255, 1, slots2);

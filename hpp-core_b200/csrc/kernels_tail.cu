@@ -1,0 +1,504 @@
+// Dichotomy, one CTA per edge: the pass that finishes the edges the batch engines hand over (interval lists
+// beyond the wavefront's capacity, the thin tail of a batch) and the path of small batches.
+//
+// Replaces Dichotomy::validateStraightPath (src/continuous-validation/dichotomy.cc:68-132) +
+// ContinuousValidation::validateConfiguration / validateIntervals (src/continuous-validation.cc:128-148,
+// include/hpp/core/continuous-validation.hh:267-298) + BodyPairCollision::validateConfiguration
+// (src/continuous-validation/body-pair-collision.cc:45-99) for ONE edge per CTA.
+//
+// Why: an edge that grazes an obstacle needs thousands of bisection samples, each depending on the previous one,
+// and keeps tens of disjoint validated intervals on the binding body pairs.  The lane-per-edge walker pays the
+// whole sample (FK, list scans, narrow phase) in one thread: ~110 us per sample on UR5, ~350 us on the 30-joint
+// tree, and the longest edge is the floor of the batch time.  Here the 128 threads of a CTA share the sample:
+//   A  joint transforms (thread per joint)  |  cover search: the validated interval of each body pair that
+//      contains t (thread per body pair; lists are 64-entry arrays in global memory, L1-resident)
+//   B  chain composition (one thread: 63 flops per joint)
+//   C  geometry placements (thread per geometry)
+//   D  narrow phase of the body pairs the reference certainly evaluates (no validated interval around t)
+//   E  replay of validateIntervals in the reference order (one thread); a covered pair whose cover turns out
+//      not to contain the running intersection needs a second narrow-phase stage (speculative: results of
+//      pairs the replay then skips are discarded, never inserted)
+//   F  interval inserts (thread per body pair), smallest-first swap, valid subset, next parameter.
+// Results are bit-identical to the walker and the oracle: same per-pair arithmetic, same order of decisions.
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+
+#include "dev_intervals.cuh"
+
+namespace hppb200 {
+
+constexpr int DT_THREADS = 128;
+constexpr int DT_MINB = 3;   // CTAs per SM the register budget is held to
+constexpr int DT_K = 64;     // validated intervals per body pair (lists in global memory)
+constexpr int DT_KS = 256;   // intervals of the edge's valid subset (shared memory)
+constexpr uint32_t DT_SMEM_LISTS = 64u * 1024u;  // shared-memory budget of the per-pair lists of the first pass
+
+struct TailArgs {
+  const double* q1;
+  const double* q2;
+  const double* L;
+  const uint32_t* edge_list;  // optional indirection
+  size_t n;
+  int reverse;
+  double tol;
+  uint32_t max_iter;
+  int overflow_reason;
+  uint8_t* valid;
+  double* t_fail;
+  double* t_last;
+  int32_t* pair;
+  uint8_t* reason;
+  unsigned long long* counter;
+  double2* lists;  // [grid][nbodypairs][K] in global memory, or null: the lists live in shared memory
+  int K;           // validated intervals per body pair
+  unsigned long long* clk;  // optional [8]: cycles of thread 0 per phase (HPPB200_WF_TRACE)
+};
+
+// dynamic shared memory of one CTA
+struct TailLayout {
+  uint32_t off_plc, off_li, off_sv, off_vmax, off_cover, off_res, off_pcov, off_pres, off_sub, off_lists, off_order, off_cnt, off_state,
+      off_pflag, off_depth, off_visit, total;
+};
+// smemK: entries per body pair of the lists kept in shared memory (0: lists in global memory)
+__host__ __device__ inline TailLayout tailLayout(const ModelView& mv, int smemK) {
+  TailLayout Lo;
+  uint32_t o = 0;
+  Lo.off_plc = o; o += (uint32_t)(mv.ngeoms + mv.njoints) * 12u * 8u;
+  Lo.off_li = o; o += (uint32_t)mv.njoints * 12u * 8u;
+  Lo.off_sv = o; o += (uint32_t)mv.nv * 8u;
+  Lo.off_vmax = o; o += (uint32_t)mv.nbodypairs * 8u;
+  o = (o + 15u) & ~15u;  // double2 records
+  Lo.off_cover = o; o += (uint32_t)mv.nbodypairs * 16u;
+  Lo.off_res = o; o += (uint32_t)mv.nbodypairs * 16u;
+  Lo.off_pcov = o; o += (uint32_t)mv.nbodypairs * 16u;  // the same two records by order position (replay)
+  Lo.off_pres = o; o += (uint32_t)mv.nbodypairs * 16u;
+  Lo.off_sub = o; o += (uint32_t)DT_KS * 16u;
+  Lo.off_lists = o; o += (uint32_t)mv.nbodypairs * (uint32_t)smemK * 16u;
+  Lo.off_order = o; o += (uint32_t)mv.nbodypairs * 2u;
+  Lo.off_cnt = o; o += (uint32_t)mv.nbodypairs * 2u;
+  Lo.off_state = o; o += (uint32_t)mv.nbodypairs;
+  Lo.off_pflag = o; o += (uint32_t)mv.nbodypairs + ((uint32_t)mv.nbodypairs + 31u) / 32u;  // + first valid_ lane per block
+  Lo.off_depth = o; o += (uint32_t)mv.njoints;
+  o = (o + 3u) & ~3u;
+  Lo.off_visit = o; o += ((uint32_t)mv.nbodypairs + 31u) / 32u * 4u;  // positions the replay has to visit
+  Lo.total = (o + 15u) & ~15u;
+  return Lo;
+}
+
+enum : uint8_t { ST_VALID = 1, ST_CAND = 2, ST_DONE = 4, ST_INSERT = 8 };
+enum : int { RUN_SAMPLE = 0, RUN_STAGE = 1, RUN_FINISHED = 2 };
+enum : uint8_t { PF_RESULT = 1, PF_HIT = 2, PF_SKIP = 4, PF_FOLD = 8 };  // per order position, replay in / out
+
+__device__ __forceinline__ void store12(double* p, const T3& X) {
+#pragma unroll
+  for (int i = 0; i < 9; ++i) p[i] = X.r[i];
+  p[9] = X.t.x; p[10] = X.t.y; p[11] = X.t.z;
+}
+
+__global__ void __launch_bounds__(DT_THREADS, DT_MINB)
+dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const Tables T = makeTables(mv.blob, mv);  // global copy (read-only, L1 resident)
+  const TailLayout Lo = tailLayout(mv, A.lists ? 0 : A.K);
+  double* plc = (double*)(smem + Lo.off_plc);  // geometry g at 12 g, joint j (1-based) at 12 (ngeoms + j - 1)
+  double* li = (double*)(smem + Lo.off_li);
+  double* sv = (double*)(smem + Lo.off_sv);
+  double* vmax = (double*)(smem + Lo.off_vmax);
+  double2* cover = (double2*)(smem + Lo.off_cover);
+  double2* res = (double2*)(smem + Lo.off_res);
+  uint16_t* order = (uint16_t*)(smem + Lo.off_order);
+  uint16_t* lcnt = (uint16_t*)(smem + Lo.off_cnt);
+  uint8_t* state = (uint8_t*)(smem + Lo.off_state);
+  double2* pcov = (double2*)(smem + Lo.off_pcov);
+  double2* pres = (double2*)(smem + Lo.off_pres);
+  uint8_t* pflag = (uint8_t*)(smem + Lo.off_pflag);  // by position: PF_* in, decision out
+  uint8_t* jdepth = (uint8_t*)(smem + Lo.off_depth);
+  uint32_t* visit = (uint32_t*)(smem + Lo.off_visit);
+  __shared__ double s_t, s_ilo, s_ihi;
+  __shared__ int s_run, s_pos, s_smallest, s_subCnt, s_overflow, s_has, s_stop, s_depth;
+  __shared__ uint32_t s_edge, s_iters;
+
+  const int tid = threadIdx.x;
+  const int NP = mv.nbodypairs, NJ = mv.njoints, NG = mv.ngeoms;
+  const double INF = CUDART_INF;
+  const bool reverse = A.reverse != 0;
+  const int K = A.K;
+  double2* lists = A.lists ? A.lists + (size_t)blockIdx.x * NP * K : (double2*)(smem + Lo.off_lists);
+  double2* sub = (double2*)(smem + Lo.off_sub);
+  __shared__ long long s_ck[8];
+  long long c0 = 0;
+  const bool timing = A.clk != nullptr && tid == 0;
+  if (timing)
+    for (int i = 0; i < 8; ++i) s_ck[i] = 0;
+#define DT_TICK(i) do { if (timing) { const long long c1 = clock64(); s_ck[i] += c1 - c0; c0 = c1; } } while (0)
+  GjkCounters cnt = {0u, 0u, 0u};
+  unsigned tests = 0, samples = 0, caps = 0, overflows = 0, discarded = 0;
+
+  if (tid == 0) {  // tree level of every joint (parents precede children)
+    int deepest = 0;
+    for (int j = 1; j <= NJ; ++j) {
+      const int parent = T.joints[j - 1].parent;
+      const int d = parent == 0 ? 1 : jdepth[parent - 1] + 1;
+      jdepth[j - 1] = (uint8_t)d;
+      deepest = d > deepest ? d : deepest;
+    }
+    s_depth = deepest;
+  }
+  for (;;) {
+    if (tid == 0) {
+      const unsigned long long i = atomicAdd(A.counter, 1ull);
+      s_has = i < A.n ? 1 : 0;
+      if (s_has) s_edge = A.edge_list ? A.edge_list[i] : (uint32_t)i;
+    }
+    __syncthreads();
+    if (!s_has) break;
+    const uint32_t edge = s_edge;
+    const double L = A.L[edge];
+    const double* q1 = A.q1 + (size_t)edge * mv.nq;
+    const double* q2 = A.q2 + (size_t)edge * mv.nq;
+    // dichotomy.cc:113-121: the valid part ends where the first (last, if reverse) validated interval ends
+    auto dichLast = [&]() -> double { return reverse ? sub[s_subCnt - 1].x : sub[0].y; };
+    auto finishEdge = [&](bool ok, int rs, double tf, double tl, int pr) {
+      A.valid[edge] = ok ? 1 : 0;
+      if (A.t_fail) A.t_fail[edge] = tf;
+      if (A.t_last) A.t_last[edge] = tl;
+      if (A.pair) A.pair[edge] = pr;
+      if (A.reason) A.reason[edge] = (uint8_t)rs;
+    };
+
+    // ---- BodyPairCollision::setupPath for every body pair (body-pair-collision.cc:101-117) ----
+    for (int p = tid; p < NP; p += DT_THREADS) { order[p] = (uint16_t)p; lcnt[p] = 0; state[p] = 0; }
+    if (L != 0)
+      for (int j = tid; j < NJ; j += DT_THREADS) {
+        const DevJoint& J = T.joints[j];
+        sv[J.idx_v] = jointVelocityNorm(q1, q2, J.idx_q, J.type == HPPB200_JOINT_FREEFLYER ? 6 : 1, L);
+      }
+    __syncthreads();
+    for (int p = tid; p < NP; p += DT_THREADS) {  // SolidSolidCollision::computeMaximalVelocity (:76-99)
+      const DevBodyPair& B = T.bodypairs[p];
+      double Vm;
+      if (L == 0) Vm = INF;
+      else {
+        double ab = 0;
+        for (int c = B.coef_begin; c < B.coef_end; ++c) ab += T.coefs[c].value * sv[T.coefs[c].idx_v];
+        Vm = ab;
+        if (B.joint_b != 0) {
+          double ba = 0;
+          for (int c = B.rcoef_begin; c < B.rcoef_end; ++c) ba += T.rcoefs[c].value * sv[T.rcoefs[c].idx_v];
+          if (ba < ab) Vm = ba;
+        }
+      }
+      vmax[p] = Vm;
+    }
+    if (tid == 0) {
+      const double t = reverse ? L : 0.0;
+      s_t = t;
+      sub[0] = make_double2(t, t);  // validSubset.unionInterval((t, t)) (dichotomy.cc:84)
+      s_subCnt = 1;
+      s_iters = 0;
+      s_run = RUN_SAMPLE;
+    }
+    __syncthreads();
+
+    for (;;) {  // one sample per turn
+      if (tid == 0) {
+        if (s_iters >= A.max_iter) {
+          ++caps;
+          finishEdge(false, HPPB200_REASON_ITER_CAP, s_t, dichLast(), -1);
+          s_run = RUN_FINISHED;
+        } else {
+          ++s_iters;
+          ++samples;
+        }
+      }
+      __syncthreads();
+      if (s_run == RUN_FINISHED) break;
+      const double t = s_t;
+      if (timing) c0 = clock64();
+
+      // ---- A: joint transforms | cover search ----
+      {
+        const EdgeQ eq = edgeQ(q1, q2, t, L);
+        for (int j = tid; j < NJ; j += DT_THREADS) store12(li + j * 12, jointLocal(T.joints[j], eq));
+      }
+      for (int p = tid; p < NP; p += DT_THREADS) {
+        uint8_t st = state[p] & ST_VALID;
+        if (!st) {
+          const int c = lcnt[p];
+          const double2* lst = lists + (size_t)p * K;
+          double2 cv = make_double2(INF, -INF);
+          if (!reverse) {  // t sits right behind the validated start: the interval around it is near the front
+            for (int i = 0; i < c; ++i) {
+              const double2 v = lst[i];
+              if (v.y >= t) { if (v.x <= t) cv = v; break; }
+            }
+          } else {
+            for (int i = c - 1; i >= 0; --i) {
+              const double2 v = lst[i];
+              if (v.x <= t) { if (t <= v.y) cv = v; break; }
+            }
+          }
+          cover[p] = cv;
+          if (cv.y == -INF) st = ST_CAND;  // no validated interval around t: evaluated whatever the order
+        }
+        state[p] = st;
+      }
+      __syncthreads();
+      DT_TICK(0);
+      // ---- B: oMi = oMi[parent] * liMi, one tree level at a time (a lane per joint of the level) ----
+      if (tid < 32) {
+        if (s_depth == NJ) {  // a chain: nothing to share out
+          if (tid == 0)
+            for (int j = 1; j <= NJ; ++j) {
+              const T3 l = load12(li + (j - 1) * 12);
+              store12(plc + (NG + j - 1) * 12, j == 1 ? l : compose(load12(plc + (NG + j - 2) * 12), l));
+            }
+        } else
+        for (int lv = 1; lv <= s_depth; ++lv) {
+          for (int j = tid + 1; j <= NJ; j += 32) {
+            if (jdepth[j - 1] != lv) continue;
+            const int parent = T.joints[j - 1].parent;
+            const T3 l = load12(li + (j - 1) * 12);
+            store12(plc + (NG + j - 1) * 12, parent == 0 ? l : compose(load12(plc + (NG + parent - 1) * 12), l));
+          }
+          __syncwarp();
+        }
+        if (tid == 0) { s_pos = 0; s_ilo = -INF; s_ihi = INF; s_smallest = 0; s_overflow = 0; s_stop = 0; }
+      }
+      __syncthreads();
+      DT_TICK(1);
+      // ---- C: oMg = oMi[joint] * placement ----
+      for (int g = tid; g < NG; g += DT_THREADS) {
+        const DevGeom& G = T.geoms[g];
+        store12(plc + g * 12, G.joint == 0 ? load12(G.P) : compose(load12(plc + (NG + G.joint - 1) * 12), load12(G.P)));
+      }
+      __syncthreads();
+      DT_TICK(2);
+
+      // ---- D / E: narrow phase of the flagged pairs, then the replay; a second stage when the replay meets a
+      //      covered pair that the reference evaluates after all ----
+      for (;;) {
+        for (int p = tid; p < NP; p += DT_THREADS) {
+          if ((state[p] & (ST_CAND | ST_DONE)) != ST_CAND) continue;
+          const DevBodyPair& B = T.bodypairs[p];
+          double dlb = INF;  // computeDistanceLowerBound (:175-198): pairs in order, the first collision reports
+          int hit = -1;
+          for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
+            const double d = pairLowerBound(T, T.bgpairs[gp], plc, 1, mv.vertices, cnt);
+            ++tests;
+            if (d <= HPPB200_COLLISION_THRESHOLD) { hit = gp; break; }
+            if (d < dlb) dlb = d;
+          }
+          if (hit >= 0) res[p] = make_double2((double)hit, -INF);
+          else {
+            double hd, ht;  // :72-85
+            if (dlb == INF) { hd = INF; ht = 0; }
+            else {
+              const double Vm = vmax[p];
+              hd = dlb / Vm;
+              ht = (Vm != 0) ? 2 * A.tol / Vm : INF;
+            }
+            res[p] = make_double2(t - (hd + ht), t + (hd + ht));
+          }
+          state[p] |= ST_DONE;
+        }
+        __syncthreads();
+        DT_TICK(3);
+        // validateIntervals in the current order.  (1) every thread lays the records out by order position;
+        // (2) one thread walks them: the running intersection is a serial dependence, so the walk is kept to a
+        // few selects per position (a valid_ pair is a pair with the result [0, L] and no cover);
+        // (3) the decisions are applied position-parallel below.
+        // Only the pairs that are not valid_ need a visit, plus the first valid_ one (it clips the running
+        // interval to [0, L]; the later ones change nothing).
+        for (int base = (s_pos & ~31) + (tid & ~31); base < NP; base += DT_THREADS) {
+          const int pos = base + (tid & 31);
+          bool nonValid = false, isValid = false;
+          if (pos >= s_pos && pos < NP) {
+            const int p = order[pos];
+            const uint8_t st = state[p];
+            double2 c = make_double2(INF, -INF), r = make_double2(0.0, L);
+            uint8_t f = PF_RESULT;
+            if (!(st & ST_VALID)) {
+              c = cover[p];
+              f = 0;
+              if (st & ST_DONE) { r = res[p]; f = (r.y == -INF) ? (PF_RESULT | PF_HIT) : PF_RESULT; }
+              nonValid = true;
+            } else isValid = true;
+            pcov[pos] = c; pres[pos] = r; pflag[pos] = f;
+          }
+          const unsigned nv = __ballot_sync(0xffffffffu, nonValid), vv = __ballot_sync(0xffffffffu, isValid);
+          if ((tid & 31) == 0) { visit[base >> 5] = nv; pflag[NP + (base >> 5)] = vv ? (uint8_t)(__ffs(vv)) : (uint8_t)0; }
+        }
+        __syncthreads();
+        if (tid == 0) {
+          int pos = s_pos, smallest = s_smallest, run = RUN_SAMPLE;
+          double ilo = s_ilo, ihi = s_ihi;
+          bool clipped = ilo >= 0.0 && ihi <= L;  // a valid_ pair was folded already
+          const int words = (NP + 31) >> 5;
+          int stop = NP;
+          for (int w = pos >> 5; w < words && run == RUN_SAMPLE; ++w) {
+            uint32_t m = visit[w];
+            const int fv = pflag[NP + w];  // 1 + lane of the first valid_ pair of this block, 0: none
+            if (fv && !clipped) { m |= 1u << (fv - 1); clipped = true; }
+            while (m) {
+              const int b = __ffs(m) - 1;
+              m &= m - 1u;
+              pos = (w << 5) + b;
+              const double2 c = pcov[pos], r = pres[pos];
+              const uint8_t f = pflag[pos];
+              const bool skip = c.x <= ilo && ihi <= c.y;  // icl::contains(validInterval_, running interval) (:56-63)
+              if (!skip && f != PF_RESULT) {  // evaluated by the reference: not computed yet, or in collision
+                if (f & PF_HIT) { finishEdge(false, HPPB200_REASON_COLLISION, t, dichLast(), (int)r.x); run = RUN_FINISHED; }
+                else run = RUN_STAGE;
+                stop = pos;
+                break;
+              }
+              pflag[pos] = skip ? PF_SKIP : PF_FOLD;
+              smallest = (!skip && ihi > r.y) ? pos : smallest;  // continuous-validation.hh:283
+              ilo = (!skip && ilo < r.x) ? r.x : ilo;
+              ihi = (!skip && r.y < ihi) ? r.y : ihi;
+            }
+          }
+          pos = stop;
+          s_stop = pos; s_smallest = smallest; s_ilo = ilo; s_ihi = ihi; s_run = run;
+        }
+        __syncthreads();
+        if (s_run == RUN_STAGE) {
+          // flag the pair the walk stopped at and every later pair that can still be evaluated (the running
+          // interval only shrinks, so a cover that contains it now is final); positions before it are decided
+          const double ilo = s_ilo, ihi = s_ihi;
+          for (int pos = s_stop + tid; pos < NP; pos += DT_THREADS) {
+            const int p2 = order[pos];
+            const uint8_t s2 = state[p2];
+            if (s2 & (ST_VALID | ST_DONE)) continue;
+            const double2 c2 = cover[p2];
+            if (!(c2.x <= ilo && ihi <= c2.y)) state[p2] = s2 | ST_CAND;
+          }
+        }
+        // decisions of the positions walked in this turn
+        for (int pos = s_pos + tid; pos < s_stop; pos += DT_THREADS) {
+          const int p = order[pos];
+          const uint8_t st = state[p];
+          if (st & ST_VALID) continue;
+          if (pflag[pos] == PF_SKIP) { if (st & ST_DONE) ++discarded; state[p] = 0; }
+          else state[p] = st | ST_INSERT;
+        }
+        __syncthreads();
+        if (tid == 0) s_pos = s_stop;
+        __syncthreads();
+        DT_TICK(4);
+        if (s_run != RUN_STAGE) break;
+        if (timing) ++s_ck[7];
+      }
+      if (s_run == RUN_FINISHED) break;
+
+      // ---- F: validInterval_.insert (:90), valid_ (:92-96) ----
+      for (int p = tid; p < NP; p += DT_THREADS) {
+        if (!(state[p] & ST_INSERT)) continue;
+        int c = lcnt[p];
+        double2* lst = lists + (size_t)p * K;
+        const double2 r = res[p];
+        if (!wdUnion(lst, 1, c, K, r.x, r.y)) { s_overflow = 1; continue; }
+        lcnt[p] = (uint16_t)c;
+        state[p] = wdContains(lst, 1, c, 0.0, L) ? ST_VALID : 0;
+      }
+      __syncthreads();
+      DT_TICK(5);
+      if (tid == 0) {
+        const double ilo = s_ilo, ihi = s_ihi;
+        int sc = s_subCnt;
+        bool over = s_overflow != 0;
+        if (!over) {
+          // src/continuous-validation.cc:144-146: smallest interval first
+          const int smallest = s_smallest;
+          if (NP > 1 && smallest != 0) { const uint16_t a0 = order[0]; order[0] = order[smallest]; order[smallest] = a0; }
+          over = !wdUnion(sub, 1, sc, DT_KS, ilo, ihi);  // dichotomy.cc:96-109
+        }
+        if (over) {
+          if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
+          finishEdge(false, A.overflow_reason, t, dichLast(), -1);
+          s_run = RUN_FINISHED;
+        } else {
+          s_subCnt = sc;
+          if (wdContains(sub, 1, sc, 0.0, L)) {
+            finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+            s_run = RUN_FINISHED;
+          } else {
+            double t0, t1;  // middle of the first non-validated gap
+            if (!reverse) { t0 = sub[0].y; t1 = sc > 1 ? sub[1].x : L; }
+            else { t0 = sub[sc - 1].x; t1 = sc > 1 ? sub[sc - 2].y : 0.0; }
+            s_t = .5 * (t0 + t1);
+            s_run = RUN_SAMPLE;
+          }
+        }
+      }
+      __syncthreads();
+      DT_TICK(6);
+      if (s_run == RUN_FINISHED) break;
+    }
+    __syncthreads();  // the edge's shared state is dead from here
+  }
+
+  if (timing)
+    for (int i = 0; i < 8; ++i) atomicAdd(A.clk + i, (unsigned long long)s_ck[i]);
+#undef DT_TICK
+  if (stats) {
+    if (tests) atomicAdd(&stats->pair_tests, (unsigned long long)tests);
+    if (cnt.iterations) atomicAdd(&stats->gjk_iterations, (unsigned long long)cnt.iterations);
+    if (cnt.cap_hits) atomicAdd(&stats->gjk_cap_hits, (unsigned long long)cnt.cap_hits);
+    if (samples) atomicAdd(&stats->edge_samples, (unsigned long long)samples);
+    if (caps) atomicAdd(&stats->iter_cap_hits, (unsigned long long)caps);
+    if (overflows) atomicAdd(&stats->overflow, (unsigned long long)overflows);
+    if (discarded) atomicAdd(&stats->discarded_tests, (unsigned long long)discarded);
+  }
+}
+
+// Runs Dichotomy on the edges of `d_list` (or on all n edges when d_list is null), one CTA per edge.  An edge whose
+// lists outgrow the capacity is reported with `overflow_reason` (counted in DeviceStats::overflow).  smemLists:
+// per-pair lists in shared memory (as many entries as DT_SMEM_LISTS holds, at most DT_K); else DT_K entries in global memory.
+bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
+                         const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
+                         uint8_t* d_reason, int overflow_reason, bool smemLists) {
+  const ModelView& mv = ws->view;
+  if (n == 0) return true;
+  if (mv.nbodypairs > 65535 || mv.nbodypairs == 0) return false;
+  int K = DT_K;
+  if (smemLists) {
+    K = std::min<int>(DT_K, (int)(DT_SMEM_LISTS / (16u * (uint32_t)mv.nbodypairs)));
+    if (K < 8) return false;
+  }
+  const TailLayout Lo = tailLayout(mv, smemLists ? K : 0);
+  if (Lo.total > 200u * 1024u) return false;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(dichTailKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Lo.total));
+  int perSM = 0;
+  HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, dichTailKernel, DT_THREADS, Lo.total));
+  if (perSM < 1) return false;
+  const size_t grid = std::min<size_t>(n, (size_t)ws->num_sms * (size_t)perSM);
+  const size_t listBytes = smemLists ? 0 : grid * (size_t)mv.nbodypairs * DT_K * sizeof(double2);
+  ws->d_tail.reserve(listBytes + 128);
+  const bool trace = std::getenv("HPPB200_WF_TRACE") != nullptr;
+  TailArgs A{};
+  A.q1 = d_q1; A.q2 = d_q2; A.L = d_L; A.edge_list = d_list; A.n = n;
+  A.reverse = reverse; A.tol = tol; A.max_iter = ws->max_iterations; A.overflow_reason = overflow_reason;
+  A.valid = d_valid; A.t_fail = d_tfail; A.t_last = d_tlast; A.pair = d_pair; A.reason = d_reason;
+  A.lists = smemLists ? nullptr : (double2*)ws->d_tail.p;
+  A.K = K;
+  A.counter = (unsigned long long*)(ws->d_tail.p + listBytes);
+  A.clk = trace ? A.counter + 1 : nullptr;
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(A.counter, 0, 9 * sizeof(unsigned long long), ws->stream));
+  dichTailKernel<<<(unsigned)grid, DT_THREADS, Lo.total, ws->stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 1;
+  if (trace) {
+    unsigned long long ck[8];
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ck, A.clk, sizeof(ck), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    std::fprintf(stderr, "[tail] n=%zu grid=%zu (%d per SM) K=%d %s smem=%u B; thread-0 Mcycles: A %.2f B %.2f C %.2f narrow %.2f replay %.2f insert %.2f next %.2f; second stages %llu\n",
+                 n, grid, perSM, K, smemLists ? "shared" : "global", Lo.total, ck[0] * 1e-6, ck[1] * 1e-6, ck[2] * 1e-6, ck[3] * 1e-6, ck[4] * 1e-6,
+                 ck[5] * 1e-6, ck[6] * 1e-6, ck[7]);
+  }
+  return true;
+}
+
+}  // namespace hppb200

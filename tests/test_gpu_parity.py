@@ -354,6 +354,44 @@ def test_humanoid_tree_convex_parity(pkg, ob, monkeypatch, name):
             assert 0.02 < r["valid"].mean() < 0.98
 
 
+@pytest.mark.parametrize("path", ["cta", "walker"])
+@pytest.mark.parametrize("reverse", [False, True])
+def test_dichotomy_cta_per_edge_parity(pkg, eng, ur5, ur5_oracle, golden_configs, monkeypatch, path, reverse):
+    """Dichotomy below the wavefront's batch size: the CTA-per-edge kernel (kernels_tail.cu: threads share one
+    sample, two-stage narrow phase, replay in the reference order) and, with HPPB200_TAIL=0, the lane-per-edge
+    walker.  Golden edges, long and short random edges, zero-length edges; all outputs bit-exact, and the
+    iteration cap is reported at the same sample."""
+    m, _ = eng
+    monkeypatch.setenv("HPPB200_WF_MIN", "100000000")
+    monkeypatch.setenv("HPPB200_TAIL", "1" if path == "cta" else "0")
+    monkeypatch.setenv("HPPB200_TAIL_MAX", "100000")
+    ws = pkg.Workspace(m, 0)
+    o = ur5_oracle
+    g1, g2 = golden_configs[0:200:2], golden_configs[1:200:2]
+    a1, a2, _ = _edges(pkg, ur5, o, 5000, 41)
+    b1, b2, _ = _edges(pkg, ur5, o, 3000, 42, short=True)
+    z = pkg.uniform_configs(ur5, 300, seed=43)
+    q1, q2 = np.concatenate([g1, a1, b1, z]), np.concatenate([g2, a2, b2, z])
+    L = o.straight_lengths(q1, q2)
+    s0 = ws.stats()
+    r = ws.validate_edges(2, 0.0, q1, q2, L, reverse=reverse)
+    s1 = ws.stats()
+    e = o.validate_edges(2, 0.0, q1, q2, L, reverse=reverse)
+    for k in ("valid", "reason", "pair", "t_last_valid"):
+        assert np.array_equal(r[k], e[k]), (path, reverse, k)
+    assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+    assert s1["iter_cap_hits"] == s0["iter_cap_hits"]
+    if path == "cta":  # one launch for the batch (+ at most the second pass for lists beyond 64 entries)
+        assert s1["kernel_launches"] - s0["kernel_launches"] <= 3
+    ws.set_max_iterations(7)
+    r = ws.validate_edges(2, 0.0, q1[:2000], q2[:2000], L[:2000], reverse=reverse)
+    e = o.validate_edges(2, 0.0, q1[:2000], q2[:2000], L[:2000], reverse=reverse, max_iter=7)
+    for k in ("valid", "reason", "pair", "t_last_valid"):
+        assert np.array_equal(r[k], e[k]), (path, reverse, k, "cap")
+    assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+    assert (r["reason"] == 3).any()
+
+
 @pytest.mark.parametrize("wf_min", ["1", "100000000"])
 def test_freeflyer_humanoid_parity(pkg, ob, monkeypatch, wf_min):
     """BASELINE configs[3] model WITH its free-flyer root (R^3 x SO(3), nq = 37, nv = 36): FK from the quaternion,

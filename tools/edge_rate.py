@@ -18,7 +18,7 @@ o = ob.Oracle(desc)
 q1 = pkg.uniform_configs(desc, n, seed=101)
 if step > 0:
     d = np.random.default_rng(5).normal(size=q1.shape)
-    q2 = np.clip(q1 + step * d / np.linalg.norm(d, axis=1, keepdims=True), desc.q_lower, desc.q_upper)
+    q2 = pkg.normalize_quaternions(desc, np.clip(q1 + step * d / np.linalg.norm(d, axis=1, keepdims=True), desc.q_lower, desc.q_upper))
 else:
     q2 = pkg.uniform_configs(desc, n, seed=102)
 L = ws.straight_lengths(q1, q2)
