@@ -163,7 +163,7 @@ struct Workspace {
   DeviceBuffer<unsigned char> d_state, d_tail;
   bool use_tail = true;        // Dichotomy: CTA-per-edge pass for handed-over edges (HPPB200_TAIL=0: walker large-list pass only)
   bool tail_smem = true;       // first CTA-per-edge pass keeps the per-pair lists in shared memory (HPPB200_TAIL_SMEM)
-  size_t tail_max = 8192;      // Dichotomy batches up to this size go to the CTA-per-edge kernel directly (HPPB200_TAIL_MAX)
+  size_t tail_max = ~size_t(0);      // Dichotomy batches up to this size that the wavefront engine does not take go to the CTA-per-edge kernel (HPPB200_TAIL_MAX)
   void syncStats();
 };
 

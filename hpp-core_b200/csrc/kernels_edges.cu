@@ -637,8 +637,9 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   bool engineDone = false;
   // Large batches: round-synchronous wavefront engine (kernels_wavefront.cu); its ~600 rounds of a few kernels
   // each are a fixed latency that small batches do not amortise, those go to the CTA engine.
-  // (Dichotomy's rounds are heavier and its tail longer: the break-even batch is about four times larger)
-  const size_t wfMin = method == HPPB200_METHOD_DICHOTOMY ? 4 * ws->wavefront_min : ws->wavefront_min;
+  // (Dichotomy: the CTA-per-edge kernel below takes the batches under 50 k edges and the wavefront's tail;
+  //  measured 200 k UR5 edges: wavefront 1.11 M edges/s, CTA per edge 0.64 M, walker 0.73 M; 50 k: 0.65 M vs 0.5 M)
+  const size_t wfMin = method == HPPB200_METHOD_DICHOTOMY ? ws->wavefront_min / 2 : ws->wavefront_min;
   if (method != HPPB200_METHOD_DISCRETIZED && ws->use_engine && ws->engine_kind >= 2 && n >= wfMin)
     engineDone = launchWavefront(ws, method, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair,
                                             d_reason, REASON_OVERFLOW_INTERNAL);
