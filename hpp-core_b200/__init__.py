@@ -50,7 +50,7 @@ ABI_SYMBOLS = [
     "hppb200_model_num_coefficients", "hppb200_model_get_coefficients", "hppb200_model_get_body_radii",
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
     "hppb200_validate_configs", "hppb200_geometry_placements", "hppb200_pair_distances",
-    "hppb200_straight_lengths", "hppb200_validate_edges", "hppb200_workspace_set_max_iterations",
+    "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_workspace_set_max_iterations",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_size",
     "hppb200_knn_query", "hppb200_knn_within_ball",
 ]
@@ -227,6 +227,16 @@ class Workspace:
                                               _p(L, _dp)))
         return L
 
+    def path_eval(self, q1, q2, L, t):
+        """StraightPath::impl_compute for many edges: the configuration of edge i at parameter t[i]."""
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.model.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.model.nq)
+        L, t = np.ascontiguousarray(L, np.float64), np.ascontiguousarray(t, np.float64)
+        q = np.zeros_like(q1)
+        _check(lib().hppb200_path_eval(self.h, _p(q1, _dp), _p(q2, _dp), _p(L, _dp), _p(t, _dp), C.c_size_t(q1.shape[0]),
+                                       C.c_uint32(0), _p(q, _dp)))
+        return q
+
     def validate_edges(self, method, param, q1, q2, L, reverse=False, check_bounds=False):
         q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.model.nq)
         q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.model.nq)
@@ -286,5 +296,6 @@ class NearestNeighbor:
         return [idx[i, :min(count[i], cap)].copy() for i in range(n)], count
 
 
+from .planners import BiRRTPlanner, EngineBackend, Roadmap  # noqa: E402,F401
 from .validators import (CollisionValidation, ConfigValidations, Dichotomy, Discretized,  # noqa: E402,F401
                          JointBoundValidation, Progressive, StraightPath, ValidationReport)

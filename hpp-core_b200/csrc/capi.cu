@@ -287,6 +287,29 @@ int hppb200_straight_lengths(hppb200_workspace* wsp, const double* q1, const dou
   });
 }
 
+int hppb200_path_eval(hppb200_workspace* wsp, const double* q1, const double* q2, const double* L, const double* t, size_t n,
+                      uint32_t flags, double* q) {
+  return guarded([&] {
+    if (!wsp || (n && (!q1 || !q2 || !L || !t || !q))) throw std::invalid_argument("null argument");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq;
+    if (flags & HPPB200_DEVICE_POINTERS) { launchPathEval(ws, q1, q2, L, t, n, q); HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream)); return; }
+    ws->d_q.reserve(n * nq);
+    ws->d_q2.reserve(n * nq);
+    ws->d_L.reserve(n);
+    ws->d_tfail.reserve(n);
+    ws->d_scratch.reserve(n * nq);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q1, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q2.p, q2, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_L.p, L, n * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_tfail.p, t, n * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchPathEval(ws, ws->d_q.p, ws->d_q2.p, ws->d_L.p, ws->d_tfail.p, n, ws->d_scratch.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(q, ws->d_scratch.p, n * nq * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  });
+}
+
 int hppb200_validate_edges(hppb200_workspace* wsp, int method, double param, int reverse, const double* q1,
                            const double* q2, const double* L, size_t n, uint32_t flags, uint8_t* valid, double* t_fail,
                            double* t_last_valid, int32_t* pair, uint8_t* reason) {

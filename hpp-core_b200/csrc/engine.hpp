@@ -176,6 +176,7 @@ void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t 
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg);
 void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_dist);
 void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2, size_t n, double* d_L);
+void launchPathEval(Workspace* ws, const double* d_q1, const double* d_q2, const double* d_L, const double* d_t, size_t n, double* d_q);
 bool launchProgressiveEngine(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
                              const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                              int32_t* d_pair, uint8_t* d_reason, int overflow_reason);

@@ -534,6 +534,31 @@ __global__ void straightLengthsKernel(ModelView mv, const double* __restrict__ q
   L[i] = sqrt(res);
 }
 
+// Path::eval -> StraightPath::impl_compute (reference src/straight-path.cc:91-110), one thread per edge
+__global__ void pathEvalKernel(ModelView mv, const double* __restrict__ q1, const double* __restrict__ q2,
+                               const double* __restrict__ L, const double* __restrict__ t, size_t n, double* __restrict__ q) {
+  const Tables T = makeTables(mv.blob, mv);
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const EdgeQ eq = edgeQ(q1 + i * (size_t)mv.nq, q2 + i * (size_t)mv.nq, t[i], L[i]);
+  double* out = q + i * (size_t)mv.nq;
+  for (int j = 0; j < mv.njoints; ++j) {
+    const DevJoint& J = T.joints[j];
+    if (J.type == HPPB200_JOINT_FREEFLYER) {
+      double f[7];
+      eq.freeflyer(J.idx_q, f);
+      for (int k = 0; k < 7; ++k) out[J.idx_q + k] = f[k];
+    } else out[J.idx_q] = eq(J.idx_q);
+  }
+}
+
+void launchPathEval(Workspace* ws, const double* d_q1, const double* d_q2, const double* d_L, const double* d_t, size_t n, double* d_q) {
+  if (n == 0) return;
+  pathEvalKernel<<<(unsigned)((n + 255) / 256), 256, 0, ws->stream>>>(ws->view, d_q1, d_q2, d_L, d_t, n, d_q);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 1;
+}
+
 void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2, size_t n, double* d_L) {
   if (n == 0) return;
   const unsigned grid = (unsigned)((n + 255) / 256);

@@ -44,8 +44,13 @@ class StraightPath:
     def timeRange(self):
         return (0.0, self.length)
 
-    def extract(self, t0, t1):
-        """StraightPath::impl_extract (src/straight-path.cc:142-158): end points by interpolation."""
+    def extract(self, t0, t1, workspace=None):
+        """StraightPath::impl_extract (src/straight-path.cc:142-158): a new path between eval(t0) and eval(t1).
+        With a workspace the two configurations come from hppb200_path_eval (any joint type); without one the
+        interpolation is done here and is only right for vector-space joints."""
+        if workspace is not None:
+            q = workspace.path_eval([self.initial, self.initial], [self.end, self.end], [self.length] * 2, [t0, t1])
+            return StraightPath(q[0], q[1], abs(t1 - t0))
         def at(t):
             if t == 0.0 or self.length == 0.0:
                 return self.initial.copy()
@@ -130,7 +135,7 @@ class _PathValidator:
         if r["valid"][0]:
             return True, path, None
         tl = float(r["t_last_valid"][0])
-        part = path.extract(tl, path.length) if reverse else path.extract(0.0, tl)
+        part = path.extract(tl, path.length, self.ws) if reverse else path.extract(0.0, tl, self.ws)
         return False, part, ValidationReport(r["reason"][0], r["pair"][0], parameter=float(r["t_fail"][0]))
 
     def validate_config(self, q):

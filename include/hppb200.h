@@ -23,6 +23,9 @@
  *                                 (src/steering-method/straight.cc:38-51) /
  *                                 WeighedDistance::impl_distance
  *                                 (src/weighed-distance.cc:272-289)
+ *   hppb200_path_eval          <- Path::eval (include/hpp/core/path.hh:135-140) ->
+ *                                 StraightPath::impl_compute (src/straight-path.cc:91-110),
+ *                                 which StraightPath::impl_extract (:142-158) is built on
  *   hppb200_knn_*              <- nearestNeighbor::Basic::{search,KnearestSearch,
  *                                 withinBall} (src/nearest-neighbor/basic.cc:52-181)
  *   hppb200_model_*            <- ObstacleUser::{addRobotCollisionPairs,addObstacle,
@@ -232,6 +235,12 @@ int hppb200_pair_distances(hppb200_workspace* ws, const double* q, size_t n,
 /* L[i] = WeighedDistance(q1[i], q2[i]) (steeringMethod::Straight). */
 int hppb200_straight_lengths(hppb200_workspace* ws, const double* q1,
                              const double* q2, size_t n, uint32_t flags, double* L);
+
+/* q[i] = configuration of edge i at parameter t[i] in [0, L[i]]: the stored end points bit-exactly at
+   t = 0 / t = L (and for L = 0), LiegroupSpace::interpolate(q1, q2, t / L) otherwise (R^n joints linear,
+   free-flyer R^3 x SO(3)).  The adapter builds validPart = extract(0, t_last_valid) from it. */
+int hppb200_path_eval(hppb200_workspace* ws, const double* q1, const double* q2, const double* L,
+                      const double* t, size_t n, uint32_t flags, double* q);
 
 /* Edge i is the StraightPath from q1[i] to q2[i] over [0, L[i]].
    valid [n]; t_fail [n] report->parameter (NaN when valid); t_last_valid [n] end of

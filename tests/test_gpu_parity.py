@@ -426,6 +426,34 @@ def test_freeflyer_humanoid_parity(pkg, ob, monkeypatch, wf_min):
             assert 0.02 < r["valid"].mean() < 0.98
 
 
+@pytest.mark.parametrize("name", ["ur5_boxes8.json", "humanoid_ff_obst6.json"])
+def test_path_eval_and_valid_part(pkg, ob, name):
+    """Path::eval / StraightPath::impl_compute for many edges (hppb200_path_eval) against the oracle, end points
+    included, and the adapter's validPart = extract(0, t_last_valid) built from it (src/straight-path.cc:142-158)."""
+    desc = pkg.ModelDescription.load(name)
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    o = ob.Oracle(desc)
+    q1, q2 = pkg.uniform_configs(desc, 3000, seed=97), pkg.uniform_configs(desc, 3000, seed=98)
+    L = o.straight_lengths(q1, q2)
+    L[::7] = 0.0
+    u = np.random.default_rng(99).uniform(size=len(L))
+    u[::5] = 0.0
+    u[1::5] = 1.0
+    t = u * L
+    assert np.array_equal(ws.path_eval(q1, q2, L, t), o.interpolate(q1, q2, L, t))
+    L = o.straight_lengths(q1, q2)
+    pv = pkg.Progressive.create(ws, 1e-3)
+    e = o.validate_edges(1, 1e-3, q1[:200], q2[:200], L[:200])
+    checked = 0
+    for i in np.nonzero(e["valid"] == 0)[0][:20]:
+        ok, part, rep = pv.validate(pkg.StraightPath(q1[i], q2[i], L[i]))
+        assert not ok and rep.parameter == e["t_fail"][i] and part.length == e["t_last_valid"][i]
+        assert np.array_equal(part.initial, q1[i])
+        assert np.array_equal(part.end, o.interpolate(q1[i], q2[i], L[i:i + 1], e["t_last_valid"][i:i + 1])[0])
+        checked += 1
+    assert checked > 0
+
+
 def test_freeflyer_knn_parity(pkg, ob):
     """WeighedDistance k-NN over free-flyer configurations: translation unweighted + w^2 |log3(q_node^-1 q)|^2."""
     desc = pkg.ModelDescription.load("humanoid_ff_obst6.json")
@@ -492,3 +520,56 @@ def test_wavefront_dichotomy_other_scenes(pkg, ob, monkeypatch, name):
         for k in ("valid", "reason", "pair", "t_last_valid"):
             assert np.array_equal(r[k], e[k]), (name, rev, k)
         assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+
+
+class _OracleBackend:
+    """The same five calls as EngineBackend, answered by the CPU oracle (test infrastructure)."""
+
+    def __init__(self, o, method, param):
+        self.o, self.method, self.param = o, method, param
+
+    def append(self, q, cc):
+        self.o.knn_append(np.asarray(q, np.float64).reshape(1, -1), np.asarray([cc], np.int32))
+
+    def relabel(self, old, new):
+        self.o.knn_relabel(old, new)
+
+    def nearest(self, qs, cc):
+        idx, dist = self.o.knn_query(qs, 1, cc)
+        return idx[:, 0], dist[:, 0]
+
+    def lengths(self, q1, q2):
+        return self.o.straight_lengths(q1, q2)
+
+    def validate(self, q1, q2, L, reverse):
+        r = self.o.validate_edges(self.method, self.param, q1, q2, L, reverse=reverse)
+        return r["valid"].astype(bool), r["t_last_valid"]
+
+    def path_eval(self, q1, q2, L, t):
+        return self.o.interpolate(q1, q2, L, t)
+
+
+@pytest.mark.parametrize("name,method,param,batch", [("ur5_boxes8.json", 1, 1e-3, 0), ("ur5_boxes8.json", 2, 0.0, 0),
+                                                     ("ur5_boxes32.json", 1, 1e-3, 16), ("humanoid_ff_obst6.json", 1, 1e-3, 8)])
+def test_birrt_end_to_end_same_roadmap(pkg, ob, name, method, param, batch):
+    """BASELINE configs[2]: BiRRT (control flow of src/bi-rrt-planner.cc:109-170) on top of the engine's path
+    validation, straight-path lengths, path evaluation and nearest neighbour, next to the same planner on the
+    oracle: same seed => the same roadmap node for node and edge for edge, the same number of steps, and a
+    solution whose every edge the oracle validates."""
+    desc = pkg.ModelDescription.load(name)
+    o = ob.Oracle(desc)
+    cand = pkg.uniform_configs(desc, 400, seed=5)
+    free = cand[o.validate_configs(cand)[0] == 1]
+    q_init, q_goal = free[0], free[1]
+    gpu = pkg.BiRRTPlanner(pkg.EngineBackend(pkg, pkg.Model(desc), 0, method, param), desc, q_init, q_goal, seed=11)
+    cpu = pkg.BiRRTPlanner(_OracleBackend(ob.Oracle(desc), method, param), desc, q_init, q_goal, seed=11)
+    sg, sc = gpu.solve(max_steps=300, batch=batch), cpu.solve(max_steps=300, batch=batch)
+    assert sg == sc and gpu.solved() == cpu.solved()
+    assert np.array_equal(gpu.roadmap.nodes, cpu.roadmap.nodes)
+    assert gpu.roadmap.edges == cpu.roadmap.edges and gpu.roadmap.cc == cpu.roadmap.cc
+    assert len(gpu.roadmap.cc) > 4
+    if gpu.solved():
+        path = gpu.path()
+        assert path[0] == gpu.init and path[-1] == gpu.goal and path == cpu.path()
+        a, b = gpu.roadmap.nodes[path[:-1]], gpu.roadmap.nodes[path[1:]]
+        assert o.validate_edges(0, 0.05, a, b, o.straight_lengths(a, b))["valid"].all()
