@@ -364,21 +364,37 @@ def run_b200(args):
         # secondary metric: nearestNeighbor::Basic over a 1M-node roadmap mirror (BASELINE configs[2]); wall clock
         # through the C ABI with host pointers (query upload + result download inside), median of 20 calls
         nn = pkg.NearestNeighbor(model, local_rank)
+        os.environ["HPPB200_KNN_TC"] = "0"  # a second mirror restricted to the exact FP64 scan, for comparison
+        nn_exact = pkg.NearestNeighbor(model, local_rank)
+        del os.environ["HPPB200_KNN_TC"]
         n_nodes = 1 << 20
         nn.append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
+        nn_exact.append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
         knn = {"nodes": n_nodes, "unit": "queries/s", "bytes_per_node": 8 * nq}
-        for label, nqr, kk, reps in (("q1_k1", 1, 1, 20), ("q1_k10", 1, 10, 20), ("q1024_k1", 1024, 1, 5), ("q1024_k10", 1024, 10, 3)):
+        for label, obj, nqr, kk, reps in (("q1_k1", nn, 1, 1, 20), ("q1_k10", nn, 1, 10, 20), ("q1024_k1", nn, 1024, 1, 9),
+                                          ("q1024_k10", nn, 1024, 10, 9), ("q8192_k10", nn, 8192, 10, 5),
+                                          ("q1024_k1_exact_scan", nn_exact, 1024, 1, 5),
+                                          ("q1024_k10_exact_scan", nn_exact, 1024, 10, 3)):
             qs = pkg.uniform_configs(desc, nqr, seed=SEED + 3)
-            nn.query(qs, kk)
+            ref_idx, ref_dd = obj.query(qs, kk)
             ts = []
             for _ in range(reps):
                 t0 = time.perf_counter()
-                idx, dd = nn.query(qs, kk)
+                idx, dd = obj.query(qs, kk)
                 ts.append(time.perf_counter() - t0)
             tm = sorted(ts)[len(ts) // 2]
-            knn[label] = {"value": nqr / tm, "ms_per_call": tm * 1e3,
-                          "scan_passes": 1 if kk <= 32 else kk,
-                          "node_stream_gbs": n_nodes * 8 * nq * (1 if kk <= 32 else kk) * ((nqr + 3) // 4) / tm / 1e9}
+            st = obj.tc_stats()
+            knn[label] = {"value": nqr / tm, "ms_per_call": tm * 1e3}
+            if st["used"]:  # tcgen05 TF32 candidate pass + exact FP64 re-rank (kernels_knn_tc.cu)
+                knn[label].update({"path": "tcgen05 tf32 candidate pass + fp64 re-rank", "prefix_stages": st["stages"],
+                                   "candidates_per_query": st["candidates"] / nqr, "queries_redone_by_exact_scan": st["redone"]})
+            else:
+                knn[label].update({"path": "exact fp64 scan", "scan_passes": 1 if kk <= 32 else kk,
+                                   "node_stream_gbs": n_nodes * 8 * nq * (1 if kk <= 32 else kk) * ((nqr + 3) // 4) / tm / 1e9})
+            if label.endswith("_exact_scan"):  # both paths return the same bits
+                ti, td = nn.query(qs, kk)
+                knn[label]["identical_to_tensor_core_path"] = bool(np.array_equal(ti, idx) and np.array_equal(td, dd))
+        del nn_exact
         if not args.no_cpu:
             orc.knn_append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
             qs = pkg.uniform_configs(desc, 64, seed=SEED + 3)

@@ -52,7 +52,7 @@ ABI_SYMBOLS = [
     "hppb200_validate_configs", "hppb200_geometry_placements", "hppb200_pair_distances",
     "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_workspace_set_max_iterations",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_size",
-    "hppb200_knn_query", "hppb200_knn_within_ball",
+    "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_debug_tile",
 ]
 
 _LIB = None
@@ -286,6 +286,19 @@ class NearestNeighbor:
         _check(lib().hppb200_knn_query(self.h, _p(queries, _dp), C.c_size_t(n), C.c_int(k), C.c_int32(cc),
                                        C.c_uint32(0), _p(idx, _i64p), _p(dist, _dp)))
         return idx, dist
+
+    def tc_stats(self):
+        """(used, stages, queries redone exactly, candidates of the last stage) of the last query."""
+        out = np.zeros(4, np.int64)
+        _check(lib().hppb200_knn_tc_stats(self.h, _p(out, _i64p)))
+        return dict(used=bool(out[0]), stages=int(out[1]), redone=int(out[2]), candidates=int(out[3]))
+
+    def tc_debug_tile(self, queries, swap_offsets=0):
+        queries = np.ascontiguousarray(queries, np.float64).reshape(-1, self.model.nq)
+        out = np.zeros((128, 256), np.float32)
+        _check(lib().hppb200_knn_tc_debug_tile(self.h, _p(queries, _dp), C.c_size_t(queries.shape[0]),
+                                                 C.c_int(swap_offsets), out.ctypes.data_as(C.c_void_p)))
+        return out
 
     def within_ball(self, queries, radius, cc=-1, cap=4096):
         queries = np.ascontiguousarray(queries, np.float64).reshape(-1, self.model.nq)

@@ -11,72 +11,11 @@
 #include <cstring>
 
 #include "dev_model.cuh"
-
-struct hppb200_knn {
-  const hppb200::Model* model = nullptr;
-  int device = 0;
-  hppb200::ModelView view;
-  cudaStream_t stream = nullptr;
-  double* d_nodes = nullptr;  // [cap][nq]
-  int32_t* d_cc = nullptr;
-  size_t n = 0, cap = 0;
-  hppb200::DeviceBuffer<double> d_queries, d_dist;
-  hppb200::DeviceBuffer<long long> d_idx, d_count;
-  hppb200::DeviceBuffer<unsigned char> d_keys;  // previous keys [Q] + per-tile partial keys [tiles][Q]
-  int num_sms = 148;
-};
+#include "dev_knn.cuh"
 
 namespace hppb200 {
 
 constexpr int KNN_THREADS = 256;
-
-__device__ __forceinline__ double weighedDistanceDev(const Tables& T, const ModelView& mv, const double* __restrict__ a,
-                                                     const double* __restrict__ b) {
-  double res = 0;
-  for (int j = 0; j < mv.njoints; ++j) {
-    const DevJoint& J = T.joints[j];
-    const double w = T.weights[j];
-    const double w2 = w * w;
-    if (J.type == HPPB200_JOINT_FREEFLYER) { res += ffSquaredDistance(a + J.idx_q, b + J.idx_q, w2); continue; }
-    const double dq = b[J.idx_q] - a[J.idx_q];
-    res += (J.type <= HPPB200_JOINT_REVOLUTE_Z) ? w2 * (dq * dq) : dq * dq;
-  }
-  return sqrt(res);
-}
-
-// WeighedDistance of one node to KNN_QB queries at once: the node entry, the joint record and w^2 are loaded once
-// per joint; per query the operation sequence is the one of weighedDistanceDev (same bits).  `sq` holds the
-// queries in shared memory, `sw2` the per-joint w * w.
-template <int QB, bool FF>
-__device__ __forceinline__ void weighedDistanceBatch(const Tables& T, const ModelView& mv, const double* __restrict__ node,
-                                                     const double* sq, const double* sw2, double (&d)[QB]) {
-#pragma unroll
-  for (int q = 0; q < QB; ++q) d[q] = 0;
-  for (int j = 0; j < mv.njoints; ++j) {
-    const DevJoint& J = T.joints[j];
-    const double w2 = sw2[j];
-    if (FF && J.type == HPPB200_JOINT_FREEFLYER) {  // distance(node, query): the argument order of nearestNeighbor::Basic
-#pragma unroll
-      for (int q = 0; q < QB; ++q) d[q] += ffSquaredDistance(node + J.idx_q, sq + q * mv.nq + J.idx_q, w2);
-      continue;
-    }
-    const double a = node[J.idx_q];
-    const bool rev = J.type <= HPPB200_JOINT_REVOLUTE_Z;
-#pragma unroll
-    for (int q = 0; q < QB; ++q) {
-      const double dq = sq[q * mv.nq + J.idx_q] - a;
-      d[q] += rev ? w2 * (dq * dq) : dq * dq;
-    }
-  }
-#pragma unroll
-  for (int q = 0; q < QB; ++q) d[q] = sqrt(d[q]);
-}
-
-struct Key {
-  double d;
-  long long i;
-};
-__device__ __forceinline__ bool keyLess(const Key& a, const Key& b) { return a.d < b.d || (a.d == b.d && a.i < b.i); }
 
 // ---- tiled scan: the whole GPU works on every query -------------------------------------------------
 // Grid (node tiles, query groups): a CTA scans ITS contiguous slice of the node stream once per selection
@@ -185,16 +124,6 @@ __global__ void knnInitPrevKernel(Key* prev, int nqueries) {
 // memory, CTAs (tiles) by knnMergeTopkKernel.  Keys are (distance, node index), so the result is the reference's
 // K-nearest SET (strict '>' against the heap top keeps the earlier node, basic.cc:106) in the engine's
 // documented order (ties by node index).
-__device__ __forceinline__ void topkInsert(Key& mine, Key& kth, const Key x, int k, int lane) {
-  const unsigned FULL = 0xffffffffu;
-  const bool gt = keyLess(x, mine);  // monotone over the lanes: true from the insertion point on
-  const unsigned g = __ballot_sync(FULL, gt);
-  const Key up = {__shfl_up_sync(FULL, mine.d, 1), __shfl_up_sync(FULL, mine.i, 1)};
-  if (gt) mine = (lane > 0 && ((g >> (lane - 1)) & 1u)) ? up : x;
-  kth.d = __shfl_sync(FULL, mine.d, k - 1);
-  kth.i = __shfl_sync(FULL, mine.i, k - 1);
-}
-
 template <bool FF>
 __global__ void __launch_bounds__(KNN_THREADS)
 knnTileTopkKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __restrict__ cc, size_t n,
@@ -333,6 +262,40 @@ __global__ void relabelKernel(int32_t* cc, size_t n, int32_t from, int32_t to) {
   if (i < n && cc[i] == from) cc[i] = to;
 }
 
+// exact scan of the first nNodes nodes: k selection passes or the single-pass top-k (see the kernels above)
+void knnExactRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, int32_t cc, size_t nNodes, long long* d_i,
+                 double* d_d) {
+  const size_t nq = (size_t)nn->model->nq;
+  const size_t smemBytes = 16 + nn->view.blob_bytes + ((size_t)KNN_QB * nq + (size_t)nn->model->njoints) * sizeof(double);
+  const bool ff = nn->ff;
+  auto tileKernel = ff ? knnTileKernel<true> : knnTileKernel<false>;
+  auto topkKernel = ff ? knnTileTopkKernel<true> : knnTileTopkKernel<false>;
+  const unsigned groups = (unsigned)((nqueries + KNN_QB - 1) / KNN_QB);
+  size_t tiles = std::max<size_t>(1, std::min<size_t>((size_t)nn->num_sms * 4, (nNodes + KNN_THREADS - 1) / KNN_THREADS));
+  if (groups > 64) tiles = std::max<size_t>(1, std::min<size_t>(tiles, (size_t)nn->num_sms / 2));  // many groups fill the GPU anyway
+  if (k > 1 && k <= 32) {  // single pass (k = 1 is one selection pass anyway, without the insertion logic)
+    nn->d_keys.reserve(tiles * nqueries * (size_t)k * sizeof(Key) + 256);
+    Key* d_part = (Key*)nn->d_keys.p;
+    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(topkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+    topkKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nNodes, d_q,
+                                                                                        (int)nqueries, cc, k, d_part);
+    knnMergeTopkKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, d_i, d_d);
+    HPPB200_CUDA_CHECK(cudaGetLastError());
+    return;
+  }
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(tileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+  nn->d_keys.reserve((nqueries + tiles * nqueries) * sizeof(Key) + 256);
+  Key* d_prev = (Key*)nn->d_keys.p;
+  Key* d_part = d_prev + nqueries;
+  knnInitPrevKernel<<<(unsigned)((nqueries + 255) / 256), 256, 0, nn->stream>>>(d_prev, (int)nqueries);
+  for (int r = 0; r < k; ++r) {
+    tileKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nNodes, d_q,
+                                                                                    (int)nqueries, cc, d_prev, d_part);
+    knnReduceKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, r, d_prev, d_i, d_d);
+  }
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+}
+
 void setLastError(const std::string& s);
 
 template <typename F>
@@ -361,6 +324,8 @@ int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out) {
     nn->view = nn->model->deviceView(device);
     HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&nn->stream, cudaStreamNonBlocking));
     HPPB200_CUDA_CHECK(cudaDeviceGetAttribute(&nn->num_sms, cudaDevAttrMultiProcessorCount, device));
+    for (const DevJoint& J : nn->model->joints) nn->ff = nn->ff || J.type == HPPB200_JOINT_FREEFLYER;
+    knnTcInit(nn);
     *out = nn;
   });
 }
@@ -369,6 +334,7 @@ void hppb200_knn_destroy(hppb200_knn* nn) {
   cudaSetDevice(nn->device);
   if (nn->d_nodes) cudaFree(nn->d_nodes);
   if (nn->d_cc) cudaFree(nn->d_cc);
+  knnTcDestroy(nn);
   if (nn->stream) cudaStreamDestroy(nn->stream);
   delete nn;
 }
@@ -420,37 +386,10 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
     HPPB200_CUDA_CHECK(cudaSetDevice(nn->device));
     const size_t nq = (size_t)nn->model->nq;
     if (nqueries > 0x7fffffffull / 4) throw std::invalid_argument("too many queries in one call");
-    const size_t smemBytes = 16 + nn->view.blob_bytes + ((size_t)KNN_QB * nq + (size_t)nn->model->njoints) * sizeof(double);
-    bool ff = false;
-    for (const DevJoint& J : nn->model->joints) ff = ff || J.type == HPPB200_JOINT_FREEFLYER;
-    auto tileKernel = ff ? knnTileKernel<true> : knnTileKernel<false>;
-    auto topkKernel = ff ? knnTileTopkKernel<true> : knnTileTopkKernel<false>;
-    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(tileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
     auto run = [&](const double* d_q, long long* d_i, double* d_d) {
-      // k selection passes, each = tiled scan on the whole GPU + merge of the tiles (see knnTileKernel)
-      const unsigned groups = (unsigned)((nqueries + KNN_QB - 1) / KNN_QB);
-      size_t tiles = std::max<size_t>(1, std::min<size_t>((size_t)nn->num_sms * 4, (nn->n + KNN_THREADS - 1) / KNN_THREADS));
-      if (groups > 64) tiles = std::max<size_t>(1, std::min<size_t>(tiles, (size_t)nn->num_sms / 2));  // many groups fill the GPU anyway
-      if (k > 1 && k <= 32) {  // single pass (k = 1 is one selection pass anyway, without the insertion logic)
-        nn->d_keys.reserve(tiles * nqueries * (size_t)k * sizeof(Key) + 256);
-        Key* d_part = (Key*)nn->d_keys.p;
-        HPPB200_CUDA_CHECK(cudaFuncSetAttribute(topkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-        topkKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
-                                                                                            (int)nqueries, cc, k, d_part);
-        knnMergeTopkKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, d_i, d_d);
-        HPPB200_CUDA_CHECK(cudaGetLastError());
-        return;
-      }
-      nn->d_keys.reserve((nqueries + tiles * nqueries) * sizeof(Key) + 256);
-      Key* d_prev = (Key*)nn->d_keys.p;
-      Key* d_part = d_prev + nqueries;
-      knnInitPrevKernel<<<(unsigned)((nqueries + 255) / 256), 256, 0, nn->stream>>>(d_prev, (int)nqueries);
-      for (int r = 0; r < k; ++r) {
-        tileKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, d_q,
-                                                                                        (int)nqueries, cc, d_prev, d_part);
-        knnReduceKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, r, d_prev, d_i, d_d);
-      }
-      HPPB200_CUDA_CHECK(cudaGetLastError());
+      nn->tc_last_used = false;
+      if (knnTcEligible(nn, nqueries, k, cc)) knnTcRun(nn, d_q, nqueries, k, d_i, d_d);
+      else knnExactRun(nn, d_q, nqueries, k, cc, nn->n, d_i, d_d);
     };
     if (flags & HPPB200_DEVICE_POINTERS) {
       run(queries, (long long*)idx, dist);

@@ -268,6 +268,19 @@ size_t hppb200_knn_size(const hppb200_knn* nn);
    nearest first (-1 padded), dist [nqueries][k]. */
 int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries,
                       int k, int32_t cc, uint32_t flags, int64_t* idx, double* dist);
+/* hppb200_knn_query takes the tensor-core candidate pass (tcgen05 TF32 GEMM of the query tile against the node
+   stream + exact FP64 re-rank of the survivors; same indices and distances as the exact scan, bit for bit) when
+   the model is a vector space (no free-flyer, 3 nq + 4 <= 48), cc < 0, k <= 32, the mirror holds >= 16384 nodes
+   and the call carries >= 32 queries (env HPPB200_KNN_TC = 0 disables it, HPPB200_KNN_TC_MIN sets the query
+   count); otherwise the exact FP64 scan.  Both replace nearestNeighbor::Basic::KnearestSearch
+   (reference src/nearest-neighbor/basic.cc:84-126).
+   Statistics of the last query: out[0] 1 if the tensor-core pass ran, out[1] prefix stages, out[2] queries redone
+   by the exact scan (candidate list overflow), out[3] candidates re-ranked in the last stage. */
+int hppb200_knn_tc_stats(hppb200_knn* nn, int64_t* out /* [4] */);
+/* Test hook: approximate squared distances (the TMEM accumulator) of up to 128 queries against the first 256
+   nodes, out [128][256] row-major FP32; swap_offsets != 0 exchanges the descriptor byte offsets (bring-up). */
+int hppb200_knn_tc_debug_tile(hppb200_knn* nn, const double* queries, size_t nqueries, int swap_offsets,
+                              float* out);
 /* count [nqueries]; idx [nqueries][cap] in scan order (strict d < radius). */
 int hppb200_knn_within_ball(hppb200_knn* nn, const double* queries, size_t nqueries,
                             double radius, int32_t cc, size_t cap, int64_t* idx,

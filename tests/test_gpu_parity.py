@@ -237,6 +237,104 @@ def test_knn_parity(pkg, eng, ur5, ob):
     assert np.all(gi[:, 3:] == -1) and np.all(np.isinf(gd[:, 3:]))
 
 
+def _exact_nn(pkg, m, monkeypatch):
+    """A mirror with the tensor-core candidate pass switched off (exact FP64 scan only)."""
+    monkeypatch.setenv("HPPB200_KNN_TC", "0")
+    nn = pkg.NearestNeighbor(m, 0)
+    monkeypatch.delenv("HPPB200_KNN_TC")
+    return nn
+
+
+def test_knn_tensor_core_tile_error_bound(pkg, eng, ur5):
+    """The TMEM accumulator of the tcgen05 TF32 GEMM IS the approximate squared WeighedDistance: its error against
+    FP64 must stay far below the bound eps = 2^-16 (|a|^2 + max |b|^2) the thresholds are inflated by."""
+    m, _ = eng
+    nn = pkg.NearestNeighbor(m, 0)
+    nodes = pkg.uniform_configs(ur5, 20000, seed=91)
+    qs = pkg.uniform_configs(ur5, 100, seed=92)
+    nn.append(nodes)
+    w = np.asarray(ur5.weights)
+    ref = (((qs[:, None, :] - nodes[None, :256, :]) * w) ** 2).sum(-1)
+    tile = nn.tc_debug_tile(qs)[:100]
+    na, nb = ((qs * w) ** 2).sum(-1), ((nodes * w) ** 2).sum(-1).max()
+    eps = (na + nb) * 2.0 ** -16
+    assert np.all(np.abs(tile - ref) < 0.25 * eps[:, None])
+    assert np.all(nn.tc_debug_tile(qs)[100:] > 1e29)  # padding rows never pass a threshold
+
+
+def test_knn_tensor_core_pass_matches_exact_scan_and_oracle(pkg, eng, ur5, ob, monkeypatch):
+    """k-NN indices and distances of the tensor-core candidate pass + FP64 re-rank: identical to the exact scan
+    (1 <= k <= 32, ragged query counts, roadmap growing between queries, duplicates) and to the oracle."""
+    m, _ = eng
+    nn, ex = pkg.NearestNeighbor(m, 0), _exact_nn(pkg, m, monkeypatch)
+    o = ob.Oracle(ur5)
+    nodes = pkg.uniform_configs(ur5, 300000, seed=93)
+    nodes[250000] = nodes[77]
+    qs = pkg.uniform_configs(ur5, 333, seed=94)
+    qs[5] = nodes[77]
+    qs[6] = nodes[299999]
+    done = 0
+    for upto in (20000, 20001, 70000, 300000):  # appends between queries: the operand tiles follow the mirror
+        nn.append(nodes[done:upto]); ex.append(nodes[done:upto]); o.knn_append(nodes[done:upto], None)
+        done = upto
+        for k, nqry in ((1, 333), (10, 333), (32, 40), (7, 129)):
+            gi, gd = nn.query(qs[:nqry], k)
+            st = nn.tc_stats()
+            assert st["used"] and st["redone"] == 0, st
+            ei, ed = ex.query(qs[:nqry], k)
+            assert not ex.tc_stats()["used"]
+            assert np.array_equal(gi, ei), (upto, k)
+            assert np.array_equal(gd, ed), (upto, k)
+            assert st["candidates"] < 400 * k * nqry  # the filter does filter
+        gi, gd = nn.query(qs[:64], 10)
+        oi, od = o.knn_query(qs[:64], 10, -1)
+        srt = np.lexsort((oi, od), axis=1)
+        assert np.array_equal(gi, np.take_along_axis(oi, srt, axis=1))
+        assert np.array_equal(gd, np.take_along_axis(od, srt, axis=1))
+    assert nn.query(qs[:32], 1)[0][5, 0] == 77  # the earlier of two identical nodes
+    # below the query / node thresholds and with a connected-component filter the exact scan runs
+    nn.query(qs[:8], 3)
+    assert not nn.tc_stats()["used"]
+    nn.query(qs[:64], 3, cc=0)
+    assert not nn.tc_stats()["used"]
+
+
+def test_knn_tensor_core_pass_clustered_roadmap(pkg, eng, ur5, monkeypatch):
+    """Roadmaps are not uniform: a dense cluster appended AFTER the bootstrap prefix makes the prefix thresholds
+    loose, candidate lists overflow, and those queries are redone by the exact scan: same results either way."""
+    m, _ = eng
+    nn, ex = pkg.NearestNeighbor(m, 0), _exact_nn(pkg, m, monkeypatch)
+    rng = np.random.default_rng(5)
+    base = pkg.uniform_configs(ur5, 50000, seed=95)
+    centre = base[11]
+    cluster = centre + 1e-3 * rng.standard_normal((30000, 6))
+    nodes = np.concatenate([base, cluster, cluster[:100]])  # + exact duplicates inside the cluster
+    nn.append(nodes); ex.append(nodes)
+    qs = np.concatenate([pkg.uniform_configs(ur5, 100, seed=96), centre + 1e-3 * rng.standard_normal((60, 6))])
+    for k in (1, 5, 32):
+        gi, gd = nn.query(qs, k)
+        st = nn.tc_stats()
+        ei, ed = ex.query(qs, k)
+        assert st["used"]
+        assert np.array_equal(gi, ei) and np.array_equal(gd, ed), k
+    assert st["redone"] > 0  # the cluster queries overflowed their lists
+
+
+def test_knn_tensor_core_full_size(pkg, eng, ur5, monkeypatch):
+    """BASELINE config[2] size (1 M-node roadmap): 1024 queries, k = 10, against the exact scan."""
+    m, _ = eng
+    nn, ex = pkg.NearestNeighbor(m, 0), _exact_nn(pkg, m, monkeypatch)
+    nodes = pkg.uniform_configs(ur5, 1 << 20, seed=97)
+    nn.append(nodes); ex.append(nodes)
+    qs = pkg.uniform_configs(ur5, 1024, seed=98)
+    for k in (1, 10):
+        gi, gd = nn.query(qs, k)
+        st = nn.tc_stats()
+        ei, ed = ex.query(qs, k)
+        assert st["used"] and st["redone"] == 0 and st["stages"] == 2
+        assert np.array_equal(gi, ei) and np.array_equal(gd, ed)
+
+
 def test_full_size_properties(pkg, eng, ur5, ur5_oracle):
     """BASELINE config[1] size (1M configurations): size-independent properties —
     idempotence (same batch twice -> same flags), permutation equivariance, consistency of a
