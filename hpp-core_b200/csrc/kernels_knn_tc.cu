@@ -3,17 +3,20 @@
 //
 // For vector-space models the squared WeighedDistance is ||a'||^2 + ||b'||^2 - 2 a'.b' with a' = w o a: a GEMM of
 // the query tile against the node stream.  It runs on the 5th-generation tensor cores (tcgen05.mma kind::tf32,
-// M = 128 queries x N = 256 nodes, accumulators in TMEM) with a three-term TF32 split so that the approximate
+// M = 128 queries x N = 128 nodes, four accumulators in TMEM) with a three-term TF32 split so that the approximate
 // squared distance carries an absolute error far below the gaps that matter:
-//   query row  [ ah | ah | al | na_hi na_lo 1 1 ]      node row  [ -2bh | -2bl | -2bh | 1 1 nb_hi nb_lo ]
-// (h/l = TF32 head and tail of the FP64 value, na/nb the FP64 squared norms), i.e. K = 3 nq + 4 slots padded to 8 kc.
-// The accumulator IS the approximate squared distance, so the epilogue is one compare per (query, node) against the
-// query's threshold; survivors are appended to the query's candidate list.  The threshold is an exact upper bound of
-// the k-th distance: the k-th exact distance over a PREFIX of the nodes (first 4096 by the exact scan, then the
-// candidates of a 16x larger prefix, ...), inflated by the error bound eps = 2^-16 (na + max nb).  Every node whose
-// exact distance is <= the k-th exact distance therefore survives, and the final result is the exact FP64 top-k of
-// the survivors by the same (distance, node index) key and the same operation order as the exact scan: identical
-// indices and distances, bit for bit.  A query whose list overflows is redone by the exact scan.
+//   query row  [ ah | ah | al | na_hi na_lo 1 1 -thr_hi -thr_lo ]   node row  [ -2bh | -2bl | -2bh | 1 1 nb_hi nb_lo 1 1 ]
+// i.e. K = 3 nq + 6 slots padded to 8 kc (UR5: exactly 24).
+// (h/l = TF32 head and tail of the FP64 value, na/nb the FP64 squared norms).
+// Two more slots carry the query's threshold (-thr_hi, -thr_lo against 1, 1), so the accumulator IS the approximate
+// squared distance minus the threshold and the epilogue is a sign test: 32 FP32 columns of a TMEM lane are OR-ed
+// together; when the sign bit is set that CHUNK of 32 nodes goes to a list private to (query, CTA) (a shared-memory
+// counter, no global atomics) and the re-rank looks at all 32 exactly.  The threshold is an exact upper bound of the k-th distance: the k-th
+// exact distance over a PREFIX of the nodes (the first 512 by the re-rank kernel itself, then the candidates of a
+// <= 16x larger prefix, ...), inflated by the error bound eps = 2^-16 (na + max nb).  Every node whose exact distance
+// is <= the k-th exact distance therefore survives, and the final result is the exact FP64 top-k of the survivors by
+// the same (distance, node index) key and the same operation order as the exact scan: identical indices and
+// distances, bit for bit.  A query one of whose lists overflows is redone by the exact scan.
 #include <algorithm>
 #include <climits>
 #include <cmath>
@@ -25,14 +28,18 @@
 namespace hppb200 {
 
 constexpr int TC_M = 128;            // queries per A tile (UMMA M)
-constexpr int TC_N = 256;            // nodes per B tile (UMMA N)
-constexpr int TC_CAP = 1024;         // candidates kept per query and stage
-constexpr int TC_EPI_WARPS = 8;      // two groups of 4 warps, one per accumulator buffer
+constexpr int TC_N = 128;            // nodes per B tile (UMMA N)
+constexpr int TC_NBUF = 4;           // TMEM accumulators (TC_NBUF * TC_N = 512 columns: the whole tensor memory)
+constexpr int TC_CAPC = 16;          // candidates kept per (query, CTA) and stage when all SMs work (more per CTA otherwise)
+constexpr int TC_EPI_WARPS = 4 * TC_NBUF;  // one group of 4 warps per accumulator buffer
 constexpr int TC_THREADS = (TC_EPI_WARPS + 2) * 32;  // + bulk-copy producer warp + MMA issuer warp
-constexpr int TC_BSTAGES = 2;        // node-tile ring
+constexpr int TC_BSTAGES = 8;        // node-tile ring (at most; fewer when shared memory is short)
 constexpr int TC_MAX_KC = 6;
 constexpr int TC_MAX_QT = 8;
-constexpr size_t TC_PREFIX0 = 4096;  // nodes of the exact bootstrap scan
+constexpr size_t TC_PREFIX0 = 512;   // nodes of the exact bootstrap (re-rank kernel over the first nodes)
+constexpr double TC_RATIO = 16.0;    // prefix growth per stage (candidates per query and stage ~ k * ratio)
+constexpr int TC_LIST = 1024;         // candidate chunks a query may carry into the re-rank
+constexpr float TC_THR_MAX = 1e29f;  // thresholds are clamped below the padding norm 1e30
 constexpr size_t TC_MIN_NODES = 16384;
 
 // float index of (row r, slot s) inside a tile in the UMMA K-major no-swizzle canonical layout: 8 x 16-byte core
@@ -50,9 +57,10 @@ __device__ __forceinline__ float toTf32(double x) {
 
 // one thread per operand row: FP64 configuration -> TF32 split operand row.  side 0 = query (A), 1 = node (B).
 // rows [row0, rowsEnd) are written; rows >= nvalid are padding (norm slot 1e30: never below a threshold).
+// thr (queries only): per-row threshold folded into the operand, or null for 0.
 __global__ void knnTcPrepKernel(const double* __restrict__ src, const double* __restrict__ scale, int nq, int kc, int side,
                                 int rowsPerTile, size_t row0, size_t rowsEnd, size_t nvalid, float* __restrict__ dst,
-                                unsigned* __restrict__ maxNorm) {
+                                unsigned* __restrict__ maxNorm, const float* __restrict__ thr) {
   const size_t row = row0 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (row >= rowsEnd) return;
   float v[8 * TC_MAX_KC];
@@ -71,9 +79,13 @@ __global__ void knnTcPrepKernel(const double* __restrict__ src, const double* __
     const float nh = toTf32(norm);
     const float nl = toTf32(norm - (double)nh);
     const int o = 3 * nq;
-    if (side == 0) { v[o] = nh; v[o + 1] = nl; v[o + 2] = 1.f; v[o + 3] = 1.f; }
-    else {
-      v[o] = 1.f; v[o + 1] = 1.f; v[o + 2] = nh; v[o + 3] = nl;
+    if (side == 0) {
+      v[o] = nh; v[o + 1] = nl; v[o + 2] = 1.f; v[o + 3] = 1.f;
+      const float t = thr ? thr[row] : 0.f;  // accumulator = approximate squared distance - threshold
+      const float th = toTf32((double)t);
+      v[o + 4] = -th; v[o + 5] = -toTf32((double)t - (double)th);
+    } else {
+      v[o] = 1.f; v[o + 1] = 1.f; v[o + 2] = nh; v[o + 3] = nl; v[o + 4] = 1.f; v[o + 5] = 1.f;
       atomicMax(maxNorm, __float_as_uint(__double2float_ru(norm)));
     }
   } else {
@@ -92,8 +104,8 @@ __device__ __forceinline__ void mbarInit(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
 }
 __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  const long long t0 = clock64();
+  uint32_t done = 0, spins = 0;
+  long long t0 = 0;
   while (true) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
@@ -103,7 +115,10 @@ __device__ __forceinline__ void mbarWait(uint32_t bar, uint32_t parity) {
         : "r"(bar), "r"(parity)
         : "memory");
     if (done) break;
-    if (clock64() - t0 > 4000000000ll) __trap();  // ~2 s: a protocol error must not hang the device
+    if ((++spins & 0x3ffu) == 0) {  // a protocol error must not hang the device: trap after ~2 s
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > 4000000000ll) __trap();
+    }
   }
 }
 __device__ __forceinline__ void mbarArrive(uint32_t bar) {
@@ -130,19 +145,28 @@ __device__ __forceinline__ void tcMma(uint32_t tmem, uint64_t adesc, uint64_t bd
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-// 32 consecutive accumulator columns of this thread's TMEM lane (= query row), complete on return
+// 32 consecutive accumulator columns of this thread's TMEM lane (= query row); valid after tcWaitLoad on the same array
 __device__ __forceinline__ void tcLoad32(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n\t"
-      "tcgen05.wait::ld.sync.aligned;"
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
         "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
         "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
         "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr)
       : "memory");
+}
+// all tcgen05.ld of this thread have landed; the registers are tied to the wait so that no use moves above it
+__device__ __forceinline__ void tcWaitLoad(uint32_t (&r)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7]), "+r"(r[8]), "+r"(r[9]),
+                 "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]), "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]),
+                 "+r"(r[19]), "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]), "+r"(r[26]), "+r"(r[27]),
+                 "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+               :
+               : "memory");
 }
 // shared-memory matrix descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor: start >> 4 at [0,14), leading
 // byte offset >> 4 at [16,30), stride byte offset >> 4 at [32,46), version 1 at [46,48), layout type 0 at [61,64))
@@ -153,40 +177,44 @@ __device__ __forceinline__ uint64_t tcSmemDesc(uint32_t addr, uint32_t lbo, uint
 
 struct TcFilterArgs {
   const float* btiles;   // node operand tiles
-  const float* atiles;   // query operand tiles of this launch (nqt tiles)
-  const float* thr;      // [nqt * 128] thresholds (padding rows: -1)
-  int* cnt;              // [nqt * 128] candidates found per query (may exceed TC_CAP)
-  int* cand;             // [nqt * 128][TC_CAP] node indices
+  const float* atiles;   // query operand tiles of this launch (nqt tiles), thresholds folded in
+  int* cnt;              // [nqt * 128][gstride] candidate chunks found per (query, CTA) (may exceed capc)
+  int* cand;             // [nqt * 128][gstride * TC_CAPC] candidate chunks (32 consecutive nodes each), capc per CTA
   float* dump;           // debug: accumulator of (query tile 0, node tile 0), [128][256], or null
   unsigned ntiles;       // node tiles of the prefix
-  int nqt, kc;
+  int nqt, kc, bstages, gstride, capc;  // capc: list capacity per (query, CTA) of this launch
   int swapOffsets;       // debug: exchange the leading/stride byte offsets of the descriptors
 };
 
-// Persistent grid, one CTA per SM.  Warp 8 lane 0: bulk copies (query tiles once, node tiles through a ring);
-// warp 9 lane 0: tcgen05.mma issue, kc K = 8 steps per (node tile, query tile) into one of two 256-column TMEM
-// accumulators; warps 0-3 / 4-7: epilogue of accumulator 0 / 1 (thread = TMEM lane = query row).
+// Persistent grid, one CTA per SM.  Warp TC_EPI_WARPS lane 0: bulk copies (query tiles once, node tiles through a ring);
+// next warp lane 0: tcgen05.mma issue, kc K = 8 steps per (node tile, query tile) into one of TC_NBUF 128-column TMEM
+// accumulators; epilogue warps 4 g .. 4 g + 3 drain accumulator g (thread = TMEM lane = query row), two tcgen05.ld in
+// flight per warp.
 __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs A) {
   extern __shared__ __align__(128) unsigned char smem[];
-  uint64_t* bars = (uint64_t*)smem;  // 0: a_full, 1..2: b_full, 3..4: b_empty, 5..6: acc_full, 7..8: acc_empty
-  uint32_t* tmemPtr = (uint32_t*)(smem + 128);
+  // barriers: 0 a_full, B_FULL.. b_full, B_EMPTY.. b_empty, ACC_FULL.. acc_full, ACC_EMPTY.. acc_empty
+  constexpr int B_FULL = 1, B_EMPTY = B_FULL + TC_BSTAGES, ACC_FULL = B_EMPTY + TC_BSTAGES, ACC_EMPTY = ACC_FULL + TC_NBUF;
+  static_assert((ACC_EMPTY + TC_NBUF) * 8 <= 384, "barrier block");
+  uint64_t* bars = (uint64_t*)smem;
+  uint32_t* tmemPtr = (uint32_t*)(smem + 384);
   const uint32_t aBytes = (uint32_t)(TC_M * A.kc * 32), bBytes = (uint32_t)(TC_N * A.kc * 32);
-  unsigned char* sA = smem + 256;
+  unsigned char* sA = smem + 512;
   unsigned char* sB = sA + (size_t)A.nqt * aBytes;
-  float* sThr = (float*)(sB + (size_t)TC_BSTAGES * bBytes);
+  int* sCnt = (int*)(sB + (size_t)A.bstages * bBytes);  // candidates of this CTA per query row
   const uint32_t barBase = smemAddr(bars);
   auto bar = [&](int i) { return barBase + 8u * (uint32_t)i; };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const unsigned S = (unsigned)A.bstages;
 
   if (threadIdx.x == 0) {
     mbarInit(bar(0), 1);
-    for (int s = 0; s < TC_BSTAGES; ++s) { mbarInit(bar(1 + s), 1); mbarInit(bar(3 + s), 1); }
-    for (int b = 0; b < 2; ++b) { mbarInit(bar(5 + b), 1); mbarInit(bar(7 + b), 128); }
+    for (int s = 0; s < TC_BSTAGES; ++s) { mbarInit(bar(B_FULL + s), 1); mbarInit(bar(B_EMPTY + s), 1); }
+    for (int b = 0; b < TC_NBUF; ++b) { mbarInit(bar(ACC_FULL + b), 1); mbarInit(bar(ACC_EMPTY + b), 128); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
-  for (int x = threadIdx.x; x < A.nqt * TC_M; x += TC_THREADS) sThr[x] = A.thr[x];
-  if (warp == TC_EPI_WARPS) {  // the whole tensor memory of the SM: two 128 x 256 FP32 accumulators
+  for (int x = threadIdx.x; x < A.nqt * TC_M; x += TC_THREADS) sCnt[x] = 0;
+  if (warp == TC_EPI_WARPS) {  // the whole tensor memory of the SM: TC_NBUF accumulators of 128 x TC_N FP32
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smemAddr(tmemPtr)), "r"(512u) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -202,10 +230,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
         bulkCopy(smemAddr(sA + (size_t)qt * aBytes), A.atiles + (size_t)qt * (aBytes / 4), aBytes, bar(0));
       unsigned it = 0;
       for (unsigned t = blockIdx.x; t < A.ntiles; t += gridDim.x, ++it) {
-        const unsigned s = it % TC_BSTAGES, ph = (it / TC_BSTAGES) & 1u;
-        mbarWait(bar(3 + s), ph ^ 1u);
-        mbarExpectTx(bar(1 + s), bBytes);
-        bulkCopy(smemAddr(sB + (size_t)s * bBytes), A.btiles + (size_t)t * (bBytes / 4), bBytes, bar(1 + s));
+        const unsigned s = it % S, ph = (it / S) & 1u;
+        mbarWait(bar(B_EMPTY + s), ph ^ 1u);
+        mbarExpectTx(bar(B_FULL + s), bBytes);
+        bulkCopy(smemAddr(sB + (size_t)s * bBytes), A.btiles + (size_t)t * (bBytes / 4), bBytes, bar(B_FULL + s));
       }
     }
   } else if (warp == TC_EPI_WARPS + 1) {
@@ -217,21 +245,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
       mbarWait(bar(0), 0);
       unsigned it = 0, j = 0;
       for (unsigned t = blockIdx.x; t < A.ntiles; t += gridDim.x, ++it) {
-        const unsigned s = it % TC_BSTAGES, ph = (it / TC_BSTAGES) & 1u;
-        mbarWait(bar(1 + s), ph);
+        const unsigned s = it % S, ph = (it / S) & 1u;
+        mbarWait(bar(B_FULL + s), ph);
         tcFenceAfter();
         const uint32_t bAddr = smemAddr(sB + (size_t)s * bBytes);
         for (int qt = 0; qt < A.nqt; ++qt, ++j) {
-          const unsigned buf = j & 1u, aph = (j >> 1) & 1u;
-          mbarWait(bar(7 + buf), aph ^ 1u);
+          const unsigned buf = j % TC_NBUF, aph = (j / TC_NBUF) & 1u;
+          mbarWait(bar(ACC_EMPTY + buf), aph ^ 1u);
           tcFenceAfter();
           const uint32_t aAddr = smemAddr(sA + (size_t)qt * aBytes);
           for (int c = 0; c < A.kc; ++c)
             tcMma(tmemBase + buf * (uint32_t)TC_N, tcSmemDesc(aAddr + (uint32_t)c * 256u, lbo, sbo),
                   tcSmemDesc(bAddr + (uint32_t)c * 256u, lbo, sbo), idesc, c > 0 ? 1u : 0u);
-          tcCommit(bar(5 + buf));
+          tcCommit(bar(ACC_FULL + buf));
         }
-        tcCommit(bar(3 + s));
+        tcCommit(bar(B_EMPTY + s));
       }
     }
   } else {
@@ -241,39 +269,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
     unsigned j = 0, use = 0;
     for (unsigned t = blockIdx.x; t < A.ntiles; t += gridDim.x) {
       for (int qt = 0; qt < A.nqt; ++qt, ++j) {
-        if ((j & 1u) != group) continue;
-        mbarWait(bar(5 + group), use & 1u);
+        if (j % TC_NBUF != group) continue;
+        mbarWait(bar(ACC_FULL + group), use & 1u);
         ++use;
         tcFenceAfter();
-        const float thr = sThr[qt * TC_M + row];
         const int q = qt * TC_M + row;
-        for (int cb = 0; cb < TC_N / 32; ++cb) {
-          uint32_t r[32];
-          __syncwarp();  // tcgen05.ld is warp-collective: reconverge after the wait loop / the candidate branch
-          tcLoad32(laneAddr + (uint32_t)cb * 32u, r);
-          bool any = false;
+        // 32 columns: OR of the sign bits first; a set sign bit = approximate squared distance below the threshold
+        auto process = [&](const uint32_t (&r)[32], int cb) {
+          uint32_t any = 0;
 #pragma unroll
-          for (int i = 0; i < 32; ++i) any |= __uint_as_float(r[i]) <= thr;
-          if (any) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-              if (__uint_as_float(r[i]) <= thr) {
-                const int slot = atomicAdd(&A.cnt[q], 1);
-                if (slot < TC_CAP) A.cand[(size_t)q * TC_CAP + slot] = (int)(t * (unsigned)TC_N + (unsigned)(cb * 32 + i));
-              }
+          for (int i = 0; i < 32; ++i) any |= r[i];
+          if ((int)any < 0) {  // rare: the 32-node chunk goes to the query's list of this CTA, the re-rank looks at all 32
+            const int slot = atomicAdd(&sCnt[q], 1);
+            if (slot < A.capc)
+              A.cand[(size_t)q * A.gstride * TC_CAPC + (size_t)blockIdx.x * A.capc + slot] = (int)(t * (unsigned)(TC_N / 32) + (unsigned)cb);
           }
-          if (A.dump != nullptr && t == 0 && qt == 0) {
+          if (A.dump != nullptr && t < 2 && qt == 0) {
 #pragma unroll
-            for (int i = 0; i < 32; ++i) A.dump[(size_t)row * TC_N + cb * 32 + i] = __uint_as_float(r[i]);
+            for (int i = 0; i < 32; ++i) A.dump[(size_t)row * (2 * TC_N) + t * TC_N + cb * 32 + i] = __uint_as_float(r[i]);
           }
+          __syncwarp();  // tcgen05.ld / wait are warp-collective: reconverge after the candidate branch
+        };
+        uint32_t ra[32], rb[32];
+        __syncwarp();
+        tcLoad32(laneAddr, ra);
+#pragma unroll
+        for (int cb = 0; cb < TC_N / 32; cb += 2) {
+          tcWaitLoad(ra);
+          tcLoad32(laneAddr + (uint32_t)(cb + 1) * 32u, rb);
+          process(ra, cb);
+          tcWaitLoad(rb);
+          if (cb + 2 < TC_N / 32) tcLoad32(laneAddr + (uint32_t)(cb + 2) * 32u, ra);
+          process(rb, cb + 1);
         }
         tcFenceBefore();
-        mbarArrive(bar(7 + group));
+        mbarArrive(bar(ACC_EMPTY + group));
       }
     }
   }
   tcFenceBefore();
   __syncthreads();
+  for (int x = threadIdx.x; x < A.nqt * TC_M; x += TC_THREADS) A.cnt[(size_t)x * A.gstride + blockIdx.x] = sCnt[x];
   if (warp == TC_EPI_WARPS) {
     tcFenceAfter();
     __syncwarp();
@@ -281,29 +317,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
   }
 }
 
-// thresholds from the exact k-th distance over a node prefix: thr = d_k^2 (1 + 1e-9) + eps, eps = 2^-16 (na + max nb)
-// rounded up to FP32; rows beyond nqueries get -1 (their operand rows are padding)
-__global__ void knnTcThresholdKernel(const double* __restrict__ queries, const double* __restrict__ scale, int nq, int nqueries,
-                                     int rows, const double* __restrict__ kdist, int k, const unsigned* __restrict__ maxNorm,
-                                     float* __restrict__ thr) {
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= rows) return;
-  if (q >= nqueries) { thr[q] = -1.f; return; }
-  double na = 0;
-  for (int c = 0; c < nq; ++c) { const double x = scale[c] * queries[(size_t)q * nq + c]; na = fma(x, x, na); }
-  const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), -16) + 1e-30;
-  const double d = kdist[(size_t)q * k + (k - 1)];
-  thr[q] = __double2float_ru(d * d * (1.0 + 1e-9) + eps);  // +inf when the prefix held fewer than k nodes
-}
-
 // one warp per query: exact FP64 WeighedDistance of the candidates (operation order of the exact scan), k smallest
-// by (distance, node index).  Not final: tighten the threshold.  Final: write the result; a query whose candidate
-// list overflowed is flagged (idx[q][0] = -2, appended to `flagged`) and redone by the exact scan.
+// by (distance, node index).  Candidates: the first `prefixNodes` nodes (bootstrap, cnt == null) or the query's
+// per-CTA lists of the last filter launch.  Not final: the new threshold thr = d_k^2 (1 + 1e-6) + eps,
+// eps = 2^-16 (na + max nb), rounded up, if it is tighter.  Final: write the result; a query with an overflowed list
+// is flagged (idx[q][0] = -2, appended to `flagged`) and redone by the exact scan.
 __global__ void __launch_bounds__(128)
-knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, const double* __restrict__ queries,
+knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, const double* __restrict__ queries,
                   const double* __restrict__ scale, int nqueries, int k, const int* __restrict__ cnt, const int* __restrict__ cand,
-                  const unsigned* __restrict__ maxNorm, float* __restrict__ thr, int finalStage, long long* __restrict__ idx,
-                  double* __restrict__ dist, unsigned* __restrict__ nflagged, int* __restrict__ flagged) {
+                  int gused, int gstride, int capc, int prefixNodes, const unsigned* __restrict__ maxNorm, float* __restrict__ thr,
+                  int finalStage, long long* __restrict__ idx, double* __restrict__ dist, unsigned* __restrict__ nflagged,
+                  int* __restrict__ flagged) {
   extern __shared__ __align__(16) unsigned char rsm[];
   const Tables T = makeTables(mv.blob, mv);
   double* sw2 = (double*)rsm;
@@ -313,34 +337,70 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, const double* 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = blockIdx.x * (blockDim.x / 32) + warp;
   double* sq = sqAll + (size_t)warp * mv.nq;
+  int* list = (int*)(sqAll + (size_t)(blockDim.x / 32) * mv.nq) + (size_t)warp * TC_LIST;  // the warp's candidate chunks
   if (q < nqueries)
     for (int c = lane; c < mv.nq; c += 32) sq[c] = queries[(size_t)q * mv.nq + c];
   __syncthreads();
   if (q >= nqueries) return;
-  const int total = cnt[q];
-  if (total > TC_CAP) {
-    if (finalStage && lane == 0) {
-      idx[(size_t)q * k] = -2;
-      flagged[atomicAdd(nflagged, 1u)] = q;
+  // 1. the query's candidate chunks (32 consecutive nodes each), gathered by the lanes in parallel
+  int total = 0;
+  if (cnt == nullptr) {
+    total = (prefixNodes + 31) / 32;
+    for (int e = lane; e < total; e += 32) list[e] = e;
+  } else {
+    const int* myCnt = cnt + (size_t)q * gstride;
+    int mine = 0;  // lane l owns the lists of CTAs l, l + 32, ...
+    bool over = false;
+    for (int c = lane; c < gused; c += 32) { const int nc = myCnt[c]; over |= nc > capc; mine += nc; }
+    int incl = mine;
+    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+    total = __shfl_sync(FULL, incl, 31);
+    if (__any_sync(FULL, over) || total > TC_LIST) {
+      if (finalStage && lane == 0) {
+        idx[(size_t)q * k] = -2;
+        flagged[atomicAdd(nflagged, 1u)] = q;
+      }
+      return;  // (not final: the previous threshold stays, it is still an upper bound)
     }
-    return;  // (not final: the previous threshold stays, it is still an upper bound)
+    int o = incl - mine;
+    for (int c = lane; c < gused; c += 32) {
+      const int nc = myCnt[c];
+      for (int i = 0; i < nc; ++i) list[o++] = cand[(size_t)q * gstride * TC_CAPC + (size_t)c * capc + i];
+    }
   }
+  __syncwarp();
+  // 2. exact distances, four chunks per trip (independent row loads in flight), lane = node of the chunk
   Key acc = {CUDART_INF, LLONG_MAX}, ak = acc;
-  for (int f0 = 0; f0 < total; f0 += 32) {
-    const int f = f0 + lane;
-    Key c = {CUDART_INF, LLONG_MAX};
-    if (f < total) {
-      const long long node = cand[(size_t)q * TC_CAP + f];
-      double d1[1];
-      weighedDistanceBatch<1, false>(T, mv, nodes + (size_t)node * mv.nq, sq, sw2, d1);
-      c.d = d1[0]; c.i = node;
+  for (int e0 = 0; e0 < total; e0 += 4) {
+    long long node[4];
+    double d[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      node[u] = e0 + u < total ? (long long)list[e0 + u] * 32 + lane : (long long)n;
+      d[u] = 0;
     }
-    unsigned m = __ballot_sync(FULL, keyLess(c, ak));
-    while (m) {
-      const int src = __ffs(m) - 1;
-      m &= m - 1u;
-      const Key x = {__shfl_sync(FULL, c.d, src), __shfl_sync(FULL, c.i, src)};
-      if (keyLess(x, ak)) topkInsert(acc, ak, x, k, lane);
+    for (int j = 0; j < mv.njoints; ++j) {  // the operation order of weighedDistanceBatch<1, false>
+      const DevJoint& J = T.joints[j];
+      const double w2 = sw2[j], qv = sq[J.idx_q];
+      const bool rev = J.type <= HPPB200_JOINT_REVOLUTE_Z;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const double a = nodes[(size_t)((size_t)node[u] < n ? node[u] : 0) * mv.nq + J.idx_q];
+        const double dq = qv - a;
+        d[u] += rev ? w2 * (dq * dq) : dq * dq;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      Key c = {CUDART_INF, LLONG_MAX};
+      if ((size_t)node[u] < n) { c.d = sqrt(d[u]); c.i = node[u]; }
+      unsigned m = __ballot_sync(FULL, keyLess(c, ak));
+      while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1u;
+        const Key x = {__shfl_sync(FULL, c.d, src), __shfl_sync(FULL, c.i, src)};
+        if (keyLess(x, ak)) topkInsert(acc, ak, x, k, lane);
+      }
     }
   }
   if (finalStage) {
@@ -348,12 +408,15 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, const double* 
       idx[(size_t)q * k + lane] = acc.i != LLONG_MAX ? acc.i : -1;
       dist[(size_t)q * k + lane] = acc.d;
     }
-  } else if (lane == 0 && ak.i != LLONG_MAX) {
-    double na = 0;
-    for (int c = 0; c < mv.nq; ++c) { const double x = scale[c] * sq[c]; na = fma(x, x, na); }
-    const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), -16) + 1e-30;
-    const float t = __double2float_ru(ak.d * ak.d * (1.0 + 1e-9) + eps);
-    if (t < thr[q]) thr[q] = t;
+  } else if (lane == 0) {
+    float t = TC_THR_MAX;
+    if (ak.i != LLONG_MAX) {
+      double na = 0;
+      for (int c = 0; c < mv.nq; ++c) { const double x = scale[c] * sq[c]; na = fma(x, x, na); }
+      const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), -16) + 1e-30;
+      t = fminf(TC_THR_MAX, __double2float_ru(ak.d * ak.d * (1.0 + 1e-6) + eps));
+    }
+    if (cnt == nullptr || t < thr[q]) thr[q] = t;
   }
 }
 
@@ -373,13 +436,18 @@ __global__ void knnTcScatterResultsKernel(const long long* __restrict__ si, cons
 }
 
 // ---- host side -------------------------------------------------------------------------------------------------
-static size_t tcSmemBytes(int nqt, int kc) {
-  return 256 + (size_t)nqt * TC_M * kc * 32 + (size_t)TC_BSTAGES * TC_N * kc * 32 + (size_t)nqt * TC_M * sizeof(float);
+static size_t tcSmemBytes(int nqt, int kc, int bstages) {
+  return 512 + (size_t)nqt * TC_M * kc * 32 + (size_t)bstages * TC_N * kc * 32 + (size_t)nqt * TC_M * sizeof(int);
 }
 static int tcMaxQueryTiles(int kc) {
   int nqt = TC_MAX_QT;
-  while (nqt > 0 && tcSmemBytes(nqt, kc) > 220 * 1024) --nqt;
+  while (nqt > 0 && tcSmemBytes(nqt, kc, 2) > 220 * 1024) --nqt;
   return nqt;
+}
+static int tcStages(int nqt, int kc) {
+  int st = TC_BSTAGES;
+  while (st > 2 && tcSmemBytes(nqt, kc, st) > 220 * 1024) --st;
+  return st;
 }
 
 void knnTcInit(hppb200_knn* nn) {
@@ -388,7 +456,7 @@ void knnTcInit(hppb200_knn* nn) {
   nn->tc_kc = 0;
   if (nn->ff) return;
   const int nq = nn->model->nq;
-  const int kc = (3 * nq + 4 + 7) / 8;
+  const int kc = (3 * nq + 6 + 7) / 8;
   if (kc > TC_MAX_KC || tcMaxQueryTiles(kc) < 1) return;
   nn->tc_kc = kc;
   // per configuration coordinate: the weight of its joint for rotations, 1 for translations (weighed-distance.cc:280-287)
@@ -401,6 +469,7 @@ void knnTcInit(hppb200_knn* nn) {
   HPPB200_CUDA_CHECK(cudaMemcpy(nn->d_tc_scale.p, scale.data(), (size_t)nq * sizeof(double), cudaMemcpyHostToDevice));
   nn->d_tc_misc.reserve(4);
   HPPB200_CUDA_CHECK(cudaMemset(nn->d_tc_misc.p, 0, 4 * sizeof(unsigned)));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTcFilterKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
 }
 
 void knnTcDestroy(hppb200_knn* nn) {
@@ -434,86 +503,90 @@ static void tcSyncNodeOperand(hppb200_knn* nn) {
   if (nn->tc_n >= nn->n) return;
   const size_t row0 = (nn->tc_n / TC_N) * TC_N, rowsEnd = needTiles * TC_N;
   knnTcPrepKernel<<<(unsigned)((rowsEnd - row0 + 127) / 128), 128, 0, nn->stream>>>(nn->d_nodes, nn->d_tc_scale.p, nq, kc, 1, TC_N, row0,
-                                                                                    rowsEnd, nn->n, nn->d_tc_nodes, nn->d_tc_misc.p);
+                                                                                    rowsEnd, nn->n, nn->d_tc_nodes, nn->d_tc_misc.p, nullptr);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   nn->tc_n = nn->n;
 }
 
-static void tcLaunchFilter(hppb200_knn* nn, size_t prefixNodes, int nqtTotal, float* dump, int swapOffsets) {
+// one filter pass of `nqtTotal` query tiles over the first `prefixNodes` nodes; returns the grid used
+static int tcLaunchFilter(hppb200_knn* nn, size_t prefixNodes, int nqtTotal, float* dump, int swapOffsets) {
   const int kc = nn->tc_kc;
   const int perLaunch = tcMaxQueryTiles(kc);
   const unsigned ntiles = (unsigned)((prefixNodes + TC_N - 1) / TC_N);
+  const unsigned grid = std::min<unsigned>((unsigned)nn->num_sms, ntiles);
   for (int qt0 = 0; qt0 < nqtTotal; qt0 += perLaunch) {
     TcFilterArgs a;
     a.nqt = std::min(perLaunch, nqtTotal - qt0);
     a.kc = kc;
+    a.bstages = tcStages(a.nqt, kc);
+    a.gstride = nn->num_sms;
+    a.capc = TC_CAPC * (nn->num_sms / (int)grid);  // few CTAs (small prefix): longer lists each
     a.btiles = nn->d_tc_nodes;
     a.atiles = nn->d_tc_queries.p + (size_t)qt0 * TC_M * 8 * kc;
-    a.thr = nn->d_tc_thr.p + (size_t)qt0 * TC_M;
-    a.cnt = nn->d_tc_cnt.p + (size_t)qt0 * TC_M;
-    a.cand = nn->d_tc_cand.p + (size_t)qt0 * TC_M * TC_CAP;
+    a.cnt = nn->d_tc_cnt.p + (size_t)qt0 * TC_M * a.gstride;
+    a.cand = nn->d_tc_cand.p + (size_t)qt0 * TC_M * a.gstride * TC_CAPC;
     a.dump = qt0 == 0 ? dump : nullptr;
     a.ntiles = ntiles;
     a.swapOffsets = swapOffsets;
-    const size_t smemBytes = tcSmemBytes(a.nqt, kc);
-    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTcFilterKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
-    const unsigned grid = std::min<unsigned>((unsigned)nn->num_sms, ntiles);
-    knnTcFilterKernel<<<grid, TC_THREADS, smemBytes, nn->stream>>>(a);
+    knnTcFilterKernel<<<grid, TC_THREADS, tcSmemBytes(a.nqt, kc, a.bstages), nn->stream>>>(a);
     HPPB200_CUDA_CHECK(cudaGetLastError());
   }
+  return (int)grid;
 }
 
-static void tcPrepQueries(hppb200_knn* nn, const double* d_q, size_t nqueries, int nqtTotal) {
-  const int kc = nn->tc_kc, nq = nn->model->nq;
+static void tcReserve(hppb200_knn* nn, int nqtTotal) {
   const size_t rows = (size_t)nqtTotal * TC_M;
-  nn->d_tc_queries.reserve(rows * 8 * kc);
+  nn->d_tc_queries.reserve(rows * 8 * nn->tc_kc);
   nn->d_tc_thr.reserve(rows);
-  nn->d_tc_cnt.reserve(rows);
-  nn->d_tc_cand.reserve(rows * TC_CAP);
+  nn->d_tc_cnt.reserve(rows * nn->num_sms);
+  nn->d_tc_cand.reserve(rows * nn->num_sms * TC_CAPC);
   nn->d_tc_flagged.reserve(rows);
-  knnTcPrepKernel<<<(unsigned)((rows + 127) / 128), 128, 0, nn->stream>>>(d_q, nn->d_tc_scale.p, nq, kc, 0, TC_M, 0, rows, nqueries,
-                                                                          nn->d_tc_queries.p, nn->d_tc_misc.p);
+}
+// query operand tiles with the current thresholds folded in (thr == null: 0)
+static void tcPrepQueries(hppb200_knn* nn, const double* d_q, size_t nqueries, int nqtTotal, const float* thr) {
+  const size_t rows = (size_t)nqtTotal * TC_M;
+  knnTcPrepKernel<<<(unsigned)((rows + 127) / 128), 128, 0, nn->stream>>>(d_q, nn->d_tc_scale.p, nn->model->nq, nn->tc_kc, 0, TC_M, 0, rows,
+                                                                          nqueries, nn->d_tc_queries.p, nn->d_tc_misc.p, thr);
   HPPB200_CUDA_CHECK(cudaGetLastError());
 }
 
-void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long long* d_i, double* d_d) {
+static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long long* d_i, double* d_d) {
   const int nq = nn->model->nq;
   const int nqtTotal = (int)((nqueries + TC_M - 1) / TC_M);
-  const size_t rows = (size_t)nqtTotal * TC_M;
-  tcSyncNodeOperand(nn);
-  tcPrepQueries(nn, d_q, nqueries, nqtTotal);
-  // bootstrap: exact k-th distance over the first TC_PREFIX0 nodes
-  nn->d_tc_kdist.reserve(nqueries * (size_t)k);
-  nn->d_tc_kidx.reserve(nqueries * (size_t)k);
-  knnExactRun(nn, d_q, nqueries, k, -1, TC_PREFIX0, nn->d_tc_kidx.p, nn->d_tc_kdist.p);
-  knnTcThresholdKernel<<<(unsigned)((rows + 255) / 256), 256, 0, nn->stream>>>(d_q, nn->d_tc_scale.p, nq, (int)nqueries, (int)rows,
-                                                                                nn->d_tc_kdist.p, k, nn->d_tc_misc.p, nn->d_tc_thr.p);
-  // prefixes growing geometrically (<= 32x per stage) up to the whole roadmap
-  const double ratio = (double)nn->n / (double)TC_PREFIX0;
-  const int nstages = ratio <= 32.0 ? 1 : (ratio <= 1024.0 ? 2 : 3);
-  const size_t rerankSmem = ((size_t)nn->model->njoints + 4 * (size_t)nq) * sizeof(double);
+  tcReserve(nn, nqtTotal);
+  const size_t rerankSmem = ((size_t)nn->model->njoints + 4 * (size_t)nq) * sizeof(double) + 4 * TC_LIST * sizeof(int);
+  const unsigned rerankGrid = (unsigned)((nqueries + 3) / 4);
   HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_tc_misc.p + 1, 0, sizeof(unsigned), nn->stream));
+  // bootstrap: exact k-th distance over the first TC_PREFIX0 nodes -> first thresholds
+  knnTcRerankKernel<<<rerankGrid, 128, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k, nullptr,
+                                                                 nullptr, 0, 0, 0, (int)TC_PREFIX0, nn->d_tc_misc.p, nn->d_tc_thr.p, 0, d_i, d_d,
+                                                                 nn->d_tc_misc.p + 1, nn->d_tc_flagged.p);
+  // prefixes growing geometrically (<= TC_RATIO per stage) up to the whole roadmap
+  const double ratio = (double)nn->n / (double)TC_PREFIX0;
+  const int nstages = std::max(1, (int)std::ceil(std::log(ratio) / std::log(TC_RATIO) - 1e-9));
   for (int s = 1; s <= nstages; ++s) {
     size_t prefix = nn->n;
     if (s < nstages) {
       prefix = (size_t)((double)TC_PREFIX0 * std::pow(ratio, (double)s / nstages));
       prefix = std::min(nn->n, (prefix + TC_N - 1) / TC_N * TC_N);
     }
-    HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_tc_cnt.p, 0, rows * sizeof(int), nn->stream));
-    tcLaunchFilter(nn, prefix, nqtTotal, nullptr, 0);
-    knnTcRerankKernel<<<(unsigned)((nqueries + 3) / 4), 128, rerankSmem, nn->stream>>>(
-        nn->view, nn->d_nodes, d_q, nn->d_tc_scale.p, (int)nqueries, k, nn->d_tc_cnt.p, nn->d_tc_cand.p, nn->d_tc_misc.p, nn->d_tc_thr.p,
-        s == nstages ? 1 : 0, d_i, d_d, nn->d_tc_misc.p + 1, nn->d_tc_flagged.p);
+    tcPrepQueries(nn, d_q, nqueries, nqtTotal, nn->d_tc_thr.p);
+    const int gused = tcLaunchFilter(nn, prefix, nqtTotal, nullptr, 0);
+    knnTcRerankKernel<<<rerankGrid, 128, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k,
+                                                                   nn->d_tc_cnt.p, nn->d_tc_cand.p, gused, nn->num_sms, TC_CAPC * (nn->num_sms / gused), 0,
+                                                                   nn->d_tc_misc.p,
+                                                                   nn->d_tc_thr.p, s == nstages ? 1 : 0, d_i, d_d, nn->d_tc_misc.p + 1,
+                                                                   nn->d_tc_flagged.p);
     HPPB200_CUDA_CHECK(cudaGetLastError());
   }
-  // queries whose final candidate list overflowed: exact scan
+  // queries with an overflowed list in the last stage: exact scan
   unsigned nflagged = 0;
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&nflagged, nn->d_tc_misc.p + 1, sizeof(unsigned), cudaMemcpyDeviceToHost, nn->stream));
   HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
-  nn->tc_last_used = true;
   nn->tc_last_stages = nstages;
-  nn->tc_last_overflow = nflagged;
-  nn->tc_last_rows = rows;
+  nn->tc_last_overflow += nflagged;
+  nn->tc_last_rows = (size_t)nqtTotal * TC_M;
+  nn->tc_last_gused = (int)std::min<size_t>((size_t)nn->num_sms, (nn->n + TC_N - 1) / TC_N);
   if (nflagged) {
     DeviceBuffer<double> gq, gd;
     DeviceBuffer<long long> gi;
@@ -526,6 +599,17 @@ void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long l
                                                                                            d_i, d_d);
     HPPB200_CUDA_CHECK(cudaGetLastError());
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
+  }
+}
+
+void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long long* d_i, double* d_d) {
+  tcSyncNodeOperand(nn);
+  nn->tc_last_used = true;
+  nn->tc_last_overflow = 0;
+  const size_t chunk = 8192;  // bounds the candidate buffers (9.5 KB per query)
+  for (size_t q0 = 0; q0 < nqueries; q0 += chunk) {
+    const size_t nqc = std::min(chunk, nqueries - q0);
+    tcRunChunk(nn, d_q + q0 * (size_t)nn->model->nq, nqc, k, d_i + q0 * (size_t)k, d_d + q0 * (size_t)k);
   }
 }
 
@@ -546,9 +630,10 @@ int hppb200_knn_tc_stats(hppb200_knn* nn, int64_t* out) {
     out[2] = (int64_t)nn->tc_last_overflow;
     out[3] = 0;
     if (nn->tc_last_used && nn->d_tc_cnt.p) {  // candidates of the last stage, summed on the host
-      std::vector<int> h(nn->tc_last_rows);
+      std::vector<int> h(nn->tc_last_rows * (size_t)nn->num_sms);  // (of the last chunk of 8192 queries)
       HPPB200_CUDA_CHECK(cudaMemcpy(h.data(), nn->d_tc_cnt.p, h.size() * sizeof(int), cudaMemcpyDeviceToHost));
-      for (int c : h) out[3] += c > 0 ? c : 0;
+      for (size_t r = 0; r < nn->tc_last_rows; ++r)
+        for (int c = 0; c < nn->tc_last_gused; ++c) out[3] += h[r * (size_t)nn->num_sms + c];
     }
     return HPPB200_OK;
   } catch (const std::exception& e) {
@@ -566,13 +651,13 @@ int hppb200_knn_tc_debug_tile(hppb200_knn* nn, const double* queries, size_t nqu
     nn->d_queries.reserve(nqueries * nq);
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(nn->d_queries.p, queries, nqueries * nq * sizeof(double), cudaMemcpyHostToDevice, nn->stream));
     tcSyncNodeOperand(nn);
-    tcPrepQueries(nn, nn->d_queries.p, nqueries, 1);
+    tcReserve(nn, 1);
+    tcPrepQueries(nn, nn->d_queries.p, nqueries, 1, nullptr);  // threshold 0: the accumulator is the squared distance
     DeviceBuffer<float> dump;
-    dump.reserve((size_t)TC_M * TC_N);
-    HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_tc_cnt.p, 0, TC_M * sizeof(int), nn->stream));
-    HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_tc_thr.p, 0xff, TC_M * sizeof(float), nn->stream));  // NaN: nothing passes
-    tcLaunchFilter(nn, std::min<size_t>(nn->n, TC_N), 1, dump.p, swap_offsets);
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(out, dump.p, (size_t)TC_M * TC_N * sizeof(float), cudaMemcpyDeviceToHost, nn->stream));
+    dump.reserve((size_t)TC_M * 2 * TC_N);
+    HPPB200_CUDA_CHECK(cudaMemsetAsync(dump.p, 0, (size_t)TC_M * 2 * TC_N * sizeof(float), nn->stream));
+    tcLaunchFilter(nn, std::min<size_t>(nn->n, 2 * TC_N), 1, dump.p, swap_offsets);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(out, dump.p, (size_t)TC_M * 2 * TC_N * sizeof(float), cudaMemcpyDeviceToHost, nn->stream));
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
     return HPPB200_OK;
   } catch (const std::invalid_argument& e) {

@@ -34,6 +34,7 @@ struct hppb200_knn {
   unsigned long long tc_last_candidates = 0, tc_last_overflow = 0;
   int tc_last_stages = 0;
   size_t tc_last_rows = 0;
+  int tc_last_gused = 0;
   bool tc_last_used = false;
 };
 

@@ -275,7 +275,8 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries,
    count); otherwise the exact FP64 scan.  Both replace nearestNeighbor::Basic::KnearestSearch
    (reference src/nearest-neighbor/basic.cc:84-126).
    Statistics of the last query: out[0] 1 if the tensor-core pass ran, out[1] prefix stages, out[2] queries redone
-   by the exact scan (candidate list overflow), out[3] candidates re-ranked in the last stage. */
+   by the exact scan (candidate list overflow), out[3] candidate chunks (32 consecutive nodes each) re-ranked in
+   the last stage. */
 int hppb200_knn_tc_stats(hppb200_knn* nn, int64_t* out /* [4] */);
 /* Test hook: approximate squared distances (the TMEM accumulator) of up to 128 queries against the first 256
    nodes, out [128][256] row-major FP32; swap_offsets != 0 exchanges the descriptor byte offsets (bring-up). */
