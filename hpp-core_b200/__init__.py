@@ -52,7 +52,7 @@ ABI_SYMBOLS = [
     "hppb200_validate_configs", "hppb200_geometry_placements", "hppb200_pair_distances",
     "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_workspace_set_max_iterations",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_size",
-    "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_debug_tile",
+    "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_tc_debug_tile",
 ]
 
 _LIB = None
@@ -291,7 +291,10 @@ class NearestNeighbor:
         """(used, stages, queries redone exactly, candidates of the last stage) of the last query."""
         out = np.zeros(4, np.int64)
         _check(lib().hppb200_knn_tc_stats(self.h, _p(out, _i64p)))
-        return dict(used=bool(out[0]), stages=int(out[1]), redone=int(out[2]), candidates=int(out[3]))
+        ms, pairs = C.c_double(0), C.c_double(0)
+        _check(lib().hppb200_knn_tc_filter_time(self.h, C.byref(ms), C.byref(pairs)))
+        return dict(used=bool(out[0]), stages=int(out[1]), redone=int(out[2]), candidates=int(out[3]),
+                    filter_ms=ms.value, filter_pairs=pairs.value)
 
     def tc_debug_tile(self, queries, swap_offsets=0):
         queries = np.ascontiguousarray(queries, np.float64).reshape(-1, self.model.nq)

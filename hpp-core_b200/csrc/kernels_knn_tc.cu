@@ -10,8 +10,8 @@
 // (h/l = TF32 head and tail of the FP64 value, na/nb the FP64 squared norms).
 // Two more slots carry the query's threshold (-thr_hi, -thr_lo against 1, 1), so the accumulator IS the approximate
 // squared distance minus the threshold and the epilogue is a sign test: 32 FP32 columns of a TMEM lane are OR-ed
-// together; when the sign bit is set that CHUNK of 32 nodes goes to a list private to (query, CTA) (a shared-memory
-// counter, no global atomics) and the re-rank looks at all 32 exactly.  The threshold is an exact upper bound of the k-th distance: the k-th
+// together; when the sign bit is set the GROUPS of 8 nodes holding a hit go to a list private to (query, CTA) (a
+// shared-memory counter, no global atomics) and the re-rank looks at all 8 exactly.  The threshold is an exact upper bound of the k-th distance: the k-th
 // exact distance over a PREFIX of the nodes (the first 512 by the re-rank kernel itself, then the candidates of a
 // <= 16x larger prefix, ...), inflated by the error bound eps = 2^-16 (na + max nb).  Every node whose exact distance
 // is <= the k-th exact distance therefore survives, and the final result is the exact FP64 top-k of the survivors by
@@ -38,7 +38,7 @@ constexpr int TC_MAX_KC = 6;
 constexpr int TC_MAX_QT = 8;
 constexpr size_t TC_PREFIX0 = 512;   // nodes of the exact bootstrap (re-rank kernel over the first nodes)
 constexpr double TC_RATIO = 16.0;    // prefix growth per stage (candidates per query and stage ~ k * ratio)
-constexpr int TC_LIST = 1024;         // candidate chunks a query may carry into the re-rank
+constexpr int TC_LIST = 2048;         // candidate groups a query may carry into the re-rank
 constexpr float TC_THR_MAX = 1e29f;  // thresholds are clamped below the padding norm 1e30
 constexpr size_t TC_MIN_NODES = 16384;
 
@@ -178,8 +178,8 @@ __device__ __forceinline__ uint64_t tcSmemDesc(uint32_t addr, uint32_t lbo, uint
 struct TcFilterArgs {
   const float* btiles;   // node operand tiles
   const float* atiles;   // query operand tiles of this launch (nqt tiles), thresholds folded in
-  int* cnt;              // [nqt * 128][gstride] candidate chunks found per (query, CTA) (may exceed capc)
-  int* cand;             // [nqt * 128][gstride * TC_CAPC] candidate chunks (32 consecutive nodes each), capc per CTA
+  int* cnt;              // [nqt * 128][gstride] candidate groups found per (query, CTA) (may exceed capc)
+  int* cand;             // [nqt * 128][gstride * TC_CAPC] candidate groups (8 consecutive nodes each), capc per CTA
   float* dump;           // debug: accumulator of (query tile 0, node tile 0), [128][256], or null
   unsigned ntiles;       // node tiles of the prefix
   int nqt, kc, bstages, gstride, capc;  // capc: list capacity per (query, CTA) of this launch
@@ -279,10 +279,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
           uint32_t any = 0;
 #pragma unroll
           for (int i = 0; i < 32; ++i) any |= r[i];
-          if ((int)any < 0) {  // rare: the 32-node chunk goes to the query's list of this CTA, the re-rank looks at all 32
-            const int slot = atomicAdd(&sCnt[q], 1);
-            if (slot < A.capc)
-              A.cand[(size_t)q * A.gstride * TC_CAPC + (size_t)blockIdx.x * A.capc + slot] = (int)(t * (unsigned)(TC_N / 32) + (unsigned)cb);
+          if ((int)any < 0) {  // rare: the groups of 8 nodes holding a hit go to the query's list of this CTA
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              const uint32_t o = r[8 * g] | r[8 * g + 1] | r[8 * g + 2] | r[8 * g + 3] | r[8 * g + 4] | r[8 * g + 5] | r[8 * g + 6] | r[8 * g + 7];
+              if ((int)o < 0) {
+                const int slot = atomicAdd(&sCnt[q], 1);
+                if (slot < A.capc)
+                  A.cand[(size_t)q * A.gstride * TC_CAPC + (size_t)blockIdx.x * A.capc + slot] =
+                      (int)(t * (unsigned)(TC_N / 8) + (unsigned)(cb * 4 + g));
+              }
+            }
           }
           if (A.dump != nullptr && t < 2 && qt == 0) {
 #pragma unroll
@@ -317,91 +324,97 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
   }
 }
 
-// one warp per query: exact FP64 WeighedDistance of the candidates (operation order of the exact scan), k smallest
-// by (distance, node index).  Candidates: the first `prefixNodes` nodes (bootstrap, cnt == null) or the query's
-// per-CTA lists of the last filter launch.  Not final: the new threshold thr = d_k^2 (1 + 1e-6) + eps,
-// eps = 2^-16 (na + max nb), rounded up, if it is tighter.  Final: write the result; a query with an overflowed list
-// is flagged (idx[q][0] = -2, appended to `flagged`) and redone by the exact scan.
-__global__ void __launch_bounds__(128)
+// one CTA per query: exact FP64 WeighedDistance of the candidates (operation order of the exact scan), k smallest
+// by (distance, node index).  A candidate is a group of 8 consecutive nodes: the first `prefixNodes` nodes
+// (bootstrap, cnt == null) or the query's per-CTA lists of the last filter launch, compacted into shared memory by
+// warp 0; every warp then takes 4 groups per trip (lane = node), keeps its k best sorted across the lanes, and warp
+// 0 merges.  Not final: the new threshold thr = d_k^2 (1 + 1e-6) + eps, eps = 2^-16 (na + max nb), rounded up, if
+// it is tighter.  Final: write the result; a query with an overflowed list is flagged (idx[q][0] = -2, appended to
+// `flagged`) and redone by the exact scan.
+constexpr int TC_RR_WARPS = 4;
+__global__ void __launch_bounds__(TC_RR_WARPS * 32)
 knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, const double* __restrict__ queries,
                   const double* __restrict__ scale, int nqueries, int k, const int* __restrict__ cnt, const int* __restrict__ cand,
                   int gused, int gstride, int capc, int prefixNodes, const unsigned* __restrict__ maxNorm, float* __restrict__ thr,
                   int finalStage, long long* __restrict__ idx, double* __restrict__ dist, unsigned* __restrict__ nflagged,
                   int* __restrict__ flagged) {
   extern __shared__ __align__(16) unsigned char rsm[];
+  __shared__ Key lists[TC_RR_WARPS][32];
+  __shared__ int sTotal;
   const Tables T = makeTables(mv.blob, mv);
   double* sw2 = (double*)rsm;
-  double* sqAll = sw2 + mv.njoints;
-  for (int j = threadIdx.x; j < mv.njoints; j += blockDim.x) { const double w = T.weights[j]; sw2[j] = w * w; }
+  double* sq = sw2 + mv.njoints;
+  int* list = (int*)(sq + mv.nq);  // the query's candidate groups
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q = blockIdx.x * (blockDim.x / 32) + warp;
-  double* sq = sqAll + (size_t)warp * mv.nq;
-  int* list = (int*)(sqAll + (size_t)(blockDim.x / 32) * mv.nq) + (size_t)warp * TC_LIST;  // the warp's candidate chunks
-  if (q < nqueries)
-    for (int c = lane; c < mv.nq; c += 32) sq[c] = queries[(size_t)q * mv.nq + c];
-  __syncthreads();
-  if (q >= nqueries) return;
-  // 1. the query's candidate chunks (32 consecutive nodes each), gathered by the lanes in parallel
-  int total = 0;
-  if (cnt == nullptr) {
-    total = (prefixNodes + 31) / 32;
-    for (int e = lane; e < total; e += 32) list[e] = e;
-  } else {
-    const int* myCnt = cnt + (size_t)q * gstride;
-    int mine = 0;  // lane l owns the lists of CTAs l, l + 32, ...
-    bool over = false;
-    for (int c = lane; c < gused; c += 32) { const int nc = myCnt[c]; over |= nc > capc; mine += nc; }
-    int incl = mine;
-    for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
-    total = __shfl_sync(FULL, incl, 31);
-    if (__any_sync(FULL, over) || total > TC_LIST) {
-      if (finalStage && lane == 0) {
-        idx[(size_t)q * k] = -2;
-        flagged[atomicAdd(nflagged, 1u)] = q;
+  const int q = blockIdx.x;
+  for (int j = threadIdx.x; j < mv.njoints; j += blockDim.x) { const double w = T.weights[j]; sw2[j] = w * w; }
+  for (int c = threadIdx.x; c < mv.nq; c += blockDim.x) sq[c] = queries[(size_t)q * mv.nq + c];
+  // 1. the candidate groups, gathered by the lanes of warp 0 in parallel
+  if (warp == 0) {
+    int total = 0;
+    if (cnt == nullptr) {
+      total = (prefixNodes + 7) / 8;
+      for (int e = lane; e < total; e += 32) list[e] = e;
+    } else {
+      const int* myCnt = cnt + (size_t)q * gstride;
+      int mine = 0;  // lane l owns the lists of CTAs l, l + 32, ...
+      bool over = false;
+      for (int c = lane; c < gused; c += 32) { const int nc = myCnt[c]; over |= nc > capc; mine += nc; }
+      int incl = mine;
+      for (int o = 1; o < 32; o <<= 1) { const int v = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += v; }
+      total = __shfl_sync(FULL, incl, 31);
+      if (__any_sync(FULL, over) || total > TC_LIST) total = -1;
+      else {
+        int o = incl - mine;
+        for (int c = lane; c < gused; c += 32) {
+          const int nc = myCnt[c];
+          for (int i = 0; i < nc; ++i) list[o++] = cand[(size_t)q * gstride * TC_CAPC + (size_t)c * capc + i];
+        }
       }
-      return;  // (not final: the previous threshold stays, it is still an upper bound)
     }
-    int o = incl - mine;
-    for (int c = lane; c < gused; c += 32) {
-      const int nc = myCnt[c];
-      for (int i = 0; i < nc; ++i) list[o++] = cand[(size_t)q * gstride * TC_CAPC + (size_t)c * capc + i];
-    }
+    if (lane == 0) sTotal = total;
   }
-  __syncwarp();
-  // 2. exact distances, four chunks per trip (independent row loads in flight), lane = node of the chunk
+  __syncthreads();
+  const int total = sTotal;
+  if (total < 0) {
+    if (finalStage && threadIdx.x == 0) {
+      idx[(size_t)q * k] = -2;
+      flagged[atomicAdd(nflagged, 1u)] = q;
+    }
+    return;  // (not final: the previous threshold stays, it is still an upper bound)
+  }
+  // 2. exact distances: 4 groups of 8 nodes per warp and trip
   Key acc = {CUDART_INF, LLONG_MAX}, ak = acc;
-  for (int e0 = 0; e0 < total; e0 += 4) {
-    long long node[4];
-    double d[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      node[u] = e0 + u < total ? (long long)list[e0 + u] * 32 + lane : (long long)n;
-      d[u] = 0;
+  auto offer = [&](const Key c) {
+    unsigned m = __ballot_sync(FULL, keyLess(c, ak));
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1u;
+      const Key x = {__shfl_sync(FULL, c.d, src), __shfl_sync(FULL, c.i, src)};
+      if (keyLess(x, ak)) topkInsert(acc, ak, x, k, lane);
     }
-    for (int j = 0; j < mv.njoints; ++j) {  // the operation order of weighedDistanceBatch<1, false>
-      const DevJoint& J = T.joints[j];
-      const double w2 = sw2[j], qv = sq[J.idx_q];
-      const bool rev = J.type <= HPPB200_JOINT_REVOLUTE_Z;
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const double a = nodes[(size_t)((size_t)node[u] < n ? node[u] : 0) * mv.nq + J.idx_q];
-        const double dq = qv - a;
-        d[u] += rev ? w2 * (dq * dq) : dq * dq;
+  };
+  for (int e0 = warp * 4; e0 < total; e0 += TC_RR_WARPS * 4) {
+    const int e = e0 + (lane >> 3);
+    Key c = {CUDART_INF, LLONG_MAX};
+    if (e < total) {
+      const long long node = (long long)list[e] * 8 + (lane & 7);
+      if ((size_t)node < n) {
+        double d1[1];
+        weighedDistanceBatch<1, false>(T, mv, nodes + (size_t)node * mv.nq, sq, sw2, d1);
+        c.d = d1[0]; c.i = node;
       }
     }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      Key c = {CUDART_INF, LLONG_MAX};
-      if ((size_t)node[u] < n) { c.d = sqrt(d[u]); c.i = node[u]; }
-      unsigned m = __ballot_sync(FULL, keyLess(c, ak));
-      while (m) {
-        const int src = __ffs(m) - 1;
-        m &= m - 1u;
-        const Key x = {__shfl_sync(FULL, c.d, src), __shfl_sync(FULL, c.i, src)};
-        if (keyLess(x, ak)) topkInsert(acc, ak, x, k, lane);
-      }
-    }
+    offer(c);
+  }
+  lists[warp][lane] = acc;
+  __syncthreads();
+  if (warp != 0) return;
+  for (int w = 1; w < TC_RR_WARPS; ++w) {
+    Key c = lists[w][lane];
+    if (lane >= k) { c.d = CUDART_INF; c.i = LLONG_MAX; }
+    offer(c);
   }
   if (finalStage) {
     if (lane < k) {
@@ -470,11 +483,16 @@ void knnTcInit(hppb200_knn* nn) {
   nn->d_tc_misc.reserve(4);
   HPPB200_CUDA_CHECK(cudaMemset(nn->d_tc_misc.p, 0, 4 * sizeof(unsigned)));
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTcFilterKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+  HPPB200_CUDA_CHECK(cudaEventCreate(&nn->tc_ev0));
+  HPPB200_CUDA_CHECK(cudaEventCreate(&nn->tc_ev1));
 }
 
 void knnTcDestroy(hppb200_knn* nn) {
   if (nn->d_tc_nodes) cudaFree(nn->d_tc_nodes);
   nn->d_tc_nodes = nullptr;
+  if (nn->tc_ev0) cudaEventDestroy(nn->tc_ev0);
+  if (nn->tc_ev1) cudaEventDestroy(nn->tc_ev1);
+  nn->tc_ev0 = nn->tc_ev1 = nullptr;
 }
 
 bool knnTcEligible(const hppb200_knn* nn, size_t nqueries, int k, int32_t cc) {
@@ -554,11 +572,11 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   const int nq = nn->model->nq;
   const int nqtTotal = (int)((nqueries + TC_M - 1) / TC_M);
   tcReserve(nn, nqtTotal);
-  const size_t rerankSmem = ((size_t)nn->model->njoints + 4 * (size_t)nq) * sizeof(double) + 4 * TC_LIST * sizeof(int);
-  const unsigned rerankGrid = (unsigned)((nqueries + 3) / 4);
+  const size_t rerankSmem = ((size_t)nn->model->njoints + (size_t)nq) * sizeof(double) + TC_LIST * sizeof(int);
+  const unsigned rerankGrid = (unsigned)nqueries;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_tc_misc.p + 1, 0, sizeof(unsigned), nn->stream));
   // bootstrap: exact k-th distance over the first TC_PREFIX0 nodes -> first thresholds
-  knnTcRerankKernel<<<rerankGrid, 128, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k, nullptr,
+  knnTcRerankKernel<<<rerankGrid, TC_RR_WARPS * 32, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k, nullptr,
                                                                  nullptr, 0, 0, 0, (int)TC_PREFIX0, nn->d_tc_misc.p, nn->d_tc_thr.p, 0, d_i, d_d,
                                                                  nn->d_tc_misc.p + 1, nn->d_tc_flagged.p);
   // prefixes growing geometrically (<= TC_RATIO per stage) up to the whole roadmap
@@ -571,8 +589,10 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
       prefix = std::min(nn->n, (prefix + TC_N - 1) / TC_N * TC_N);
     }
     tcPrepQueries(nn, d_q, nqueries, nqtTotal, nn->d_tc_thr.p);
+    if (s == nstages) HPPB200_CUDA_CHECK(cudaEventRecord(nn->tc_ev0, nn->stream));  // the whole-roadmap pass, timed
     const int gused = tcLaunchFilter(nn, prefix, nqtTotal, nullptr, 0);
-    knnTcRerankKernel<<<rerankGrid, 128, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k,
+    if (s == nstages) HPPB200_CUDA_CHECK(cudaEventRecord(nn->tc_ev1, nn->stream));
+    knnTcRerankKernel<<<rerankGrid, TC_RR_WARPS * 32, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k,
                                                                    nn->d_tc_cnt.p, nn->d_tc_cand.p, gused, nn->num_sms, TC_CAPC * (nn->num_sms / gused), 0,
                                                                    nn->d_tc_misc.p,
                                                                    nn->d_tc_thr.p, s == nstages ? 1 : 0, d_i, d_d, nn->d_tc_misc.p + 1,
@@ -583,6 +603,10 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   unsigned nflagged = 0;
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&nflagged, nn->d_tc_misc.p + 1, sizeof(unsigned), cudaMemcpyDeviceToHost, nn->stream));
   HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
+  float fms = 0;
+  HPPB200_CUDA_CHECK(cudaEventElapsedTime(&fms, nn->tc_ev0, nn->tc_ev1));
+  nn->tc_last_filter_ms += fms;
+  nn->tc_last_filter_pairs += (double)nqtTotal * TC_M * (double)((nn->n + TC_N - 1) / TC_N * TC_N);
   nn->tc_last_stages = nstages;
   nn->tc_last_overflow += nflagged;
   nn->tc_last_rows = (size_t)nqtTotal * TC_M;
@@ -606,6 +630,8 @@ void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long l
   tcSyncNodeOperand(nn);
   nn->tc_last_used = true;
   nn->tc_last_overflow = 0;
+  nn->tc_last_filter_ms = 0;
+  nn->tc_last_filter_pairs = 0;
   const size_t chunk = 8192;  // bounds the candidate buffers (9.5 KB per query)
   for (size_t q0 = 0; q0 < nqueries; q0 += chunk) {
     const size_t nqc = std::min(chunk, nqueries - q0);
@@ -640,6 +666,13 @@ int hppb200_knn_tc_stats(hppb200_knn* nn, int64_t* out) {
     setLastError(e.what());
     return std::strncmp(e.what(), "CUDA", 4) == 0 ? HPPB200_ERR_CUDA : HPPB200_ERR_INVALID_ARGUMENT;
   }
+}
+
+int hppb200_knn_tc_filter_time(hppb200_knn* nn, double* ms, double* pairs) {
+  if (!nn || !ms || !pairs) { setLastError("null argument"); return HPPB200_ERR_INVALID_ARGUMENT; }
+  *ms = nn->tc_last_used ? nn->tc_last_filter_ms : 0.0;
+  *pairs = nn->tc_last_used ? nn->tc_last_filter_pairs : 0.0;
+  return HPPB200_OK;
 }
 
 int hppb200_knn_tc_debug_tile(hppb200_knn* nn, const double* queries, size_t nqueries, int swap_offsets, float* out) {

@@ -36,6 +36,8 @@ struct hppb200_knn {
   size_t tc_last_rows = 0;
   int tc_last_gused = 0;
   bool tc_last_used = false;
+  double tc_last_filter_ms = 0, tc_last_filter_pairs = 0;  // whole-roadmap filter pass of the last query (CUDA events)
+  cudaEvent_t tc_ev0 = nullptr, tc_ev1 = nullptr;
 };
 
 namespace hppb200 {

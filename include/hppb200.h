@@ -275,9 +275,12 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries,
    count); otherwise the exact FP64 scan.  Both replace nearestNeighbor::Basic::KnearestSearch
    (reference src/nearest-neighbor/basic.cc:84-126).
    Statistics of the last query: out[0] 1 if the tensor-core pass ran, out[1] prefix stages, out[2] queries redone
-   by the exact scan (candidate list overflow), out[3] candidate chunks (32 consecutive nodes each) re-ranked in
+   by the exact scan (candidate list overflow), out[3] candidate groups (8 consecutive nodes each) re-ranked in
    the last stage. */
 int hppb200_knn_tc_stats(hppb200_knn* nn, int64_t* out /* [4] */);
+/* Device time (CUDA events on the mirror's stream) of the whole-roadmap tcgen05 filter pass of the last query and
+   the (query, node) pairs it evaluated (padded to tiles): the kernel the k-NN roofline is reported on. */
+int hppb200_knn_tc_filter_time(hppb200_knn* nn, double* ms, double* pairs);
 /* Test hook: approximate squared distances (the TMEM accumulator) of up to 128 queries against the first 256
    nodes, out [128][256] row-major FP32; swap_offsets != 0 exchanges the descriptor byte offsets (bring-up). */
 int hppb200_knn_tc_debug_tile(hppb200_knn* nn, const double* queries, size_t nqueries, int swap_offsets,
