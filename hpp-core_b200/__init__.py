@@ -312,6 +312,6 @@ class NearestNeighbor:
         return [idx[i, :min(count[i], cap)].copy() for i in range(n)], count
 
 
-from .planners import BiRRTPlanner, EngineBackend, Roadmap  # noqa: E402,F401
+from .planners import BiRRTPlanner, EngineBackend, KPrmStar, Roadmap  # noqa: E402,F401
 from .validators import (CollisionValidation, ConfigValidations, Dichotomy, Discretized,  # noqa: E402,F401
                          JointBoundValidation, Progressive, StraightPath, ValidationReport)

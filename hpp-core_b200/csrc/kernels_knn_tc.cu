@@ -39,6 +39,8 @@ constexpr int TC_MAX_QT = 8;
 constexpr size_t TC_PREFIX0 = 512;   // nodes of the exact bootstrap (re-rank kernel over the first nodes)
 constexpr double TC_RATIO = 16.0;    // prefix growth per stage (candidates per query and stage ~ k * ratio)
 constexpr int TC_LIST = 2048;         // candidate groups a query may carry into the re-rank
+constexpr int TC_KEYS = 2048;         // exact keys a query may keep for the sort path (k > 32)
+constexpr int TC_MAX_K = 256;
 constexpr float TC_THR_MAX = 1e29f;  // thresholds are clamped below the padding norm 1e30
 constexpr size_t TC_MIN_NODES = 16384;
 
@@ -340,7 +342,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
                   int* __restrict__ flagged) {
   extern __shared__ __align__(16) unsigned char rsm[];
   __shared__ Key lists[TC_RR_WARPS][32];
-  __shared__ int sTotal;
+  __shared__ int sTotal, sKept;
   const Tables T = makeTables(mv.blob, mv);
   double* sw2 = (double*)rsm;
   double* sq = sw2 + mv.njoints;
@@ -383,6 +385,66 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
       flagged[atomicAdd(nflagged, 1u)] = q;
     }
     return;  // (not final: the previous threshold stays, it is still an upper bound)
+  }
+  if (k > 32) {
+    // 2'. k > 32: the exact keys not above the current threshold (an upper bound of the k-th squared distance, so no
+    // top-k node is dropped) are collected in shared memory and sorted by a bitonic network; first k = the result
+    Key* keys = (Key*)(rsm + (((size_t)(mv.njoints + mv.nq) * sizeof(double) + TC_LIST * sizeof(int) + 15) & ~(size_t)15));
+    const double bound = cnt == nullptr ? CUDART_INF : (double)thr[q] * (1.0 + 1e-9);
+    if (threadIdx.x == 0) sKept = 0;
+    __syncthreads();
+    for (int e0 = warp * 4; e0 < total; e0 += TC_RR_WARPS * 4) {
+      const int e = e0 + (lane >> 3);
+      if (e < total) {
+        const long long node = (long long)list[e] * 8 + (lane & 7);
+        if ((size_t)node < n) {
+          double d1[1];
+          weighedDistanceBatch<1, false>(T, mv, nodes + (size_t)node * mv.nq, sq, sw2, d1);
+          if (d1[0] * d1[0] <= bound) {
+            const int slot = atomicAdd(&sKept, 1);
+            if (slot < TC_KEYS) { keys[slot].d = d1[0]; keys[slot].i = node; }
+          }
+        }
+      }
+    }
+    __syncthreads();
+    const int kept = sKept;
+    if (kept > TC_KEYS) {
+      if (finalStage && threadIdx.x == 0) {
+        idx[(size_t)q * k] = -2;
+        flagged[atomicAdd(nflagged, 1u)] = q;
+      }
+      return;
+    }
+    int P = 64;
+    while (P < kept || P < k) P <<= 1;
+    for (int x = kept + threadIdx.x; x < P; x += blockDim.x) { keys[x].d = CUDART_INF; keys[x].i = LLONG_MAX; }
+    for (int size = 2; size <= P; size <<= 1)
+      for (int stride = size >> 1; stride > 0; stride >>= 1) {
+        __syncthreads();
+        for (int t = threadIdx.x; t < P / 2; t += blockDim.x) {
+          const int i = (t / stride) * 2 * stride + (t % stride), j = i + stride;
+          const Key a = keys[i], b = keys[j];
+          if (keyLess(b, a) == ((i & size) == 0)) { keys[i] = b; keys[j] = a; }
+        }
+      }
+    __syncthreads();
+    if (finalStage) {
+      for (int x = threadIdx.x; x < k; x += blockDim.x) {
+        idx[(size_t)q * k + x] = keys[x].i != LLONG_MAX ? keys[x].i : -1;
+        dist[(size_t)q * k + x] = keys[x].d;
+      }
+    } else if (threadIdx.x == 0) {
+      float t = TC_THR_MAX;
+      if (keys[k - 1].i != LLONG_MAX) {
+        double na = 0;
+        for (int c = 0; c < mv.nq; ++c) { const double x = scale[c] * sq[c]; na = fma(x, x, na); }
+        const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), -16) + 1e-30;
+        t = fminf(TC_THR_MAX, __double2float_ru(keys[k - 1].d * keys[k - 1].d * (1.0 + 1e-6) + eps));
+      }
+      if (cnt == nullptr || t < thr[q]) thr[q] = t;
+    }
+    return;
   }
   // 2. exact distances: 4 groups of 8 nodes per warp and trip
   Key acc = {CUDART_INF, LLONG_MAX}, ak = acc;
@@ -496,7 +558,7 @@ void knnTcDestroy(hppb200_knn* nn) {
 }
 
 bool knnTcEligible(const hppb200_knn* nn, size_t nqueries, int k, int32_t cc) {
-  return nn->tc_enabled && nn->tc_kc > 0 && cc < 0 && k >= 1 && k <= 32 && nn->n >= TC_MIN_NODES &&
+  return nn->tc_enabled && nn->tc_kc > 0 && cc < 0 && k >= 1 && k <= TC_MAX_K && nn->n >= TC_MIN_NODES &&
          nqueries >= (size_t)nn->tc_min_queries && nn->n < 0x7fffff00ull;
 }
 
@@ -572,7 +634,8 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   const int nq = nn->model->nq;
   const int nqtTotal = (int)((nqueries + TC_M - 1) / TC_M);
   tcReserve(nn, nqtTotal);
-  const size_t rerankSmem = ((size_t)nn->model->njoints + (size_t)nq) * sizeof(double) + TC_LIST * sizeof(int);
+  const size_t rerankSmem = ((size_t)nn->model->njoints + (size_t)nq) * sizeof(double) + TC_LIST * sizeof(int) + 16 +
+                            (k > 32 ? TC_KEYS * sizeof(Key) : 0);
   const unsigned rerankGrid = (unsigned)nqueries;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_tc_misc.p + 1, 0, sizeof(unsigned), nn->stream));
   // bootstrap: exact k-th distance over the first TC_PREFIX0 nodes -> first thresholds
@@ -581,7 +644,9 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
                                                                  nn->d_tc_misc.p + 1, nn->d_tc_flagged.p);
   // prefixes growing geometrically (<= TC_RATIO per stage) up to the whole roadmap
   const double ratio = (double)nn->n / (double)TC_PREFIX0;
-  const int nstages = std::max(1, (int)std::ceil(std::log(ratio) / std::log(TC_RATIO) - 1e-9));
+  // (large k: about 512 candidate groups per query and stage at most, so that the per-CTA lists do not overflow)
+  const double stageRatio = std::max(2.0, std::min(TC_RATIO, 512.0 / (double)k));
+  const int nstages = std::max(1, (int)std::ceil(std::log(ratio) / std::log(stageRatio) - 1e-9));
   for (int s = 1; s <= nstages; ++s) {
     size_t prefix = nn->n;
     if (s < nstages) {

@@ -26,12 +26,23 @@ class EngineBackend:
     def append(self, q, cc):
         self.nn.append(np.asarray(q, np.float64).reshape(1, -1), np.asarray([cc], np.int32))
 
+    def append_many(self, qs, ccs):
+        self.nn.append(np.asarray(qs, np.float64), np.asarray(ccs, np.int32))
+
     def relabel(self, old, new):
         self.nn.relabel(old, new)
 
     def nearest(self, qs, cc):
         idx, dist = self.nn.query(qs, 1, cc)
         return idx[:, 0], dist[:, 0]
+
+    def knearest(self, qs, k):
+        """Roadmap::nearestNodes(q, k) over the whole roadmap, nearest first (-1 padded)."""
+        return self.nn.query(qs, k, -1)[0]
+
+    def config_valid(self, qs):
+        """ConfigValidations::validate (collision validation + joint bounds as in the default problem)."""
+        return self.ws.validate_configs(qs, check_bounds=True)[0].astype(bool)
 
     def lengths(self, q1, q2):
         return self.ws.straight_lengths(q1, q2)
@@ -52,6 +63,8 @@ class Roadmap:
         self.nodes = np.zeros((0, nq))
         self.cc = []
         self.edges = []
+        self.edge_set = set()
+        self.next_cc = 1 << 20  # labels of components created by add_nodes (planners use small labels themselves)
 
     def add_node(self, q, cc):
         # Roadmap::addNode (:104-117): an existing node with exactly this configuration is reused
@@ -64,7 +77,32 @@ class Roadmap:
         self.b.append(q, cc)
         return len(self.cc) - 1
 
+    def add_nodes(self, qs):
+        """Roadmap::addNode for a batch of NEW configurations (each its own connected component): one append; a
+        configuration equal to an existing node is reused, as in :104-117 (looked up on the host here)."""
+        seen = getattr(self, "_seen", None)
+        if seen is None:
+            seen = self._seen = {self.nodes[i].tobytes(): i for i in range(len(self.cc))}
+        out, fresh = [], []
+        for q in qs:
+            key = q.tobytes()
+            if key not in seen:
+                seen[key] = len(self.cc) + len(fresh)
+                fresh.append(q)
+            out.append(seen[key])
+        if fresh:
+            ccs = list(range(self.next_cc, self.next_cc + len(fresh)))
+            self.next_cc += len(fresh)
+            self.nodes = np.vstack([self.nodes, np.asarray(fresh)])
+            self.cc.extend(ccs)
+            self.b.append_many(np.asarray(fresh), ccs)
+        return out
+
+    def has_edge(self, a, b):
+        return (a, b) in self.edge_set or (b, a) in self.edge_set
+
     def add_edge(self, a, b):
+        self.edge_set.add((a, b))
         self.edges.append((a, b))
         ca, cb = self.cc[a], self.cc[b]
         if ca != cb:  # ConnectedComponent::merge: the second component joins the first
@@ -195,3 +233,111 @@ class BiRRTPlanner:
             out.append(n)
             n = prev[n]
         return out[::-1]
+
+
+class KPrmStar:
+    """kPrmStar (reference src/path-planner/k-prm-star.cc:59-222) on the same backend interface.
+
+    `solve_sequential` follows the reference state machine item by item: BUILD_ROADMAP (generateRandomConfig :100-132:
+    shoot until valid, at most 10000 tries, addNode, until numberOfNodes nodes), LINK_NODES (linkNodes :134-151 +
+    connectNodeToClosestNeighbors :153-193: every node in insertion order against its k = floor(2e ln N + .5) nearest
+    nodes of the WHOLE roadmap, nearest first, skipping itself and neighbours that already have an edge to it;
+    steer, validate forward, addEdges), CONNECT_INIT_GOAL (:195-217).
+    `solve_batch` produces the same roadmap from four batches: configurations validated together (shots consumed in
+    the same order), ONE k-NN call for all nodes, the edge validations the reference always performs, then the ones
+    it performs only because the mirrored edge failed (a node pair (i, j), i > j, i among j's neighbours, is tried
+    from i only if j -> i was invalid).  CONNECT_INIT_GOAL repeats validations whose (deterministic) outcome is known
+    and cannot add an edge, so the batch form has nothing to do there."""
+
+    K_PRM = 2.0 * np.e
+
+    def __init__(self, backend, desc, q_init, q_goal, number_of_nodes, seed=1):
+        if number_of_nodes <= 0:
+            raise RuntimeError("kPrmStar: Number nodes should be positive, got %d" % number_of_nodes)  # :63-67
+        self.b, self.desc, self.seed, self.n = backend, desc, seed, int(number_of_nodes)
+        self.k = int(np.floor(self.K_PRM * np.log(float(self.n)) + 0.5))
+        self.roadmap = Roadmap(backend, desc.nq)
+        self.init = self.roadmap.add_node(np.asarray(q_init, np.float64), 0)
+        self.goal = self.roadmap.add_node(np.asarray(q_goal, np.float64), 1)
+        self.shots = 0
+
+    def solved(self):
+        return self.roadmap.cc[self.init] == self.roadmap.cc[self.goal]
+
+    def _edge_valid(self, i, j):
+        rm = self.roadmap
+        qi, qj = rm.nodes[i].reshape(1, -1), rm.nodes[j].reshape(1, -1)
+        return bool(self.b.validate(qi, qj, self.b.lengths(qi, qj), False)[0][0])
+
+    def _connect(self, i, nbrs):
+        rm = self.roadmap
+        for j in nbrs:
+            j = int(j)
+            if j >= 0 and j != i and not rm.has_edge(j, i) and self._edge_valid(i, j):
+                rm.add_edge(i, j)
+
+    def solve_sequential(self):
+        rm, b = self.roadmap, self.b
+        while len(rm.cc) < self.n:
+            tries, valid = 0, False
+            while not valid and tries < 10000:
+                q = uniform_configs(self.desc, 1, seed=self.seed, offset=self.shots)
+                self.shots += 1
+                valid = bool(b.config_valid(q)[0])
+                tries += 1
+            if not valid:
+                raise RuntimeError("Failed to generate free configuration after 10000 trials.")
+            rm.add_nodes(q)
+        for i in range(len(rm.cc)):
+            self._connect(i, b.knearest(rm.nodes[i].reshape(1, -1), self.k)[0])
+        if not any(self.init in e for e in rm.edges):
+            self._connect(self.init, b.knearest(rm.nodes[self.init].reshape(1, -1), self.k)[0])
+        if not any(self.goal in e for e in rm.edges):
+            self._connect(self.goal, b.knearest(rm.nodes[self.goal].reshape(1, -1), self.k)[0])
+        return self.solved()
+
+    def solve_batch(self, shoot_batch=4096):
+        rm, b = self.roadmap, self.b
+        invalid_run = 0
+        while len(rm.cc) < self.n:
+            q = uniform_configs(self.desc, shoot_batch, seed=self.seed, offset=self.shots)
+            ok = b.config_valid(q)
+            take = np.nonzero(ok)[0][:self.n - len(rm.cc)]
+            used = shoot_batch if len(rm.cc) + len(take) < self.n else int(take[-1]) + 1  # shots the reference consumes
+            run = invalid_run
+            for v in ok[:used]:
+                run = 0 if v else run + 1
+                if run >= 10000:
+                    raise RuntimeError("Failed to generate free configuration after 10000 trials.")
+            invalid_run = run
+            self.shots += used
+            rm.add_nodes(q[take])
+        n = len(rm.cc)
+        nbrs = b.knearest(rm.nodes, self.k)
+        nbr_sets = [set(int(x) for x in row if x >= 0) for row in nbrs]
+        first, second = [], []  # always validated / validated only when the mirrored edge failed
+        for i in range(n):
+            for j in nbrs[i]:
+                j = int(j)
+                if j < 0 or j == i:
+                    continue
+                (second if (j < i and i in nbr_sets[j]) else first).append((i, j))
+
+        def validate(pairs):
+            if not pairs:
+                return {}
+            a = np.array([p[0] for p in pairs])
+            c = np.array([p[1] for p in pairs])
+            qa, qc = rm.nodes[a], rm.nodes[c]
+            ok = b.validate(qa, qc, b.lengths(qa, qc), False)[0]
+            return {p: bool(v) for p, v in zip(pairs, ok)}
+
+        ok = validate(first)
+        ok.update(validate([(i, j) for (i, j) in second if not ok[(j, i)]]))
+        self.validated_edges = len(ok)
+        for i in range(n):
+            for j in nbrs[i]:
+                j = int(j)
+                if j >= 0 and j != i and not rm.has_edge(j, i) and ok.get((i, j), False):
+                    rm.add_edge(i, j)
+        return self.solved()

@@ -1,0 +1,42 @@
+"""The planner backend interface of hpp-core_b200/planners.py answered by the CPU oracle (test infrastructure:
+only tests may import oracle/)."""
+import numpy as np
+
+
+class OracleBackend:
+    """The same calls as EngineBackend, answered by the CPU oracle."""
+
+    def __init__(self, o, method, param):
+        self.o, self.method, self.param = o, method, param
+
+    def append(self, q, cc):
+        self.o.knn_append(np.asarray(q, np.float64).reshape(1, -1), np.asarray([cc], np.int32))
+
+    def append_many(self, qs, ccs):
+        self.o.knn_append(np.asarray(qs, np.float64), np.asarray(ccs, np.int32))
+
+    def relabel(self, old, new):
+        self.o.knn_relabel(old, new)
+
+    def nearest(self, qs, cc):
+        idx, dist = self.o.knn_query(qs, 1, cc)
+        return idx[:, 0], dist[:, 0]
+
+    def knearest(self, qs, k):
+        idx, dist = self.o.knn_query(np.asarray(qs, np.float64), k, -1)
+        srt = np.lexsort((idx, dist), axis=1)  # ties of std::priority_queue canonicalised by node index
+        idx = np.take_along_axis(idx, srt, axis=1)
+        return idx
+
+    def config_valid(self, qs):
+        return self.o.validate_configs(qs, check_bounds=True)[0].astype(bool)
+
+    def lengths(self, q1, q2):
+        return self.o.straight_lengths(q1, q2)
+
+    def validate(self, q1, q2, L, reverse):
+        r = self.o.validate_edges(self.method, self.param, q1, q2, L, reverse=reverse)
+        return r["valid"].astype(bool), r["t_last_valid"]
+
+    def path_eval(self, q1, q2, L, t):
+        return self.o.interpolate(q1, q2, L, t)

@@ -277,7 +277,7 @@ def test_knn_tensor_core_pass_matches_exact_scan_and_oracle(pkg, eng, ur5, ob, m
     for upto in (20000, 20001, 70000, 300000):  # appends between queries: the operand tiles follow the mirror
         nn.append(nodes[done:upto]); ex.append(nodes[done:upto]); o.knn_append(nodes[done:upto], None)
         done = upto
-        for k, nqry in ((1, 333), (10, 333), (32, 40), (7, 129)):
+        for k, nqry in ((1, 333), (10, 333), (32, 40), (7, 129), (33, 64), (75, 100)):
             gi, gd = nn.query(qs[:nqry], k)
             st = nn.tc_stats()
             assert st["used"] and st["redone"] == 0, st
@@ -318,6 +318,27 @@ def test_knn_tensor_core_pass_clustered_roadmap(pkg, eng, ur5, monkeypatch):
         assert st["used"]
         assert np.array_equal(gi, ei) and np.array_equal(gd, ed), k
     assert st["redone"] > 0  # the cluster queries overflowed their lists (3750 chunks of 32 nodes over 148 CTAs)
+
+
+def test_kprm_star_batch_same_roadmap_as_oracle(pkg, ob):
+    """kPRM* (src/path-planner/k-prm-star.cc) from four batches on the engine -- configurations, ONE k-NN call over
+    all nodes (k = 53 > 32: tensor-core pass + sorted exact re-rank), two edge batches -- next to the same planner on
+    the oracle: same nodes, same edges in the same order, same components."""
+    desc = pkg.ModelDescription.load("ur5_boxes8.json")
+    o = ob.Oracle(desc)
+    cand = pkg.uniform_configs(desc, 400, seed=5)
+    free = cand[o.validate_configs(cand, check_bounds=True)[0] == 1]
+    n = 17000
+    eb = pkg.EngineBackend(pkg, pkg.Model(desc), 0, 1, 1e-3)
+    gpu = pkg.KPrmStar(eb, desc, free[0], free[1], n, seed=21)
+    cpu = pkg.KPrmStar(_OracleBackend(ob.Oracle(desc), 1, 1e-3), desc, free[0], free[1], n, seed=21)
+    assert gpu.k == 53
+    sg, sc = gpu.solve_batch(), cpu.solve_batch()
+    assert eb.nn.tc_stats()["used"] and eb.nn.tc_stats()["redone"] == 0
+    assert sg == sc and gpu.shots == cpu.shots and gpu.validated_edges == cpu.validated_edges
+    assert np.array_equal(gpu.roadmap.nodes, cpu.roadmap.nodes)
+    assert gpu.roadmap.edges == cpu.roadmap.edges and gpu.roadmap.cc == cpu.roadmap.cc
+    assert len(gpu.roadmap.edges) > n
 
 
 def test_knn_tensor_core_full_size(pkg, eng, ur5, monkeypatch):
@@ -620,31 +641,7 @@ def test_wavefront_dichotomy_other_scenes(pkg, ob, monkeypatch, name):
         assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
 
 
-class _OracleBackend:
-    """The same five calls as EngineBackend, answered by the CPU oracle (test infrastructure)."""
-
-    def __init__(self, o, method, param):
-        self.o, self.method, self.param = o, method, param
-
-    def append(self, q, cc):
-        self.o.knn_append(np.asarray(q, np.float64).reshape(1, -1), np.asarray([cc], np.int32))
-
-    def relabel(self, old, new):
-        self.o.knn_relabel(old, new)
-
-    def nearest(self, qs, cc):
-        idx, dist = self.o.knn_query(qs, 1, cc)
-        return idx[:, 0], dist[:, 0]
-
-    def lengths(self, q1, q2):
-        return self.o.straight_lengths(q1, q2)
-
-    def validate(self, q1, q2, L, reverse):
-        r = self.o.validate_edges(self.method, self.param, q1, q2, L, reverse=reverse)
-        return r["valid"].astype(bool), r["t_last_valid"]
-
-    def path_eval(self, q1, q2, L, t):
-        return self.o.interpolate(q1, q2, L, t)
+from oracle_backend import OracleBackend as _OracleBackend  # noqa: E402  (tests/oracle_backend.py)
 
 
 @pytest.mark.parametrize("name,method,param,batch", [("ur5_boxes8.json", 1, 1e-3, 0), ("ur5_boxes8.json", 2, 0.0, 0),
