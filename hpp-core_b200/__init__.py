@@ -51,7 +51,7 @@ ABI_SYMBOLS = [
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
     "hppb200_validate_configs", "hppb200_geometry_placements", "hppb200_pair_distances",
     "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_workspace_set_max_iterations",
-    "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_size",
+    "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_set_labels", "hppb200_knn_size",
     "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_tc_debug_tile",
 ]
 
@@ -278,6 +278,10 @@ class NearestNeighbor:
 
     def relabel(self, from_cc, to_cc):
         _check(lib().hppb200_knn_relabel(self.h, C.c_int32(from_cc), C.c_int32(to_cc)))
+
+    def set_labels(self, cc):
+        cc = np.ascontiguousarray(cc, np.int32)
+        _check(lib().hppb200_knn_set_labels(self.h, _p(cc, _ip), C.c_size_t(cc.shape[0])))
 
     def query(self, queries, k=1, cc=-1):
         queries = np.ascontiguousarray(queries, np.float64).reshape(-1, self.model.nq)

@@ -378,6 +378,17 @@ int hppb200_knn_relabel(hppb200_knn* nn, int32_t from_cc, int32_t to_cc) {
   });
 }
 
+int hppb200_knn_set_labels(hppb200_knn* nn, const int32_t* cc, size_t n) {
+  return guardedKnn([&] {
+    if (!nn || (n && !cc)) throw std::invalid_argument("null argument");
+    if (n != nn->n) throw std::invalid_argument("label count differs from the number of nodes");
+    if (n == 0) return;
+    HPPB200_CUDA_CHECK(cudaSetDevice(nn->device));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(nn->d_cc, cc, n * sizeof(int32_t), cudaMemcpyHostToDevice, nn->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
+  });
+}
+
 int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, int k, int32_t cc, uint32_t flags,
                       int64_t* idx, double* dist) {
   return guardedKnn([&] {

@@ -528,6 +528,8 @@ static int tcStages(int nqt, int kc) {
 void knnTcInit(hppb200_knn* nn) {
   if (const char* v = std::getenv("HPPB200_KNN_TC")) nn->tc_enabled = std::atoi(v) != 0;
   if (const char* v = std::getenv("HPPB200_KNN_TC_MIN")) nn->tc_min_queries = std::max(1, std::atoi(v));
+  nn->tc_ratio = TC_RATIO;
+  if (const char* v = std::getenv("HPPB200_KNN_TC_RATIO")) nn->tc_ratio = std::max(2.0, std::atof(v));
   nn->tc_kc = 0;
   if (nn->ff) return;
   const int nq = nn->model->nq;
@@ -645,7 +647,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   // prefixes growing geometrically (<= TC_RATIO per stage) up to the whole roadmap
   const double ratio = (double)nn->n / (double)TC_PREFIX0;
   // (large k: about 512 candidate groups per query and stage at most, so that the per-CTA lists do not overflow)
-  const double stageRatio = std::max(2.0, std::min(TC_RATIO, 512.0 / (double)k));
+  const double stageRatio = std::max(2.0, std::min(nn->tc_ratio, 512.0 / (double)k));
   const int nstages = std::max(1, (int)std::ceil(std::log(ratio) / std::log(stageRatio) - 1e-9));
   for (int s = 1; s <= nstages; ++s) {
     size_t prefix = nn->n;

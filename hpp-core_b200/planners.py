@@ -32,6 +32,9 @@ class EngineBackend:
     def relabel(self, old, new):
         self.nn.relabel(old, new)
 
+    def set_labels(self, cc):
+        self.nn.set_labels(cc)
+
     def nearest(self, qs, cc):
         idx, dist = self.nn.query(qs, 1, cc)
         return idx[:, 0], dist[:, 0]
@@ -62,9 +65,26 @@ class Roadmap:
         self.b = backend
         self.nodes = np.zeros((0, nq))
         self.cc = []
-        self.edges = []
-        self.edge_set = set()
+        self._edges, self._edge_set, self._blocks, self._set_upto = [], set(), [], 0
         self.next_cc = 1 << 20  # labels of components created by add_nodes (planners use small labels themselves)
+
+    @property
+    def edges(self):
+        """(a, b) in insertion order; bulk additions are kept as arrays until somebody looks"""
+        for blk in self._blocks:
+            self._edges.extend(map(tuple, blk.tolist()))
+        self._blocks = []
+        return self._edges
+
+    @property
+    def edge_set(self):
+        e = self.edges
+        self._edge_set.update(e[self._set_upto:])
+        self._set_upto = len(e)
+        return self._edge_set
+
+    def num_edges(self):
+        return len(self._edges) + sum(len(b) for b in self._blocks)
 
     def add_node(self, q, cc):
         # Roadmap::addNode (:104-117): an existing node with exactly this configuration is reused
@@ -98,11 +118,51 @@ class Roadmap:
             self.b.append_many(np.asarray(fresh), ccs)
         return out
 
+    def add_edges(self, pairs):
+        """`add_edge` for many edges in the given order with the same final state: the component merges are those of
+        the first-come spanning forest (minimum spanning forest with the edge rank as weight), replayed in order; the
+        device mirror receives the final labels in one call."""
+        from scipy.sparse import coo_matrix
+        from scipy.sparse.csgraph import minimum_spanning_tree
+        pairs = np.asarray(pairs, np.int64).reshape(-1, 2)
+        if len(pairs) == 0:
+            return
+        self._blocks.append(pairs)
+        n = len(self.cc)
+        cc = np.asarray(self.cc, np.int64)
+        labels, rep = np.unique(cc, return_index=True)           # first node of every existing component
+        rep_of = rep[np.searchsorted(labels, cc)]
+        a, c = rep_of[pairs[:, 0]], rep_of[pairs[:, 1]]
+        keep = a != c
+        lo, hi = np.minimum(a, c), np.maximum(a, c)
+        _, firsts = np.unique((lo * n + hi)[keep], return_index=True)
+        ranks = np.nonzero(keep)[0][firsts]                      # first occurrence of every unordered component pair
+        g = coo_matrix((ranks + 1.0, (lo[ranks], hi[ranks])), shape=(n, n))
+        msf = minimum_spanning_tree(g.tocsr()).tocoo()
+        merge_ranks = np.sort(msf.data.astype(np.int64) - 1)
+        parent = np.arange(n)
+
+        def root(x):
+            while parent[x] != x:
+                parent[x] = parent[parent[x]]
+                x = parent[x]
+            return x
+
+        for r in merge_ranks:                                    # ConnectedComponent::merge: the second joins the first
+            ra, rc = root(a[r]), root(c[r])
+            if ra != rc:
+                parent[rc] = ra
+        final = np.arange(n)
+        for x in rep.tolist():
+            final[x] = root(x)
+        new_cc = cc[final[rep_of]]
+        self.cc = new_cc.tolist()
+        self.b.set_labels(new_cc.astype(np.int32))
+
     def has_edge(self, a, b):
         return (a, b) in self.edge_set or (b, a) in self.edge_set
 
     def add_edge(self, a, b):
-        self.edge_set.add((a, b))
         self.edges.append((a, b))
         ca, cb = self.cc[a], self.cc[b]
         if ca != cb:  # ConnectedComponent::merge: the second component joins the first
@@ -297,7 +357,10 @@ class KPrmStar:
         return self.solved()
 
     def solve_batch(self, shoot_batch=4096):
+        import time
         rm, b = self.roadmap, self.b
+        tm = self.timings = {}
+        t0 = time.perf_counter()
         invalid_run = 0
         while len(rm.cc) < self.n:
             q = uniform_configs(self.desc, shoot_batch, seed=self.seed, offset=self.shots)
@@ -313,31 +376,44 @@ class KPrmStar:
             self.shots += used
             rm.add_nodes(q[take])
         n = len(rm.cc)
-        nbrs = b.knearest(rm.nodes, self.k)
-        nbr_sets = [set(int(x) for x in row if x >= 0) for row in nbrs]
-        first, second = [], []  # always validated / validated only when the mirrored edge failed
-        for i in range(n):
-            for j in nbrs[i]:
-                j = int(j)
-                if j < 0 or j == i:
-                    continue
-                (second if (j < i and i in nbr_sets[j]) else first).append((i, j))
+        tm["nodes (shoot + config validation + append)"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        nbrs = np.asarray(b.knearest(rm.nodes, self.k), np.int64)
+        tm["k-NN (one call)"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        i_of = np.repeat(np.arange(n, dtype=np.int64), nbrs.shape[1])
+        j_of = nbrs.ravel()
+        cand = (j_of >= 0) & (j_of != i_of)                      # directed candidates (i, j), j among i's neighbours
+        keys = np.sort((i_of * n + j_of)[cand])
+        mirror = j_of * n + i_of                                 # is i among j's neighbours?
+        pos = np.minimum(np.searchsorted(keys, mirror), max(len(keys) - 1, 0))
+        mirrored = cand & (keys[pos] == mirror) if len(keys) else np.zeros_like(cand)
+        second = cand & (j_of < i_of) & mirrored                 # tried by the reference only if j -> i was invalid
+        first = cand & ~second                                   # always tried
 
-        def validate(pairs):
-            if not pairs:
-                return {}
-            a = np.array([p[0] for p in pairs])
-            c = np.array([p[1] for p in pairs])
+        def validate(sel):
+            a, c = i_of[sel], j_of[sel]
+            if len(a) == 0:
+                return np.zeros(0, bool)
             qa, qc = rm.nodes[a], rm.nodes[c]
-            ok = b.validate(qa, qc, b.lengths(qa, qc), False)[0]
-            return {p: bool(v) for p, v in zip(pairs, ok)}
+            return np.asarray(b.validate(qa, qc, b.lengths(qa, qc), False)[0], bool)
 
-        ok = validate(first)
-        ok.update(validate([(i, j) for (i, j) in second if not ok[(j, i)]]))
-        self.validated_edges = len(ok)
-        for i in range(n):
-            for j in nbrs[i]:
-                j = int(j)
-                if j >= 0 and j != i and not rm.has_edge(j, i) and ok.get((i, j), False):
-                    rm.add_edge(i, j)
+        ok = np.zeros(len(i_of), bool)
+        f_idx = np.nonzero(first)[0]
+        tm["candidate pairs (host)"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        ok[f_idx] = validate(f_idx)
+        # outcome of the mirrored edge (j, i) of every `second` candidate: it is a `first` candidate of node j
+        f_keys = (i_of * n + j_of)[f_idx]
+        order = np.argsort(f_keys)
+        s_idx = np.nonzero(second)[0]
+        m_ok = ok[f_idx[order[np.searchsorted(f_keys[order], mirror[s_idx])]]] if len(s_idx) else np.zeros(0, bool)
+        s_idx = s_idx[~m_ok]
+        ok[s_idx] = validate(s_idx)
+        self.validated_edges = int(len(f_idx) + len(s_idx))
+        tm["edge validation (two batches, host gathers included)"] = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        e_idx = np.nonzero(ok)[0]                                # node by node, nearest neighbour first: the reference order
+        rm.add_edges(np.stack([i_of[e_idx], j_of[e_idx]], axis=1))
+        tm["roadmap edges + components (host)"] = time.perf_counter() - t0
         return self.solved()

@@ -263,6 +263,9 @@ void hppb200_knn_destroy(hppb200_knn* nn);
    label per node (may be NULL = 0). */
 int hppb200_knn_append(hppb200_knn* nn, const double* q, const int32_t* cc, size_t n);
 int hppb200_knn_relabel(hppb200_knn* nn, int32_t from_cc, int32_t to_cc);
+/* All connected-component labels at once, cc [n], n == hppb200_knn_size (many ConnectedComponent::merge calls of a
+   batched planner step collapsed into their final labelling; reference src/roadmap.cc:209-255). */
+int hppb200_knn_set_labels(hppb200_knn* nn, const int32_t* cc, size_t n);
 size_t hppb200_knn_size(const hppb200_knn* nn);
 /* queries [nqueries][nq]; cc < 0 searches the whole roadmap.  idx [nqueries][k]
    nearest first (-1 padded), dist [nqueries][k]. */

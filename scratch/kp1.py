@@ -28,7 +28,7 @@ for k in (33, 75, 128):
 o = ob.Oracle(ur5)
 cand = pkg.uniform_configs(ur5, 400, seed=5)
 free = cand[o.validate_configs(cand, check_bounds=True)[0] == 1]
-for n in (17000, 100000):
+for n in (17000, 100000, 400000):
     eb = pkg.EngineBackend(pkg, m, 0, 1, 1e-3)
     gpu = pkg.KPrmStar(eb, ur5, free[0], free[1], n, seed=21)
     t0 = time.perf_counter(); gpu.solve_batch(); tg = time.perf_counter() - t0

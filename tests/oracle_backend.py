@@ -9,14 +9,30 @@ class OracleBackend:
     def __init__(self, o, method, param):
         self.o, self.method, self.param = o, method, param
 
+    def _track(self, ccs):
+        self._labels = np.concatenate([getattr(self, "_labels", np.zeros(0, np.int64)), np.asarray(ccs, np.int64).ravel()])
+
     def append(self, q, cc):
+        self._track([cc])
         self.o.knn_append(np.asarray(q, np.float64).reshape(1, -1), np.asarray([cc], np.int32))
 
     def append_many(self, qs, ccs):
+        self._track(ccs)
         self.o.knn_append(np.asarray(qs, np.float64), np.asarray(ccs, np.int32))
 
     def relabel(self, old, new):
+        self._labels[self._labels == old] = new
         self.o.knn_relabel(old, new)
+
+    def set_labels(self, cc):
+        """final labels of a bulk merge, replayed as (old -> new) relabels of the nodes whose label changed"""
+        cc = np.asarray(cc, np.int64)
+        old = getattr(self, "_labels", None)
+        if old is None or len(old) != len(cc):
+            raise RuntimeError("set_labels needs the labels given at append time")
+        for o_, n_ in sorted({(int(a), int(b)) for a, b in zip(old, cc) if a != b}):
+            self.o.knn_relabel(o_, n_)
+        self._labels = cc.copy()
 
     def nearest(self, qs, cc):
         idx, dist = self.o.knn_query(qs, 1, cc)
