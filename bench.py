@@ -306,8 +306,12 @@ def run_b200(args):
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     roofline = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": "hppb200_measure_fp64_peak (DFMA chains, measured live)",
-                "kernel": "validateConfigsKernel", "algorithmic_flops_per_config": work["flops_per_config"],
+                # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, 1 M configurations
+                # (profiles/r1b_configPass_gjkJobs_ncu_full.txt): the placement scratch written once per configuration;
+                # removing it was measured slower
+                "traffic": 832.2e6 if n == (1 << 20) else None, "traffic_unit": "B per launch of configPassKernel",
+                "peak_source": "hppb200_measure_fp64_peak (DFMA chains, measured live)",
+                "kernel": "configPassKernel + gjkJobsKernel", "algorithmic_flops_per_config": work["flops_per_config"],
                 "hbm": {"achieved": BYTES_PER_CONFIG * n / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
                         "frac": BYTES_PER_CONFIG * n / per_launch_s / 1e9 / hbm_peak,
                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},

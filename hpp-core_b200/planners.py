@@ -39,9 +39,10 @@ class EngineBackend:
         idx, dist = self.nn.query(qs, 1, cc)
         return idx[:, 0], dist[:, 0]
 
-    def knearest(self, qs, k):
+    def knearest(self, qs, k, with_dist=False):
         """Roadmap::nearestNodes(q, k) over the whole roadmap, nearest first (-1 padded)."""
-        return self.nn.query(qs, k, -1)[0]
+        idx, dist = self.nn.query(qs, k, -1)
+        return (idx, dist) if with_dist else idx
 
     def config_valid(self, qs):
         """ConfigValidations::validate (collision validation + joint bounds as in the default problem)."""
@@ -320,6 +321,7 @@ class KPrmStar:
         self.init = self.roadmap.add_node(np.asarray(q_init, np.float64), 0)
         self.goal = self.roadmap.add_node(np.asarray(q_goal, np.float64), 1)
         self.shots = 0
+        self.symmetric_distance = int(desc.nq) == int(getattr(desc, "nv", desc.nq))  # no free-flyer joint
 
     def solved(self):
         return self.roadmap.cc[self.init] == self.roadmap.cc[self.goal]
@@ -378,16 +380,26 @@ class KPrmStar:
         n = len(rm.cc)
         tm["nodes (shoot + config validation + append)"] = time.perf_counter() - t0
         t0 = time.perf_counter()
-        nbrs = np.asarray(b.knearest(rm.nodes, self.k), np.int64)
+        nbrs, dist = b.knearest(rm.nodes, self.k, with_dist=True)
+        nbrs = np.asarray(nbrs, np.int64)
         tm["k-NN (one call)"] = time.perf_counter() - t0
         t0 = time.perf_counter()
         i_of = np.repeat(np.arange(n, dtype=np.int64), nbrs.shape[1])
         j_of = nbrs.ravel()
         cand = (j_of >= 0) & (j_of != i_of)                      # directed candidates (i, j), j among i's neighbours
-        keys = np.sort((i_of * n + j_of)[cand])
-        mirror = j_of * n + i_of                                 # is i among j's neighbours?
-        pos = np.minimum(np.searchsorted(keys, mirror), max(len(keys) - 1, 0))
-        mirrored = cand & (keys[pos] == mirror) if len(keys) else np.zeros_like(cand)
+        mirror = j_of * n + i_of
+        if getattr(self.desc, "has_freeflyer", False) or not self.symmetric_distance:
+            keys = np.sort((i_of * n + j_of)[cand])              # is i among j's neighbours?  by lookup
+            pos = np.minimum(np.searchsorted(keys, mirror), max(len(keys) - 1, 0))
+            mirrored = cand & (keys[pos] == mirror) if len(keys) else np.zeros_like(cand)
+        else:
+            # WeighedDistance on a vector space is symmetric bit for bit ((a - b)^2 == (b - a)^2, same summation order),
+            # and the k nearest are the k smallest (distance, index) keys: i is among j's neighbours iff its key is not
+            # above j's last one
+            jj = np.where(cand, j_of, 0)
+            d_ij = np.asarray(dist).ravel()
+            d_last, i_last = np.asarray(dist)[jj, -1], nbrs[jj, -1]
+            mirrored = cand & ((i_last < 0) | (d_ij < d_last) | ((d_ij == d_last) & (i_of <= i_last)))
         second = cand & (j_of < i_of) & mirrored                 # tried by the reference only if j -> i was invalid
         first = cand & ~second                                   # always tried
 
@@ -403,11 +415,14 @@ class KPrmStar:
         tm["candidate pairs (host)"] = time.perf_counter() - t0
         t0 = time.perf_counter()
         ok[f_idx] = validate(f_idx)
-        # outcome of the mirrored edge (j, i) of every `second` candidate: it is a `first` candidate of node j
-        f_keys = (i_of * n + j_of)[f_idx]
-        order = np.argsort(f_keys)
+        # outcome of the mirrored edge (j, i) of every `second` candidate: it is a mirrored `first` candidate of node j
+        # (j < i); both sets hold every mirrored unordered pair once, so sorting by the pair key aligns them
+        fm_idx = np.nonzero(first & mirrored & (i_of < j_of))[0]
         s_idx = np.nonzero(second)[0]
-        m_ok = ok[f_idx[order[np.searchsorted(f_keys[order], mirror[s_idx])]]] if len(s_idx) else np.zeros(0, bool)
+        fm_idx = fm_idx[np.argsort((i_of * n + j_of)[fm_idx])]
+        s_idx = s_idx[np.argsort(mirror[s_idx])]
+        assert len(fm_idx) == len(s_idx)
+        m_ok = ok[fm_idx]
         s_idx = s_idx[~m_ok]
         ok[s_idx] = validate(s_idx)
         self.validated_edges = int(len(f_idx) + len(s_idx))

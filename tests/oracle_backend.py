@@ -38,11 +38,11 @@ class OracleBackend:
         idx, dist = self.o.knn_query(qs, 1, cc)
         return idx[:, 0], dist[:, 0]
 
-    def knearest(self, qs, k):
+    def knearest(self, qs, k, with_dist=False):
         idx, dist = self.o.knn_query(np.asarray(qs, np.float64), k, -1)
         srt = np.lexsort((idx, dist), axis=1)  # ties of std::priority_queue canonicalised by node index
-        idx = np.take_along_axis(idx, srt, axis=1)
-        return idx
+        idx, dist = np.take_along_axis(idx, srt, axis=1), np.take_along_axis(dist, srt, axis=1)
+        return (idx, dist) if with_dist else idx
 
     def config_valid(self, qs):
         return self.o.validate_configs(qs, check_bounds=True)[0].astype(bool)
