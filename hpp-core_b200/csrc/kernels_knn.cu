@@ -16,6 +16,7 @@
 namespace hppb200 {
 
 constexpr int KNN_THREADS = 256;
+constexpr size_t KNN_STAGE_BYTES = 256 * 1024;
 
 // ---- tiled scan: the whole GPU works on every query -------------------------------------------------
 // Grid (node tiles, query groups): a CTA scans ITS contiguous slice of the node stream once per selection
@@ -57,7 +58,7 @@ knnTileKernel(ModelView mv, const double* __restrict__ nodes, const int32_t* __r
 #pragma unroll
   for (int j = 0; j < KNN_QB; ++j) {
     const int q = (q0 + j < nqueries) ? q0 + j : nqueries - 1;  // padding lanes repeat the last query
-    pv[j] = prev[q];
+    pv[j] = prev ? prev[q] : Key{-1.0, -1};  // (first pass: everything is admissible)
     best[j].d = CUDART_INF; best[j].i = LLONG_MAX;
   }
   for (size_t i = lo + threadIdx.x; i < hi; i += KNN_THREADS) {
@@ -276,21 +277,18 @@ void knnExactRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, int
   if (k > 1 && k <= 32) {  // single pass (k = 1 is one selection pass anyway, without the insertion logic)
     nn->d_keys.reserve(tiles * nqueries * (size_t)k * sizeof(Key) + 256);
     Key* d_part = (Key*)nn->d_keys.p;
-    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(topkKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
     topkKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nNodes, d_q,
                                                                                         (int)nqueries, cc, k, d_part);
     knnMergeTopkKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, d_i, d_d);
     HPPB200_CUDA_CHECK(cudaGetLastError());
     return;
   }
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(tileKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
   nn->d_keys.reserve((nqueries + tiles * nqueries) * sizeof(Key) + 256);
   Key* d_prev = (Key*)nn->d_keys.p;
   Key* d_part = d_prev + nqueries;
-  knnInitPrevKernel<<<(unsigned)((nqueries + 255) / 256), 256, 0, nn->stream>>>(d_prev, (int)nqueries);
   for (int r = 0; r < k; ++r) {
     tileKernel<<<dim3((unsigned)tiles, groups), KNN_THREADS, smemBytes, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nNodes, d_q,
-                                                                                    (int)nqueries, cc, d_prev, d_part);
+                                                                                    (int)nqueries, cc, r ? d_prev : nullptr, d_part);
     knnReduceKernel<<<(unsigned)((nqueries + 3) / 4), 128, 0, nn->stream>>>(d_part, (int)tiles, (int)nqueries, k, r, d_prev, d_i, d_d);
   }
   HPPB200_CUDA_CHECK(cudaGetLastError());
@@ -325,6 +323,15 @@ int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out) {
     HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&nn->stream, cudaStreamNonBlocking));
     HPPB200_CUDA_CHECK(cudaDeviceGetAttribute(&nn->num_sms, cudaDevAttrMultiProcessorCount, device));
     for (const DevJoint& J : nn->model->joints) nn->ff = nn->ff || J.type == HPPB200_JOINT_FREEFLYER;
+    {
+      const size_t smemBytes = 16 + nn->view.blob_bytes + ((size_t)KNN_QB * nn->model->nq + (size_t)nn->model->njoints) * sizeof(double);
+      HPPB200_CUDA_CHECK(cudaFuncSetAttribute(nn->ff ? knnTileKernel<true> : knnTileKernel<false>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+      HPPB200_CUDA_CHECK(cudaFuncSetAttribute(nn->ff ? knnTileTopkKernel<true> : knnTileTopkKernel<false>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
+      // pinned staging for small calls (a planner's single queries): truly asynchronous copies, one sync per call
+      HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&nn->h_stage, KNN_STAGE_BYTES, cudaHostAllocDefault));
+    }
     knnTcInit(nn);
     *out = nn;
   });
@@ -335,6 +342,7 @@ void hppb200_knn_destroy(hppb200_knn* nn) {
   if (nn->d_nodes) cudaFree(nn->d_nodes);
   if (nn->d_cc) cudaFree(nn->d_cc);
   knnTcDestroy(nn);
+  if (nn->h_stage) cudaFreeHost(nn->h_stage);
   if (nn->stream) cudaStreamDestroy(nn->stream);
   delete nn;
 }
@@ -410,10 +418,23 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
     nn->d_queries.reserve(nqueries * nq);
     nn->d_idx.reserve(nqueries * k);
     nn->d_dist.reserve(nqueries * k);
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(nn->d_queries.p, queries, nqueries * nq * sizeof(double), cudaMemcpyHostToDevice, nn->stream));
+    const size_t qBytes = nqueries * nq * sizeof(double), rBytes = nqueries * (size_t)k * sizeof(double);
+    if (qBytes + 2 * rBytes <= KNN_STAGE_BYTES) {  // small call: through the pinned staging block
+      unsigned char* h = nn->h_stage;
+      std::memcpy(h, queries, qBytes);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(nn->d_queries.p, h, qBytes, cudaMemcpyHostToDevice, nn->stream));
+      run(nn->d_queries.p, nn->d_idx.p, nn->d_dist.p);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(h + qBytes, nn->d_idx.p, rBytes, cudaMemcpyDeviceToHost, nn->stream));
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(h + qBytes + rBytes, nn->d_dist.p, rBytes, cudaMemcpyDeviceToHost, nn->stream));
+      HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
+      std::memcpy(idx, h + qBytes, rBytes);
+      std::memcpy(dist, h + qBytes + rBytes, rBytes);
+      return;
+    }
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(nn->d_queries.p, queries, qBytes, cudaMemcpyHostToDevice, nn->stream));
     run(nn->d_queries.p, nn->d_idx.p, nn->d_dist.p);
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(idx, nn->d_idx.p, nqueries * k * sizeof(int64_t), cudaMemcpyDeviceToHost, nn->stream));
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(dist, nn->d_dist.p, nqueries * k * sizeof(double), cudaMemcpyDeviceToHost, nn->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(idx, nn->d_idx.p, rBytes, cudaMemcpyDeviceToHost, nn->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(dist, nn->d_dist.p, rBytes, cudaMemcpyDeviceToHost, nn->stream));
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
   });
 }

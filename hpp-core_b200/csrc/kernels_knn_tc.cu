@@ -347,11 +347,27 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
   double* sw2 = (double*)rsm;
   double* sq = sw2 + mv.njoints;
   int* list = (int*)(sq + mv.nq);  // the query's candidate groups
+  int* sJoint = list + TC_LIST;    // per joint: configuration index * 2 + (1 if its distance term is weighted)
   const unsigned FULL = 0xffffffffu;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = blockIdx.x;
-  for (int j = threadIdx.x; j < mv.njoints; j += blockDim.x) { const double w = T.weights[j]; sw2[j] = w * w; }
+  for (int j = threadIdx.x; j < mv.njoints; j += blockDim.x) {
+    const double w = T.weights[j];
+    sw2[j] = w * w;
+    sJoint[j] = T.joints[j].idx_q * 2 + (T.joints[j].type <= HPPB200_JOINT_REVOLUTE_Z ? 1 : 0);
+  }
   for (int c = threadIdx.x; c < mv.nq; c += blockDim.x) sq[c] = queries[(size_t)q * mv.nq + c];
+  // WeighedDistance(node, query) with the joint records in shared memory: the operation order of
+  // weighedDistanceBatch<1, false> (dev_knn.cuh), hence the exact scan's bits
+  auto exactDistance = [&](const double* __restrict__ node) {
+    double d = 0;
+    for (int j = 0; j < mv.njoints; ++j) {
+      const int c = sJoint[j] >> 1;
+      const double dq = sq[c] - node[c];
+      d += (sJoint[j] & 1) ? sw2[j] * (dq * dq) : dq * dq;
+    }
+    return sqrt(d);
+  };
   // 1. the candidate groups, gathered by the lanes of warp 0 in parallel
   if (warp == 0) {
     int total = 0;
@@ -389,7 +405,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
   if (k > 32) {
     // 2'. k > 32: the exact keys not above the current threshold (an upper bound of the k-th squared distance, so no
     // top-k node is dropped) are collected in shared memory and sorted by a bitonic network; first k = the result
-    Key* keys = (Key*)(rsm + (((size_t)(mv.njoints + mv.nq) * sizeof(double) + TC_LIST * sizeof(int) + 15) & ~(size_t)15));
+    Key* keys = (Key*)(rsm + (((size_t)(mv.njoints + mv.nq) * sizeof(double) + (TC_LIST + mv.njoints) * sizeof(int) + 15) & ~(size_t)15));
     const double bound = cnt == nullptr ? CUDART_INF : (double)thr[q] * (1.0 + 1e-9);
     if (threadIdx.x == 0) sKept = 0;
     __syncthreads();
@@ -398,11 +414,10 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
       if (e < total) {
         const long long node = (long long)list[e] * 8 + (lane & 7);
         if ((size_t)node < n) {
-          double d1[1];
-          weighedDistanceBatch<1, false>(T, mv, nodes + (size_t)node * mv.nq, sq, sw2, d1);
-          if (d1[0] * d1[0] <= bound) {
+          const double d1 = exactDistance(nodes + (size_t)node * mv.nq);
+          if (d1 * d1 <= bound) {
             const int slot = atomicAdd(&sKept, 1);
-            if (slot < TC_KEYS) { keys[slot].d = d1[0]; keys[slot].i = node; }
+            if (slot < TC_KEYS) { keys[slot].d = d1; keys[slot].i = node; }
           }
         }
       }
@@ -462,11 +477,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
     Key c = {CUDART_INF, LLONG_MAX};
     if (e < total) {
       const long long node = (long long)list[e] * 8 + (lane & 7);
-      if ((size_t)node < n) {
-        double d1[1];
-        weighedDistanceBatch<1, false>(T, mv, nodes + (size_t)node * mv.nq, sq, sw2, d1);
-        c.d = d1[0]; c.i = node;
-      }
+      if ((size_t)node < n) { c.d = exactDistance(nodes + (size_t)node * mv.nq); c.i = node; }
     }
     offer(c);
   }
@@ -636,7 +647,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   const int nq = nn->model->nq;
   const int nqtTotal = (int)((nqueries + TC_M - 1) / TC_M);
   tcReserve(nn, nqtTotal);
-  const size_t rerankSmem = ((size_t)nn->model->njoints + (size_t)nq) * sizeof(double) + TC_LIST * sizeof(int) + 16 +
+  const size_t rerankSmem = ((size_t)nn->model->njoints + (size_t)nq) * sizeof(double) + (TC_LIST + (size_t)nn->model->njoints) * sizeof(int) + 16 +
                             (k > 32 ? TC_KEYS * sizeof(Key) : 0);
   const unsigned rerankGrid = (unsigned)nqueries;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_tc_misc.p + 1, 0, sizeof(unsigned), nn->stream));

@@ -15,6 +15,7 @@ struct hppb200_knn {
   hppb200::DeviceBuffer<long long> d_idx, d_count;
   hppb200::DeviceBuffer<unsigned char> d_keys;  // previous keys [Q] + per-tile partial keys [tiles][Q]
   int num_sms = 148;
+  unsigned char* h_stage = nullptr;  // pinned staging block for small query calls
 
   // ---- tensor-core candidate pass (kernels_knn_tc.cu) ----
   bool ff = false;           // the model has free-flyer joints (no GEMM form of the distance)
