@@ -339,6 +339,10 @@ def test_kprm_star_batch_same_roadmap_as_oracle(pkg, ob):
     assert np.array_equal(gpu.roadmap.nodes, cpu.roadmap.nodes)
     assert gpu.roadmap.edges == cpu.roadmap.edges and gpu.roadmap.cc == cpu.roadmap.cc
     assert len(gpu.roadmap.edges) > n
+    # the device mirror received the final component labels (hppb200_knn_set_labels): component-restricted searches agree
+    qs = pkg.uniform_configs(desc, 16, seed=77)
+    for lab in sorted(set(gpu.roadmap.cc))[:3]:
+        assert np.array_equal(eb.nearest(qs, lab)[0], cpu.b.nearest(qs, lab)[0])
 
 
 def test_knn_tensor_core_full_size(pkg, eng, ur5, monkeypatch):
