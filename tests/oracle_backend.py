@@ -3,6 +3,11 @@ only tests may import oracle/)."""
 import numpy as np
 
 
+def _threads(n):
+    """item-by-item planner calls stay on one thread (an OpenMP team per single edge only spins); batches use all"""
+    return 1 if n < 64 else 0
+
+
 class OracleBackend:
     """The same calls as EngineBackend, answered by the CPU oracle."""
 
@@ -35,23 +40,23 @@ class OracleBackend:
         self._labels = cc.copy()
 
     def nearest(self, qs, cc):
-        idx, dist = self.o.knn_query(qs, 1, cc)
+        idx, dist = self.o.knn_query(qs, 1, cc, nthreads=_threads(len(qs)))
         return idx[:, 0], dist[:, 0]
 
     def knearest(self, qs, k, with_dist=False):
-        idx, dist = self.o.knn_query(np.asarray(qs, np.float64), k, -1)
+        idx, dist = self.o.knn_query(np.asarray(qs, np.float64), k, -1, nthreads=_threads(len(qs)))
         srt = np.lexsort((idx, dist), axis=1)  # ties of std::priority_queue canonicalised by node index
         idx, dist = np.take_along_axis(idx, srt, axis=1), np.take_along_axis(dist, srt, axis=1)
         return (idx, dist) if with_dist else idx
 
     def config_valid(self, qs):
-        return self.o.validate_configs(qs, check_bounds=True)[0].astype(bool)
+        return self.o.validate_configs(qs, check_bounds=True, nthreads=_threads(len(qs)))[0].astype(bool)
 
     def lengths(self, q1, q2):
         return self.o.straight_lengths(q1, q2)
 
     def validate(self, q1, q2, L, reverse):
-        r = self.o.validate_edges(self.method, self.param, q1, q2, L, reverse=reverse)
+        r = self.o.validate_edges(self.method, self.param, q1, q2, L, reverse=reverse, nthreads=_threads(len(L)))
         return r["valid"].astype(bool), r["t_last_valid"]
 
     def path_eval(self, q1, q2, L, t):
