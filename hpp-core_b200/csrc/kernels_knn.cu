@@ -407,7 +407,7 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
     if (nqueries > 0x7fffffffull / 4) throw std::invalid_argument("too many queries in one call");
     auto run = [&](const double* d_q, long long* d_i, double* d_d) {
       nn->tc_last_used = false;
-      if (knnTcEligible(nn, nqueries, k, cc)) knnTcRun(nn, d_q, nqueries, k, d_i, d_d);
+      if (knnTcEligible(nn, nqueries, k, cc)) knnTcRun(nn, d_q, nqueries, k, cc, d_i, d_d);
       else knnExactRun(nn, d_q, nqueries, k, cc, nn->n, d_i, d_d);
     };
     if (flags & HPPB200_DEVICE_POINTERS) {

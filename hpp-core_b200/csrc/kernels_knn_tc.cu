@@ -339,7 +339,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
                   const double* __restrict__ scale, int nqueries, int k, const int* __restrict__ cnt, const int* __restrict__ cand,
                   int gused, int gstride, int capc, int prefixNodes, const unsigned* __restrict__ maxNorm, float* __restrict__ thr,
                   int finalStage, long long* __restrict__ idx, double* __restrict__ dist, unsigned* __restrict__ nflagged,
-                  int* __restrict__ flagged) {
+                  int* __restrict__ flagged, const int32_t* __restrict__ ccOf, int32_t ccFilter) {
   extern __shared__ __align__(16) unsigned char rsm[];
   __shared__ Key lists[TC_RR_WARPS][32];
   __shared__ int sTotal, sKept;
@@ -413,7 +413,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
       const int e = e0 + (lane >> 3);
       if (e < total) {
         const long long node = (long long)list[e] * 8 + (lane & 7);
-        if ((size_t)node < n) {
+        if ((size_t)node < n && (ccFilter < 0 || ccOf[node] == ccFilter)) {
           const double d1 = exactDistance(nodes + (size_t)node * mv.nq);
           if (d1 * d1 <= bound) {
             const int slot = atomicAdd(&sKept, 1);
@@ -477,7 +477,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
     Key c = {CUDART_INF, LLONG_MAX};
     if (e < total) {
       const long long node = (long long)list[e] * 8 + (lane & 7);
-      if ((size_t)node < n) { c.d = exactDistance(nodes + (size_t)node * mv.nq); c.i = node; }
+      if ((size_t)node < n && (ccFilter < 0 || ccOf[node] == ccFilter)) { c.d = exactDistance(nodes + (size_t)node * mv.nq); c.i = node; }
     }
     offer(c);
   }
@@ -571,7 +571,8 @@ void knnTcDestroy(hppb200_knn* nn) {
 }
 
 bool knnTcEligible(const hppb200_knn* nn, size_t nqueries, int k, int32_t cc) {
-  return nn->tc_enabled && nn->tc_kc > 0 && cc < 0 && k >= 1 && k <= TC_MAX_K && nn->n >= TC_MIN_NODES &&
+  (void)cc;  // a component filter is applied by the exact re-rank; sparse components end in the exact scan
+  return nn->tc_enabled && nn->tc_kc > 0 && k >= 1 && k <= TC_MAX_K && nn->n >= TC_MIN_NODES &&
          nqueries >= (size_t)nn->tc_min_queries && nn->n < 0x7fffff00ull;
 }
 
@@ -643,7 +644,7 @@ static void tcPrepQueries(hppb200_knn* nn, const double* d_q, size_t nqueries, i
   HPPB200_CUDA_CHECK(cudaGetLastError());
 }
 
-static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long long* d_i, double* d_d) {
+static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, int32_t cc, long long* d_i, double* d_d) {
   const int nq = nn->model->nq;
   const int nqtTotal = (int)((nqueries + TC_M - 1) / TC_M);
   tcReserve(nn, nqtTotal);
@@ -654,7 +655,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   // bootstrap: exact k-th distance over the first TC_PREFIX0 nodes -> first thresholds
   knnTcRerankKernel<<<rerankGrid, TC_RR_WARPS * 32, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k, nullptr,
                                                                  nullptr, 0, 0, 0, (int)TC_PREFIX0, nn->d_tc_misc.p, nn->d_tc_thr.p, 0, d_i, d_d,
-                                                                 nn->d_tc_misc.p + 1, nn->d_tc_flagged.p);
+                                                                 nn->d_tc_misc.p + 1, nn->d_tc_flagged.p, nn->d_cc, cc);
   // prefixes growing geometrically (<= TC_RATIO per stage) up to the whole roadmap
   const double ratio = (double)nn->n / (double)TC_PREFIX0;
   // (large k: about 512 candidate groups per query and stage at most, so that the per-CTA lists do not overflow)
@@ -674,7 +675,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
                                                                    nn->d_tc_cnt.p, nn->d_tc_cand.p, gused, nn->num_sms, TC_CAPC * (nn->num_sms / gused), 0,
                                                                    nn->d_tc_misc.p,
                                                                    nn->d_tc_thr.p, s == nstages ? 1 : 0, d_i, d_d, nn->d_tc_misc.p + 1,
-                                                                   nn->d_tc_flagged.p);
+                                                                   nn->d_tc_flagged.p, nn->d_cc, cc);
     HPPB200_CUDA_CHECK(cudaGetLastError());
   }
   // queries with an overflowed list in the last stage: exact scan
@@ -696,7 +697,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
     gd.reserve((size_t)nflagged * k);
     gi.reserve((size_t)nflagged * k);
     knnTcGatherQueriesKernel<<<(nflagged * (unsigned)nq + 255) / 256, 256, 0, nn->stream>>>(d_q, nn->d_tc_flagged.p, (int)nflagged, nq, gq.p);
-    knnExactRun(nn, gq.p, nflagged, k, -1, nn->n, gi.p, gd.p);
+    knnExactRun(nn, gq.p, nflagged, k, cc, nn->n, gi.p, gd.p);
     knnTcScatterResultsKernel<<<(nflagged * (unsigned)k + 255) / 256, 256, 0, nn->stream>>>(gi.p, gd.p, nn->d_tc_flagged.p, (int)nflagged, k,
                                                                                            d_i, d_d);
     HPPB200_CUDA_CHECK(cudaGetLastError());
@@ -704,7 +705,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   }
 }
 
-void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long long* d_i, double* d_d) {
+void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, int32_t cc, long long* d_i, double* d_d) {
   tcSyncNodeOperand(nn);
   nn->tc_last_used = true;
   nn->tc_last_overflow = 0;
@@ -713,7 +714,7 @@ void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long l
   const size_t chunk = 8192;  // bounds the candidate buffers (9.5 KB per query)
   for (size_t q0 = 0; q0 < nqueries; q0 += chunk) {
     const size_t nqc = std::min(chunk, nqueries - q0);
-    tcRunChunk(nn, d_q + q0 * (size_t)nn->model->nq, nqc, k, d_i + q0 * (size_t)k, d_d + q0 * (size_t)k);
+    tcRunChunk(nn, d_q + q0 * (size_t)nn->model->nq, nqc, k, cc, d_i + q0 * (size_t)k, d_d + q0 * (size_t)k);
   }
 }
 

@@ -54,7 +54,7 @@ void knnExactRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, int
                  double* d_d);
 // tensor-core candidate pass + exact FP64 re-rank (kernels_knn_tc.cu); same results as knnExactRun over all nodes
 bool knnTcEligible(const hppb200_knn* nn, size_t nqueries, int k, int32_t cc);
-void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, long long* d_i, double* d_d);
+void knnTcRun(hppb200_knn* nn, const double* d_q, size_t nqueries, int k, int32_t cc, long long* d_i, double* d_d);
 void knnTcInit(hppb200_knn* nn);
 void knnTcDestroy(hppb200_knn* nn);
 

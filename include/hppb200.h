@@ -273,7 +273,8 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries,
                       int k, int32_t cc, uint32_t flags, int64_t* idx, double* dist);
 /* hppb200_knn_query takes the tensor-core candidate pass (tcgen05 TF32 GEMM of the query tile against the node
    stream + exact FP64 re-rank of the survivors; same indices and distances as the exact scan, bit for bit) when
-   the model is a vector space (no free-flyer, 3 nq + 6 <= 48), cc < 0, k <= 256, the mirror holds >= 16384 nodes
+   the model is a vector space (no free-flyer, 3 nq + 6 <= 48), k <= 256 (a component filter cc >= 0 is applied by
+   the exact re-rank), the mirror holds >= 16384 nodes
    and the call carries >= 32 queries (env HPPB200_KNN_TC = 0 disables it, HPPB200_KNN_TC_MIN sets the query
    count); otherwise the exact FP64 scan.  Both replace nearestNeighbor::Basic::KnearestSearch
    (reference src/nearest-neighbor/basic.cc:84-126).

@@ -292,11 +292,20 @@ def test_knn_tensor_core_pass_matches_exact_scan_and_oracle(pkg, eng, ur5, ob, m
         assert np.array_equal(gi, np.take_along_axis(oi, srt, axis=1))
         assert np.array_equal(gd, np.take_along_axis(od, srt, axis=1))
     assert nn.query(qs[:32], 1)[0][5, 0] == 77  # the earlier of two identical nodes
-    # below the query / node thresholds and with a connected-component filter the exact scan runs
+    # below the query threshold the exact scan runs
     nn.query(qs[:8], 3)
     assert not nn.tc_stats()["used"]
-    nn.query(qs[:64], 3, cc=0)
-    assert not nn.tc_stats()["used"]
+    # a connected-component filter is applied by the exact re-rank (thresholds = k-th distance INSIDE the component);
+    # a component with fewer than k nodes in every prefix ends in the exact scan: same results either way
+    lab = (np.arange(len(nodes)) % 3).astype(np.int32)
+    lab[1000:1010] = 7
+    nn2, ex2 = pkg.NearestNeighbor(m, 0), _exact_nn(pkg, m, monkeypatch)
+    nn2.append(nodes, lab); ex2.append(nodes, lab)
+    for k, c in ((1, 0), (5, 2), (12, 7), (40, 1)):
+        gi, gd = nn2.query(qs[:100], k, cc=c)
+        assert nn2.tc_stats()["used"]
+        ei, ed = ex2.query(qs[:100], k, cc=c)
+        assert np.array_equal(gi, ei) and np.array_equal(gd, ed), (k, c)
 
 
 def test_knn_tensor_core_pass_clustered_roadmap(pkg, eng, ur5, monkeypatch):
