@@ -339,7 +339,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
                   const double* __restrict__ scale, int nqueries, int k, const int* __restrict__ cnt, const int* __restrict__ cand,
                   int gused, int gstride, int capc, int prefixNodes, const unsigned* __restrict__ maxNorm, float* __restrict__ thr,
                   int finalStage, long long* __restrict__ idx, double* __restrict__ dist, unsigned* __restrict__ nflagged,
-                  int* __restrict__ flagged, const int32_t* __restrict__ ccOf, int32_t ccFilter) {
+                  int* __restrict__ flagged, const int32_t* __restrict__ ccOf, int32_t ccFilter, int prefilter) {
   extern __shared__ __align__(16) unsigned char rsm[];
   __shared__ Key lists[TC_RR_WARPS][32];
   __shared__ int sTotal, sKept;
@@ -472,12 +472,16 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
       if (keyLess(x, ak)) topkInsert(acc, ak, x, k, lane);
     }
   };
+  const double bound2 = (cnt == nullptr || !prefilter) ? CUDART_INF : (double)thr[q] * (1.0 + 1e-9);
   for (int e0 = warp * 4; e0 < total; e0 += TC_RR_WARPS * 4) {
     const int e = e0 + (lane >> 3);
     Key c = {CUDART_INF, LLONG_MAX};
     if (e < total) {
       const long long node = (long long)list[e] * 8 + (lane & 7);
-      if ((size_t)node < n && (ccFilter < 0 || ccOf[node] == ccFilter)) { c.d = exactDistance(nodes + (size_t)node * mv.nq); c.i = node; }
+      if ((size_t)node < n && (ccFilter < 0 || ccOf[node] == ccFilter)) {
+        const double d1 = exactDistance(nodes + (size_t)node * mv.nq);
+        if (d1 * d1 <= bound2) { c.d = d1; c.i = node; }  // above the threshold (an upper bound of the k-th): never in the top k
+      }
     }
     offer(c);
   }
@@ -539,6 +543,7 @@ static int tcStages(int nqt, int kc) {
 void knnTcInit(hppb200_knn* nn) {
   if (const char* v = std::getenv("HPPB200_KNN_TC")) nn->tc_enabled = std::atoi(v) != 0;
   if (const char* v = std::getenv("HPPB200_KNN_TC_MIN")) nn->tc_min_queries = std::max(1, std::atoi(v));
+  if (const char* v = std::getenv("HPPB200_KNN_TC_PREFILTER")) nn->tc_prefilter = std::atoi(v) != 0;
   nn->tc_ratio = TC_RATIO;
   if (const char* v = std::getenv("HPPB200_KNN_TC_RATIO")) nn->tc_ratio = std::max(2.0, std::atof(v));
   nn->tc_kc = 0;
@@ -655,7 +660,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
   // bootstrap: exact k-th distance over the first TC_PREFIX0 nodes -> first thresholds
   knnTcRerankKernel<<<rerankGrid, TC_RR_WARPS * 32, rerankSmem, nn->stream>>>(nn->view, nn->d_nodes, nn->n, d_q, nn->d_tc_scale.p, (int)nqueries, k, nullptr,
                                                                  nullptr, 0, 0, 0, (int)TC_PREFIX0, nn->d_tc_misc.p, nn->d_tc_thr.p, 0, d_i, d_d,
-                                                                 nn->d_tc_misc.p + 1, nn->d_tc_flagged.p, nn->d_cc, cc);
+                                                                 nn->d_tc_misc.p + 1, nn->d_tc_flagged.p, nn->d_cc, cc, nn->tc_prefilter ? 1 : 0);
   // prefixes growing geometrically (<= TC_RATIO per stage) up to the whole roadmap
   const double ratio = (double)nn->n / (double)TC_PREFIX0;
   // (large k: about 512 candidate groups per query and stage at most, so that the per-CTA lists do not overflow)
@@ -675,7 +680,7 @@ static void tcRunChunk(hppb200_knn* nn, const double* d_q, size_t nqueries, int 
                                                                    nn->d_tc_cnt.p, nn->d_tc_cand.p, gused, nn->num_sms, TC_CAPC * (nn->num_sms / gused), 0,
                                                                    nn->d_tc_misc.p,
                                                                    nn->d_tc_thr.p, s == nstages ? 1 : 0, d_i, d_d, nn->d_tc_misc.p + 1,
-                                                                   nn->d_tc_flagged.p, nn->d_cc, cc);
+                                                                   nn->d_tc_flagged.p, nn->d_cc, cc, nn->tc_prefilter ? 1 : 0);
     HPPB200_CUDA_CHECK(cudaGetLastError());
   }
   // queries with an overflowed list in the last stage: exact scan
