@@ -21,7 +21,7 @@ struct hppb200_knn {
   bool ff = false;           // the model has free-flyer joints (no GEMM form of the distance)
   int tc_kc = 0;             // K = 8 * tc_kc operand slots per node (0: model not eligible)
   int tc_min_queries = 32;   // HPPB200_KNN_TC_MIN
-  bool tc_prefilter = false; // HPPB200_KNN_TC_PREFILTER: k <= 32 re-rank drops keys above the threshold before insertion
+  bool tc_prefilter = true;  // HPPB200_KNN_TC_PREFILTER (0 switches it off): k <= 32 re-rank drops keys above the threshold before insertion
   double tc_ratio = 16.0;    // HPPB200_KNN_TC_RATIO: prefix growth per stage
   bool tc_enabled = true;    // HPPB200_KNN_TC
   float* d_tc_nodes = nullptr;   // node operand tiles in the UMMA K-major canonical layout, [tile][256 x 8 kc] tf32
