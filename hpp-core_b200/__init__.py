@@ -22,7 +22,7 @@ from .model_io import (ModelDescription, freeflyer_ranks, hppb200_model_desc, no
                        uniform_configs)
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libhppb200.so")
+LIB_PATH = os.environ.get("HPPB200_LIB") or os.path.join(HERE, "libhppb200.so")  # (HPPB200_LIB: A/B builds of the same library)
 
 OK, ERR_INVALID_ARGUMENT, ERR_RUNTIME, ERR_CUDA, ERR_UNSUPPORTED = range(5)
 METHOD_DISCRETIZED, METHOD_PROGRESSIVE, METHOD_DICHOTOMY = 0, 1, 2

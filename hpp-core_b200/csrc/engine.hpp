@@ -160,7 +160,8 @@ struct Workspace {
   DeviceBuffer<int32_t> d_pair, d_pair_int;
   DeviceBuffer<unsigned long long> d_jobs;
   unsigned long long last_jobs = 0;
-  DeviceBuffer<unsigned char> d_state, d_tail;
+  DeviceBuffer<unsigned char> d_state, d_tail, d_sort;
+  bool wavefront_lpt = true;   // wavefront engines pull the edges longest first (kernels_sort.cu; HPPB200_WF_LPT=0: input order)
   bool use_tail = true;        // Dichotomy: CTA-per-edge pass for handed-over edges (HPPB200_TAIL=0: walker large-list pass only)
   bool tail_smem = true;       // first CTA-per-edge pass keeps the per-pair lists in shared memory (HPPB200_TAIL_SMEM)
   size_t tail_max = ~size_t(0);      // Dichotomy batches up to this size that the wavefront engine does not take go to the CTA-per-edge kernel (HPPB200_TAIL_MAX)
@@ -180,6 +181,7 @@ void launchPathEval(Workspace* ws, const double* d_q1, const double* d_q2, const
 bool launchProgressiveEngine(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2,
                              const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                              int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
+const uint32_t* sortEdgesByLength(Workspace* ws, const double* d_L, size_t n);
 bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const double* d_q1, const double* d_q2,
                                 const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                                 int32_t* d_pair, uint8_t* d_reason, int overflow_reason);

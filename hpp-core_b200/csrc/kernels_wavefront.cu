@@ -69,12 +69,15 @@ struct WFArgs {
   int overflow_reason;
   double alpha;
   unsigned long long* counter;  // next edge to hand out
-  uint32_t E;                   // edge slots
+  const uint32_t* perm;         // hand-out order (longest edge first, kernels_sort.cu); null: input order
+  uint32_t E;                   // edge slots (allocation stride of the [..][E] arrays)
+  uint32_t Ecur;                // slots the grids cover; shrinks when the live slots are compacted
   int fkSlots;
   double2* lohi;       // [NP][E] by order position
   uint16_t* ord;       // [E][ordStride] pair id at order position, one record per slot (its reads stay in L1)
   uint32_t ordStride;  // NP rounded up to 16 entries (32 bytes)
   double* vmax;        // [NP][E] by pair id: SolidSolidCollision::computeMaximalVelocity, fixed per edge
+  double2* vht;        // Progressive: [NP][E] by pair id: (Vmax, 2 tol / Vmax), both fixed per edge (body-pair-collision.cc:80-84)
   double* sv;          // [nv][E] per-joint velocity norms (refill scratch)
   double* st_t;        // [E] ...
   double* st_last;
@@ -196,7 +199,8 @@ __device__ __forceinline__ void wfNewEdgeTables(const ModelView& mv, const WFArg
           if (ba < ab) Vm = ba;
         }
       }
-      A.vmax[(size_t)id * E + es] = Vm;
+      if (A.vht) A.vht[(size_t)id * E + es] = make_double2(Vm, (Vm != 0) ? 2 * A.tol / Vm : INF);
+      else A.vmax[(size_t)id * E + es] = Vm;
       if (A.lohi) A.lohi[(size_t)id * E + es] = make_double2(INF, -INF);
       A.ord[(size_t)es * A.ordStride + id] = (uint16_t)id;
     }
@@ -515,7 +519,7 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
         const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
         if (idx >= A.n) retired = true;
         else {
-          edge = (uint32_t)idx;
+          edge = A.perm ? A.perm[idx] : (uint32_t)idx;
           const double* q1 = A.q1 + (size_t)edge * mv.nq;
           const double* q2 = A.q2 + (size_t)edge * mv.nq;
           L = A.L[edge];
@@ -558,6 +562,393 @@ wfControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
   wfEmitJobs<W>(A, T, e, lane, active, cand, nEm, sCnt, ctl);
 
   // ---- store the slot state -------------------------------------------------------------------------  @region store
+  A.st_flags[e] = (uint8_t)((active ? 1 : 0) | (retired ? 2 : 0) | (finished << 2) | ((active && needFK) ? 16 : 0));
+  if (active) {
+    A.st_t[e] = t; A.st_last[e] = lastValid; A.st_hp[e] = hp; A.st_ilo[e] = ilo; A.st_ihi[e] = ihi; A.st_L[e] = L;
+    A.st_edge[e] = edge; A.st_iters[e] = iters;
+    A.st_pos[e] = (uint32_t)pos | ((uint32_t)smallest << 16);
+    A.st_nEm[e] = (uint8_t)nEm;
+#pragma unroll
+    for (int w = 0; w < W; ++w) A.st_vmask[(size_t)w * E + e] = vmask[w];
+  }
+  wfPublish(A, stats, sCnt, lane, retired, samples, discarded, caps, overflows);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Control kernel, Progressive, second form (round 2).  Same replay, same results; what changed is HOW a thread
+// walks the pair positions.  The first form walked them one by one with the whole decision tree inside the loop:
+// ~12 k warp instructions per warp at 14.7 of 32 lanes (ncu r1j), because the ~5 positions per sample where the
+// reference really evaluates a pair ("events") sit at different positions in different lanes and every one of
+// them serialised the warp.  Here the walk is split into phases every lane runs in step:
+//   1. FIRST EVENT: the first non-valid_ position from `pos` (it is evaluated for sure: the running interval is
+//      still infinite, or the replay stopped there last round).
+//   2. UNIFORM PASS over all later positions, 8 independent 16-byte loads in flight, no decision inside: two bit
+//      masks, M = "not covered by the running interval as it is NOW" and C = "candidate of the next sample under
+//      the window predicted NOW".  The running interval only shrinks, so a position covered now stays covered:
+//      M and C are supersets of what the exact replay / the final prediction will need.
+//   3. EVENT LOOP over the bits of M in position order (a handful): re-test against the current running interval,
+//      fold the pair's result (BodyPairCollision::validateConfiguration :65-89, formerly wfFoldKernel) and
+//      intersect, exactly like validateIntervals.  Lanes process their j-th event together.
+//   4. Sample complete: the bits of C are re-tested against the final window; or a result was missing: the
+//      remaining bits of M are the candidates of the current sample.
+template <int W>
+__device__ __forceinline__ int maskFirstFrom(const u64 (&m)[W], int from) {  // first set bit at a position >= from, -1 if none
+#pragma unroll
+  for (int w = 0; w < W; ++w) {
+    const int lo = from - 64 * w;
+    if (lo >= 64) continue;
+    u64 x = m[w];
+    if (lo > 0) x &= ~0ull << lo;
+    if (x) return 64 * w + __ffsll((long long)x) - 1;
+  }
+  return -1;
+}
+template <int W>
+__device__ __forceinline__ void maskClear(u64 (&m)[W], int p) {
+  if (W == 1) { m[0] &= ~(1ull << p); return; }
+#pragma unroll
+  for (int w = 0; w < W; ++w)
+    if ((p >> 6) == w) m[w] &= ~(1ull << (p & 63));
+}
+template <int W, int N>
+__device__ __forceinline__ void chunkOrN(u64 (&m)[W], int c0, unsigned bits) {
+  if (W == 1) { if (c0 < 64) m[0] |= (u64)bits << c0; return; }
+#pragma unroll
+  for (int k = 0; k < N; ++k) maskSet<W>(m, c0 + k, (bits >> k) & 1u);
+}
+constexpr int WP_CH = 8;  // positions per trip of the uniform pass
+
+#ifndef WF_PC_MINB
+#define WF_PC_MINB 8
+#endif
+template <int W>
+__global__ void __launch_bounds__(WF_CTHREADS, W == 1 ? WF_PC_MINB : 4)
+wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
+  // shared memory: [0,8) mbarrier | [16,48) block counters | model blob prefix
+  extern __shared__ __align__(16) unsigned char smem[];
+  uint64_t* bar = (uint64_t*)smem;
+  unsigned* sCnt = (unsigned*)(smem + 16);
+  unsigned char* sblob = smem + 48;
+  if (threadIdx.x < 8) sCnt[threadIdx.x] = 0u;
+  stageBlobTMA(sblob, mv.blob, mv.edge_blob_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
+
+  const unsigned FULL = 0xffffffffu;
+  const uint32_t E = A.E;
+  const uint32_t e = blockIdx.x * WF_CTHREADS + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const int NP = mv.nbodypairs;
+  const double INF = CUDART_INF;
+  const bool reverse = A.reverse != 0;
+  WFRoundCtl* ctl = A.ctl + (A.round & 1);
+  if (e == 0) {  // the other parity was consumed by the previous round's narrow phase
+    WFRoundCtl* nx = A.ctl + ((A.round + 1) & 1);
+    nx->nG = 0; nx->nC = 0; nx->headG = 0; nx->headC = 0;
+  }
+
+  const uint8_t flags0 = A.st_flags[e];
+  bool active = (flags0 & 1) != 0, retired = (flags0 & 2) != 0;
+  int finished = (flags0 >> 2) & 3;
+  double t = 0, lastValid = 0, hp = INF, ilo = -INF, ihi = INF, L = 0;
+  uint32_t edge = 0, iters = 0;
+  int pos = 0, smallest = 0, nEm = 0;
+  if (active) {
+    t = A.st_t[e]; lastValid = A.st_last[e]; hp = A.st_hp[e]; ilo = A.st_ilo[e]; ihi = A.st_ihi[e]; L = A.st_L[e];
+    edge = A.st_edge[e]; iters = A.st_iters[e];
+    const uint32_t ps = A.st_pos[e];
+    pos = (int)(ps & 0xffffu); smallest = (int)(ps >> 16);
+    nEm = A.st_nEm[e];
+  }
+  unsigned samples = 0, caps = 0, overflows = 0, discarded = 0;
+  bool needSample = false, needFK = false;
+  u64 cand[W], vmask[W];
+#pragma unroll
+  for (int w = 0; w < W; ++w) { cand[w] = 0ull; vmask[w] = active ? A.st_vmask[(size_t)w * E + e] : 0ull; }
+
+  auto finishEdge = [&](bool ok, int rs, double tf, double tl, int pr) {
+    A.valid[edge] = ok ? 1 : 0;
+    if (A.t_fail) A.t_fail[edge] = tf;
+    if (A.t_last) A.t_last[edge] = tl;
+    if (A.pair) A.pair[edge] = pr;
+    if (A.reason) A.reason[edge] = (uint8_t)rs;
+    active = false;
+  };
+
+  // ---- FOLD: last round's distances of every emitted body pair -> validated interval, all of them up front (the loads
+  // of the nEm entries are independent; inside the event loop they were a chain of four dependent global loads each).
+  // BodyPairCollision::validateConfiguration :65-89 up to the interval [t - (hd + ht), t + (hd + ht)]; a collision is
+  // kept as (geometry pair, -inf).  Whether an interval is USED is decided by the replay below.
+  if (active) {
+    const uint16_t* od = A.ord + (size_t)e * A.ordStride;
+    for (int k = 0; k < nEm; ++k) {
+      const int p = A.emPos[(size_t)k * E + e];
+      const int r0 = A.emRes[(size_t)k * E + e];
+      const int id = od[p];
+      const DevBodyPair& B = T.bodypairs[id];
+      double dlb = INF;  // computeDistanceLowerBound (:175-198): geometry pairs in order, first collision reports
+      int hit = -1;
+      for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
+        const double d = A.res[(size_t)(r0 + gp - B.pair_begin) * E + e];
+        if (d <= HPPB200_COLLISION_THRESHOLD) { hit = gp; break; }
+        if (d < dlb) dlb = d;
+      }
+      double2 f;
+      if (hit >= 0) f = make_double2((double)hit, -INF);
+      else {
+        double hd, ht;  // :72-85
+        if (dlb == INF) { hd = INF; ht = 0; }
+        else {
+          const double2 vh = A.vht[(size_t)id * E + e];
+          hd = dlb / vh.x;
+          ht = vh.y;
+        }
+        f = make_double2(t - (hd + ht), t + (hd + ht));
+      }
+      A.fold[(size_t)k * E + e] = f;
+    }
+  }
+
+  // The phases below are separated by __syncwarp(): the event loops have data-dependent trip counts, and without
+  // an explicit reconvergence point the lanes that leave a loop early run the rest of the kernel on their own
+  // (measured: 3.2 of 32 lanes in the completion code).
+  __syncwarp();
+  double2* col = A.lohi + e;  // position p at col[p * E]
+  u64 nonv[W], M[W];
+#pragma unroll
+  for (int w = 0; w < W; ++w) {
+    const int left = NP - 64 * w;
+    nonv[w] = ~vmask[w] & (left >= 64 ? ~0ull : (left > 0 ? (1ull << left) - 1ull : 0ull));
+    M[w] = 0ull;
+  }
+  // first valid_ position from `pos`: the only one that can still change the running interval (positions before
+  // `pos` were walked in an earlier round of this sample; some of them became valid_ IN this sample, as events)
+  const int pv = maskFirstFrom<W>(vmask, pos);
+  const bool scanning = active;  // slots that hold an edge at the start of the round
+  bool vdone = false, stop = false, emit = false;
+  int cursor = 0;
+  int nextP = (scanning && nEm > 0) ? (int)A.emPos[e] : -1;
+
+  // events of the positions in Mk, in order (validateIntervals, continuous-validation.hh:267-298)
+  auto runEvents = [&](u64 (&Mk)[W]) {
+    for (;;) {
+      const int p = maskFirstFrom<W>(Mk, 0);
+      if (p < 0) break;
+      maskClear<W>(Mk, p);
+      if (!vdone && pv >= 0 && pv < p) {  // a valid_ pair before p: interval = timeRange (body-pair-collision.cc:51-55)
+        if (ihi > L) smallest = pv;
+        ilo = (ilo < 0.0) ? 0.0 : ilo;
+        ihi = (L < ihi) ? L : ihi;
+        vdone = true;
+      }
+      const double2 lh = col[(size_t)p * E];
+      if (lh.x <= ilo && ihi <= lh.y) continue;  // validInterval_ contains the running interval (:56-63)
+      while (nextP >= 0 && nextP < p) {  // results of pairs the replay skipped
+        ++discarded;
+        ++cursor;
+        nextP = cursor < nEm ? (int)A.emPos[(size_t)cursor * E + e] : -1;
+      }
+      if (nextP != p) {  // the reference evaluates this pair now and its distance is not there yet
+        emit = true;
+        pos = p;
+        stop = true;
+        break;
+      }
+      const double2 rr = A.fold[(size_t)cursor * E + e];
+      ++cursor;
+      nextP = cursor < nEm ? (int)A.emPos[(size_t)cursor * E + e] : -1;
+      const double a = rr.x, bb = rr.y;
+      if (bb == -INF) {  // collision: a carries the geometry pair
+        finishEdge(false, HPPB200_REASON_COLLISION, t, lastValid, (int)a);
+        stop = true;
+        break;
+      }
+      const double l = lh.x, h = lh.y;
+      if (!(l > h) && (h < a || bb < l)) {
+        // validInterval_.insert (:90) would open a second interval: hand the edge to the walker
+        ++overflows;
+        finishEdge(false, A.overflow_reason, t, lastValid, -1);
+        stop = true;
+        break;
+      }
+      double nl = a, nh = bb;
+      if (!(l > h)) { nl = (a < l) ? a : l; nh = (h > bb) ? h : bb; }
+      if (nl <= 0.0 && L <= nh) {  // valid_ (:92-96), stored as lo = -inf
+        nl = -INF; nh = INF;
+        maskSet<W>(vmask, p, true);
+        maskClear<W>(nonv, p);
+      }
+      col[(size_t)p * E] = make_double2(nl, nh);
+      if (ihi > bb) smallest = p;  // validateIntervals: fold into the running intersection
+      ilo = (ilo < a) ? a : ilo;
+      ihi = (bb < ihi) ? bb : ihi;
+    }
+  };
+  // uniform pass over the non-valid_ positions >= from: Mo = those whose interval does not contain [xl, xh]
+  auto pass = [&](int from, double xl, double xh, u64 (&Mo)[W]) {
+    u64 need[W];
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      const int lo = from - 64 * w;
+      need[w] = lo >= 64 ? 0ull : (lo > 0 ? nonv[w] & (~0ull << lo) : nonv[w]);
+    }
+    for (int c0 = 0; c0 < NP; c0 += WP_CH) {
+      const unsigned nb = chunkBitsN<W, WP_CH>(need, c0);
+      double2 v[WP_CH];
+#pragma unroll
+      for (int k = 0; k < WP_CH; ++k) {
+        v[k] = make_double2(-INF, INF);
+        if ((nb >> k) & 1u) v[k] = col[(size_t)(c0 + k) * E];
+      }
+      unsigned mb = 0u;
+#pragma unroll
+      for (int k = 0; k < WP_CH; ++k) mb |= (!(v[k].x <= xl && xh <= v[k].y) ? 1u : 0u) << k;
+      chunkOrN<W, WP_CH>(Mo, c0, mb & nb);
+    }
+  };
+
+  // ---- phase 1: the first event ----------------------------------------------------------------------
+  int from = NP;
+  if (scanning) {
+    const int p0 = maskFirstFrom<W>(nonv, pos);
+    if (p0 >= 0) {
+      from = p0 + 1;
+      maskSet<W>(M, p0, true);
+      runEvents(M);
+    }
+  }
+  __syncwarp();
+  // ---- phase 2: uniform pass against the running interval as it is now ------------------------------------
+  const bool passed = scanning && !stop;
+  if (passed) pass(from, ilo, ihi, M);
+  __syncwarp();
+  // ---- phase 3: the other events -------------------------------------------------------------------------
+  if (passed) runEvents(M);
+  __syncwarp();
+  // ---- phase 4: candidates.  A result was missing: the later pairs the window of the CURRENT sample does not cover
+  // (and the missing one); the sample is complete: the pairs the window of the NEXT sample does not cover
+  // (predicted t' = end of the intersection, window alpha x step).
+  const bool complete = scanning && !stop && !emit;
+  double wl = 0, wh = 0;
+  if (emit) { wl = fmax(ilo, t - hp); wh = fmin(ihi, t + hp); }
+  if (complete) {
+    if (!vdone && pv >= 0) {  // a valid_ pair after the last event
+      if (ihi > L) smallest = pv;
+      ilo = (ilo < 0.0) ? 0.0 : ilo;
+      ihi = (L < ihi) ? L : ihi;
+    }
+    discarded += (unsigned)(nEm - cursor);
+    const double tn = reverse ? ilo : ihi;
+    const double hn = A.alpha * fabs(tn - t);
+    wl = tn - hn; wh = tn + hn;
+  }
+  if (complete || (emit && !passed)) pass(complete ? 0 : pos + 1, wl, wh, cand);
+  __syncwarp();
+  if (emit) {
+    if (passed) {
+      for (int left = A.rb - 1; left > 0;) {  // the remaining bits of M are after `pos`; at most rb body pairs are emitted
+        const int p = maskFirstFrom<W>(M, 0);
+        if (p < 0) break;
+        maskClear<W>(M, p);
+        const double2 lh = col[(size_t)p * E];
+        if (!(lh.x <= wl && wh <= lh.y)) { maskSet<W>(cand, p, true); --left; }
+      }
+    }
+    maskSet<W>(cand, pos, true);
+  }
+  __syncwarp();
+  // ---- phase 5: end of the sample ---------------------------------------------------------------------
+  if (complete) {
+    // src/continuous-validation.cc:144-146: smallest interval first
+    if (NP > 1 && smallest != 0) {
+      const size_t is = (size_t)smallest * E;
+      const double2 x0 = col[0], xs = col[is];
+      uint16_t* odw = A.ord + (size_t)e * A.ordStride;
+      const uint16_t o0 = odw[0], os = odw[smallest];
+      col[0] = xs; col[is] = x0;
+      odw[0] = os; odw[smallest] = o0;
+      const bool c0 = maskGet<W>(cand, 0), cs = maskGet<W>(cand, smallest);
+      maskPut<W>(cand, 0, cs); maskPut<W>(cand, smallest, c0);
+      const bool v0 = maskGet<W>(vmask, 0), vs = maskGet<W>(vmask, smallest);
+      maskPut<W>(vmask, 0, vs); maskPut<W>(vmask, smallest, v0);
+    }
+    // progressive.cc:104-117
+    const double tprev = t;
+    t = reverse ? ilo : ihi;
+    lastValid = tprev;
+    hp = A.alpha * fabs(t - tprev);
+    if (reverse ? t <= 0.0 : t >= L) { t = reverse ? 0.0 : L; finished++; }
+    if (finished >= 2) finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+    else {
+      needSample = true;
+      // the first non-valid pair of the new order is evaluated by the reference for sure
+      int first = -1;
+#pragma unroll
+      for (int w = W - 1; w >= 0; --w) {
+        const u64 nv = ~vmask[w];
+        if (nv) first = w * 64 + __ffsll((long long)nv) - 1;
+      }
+      if (first >= 0 && first < NP) maskPut<W>(cand, first, true);
+#pragma unroll
+      for (int w = 0; w < W; ++w) cand[w] &= ~vmask[w];
+    }
+  }
+  __syncwarp();
+
+  // ---- REFILL: free slots pull the next edges (ballot + popc prefix, one atomic per warp) --------
+  {
+    const bool want = !active && !retired;
+    const unsigned m = __ballot_sync(FULL, want);
+    if (m) {
+      const int leader = __ffs(m) - 1;
+      unsigned long long b = 0;
+      if (lane == leader) b = atomicAdd(A.counter, (unsigned long long)__popc(m));
+      b = __shfl_sync(FULL, b, leader);
+      bool got = false;
+      if (want) {
+        const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
+        if (idx >= A.n) retired = true;
+        else {
+          edge = A.perm ? A.perm[idx] : (uint32_t)idx;
+          L = A.L[edge];
+          iters = 0;
+          finished = 0;
+          lastValid = reverse ? L : 0.0;
+          t = lastValid;
+          hp = INF;
+          if (reverse ? t <= 0.0 : t >= L) finished++;
+#pragma unroll
+          for (int w = 0; w < W; ++w) {
+            vmask[w] = 0ull;
+            const int left = NP - 64 * w;
+            cand[w] = left >= 64 ? ~0ull : (left > 0 ? (1ull << left) - 1ull : 0ull);
+          }
+          active = true;
+          needSample = true;
+          got = true;
+        }
+      }
+      wfNewEdgeTables(mv, A, T, e, lane, got, edge, L);
+      __syncwarp();
+    }
+  }
+
+  // ---- next sample ---------------------------------------------------------------------------------
+  if (needSample) {
+    if (iters >= A.max_iter) {
+      ++caps;
+      finishEdge(false, HPPB200_REASON_ITER_CAP, t, lastValid, -1);
+    } else {
+      ++iters;
+      ++samples;
+      pos = 0; smallest = 0; ilo = -INF; ihi = INF; nEm = 0;
+      needFK = true;  // wfFkKernel computes the placements at t
+    }
+  }
+
+  // ---- EMIT: one job per geometry pair of every candidate, in position order -------------------------
+  wfEmitJobs<W>(A, T, e, lane, active, cand, nEm, sCnt, ctl);
+
+  // ---- store the slot state -------------------------------------------------------------------------
   A.st_flags[e] = (uint8_t)((active ? 1 : 0) | (retired ? 2 : 0) | (finished << 2) | ((active && needFK) ? 16 : 0));
   if (active) {
     A.st_t[e] = t; A.st_last[e] = lastValid; A.st_hp[e] = hp; A.st_ilo[e] = ilo; A.st_ihi[e] = ihi; A.st_L[e] = L;
@@ -794,7 +1185,7 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
         const unsigned long long idx = b + __popc(m & ((1u << lane) - 1u));
         if (idx >= A.n) retired = true;
         else {
-          edge = (uint32_t)idx;
+          edge = A.perm ? A.perm[idx] : (uint32_t)idx;
           L = A.L[edge];
           iters = 0;
           t = reverse ? L : 0.0;
@@ -860,9 +1251,9 @@ wfFoldKernel(ModelView mv, WFArgs A) {
   const Tables T = makeTables(mv.blob, mv);  // global copy (read-only, L1 resident)
   const uint32_t E = A.E;
   const size_t idx = (size_t)blockIdx.x * 256 + threadIdx.x;
-  if (idx >= (size_t)E * A.rb) return;
-  const uint32_t e = (uint32_t)(idx % E);
-  const int k = (int)(idx / E);
+  if (idx >= (size_t)A.Ecur * A.rb) return;
+  const uint32_t e = (uint32_t)(idx % A.Ecur);
+  const int k = (int)(idx / A.Ecur);
   if (!(A.st_flags[e] & 1) || k >= (int)A.st_nEm[e]) return;
   const double INF = CUDART_INF;
   const int p = A.emPos[(size_t)k * E + e];
@@ -1093,6 +1484,65 @@ __global__ void wfAbandonKernel(WFArgs A, DeviceStats* stats) {
   atomicAdd(&stats->overflow, 1ull);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Slot compaction.  Once the edge counter is exhausted, finished slots stay empty; the thread-per-slot kernels
+// then pay a full warp for every warp that still holds ONE edge (measured r2: with 2 % of the slots alive the
+// control kernel still took 25 % of a full round, and 720 of the 896 rounds of a 1 M-edge batch are such rounds).
+// Between two rounds (job lists consumed, nothing in flight) the host moves the live slots above the new extent
+// into the free slots below it and shrinks the grids: a round then costs what its live edges cost.
+// Which slot an edge lives in never reaches a result.
+struct WFMoveEntry {
+  unsigned char* base;
+  uint32_t elem;        // bytes per element
+  uint32_t count;       // elements per slot
+  uint32_t slotMajor;   // 1: [E][count] (contiguous per slot), 0: [count][E]
+};
+constexpr int WF_MOVE_MAX = 32;
+struct WFMoveTable {
+  WFMoveEntry ent[WF_MOVE_MAX];
+  int n;
+};
+
+__global__ void wfCompactListKernel(WFArgs A, uint32_t Ecur, uint32_t Enew, uint32_t* src, uint32_t* dst, unsigned* cnt) {
+  const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= Ecur) return;
+  const bool live = (A.st_flags[e] & 1) != 0;
+  if (e >= Enew) { if (live) src[atomicAdd(&cnt[0], 1u)] = e; }
+  else if (!live) dst[atomicAdd(&cnt[1], 1u)] = e;
+}
+
+// one warp per moved slot
+__global__ void __launch_bounds__(256)
+wfCompactMoveKernel(WFArgs A, WFMoveTable tab, const uint32_t* src, const uint32_t* dst, const unsigned* cnt) {
+  const unsigned w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= cnt[0]) return;
+  const uint32_t s = src[w], d = dst[w];
+  const size_t E = A.E;
+  for (int i = 0; i < tab.n; ++i) {
+    const WFMoveEntry en = tab.ent[i];
+    if (en.slotMajor) {
+      const size_t bytes = (size_t)en.elem * en.count;  // multiples of 4 by construction
+      const uint32_t* ps = (const uint32_t*)(en.base + s * bytes);
+      uint32_t* pd = (uint32_t*)(en.base + d * bytes);
+      for (size_t k = lane; k < bytes / 4; k += 32) pd[k] = ps[k];
+    } else {
+      for (uint32_t k = lane; k < en.count; k += 32) {
+        const unsigned char* ps = en.base + ((size_t)k * E + s) * en.elem;
+        unsigned char* pd = en.base + ((size_t)k * E + d) * en.elem;
+        switch (en.elem) {
+          case 16: *(double2*)pd = *(const double2*)ps; break;
+          case 8: *(unsigned long long*)pd = *(const unsigned long long*)ps; break;
+          case 4: *(uint32_t*)pd = *(const uint32_t*)ps; break;
+          case 2: *(uint16_t*)pd = *(const uint16_t*)ps; break;
+          default: *pd = *ps; break;
+        }
+      }
+    }
+  }
+  __syncwarp();
+  if (lane == 0) A.st_flags[s] = 2;  // (its flags were copied to d above)
+}
+
 namespace {
 struct Carver {
   size_t off = 0;
@@ -1126,6 +1576,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   A.q1 = d_q1; A.q2 = d_q2; A.L = d_L; A.n = n; A.reverse = reverse; A.tol = tol; A.max_iter = ws->max_iterations;
   A.valid = d_valid; A.t_fail = d_tfail; A.t_last = d_tlast; A.pair = d_pair; A.reason = d_reason;
   A.overflow_reason = overflow_reason;
+  A.perm = (ws->wavefront_lpt && n > 1) ? sortEdgesByLength(ws, d_L, n) : nullptr;
   A.alpha = ws->engine_alpha;
   A.refill_min = WF_REFILL_MIN;
   if (const char* v = std::getenv("HPPB200_WF_REFILL")) A.refill_min = std::atoi(v);
@@ -1147,7 +1598,11 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   const size_t o_counter = c.take<unsigned long long>(1), o_ctl = c.take<WFRoundCtl>(2), o_alive = c.take<unsigned>(BATCH);
   const bool dich = method == HPPB200_METHOD_DICHOTOMY;
   const size_t o_lohi = c.take<double2>(dich ? 0 : (size_t)NP * E), o_ord = c.take<uint16_t>((size_t)((NP + 15) / 16 * 16) * E);
-  const size_t o_vmax = c.take<double>((size_t)NP * E), o_sv = c.take<double>((size_t)mv.nv * E);
+  int controlForm = 2;  // Progressive: 2 = phase-convergent control kernel with the fold inside; 1 = first form + wfFoldKernel
+  if (const char* v = std::getenv("HPPB200_WF_CONTROL")) controlForm = std::atoi(v);
+  const bool foldKernel = dich || controlForm == 1;
+  const size_t o_vmax = c.take<double>(foldKernel ? (size_t)NP * E : 0), o_sv = c.take<double>((size_t)mv.nv * E);
+  const size_t o_vht = c.take<double2>(foldKernel ? 0 : (size_t)NP * E);
   const size_t o_t = c.take<double>(E), o_last = c.take<double>(E), o_hp = c.take<double>(E), o_ilo = c.take<double>(E);
   const size_t o_ihi = c.take<double>(E), o_L = c.take<double>(E);
   const size_t o_edge = c.take<uint32_t>(E), o_iters = c.take<uint32_t>(E), o_pos = c.take<uint32_t>(E);
@@ -1161,6 +1616,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   const size_t o_fold = c.take<double2>(RB * E);
   const size_t o_res = c.take<double>(RG * E), o_plc = c.take<double>(E * (size_t)A.fkSlots * 12);
   const size_t o_jG = c.take<unsigned long long>(E * RG), o_jC = c.take<unsigned long long>(E * RG);
+  const size_t o_cmp = c.take<uint32_t>(2 * E + 4);  // compaction: source slots, destination slots, two counters
   ws->d_state.reserve(c.off + 256);
   unsigned char* base = ws->d_state.p;
   A.counter = (unsigned long long*)(base + o_counter);
@@ -1168,6 +1624,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   A.alive = (unsigned*)(base + o_alive);
   A.lohi = dich ? nullptr : (double2*)(base + o_lohi); A.ord = (uint16_t*)(base + o_ord); A.ordStride = (uint32_t)((NP + 15) / 16 * 16);
   A.vmax = (double*)(base + o_vmax); A.sv = (double*)(base + o_sv);
+  A.vht = foldKernel ? nullptr : (double2*)(base + o_vht);
   A.st_t = (double*)(base + o_t); A.st_last = (double*)(base + o_last); A.st_hp = (double*)(base + o_hp);
   A.st_ilo = (double*)(base + o_ilo); A.st_ihi = (double*)(base + o_ihi); A.st_L = (double*)(base + o_L);
   A.st_edge = (uint32_t*)(base + o_edge); A.st_iters = (uint32_t*)(base + o_iters); A.st_pos = (uint32_t*)(base + o_pos);
@@ -1178,18 +1635,45 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   A.res = (double*)(base + o_res); A.plc = (double*)(base + o_plc);
   A.jobsG = (unsigned long long*)(base + o_jG); A.jobsC = (unsigned long long*)(base + o_jC);
 
-  const size_t smemCtl = dich ? 48 + mv.edge_blob_bytes : smemC;
-  auto kc = dich ? (W == 1 ? wfDichControlKernel<1> : wfDichControlKernel<4>) : (W == 1 ? wfControlKernel<1> : wfControlKernel<4>);
+  const size_t smemCtl = (foldKernel && !dich) ? smemC : 48 + mv.edge_blob_bytes;
+  auto kc = dich ? (W == 1 ? wfDichControlKernel<1> : wfDichControlKernel<4>)
+                 : (controlForm == 1 ? (W == 1 ? wfControlKernel<1> : wfControlKernel<4>)
+                                     : (W == 1 ? wfProgControlKernel<1> : wfProgControlKernel<4>));
   auto kf = tree ? wfFkKernel<true> : wfFkKernel<false>;
   const size_t smemF = 16 + (WF_CTHREADS / 32) * WF_FK_TILE + mv.edge_blob_bytes;
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
-  const unsigned gridF = (unsigned)((E * RB + 255) / 256);
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemCtl));
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(wfNarrowKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemN));
   int perSM = 0;
   HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, wfNarrowKernel, WF_NTHREADS, smemN));
   if (perSM < 1) return false;
-  const unsigned gridN = (unsigned)(ws->num_sms * perSM), gridC = (unsigned)(E / WF_CTHREADS);
+  const unsigned gridN = (unsigned)(ws->num_sms * perSM);
+  unsigned gridC = (unsigned)(E / WF_CTHREADS), gridF = (unsigned)((E * RB + 255) / 256);
+  A.Ecur = (uint32_t)E;
+
+  // slot compaction (see wfCompactMoveKernel): every per-slot array that carries state from one round to the next
+  WFMoveTable mt{};
+  auto addMove = [&](void* base, size_t elem, size_t count, bool slotMajor) {
+    if (!base || !count || mt.n >= WF_MOVE_MAX) return;
+    mt.ent[mt.n++] = WFMoveEntry{(unsigned char*)base, (uint32_t)elem, (uint32_t)count, slotMajor ? 1u : 0u};
+  };
+  addMove(A.lohi, 16, NP, false); addMove(A.ord, 2, A.ordStride, true);
+  addMove(foldKernel ? (void*)A.vmax : (void*)A.vht, foldKernel ? 8 : 16, NP, false);
+  addMove(A.st_t, 8, 1, false); addMove(A.st_last, 8, 1, false); addMove(A.st_hp, 8, 1, false); addMove(A.st_ilo, 8, 1, false);
+  addMove(A.st_ihi, 8, 1, false); addMove(A.st_L, 8, 1, false); addMove(A.st_edge, 4, 1, false); addMove(A.st_iters, 4, 1, false);
+  addMove(A.st_pos, 4, 1, false); addMove(A.st_flags, 1, 1, false); addMove(A.st_nEm, 1, 1, false);
+  addMove(A.st_vmask, 8, W, false);
+  if (dich) {
+    addMove(A.st_cbits, 8, (size_t)4 * W, false); addMove(A.ivl, 16, (size_t)NP * WD_K, false);
+    addMove(A.sub, 16, WD_KS, false); addMove(A.st_subCnt, 1, 1, false);
+  }
+  addMove(A.emPos, 2, RB, false); addMove(A.emRes, 1, RB, false); addMove(A.res, 8, RG, false);
+  addMove(A.plc, 8, (size_t)A.fkSlots * 12, true);
+  uint32_t* d_src = (uint32_t*)(base + o_cmp);
+  uint32_t* d_dst = d_src + E;
+  unsigned* d_cnt = (unsigned*)(d_dst + E);
+  bool compactOn = true;
+  if (const char* v = std::getenv("HPPB200_WF_COMPACT")) compactOn = std::atoi(v) != 0;
 
   wfInitKernel<<<(unsigned)((E + 255) / 256), 256, 0, ws->stream>>>(A);
   HPPB200_CUDA_CHECK(cudaGetLastError());
@@ -1198,6 +1682,9 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   unsigned h_alive = 1;
   const bool trace = std::getenv("HPPB200_WF_TRACE") != nullptr;  // per-round kernel times on stderr (debug)
   std::vector<cudaEvent_t> evs;
+  struct TraceRow { unsigned alive, nG, nC; };
+  std::vector<TraceRow> traceRows;
+  const bool traceAll = trace && std::atoi(std::getenv("HPPB200_WF_TRACE")) > 1;
   while (h_alive) {
     HPPB200_CUDA_CHECK(cudaMemsetAsync(A.alive, 0, BATCH * sizeof(unsigned), ws->stream));
     for (int k = 0; k < BATCH; ++k, ++round) {
@@ -1211,7 +1698,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
         evs.push_back(ev);
       };
       mark();
-      if (round > 0) wfFoldKernel<<<gridF, 256, 0, ws->stream>>>(mv, A);
+      if (round > 0 && foldKernel) wfFoldKernel<<<gridF, 256, 0, ws->stream>>>(mv, A);
       mark();
       kc<<<gridC, WF_CTHREADS, smemCtl, ws->stream>>>(mv, A, ws->d_stats);
       mark();
@@ -1219,25 +1706,51 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
       mark();
       wfNarrowKernel<<<gridN, WF_NTHREADS, smemN, ws->stream>>>(mv, A, ws->d_stats);
       mark();
+      if (traceAll) {  // debug only: one synchronisation per round
+        TraceRow row{};
+        WFRoundCtl c{};
+        cudaMemcpyAsync(&c, A.ctl + (round & 1), sizeof(c), cudaMemcpyDeviceToHost, ws->stream);
+        cudaMemcpyAsync(&row.alive, A.alive + k, sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream);
+        cudaStreamSynchronize(ws->stream);
+        row.nG = c.nG; row.nC = c.nC;
+        traceRows.push_back(row);
+      }
     }
     HPPB200_CUDA_CHECK(cudaGetLastError());
     ws->stats.kernel_launches += 4 * BATCH;
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h_alive, A.alive + (BATCH - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream));
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
     if (h_alive && h_alive <= tailSlots) {  // (slots hold edges only: the edge counter is exhausted long before)
-      wfAbandonKernel<<<(unsigned)((E + 255) / 256), 256, 0, ws->stream>>>(A, ws->d_stats);
+      wfAbandonKernel<<<(unsigned)((A.Ecur + 255) / 256), 256, 0, ws->stream>>>(A, ws->d_stats);
       HPPB200_CUDA_CHECK(cudaGetLastError());
       ws->stats.kernel_launches += 1;
       break;
     }
+    // fewer live slots than the grids cover (only once the edge counter is exhausted): compact and shrink
+    const uint32_t Enew = (uint32_t)(((size_t)h_alive + WF_CTHREADS - 1) / WF_CTHREADS * WF_CTHREADS);
+    if (compactOn && h_alive && (size_t)Enew * 8 <= (size_t)A.Ecur * 7) {
+      HPPB200_CUDA_CHECK(cudaMemsetAsync(d_cnt, 0, 2 * sizeof(unsigned), ws->stream));
+      wfCompactListKernel<<<(A.Ecur + 255) / 256, 256, 0, ws->stream>>>(A, A.Ecur, Enew, d_src, d_dst, d_cnt);
+      const unsigned maxMoves = A.Ecur - Enew;  // at most that many live slots above the new extent
+      wfCompactMoveKernel<<<(maxMoves + 7) / 8, 256, 0, ws->stream>>>(A, mt, d_src, d_dst, d_cnt);
+      HPPB200_CUDA_CHECK(cudaGetLastError());
+      ws->stats.kernel_launches += 2;
+      A.Ecur = Enew;
+      gridC = Enew / WF_CTHREADS;
+      gridF = (unsigned)(((size_t)Enew * RB + 255) / 256);
+    }
   }
   if (trace) {
     double tt[4] = {0, 0, 0, 0};
+    const bool all = std::atoi(std::getenv("HPPB200_WF_TRACE")) > 1;  // 2: every round, with the alive slots and job counts
     for (size_t r = 0; r + 4 < evs.size(); r += 5) {
       float d[4];
       for (int j = 0; j < 4; ++j) { cudaEventElapsedTime(&d[j], evs[r + j], evs[r + j + 1]); tt[j] += d[j]; }
       const size_t k = r / 5;
-      if (k < 4 || k % 64 == 0)
+      if (all && k < traceRows.size())
+        std::fprintf(stderr, "[wfr] %zu %u %u %u %.1f %.1f %.1f %.1f\n", k, traceRows[k].alive, traceRows[k].nG, traceRows[k].nC,
+                     d[0] * 1e3, d[1] * 1e3, d[2] * 1e3, d[3] * 1e3);
+      else if (k < 4 || k % 64 == 0)
         std::fprintf(stderr, "[wf] round %zu fold %.1f control %.1f fk %.1f narrow %.1f us\n", k, d[0] * 1e3, d[1] * 1e3, d[2] * 1e3, d[3] * 1e3);
     }
     std::fprintf(stderr, "[wf] E=%u gridC=%u gridN=%u rounds=%d fold %.2f control %.2f fk %.2f narrow %.2f ms\n", A.E, gridC, gridN, round,
