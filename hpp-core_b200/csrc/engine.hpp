@@ -165,6 +165,7 @@ struct Workspace {
   bool use_tail = true;        // Dichotomy: CTA-per-edge pass for handed-over edges (HPPB200_TAIL=0: walker large-list pass only)
   bool tail_smem = true;       // first CTA-per-edge pass keeps the per-pair lists in shared memory (HPPB200_TAIL_SMEM)
   size_t tail_max = ~size_t(0);      // Dichotomy batches up to this size that the wavefront engine does not take go to the CTA-per-edge kernel (HPPB200_TAIL_MAX)
+  size_t prog_tail_max = 4096;         // Progressive batches up to this size go to the CTA-per-edge kernel (HPPB200_PROG_TAIL_MAX)
   void syncStats();
 };
 
@@ -185,6 +186,22 @@ const uint32_t* sortEdgesByLength(Workspace* ws, const double* d_L, size_t n);
 bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const double* d_q1, const double* d_q2,
                                 const double* d_L, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                                 int32_t* d_pair, uint8_t* d_reason, int overflow_reason);
+// State of wavefront slots (kernels_wavefront.cu) from which the CTA-per-edge kernel continues Progressive edges.
+struct TailResume {
+  const uint32_t* slots = nullptr;  // the slots to take over (one edge each, at a sample boundary)
+  uint32_t E = 0, ordStride = 0;
+  const double2* lohi = nullptr;             // [NP][E] validated interval by order position
+  const uint16_t* ord = nullptr;             // [E][ordStride] pair id by order position
+  const unsigned long long* st_vmask = nullptr;  // [W][E] valid_ bits by order position
+  const double* st_t = nullptr;
+  const double* st_last = nullptr;
+  const uint32_t* st_iters = nullptr;
+  const uint32_t* st_edge = nullptr;
+  const uint8_t* st_flags = nullptr;         // bits 2-3: `finished`
+};
+bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
+                    const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
+                    uint8_t* d_reason, int overflow_reason, bool smemLists, const TailResume* resume);
 bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
                          const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
                          uint8_t* d_reason, int overflow_reason, bool smemLists);

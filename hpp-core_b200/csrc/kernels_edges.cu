@@ -668,6 +668,13 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   if (method != HPPB200_METHOD_DISCRETIZED && ws->use_engine && ws->engine_kind >= 2 && n >= wfMin)
     engineDone = launchWavefront(ws, method, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair,
                                             d_reason, REASON_OVERFLOW_INTERNAL);
+  // Progressive, small batches: one CTA per edge (kernels_tail.cu), the latency of a sample instead of the CTA engine's ticks
+  if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_tail && n <= ws->prog_tail_max) {
+    const int k = std::min(64, (int)(65536 / (16 * std::max(1, (int)ws->view.nbodypairs))));
+    if (k >= 8)
+      engineDone = launchEdgeTail(ws, method, param, reverse, d_q1, d_q2, d_L, nullptr, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,
+                                  REASON_OVERFLOW_INTERNAL, true, nullptr);
+  }
   if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_engine)
     engineDone = launchProgressiveEngine(ws, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,
                                          REASON_OVERFLOW_INTERNAL);

@@ -1,5 +1,7 @@
-// Dichotomy, one CTA per edge: the pass that finishes the edges the batch engines hand over (interval lists
-// beyond the wavefront's capacity, the thin tail of a batch) and the path of small batches.
+// Dichotomy and Progressive, one CTA per edge: the pass that finishes the edges the batch engines hand over (interval
+// lists beyond the wavefront's capacity, the thin tail of a batch) and the path of small batches.  METHOD selects
+// the outer loop (dichotomy.cc:68-132 / progressive.cc:78-129); the sample itself (validateConfiguration) is shared.
+// Progressive can RESUME edges from the wavefront engine's slot state at a sample boundary (TailResume).
 //
 // Replaces Dichotomy::validateStraightPath (src/continuous-validation/dichotomy.cc:68-132) +
 // ContinuousValidation::validateConfiguration / validateIntervals (src/continuous-validation.cc:128-148,
@@ -53,6 +55,7 @@ struct TailArgs {
   double2* lists;  // [grid][nbodypairs][K] in global memory, or null: the lists live in shared memory
   int K;           // validated intervals per body pair
   unsigned long long* clk;  // optional [8]: cycles of thread 0 per phase (HPPB200_WF_TRACE)
+  TailResume resume;        // Progressive: continue the edges of these wavefront slots (slots == null: start edges afresh)
 };
 
 // dynamic shared memory of one CTA
@@ -96,8 +99,10 @@ __device__ __forceinline__ void store12(double* p, const T3& X) {
   p[9] = X.t.x; p[10] = X.t.y; p[11] = X.t.z;
 }
 
+template <int METHOD>
 __global__ void __launch_bounds__(DT_THREADS, DT_MINB)
-dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
+edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
+  constexpr bool PROG = METHOD == HPPB200_METHOD_PROGRESSIVE;
   extern __shared__ __align__(16) unsigned char smem[];
   const Tables T = makeTables(mv.blob, mv);  // global copy (read-only, L1 resident)
   const TailLayout Lo = tailLayout(mv, A.lists ? 0 : A.K);
@@ -115,9 +120,9 @@ dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
   uint8_t* pflag = (uint8_t*)(smem + Lo.off_pflag);  // by position: PF_* in, decision out
   uint8_t* jdepth = (uint8_t*)(smem + Lo.off_depth);
   uint32_t* visit = (uint32_t*)(smem + Lo.off_visit);
-  __shared__ double s_t, s_ilo, s_ihi;
-  __shared__ int s_run, s_pos, s_smallest, s_subCnt, s_overflow, s_has, s_stop, s_depth;
-  __shared__ uint32_t s_edge, s_iters;
+  __shared__ double s_t, s_ilo, s_ihi, s_last;
+  __shared__ int s_run, s_pos, s_smallest, s_subCnt, s_overflow, s_has, s_stop, s_depth, s_finished;
+  __shared__ uint32_t s_edge, s_iters, s_slot;
 
   const int tid = threadIdx.x;
   const int NP = mv.nbodypairs, NJ = mv.njoints, NG = mv.ngeoms;
@@ -149,7 +154,10 @@ dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
     if (tid == 0) {
       const unsigned long long i = atomicAdd(A.counter, 1ull);
       s_has = i < A.n ? 1 : 0;
-      if (s_has) s_edge = A.edge_list ? A.edge_list[i] : (uint32_t)i;
+      if (s_has) {
+        if (A.resume.slots) { s_slot = A.resume.slots[i]; s_edge = A.resume.st_edge[s_slot]; }
+        else s_edge = A.edge_list ? A.edge_list[i] : (uint32_t)i;
+      }
     }
     __syncthreads();
     if (!s_has) break;
@@ -158,7 +166,8 @@ dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
     const double* q1 = A.q1 + (size_t)edge * mv.nq;
     const double* q2 = A.q2 + (size_t)edge * mv.nq;
     // dichotomy.cc:113-121: the valid part ends where the first (last, if reverse) validated interval ends
-    auto dichLast = [&]() -> double { return reverse ? sub[s_subCnt - 1].x : sub[0].y; };
+    // Progressive: lastValidTime = the last sampled valid parameter (progressive.cc:113-114)
+    auto dichLast = [&]() -> double { return PROG ? s_last : (reverse ? sub[s_subCnt - 1].x : sub[0].y); };
     auto finishEdge = [&](bool ok, int rs, double tf, double tl, int pr) {
       A.valid[edge] = ok ? 1 : 0;
       if (A.t_fail) A.t_fail[edge] = tf;
@@ -198,6 +207,30 @@ dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
       s_subCnt = 1;
       s_iters = 0;
       s_run = RUN_SAMPLE;
+      s_last = t;                                            // progressive.cc:93-100
+      s_finished = (reverse ? t <= 0.0 : t >= L) ? 1 : 0;  // a zero-length path: one configuration to validate
+    }
+    if (PROG && A.resume.slots) {
+      // continue an edge of the wavefront engine (kernels_wavefront.cu) at a sample boundary: order, one validated
+      // interval per pair (by order position there, by pair here), valid_ bits, t, lastValidTime, counters
+      __syncthreads();
+      const TailResume& R = A.resume;
+      const uint32_t e = s_slot;
+      for (int pos = tid; pos < NP; pos += DT_THREADS) {
+        const int id = R.ord[(size_t)e * R.ordStride + pos];
+        order[pos] = (uint16_t)id;
+        const double2 lh = R.lohi[(size_t)pos * R.E + e];
+        const bool isValid = (R.st_vmask[(size_t)(pos >> 6) * R.E + e] >> (pos & 63)) & 1ull;
+        lists[(size_t)id * K] = lh;
+        lcnt[id] = (lh.x > lh.y) ? 0 : 1;
+        state[id] = isValid ? ST_VALID : 0;
+      }
+      if (tid == 0) {
+        s_t = R.st_t[e];
+        s_last = R.st_last[e];
+        s_iters = R.st_iters[e];
+        s_finished = (R.st_flags[e] >> 2) & 3;
+      }
     }
     __syncthreads();
 
@@ -413,12 +446,23 @@ dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
           // src/continuous-validation.cc:144-146: smallest interval first
           const int smallest = s_smallest;
           if (NP > 1 && smallest != 0) { const uint16_t a0 = order[0]; order[0] = order[smallest]; order[smallest] = a0; }
-          over = !wdUnion(sub, 1, sc, DT_KS, ilo, ihi);  // dichotomy.cc:96-109
+          if (!PROG) over = !wdUnion(sub, 1, sc, DT_KS, ilo, ihi);  // dichotomy.cc:96-109
         }
         if (over) {
           if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
           finishEdge(false, A.overflow_reason, t, dichLast(), -1);
           s_run = RUN_FINISHED;
+        } else if (PROG) {  // progressive.cc:104-117
+          double tn = reverse ? ilo : ihi;
+          s_last = t;
+          if (reverse ? tn <= 0.0 : tn >= L) { tn = reverse ? 0.0 : L; s_finished++; }
+          if (s_finished >= 2) {
+            finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
+            s_run = RUN_FINISHED;
+          } else {
+            s_t = tn;
+            s_run = RUN_SAMPLE;
+          }
         } else {
           s_subCnt = sc;
           if (wdContains(sub, 1, sc, 0.0, L)) {
@@ -454,13 +498,14 @@ dichTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
   }
 }
 
-// Runs Dichotomy on the edges of `d_list` (or on all n edges when d_list is null), one CTA per edge.  An edge whose
+// Runs Dichotomy or Progressive on the edges of `d_list` (or on all n edges when d_list is null), one CTA per edge.  An edge whose
 // lists outgrow the capacity is reported with `overflow_reason` (counted in DeviceStats::overflow).  smemLists:
 // per-pair lists in shared memory (as many entries as DT_SMEM_LISTS holds, at most DT_K); else DT_K entries in global memory.
-bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
-                         const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
-                         uint8_t* d_reason, int overflow_reason, bool smemLists) {
+bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
+                    const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
+                    uint8_t* d_reason, int overflow_reason, bool smemLists, const TailResume* resume) {
   const ModelView& mv = ws->view;
+  auto kern = method == HPPB200_METHOD_PROGRESSIVE ? edgeTailKernel<HPPB200_METHOD_PROGRESSIVE> : edgeTailKernel<HPPB200_METHOD_DICHOTOMY>;
   if (n == 0) return true;
   if (mv.nbodypairs > 65535 || mv.nbodypairs == 0) return false;
   int K = DT_K;
@@ -470,9 +515,9 @@ bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d
   }
   const TailLayout Lo = tailLayout(mv, smemLists ? K : 0);
   if (Lo.total > 200u * 1024u) return false;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(dichTailKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Lo.total));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Lo.total));
   int perSM = 0;
-  HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, dichTailKernel, DT_THREADS, Lo.total));
+  HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, DT_THREADS, Lo.total));
   if (perSM < 1) return false;
   const size_t grid = std::min<size_t>(n, (size_t)ws->num_sms * (size_t)perSM);
   const size_t listBytes = smemLists ? 0 : grid * (size_t)mv.nbodypairs * DT_K * sizeof(double2);
@@ -484,10 +529,11 @@ bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d
   A.valid = d_valid; A.t_fail = d_tfail; A.t_last = d_tlast; A.pair = d_pair; A.reason = d_reason;
   A.lists = smemLists ? nullptr : (double2*)ws->d_tail.p;
   A.K = K;
+  if (resume) A.resume = *resume;
   A.counter = (unsigned long long*)(ws->d_tail.p + listBytes);
   A.clk = trace ? A.counter + 1 : nullptr;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.counter, 0, 9 * sizeof(unsigned long long), ws->stream));
-  dichTailKernel<<<(unsigned)grid, DT_THREADS, Lo.total, ws->stream>>>(mv, A, ws->d_stats);
+  kern<<<(unsigned)grid, DT_THREADS, Lo.total, ws->stream>>>(mv, A, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 1;
   if (trace) {
@@ -501,4 +547,13 @@ bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d
   return true;
 }
 
+}  // namespace hppb200
+
+namespace hppb200 {
+bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
+                         const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
+                         uint8_t* d_reason, int overflow_reason, bool smemLists) {
+  return launchEdgeTail(ws, HPPB200_METHOD_DICHOTOMY, tol, reverse, d_q1, d_q2, d_L, d_list, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,
+                        overflow_reason, smemLists, nullptr);
+}
 }  // namespace hppb200

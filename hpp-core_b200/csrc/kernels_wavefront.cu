@@ -70,6 +70,9 @@ struct WFArgs {
   double alpha;
   unsigned long long* counter;  // next edge to hand out
   const uint32_t* perm;         // hand-out order (longest edge first, kernels_sort.cu); null: input order
+  int handover;                 // Progressive: slots that reach a sample boundary leave for the CTA-per-edge kernel
+  uint32_t* hoList;             // ... their slot numbers
+  unsigned* hoCount;
   uint32_t E;                   // edge slots (allocation stride of the [..][E] arrays)
   uint32_t Ecur;                // slots the grids cover; shrinks when the live slots are compacted
   int fkSlots;
@@ -933,10 +936,17 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
   }
 
   // ---- next sample ---------------------------------------------------------------------------------
+  bool handed = false;
   if (needSample) {
     if (iters >= A.max_iter) {
       ++caps;
       finishEdge(false, HPPB200_REASON_ITER_CAP, t, lastValid, -1);
+    } else if (A.handover) {
+      // thin tail of the batch: the edge continues in the CTA-per-edge kernel (kernels_tail.cu) from the state stored
+      // below; a round of three launches for a handful of slots is latency, not throughput
+      handed = true;
+      active = false;
+      retired = true;
     } else {
       ++iters;
       ++samples;
@@ -950,7 +960,7 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
 
   // ---- store the slot state -------------------------------------------------------------------------
   A.st_flags[e] = (uint8_t)((active ? 1 : 0) | (retired ? 2 : 0) | (finished << 2) | ((active && needFK) ? 16 : 0));
-  if (active) {
+  if (active || handed) {
     A.st_t[e] = t; A.st_last[e] = lastValid; A.st_hp[e] = hp; A.st_ilo[e] = ilo; A.st_ihi[e] = ihi; A.st_L[e] = L;
     A.st_edge[e] = edge; A.st_iters[e] = iters;
     A.st_pos[e] = (uint32_t)pos | ((uint32_t)smallest << 16);
@@ -958,6 +968,7 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
 #pragma unroll
     for (int w = 0; w < W; ++w) A.st_vmask[(size_t)w * E + e] = vmask[w];
   }
+  if (handed) A.hoList[atomicAdd(A.hoCount, 1u)] = e;
   wfPublish(A, stats, sCnt, lane, retired, samples, discarded, caps, overflows);
 }
 
@@ -1617,6 +1628,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   const size_t o_res = c.take<double>(RG * E), o_plc = c.take<double>(E * (size_t)A.fkSlots * 12);
   const size_t o_jG = c.take<unsigned long long>(E * RG), o_jC = c.take<unsigned long long>(E * RG);
   const size_t o_cmp = c.take<uint32_t>(2 * E + 4);  // compaction: source slots, destination slots, two counters
+  const size_t o_ho = c.take<uint32_t>(E + 4);       // hand-over to the CTA-per-edge kernel: counter, slot list
   ws->d_state.reserve(c.off + 256);
   unsigned char* base = ws->d_state.p;
   A.counter = (unsigned long long*)(base + o_counter);
@@ -1674,12 +1686,22 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   unsigned* d_cnt = (unsigned*)(d_dst + E);
   bool compactOn = true;
   if (const char* v = std::getenv("HPPB200_WF_COMPACT")) compactOn = std::atoi(v) != 0;
+  // Progressive: when this few slots are alive the edges continue one CTA each (kernels_tail.cu), from where they are
+  A.hoCount = (unsigned*)(base + o_ho);
+  A.hoList = (uint32_t*)(base + o_ho) + 4;
+  unsigned handSlots = (!dich && !foldKernel) ? 4096u : 0u;
+  if (const char* v = std::getenv("HPPB200_WF_HAND")) handSlots = (!dich && !foldKernel) ? (unsigned)std::atol(v) : 0u;
+  const int tailK = std::min(64, (int)(65536 / (16 * std::max(1, NP))));
+  if (tailK < 8) handSlots = 0;
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(A.hoCount, 0, 4 * sizeof(unsigned), ws->stream));
+  int batch = BATCH;
 
   wfInitKernel<<<(unsigned)((E + 255) / 256), 256, 0, ws->stream>>>(A);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 1;
   int round = 0;
   unsigned h_alive = 1;
+  unsigned long long h_counter = 0;
   const bool trace = std::getenv("HPPB200_WF_TRACE") != nullptr;  // per-round kernel times on stderr (debug)
   std::vector<cudaEvent_t> evs;
   struct TraceRow { unsigned alive, nG, nC; };
@@ -1687,7 +1709,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   const bool traceAll = trace && std::atoi(std::getenv("HPPB200_WF_TRACE")) > 1;
   while (h_alive) {
     HPPB200_CUDA_CHECK(cudaMemsetAsync(A.alive, 0, BATCH * sizeof(unsigned), ws->stream));
-    for (int k = 0; k < BATCH; ++k, ++round) {
+    for (int k = 0; k < batch; ++k, ++round) {
       A.round = round;
       A.aliveIdx = k;
       auto mark = [&]() {
@@ -1717,18 +1739,24 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
       }
     }
     HPPB200_CUDA_CHECK(cudaGetLastError());
-    ws->stats.kernel_launches += 4 * BATCH;
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h_alive, A.alive + (BATCH - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream));
+    ws->stats.kernel_launches += (foldKernel ? 4 : 3) * batch;
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h_alive, A.alive + (batch - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h_counter, A.counter, sizeof(h_counter), cudaMemcpyDeviceToHost, ws->stream));
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    const bool exhausted = h_counter >= (unsigned long long)n;  // every edge has been handed to a slot
     if (h_alive && h_alive <= tailSlots) {  // (slots hold edges only: the edge counter is exhausted long before)
       wfAbandonKernel<<<(unsigned)((A.Ecur + 255) / 256), 256, 0, ws->stream>>>(A, ws->d_stats);
       HPPB200_CUDA_CHECK(cudaGetLastError());
       ws->stats.kernel_launches += 1;
       break;
     }
+    if (handSlots && !A.handover && exhausted && h_alive && h_alive <= handSlots) {
+      A.handover = 1;  // (slots in the middle of a sample finish it first: a few more rounds)
+      batch = 2;
+    }
     // fewer live slots than the grids cover (only once the edge counter is exhausted): compact and shrink
     const uint32_t Enew = (uint32_t)(((size_t)h_alive + WF_CTHREADS - 1) / WF_CTHREADS * WF_CTHREADS);
-    if (compactOn && h_alive && (size_t)Enew * 8 <= (size_t)A.Ecur * 7) {
+    if (compactOn && !A.handover && exhausted && h_alive && (size_t)Enew * 8 <= (size_t)A.Ecur * 7) {
       HPPB200_CUDA_CHECK(cudaMemsetAsync(d_cnt, 0, 2 * sizeof(unsigned), ws->stream));
       wfCompactListKernel<<<(A.Ecur + 255) / 256, 256, 0, ws->stream>>>(A, A.Ecur, Enew, d_src, d_dst, d_cnt);
       const unsigned maxMoves = A.Ecur - Enew;  // at most that many live slots above the new extent
@@ -1738,6 +1766,20 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
       A.Ecur = Enew;
       gridC = Enew / WF_CTHREADS;
       gridF = (unsigned)(((size_t)Enew * RB + 255) / 256);
+    }
+  }
+  if (A.handover) {
+    unsigned nho = 0;
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(&nho, A.hoCount, sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    if (trace) std::fprintf(stderr, "[wf] %u edges continue one CTA each after round %d\n", nho, round);
+    if (nho) {
+      TailResume R;
+      R.slots = A.hoList; R.E = A.E; R.ordStride = A.ordStride; R.lohi = A.lohi; R.ord = A.ord; R.st_vmask = A.st_vmask;
+      R.st_t = A.st_t; R.st_last = A.st_last; R.st_iters = A.st_iters; R.st_edge = A.st_edge; R.st_flags = A.st_flags;
+      if (!launchEdgeTail(ws, method, tol, reverse, d_q1, d_q2, d_L, nullptr, nho, d_valid, d_tfail, d_tlast, d_pair, d_reason,
+                          overflow_reason, true, &R))
+        throw std::runtime_error("wavefront hand-over: the CTA-per-edge kernel does not fit this model");
     }
   }
   if (trace) {
