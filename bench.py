@@ -13,8 +13,11 @@ the path.  One JSON line on rank 0 (contract in the task statement):
   roofline   FP64 pipe (the kernel is compute bound: 53 algorithmic bytes vs ~5e4 flops per
              configuration); achieved = oracle-counted algorithmic flops / kernel time, peak =
              DFMA peak measured live by hppb200_measure_fp64_peak; the HBM view is reported beside it
-  cpu_baseline  the oracle (CPU restatement of the reference algorithm) on a bounded sample
-  edges      secondary metric: Progressive(1e-3) StraightPath edges/s on the same scene
+  cpu_baseline  the oracle (CPU restatement of the reference algorithm) on a bounded sample, warm-up + best of 3
+  edges      the metric's other half: validated StraightPath edges/s — Progressive(1e-3) and Dichotomy(0) on 1 M random
+             UR5 edges (one GPU's share of BASELINE configs[4]), Discretized(0.05), and BASELINE configs[3]:
+             Dichotomy on 1 M local edges of the 30-joint tree model with convex meshes; each with its own FP64
+             roofline (oracle-counted flops of THAT batch / CUDA-event time / live DFMA peak), e2e and cpu_baseline
 `--impl reference` times the reference algorithm's CPU implementation (oracle port: the reference
 binary cannot be built here) on all host threads.
 """
@@ -36,9 +39,19 @@ N_EDGES = 1 << 17            # edges per GPU for the secondary metric (Discretiz
 N_EDGES_PROG = 1 << 20       # Progressive, Dichotomy: 1M edges per GPU (BASELINE configs[4]: 10M edges over 8 GPUs)
 SEED = 12345
 MODEL = "ur5_boxes8.json"
+MODEL_HUMANOID = "humanoid_obst16.json"   # BASELINE configs[3]: 30-joint tree, 133 body pairs, convex meshes
+HUMANOID_STEP = 0.2                        # local ("RRT-like") edges: |q2 - q1| = 0.2
 # Algorithmic flop model (FMA = 2): FK = 126*njoints + 63*ngeoms + 40*njoints (sincos);
 # closed-form pair ~110; GJK call = 70 (relative placement + sqrt) + 110 per iteration.
 FLOPS_FK = 126 * 6 + 63 * 8 + 40 * 6
+
+
+def flops_fk(desc):
+    return 126 * desc.njoints + 63 * desc.ngeoms + 40 * desc.njoints
+
+
+WORKLOAD = ("UR5 + 8 boxes: 1M uniform random configurations through CollisionValidation "
+            "(FK + narrow phase) per GPU per step (BASELINE configs[1])")
 FLOPS_CLOSED = 110
 FLOPS_GJK_CALL = 70
 FLOPS_GJK_ITER = 110
@@ -106,7 +119,18 @@ def oracle_counts(orc, q):
                 closed_per_config=cl / n)
 
 
-def cpu_rate_configs(orc, desc, mio, threads, budget_s=12.0):
+def best_of(fn, reps=3):
+    """warm-up call, then the best of `reps` timed calls"""
+    fn()
+    best = 1e30
+    for _ in range(reps):
+        t = time.perf_counter()
+        fn()
+        best = min(best, time.perf_counter() - t)
+    return best
+
+
+def cpu_rate_configs(orc, desc, mio, threads, budget_s=4.0):
     """oracle configs/s on a bounded sample of the same workload (first configurations of rank 0's batch)."""
     q = mio.uniform_configs(desc, 20000, seed=SEED)
     t = time.perf_counter()
@@ -114,22 +138,32 @@ def cpu_rate_configs(orc, desc, mio, threads, budget_s=12.0):
     rate = 20000 / (time.perf_counter() - t)
     n = int(min(N_CONFIGS, max(20000, rate * budget_s)))
     q = mio.uniform_configs(desc, n, seed=SEED)
-    t = time.perf_counter()
-    orc.validate_configs(q, nthreads=threads)
-    dt = time.perf_counter() - t
+    dt = best_of(lambda: orc.validate_configs(q, nthreads=threads))
     return n / dt, n, dt
 
 
-def cpu_rate_edges(orc, q1, q2, L, threads, budget_s=10.0):
+def cpu_rate_edges(orc, meth, par, q1, q2, L, threads, budget_s=3.0):
     n0 = min(2000, len(L))
     t = time.perf_counter()
-    orc.validate_edges(1, 1e-3, q1[:n0], q2[:n0], L[:n0], nthreads=threads)
+    orc.validate_edges(meth, par, q1[:n0], q2[:n0], L[:n0], nthreads=threads)
     rate = n0 / (time.perf_counter() - t)
     n = int(min(len(L), max(n0, rate * budget_s)))
-    t = time.perf_counter()
-    orc.validate_edges(1, 1e-3, q1[:n], q2[:n], L[:n], nthreads=threads)
-    dt = time.perf_counter() - t
+    dt = best_of(lambda: orc.validate_edges(meth, par, q1[:n], q2[:n], L[:n], nthreads=threads))
     return n / dt, n, dt
+
+
+def oracle_edge_work(orc, desc, meth, par, q1, q2, L, n=20000):
+    """Algorithmic flops per edge of the REFERENCE algorithm on the first n edges of the batch (oracle counters)."""
+    n = min(n, len(L))
+    c0 = orc.counters()
+    orc.validate_edges(meth, par, q1[:n], q2[:n], L[:n])
+    c1 = orc.counters()
+    d = {k: (c1[k] - c0[k]) / n for k in c1}
+    flops = (d["samples"] * (flops_fk(desc) + 3 * desc.nq) + d["closed_form_calls"] * FLOPS_CLOSED
+             + d["gjk_calls"] * FLOPS_GJK_CALL + d["gjk_iterations"] * FLOPS_GJK_ITER)
+    return dict(flops_per_edge=flops, samples_per_edge=d["samples"], gjk_calls_per_edge=d["gjk_calls"],
+                gjk_iters_per_edge=d["gjk_iterations"], closed_per_edge=d["closed_form_calls"],
+                body_pair_evals_per_edge=d["pair_evals"], counted_on=n)
 
 
 def run_reference(args):
@@ -162,9 +196,8 @@ def run_reference(args):
         "impl": "reference", "metric": "validated configs/sec", "value": value, "unit": "configs/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "UR5 + 8 boxes: uniform random configurations through CollisionValidation "
-                               "(FK + narrow phase), CPU reference algorithm", "model": MODEL,
-                   "configs_per_step": n, "seed": SEED},
+        "config": {"workload": WORKLOAD, "model": MODEL, "configs_per_gpu_per_step": N_CONFIGS, "seed": SEED,
+                   "reference_sample_per_step": n},
         "cpu_baseline": {"value": value, "unit": "configs/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": "configs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -186,7 +219,10 @@ def run_b200(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        os.environ["NCCL_DEBUG"] = os.environ.get("HPPB200_NCCL_DEBUG", "NONE")  # keep stdout to the one JSON line
+        # NCCL's own log (rank counts, NVLS/ring choice) goes to stderr so that stdout stays the one JSON line
+        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
 
     desc = pkg.ModelDescription.load(MODEL)
@@ -259,7 +295,7 @@ def run_b200(args):
 
     # ---- N > 1: every rank validates its own shard of edges (Progressive), validity masks all-gathered ----
     edges_sharded = None
-    if world > 1 and not args.no_edges:
+    if not args.no_edges:
         ne = N_EDGES_PROG
         cfg = pkg.uniform_configs(desc, 2 * ne, seed=SEED + 1, offset=rank * 2 * ne)
         s1d = torch.from_numpy(np.ascontiguousarray(cfg[0::2])).to(dev)
@@ -270,16 +306,18 @@ def run_b200(args):
         stl = torch.empty(ne, dtype=torch.float64, device=dev)
         spr = torch.empty(ne, dtype=torch.int32, device=dev)
         srs = torch.empty(ne, dtype=torch.uint8, device=dev)
-        sv_all = torch.empty(ne * world, dtype=torch.uint8, device=dev)
+        sv_all = torch.empty(ne * world, dtype=torch.uint8, device=dev) if world > 1 else None
 
         def shard_call():
             ws.validate_edges_ptr(pkg.METHOD_PROGRESSIVE, 1e-3, False, s1d.data_ptr(), s2d.data_ptr(), sLd.data_ptr(), ne,
                                   sv.data_ptr(), stf.data_ptr(), stl.data_ptr(), spr.data_ptr(), srs.data_ptr(), FLAGS_DEV)
-            dist.all_gather_into_tensor(sv_all, sv)
+            if world > 1:
+                dist.all_gather_into_tensor(sv_all, sv)
         ms_s, _, _ = timed(shard_call, 3, 1)
         edges_sharded = {"value": world * ne * 3 / (ms_s * 1e-3), "unit": "edges/s", "edges_per_gpu": ne, "param": 1e-3,
-                         "method": "progressive", "collective": "all_gather of uint8 validity masks (NCCL)",
-                         "valid_frac_all_ranks": float(sv_all.float().mean().item())}
+                         "method": "progressive", "ms_per_call": ms_s / 3,
+                         "collective": "all_gather of uint8 validity masks (NCCL)" if world > 1 else "none",
+                         "valid_frac_all_ranks": float((sv_all if world > 1 else sv).float().mean().item())}
         del s1d, s2d, sLd, sv, stf, stl, spr, srs, sv_all
 
     if rank != 0:
@@ -305,11 +343,17 @@ def run_b200(args):
     except Exception:
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    traffic = {}
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch from an `ncu --set full` capture of THIS build
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except Exception:
+        pass
     roofline = {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 # dram__bytes_read.sum + dram__bytes_write.sum per launch, ncu --set full, 1 M configurations
                 # (profiles/r1b_configPass_gjkJobs_ncu_full.txt): the placement scratch written once per configuration;
                 # removing it was measured slower
-                "traffic": 832.2e6 if n == (1 << 20) else None, "traffic_unit": "B per launch of configPassKernel",
+                "traffic": traffic.get("configPassKernel_dram_bytes") if n == (1 << 20) else None,
+                "traffic_unit": "B per launch of configPassKernel", "traffic_source": traffic.get("source"),
                 "peak_source": "hppb200_measure_fp64_peak (DFMA chains, measured live)",
                 "kernel": "configPassKernel + gjkJobsKernel", "algorithmic_flops_per_config": work["flops_per_config"],
                 "hbm": {"achieved": BYTES_PER_CONFIG * n / per_launch_s / 1e9, "peak": hbm_peak, "unit": "GB/s",
@@ -324,44 +368,86 @@ def run_b200(args):
                "sample": "first %d of the %d configurations of the step batch, %.1f s" % (ns, n, dt)}
     edges = None
     if not args.no_edges:
-        ne_max = max(N_EDGES, N_EDGES_PROG)
-        ne = ne_max
-        cfg = pkg.uniform_configs(desc, 2 * ne, seed=SEED + 1, offset=0)
-        e1h = torch.from_numpy(np.ascontiguousarray(cfg[0::2])).pin_memory()
-        e2h = torch.from_numpy(np.ascontiguousarray(cfg[1::2])).pin_memory()
-        L_h = torch.from_numpy(ws.straight_lengths(e1h.numpy(), e2h.numpy())).pin_memory()
-        e1d, e2d, Ld = e1h.to(dev), e2h.to(dev), L_h.to(dev)
-        ev_d = torch.empty(ne, dtype=torch.uint8, device=dev)
-        tf_d = torch.empty(ne, dtype=torch.float64, device=dev)
-        tl_d = torch.empty(ne, dtype=torch.float64, device=dev)
-        pr_d = torch.empty(ne, dtype=torch.int32, device=dev)
-        rs_d = torch.empty(ne, dtype=torch.uint8, device=dev)
-        ev_h = torch.empty(ne, dtype=torch.uint8).pin_memory()
-        tf_h = torch.empty(ne, dtype=torch.float64).pin_memory()
+        def edge_suite(label, e_desc, e_model, e_ws, e_orc, meth, par, q1n, q2n, ne):
+            """device (inputs in HBM), e2e (host buffers, all five outputs copied back), roofline, cpu_baseline"""
+            e1h = torch.from_numpy(np.ascontiguousarray(q1n)).pin_memory()
+            e2h = torch.from_numpy(np.ascontiguousarray(q2n)).pin_memory()
+            L_h = torch.from_numpy(e_ws.straight_lengths(e1h.numpy(), e2h.numpy())).pin_memory()
+            e1d, e2d, Ld = e1h.to(dev), e2h.to(dev), L_h.to(dev)
+            ev_d = torch.empty(ne, dtype=torch.uint8, device=dev)
+            tf_d = torch.empty(ne, dtype=torch.float64, device=dev)
+            tl_d = torch.empty(ne, dtype=torch.float64, device=dev)
+            pr_d = torch.empty(ne, dtype=torch.int32, device=dev)
+            rs_d = torch.empty(ne, dtype=torch.uint8, device=dev)
+            ev_h = torch.empty(ne, dtype=torch.uint8).pin_memory()
+            tf_h = torch.empty(ne, dtype=torch.float64).pin_memory()
+            tl_h = torch.empty(ne, dtype=torch.float64).pin_memory()
+            pr_h = torch.empty(ne, dtype=torch.int32).pin_memory()
+            rs_h = torch.empty(ne, dtype=torch.uint8).pin_memory()
+
+            def dev_call():
+                e_ws.validate_edges_ptr(meth, par, False, e1d.data_ptr(), e2d.data_ptr(), Ld.data_ptr(), ne, ev_d.data_ptr(),
+                                        tf_d.data_ptr(), tl_d.data_ptr(), pr_d.data_ptr(), rs_d.data_ptr(), FLAGS_DEV)
+
+            def host_call():
+                e_ws.validate_edges_ptr(meth, par, False, e1h.data_ptr(), e2h.data_ptr(), L_h.data_ptr(), ne, ev_h.data_ptr(),
+                                        tf_h.data_ptr(), tl_h.data_ptr(), pr_h.data_ptr(), rs_h.data_ptr(), 0)
+            s0 = e_ws.stats()
+            ms_d, _, _ = timed(dev_call, 3, 1, all_ranks=False)
+            s1 = e_ws.stats()
+            ms_h, _, _ = timed(host_call, 3, 1, all_ranks=False)
+            same = bool(torch.equal(ev_h, ev_d.cpu()) and torch.equal(pr_h, pr_d.cpu()))
+            out = {"value": ne * 3 / (ms_d * 1e-3), "unit": "edges/s", "n_edges": ne, "param": par, "model": e_desc.name,
+                   "ms_per_call": ms_d / 3,
+                   "e2e": {"value": ne * 3 / (ms_h * 1e-3), "unit": "edges/s", "ms_per_call": ms_h / 3,
+                           "h2d_bytes_per_step": ne * (2 * e_model.nq + 1) * 8, "d2h_bytes_per_step": ne * (1 + 8 + 8 + 4 + 1)},
+                   "device_and_host_paths_identical": same,
+                   "valid_frac": float(ev_h.numpy()[:ne].mean()),
+                   "kernel_launches_per_call": (s1["kernel_launches"] - s0["kernel_launches"]) / 4,
+                   "samples_per_edge": (s1["edge_samples"] - s0["edge_samples"]) / (4 * ne),
+                   "pair_tests_per_edge": (s1["pair_tests"] - s0["pair_tests"]) / (4 * ne)}
+            if not args.no_cpu:
+                q1s, q2s, Ls = e1h.numpy(), e2h.numpy(), L_h.numpy()
+                work = oracle_edge_work(e_orc, e_desc, meth, par, q1s, q2s, Ls)
+                ach = work["flops_per_edge"] * ne / (ms_d * 1e-3 / 3) / 1e12
+                out["roofline"] = {"bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                                   "algorithmic_flops_per_edge": work["flops_per_edge"], "work": work,
+                                   "peak_source": "hppb200_measure_fp64_peak (DFMA chains, measured live)",
+                                   "kernel_shares": traffic.get(label + "_kernel_shares"),
+                                   "hbm": {"achieved": ne * ((2 * e_model.nq + 1) * 8 + 22) / (ms_d * 1e-3 / 3) / 1e9,
+                                           "peak": hbm_peak, "unit": "GB/s"}}
+                # parity of the leading edges against the oracle (the same call the counters came from)
+                chk = min(ne, 20000)
+                oe = e_orc.validate_edges(meth, par, q1s[:chk], q2s[:chk], Ls[:chk])
+                out["parity_vs_oracle"] = bool(np.array_equal(oe["valid"], ev_h.numpy()[:chk])
+                                               and np.array_equal(oe["t_fail"], tf_h.numpy()[:chk], equal_nan=True)
+                                               and np.array_equal(oe["t_last_valid"], tl_h.numpy()[:chk])
+                                               and np.array_equal(oe["pair"], pr_h.numpy()[:chk]))
+                rate, ns, dt = cpu_rate_edges(e_orc, meth, par, q1s, q2s, Ls, threads)
+                out["cpu_baseline"] = {"value": rate, "unit": "edges/s", "cores": threads, "kind": "port",
+                                       "sample": "first %d of the %d edges, warm-up + best of 3 (%.1f s)" % (ns, ne, dt)}
+            return out
+
+        cfg = pkg.uniform_configs(desc, 2 * N_EDGES_PROG, seed=SEED + 1, offset=0)
         res = {}
         for name, meth, par in (("progressive", pkg.METHOD_PROGRESSIVE, 1e-3), ("discretized", pkg.METHOD_DISCRETIZED, 0.05),
                                 ("dichotomy", pkg.METHOD_DICHOTOMY, 0.0)):
             ne = N_EDGES if name == "discretized" else N_EDGES_PROG  # leading `ne` edges of the same stream
-
-            def dev_call():
-                ws.validate_edges_ptr(meth, par, False, e1d.data_ptr(), e2d.data_ptr(), Ld.data_ptr(), ne, ev_d.data_ptr(),
-                                      tf_d.data_ptr(), tl_d.data_ptr(), pr_d.data_ptr(), rs_d.data_ptr(), FLAGS_DEV)
-
-            def host_call():
-                ws.validate_edges_ptr(meth, par, False, e1h.data_ptr(), e2h.data_ptr(), L_h.data_ptr(), ne, ev_h.data_ptr(),
-                                      tf_h.data_ptr(), 0, 0, 0, 0)
-            s0 = ws.stats()
-            ms_d, _, _ = timed(dev_call, 3, 1, all_ranks=False)
-            s1 = ws.stats()
-            ms_h, _, _ = timed(host_call, 3, 1, all_ranks=False)
-            res[name] = {"value": ne * 3 / (ms_d * 1e-3), "e2e": ne * 3 / (ms_h * 1e-3), "unit": "edges/s", "n_edges": ne,
-                         "param": par, "valid_frac": float(ev_h.numpy()[:ne].mean()),
-                         "samples_per_edge": (s1["edge_samples"] - s0["edge_samples"]) / (4 * ne),
-                         "pair_tests_per_edge": (s1["pair_tests"] - s0["pair_tests"]) / (4 * ne)}
-        if not args.no_cpu:
-            rate, ns, dt = cpu_rate_edges(orc, e1h.numpy(), e2h.numpy(), L_h.numpy(), threads)
-            res["progressive"]["cpu_baseline"] = {"value": rate, "unit": "edges/s", "cores": threads, "kind": "port",
-                                                  "sample": "first %d of the %d edges, %.1f s" % (ns, N_EDGES_PROG, dt)}
+            res[name] = edge_suite(name, desc, model, ws, orc, meth, par, cfg[0:2 * ne:2], cfg[1:2 * ne:2], ne)
+        # BASELINE configs[3]: 30-joint tree with convex meshes, Dichotomy, 1 M local edges
+        hdesc = pkg.ModelDescription.load(MODEL_HUMANOID)
+        hmodel = pkg.Model(hdesc)
+        hws = pkg.Workspace(hmodel, local_rank)
+        hws.set_stream(stream.cuda_stream)
+        horc = ob.Oracle(hdesc)
+        hq1 = pkg.uniform_configs(hdesc, N_EDGES_PROG, seed=SEED + 5)
+        hd = pkg.uniform_configs(hdesc, N_EDGES_PROG, seed=SEED + 6) - hq1
+        hq2 = pkg.normalize_quaternions(hdesc, np.clip(hq1 + HUMANOID_STEP * hd / np.linalg.norm(hd, axis=1, keepdims=True),
+                                                       hdesc.q_lower, hdesc.q_upper))
+        for name, meth, par in (("dichotomy_humanoid", pkg.METHOD_DICHOTOMY, 0.0), ("progressive_humanoid", pkg.METHOD_PROGRESSIVE, 1e-3)):
+            res[name] = edge_suite(name, hdesc, hmodel, hws, horc, meth, par, hq1, hq2, N_EDGES_PROG)
+            res[name]["edges"] = "local: |q2 - q1| = %g in configuration space (SURVEY 8d C4)" % HUMANOID_STEP
+        del hws, hmodel
         edges = res
     knn = None
     if not args.no_edges:
@@ -424,9 +510,7 @@ def run_b200(args):
         "metric": "validated configs/sec", "value": value, "unit": "configs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "UR5 + 8 boxes: 1M uniform random configurations through CollisionValidation "
-                               "(FK + narrow phase) per GPU per step (BASELINE configs[1])",
-                   "model": MODEL, "configs_per_gpu_per_step": n, "seed": SEED, "pairs": int(len(model.config_pairs()[0])),
+        "config": {"workload": WORKLOAD, "model": MODEL, "configs_per_gpu_per_step": n, "seed": SEED, "pairs": int(len(model.config_pairs()[0])),
                    "l2": "flushed between timed steps (256 MiB memset, untimed)",
                    "collective": "all_gather of uint8 validity masks (NCCL)" if world > 1 else "none"},
         "e2e": {"value": e2e_value, "unit": "configs/s", "h2d_bytes_per_step": n * nq * 8, "d2h_bytes_per_step": n * 6,

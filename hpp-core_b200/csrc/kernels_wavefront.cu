@@ -1589,6 +1589,12 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   A.overflow_reason = overflow_reason;
   A.perm = (ws->wavefront_lpt && n > 1) ? sortEdgesByLength(ws, d_L, n) : nullptr;
   A.alpha = ws->engine_alpha;
+  // Progressive, second control form: the candidate window is computed from the FINAL intersection of the sample, so it
+  // needs no slack: alpha 1.0 (discarded tests 9 % -> 1.3 %, same number of rounds; 217 -> 209 ms per 1 M UR5 edges)
+  if (method == HPPB200_METHOD_PROGRESSIVE) {
+    A.alpha = 1.0;
+    if (const char* v = std::getenv("HPPB200_WF_ALPHA")) A.alpha = std::atof(v);
+  }
   A.refill_min = WF_REFILL_MIN;
   if (const char* v = std::getenv("HPPB200_WF_REFILL")) A.refill_min = std::atoi(v);
   A.fkSlots = mv.ngeoms + (tree ? mv.njoints : 0);

@@ -158,9 +158,10 @@ int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse
   if (nthreads <= 0) nthreads = omp_get_max_threads();
   if (order_mode == ORDER_PERSISTENT) nthreads = 1;  // history-dependent: sequential like one reference thread
   int err = 0;
-  uint64_t evals = 0, nsamples = 0;
-#pragma omp parallel num_threads(nthreads) reduction(+ : evals, nsamples)
+  uint64_t evals = 0, nsamples = 0, calls = 0, iters = 0, closed = 0;
+#pragma omp parallel num_threads(nthreads) reduction(+ : evals, nsamples, calls, iters, closed)
   {
+    GjkStats st;  // per thread: GJK calls / iterations / closed-form calls of the edges it validates
     try {
       std::unique_ptr<Discretized> disc;
       std::unique_ptr<Progressive> prog;
@@ -173,9 +174,9 @@ int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse
         StraightPath path(d, q1 + (size_t)i * d.nq, q2 + (size_t)i * d.nq, L[i]);
         PathReport R;
         uint64_t ev = 0;
-        if (disc) R = disc->validate(path, reverse != 0);
-        else if (prog) R = prog->validate(path, reverse != 0, nullptr, &ev);
-        else R = dich->validate(path, reverse != 0, nullptr, &ev);
+        if (disc) R = disc->validate(path, reverse != 0, &st);
+        else if (prog) R = prog->validate(path, reverse != 0, &st, &ev);
+        else R = dich->validate(path, reverse != 0, &st, &ev);
         valid[i] = R.valid ? 1 : 0;
         if (t_fail) t_fail[i] = R.parameter;
         if (t_last_valid) t_last_valid[i] = R.lastValid;
@@ -188,8 +189,10 @@ int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse
 #pragma omp critical
       { g_err = e.what(); err = 2; }
     }
+    calls += st.calls; iters += st.iterations; closed += st.closed;
   }
   h->pairEvals += evals; h->samples += nsamples;
+  h->stats.calls += calls; h->stats.iterations += iters; h->stats.closed += closed;
   return err;
 }
 
