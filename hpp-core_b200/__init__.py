@@ -45,7 +45,7 @@ class hppb200_stats(C.Structure):
 ABI_SYMBOLS = [
     "hppb200_abi_version", "hppb200_last_error", "hppb200_device_count", "hppb200_measure_fp64_peak",
     "hppb200_model_create", "hppb200_model_destroy", "hppb200_model_nq", "hppb200_model_nv",
-    "hppb200_model_num_config_pairs", "hppb200_model_get_config_pairs", "hppb200_model_num_body_pairs",
+    "hppb200_model_num_config_pairs", "hppb200_model_get_config_pairs", "hppb200_model_num_parameterized_pairs", "hppb200_model_num_body_pairs",
     "hppb200_model_get_body_pairs", "hppb200_model_num_body_geom_pairs", "hppb200_model_get_body_geom_pairs",
     "hppb200_model_num_coefficients", "hppb200_model_get_coefficients", "hppb200_model_get_body_radii",
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",

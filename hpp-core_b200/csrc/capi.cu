@@ -131,6 +131,7 @@ int hppb200_model_get_config_pairs(const hppb200_model* m, int32_t* a, int32_t* 
   }
   return HPPB200_OK;
 }
+int hppb200_model_num_parameterized_pairs(const hppb200_model* m) { return m->impl.nParameterized; }
 int hppb200_model_num_body_pairs(const hppb200_model* m) { return (int)m->impl.bodyPairs.size(); }
 int hppb200_model_get_body_pairs(const hppb200_model* m, int32_t* ja, int32_t* jb, int32_t* pair_begin,
                                  int32_t* coef_begin, int32_t* rcoef_begin) {

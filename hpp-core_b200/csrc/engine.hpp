@@ -92,7 +92,9 @@ struct Model {
   std::vector<double> lower, upper, weights, margins, vertices, radii;
   double break_distance = 1e-2;
   // reference-order tables (for the query API and reports)
-  std::vector<DevPair> cPairs;        // first/second as in cPairs_ (NOT canonicalised)
+  std::vector<DevPair> cPairs;        // first/second as in cPairs_ (NOT canonicalised); pPairs_ appended when checked
+  std::vector<DevPair> pPairs, dPairs;  // parameterized / disabled pairs (ObstacleUser::filterCollisionPairs)
+  int nParameterized = 0;             // trailing entries of cPairs that are pPairs_
   std::vector<BodyPairHost> bodyPairs;
   // device
   std::vector<unsigned char> blob;
@@ -102,6 +104,7 @@ struct Model {
  private:
   void buildConfigPairs(const hppb200_model_desc& d);
   void buildBodyPairs(const hppb200_model_desc& d);
+  void applyPairOps(const hppb200_model_desc& d);
   void buildBlob();
   double margin(int j1, int j2) const { return margins.empty() ? 0.0 : margins[(size_t)j1 * (njoints + 1) + j2]; }
   mutable std::mutex mu_;

@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstring>
+#include <functional>
 
 #include "engine.hpp"
 
@@ -147,7 +148,112 @@ Model::Model(const hppb200_model_desc& d) {
   }
   buildConfigPairs(d);
   buildBodyPairs(d);
+  applyPairOps(d);
+  if (d.check_parameterized) {  // CollisionValidation::validate tests pPairs_ after cPairs_ (collision-validation.cc:62-67)
+    nParameterized = (int)pPairs.size();
+    cPairs.insert(cPairs.end(), pPairs.begin(), pPairs.end());
+  }
   buildBlob();
+}
+
+// The ObstacleUserInterface calls an hpp-core validator received after construction, replayed in order on the two
+// tables (configuration pairs: reference src/obstacle-user.cc:60-220; continuous body pairs:
+// src/continuous-validation.cc:224-367, solid-solid-collision.cc:101-122).
+void Model::applyPairOps(const hppb200_model_desc& d) {
+  if (d.npair_ops <= 0) return;
+  if (!d.pair_ops) throw std::invalid_argument("pair_ops is null");
+  const int n1 = njoints + 1;
+  auto jointOf = [&](int ref) { return ref >= 0 ? geoms[ref].joint : 0; };
+  auto checkObstacle = [&](int o) { if (o < 0 || o >= (int)obstacles.size()) throw std::invalid_argument("pair op: obstacle index out of range"); };
+  auto checkJoint = [&](int j) { if (j < 1 || j > njoints) throw std::invalid_argument("pair op: joint index out of range"); };
+  for (int k = 0; k < d.npair_ops; ++k) {
+    const hppb200_pair_op& op = d.pair_ops[k];
+    switch (op.kind) {
+      case HPPB200_OP_ADD_OBSTACLE_TO_JOINT: {  // obstacle-user.cc:60-76
+        checkObstacle(op.a); checkJoint(op.b);
+        std::vector<int> stack{op.b};
+        // recursion of the reference: the joint's inner objects, then each child joint in order (depth first)
+        std::function<void(int)> add = [&](int j) {
+          for (int g = 0; g < (int)geoms.size(); ++g)
+            if (geoms[g].joint == j) cPairs.push_back(DevPair{g, -(op.a + 1), 0, 0, 0.0, 0.0});
+          if (op.flag)
+            for (int c = 1; c <= njoints; ++c)
+              if (joints[c - 1].parent == j) add(c);
+        };
+        add(op.b);
+        break;
+      }
+      case HPPB200_OP_REMOVE_OBSTACLE_FROM_JOINT: {  // obstacle-user.cc:87-118, continuous-validation.cc:224-252
+        checkObstacle(op.a); checkJoint(op.b);
+        const int oref = -(op.a + 1);
+        for (int g = 0; g < (int)geoms.size(); ++g) {
+          if (geoms[g].joint != op.b) continue;
+          size_t deleted = 0;
+          for (size_t i = 0; i < cPairs.size();)
+            if (cPairs[i].a == g && cPairs[i].b == oref) { cPairs.erase(cPairs.begin() + i); ++deleted; }
+            else ++i;
+          if (!deleted) throw std::runtime_error("removeObstacleFromJoint: the obstacle is not registered as obstacle for the joint");
+        }
+        bool removed = false, hasBody = false;
+        for (const DevGeom& G : geoms) hasBody = hasBody || G.joint == op.b;
+        for (size_t i = 0; i < bodyPairs.size();) {
+          BodyPairHost& bp = bodyPairs[i];
+          bool erased = false;
+          if (bp.joint_a == op.b && bp.joint_b == 0) {
+            const size_t before = bp.pairs.size();
+            bp.pairs.erase(std::remove_if(bp.pairs.begin(), bp.pairs.end(), [&](const DevPair& p) { return p.b == oref; }), bp.pairs.end());
+            if (bp.pairs.size() != before) {
+              removed = true;
+              if (bp.pairs.empty()) { bodyPairs.erase(bodyPairs.begin() + i); erased = true; }
+            }
+          }
+          if (!erased) ++i;
+        }
+        if (hasBody && !removed) throw std::runtime_error("removeObstacleFromJoint: the obstacle is not registered as obstacle for the joint");
+        break;
+      }
+      case HPPB200_OP_FILTER_COLLISION_PAIRS: {  // obstacle-user.cc:120-164, continuous-validation.cc:266-300
+        if (!op.data) throw std::invalid_argument("filterCollisionPairs: null relative-motion matrix");
+        const int32_t* M = (const int32_t*)op.data;
+        for (size_t i = 0; i < cPairs.size();) {
+          const int m = M[(size_t)jointOf(cPairs[i].a) * n1 + jointOf(cPairs[i].b)];
+          if (m == 1) { pPairs.push_back(cPairs[i]); cPairs.erase(cPairs.begin() + i); }
+          else if (m == 0) { dPairs.push_back(cPairs[i]); cPairs.erase(cPairs.begin() + i); }
+          else ++i;
+        }
+        for (size_t i = 0; i < bodyPairs.size();) {
+          const int m = M[(size_t)bodyPairs[i].joint_a * n1 + bodyPairs[i].joint_b];
+          if (m == 0 || m == 1) bodyPairs.erase(bodyPairs.begin() + i);  // "Parameterized collision pairs treated as Constrained"
+          else ++i;
+        }
+        break;
+      }
+      case HPPB200_OP_SET_SECURITY_MARGINS: {  // obstacle-user.cc:166-196, continuous-validation.cc:302-330
+        if (!op.data) throw std::invalid_argument("setSecurityMargins: null matrix");
+        const double* M = (const double*)op.data;
+        for (std::vector<DevPair>* tab : {&cPairs, &pPairs, &dPairs})
+          for (DevPair& p : *tab) p.margin = M[(size_t)jointOf(p.a) * n1 + jointOf(p.b)];
+        for (BodyPairHost& bp : bodyPairs)
+          for (DevPair& p : bp.pairs) p.margin = M[(size_t)bp.joint_a * n1 + bp.joint_b];
+        break;
+      }
+      case HPPB200_OP_SET_MARGIN_BETWEEN_BODIES: {  // obstacle-user.cc:198-220, continuous-validation.cc:332-367
+        auto matches = [&](const DevPair& p) { return (p.a == op.a && p.b == op.b) || (p.a == op.b && p.b == op.a); };
+        bool found = false;
+        for (std::vector<DevPair>* tab : {&cPairs, &pPairs, &dPairs}) {
+          for (DevPair& p : *tab)
+            if (matches(p)) { p.margin = op.value; found = true; break; }  // first match only
+          if (found) break;
+        }
+        for (BodyPairHost& bp : bodyPairs)  // every match; the reference never reports a miss here (found starts true)
+          for (DevPair& p : bp.pairs)
+            if (matches(p)) p.margin = op.value;
+        if (!found) throw std::invalid_argument("setSecurityMarginBetweenBodies: could not find a collision pair between the two bodies");
+        break;
+      }
+      default: throw std::invalid_argument("unknown pair op");
+    }
+  }
 }
 
 // cPairs_ order: active self pairs, then for every obstacle (call order) every moving joint
@@ -158,10 +264,12 @@ void Model::buildConfigPairs(const hppb200_model_desc& d) {
     if (a < 0 || b < 0 || a >= (int)geoms.size() || b >= (int)geoms.size()) throw std::invalid_argument("self pair index out of range");
     cPairs.push_back(DevPair{a, b, 0, 0, margin(geoms[a].joint, geoms[b].joint), 0.0});
   }
-  for (int o = 0; o < (int)obstacles.size(); ++o)
+  for (int o = 0; o < (int)obstacles.size(); ++o) {
+    if (d.obst_global && !d.obst_global[o]) continue;  // only paired through HPPB200_OP_ADD_OBSTACLE_TO_JOINT
     for (int j = 1; j <= njoints; ++j)
       for (int g = 0; g < (int)geoms.size(); ++g)
         if (geoms[g].joint == j) cPairs.push_back(DevPair{g, -(o + 1), 0, 0, margin(j, 0), 0.0});
+  }
 }
 
 void Model::buildBodyPairs(const hppb200_model_desc& d) {
@@ -241,6 +349,7 @@ void Model::buildBodyPairs(const hppb200_model_desc& d) {
   // obstacles: one body pair per (joint carrying a body, obstacle)
   for (int o = 0; o < (int)obstacles.size(); ++o)
     for (int j = 1; j <= njoints; ++j) {
+      if (d.obst_global && !d.obst_global[o]) continue;
       BodyPairHost bp;
       bp.joint_a = j;
       bp.joint_b = 0;

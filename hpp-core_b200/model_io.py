@@ -13,6 +13,15 @@ c_double_p = C.POINTER(C.c_double)
 c_int32_p = C.POINTER(C.c_int32)
 
 
+class hppb200_pair_op(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("a", C.c_int32), ("b", C.c_int32), ("flag", C.c_int32), ("value", C.c_double),
+                ("data", C.c_void_p)]
+
+
+OP_ADD_OBSTACLE_TO_JOINT, OP_REMOVE_OBSTACLE_FROM_JOINT, OP_FILTER_COLLISION_PAIRS, OP_SET_SECURITY_MARGINS, \
+    OP_SET_MARGIN_BETWEEN_BODIES = 1, 2, 3, 4, 5
+
+
 class hppb200_model_desc(C.Structure):
     _fields_ = [
         ("njoints", C.c_int32),
@@ -41,6 +50,10 @@ class hppb200_model_desc(C.Structure):
         ("security_margins", c_double_p),
         ("break_distance", C.c_double),
         ("weights", c_double_p),
+        ("obst_global", C.POINTER(C.c_uint8)),
+        ("npair_ops", C.c_int32),
+        ("pair_ops", C.POINTER(hppb200_pair_op)),
+        ("check_parameterized", C.c_int32),
     ]
 
 
@@ -91,6 +104,13 @@ class ModelDescription:
         self.weights = None if w is None else _f64(w)
         self.geom_names = d.get("geom_names")
         self.obst_names = d.get("obst_names")
+        # pair-table edits (ObstacleUserInterface call log): list of (kind, a, b, flag, value, data) with data a matrix
+        # ((njoints+1)^2 int32 for OP_FILTER_COLLISION_PAIRS, float64 for OP_SET_SECURITY_MARGINS) or None
+        og = d.get("obst_global")
+        self.obst_global = None if og is None else np.ascontiguousarray(np.asarray(og, dtype=np.uint8))
+        self.pair_ops = [tuple(op) for op in d.get("pair_ops", [])]
+        self.check_parameterized = bool(d.get("check_parameterized", False))
+        self._op_keep = []
 
     @classmethod
     def load(cls, path):
@@ -126,6 +146,24 @@ class ModelDescription:
         s.security_margins = dp(self.security_margins)
         s.break_distance = self.break_distance
         s.weights = dp(self.weights)
+        if self.obst_global is not None and self.obst_global.size:
+            s.obst_global = self.obst_global.ctypes.data_as(C.POINTER(C.c_uint8))
+        s.check_parameterized = 1 if self.check_parameterized else 0
+        if self.pair_ops:
+            n1 = self.njoints + 1
+            arr = (hppb200_pair_op * len(self.pair_ops))()
+            keep = []
+            for i, op in enumerate(self.pair_ops):
+                kind, a, b, flag, value, data = (list(op) + [0, 0, 0, 0.0, None])[:6]
+                arr[i].kind, arr[i].a, arr[i].b, arr[i].flag, arr[i].value = int(kind), int(a), int(b), int(flag), float(value)
+                if data is not None:
+                    m = np.ascontiguousarray(np.asarray(data, dtype=np.int32 if kind == OP_FILTER_COLLISION_PAIRS else np.float64)
+                                             ).reshape(n1, n1)
+                    keep.append(m)
+                    arr[i].data = m.ctypes.data
+            self._op_keep = [arr, keep]  # owned as long as the description
+            s.npair_ops = len(self.pair_ops)
+            s.pair_ops = C.cast(arr, C.POINTER(hppb200_pair_op))
         return s
 
 

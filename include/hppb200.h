@@ -52,7 +52,7 @@
 extern "C" {
 #endif
 
-#define HPPB200_ABI_VERSION 1
+#define HPPB200_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -146,7 +146,37 @@ typedef struct hppb200_model_desc {
                                      only affects BVH pairs in coal, kept for API
                                      fidelity */
   const double* weights;          /* [njoints] WeighedDistance::weights(); NULL = 1 */
+
+  /* ---- pair-table edits (ABI version 2; all zero = none) -------------------------------
+     obst_global[k] != 0 (or obst_global == NULL): obstacle k was passed to addObstacle()
+     (paired with every joint, reference src/obstacle-user.cc:53-58, continuous-validation.cc
+     :103-118); 0: the object only exists for HPPB200_OP_ADD_OBSTACLE_TO_JOINT.
+     pair_ops are applied in order AFTER the base tables (self pairs, global obstacles,
+     security_margins) are built; the adapter keeps the log of the calls it received through
+     ObstacleUserInterface and rebuilds the model when it changes. */
+  const uint8_t* obst_global;     /* [nobstacles] or NULL                           */
+  int32_t npair_ops;
+  const struct hppb200_pair_op* pair_ops;
+  int32_t check_parameterized;    /* CollisionValidation::checkParameterized_       */
 } hppb200_model_desc;
+
+/* One recorded call of the ObstacleUserInterface (reference include/hpp/core/obstacle-user.hh:47-88,
+   src/obstacle-user.cc:60-220, src/continuous-validation.cc:224-367).  Geometry references: >= 0 robot
+   geometry, -(k+1) obstacle k.  Joint indices are pinocchio's (1..njoints). */
+#define HPPB200_OP_ADD_OBSTACLE_TO_JOINT 1      /* a = obstacle k, b = joint, flag = includeChildren; configuration
+                                                   validation only (ContinuousValidation has no such call)        */
+#define HPPB200_OP_REMOVE_OBSTACLE_FROM_JOINT 2 /* a = obstacle k, b = joint; not registered => HPPB200_ERR_RUNTIME */
+#define HPPB200_OP_FILTER_COLLISION_PAIRS 3     /* data = int32 [(njoints+1)^2] row-major RelativeMotion matrix:
+                                                   0 Constrained (disabled), 1 Parameterized, 2 Unconstrained    */
+#define HPPB200_OP_SET_SECURITY_MARGINS 4       /* data = double [(njoints+1)^2] row-major                       */
+#define HPPB200_OP_SET_MARGIN_BETWEEN_BODIES 5  /* a, b = geometry references, value = margin; configuration table:
+                                                   first matching pair, none => HPPB200_ERR_INVALID_ARGUMENT;
+                                                   continuous table: every matching pair                         */
+typedef struct hppb200_pair_op {
+  int32_t kind, a, b, flag;
+  double value;
+  const void* data;
+} hppb200_pair_op;
 
 typedef struct hppb200_model hppb200_model;         /* immutable compiled tables   */
 typedef struct hppb200_workspace hppb200_workspace; /* one CUDA stream + scratch   */
@@ -183,6 +213,9 @@ int hppb200_model_nv(const hppb200_model* m);
 int hppb200_model_num_config_pairs(const hppb200_model* m);
 int hppb200_model_get_config_pairs(const hppb200_model* m, int32_t* geomA,
                                    int32_t* geomB, double* margin);
+/* How many trailing entries of that table are pPairs_ (parameterized pairs, tested after cPairs_ when
+   check_parameterized is set; reference src/collision-validation.cc:62-67); 0 otherwise. */
+int hppb200_model_num_parameterized_pairs(const hppb200_model* m);
 /* Continuous-validation body pairs in intervalValidations_ order. */
 int hppb200_model_num_body_pairs(const hppb200_model* m);
 /* joint_a/joint_b [nbp]; geom-pair range [pair_begin[i], pair_begin[i+1]) into

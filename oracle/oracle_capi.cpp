@@ -56,10 +56,10 @@ void oracle_difference(OracleHandle* h, const double* q1, const double* q2, size
 }
 
 // ---- tables -----------------------------------------------------------------
-int oracle_num_config_pairs(OracleHandle* h) { return (int)ObstacleUser(*h->dev).cPairs.size(); }
+int oracle_num_config_pairs(OracleHandle* h) { return (int)ObstacleUser(*h->dev).checkedPairs().size(); }
 void oracle_get_config_pairs(OracleHandle* h, int32_t* a, int32_t* b, double* margin) {
-  ObstacleUser ou(*h->dev);
-  for (size_t i = 0; i < ou.cPairs.size(); ++i) { a[i] = ou.cPairs[i].first; b[i] = ou.cPairs[i].second; margin[i] = ou.cPairs[i].margin; }
+  const std::vector<CollisionPair> cp = ObstacleUser(*h->dev).checkedPairs();
+  for (size_t i = 0; i < cp.size(); ++i) { a[i] = cp[i].first; b[i] = cp[i].second; margin[i] = cp[i].margin; }
 }
 int oracle_num_body_pairs(OracleHandle* h) { return (int)ContinuousValidation(*h->dev, 0).intervalValidations_.size(); }
 int oracle_num_body_geom_pairs(OracleHandle* h) { return (int)ContinuousValidation(*h->dev, 0).allGeomPairs.size(); }
@@ -106,12 +106,12 @@ void oracle_geometry_placements(OracleHandle* h, const double* q, size_t n, doub
 }
 void oracle_pair_distances(OracleHandle* h, const double* q, size_t n, double* dist) {
   const Device& d = *h->dev;
-  ObstacleUser ou(d);
+  const std::vector<CollisionPair> cp = ObstacleUser(d).checkedPairs();
   DeviceData data;
   for (size_t i = 0; i < n; ++i) {
     d.forwardKinematics(q + i * d.nq, data);
-    for (size_t p = 0; p < ou.cPairs.size(); ++p)
-      dist[i * ou.cPairs.size() + p] = collidePair(d, data, ou.cPairs[p], nullptr).distanceLowerBound;
+    for (size_t p = 0; p < cp.size(); ++p)
+      dist[i * cp.size() + p] = collidePair(d, data, cp[p], nullptr).distanceLowerBound;
   }
 }
 // distance between two shapes given as (type, params[4], placement[12]); convex verts optional

@@ -206,7 +206,7 @@ struct ContinuousValidation {
     // AddObstacle::doExecute :103-118 — one body pair per (joint with body, obstacle)
     for (size_t o = 0; o < d.obstacles.size(); ++o)
       for (int j = 1; j <= d.njoints(); ++j) {
-        if (!d.jointHasBody(j)) continue;
+        if (!d.isGlobal(o) || !d.jointHasBody(j)) continue;
         SolidSolidCollision ss;
         ss.dev = &d; ss.joint_a = j; ss.joint_b = 0; ss.tolerance = tol;
         for (size_t g = 0; g < d.geoms.size(); ++g)
@@ -214,9 +214,56 @@ struct ContinuousValidation {
         ss.setCoefficients(radii);
         intervalValidations_.push_back(ss);
       }
+    for (const PairOp& op : d.pairOps) apply(op);
     int id = 0;
     for (auto& ss : intervalValidations_)
       for (auto& p : ss.pairs) { ss.pairIds.push_back(id++); allGeomPairs.push_back(p); }
+  }
+
+  // ObstacleUserInterface calls on a ContinuousValidation (src/continuous-validation.cc:224-367)
+  void apply(const PairOp& op) {
+    const size_t n1 = dev->joints.size();
+    switch (op.kind) {
+      case HPPB200_OP_ADD_OBSTACLE_TO_JOINT: break;  // not part of the interface of a path validation
+      case HPPB200_OP_REMOVE_OBSTACLE_FROM_JOINT: {  // :224-252 + SolidSolidCollision::removeObjectTo_b (:101-122)
+        if (!dev->jointHasBody(op.b)) break;  // (the configuration validator only walks the inner objects of the body)
+        bool removed = false;
+        for (size_t i = 0; i < intervalValidations_.size();) {
+          SolidSolidCollision& bpc = intervalValidations_[i];
+          bool erased = false;
+          if (bpc.joint_a == op.b && bpc.joint_b == 0) {
+            std::vector<CollisionPair> kept;
+            for (auto& p : bpc.pairs)
+              if (p.second != -(op.a + 1)) kept.push_back(p);
+            if (kept.size() != bpc.pairs.size()) {
+              removed = true;
+              bpc.pairs = kept;
+              if (kept.empty()) { intervalValidations_.erase(intervalValidations_.begin() + i); erased = true; }
+            }
+          }
+          if (!erased) ++i;
+        }
+        if (!removed) throw std::runtime_error("ContinuousValidation::removeObstacleFromJoint: obstacle is not registered as obstacle for joint");
+        break;
+      }
+      case HPPB200_OP_FILTER_COLLISION_PAIRS:  // :266-300 (Parameterized treated as Constrained)
+        for (size_t i = 0; i < intervalValidations_.size();) {
+          const int m = op.relativeMotion[(size_t)intervalValidations_[i].joint_a * n1 + intervalValidations_[i].joint_b];
+          if (m == 0 || m == 1) intervalValidations_.erase(intervalValidations_.begin() + i);
+          else ++i;
+        }
+        break;
+      case HPPB200_OP_SET_SECURITY_MARGINS:  // :302-330
+        for (auto& bpc : intervalValidations_)
+          for (auto& p : bpc.pairs) p.margin = op.matrix[(size_t)bpc.joint_a * n1 + bpc.joint_b];
+        break;
+      case HPPB200_OP_SET_MARGIN_BETWEEN_BODIES:  // :332-367 (every matching pair; `found` starts true: never throws)
+        for (auto& bpc : intervalValidations_)
+          for (auto& p : bpc.pairs)
+            if ((p.first == op.a && p.second == op.b) || (p.first == op.b && p.second == op.a)) p.margin = op.value;
+        break;
+      default: throw std::invalid_argument("unknown pair op");
+    }
   }
 
   // include/hpp/core/continuous-validation.hh:267-298 + src/continuous-validation.cc:128-148

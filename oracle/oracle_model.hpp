@@ -36,7 +36,19 @@ struct DeviceData {
 inline int jointNq(int type) { return type == HPPB200_JOINT_FREEFLYER ? 7 : 1; }
 inline int jointNv(int type) { return type == HPPB200_JOINT_FREEFLYER ? 6 : 1; }
 
+// One recorded ObstacleUserInterface call (include/hpp/core/obstacle-user.hh:47-88), see hppb200_pair_op
+struct PairOp {
+  int kind = 0, a = 0, b = 0, flag = 0;
+  double value = 0;
+  std::vector<int> relativeMotion;  // (njoints+1)^2, RelativeMotion::matrix_type
+  std::vector<double> matrix;       // (njoints+1)^2 security margins
+};
+
 struct Device {
+  std::vector<PairOp> pairOps;
+  std::vector<unsigned char> obstGlobal;  // empty: every obstacle went through addObstacle()
+  bool checkParameterized = false;
+  bool isGlobal(size_t o) const { return obstGlobal.empty() || obstGlobal[o] != 0; }
   std::vector<Joint> joints;  // index 0 = universe placeholder
   std::vector<Geometry> geoms;
   std::vector<Geometry> obstacles;
@@ -101,6 +113,17 @@ struct Device {
     weights.assign(d.njoints, 1.0);
     if (d.weights) weights.assign(d.weights, d.weights + d.njoints);
     breakDistance = d.break_distance;
+    if (d.obst_global) obstGlobal.assign(d.obst_global, d.obst_global + d.nobstacles);
+    checkParameterized = d.check_parameterized != 0;
+    const size_t nn = (size_t)(d.njoints + 1) * (size_t)(d.njoints + 1);
+    for (int k = 0; k < d.npair_ops; ++k) {
+      const hppb200_pair_op& o = d.pair_ops[k];
+      PairOp op;
+      op.kind = o.kind; op.a = o.a; op.b = o.b; op.flag = o.flag; op.value = o.value;
+      if (o.kind == HPPB200_OP_FILTER_COLLISION_PAIRS && o.data) op.relativeMotion.assign((const int32_t*)o.data, (const int32_t*)o.data + nn);
+      if (o.kind == HPPB200_OP_SET_SECURITY_MARGINS && o.data) op.matrix.assign((const double*)o.data, (const double*)o.data + nn);
+      pairOps.push_back(op);
+    }
   }
 
   // pinocchio joint transform M_joint(q)

@@ -44,16 +44,66 @@ struct ObstacleUser {
   const Device* dev;
   std::vector<CollisionPair> cPairs;
 
+  std::vector<CollisionPair> pPairs, dPairs;  // parameterized / disabled (filterCollisionPairs)
+
   explicit ObstacleUser(const Device& d) : dev(&d) {
     for (auto& sp : d.selfPairs) cPairs.push_back({sp.first, sp.second, 0.0});  // addRobotCollisionPairs
-    for (size_t o = 0; o < d.obstacles.size(); ++o) addObstacle((int)o);
+    for (size_t o = 0; o < d.obstacles.size(); ++o)
+      if (d.isGlobal(o)) addObstacle((int)o);
     setSecurityMargins();
+    for (const PairOp& op : d.pairOps) apply(op);
   }
   void addObstacle(int o) {
     // robot_->nbJoints()/jointAt(j): moving joints only, model joint j+1 (Appendix A.3)
-    for (int j = 1; j <= dev->njoints(); ++j)
-      for (size_t g = 0; g < dev->geoms.size(); ++g)
-        if (dev->geoms[g].joint == j) cPairs.push_back({(int)g, -(o + 1), 0.0});
+    for (int j = 1; j <= dev->njoints(); ++j) addObstacleToJoint(o, j, false);
+  }
+  // src/obstacle-user.cc:60-76
+  void addObstacleToJoint(int o, int joint, bool includeChildren) {
+    for (size_t g = 0; g < dev->geoms.size(); ++g)
+      if (dev->geoms[g].joint == joint) cPairs.push_back({(int)g, -(o + 1), 0.0});
+    if (includeChildren)
+      for (int c = 1; c <= dev->njoints(); ++c)
+        if (dev->joints[c].parent == joint) addObstacleToJoint(o, c, includeChildren);
+  }
+  int jointOf(int ref) const { return ref >= 0 ? dev->geoms[ref].joint : 0; }
+  void apply(const PairOp& op) {
+    const size_t n1 = dev->joints.size();
+    switch (op.kind) {
+      case HPPB200_OP_ADD_OBSTACLE_TO_JOINT: addObstacleToJoint(op.a, op.b, op.flag != 0); break;
+      case HPPB200_OP_REMOVE_OBSTACLE_FROM_JOINT:  // :87-118
+        for (size_t g = 0; g < dev->geoms.size(); ++g) {
+          if (dev->geoms[g].joint != op.b) continue;
+          size_t nbDelPairs = 0;
+          for (size_t i = 0; i < cPairs.size();) {
+            if (cPairs[i].first == (int)g && cPairs[i].second == -(op.a + 1)) { cPairs.erase(cPairs.begin() + i); ++nbDelPairs; }
+            else ++i;
+          }
+          if (nbDelPairs == 0) throw std::runtime_error("ObstacleUser::removeObstacleFromJoint: obstacle is not registered as obstacle for joint");
+        }
+        break;
+      case HPPB200_OP_FILTER_COLLISION_PAIRS:  // :120-164
+        for (size_t i = 0; i < cPairs.size();) {
+          const int m = op.relativeMotion[(size_t)jointOf(cPairs[i].first) * n1 + jointOf(cPairs[i].second)];
+          if (m == 1) { pPairs.push_back(cPairs[i]); cPairs.erase(cPairs.begin() + i); }        // Parameterized
+          else if (m == 0) { dPairs.push_back(cPairs[i]); cPairs.erase(cPairs.begin() + i); }   // Constrained
+          else ++i;
+        }
+        break;
+      case HPPB200_OP_SET_SECURITY_MARGINS:  // :166-196
+        for (auto* tab : {&cPairs, &pPairs, &dPairs})
+          for (auto& p : *tab) p.margin = op.matrix[(size_t)jointOf(p.first) * n1 + jointOf(p.second)];
+        break;
+      case HPPB200_OP_SET_MARGIN_BETWEEN_BODIES: {  // :198-220
+        auto setMargin = [&](std::vector<CollisionPair>& pairs) {
+          for (auto& p : pairs)
+            if ((p.first == op.a && p.second == op.b) || (p.first == op.b && p.second == op.a)) { p.margin = op.value; return true; }
+          return false;
+        };
+        if (setMargin(cPairs) || setMargin(pPairs) || setMargin(dPairs)) break;
+        throw std::invalid_argument("Could not find a collision pair between the two bodies");
+      }
+      default: throw std::invalid_argument("unknown pair op");
+    }
   }
   void setSecurityMargins() {
     for (auto& p : cPairs) {
@@ -63,9 +113,15 @@ struct ObstacleUser {
     }
   }
   // src/obstacle-user.cc:42-51 — sequential loop, stop at first hit.
-  bool collide(const DeviceData& data, size_t& i, GjkStats* st) const {
-    for (i = 0; i < cPairs.size(); ++i)
-      if (collidePair(*dev, data, cPairs[i], st).collision) return true;
+  // the pairs CollisionValidation::validate walks, in order (what the engine's table holds)
+  std::vector<CollisionPair> checkedPairs() const {
+    std::vector<CollisionPair> v(cPairs);
+    if (dev->checkParameterized) v.insert(v.end(), pPairs.begin(), pPairs.end());
+    return v;
+  }
+  bool collide(const std::vector<CollisionPair>& pairs, const DeviceData& data, size_t& i, GjkStats* st) const {
+    for (i = 0; i < pairs.size(); ++i)
+      if (collidePair(*dev, data, pairs[i], st).collision) return true;
     return false;
   }
 };
@@ -82,9 +138,15 @@ struct CollisionValidation : ObstacleUser {
     DeviceData data;
     dev->forwardKinematics(q, data);
     size_t i = 0;
-    if (collide(data, i, st)) {
+    bool hit = collide(cPairs, data, i, st);
+    size_t base = 0;
+    if (!hit && dev->checkParameterized) {  // :62-67
+      hit = collide(pPairs, data, i, st);
+      base = cPairs.size();  // reported as an index into cPairs ++ pPairs (the table the ABI exposes)
+    }
+    if (hit) {
       rep.reason = HPPB200_REASON_COLLISION;
-      rep.index = (int)i;
+      rep.index = (int)(base + i);
       return false;
     }
     rep = ConfigReport();

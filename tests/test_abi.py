@@ -19,7 +19,7 @@ def test_library_exports_header_symbols(pkg):
     L = pkg.lib()
     for s in declared:
         assert hasattr(L, s), s
-    assert L.hppb200_abi_version() == 1
+    assert L.hppb200_abi_version() == 2
 
 
 def test_struct_layout_matches_header(pkg):
@@ -59,6 +59,76 @@ def test_security_margins_and_errors(pkg, ob):
     bad.joint_parent[2] = 5  # parent after child
     with pytest.raises(ValueError):
         pkg.Model(bad)
+
+
+def pair_op_model(pkg, name="ur5_boxes8.json"):
+    """A model whose validators received every ObstacleUserInterface call after construction (include/hpp/core/
+    obstacle-user.hh:47-88): obstacle 7 only attached to joint 2 and its children, obstacle 0 removed from joint 3,
+    a relative-motion filter (joints 1-2 constrained, 4-6 parameterized), a margin matrix, one margin between two bodies."""
+    from hpp_core_b200 import model_io as mio
+    desc = pkg.ModelDescription.load(name)
+    nj = desc.njoints
+    og = np.ones(desc.nobstacles, np.uint8)
+    og[7] = 0
+    desc.obst_global = og
+    rel = np.full((nj + 1, nj + 1), 2, np.int32)
+    np.fill_diagonal(rel, 0)
+    rel[1, 2] = rel[2, 1] = 0
+    rel[4, 6] = rel[6, 4] = 1
+    rel[5, 0] = rel[0, 5] = 0   # joint 5 rigidly fixed to the environment: its obstacle pairs go away
+    mar = (np.arange((nj + 1) ** 2, dtype=np.float64).reshape(nj + 1, nj + 1) % 5) * 2e-3
+    mar = np.minimum(mar, mar.T)
+    geom_j3 = int(np.nonzero(desc.geom_joint == 3)[0][0])
+    desc.pair_ops = [(mio.OP_ADD_OBSTACLE_TO_JOINT, 7, 2, 1, 0.0, None),
+                     (mio.OP_REMOVE_OBSTACLE_FROM_JOINT, 0, 3, 0, 0.0, None),
+                     (mio.OP_SET_SECURITY_MARGINS, 0, 0, 0, 0.0, mar),
+                     (mio.OP_FILTER_COLLISION_PAIRS, 0, 0, 0, 0.0, rel),
+                     (mio.OP_SET_MARGIN_BETWEEN_BODIES, geom_j3, -2, 0, 0.0123, None)]
+    return desc
+
+
+@pytest.mark.parametrize("check_parameterized", [False, True])
+def test_pair_table_edits_match_oracle(pkg, ob, check_parameterized):
+    """addObstacleToJoint / removeObstacleFromJoint / filterCollisionPairs / setSecurityMargins /
+    setSecurityMarginBetweenBodies (reference src/obstacle-user.cc:60-220, src/continuous-validation.cc:224-367):
+    the engine's model compiler and the oracle apply the same call log to both pair tables."""
+    desc = pair_op_model(pkg)
+    desc.check_parameterized = check_parameterized
+    base = pkg.Model(pkg.ModelDescription.load("ur5_boxes8.json"))
+    m, o = pkg.Model(desc), ob.Oracle(desc)
+    a, b, mg = m.config_pairs()
+    for x, y in zip((a, b, mg), o.config_pairs()):
+        assert np.array_equal(x, y)
+    assert len(a) != len(base.config_pairs()[0])
+    npar = pkg.lib().hppb200_model_num_parameterized_pairs(m.h)
+    assert (npar > 0) == check_parameterized
+    gj = desc.geom_joint
+    jb = np.where(b >= 0, gj[np.maximum(b, 0)], 0)
+    # obstacle 7 only on joints >= 2; obstacle 0 not on joint 3; constrained joint pairs gone; one edited margin
+    assert not np.any((b == -8) & (gj[a] < 2)) and np.any(b == -8)
+    assert not np.any((b == -1) & (gj[a] == 3))
+    assert not np.any((gj[a] == 5) & (jb == 0))
+    assert 0.0123 in mg
+    bm, bo = m.body_pairs(), o.body_pairs()
+    for k in bm:
+        assert np.array_equal(bm[k], bo[k]), k
+    assert not np.any((bm["joint_a"] == 5) & (bm["joint_b"] == 0))
+    assert not np.any(bm["geomB"] == -8)  # ContinuousValidation has no addObstacleToJoint
+    assert 0.0123 in bm["margin"]
+
+
+def test_pair_table_edit_errors(pkg, ob):
+    from hpp_core_b200 import model_io as mio
+    desc = pkg.ModelDescription.load("ur5_boxes8.json")
+    desc.pair_ops = [(mio.OP_REMOVE_OBSTACLE_FROM_JOINT, 0, 3, 0, 0.0, None)] * 2  # second removal: not registered any more
+    with pytest.raises(pkg.EngineError):  # std::runtime_error in the reference (obstacle-user.cc:104-110)
+        pkg.Model(desc)
+    desc.pair_ops = [(mio.OP_SET_MARGIN_BETWEEN_BODIES, 0, 0, 0, 0.1, None)]  # no such pair: std::invalid_argument (:216-219)
+    with pytest.raises(ValueError):
+        pkg.Model(desc)
+    desc.pair_ops = [(99, 0, 0, 0, 0.0, None)]
+    with pytest.raises(ValueError):
+        pkg.Model(desc)
 
 
 def test_no_cpu_fallback(pkg):

@@ -681,3 +681,31 @@ def test_birrt_end_to_end_same_roadmap(pkg, ob, name, method, param, batch):
         assert path[0] == gpu.init and path[-1] == gpu.goal and path == cpu.path()
         a, b = gpu.roadmap.nodes[path[:-1]], gpu.roadmap.nodes[path[1:]]
         assert o.validate_edges(0, 0.05, a, b, o.straight_lengths(a, b))["valid"].all()
+
+
+@pytest.mark.parametrize("check_parameterized", [False, True])
+def test_pair_table_edits_gpu_parity(pkg, ob, monkeypatch, check_parameterized):
+    """A model edited through the ObstacleUserInterface call log (tests/test_abi.py::pair_op_model): configuration
+    validation (flags, first pair in the edited table, distances) and the three path validations agree with the oracle."""
+    from test_abi import pair_op_model
+    desc = pair_op_model(pkg)
+    desc.check_parameterized = check_parameterized
+    o = ob.Oracle(desc)
+    m = pkg.Model(desc)
+    ws = pkg.Workspace(m, 0)
+    q = pkg.uniform_configs(desc, 30000, seed=91)
+    for a, b in zip(ws.validate_configs(q), o.validate_configs(q)):
+        assert np.array_equal(a, b)
+    assert np.array_equal(ws.pair_distances(q[:500]), o.pair_distances(q[:500]))
+    base = pkg.Workspace(pkg.Model(pkg.ModelDescription.load("ur5_boxes8.json")), 0)
+    assert not np.array_equal(base.validate_configs(q)[0], ws.validate_configs(q)[0])  # the edits change flags
+    q1, q2, L = _edges(pkg, desc, o, 3000, 92)
+    for wf in ("100000000", "1"):
+        monkeypatch.setenv("HPPB200_WF_MIN", wf)
+        w2 = pkg.Workspace(m, 0)
+        for meth, par in ((0, 0.05), (1, 1e-3), (2, 0.0)):
+            r = w2.validate_edges(meth, par, q1, q2, L)
+            e = o.validate_edges(meth, par, q1, q2, L)
+            for k in ("valid", "reason", "pair", "t_last_valid"):
+                assert np.array_equal(r[k], e[k]), (wf, meth, k)
+            assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
