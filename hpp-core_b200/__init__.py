@@ -50,7 +50,7 @@ ABI_SYMBOLS = [
     "hppb200_model_num_coefficients", "hppb200_model_get_coefficients", "hppb200_model_get_body_radii",
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
     "hppb200_validate_configs", "hppb200_geometry_placements", "hppb200_pair_distances",
-    "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_workspace_set_max_iterations",
+    "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edge_chains", "hppb200_workspace_set_max_iterations",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_set_labels", "hppb200_knn_size",
     "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_tc_debug_tile",
 ]
@@ -249,6 +249,23 @@ class Workspace:
                                 valid.ctypes.data, t_fail.ctypes.data, t_last.ctypes.data, pair.ctypes.data,
                                 reason.ctypes.data, CHECK_JOINT_BOUNDS if check_bounds else 0)
         return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason)
+
+
+    def validate_edge_chains(self, method, param, q1, q2, L, chain_begin, reverse=False):
+        """PathVectors of StraightPaths (ContinuousValidation::validate recursion, src/continuous-validation.cc:153-192)."""
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.model.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.model.nq)
+        L = np.ascontiguousarray(L, np.float64)
+        cb = np.ascontiguousarray(chain_begin, np.int32)
+        nc = cb.shape[0] - 1
+        valid, reason = np.zeros(nc, np.uint8), np.zeros(nc, np.uint8)
+        t_fail, t_last = np.zeros(nc), np.zeros(nc)
+        pair, bad = np.full(nc, -1, np.int32), np.full(nc, -1, np.int32)
+        _check(lib().hppb200_validate_edge_chains(self.h, C.c_int(method), C.c_double(param), C.c_int(1 if reverse else 0),
+                                                  _p(q1, _dp), _p(q2, _dp), _p(L, _dp), C.c_size_t(q1.shape[0]), _p(cb, _ip),
+                                                  C.c_size_t(nc), C.c_uint32(0), _p(valid, _u8p), _p(t_fail, _dp), _p(t_last, _dp),
+                                                  _p(pair, _ip), _p(reason, _u8p), _p(bad, _ip)))
+        return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, first_bad_edge=bad)
 
 
 class NearestNeighbor:

@@ -357,4 +357,54 @@ int hppb200_validate_edges(hppb200_workspace* wsp, int method, double param, int
   });
 }
 
+int hppb200_validate_edge_chains(hppb200_workspace* wsp, int method, double param, int reverse, const double* q1, const double* q2,
+                                 const double* L, size_t n_edges, const int32_t* chain_begin, size_t n_chains, uint32_t flags,
+                                 uint8_t* valid, double* t_fail, double* t_last_valid, int32_t* pair, uint8_t* reason,
+                                 int32_t* first_bad_edge) {
+  return guarded([&] {
+    if (!wsp || (n_chains && (!chain_begin || !valid)) || (n_edges && (!q1 || !q2 || !L))) throw std::invalid_argument("null argument");
+    if (method == HPPB200_METHOD_DISCRETIZED)  // Discretized walks a PathVector as ONE path (discretized.cc:55-107): no recursion to replay
+      throw std::runtime_error("edge chains replay the PathVector recursion of the continuous validations only");
+    if (method == HPPB200_METHOD_PROGRESSIVE && !(param > 0))
+      throw std::runtime_error("tolerance should be positive for progressive continuous validation.");
+    if (method == HPPB200_METHOD_DICHOTOMY && param != 0) throw std::runtime_error("Dichotomy path validation method does not support penetration.");
+    if (method != HPPB200_METHOD_PROGRESSIVE && method != HPPB200_METHOD_DICHOTOMY) throw std::invalid_argument("unknown method");
+    if (n_edges > 0x7fffffffull) throw std::invalid_argument("at most 2^31-1 edges per call");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq, n = n_edges;
+    const bool dev = (flags & HPPB200_DEVICE_POINTERS) != 0;
+    ws->d_valid.reserve(n); ws->d_reason.reserve(n); ws->d_pair.reserve(n); ws->d_tfail.reserve(n); ws->d_tlast.reserve(n);
+    Timed tm(ws);
+    const double *dq1 = q1, *dq2 = q2, *dL = L;
+    const int32_t* dcb = chain_begin;
+    if (!dev) {
+      ws->d_q.reserve(n * nq); ws->d_q2.reserve(n * nq); ws->d_L.reserve(n); ws->d_chain.reserve(n_chains + 1);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q1, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q2.p, q2, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_L.p, L, n * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_chain.p, chain_begin, (n_chains + 1) * sizeof(int32_t), cudaMemcpyHostToDevice, ws->stream));
+      dq1 = ws->d_q.p; dq2 = ws->d_q2.p; dL = ws->d_L.p; dcb = ws->d_chain.p;
+    }
+    if (n) launchValidateEdges(ws, method, param, reverse, dq1, dq2, dL, n, flags, ws->d_valid.p, ws->d_tfail.p, ws->d_tlast.p, ws->d_pair.p,
+                               ws->d_reason.p);
+    if (dev) {
+      launchChainReduce(ws, dcb, n_chains, reverse, dL, ws->d_valid.p, ws->d_tfail.p, ws->d_tlast.p, ws->d_pair.p, ws->d_reason.p, valid, t_fail,
+                        t_last_valid, pair, reason, first_bad_edge);
+    } else {
+      ws->d_cvalid.reserve(n_chains); ws->d_creason.reserve(n_chains); ws->d_cpair.reserve(n_chains); ws->d_cbad.reserve(n_chains);
+      ws->d_ctfail.reserve(n_chains); ws->d_ctlast.reserve(n_chains);
+      launchChainReduce(ws, dcb, n_chains, reverse, dL, ws->d_valid.p, ws->d_tfail.p, ws->d_tlast.p, ws->d_pair.p, ws->d_reason.p, ws->d_cvalid.p,
+                        ws->d_ctfail.p, ws->d_ctlast.p, ws->d_cpair.p, ws->d_creason.p, ws->d_cbad.p);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_cvalid.p, n_chains, cudaMemcpyDeviceToHost, ws->stream));
+      if (t_fail) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_fail, ws->d_ctfail.p, n_chains * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+      if (t_last_valid) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_last_valid, ws->d_ctlast.p, n_chains * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+      if (pair) HPPB200_CUDA_CHECK(cudaMemcpyAsync(pair, ws->d_cpair.p, n_chains * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+      if (reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(reason, ws->d_creason.p, n_chains, cudaMemcpyDeviceToHost, ws->stream));
+      if (first_bad_edge) HPPB200_CUDA_CHECK(cudaMemcpyAsync(first_bad_edge, ws->d_cbad.p, n_chains * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    }
+    tm.stop();
+  });
+}
+
 }  // extern "C"

@@ -160,7 +160,9 @@ struct Workspace {
   DeviceBuffer<uint16_t> d_sv_order;
   DeviceBuffer<uint8_t> d_sv_flags;
   DeviceBuffer<unsigned long long> d_count;
-  DeviceBuffer<int32_t> d_pair, d_pair_int;
+  DeviceBuffer<int32_t> d_pair, d_pair_int, d_chain, d_cpair, d_cbad;
+  DeviceBuffer<uint8_t> d_cvalid, d_creason;
+  DeviceBuffer<double> d_ctfail, d_ctlast;
   DeviceBuffer<unsigned long long> d_jobs;
   unsigned long long last_jobs = 0;
   DeviceBuffer<unsigned char> d_state, d_tail, d_sort;
@@ -208,6 +210,9 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
 bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
                          const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
                          uint8_t* d_reason, int overflow_reason, bool smemLists);
+void launchChainReduce(Workspace* ws, const int32_t* d_chainBegin, size_t nChains, int reverse, const double* d_L, const uint8_t* eValid,
+                       const double* eTfail, const double* eTlast, const int32_t* ePair, const uint8_t* eReason, uint8_t* valid,
+                       double* tFail, double* tLast, int32_t* pair, uint8_t* reason, int32_t* firstBad);
 void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1,
                          const double* d_q2, const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid,
                          double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason);

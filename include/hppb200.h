@@ -286,6 +286,19 @@ int hppb200_validate_edges(hppb200_workspace* ws, int method, double param,
                            const double* L, size_t n, uint32_t flags,
                            uint8_t* valid, double* t_fail, double* t_last_valid,
                            int32_t* pair, uint8_t* reason);
+/* A PathVector of StraightPaths per chain (what RandomShortcut and the other optimisers hand to the path validation):
+   chain c = edges [chain_begin[c], chain_begin[c+1]) in path order; chain_begin has n_chains + 1 entries.  Replays the
+   recursion of ContinuousValidation::validate (reference src/continuous-validation.cc:153-192) for Progressive and
+   Dichotomy: all leaves are validated as one batch, then per chain the first invalid leaf in walking order (last to
+   first when reverse) decides.  Outputs per chain, in the PathVector's own parameterisation: valid; t_fail =
+   report->parameter (NaN when valid); t_last_valid = end of the valid part (forward: validPart = extract(0,
+   t_last_valid); reverse: start of the valid part); pair, reason of the failing leaf; first_bad_edge = its edge index
+   (-1 when valid).  Discretized treats a PathVector as one path: HPPB200_ERR_RUNTIME. */
+int hppb200_validate_edge_chains(hppb200_workspace* ws, int method, double param, int reverse,
+                                 const double* q1, const double* q2, const double* L, size_t n_edges,
+                                 const int32_t* chain_begin, size_t n_chains, uint32_t flags,
+                                 uint8_t* valid, double* t_fail, double* t_last_valid, int32_t* pair,
+                                 uint8_t* reason, int32_t* first_bad_edge);
 /* Iteration cap per edge for continuous methods (default 1<<20). */
 int hppb200_workspace_set_max_iterations(hppb200_workspace* ws, uint32_t max_iter);
 

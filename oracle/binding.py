@@ -163,6 +163,23 @@ class Oracle:
             raise RuntimeError(lib().oracle_last_error().decode())
         return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, samples=samples)
 
+    def validate_edge_chains(self, method, param, q1, q2, L, chain_begin, reverse=False, nthreads=0):
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.nq)
+        L = np.ascontiguousarray(L, np.float64)
+        cb = np.ascontiguousarray(chain_begin, np.int32)
+        nc = cb.shape[0] - 1
+        valid, reason = np.zeros(nc, np.uint8), np.zeros(nc, np.uint8)
+        t_fail, t_last = np.zeros(nc), np.zeros(nc)
+        pair, bad = np.zeros(nc, np.int32), np.zeros(nc, np.int32)
+        rc = lib().oracle_validate_edge_chains(self.h, C.c_int(method), C.c_double(param), C.c_int(1 if reverse else 0),
+                                               _p(q1, dp), _p(q2, dp), _p(L, dp), _p(cb, ip), C.c_size_t(nc), _p(valid, u8p),
+                                               _p(t_fail, dp), _p(t_last, dp), _p(pair, ip), _p(reason, u8p), _p(bad, ip),
+                                               C.c_int(nthreads))
+        if rc != 0:
+            raise RuntimeError(lib().oracle_last_error().decode())
+        return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, first_bad_edge=bad)
+
     def counters(self):
         c = np.zeros(5, np.uint64)
         lib().oracle_get_counters(self.h, _p(c, u64p))

@@ -196,6 +196,67 @@ int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse
   return err;
 }
 
+// ContinuousValidation::validate on a PathVector of StraightPaths (src/continuous-validation.cc:153-192), restated as the
+// reference runs it: sub-path after sub-path, stop at the first invalid one, offset its report by the accumulated `param`.
+// t_last_valid = end (reverse: start) of the valid part in the PathVector's parameterisation.
+int oracle_validate_edge_chains(OracleHandle* h, int method, double param, int reverse, const double* q1, const double* q2,
+                                const double* L, const int32_t* chain_begin, size_t n_chains, uint8_t* valid, double* t_fail,
+                                double* t_last_valid, int32_t* pair, uint8_t* reason, int32_t* first_bad, int nthreads) {
+  const Device& d = *h->dev;
+  if (nthreads <= 0) nthreads = omp_get_max_threads();
+  int err = 0;
+#pragma omp parallel num_threads(nthreads)
+  {
+    try {
+      std::unique_ptr<Progressive> prog;
+      std::unique_ptr<Dichotomy> dich;
+      if (method == HPPB200_METHOD_PROGRESSIVE) prog.reset(new Progressive(d, param));
+      else if (method == HPPB200_METHOD_DICHOTOMY) dich.reset(new Dichotomy(d, param));
+      else throw std::runtime_error("PathVector recursion: continuous validations only");
+      auto validateLeaf = [&](long i) {
+        StraightPath path(d, q1 + (size_t)i * d.nq, q2 + (size_t)i * d.nq, L[i]);
+        return prog ? prog->validate(path, reverse != 0) : dich->validate(path, reverse != 0);
+      };
+#pragma omp for schedule(dynamic, 4)
+      for (long c = 0; c < (long)n_chains; ++c) {
+        const long b = chain_begin[c], e = chain_begin[c + 1];
+        bool ok = true;
+        double tf = std::nan(""), tl = 0;
+        int pr = -1, rs = HPPB200_REASON_VALID;
+        long bad = -1;
+        if (!reverse) {
+          double prm = 0;  // :180
+          for (long i = b; i < e; ++i) {
+            PathReport R = validateLeaf(i);
+            if (R.valid) prm += L[i];  // localPath->length()
+            else { ok = false; tf = R.parameter + prm; tl = prm + R.lastValid; pr = R.index; rs = R.reason; bad = i; break; }
+          }
+          if (ok) tl = prm;
+        } else {
+          double prm = 0;  // path->length(): the PathVector's time range grows by each appended length
+          for (long i = b; i < e; ++i) prm += L[i];
+          for (long i = e; i != b; --i) {
+            PathReport R = validateLeaf(i - 1);
+            if (R.valid) prm -= L[i - 1];
+            else { ok = false; tf = R.parameter + (prm - L[i - 1]); tl = (prm - L[i - 1]) + R.lastValid; pr = R.index; rs = R.reason; bad = i - 1; break; }
+          }
+          if (ok) tl = 0;
+        }
+        valid[c] = ok ? 1 : 0;
+        if (t_fail) t_fail[c] = tf;
+        if (t_last_valid) t_last_valid[c] = tl;
+        if (pair) pair[c] = pr;
+        if (reason) reason[c] = (uint8_t)rs;
+        if (first_bad) first_bad[c] = (int32_t)bad;
+      }
+    } catch (std::exception& e) {
+#pragma omp critical
+      { g_err = e.what(); err = 2; }
+    }
+  }
+  return err;
+}
+
 void oracle_get_counters(OracleHandle* h, uint64_t* out5) {
   out5[0] = h->stats.calls; out5[1] = h->stats.iterations; out5[2] = h->pairEvals; out5[3] = h->samples; out5[4] = h->stats.closed;
 }

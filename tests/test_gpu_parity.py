@@ -709,3 +709,39 @@ def test_pair_table_edits_gpu_parity(pkg, ob, monkeypatch, check_parameterized):
             for k in ("valid", "reason", "pair", "t_last_valid"):
                 assert np.array_equal(r[k], e[k]), (wf, meth, k)
             assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+
+
+@pytest.mark.parametrize("method,param", [(1, 1e-3), (2, 0.0)])
+@pytest.mark.parametrize("reverse", [False, True])
+def test_edge_chains_pathvector_recursion(pkg, eng, ur5, ur5_oracle, method, param, reverse):
+    """PathVectors of straight segments (what RandomShortcut hands to pathValidation()->validate): the engine validates
+    all leaves as one batch and cuts each chain at its first failing leaf on the device; the oracle walks the
+    sub-paths one by one like ContinuousValidation::validate (src/continuous-validation.cc:153-192)."""
+    m, ws = eng
+    rng = np.random.default_rng(17)
+    way = pkg.uniform_configs(ur5, 4000, seed=71)
+    # chains through consecutive way points, short steps so that many chains are valid for several leaves
+    lens = rng.integers(0, 7, size=600)  # includes empty PathVectors
+    q1, q2, cb = [], [], [0]
+    k = 0
+    for n in lens:
+        a = way[k]
+        for j in range(n):
+            d = way[k + j + 1] - a
+            b = np.clip(a + 0.4 * d / np.linalg.norm(d), -np.pi, np.pi)
+            q1.append(a); q2.append(b)
+            a = b
+        k += n + 1
+        cb.append(len(q1))
+    q1, q2 = np.array(q1), np.array(q2)
+    L = ur5_oracle.straight_lengths(q1, q2)
+    r = ws.validate_edge_chains(method, param, q1, q2, L, cb, reverse=reverse)
+    e = ur5_oracle.validate_edge_chains(method, param, q1, q2, L, cb, reverse=reverse)
+    for key in ("valid", "reason", "pair", "first_bad_edge", "t_last_valid"):
+        assert np.array_equal(r[key], e[key]), key
+    assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+    assert 0.05 < r["valid"].mean() < 0.95 and (r["first_bad_edge"] > np.array(cb[:-1])).any()  # failures beyond the first leaf
+    empty = np.nonzero(lens == 0)[0]
+    assert r["valid"][empty].all() and (r["t_last_valid"][empty] == 0).all()
+    with pytest.raises(pkg.EngineError):
+        ws.validate_edge_chains(0, 0.05, q1, q2, L, cb)
