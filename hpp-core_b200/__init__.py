@@ -49,7 +49,7 @@ ABI_SYMBOLS = [
     "hppb200_model_get_body_pairs", "hppb200_model_num_body_geom_pairs", "hppb200_model_get_body_geom_pairs",
     "hppb200_model_num_coefficients", "hppb200_model_get_coefficients", "hppb200_model_get_body_radii",
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
-    "hppb200_validate_configs", "hppb200_geometry_placements", "hppb200_pair_distances",
+    "hppb200_validate_configs", "hppb200_validate_configs_noalloc", "hppb200_geometry_placements", "hppb200_pair_distances",
     "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edge_chains", "hppb200_workspace_set_max_iterations",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_set_labels", "hppb200_knn_size",
     "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_tc_debug_tile",
@@ -188,6 +188,12 @@ class Workspace:
         _check(lib().hppb200_validate_configs(self.h, C.c_void_p(q_ptr), C.c_size_t(n), C.c_uint32(flags),
                                               C.c_void_p(valid_ptr), C.c_void_p(first_ptr or None),
                                               C.c_void_p(reason_ptr or None)))
+
+    def validate_configs_noalloc_ptr(self, q_ptr, n, valid_ptr, first_ptr, reason_ptr, flags=DEVICE_POINTERS):
+        """hppb200_validate_configs_noalloc: device pointers only, scratch in the library's static device array."""
+        _check(lib().hppb200_validate_configs_noalloc(self.h, C.c_void_p(q_ptr), C.c_size_t(n), C.c_uint32(flags),
+                                                      C.c_void_p(valid_ptr or None), C.c_void_p(first_ptr or None),
+                                                      C.c_void_p(reason_ptr or None)))
 
     def validate_edges_ptr(self, method, param, reverse, q1_ptr, q2_ptr, L_ptr, n, valid_ptr, tfail_ptr=0,
                            tlast_ptr=0, pair_ptr=0, reason_ptr=0, flags=0):

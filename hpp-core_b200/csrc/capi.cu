@@ -193,6 +193,7 @@ int hppb200_workspace_create(const hppb200_model* m, int device, hppb200_workspa
   return guarded([&] {
     if (!m || !out) throw std::invalid_argument("null argument");
     *out = new hppb200_workspace(&m->impl, device);
+    try { noallocSetup(device); } catch (...) {}  // set-up of hppb200_validate_configs_noalloc (it reports a failure itself)
   });
 }
 void hppb200_workspace_destroy(hppb200_workspace* ws) { delete ws; }
@@ -238,6 +239,20 @@ int hppb200_validate_configs(hppb200_workspace* wsp, const double* q, size_t n, 
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_valid.p, n, cudaMemcpyDeviceToHost, ws->stream));
     if (first_pair) HPPB200_CUDA_CHECK(cudaMemcpyAsync(first_pair, ws->d_pair.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
     if (reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(reason, ws->d_reason.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    tm.stop();
+  });
+}
+
+int hppb200_validate_configs_noalloc(hppb200_workspace* wsp, const double* q, size_t n, uint32_t flags, uint8_t* valid,
+                                     int32_t* first_pair, uint8_t* reason) {
+  return guarded([&] {
+    if (!wsp) throw std::invalid_argument("null argument");
+    if (!(flags & HPPB200_DEVICE_POINTERS))
+      throw std::invalid_argument("hppb200_validate_configs_noalloc takes device pointers only (HPPB200_DEVICE_POINTERS): staging host buffers would allocate");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    Timed tm(ws);
+    launchValidateConfigsNoAlloc(ws, q, n, flags, valid, first_pair, reason);
     tm.stop();
   });
 }

@@ -180,6 +180,9 @@ double measureFp64Peak(int device);
 // kernel launchers (kernels_config.cu / kernels_edges.cu), all asynchronous on ws->stream
 void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
                            int32_t* d_first, uint8_t* d_reason);
+void noallocSetup(int device);  // resolves the static scratch array's device address (cudaGetSymbolAddress), once per device
+void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first,
+                                  uint8_t* d_reason);
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg);
 void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_dist);
 void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2, size_t n, double* d_L);

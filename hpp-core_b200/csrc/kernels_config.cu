@@ -425,6 +425,80 @@ void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t 
   ws->last_jobs = njobs;
   if (njobs > 2 * n + 4096) launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
 }
+// ------------------------------------------------------------------------------------------------
+// hppb200_validate_configs_noalloc: the same two kernels (configPassKernel + gjkJobsKernel) with their scratch
+// (job counter, job queue, placement SoA) in a file-scope device array instead of the workspace's cudaMalloc'ed
+// buffers, for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+// No counterpart in the reference.
+// The array is per device (every GPU that loads the library holds HPPB200_NOALLOC_SCRATCH_BYTES until exit), shared
+// by every call and keeps the last call's contents: the job counter is cleared at the start of each call (nothing
+// else must start at zero: the queue and the placements are written before they are read), and calls that overlap on
+// the GPU race on it.
+static __device__ __align__(256) unsigned char g_noallocScratch[HPPB200_NOALLOC_SCRATCH_BYTES];
+
+// The array's name is a host-side stand-in in host code: the device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static unsigned char* noallocScratchAddress(int device) {
+  static std::mutex mu;
+  static unsigned char* ptr[64] = {};
+  if (device < 0 || device >= 64) throw std::invalid_argument("device index out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[device]) {
+    HPPB200_CUDA_CHECK(cudaSetDevice(device));
+    void* p = nullptr;
+    HPPB200_CUDA_CHECK(cudaGetSymbolAddress(&p, g_noallocScratch));
+    if (!p) throw std::runtime_error("cudaGetSymbolAddress returned a null scratch address");
+    ptr[device] = (unsigned char*)p;
+  }
+  return ptr[device];
+}
+void noallocSetup(int device) { (void)noallocScratchAddress(device); }
+
+void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first,
+                                  uint8_t* d_reason) {
+  if (n == 0) return;
+  if (!d_q || !d_valid || !d_first || !d_reason) throw std::invalid_argument("hppb200_validate_configs_noalloc: q, valid, first_pair and reason are required");
+  const bool tree = modelIsTree(ws->model);
+  const ModelView& mv = ws->view;
+  const size_t slots = (size_t)mv.ngeoms + (tree ? mv.njoints : 0);
+  const size_t cap = 2 * n + 4096;                       // job queue entries, as in launchValidateTwoKernel
+  const size_t offJobs = 256, offPlc = (offJobs + cap * sizeof(unsigned long long) + 255) & ~size_t(255);
+  const size_t need = offPlc + slots * 12 * n * sizeof(double);
+  if (need > (size_t)HPPB200_NOALLOC_SCRATCH_BYTES) {
+    const size_t perConfig = slots * 96 + 16;
+    throw std::invalid_argument("hppb200_validate_configs_noalloc: " + std::to_string(n) + " configurations need " + std::to_string(need) +
+                                " B of scratch, the static array holds " + std::to_string((size_t)HPPB200_NOALLOC_SCRATCH_BYTES) + " B (at most " +
+                                std::to_string(((size_t)HPPB200_NOALLOC_SCRATCH_BYTES - 33536) / perConfig) +
+                                " configurations per call for this model); use hppb200_validate_configs or split the batch");
+  }
+  unsigned char* base = noallocScratchAddress(ws->device);
+  ValidateArgs A{};
+  A.q = d_q; A.n = n; A.flags = flags; A.valid = d_valid; A.first = (uint32_t*)d_first; A.reason = d_reason;
+  A.njobs = (unsigned long long*)base;
+  A.jobs = (unsigned long long*)(base + offJobs);
+  A.jobs_cap = cap;
+  A.oMg = (double*)(base + offPlc);
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), ws->stream));  // the one thing that must start at zero
+  const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
+                       (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
+  if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
+  auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+  k1<<<(unsigned)((n + K1_THREADS - 1) / K1_THREADS), K1_THREADS, smem1, ws->stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  const size_t smem2 = 16 + mv.blob_bytes;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  gjkJobsKernel<<<(unsigned)((size_t)ws->num_sms * 4), 256, smem2, ws->stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 2;
+  ws->stats.configs += n;
+  // queue overflow: same rule as launchValidateConfigs (the fused single kernel needs no scratch at all)
+  unsigned long long njobs = 0;
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&njobs, A.njobs, sizeof(njobs), cudaMemcpyDeviceToHost, ws->stream));
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  if (njobs > cap) launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
+}
+
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg) {
   launchConfigKernel(ws, d_q, n, 0, MODE_PLACEMENTS, nullptr, nullptr, nullptr, d_oMg);
 }

@@ -253,6 +253,22 @@ int hppb200_validate_configs(hppb200_workspace* ws, const double* q, size_t n,
                              uint32_t flags, uint8_t* valid, int32_t* first_pair,
                              uint8_t* reason);
 
+/* Same result as hppb200_validate_configs, for callers that cannot allocate device memory (CUDA graph capture, serving
+   loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+   Calls no cudaMalloc / cudaFree / allocating library routine: the kernels' scratch (job counter, job
+   queue, geometry placements) lives in ONE static device array of HPPB200_NOALLOC_SCRATCH_BYTES per GPU, held by every
+   GPU that loads the library until the process exits.  Requirements: flags must contain HPPB200_DEVICE_POINTERS (q,
+   valid, first_pair, reason all device pointers, all non-NULL); n limited by the array:
+   256 + 8 (2 n + 4096) + 96 (ngeoms [+ njoints for tree-shaped robots]) n bytes must fit, i.e. about 85 000
+   configurations per call for UR5 (8 geometries); more => HPPB200_ERR_INVALID_ARGUMENT with the limit in the message.
+   The array is shared by every workspace and call on that GPU and keeps the last call's contents (the call clears the
+   job counter itself, nothing else needs to start at zero): calls that overlap on the GPU (two workspaces / streams /
+   threads) race on it - serialise them.  The first workspace created on a device resolves the array's address. */
+#define HPPB200_NOALLOC_SCRATCH_BYTES (64u << 20)
+int hppb200_validate_configs_noalloc(hppb200_workspace* ws, const double* q, size_t n,
+                                     uint32_t flags, uint8_t* valid, int32_t* first_pair,
+                                     uint8_t* reason);
+
 /* Forward kinematics only: oMg [n][ngeoms][12] robot geometry world placements
    (pinocchio::forwardKinematics + updateGeometryPlacements). Test/diagnostic. */
 int hppb200_geometry_placements(hppb200_workspace* ws, const double* q, size_t n,
