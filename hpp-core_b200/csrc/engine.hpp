@@ -141,6 +141,9 @@ struct Workspace {
   cudaStream_t stream = nullptr;
   bool own_stream = true;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t stream2 = nullptr, stream3 = nullptr, stream4 = nullptr;  // H2D / D2H streams of the sliced host-pointer path (created on first use)
+  std::vector<cudaEvent_t> evSlice;
+  cudaEvent_t evFork = nullptr, evJoin = nullptr;
   ModelView view;
   DeviceStats* d_stats = nullptr;
   hppb200_stats stats{};
@@ -183,6 +186,8 @@ void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t 
 void noallocSetup(int device);  // resolves the static scratch array's device address (cudaGetSymbolAddress), once per device
 void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first,
                                   uint8_t* d_reason);
+void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint32_t flags, uint8_t* h_valid, int32_t* h_first,
+                               uint8_t* h_reason);
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg);
 void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_dist);
 void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2, size_t n, double* d_L);

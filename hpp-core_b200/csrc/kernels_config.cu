@@ -16,6 +16,8 @@
 //      shared memory; a lane skips a pair whose index is already above its configuration's
 //      current minimum (the reference's early exit).
 // FP64 throughout; bound by the FP64 pipe, not HBM (53 algorithmic bytes per configuration).
+#include <cstdio>
+
 #include "dev_model.cuh"
 
 namespace hppb200 {
@@ -357,6 +359,42 @@ gjkJobsKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
   }
 }
 
+// The two kernels on `stream`, scratch given by the caller: oMg [slots*12][n], njobs (one counter), jobs [cap].
+// streamJobs / evPass: when given, gjkJobsKernel runs on its own stream behind the event recorded after configPassKernel
+// (a latency-bound kernel: it overlaps the next slice's configPassKernel).
+static void launchTwoKernelsOn(Workspace* ws, cudaStream_t stream, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
+                               int32_t* d_first, uint8_t* d_reason, double* oMg, unsigned long long* njobs, unsigned long long* jobs,
+                               size_t cap, cudaStream_t streamJobs = nullptr, cudaEvent_t evPass = nullptr) {
+  const bool tree = modelIsTree(ws->model);
+  const ModelView& mv = ws->view;
+  ValidateArgs A{};
+  A.q = d_q; A.n = n; A.flags = flags; A.valid = d_valid; A.first = (uint32_t*)d_first; A.reason = d_reason;
+  A.oMg = oMg;
+  A.njobs = njobs;
+  A.jobs = jobs;
+  A.jobs_cap = cap;
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), stream));
+  const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
+                       (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
+  if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
+  auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+  k1<<<(unsigned)((n + K1_THREADS - 1) / K1_THREADS), K1_THREADS, smem1, stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  const size_t smem2 = 16 + mv.blob_bytes;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  size_t grid2 = (size_t)ws->num_sms * 4;
+  if (streamJobs) {
+    HPPB200_CUDA_CHECK(cudaEventRecord(evPass, stream));
+    HPPB200_CUDA_CHECK(cudaStreamWaitEvent(streamJobs, evPass, 0));
+    stream = streamJobs;
+  }
+  gjkJobsKernel<<<(unsigned)grid2, 256, smem2, stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 2;
+  ws->stats.configs += n;
+}
+
 // Jobs that did not fit the queue (pathological scenes): detected on the host, which re-runs the
 // batch through the single-kernel path below (still on the device).
 static void launchValidateTwoKernel(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
@@ -370,27 +408,7 @@ static void launchValidateTwoKernel(Workspace* ws, const double* d_q, size_t n, 
   ws->d_scratch.reserve(slots * 12 * n);
   const size_t cap = 2 * n + 4096;
   ws->d_jobs.reserve(cap + 1);
-  ValidateArgs A{};
-  A.q = d_q; A.n = n; A.flags = flags; A.valid = d_valid; A.first = (uint32_t*)d_first; A.reason = d_reason;
-  A.oMg = ws->d_scratch.p;
-  A.njobs = ws->d_jobs.p;
-  A.jobs = ws->d_jobs.p + 1;
-  A.jobs_cap = cap;
-  HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), ws->stream));
-  const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
-                       (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
-  if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
-  auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-  k1<<<(unsigned)((n + K1_THREADS - 1) / K1_THREADS), K1_THREADS, smem1, ws->stream>>>(mv, A, ws->d_stats);
-  HPPB200_CUDA_CHECK(cudaGetLastError());
-  const size_t smem2 = 16 + mv.blob_bytes;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  size_t grid2 = (size_t)ws->num_sms * 4;
-  gjkJobsKernel<<<(unsigned)grid2, 256, smem2, ws->stream>>>(mv, A, ws->d_stats);
-  HPPB200_CUDA_CHECK(cudaGetLastError());
-  ws->stats.kernel_launches += 2;
-  ws->stats.configs += n;
+  launchTwoKernelsOn(ws, ws->stream, d_q, n, flags, d_valid, d_first, d_reason, ws->d_scratch.p, ws->d_jobs.p, ws->d_jobs.p + 1, cap);
 }
 
 static void launchConfigKernel(Workspace* ws, const double* d_q, size_t n, uint32_t flags, int mode, uint8_t* d_valid,
@@ -497,6 +515,115 @@ void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, ui
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(&njobs, A.njobs, sizeof(njobs), cudaMemcpyDeviceToHost, ws->stream));
   HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
   if (njobs > cap) launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
+}
+
+// Host-pointer path of hppb200_validate_configs: the batch in slices on three streams (H2D, kernels, D2H), so that the
+// H2D copy of slice i + 1 runs under the kernels of slice i and the D2H of slice i - 1 behind them (the monolithic copy -> kernels ->
+// copy sequence left the copy engines and the SMs idle in turn: 2.17 ms end to end for 1.14 ms of kernels).
+// Every slice has its own placement / queue region; the queue-overflow counters are read once at the end.
+// Returns with everything complete (both streams synchronised); ws->ev1 is recorded on ws->stream at the end.
+void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint32_t flags, uint8_t* h_valid, int32_t* h_first,
+                               uint8_t* h_reason) {
+  if (n == 0) return;
+  if (n > 0xffffffffull) throw std::invalid_argument("at most 2^32-1 configurations per call");
+  const bool tree = modelIsTree(ws->model);
+  const ModelView& mv = ws->view;
+  const size_t nq = (size_t)ws->model->nq;
+  const size_t slots = (size_t)mv.ngeoms + (tree ? mv.njoints : 0);
+  // slice sizes in whole WAVES of configPassKernel (resident CTAs x 128 configurations; a slice of 1.15 waves costs 2):
+  // one wave first (the kernels start after its copy), then doubling up to `maxWaves`; the H2D stream runs ahead of the
+  // compute stream (0.86 ns vs 1.09 ns per UR5 configuration), the D2H stream behind it
+  size_t wave;
+  {
+    const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
+                         (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
+    if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
+    auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
+    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    int perSM = 0;
+    HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k1, K1_THREADS, smem1));
+    wave = (size_t)std::max(1, perSM) * (size_t)ws->num_sms * K1_THREADS;
+  }
+  size_t maxWaves = 4;
+  if (const char* v = std::getenv("HPPB200_CFG_SLICE_WAVES")) maxWaves = std::max<size_t>(1, (size_t)std::atoll(v));
+  std::vector<size_t> offs, lens;
+  for (size_t off = 0, w = 1; off < n; w = std::min(maxWaves, w * 2)) {
+    size_t m = std::min(w * wave, n - off);
+    if (n - off - m < wave / 2) m = n - off;  // no tiny last slice
+    offs.push_back(off); lens.push_back(m);
+    off += m;
+  }
+  const size_t ns = offs.size();
+  ws->d_q.reserve(n * nq);
+  ws->d_valid.reserve(n);
+  ws->d_pair.reserve(n);
+  ws->d_reason.reserve(n);
+  ws->d_scratch.reserve(slots * 12 * n);
+  const size_t capAll = 2 * n + 4096 * ns;
+  ws->d_jobs.reserve(capAll + ns + 1);
+  if (!ws->stream2) {
+    HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->stream2, cudaStreamNonBlocking));
+    HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->stream3, cudaStreamNonBlocking));
+    // (a high-priority stream for gjkJobsKernel was measured slower: 655 vs 697 M configurations/s end to end)
+    HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->stream4, cudaStreamNonBlocking));
+    HPPB200_CUDA_CHECK(cudaEventCreateWithFlags(&ws->evJoin, cudaEventDisableTiming));
+    HPPB200_CUDA_CHECK(cudaEventCreateWithFlags(&ws->evFork, cudaEventDisableTiming));
+  }
+  while (ws->evSlice.size() < 3 * ns) {
+    cudaEvent_t e;
+    HPPB200_CUDA_CHECK(cudaEventCreate(&e));  // (timing kept: HPPB200_CFG_TRACE prints the slice timeline)
+    ws->evSlice.push_back(e);
+  }
+  HPPB200_CUDA_CHECK(cudaEventRecord(ws->evFork, ws->stream));  // (the staging buffers may still be read by earlier work)
+  HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream2, ws->evFork, 0));
+  unsigned long long* counters = ws->d_jobs.p;       // [ns]
+  unsigned long long* queue = ws->d_jobs.p + ns;     // slice k at 2 * off + 4096 * k
+  for (size_t k = 0; k < ns; ++k) {
+    const size_t off = offs[k], m = lens[k];
+    cudaEvent_t evIn = ws->evSlice[3 * k], evDone = ws->evSlice[3 * k + 1], evPass = ws->evSlice[3 * k + 2];
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p + off * nq, h_q + off * nq, m * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream2));
+    HPPB200_CUDA_CHECK(cudaEventRecord(evIn, ws->stream2));
+    HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream, evIn, 0));
+    launchTwoKernelsOn(ws, ws->stream, ws->d_q.p + off * nq, m, flags, ws->d_valid.p + off, ws->d_pair.p + off, ws->d_reason.p + off,
+                       ws->d_scratch.p + slots * 12 * off, counters + k, queue + 2 * off + 4096 * k, 2 * m + 4096, ws->stream4, evPass);
+    HPPB200_CUDA_CHECK(cudaEventRecord(evDone, ws->stream4));
+    HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream3, evDone, 0));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_valid + off, ws->d_valid.p + off, m, cudaMemcpyDeviceToHost, ws->stream3));
+    if (h_first) HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_first + off, ws->d_pair.p + off, m * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream3));
+    if (h_reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_reason + off, ws->d_reason.p + off, m, cudaMemcpyDeviceToHost, ws->stream3));
+  }
+  HPPB200_CUDA_CHECK(cudaEventRecord(ws->evJoin, ws->stream3));
+  HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream, ws->evJoin, 0));
+  std::vector<unsigned long long> h_cnt(ns);
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_cnt.data(), counters, ns * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ws->stream));
+  HPPB200_CUDA_CHECK(cudaEventRecord(ws->ev1, ws->stream));
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  if (std::getenv("HPPB200_CFG_TRACE")) {
+    for (size_t k = 0; k < ns; ++k) {
+      float a = 0, b = 0;
+      float c = 0;
+      cudaEventElapsedTime(&a, ws->ev0, ws->evSlice[3 * k]);
+      cudaEventElapsedTime(&b, ws->ev0, ws->evSlice[3 * k + 1]);
+      cudaEventElapsedTime(&c, ws->ev0, ws->evSlice[3 * k + 2]);
+      std::fprintf(stderr, "[cfg] slice %zu: %zu configurations, H2D done at %.3f ms, configPass at %.3f, gjkJobs at %.3f ms\n", k, lens[k], a, c, b);
+    }
+    float t = 0;
+    cudaEventElapsedTime(&t, ws->ev0, ws->ev1);
+    std::fprintf(stderr, "[cfg] all copied back at %.3f ms\n", t);
+  }
+  ws->last_jobs = 0;
+  for (size_t k = 0; k < ns; ++k) {
+    const size_t off = offs[k], m = lens[k];
+    ws->last_jobs += h_cnt[k];
+    if (h_cnt[k] <= 2 * m + 4096) continue;
+    // queue overflow in this slice: the fused single kernel needs no queue (same rule as launchValidateConfigs)
+    launchConfigKernel(ws, ws->d_q.p + off * nq, m, flags, MODE_VALIDATE, ws->d_valid.p + off, ws->d_pair.p + off, ws->d_reason.p + off, nullptr);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_valid + off, ws->d_valid.p + off, m, cudaMemcpyDeviceToHost, ws->stream));
+    if (h_first) HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_first + off, ws->d_pair.p + off, m * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    if (h_reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_reason + off, ws->d_reason.p + off, m, cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaEventRecord(ws->ev1, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  }
 }
 
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg) {
