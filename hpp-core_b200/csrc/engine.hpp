@@ -105,6 +105,7 @@ struct Model {
   void buildConfigPairs(const hppb200_model_desc& d);
   void buildBodyPairs(const hppb200_model_desc& d);
   void applyPairOps(const hppb200_model_desc& d);
+  void finishBodyPair(BodyPairHost& bp) const;
   void buildBlob();
   double margin(int j1, int j2) const { return margins.empty() ? 0.0 : margins[(size_t)j1 * (njoints + 1) + j2]; }
   mutable std::mutex mu_;

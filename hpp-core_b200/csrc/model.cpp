@@ -183,6 +183,23 @@ void Model::applyPairOps(const hppb200_model_desc& d) {
         add(op.b);
         break;
       }
+      case HPPB200_OP_ADD_OBSTACLE: {  // obstacle-user.cc:53-58 (default request: margin 0), continuous-validation.cc:103-118
+        checkObstacle(op.a);
+        for (int j = 1; j <= njoints; ++j) {
+          BodyPairHost bp;
+          bp.joint_a = j;
+          bp.joint_b = 0;
+          for (int g = 0; g < (int)geoms.size(); ++g)
+            if (geoms[g].joint == j) {
+              cPairs.push_back(DevPair{g, -(op.a + 1), 0, 0, 0.0, 0.0});
+              bp.pairs.push_back(DevPair{g, -(op.a + 1), 0, 0, 0.0, 0.0});
+            }
+          if (bp.pairs.empty()) continue;
+          finishBodyPair(bp);
+          bodyPairs.push_back(bp);
+        }
+        break;
+      }
       case HPPB200_OP_REMOVE_OBSTACLE_FROM_JOINT: {  // obstacle-user.cc:87-118, continuous-validation.cc:224-252
         checkObstacle(op.a); checkJoint(op.b);
         const int oref = -(op.a + 1);
@@ -272,7 +289,9 @@ void Model::buildConfigPairs(const hppb200_model_desc& d) {
   }
 }
 
-void Model::buildBodyPairs(const hppb200_model_desc& d) {
+// Joint sequence and velocity coefficients of one body pair (SolidSolidCollision::Model::computeSequenceOfJoints /
+// computeCoefficients / setCoefficients, reference src/continuous-validation/solid-solid-collision.cc:162-244)
+void Model::finishBodyPair(BodyPairHost& bp) const {
   auto parentOf = [&](int j) { return joints[j - 1].parent; };
   auto linVel = [&](int j) { int t = joints[j - 1].type; return (t >= HPPB200_JOINT_PRISMATIC_X) ? 1.0 : 0.0; };
   auto angVel = [&](int j) { int t = joints[j - 1].type; return (t <= HPPB200_JOINT_REVOLUTE_Z || t == HPPB200_JOINT_FREEFLYER) ? 1.0 : 0.0; };
@@ -311,7 +330,6 @@ void Model::buildBodyPairs(const hppb200_model_desc& d) {
     }
     return out;
   };
-  auto finish = [&](BodyPairHost& bp) {
     std::vector<int> up, down;  // climb from the larger index until both meet
     int ia = bp.joint_a, ib = bp.joint_b;
     while (ia != ib) {
@@ -326,7 +344,10 @@ void Model::buildBodyPairs(const hppb200_model_desc& d) {
       std::reverse(seq.begin(), seq.end());
       bp.rcoefs = coefficients(seq, bp.joint_a);
     }
-  };
+}
+
+void Model::buildBodyPairs(const hppb200_model_desc& d) {
+  auto finish = [&](BodyPairHost& bp) { finishBodyPair(bp); };
   // self pairs: one body pair per ordered joint pair, in order of first appearance
   std::map<std::pair<int, int>, size_t> seen;
   for (int p = 0; p < d.nself_pairs; ++p) {

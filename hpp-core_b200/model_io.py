@@ -20,6 +20,7 @@ class hppb200_pair_op(C.Structure):
 
 OP_ADD_OBSTACLE_TO_JOINT, OP_REMOVE_OBSTACLE_FROM_JOINT, OP_FILTER_COLLISION_PAIRS, OP_SET_SECURITY_MARGINS, \
     OP_SET_MARGIN_BETWEEN_BODIES = 1, 2, 3, 4, 5
+OP_ADD_OBSTACLE = 6
 
 
 class hppb200_model_desc(C.Structure):

@@ -172,6 +172,10 @@ typedef struct hppb200_model_desc {
 #define HPPB200_OP_SET_MARGIN_BETWEEN_BODIES 5  /* a, b = geometry references, value = margin; configuration table:
                                                    first matching pair, none => HPPB200_ERR_INVALID_ARGUMENT;
                                                    continuous table: every matching pair                         */
+#define HPPB200_OP_ADD_OBSTACLE 6               /* a = obstacle k (obst_global[k] = 0): addObstacle() called at this point
+                                                   of the log, i.e. after earlier filters / margin matrices, which
+                                                   therefore do not apply to its pairs (obstacle-user.cc:53-58,
+                                                   continuous-validation.cc:103-118)                              */
 typedef struct hppb200_pair_op {
   int32_t kind, a, b, flag;
   double value;

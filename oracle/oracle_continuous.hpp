@@ -225,6 +225,19 @@ struct ContinuousValidation {
     const size_t n1 = dev->joints.size();
     switch (op.kind) {
       case HPPB200_OP_ADD_OBSTACLE_TO_JOINT: break;  // not part of the interface of a path validation
+      case HPPB200_OP_ADD_OBSTACLE: {  // AddObstacle::doExecute :103-118, default request (margin 0)
+        const std::vector<double> radii = dev->bodyRadii();
+        for (int j = 1; j <= dev->njoints(); ++j) {
+          if (!dev->jointHasBody(j)) continue;
+          SolidSolidCollision ss;
+          ss.dev = dev; ss.joint_a = j; ss.joint_b = 0; ss.tolerance = tolerance;
+          for (size_t g = 0; g < dev->geoms.size(); ++g)
+            if (dev->geoms[g].joint == j) ss.pairs.push_back({(int)g, -(op.a + 1), 0.0});
+          ss.setCoefficients(radii);
+          intervalValidations_.push_back(ss);
+        }
+        break;
+      }
       case HPPB200_OP_REMOVE_OBSTACLE_FROM_JOINT: {  // :224-252 + SolidSolidCollision::removeObjectTo_b (:101-122)
         if (!dev->jointHasBody(op.b)) break;  // (the configuration validator only walks the inner objects of the body)
         bool removed = false;

@@ -70,6 +70,7 @@ struct ObstacleUser {
     const size_t n1 = dev->joints.size();
     switch (op.kind) {
       case HPPB200_OP_ADD_OBSTACLE_TO_JOINT: addObstacleToJoint(op.a, op.b, op.flag != 0); break;
+      case HPPB200_OP_ADD_OBSTACLE: addObstacle(op.a); break;  // cRequests_.push_back(defaultRequest_): margin 0
       case HPPB200_OP_REMOVE_OBSTACLE_FROM_JOINT:  // :87-118
         for (size_t g = 0; g < dev->geoms.size(); ++g) {
           if (dev->geoms[g].joint != op.b) continue;

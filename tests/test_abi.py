@@ -70,6 +70,7 @@ def pair_op_model(pkg, name="ur5_boxes8.json"):
     nj = desc.njoints
     og = np.ones(desc.nobstacles, np.uint8)
     og[7] = 0
+    og[6] = 0   # obstacle 6 is added by addObstacle() AFTER the margin matrix and the filter: margin 0, not filtered
     desc.obst_global = og
     rel = np.full((nj + 1, nj + 1), 2, np.int32)
     np.fill_diagonal(rel, 0)
@@ -83,6 +84,7 @@ def pair_op_model(pkg, name="ur5_boxes8.json"):
                      (mio.OP_REMOVE_OBSTACLE_FROM_JOINT, 0, 3, 0, 0.0, None),
                      (mio.OP_SET_SECURITY_MARGINS, 0, 0, 0, 0.0, mar),
                      (mio.OP_FILTER_COLLISION_PAIRS, 0, 0, 0, 0.0, rel),
+                     (mio.OP_ADD_OBSTACLE, 6, 0, 0, 0.0, None),
                      (mio.OP_SET_MARGIN_BETWEEN_BODIES, geom_j3, -2, 0, 0.0123, None)]
     return desc
 
@@ -107,12 +109,16 @@ def test_pair_table_edits_match_oracle(pkg, ob, check_parameterized):
     # obstacle 7 only on joints >= 2; obstacle 0 not on joint 3; constrained joint pairs gone; one edited margin
     assert not np.any((b == -8) & (gj[a] < 2)) and np.any(b == -8)
     assert not np.any((b == -1) & (gj[a] == 3))
-    assert not np.any((gj[a] == 5) & (jb == 0))
+    assert not np.any((gj[a] == 5) & (jb == 0) & (b != -7))  # (-7: the obstacle added after the filter)
     assert 0.0123 in mg
+    assert np.any((b == -7) & (gj[a] == 5)) and np.all(mg[b == -7] == 0)  # late obstacle: unfiltered, default margin
     bm, bo = m.body_pairs(), o.body_pairs()
     for k in bm:
         assert np.array_equal(bm[k], bo[k]), k
-    assert not np.any((bm["joint_a"] == 5) & (bm["joint_b"] == 0))
+    late = np.zeros(len(bm["joint_a"]), bool)
+    for i in range(len(late)):
+        late[i] = np.all(bm["geomB"][bm["pair_begin"][i]:bm["pair_begin"][i + 1]] == -7)
+    assert not np.any((bm["joint_a"] == 5) & (bm["joint_b"] == 0) & ~late) and np.any((bm["joint_a"] == 5) & late)
     assert not np.any(bm["geomB"] == -8)  # ContinuousValidation has no addObstacleToJoint
     assert 0.0123 in bm["margin"]
 
