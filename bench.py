@@ -66,6 +66,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-edges", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--full-size", action="store_true",
+                    help="also run BASELINE configs[4] at its stated per-GPU size: 12.5 M configurations and 1.25 M edges per rank, one call each")
     return ap.parse_args()
 
 
@@ -239,16 +241,18 @@ def run_b200(args):
     valid_d = torch.empty(n, dtype=torch.uint8, device=dev)
     first_d = torch.empty(n, dtype=torch.int32, device=dev)
     reason_d = torch.empty(n, dtype=torch.uint8, device=dev)
-    valid_all = torch.empty(n * world, dtype=torch.uint8, device=dev) if world > 1 else None
     valid_h = torch.empty(n, dtype=torch.uint8).pin_memory()
     first_h = torch.empty(n, dtype=torch.int32).pin_memory()
     reason_h = torch.empty(n, dtype=torch.uint8).pin_memory()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
+    from hpp_core_b200 import sharding as sh
+    gathered = {}
+
     def step_device():
         ws.validate_configs_ptr(q_dev.data_ptr(), n, valid_d.data_ptr(), first_d.data_ptr(), reason_d.data_ptr(), FLAGS_DEV)
-        if world > 1:  # the path's only exchange: gather of the validity masks (1 B per configuration)
-            dist.all_gather_into_tensor(valid_all, valid_d)
+        if world > 1:  # the path's only exchange: gather of the validity masks, bit-packed (1 bit per configuration)
+            gathered["valid_all"], _ = sh.all_gather_mask_packed(valid_d)
 
     def step_e2e():
         ws.validate_configs_ptr(q_host.data_ptr(), n, valid_h.data_ptr(), first_h.data_ptr(), reason_h.data_ptr(), 0)
@@ -292,6 +296,8 @@ def run_b200(args):
     e2e_value = world * n * args.steps / (e2e_ms * 1e-3)
     # identical results on both paths
     assert torch.equal(valid_h, valid_d.cpu()) and torch.equal(first_h, first_d.cpu())
+    if world > 1:  # the gathered mask holds this rank's flags at its place
+        assert torch.equal(gathered["valid_all"][rank * n:(rank + 1) * n], valid_d)
 
     # ---- N > 1: every rank validates its own shard of edges (Progressive), validity masks all-gathered ----
     edges_sharded = None
@@ -306,19 +312,90 @@ def run_b200(args):
         stl = torch.empty(ne, dtype=torch.float64, device=dev)
         spr = torch.empty(ne, dtype=torch.int32, device=dev)
         srs = torch.empty(ne, dtype=torch.uint8, device=dev)
-        sv_all = torch.empty(ne * world, dtype=torch.uint8, device=dev) if world > 1 else None
 
         def shard_call():
             ws.validate_edges_ptr(pkg.METHOD_PROGRESSIVE, 1e-3, False, s1d.data_ptr(), s2d.data_ptr(), sLd.data_ptr(), ne,
                                   sv.data_ptr(), stf.data_ptr(), stl.data_ptr(), spr.data_ptr(), srs.data_ptr(), FLAGS_DEV)
             if world > 1:
-                dist.all_gather_into_tensor(sv_all, sv)
+                gathered["sv_all"], _ = sh.all_gather_mask_packed(sv)
         ms_s, _, _ = timed(shard_call, 3, 1)
+        sv_all = gathered.get("sv_all")
         edges_sharded = {"value": world * ne * 3 / (ms_s * 1e-3), "unit": "edges/s", "edges_per_gpu": ne, "param": 1e-3,
                          "method": "progressive", "ms_per_call": ms_s / 3,
-                         "collective": "all_gather of uint8 validity masks (NCCL)" if world > 1 else "none",
+                         "collective": "all_gather of bit-packed validity masks (NCCL, 1 bit per edge)" if world > 1 else "none",
                          "valid_frac_all_ranks": float((sv_all if world > 1 else sv).float().mean().item())}
         del s1d, s2d, sLd, sv, stf, stl, spr, srs, sv_all
+
+    # ---- every rank: node-sharded k-NN (1 M roadmap nodes split by node index, queries replicated), candidates
+    #      all-gathered and merged ON THE DEVICE with the reference tie rule (hppb200_knn_merge_shards) ----
+    knn_sharded = None
+    if not args.no_edges:
+        n_nodes, nqr, kk = 1 << 20, 1024, 10
+        nb, ne_ = sh.node_owner_ranges(n_nodes, world)[rank]
+        nodes_local = pkg.uniform_configs(desc, ne_ - nb, seed=SEED + 2, offset=nb)
+        nn_local = pkg.NearestNeighbor(model, local_rank)
+        nn_local.append(nodes_local)
+        qs_d = torch.from_numpy(pkg.uniform_configs(desc, nqr, seed=SEED + 3)).to(dev)
+        li = torch.empty((nqr, kk), dtype=torch.int64, device=dev)
+        ld = torch.empty((nqr, kk), dtype=torch.float64, device=dev)
+        gi = torch.empty((world, nqr, kk), dtype=torch.int64, device=dev)
+        gd = torch.empty((world, nqr, kk), dtype=torch.float64, device=dev)
+
+        def knn_call():
+            nn_local.query_ptr(qs_d.data_ptr(), nqr, kk, li.data_ptr(), ld.data_ptr())
+            lg = torch.where(li >= 0, li + nb, li)  # global node indices
+            if world > 1:
+                dist.all_gather_into_tensor(gi.view(-1), lg.view(-1))
+                dist.all_gather_into_tensor(gd.view(-1), ld.view(-1))
+            else:
+                gi[0], gd[0] = lg, ld
+            gathered["knn"] = sh.merge_topk_device(gi, gd, kk)
+        ms_k, _, _ = timed(knn_call, 5, 2)
+        knn_sharded = {"value": nqr * 5 / (ms_k * 1e-3), "unit": "queries/s", "nodes": n_nodes, "nodes_per_gpu": ne_ - nb, "queries": nqr,
+                       "k": kk, "ms_per_call": ms_k / 5,
+                       "collective": "all_gather of per-rank top-k (distance f64, global index i64) + device merge" if world > 1 else "none"}
+        del nn_local
+
+    full = None
+    if args.full_size:  # BASELINE configs[4]: 100 M configurations / 10 M edges over 8 GPUs = 12.5 M / 1.25 M per rank, one call each
+        nf, nef = 12_500_000, 1_250_000
+        qf = torch.empty((nf, nq), dtype=torch.float64, device=dev)
+        for c0 in range(0, nf, 1 << 21):
+            c1 = min(nf, c0 + (1 << 21))
+            qf[c0:c1] = torch.from_numpy(pkg.uniform_configs(desc, c1 - c0, seed=SEED + 7, offset=rank * nf + c0)).to(dev)
+        vf = torch.empty(nf, dtype=torch.uint8, device=dev)
+        ff = torch.empty(nf, dtype=torch.int32, device=dev)
+        rf = torch.empty(nf, dtype=torch.uint8, device=dev)
+
+        def full_cfg():
+            ws.validate_configs_ptr(qf.data_ptr(), nf, vf.data_ptr(), ff.data_ptr(), rf.data_ptr(), FLAGS_DEV)
+            gathered["vf_all"], _ = sh.all_gather_mask_packed(vf)
+        ms_fc, _, _ = timed(full_cfg, 3, 1)
+        vfrac = float(gathered["vf_all"].float().mean().item())
+        del qf, ff, rf
+        cfge = pkg.uniform_configs(desc, 2 * nef, seed=SEED + 8, offset=rank * 2 * nef)
+        f1 = torch.from_numpy(np.ascontiguousarray(cfge[0::2])).to(dev)
+        f2 = torch.from_numpy(np.ascontiguousarray(cfge[1::2])).to(dev)
+        fL = torch.from_numpy(ws.straight_lengths(cfge[0::2], cfge[1::2])).to(dev)
+        fv = torch.empty(nef, dtype=torch.uint8, device=dev)
+        ftf = torch.empty(nef, dtype=torch.float64, device=dev)
+        ftl = torch.empty(nef, dtype=torch.float64, device=dev)
+        fpr = torch.empty(nef, dtype=torch.int32, device=dev)
+        frs = torch.empty(nef, dtype=torch.uint8, device=dev)
+
+        def full_edges():
+            ws.validate_edges_ptr(pkg.METHOD_PROGRESSIVE, 1e-3, False, f1.data_ptr(), f2.data_ptr(), fL.data_ptr(), nef, fv.data_ptr(),
+                                  ftf.data_ptr(), ftl.data_ptr(), fpr.data_ptr(), frs.data_ptr(), FLAGS_DEV)
+            gathered["fv_all"], _ = sh.all_gather_mask_packed(fv)
+        ms_fe, _, _ = timed(full_edges, 2, 1)
+        full = {"configs": {"value": world * nf * 3 / (ms_fc * 1e-3), "unit": "configs/s", "configs_per_gpu_per_call": nf,
+                            "total_configs": world * nf, "ms_per_call": ms_fc / 3, "valid_frac_all_ranks": vfrac},
+                "edges": {"value": world * nef * 2 / (ms_fe * 1e-3), "unit": "edges/s", "method": "progressive", "param": 1e-3,
+                          "edges_per_gpu_per_call": nef, "total_edges": world * nef, "ms_per_call": ms_fe / 2,
+                          "valid_frac_all_ranks": float(gathered["fv_all"].float().mean().item())},
+                "collective": "all_gather of bit-packed validity masks (NCCL)" if world > 1 else "none",
+                "note": "BASELINE configs[4]: 100 M configurations / 10 M edges over 8 GPUs; every rank validates its share in ONE call"}
+        del f1, f2, fL, fv, ftf, ftl, fpr, frs, vf
 
     if rank != 0:
         if world > 1:
@@ -506,13 +583,70 @@ def run_b200(args):
                                    "sample": "64 queries, k = 10, %.2f s" % dt}
             knn["parity_64_queries_k10"] = bool(np.array_equal(oi, gi) and np.array_equal(od, gd))
 
+    # ---- BASELINE configs[2]: BiRRT over a 1 M-node roadmap: planner steps/s through the unchanged one-item-per-call
+    #      interfaces (the honest number: every step is 2 nearest-node queries, up to 3 path validations, 1 M-node
+    #      scans) and through the batched step (one k-NN batch + one edge batch per phase), oracle backend beside it ----
+    birrt = None
+    if not args.no_edges:
+        from hpp_core_b200 import planners as pl
+        n_pre = 1 << 19  # nodes per tree: 2 x 512 k = 1 M roadmap nodes
+
+        def prefilled(backend):
+            q0, q1 = pkg.uniform_configs(desc, 1, seed=SEED + 10)[0], pkg.uniform_configs(desc, 1, seed=SEED + 11)[0]
+            planner = pl.BiRRTPlanner(backend, desc, q0, q1, seed=SEED + 12)
+            rmap = planner.roadmap
+            rmap.extend(pkg.uniform_configs(desc, n_pre - 1, seed=SEED + 13), np.zeros(n_pre - 1, np.int64))       # start tree, label 0
+            rmap.extend(pkg.uniform_configs(desc, n_pre - 1, seed=SEED + 14), np.ones(n_pre - 1, np.int64))        # goal tree, label 1
+            return planner
+
+        def step_rate(planner, nsteps, batch):
+            ts = []
+            for _ in range(nsteps):
+                t0 = time.perf_counter()
+                if batch:
+                    planner.one_step_batch(batch)
+                else:
+                    planner.one_step()
+                ts.append(time.perf_counter() - t0)
+            med = sorted(ts)[len(ts) // 2]  # (median: the first component merge relabels 512 k host labels once)
+            return (batch or 1) / med, med
+
+        eng = prefilled(pl.EngineBackend(pkg, model, local_rank, pkg.METHOD_PROGRESSIVE, 1e-3))
+        step_rate(eng, 5, 0)
+        r1, t1 = step_rate(eng, 60, 0)
+        step_rate(eng, 1, 256)
+        rb, tb = step_rate(eng, 7, 256)
+        birrt = {"roadmap_nodes": eng.roadmap.n, "unit": "planner steps/s",
+                 "single_item_calls": {"value": r1, "ms_per_step": t1 * 1e3,
+                                       "note": "BiRRTPlanner::oneStep as the reference drives it: one configuration / one edge per call"},
+                 "batched_step_256": {"value": rb, "ms_per_batch": tb * 1e3, "extensions_per_batch": 256}}
+        del eng
+        if not args.no_cpu:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            from oracle_backend import OracleBackend
+            cpu_pl = prefilled(OracleBackend(ob.Oracle(desc), pkg.METHOD_PROGRESSIVE, 1e-3))
+            step_rate(cpu_pl, 2, 0)
+            c1, ct1 = step_rate(cpu_pl, 12, 0)
+            cb, ctb = step_rate(cpu_pl, 2, 256)
+            birrt["cpu_baseline"] = {"single_item_calls": c1, "batched_step_256": cb, "unit": "planner steps/s", "cores": threads,
+                                     "kind": "port", "sample": "12 single steps / 2 batched steps over the same pre-filled roadmap"}
+            del cpu_pl
+
+    if knn_sharded is not None and world > 1:  # parity of the sharded result with the unsharded mirror (rank 0)
+        whole = pkg.NearestNeighbor(model, local_rank)
+        whole.append(pkg.uniform_configs(desc, 1 << 20, seed=SEED + 2))
+        wi, wd = whole.query(pkg.uniform_configs(desc, 1024, seed=SEED + 3), 10)
+        gi_, gd_ = gathered["knn"]
+        knn_sharded["identical_to_unsharded"] = bool(np.array_equal(gi_.cpu().numpy(), wi) and np.array_equal(gd_.cpu().numpy(), wd))
+        del whole
+
     line = {
         "metric": "validated configs/sec", "value": value, "unit": "configs/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "model": MODEL, "configs_per_gpu_per_step": n, "seed": SEED, "pairs": int(len(model.config_pairs()[0])),
                    "l2": "flushed between timed steps (256 MiB memset, untimed)",
-                   "collective": "all_gather of uint8 validity masks (NCCL)" if world > 1 else "none"},
+                   "collective": "all_gather of bit-packed validity masks (NCCL, 1 bit per configuration)" if world > 1 else "none"},
         "e2e": {"value": e2e_value, "unit": "configs/s", "h2d_bytes_per_step": n * nq * 8, "d2h_bytes_per_step": n * 6,
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": int(launches),
@@ -521,6 +655,9 @@ def run_b200(args):
         "cpu_baseline": cpu,
         "edges": edges,
         "edges_sharded": edges_sharded,
+        "knn_sharded": knn_sharded,
+        "full_size": full,
+        "birrt": birrt,
         "knn": knn,
         "parity_vs_oracle_50k": parity_ok,
     }

@@ -51,6 +51,9 @@ ABI_SYMBOLS = [
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
     "hppb200_validate_configs", "hppb200_validate_configs_noalloc", "hppb200_geometry_placements", "hppb200_pair_distances",
     "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edge_chains", "hppb200_workspace_set_max_iterations",
+    "hppb200_multi_create", "hppb200_multi_destroy", "hppb200_multi_num_devices", "hppb200_multi_workspace",
+    "hppb200_multi_validate_configs", "hppb200_multi_validate_edges",
+    "hppb200_pack_mask", "hppb200_unpack_mask", "hppb200_knn_merge_shards",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_set_labels", "hppb200_knn_size",
     "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_tc_debug_tile",
 ]
@@ -274,6 +277,53 @@ class Workspace:
         return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, first_bad_edge=bad)
 
 
+class MultiGpu:
+    """hppb200_multi_*: a device list, sharded internally (host arrays in, host arrays out)."""
+
+    def __init__(self, model, devices=None):
+        self.model = model
+        self.h = C.c_void_p()
+        dv = None if not devices else (C.c_int * len(devices))(*devices)
+        _check(lib().hppb200_multi_create(model.h, dv, C.c_int(len(devices) if devices else 0), C.byref(self.h)))
+        self.ndevices = lib().hppb200_multi_num_devices(self.h)
+
+    def __del__(self):
+        try:
+            if getattr(self, "h", None):
+                lib().hppb200_multi_destroy(self.h)
+                self.h = None
+        except Exception:  # interpreter shutdown
+            pass
+
+    def shard_stats(self, rank):
+        lib().hppb200_multi_workspace.restype = C.c_void_p
+        w = lib().hppb200_multi_workspace(self.h, C.c_int(rank))
+        s = hppb200_stats()
+        _check(lib().hppb200_get_stats(C.c_void_p(w), C.byref(s)))
+        return {k: getattr(s, k) for k, _ in s._fields_}
+
+    def validate_configs(self, q, check_bounds=False):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.model.nq)
+        n = q.shape[0]
+        valid, first, reason = np.zeros(n, np.uint8), np.full(n, -1, np.int32), np.zeros(n, np.uint8)
+        _check(lib().hppb200_multi_validate_configs(self.h, _p(q, _dp), C.c_size_t(n), C.c_uint32(CHECK_JOINT_BOUNDS if check_bounds else 0),
+                                                    _p(valid, _u8p), _p(first, _ip), _p(reason, _u8p)))
+        return valid, first, reason
+
+    def validate_edges(self, method, param, q1, q2, L, reverse=False):
+        q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.model.nq)
+        q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.model.nq)
+        L = np.ascontiguousarray(L, np.float64)
+        n = q1.shape[0]
+        valid, reason = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        t_fail, t_last = np.zeros(n), np.zeros(n)
+        pair = np.full(n, -1, np.int32)
+        _check(lib().hppb200_multi_validate_edges(self.h, C.c_int(method), C.c_double(param), C.c_int(1 if reverse else 0), _p(q1, _dp),
+                                                  _p(q2, _dp), _p(L, _dp), C.c_size_t(n), C.c_uint32(0), _p(valid, _u8p), _p(t_fail, _dp),
+                                                  _p(t_last, _dp), _p(pair, _ip), _p(reason, _u8p)))
+        return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason)
+
+
 class NearestNeighbor:
     """Device mirror of the roadmap nodes + brute-force WeighedDistance search
     (nearestNeighbor::Basic, reference src/nearest-neighbor/basic.cc)."""
@@ -313,6 +363,11 @@ class NearestNeighbor:
         _check(lib().hppb200_knn_query(self.h, _p(queries, _dp), C.c_size_t(n), C.c_int(k), C.c_int32(cc),
                                        C.c_uint32(0), _p(idx, _i64p), _p(dist, _dp)))
         return idx, dist
+
+    def query_ptr(self, q_ptr, n, k, idx_ptr, dist_ptr, cc=-1):
+        """device pointers: queries [n][nq] f64, idx [n][k] i64, dist [n][k] f64 (synchronises the mirror's stream)"""
+        _check(lib().hppb200_knn_query(self.h, C.c_void_p(q_ptr), C.c_size_t(n), C.c_int(k), C.c_int32(cc), C.c_uint32(DEVICE_POINTERS),
+                                       C.c_void_p(idx_ptr), C.c_void_p(dist_ptr)))
 
     def tc_stats(self):
         """(used, stages, queries redone exactly, candidates of the last stage) of the last query."""

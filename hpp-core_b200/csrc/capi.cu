@@ -425,4 +425,25 @@ int hppb200_validate_edge_chains(hppb200_workspace* wsp, int method, double para
   });
 }
 
+// ---- exchange helpers of the sharded form (device pointers, asynchronous on `cuda_stream`) ----
+int hppb200_pack_mask(void* cuda_stream, const uint8_t* valid, size_t n, uint32_t* bits) {
+  return guarded([&] {
+    if (n && (!valid || !bits)) throw std::invalid_argument("null argument");
+    launchPackMask((cudaStream_t)cuda_stream, valid, n, bits);
+  });
+}
+int hppb200_unpack_mask(void* cuda_stream, const uint32_t* bits, size_t n, uint8_t* valid) {
+  return guarded([&] {
+    if (n && (!valid || !bits)) throw std::invalid_argument("null argument");
+    launchUnpackMask((cudaStream_t)cuda_stream, bits, n, valid);
+  });
+}
+int hppb200_knn_merge_shards(void* cuda_stream, const double* dist, const int64_t* idx, int nshards, size_t nqueries, int k,
+                             int64_t* out_idx, double* out_dist) {
+  return guarded([&] {
+    if (nqueries && (!dist || !idx || !out_idx || !out_dist)) throw std::invalid_argument("null argument");
+    launchKnnMergeShards((cudaStream_t)cuda_stream, dist, idx, nshards, nqueries, k, out_idx, out_dist);
+  });
+}
+
 }  // extern "C"

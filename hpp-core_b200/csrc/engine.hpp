@@ -222,6 +222,9 @@ bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d
 void launchChainReduce(Workspace* ws, const int32_t* d_chainBegin, size_t nChains, int reverse, const double* d_L, const uint8_t* eValid,
                        const double* eTfail, const double* eTlast, const int32_t* ePair, const uint8_t* eReason, uint8_t* valid,
                        double* tFail, double* tLast, int32_t* pair, uint8_t* reason, int32_t* firstBad);
+void launchPackMask(cudaStream_t stream, const uint8_t* valid, size_t n, uint32_t* bits);
+void launchUnpackMask(cudaStream_t stream, const uint32_t* bits, size_t n, uint8_t* valid);
+void launchKnnMergeShards(cudaStream_t stream, const double* dist, const int64_t* idx, int W, size_t Q, int k, int64_t* outIdx, double* outDist);
 void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1,
                          const double* d_q2, const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid,
                          double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason);

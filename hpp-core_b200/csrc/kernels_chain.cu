@@ -54,3 +54,66 @@ void launchChainReduce(Workspace* ws, const int32_t* d_chainBegin, size_t nChain
 }
 
 }  // namespace hppb200
+
+// ------------------------------------------------------------------------------------------------
+// Exchange helpers of the sharded (one process per GPU) form of the path, SURVEY.md 8e: the only data that crosses
+// GPUs are validity masks and k-NN candidates.
+namespace hppb200 {
+
+// valid [n] u8 (0 / 1) -> bits [(n + 31) / 32] u32, bit i % 32 of word i / 32: the all-gather then moves n / 8 bytes
+// per rank instead of n (1 MiB -> 128 KiB per 1 M configurations; the collective is latency-bound).
+__global__ void packMaskKernel(const uint8_t* __restrict__ valid, size_t n, uint32_t* __restrict__ bits) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned b = __ballot_sync(0xffffffffu, i < n && valid[i] != 0);
+  if ((threadIdx.x & 31) == 0 && i < n) bits[i >> 5] = b;
+}
+__global__ void unpackMaskKernel(const uint32_t* __restrict__ bits, size_t n, uint8_t* __restrict__ valid) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) valid[i] = (bits[i >> 5] >> (i & 31)) & 1u;
+}
+
+// W-way merge of per-shard k-NN candidates, one thread per query.  dist / idx: [W][Q][k] (rank-major, what an
+// all-gather of the per-rank [Q][k] results produces), every list nearest first by the key (distance, GLOBAL node
+// index), padded with idx = -1.  out: the k smallest keys over all shards, same order and padding: the reference's
+// tie rule (strict '<' keeps the earlier node, src/nearest-neighbor/basic.cc:66,106) carried across shards.
+__global__ void knnMergeShardsKernel(const double* __restrict__ dist, const long long* __restrict__ idx, int W, size_t Q, int k,
+                                     long long* __restrict__ outIdx, double* __restrict__ outDist) {
+  const size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= Q) return;
+  int head[16];
+  for (int w = 0; w < W; ++w) head[w] = 0;
+  for (int j = 0; j < k; ++j) {
+    int best = -1;
+    double bd = 0;
+    long long bi = 0;
+    for (int w = 0; w < W; ++w) {
+      if (head[w] >= k) continue;
+      const size_t o = ((size_t)w * Q + q) * k + head[w];
+      const long long ci = idx[o];
+      if (ci < 0) { head[w] = k; continue; }  // padding: this shard is exhausted
+      const double cd = dist[o];
+      if (best < 0 || cd < bd || (cd == bd && ci < bi)) { best = w; bd = cd; bi = ci; }
+    }
+    if (best < 0) { outIdx[q * k + j] = -1; outDist[q * k + j] = CUDART_INF; }
+    else { outIdx[q * k + j] = bi; outDist[q * k + j] = bd; ++head[best]; }
+  }
+}
+
+void launchPackMask(cudaStream_t stream, const uint8_t* valid, size_t n, uint32_t* bits) {
+  if (!n) return;
+  packMaskKernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(valid, n, bits);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+}
+void launchUnpackMask(cudaStream_t stream, const uint32_t* bits, size_t n, uint8_t* valid) {
+  if (!n) return;
+  unpackMaskKernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(bits, n, valid);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+}
+void launchKnnMergeShards(cudaStream_t stream, const double* dist, const int64_t* idx, int W, size_t Q, int k, int64_t* outIdx, double* outDist) {
+  if (!Q || k <= 0) return;
+  if (W < 1 || W > 16) throw std::invalid_argument("knn shard merge: 1..16 shards");
+  knnMergeShardsKernel<<<(unsigned)((Q + 127) / 128), 128, 0, stream>>>(dist, (const long long*)idx, W, Q, k, (long long*)outIdx, outDist);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+}
+
+}  // namespace hppb200

@@ -64,10 +64,44 @@ class Roadmap:
 
     def __init__(self, backend, nq):
         self.b = backend
-        self.nodes = np.zeros((0, nq))
-        self.cc = []
+        # nodes and labels grow by doubling (a vstack per node is 48 MB of copying per insertion at 1 M nodes)
+        self._nodes = np.zeros((1024, nq))
+        self._cc = np.zeros(1024, np.int64)
+        self.n = 0
         self._edges, self._edge_set, self._blocks, self._set_upto = [], set(), [], 0
         self.next_cc = 1 << 20  # labels of components created by add_nodes (planners use small labels themselves)
+
+    @property
+    def nodes(self):
+        return self._nodes[:self.n]
+
+    @property
+    def cc(self):
+        """connected-component label per node (numpy view)"""
+        return self._cc[:self.n]
+
+    @cc.setter
+    def cc(self, labels):
+        labels = np.asarray(labels, np.int64)
+        assert len(labels) == self.n
+        self._cc[:self.n] = labels
+
+    def _reserve(self, extra):
+        need = self.n + extra
+        if need > len(self._cc):
+            cap = max(need, 2 * len(self._cc))
+            nodes, cc = np.zeros((cap, self._nodes.shape[1])), np.zeros(cap, np.int64)
+            nodes[:self.n], cc[:self.n] = self._nodes[:self.n], self._cc[:self.n]
+            self._nodes, self._cc = nodes, cc
+
+    def extend(self, qs, ccs):
+        """bulk append of nodes with given labels (pre-filled roadmaps), no duplicate check"""
+        qs = np.asarray(qs, np.float64).reshape(-1, self._nodes.shape[1])
+        self._reserve(len(qs))
+        self._nodes[self.n:self.n + len(qs)] = qs
+        self._cc[self.n:self.n + len(qs)] = np.asarray(ccs, np.int64)
+        self.n += len(qs)
+        self.b.append_many(qs, np.asarray(ccs, np.int32))
 
     @property
     def edges(self):
@@ -93,10 +127,12 @@ class Roadmap:
             i, _ = self.b.nearest(q.reshape(1, -1), -1)
             if np.array_equal(self.nodes[i[0]], q):
                 return int(i[0])
-        self.nodes = np.vstack([self.nodes, q.reshape(1, -1)])
-        self.cc.append(cc)
+        self._reserve(1)
+        self._nodes[self.n] = q
+        self._cc[self.n] = cc
+        self.n += 1
         self.b.append(q, cc)
-        return len(self.cc) - 1
+        return self.n - 1
 
     def add_nodes(self, qs):
         """Roadmap::addNode for a batch of NEW configurations (each its own connected component): one append; a
@@ -114,8 +150,10 @@ class Roadmap:
         if fresh:
             ccs = list(range(self.next_cc, self.next_cc + len(fresh)))
             self.next_cc += len(fresh)
-            self.nodes = np.vstack([self.nodes, np.asarray(fresh)])
-            self.cc.extend(ccs)
+            self._reserve(len(fresh))
+            self._nodes[self.n:self.n + len(fresh)] = np.asarray(fresh)
+            self._cc[self.n:self.n + len(fresh)] = ccs
+            self.n += len(fresh)
             self.b.append_many(np.asarray(fresh), ccs)
         return out
 
@@ -157,7 +195,7 @@ class Roadmap:
         for x in rep.tolist():
             final[x] = root(x)
         new_cc = cc[final[rep_of]]
-        self.cc = new_cc.tolist()
+        self.cc = new_cc
         self.b.set_labels(new_cc.astype(np.int32))
 
     def has_edge(self, a, b):
@@ -167,11 +205,11 @@ class Roadmap:
         self.edges.append((a, b))
         ca, cb = self.cc[a], self.cc[b]
         if ca != cb:  # ConnectedComponent::merge: the second component joins the first
-            self.cc = [ca if c == cb else c for c in self.cc]
-            self.b.relabel(cb, ca)
+            self.cc[self.cc == cb] = ca
+            self.b.relabel(int(cb), int(ca))
 
     def add_node_and_edge(self, near, q):
-        n = self.add_node(q, self.cc[near])
+        n = self.add_node(q, int(self.cc[near]))
         self.add_edge(near, n)
         return n
 

@@ -88,6 +88,50 @@ def all_gather_topk(local_idx, local_dist, node_offset, k, group=None):
     gd = torch.empty((world * nq,) + tuple(ld.shape[1:]), dtype=torch.float64, device=ld.device)
     dist.all_gather_into_tensor(gi, li.contiguous(), group=group)  # rank-major concatenation along dim 0
     dist.all_gather_into_tensor(gd, ld.contiguous(), group=group)
+    if gi.is_cuda:  # merge on the device (knnMergeShardsKernel): results stay in HBM
+        return merge_topk_device(gi.view(world, nq, -1), gd.view(world, nq, -1), k)
     gi = gi.view((world, nq) + tuple(li.shape[1:])).cpu().numpy()
     gd = gd.view((world, nq) + tuple(ld.shape[1:])).cpu().numpy()
     return merge_topk([gd[r] for r in range(world)], [gi[r] for r in range(world)], k)
+
+
+def merge_topk_device(gi, gd, k):
+    """gi / gd: CUDA tensors [world][nqueries][k] (global indices, -1 padded; distances), every list nearest first.
+    Returns CUDA tensors (idx [nqueries][k] int64, dist [nqueries][k] float64): hppb200_knn_merge_shards on torch's
+    current stream."""
+    import ctypes as C
+    import torch
+    from . import lib, _check
+    world, nq, kk = gi.shape
+    assert kk == k and gi.is_contiguous() and gd.is_contiguous()
+    out_i = torch.empty((nq, k), dtype=torch.int64, device=gi.device)
+    out_d = torch.empty((nq, k), dtype=torch.float64, device=gi.device)
+    stream = torch.cuda.current_stream(gi.device).cuda_stream
+    _check(lib().hppb200_knn_merge_shards(C.c_void_p(stream), C.c_void_p(gd.data_ptr()), C.c_void_p(gi.data_ptr()), C.c_int(world),
+                                          C.c_size_t(nq), C.c_int(k), C.c_void_p(out_i.data_ptr()), C.c_void_p(out_d.data_ptr())))
+    return out_i, out_d
+
+
+def all_gather_mask_packed(valid, group=None):
+    """valid: CUDA uint8 tensor [n] (same n on every rank) -> uint8 [world * n] on every rank, moving n / 8 bytes per rank:
+    bit-pack (hppb200_pack_mask), all-gather of the words, unpack; all on torch's current stream."""
+    import ctypes as C
+    import torch
+    import torch.distributed as dist
+    from . import lib, _check
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    n = valid.shape[0]
+    words = (n + 31) // 32
+    bits = torch.empty(words, dtype=torch.int32, device=valid.device)
+    stream = torch.cuda.current_stream(valid.device).cuda_stream
+    _check(lib().hppb200_pack_mask(C.c_void_p(stream), C.c_void_p(valid.data_ptr()), C.c_size_t(n), C.c_void_p(bits.data_ptr())))
+    if world == 1:
+        allbits = bits
+    else:
+        allbits = torch.empty(world * words, dtype=torch.int32, device=valid.device)
+        dist.all_gather_into_tensor(allbits, bits, group=group)
+    out = torch.empty(world * n, dtype=torch.uint8, device=valid.device)
+    for r in range(world):  # (n need not be a multiple of 32: every rank's words start at r * words)
+        _check(lib().hppb200_unpack_mask(C.c_void_p(stream), C.c_void_p(allbits.data_ptr() + 4 * r * words), C.c_size_t(n),
+                                         C.c_void_p(out.data_ptr() + r * n)))
+    return out, allbits

@@ -322,6 +322,40 @@ int hppb200_validate_edge_chains(hppb200_workspace* ws, int method, double param
 /* Iteration cap per edge for continuous methods (default 1<<20). */
 int hppb200_workspace_set_max_iterations(hppb200_workspace* ws, uint32_t max_iter);
 
+/* ---- multi-GPU: a device list, sharded internally ------------------------ */
+/* Configurations and edges are independent units (the reference validates them from an OpenMP loop with pooled state,
+   tests/test-continuous-validation.cc:324-343; src/continuous-validation.cc:193-205): a handle owns one workspace and
+   one persistent host thread per device; every call splits the caller's HOST arrays into contiguous index ranges
+   [r n / N, (r + 1) n / N), validates them concurrently through the single-GPU host-pointer path and writes the results
+   into the caller's output arrays in place (that placement is the gather of the validity masks; no collective).
+   Same outputs as the single-GPU entry points.  devices == NULL / ndevices == 0: every visible device.
+   HPPB200_DEVICE_POINTERS is rejected.  One call at a time per handle (calls are serialised internally). */
+typedef struct hppb200_multi hppb200_multi;
+int hppb200_multi_create(const hppb200_model* m, const int* devices, int ndevices, hppb200_multi** out);
+void hppb200_multi_destroy(hppb200_multi* h);
+int hppb200_multi_num_devices(const hppb200_multi* h);
+/* borrowed: the workspace of shard `rank` (statistics, iteration cap); NULL if out of range */
+hppb200_workspace* hppb200_multi_workspace(hppb200_multi* h, int rank);
+int hppb200_multi_validate_configs(hppb200_multi* h, const double* q, size_t n, uint32_t flags,
+                                   uint8_t* valid, int32_t* first_pair, uint8_t* reason);
+int hppb200_multi_validate_edges(hppb200_multi* h, int method, double param, int reverse,
+                                 const double* q1, const double* q2, const double* L, size_t n,
+                                 uint32_t flags, uint8_t* valid, double* t_fail, double* t_last_valid,
+                                 int32_t* pair, uint8_t* reason);
+
+/* Exchange helpers of the one-process-per-GPU form (bench.py --gpus N, hpp-core_b200/sharding.py), where the path's only
+   cross-GPU data are validity masks and k-NN candidates.  DEVICE pointers, asynchronous on
+   `cuda_stream` (a cudaStream_t; the caller's NCCL collective goes on the same stream).
+   pack: valid [n] (0 / 1) -> bits [(n + 31) / 32], bit (i % 32) of word (i / 32), so that the all-gather moves n / 8
+   bytes per rank; unpack is the inverse.
+   merge: dist / idx [nshards][nqueries][k] = the all-gathered per-shard results of hppb200_knn_query with GLOBAL node
+   indices (-1 padded), each list nearest first -> the k nearest over all shards by the key (distance, node index),
+   i.e. the reference's tie rule (strict '<', src/nearest-neighbor/basic.cc:66,106) carried across shards. */
+int hppb200_pack_mask(void* cuda_stream, const uint8_t* valid, size_t n, uint32_t* bits);
+int hppb200_unpack_mask(void* cuda_stream, const uint32_t* bits, size_t n, uint8_t* valid);
+int hppb200_knn_merge_shards(void* cuda_stream, const double* dist, const int64_t* idx, int nshards,
+                             size_t nqueries, int k, int64_t* out_idx, double* out_dist);
+
 /* ---- nearest neighbour (WeighedDistance brute force) ------------------- */
 int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out);
 void hppb200_knn_destroy(hppb200_knn* nn);

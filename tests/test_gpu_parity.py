@@ -346,11 +346,11 @@ def test_kprm_star_batch_same_roadmap_as_oracle(pkg, ob):
     assert eb.nn.tc_stats()["used"] and eb.nn.tc_stats()["redone"] == 0
     assert sg == sc and gpu.shots == cpu.shots and gpu.validated_edges == cpu.validated_edges
     assert np.array_equal(gpu.roadmap.nodes, cpu.roadmap.nodes)
-    assert gpu.roadmap.edges == cpu.roadmap.edges and gpu.roadmap.cc == cpu.roadmap.cc
+    assert gpu.roadmap.edges == cpu.roadmap.edges and np.array_equal(gpu.roadmap.cc, cpu.roadmap.cc)
     assert len(gpu.roadmap.edges) > n
     # the device mirror received the final component labels (hppb200_knn_set_labels): component-restricted searches agree
     qs = pkg.uniform_configs(desc, 16, seed=77)
-    for lab in sorted(set(gpu.roadmap.cc))[:3]:
+    for lab in sorted(set(gpu.roadmap.cc.tolist()))[:3]:
         assert np.array_equal(eb.nearest(qs, lab)[0], cpu.b.nearest(qs, lab)[0])
 
 
@@ -674,7 +674,7 @@ def test_birrt_end_to_end_same_roadmap(pkg, ob, name, method, param, batch):
     sg, sc = gpu.solve(max_steps=300, batch=batch), cpu.solve(max_steps=300, batch=batch)
     assert sg == sc and gpu.solved() == cpu.solved()
     assert np.array_equal(gpu.roadmap.nodes, cpu.roadmap.nodes)
-    assert gpu.roadmap.edges == cpu.roadmap.edges and gpu.roadmap.cc == cpu.roadmap.cc
+    assert gpu.roadmap.edges == cpu.roadmap.edges and np.array_equal(gpu.roadmap.cc, cpu.roadmap.cc)
     assert len(gpu.roadmap.cc) > 4
     if gpu.solved():
         path = gpu.path()
@@ -745,3 +745,73 @@ def test_edge_chains_pathvector_recursion(pkg, eng, ur5, ur5_oracle, method, par
     assert r["valid"][empty].all() and (r["t_last_valid"][empty] == 0).all()
     with pytest.raises(pkg.EngineError):
         ws.validate_edge_chains(0, 0.05, q1, q2, L, cb)
+
+
+def test_multi_gpu_device_list_entry(pkg, eng, ur5, ur5_oracle):
+    """hppb200_multi_*: a device list sharded internally.  Three shards (on one GPU box all on device 0, which exercises the
+    same splitting / threading / placement; on a multi-GPU box every visible device too): same outputs as the
+    single-GPU entry points and the oracle, ragged sizes, errors reported with the device."""
+    m, ws = eng
+    ndev = pkg.lib().hppb200_device_count()
+    for devices in ([0, 0, 0], list(range(ndev)) if ndev > 1 else None):
+        mg = pkg.MultiGpu(m, devices)
+        assert mg.ndevices == (len(devices) if devices else ndev)
+        q = pkg.uniform_configs(ur5, 100003, seed=81) * 1.03
+        got = mg.validate_configs(q, check_bounds=True)
+        ref = ws.validate_configs(q, check_bounds=True)
+        for a, b in zip(got, ref):
+            assert np.array_equal(a, b)
+        sub = slice(0, 20000)
+        for a, b in zip(got, ur5_oracle.validate_configs(q[sub], check_bounds=True)):
+            assert np.array_equal(a[sub], b)
+        assert all(mg.shard_stats(r)["configs"] > 0 for r in range(mg.ndevices))
+        q1, q2, L = _edges(pkg, ur5, ur5_oracle, 5001, 82)
+        for meth, par in ((1, 1e-3), (2, 0.0), (0, 0.05)):
+            r = mg.validate_edges(meth, par, q1, q2, L, reverse=(meth == 2))
+            e = ur5_oracle.validate_edges(meth, par, q1, q2, L, reverse=(meth == 2))
+            for k in ("valid", "reason", "pair", "t_last_valid"):
+                assert np.array_equal(r[k], e[k]), (meth, k)
+            assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+        v, f, r = mg.validate_configs(q[:2])  # fewer units than shards
+        assert np.array_equal(v, ref[0][:2])
+        with pytest.raises(RuntimeError, match="device"):
+            mg.validate_edges(1, 0.0, q1, q2, L)  # Progressive needs tol > 0: the shard's error comes back with its device
+    with pytest.raises(ValueError):
+        pkg.MultiGpu(m, [99])
+
+
+def test_exchange_helpers_pack_mask_and_knn_shard_merge(pkg, eng, ur5):
+    """Device-side helpers of the sharded form: bit-packed validity masks (n not a multiple of 32) and the W-way merge of
+    per-shard k-NN candidates against the unsharded query, duplicates across shards included (the earlier GLOBAL index wins)."""
+    import torch
+    from hpp_core_b200 import sharding as sh
+    m, ws = eng
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(3)
+    v = torch.from_numpy((rng.random(100003) < 0.4).astype(np.uint8)).to(dev)
+    out, bits = sh.all_gather_mask_packed(v)
+    assert torch.equal(out, v) and bits.numel() == (100003 + 31) // 32
+    nodes = pkg.uniform_configs(ur5, 40000, seed=91)
+    nodes[30000] = nodes[17]      # exact duplicates in different shards
+    nodes[39999] = nodes[25000]
+    qs = pkg.uniform_configs(ur5, 257, seed=92)
+    qs[0], qs[1] = nodes[17], nodes[25000]
+    whole = pkg.NearestNeighbor(m, 0)
+    whole.append(nodes)
+    for k in (1, 10, 33):
+        ri, rd = whole.query(qs, k)
+        W = 3
+        gi, gd = [], []
+        for b, e in sh.node_owner_ranges(len(nodes), W):
+            part = pkg.NearestNeighbor(m, 0)
+            part.append(nodes[b:e])
+            li, ld = part.query(qs, k)
+            li = np.where(li >= 0, li + b, li)
+            gi.append(li); gd.append(ld)
+        gi = torch.from_numpy(np.stack(gi)).to(dev).contiguous()
+        gd = torch.from_numpy(np.stack(gd)).to(dev).contiguous()
+        oi, od = sh.merge_topk_device(gi, gd, k)
+        torch.cuda.synchronize()
+        assert np.array_equal(oi.cpu().numpy(), ri) and np.array_equal(od.cpu().numpy(), rd)
+        hi, hd = sh.merge_topk([x for x in gd.cpu().numpy()], [x for x in gi.cpu().numpy()], k)
+        assert np.array_equal(hi, ri) and np.array_equal(hd, rd)

@@ -18,7 +18,7 @@ def test_kprm_star_batch_equals_sequential(pkg, ob, ur5, n, method, param):
     assert ss == sb and seq.shots == bat.shots
     assert np.array_equal(seq.roadmap.nodes, bat.roadmap.nodes) and len(seq.roadmap.cc) == n
     assert seq.roadmap.edges == bat.roadmap.edges and len(seq.roadmap.edges) > n
-    assert seq.roadmap.cc == bat.roadmap.cc
+    assert np.array_equal(seq.roadmap.cc, bat.roadmap.cc)
     # every node is collision free, every edge was validated from its first end
     assert o.validate_configs(bat.roadmap.nodes, check_bounds=True)[0].all()
     e = np.array(bat.roadmap.edges)
