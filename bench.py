@@ -222,7 +222,8 @@ def run_b200(args):
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         # NCCL's own log (rank counts, NVLS/ring choice) goes to stderr so that stdout stays the one JSON line
-        os.environ.setdefault("NCCL_DEBUG", "INFO")
+        # (the image presets NCCL_DEBUG=VERSION: override it, HPPB200_NCCL_DEBUG chooses another level)
+        os.environ["NCCL_DEBUG"] = os.environ.get("HPPB200_NCCL_DEBUG", "INFO")
         os.environ.setdefault("NCCL_DEBUG_SUBSYS", "INIT")
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
@@ -248,11 +249,13 @@ def run_b200(args):
 
     from hpp_core_b200 import sharding as sh
     gathered = {}
+    bits_d = torch.empty((n + 31) // 32, dtype=torch.int32, device=dev)
+    allbits_d = torch.empty(world * ((n + 31) // 32), dtype=torch.int32, device=dev)
 
     def step_device():
         ws.validate_configs_ptr(q_dev.data_ptr(), n, valid_d.data_ptr(), first_d.data_ptr(), reason_d.data_ptr(), FLAGS_DEV)
         if world > 1:  # the path's only exchange: gather of the validity masks, bit-packed (1 bit per configuration)
-            gathered["valid_all"], _ = sh.all_gather_mask_packed(valid_d)
+            sh.all_gather_mask_packed(valid_d, unpack=False, bits=bits_d, allbits=allbits_d)
 
     def step_e2e():
         ws.validate_configs_ptr(q_host.data_ptr(), n, valid_h.data_ptr(), first_h.data_ptr(), reason_h.data_ptr(), 0)
@@ -296,8 +299,8 @@ def run_b200(args):
     e2e_value = world * n * args.steps / (e2e_ms * 1e-3)
     # identical results on both paths
     assert torch.equal(valid_h, valid_d.cpu()) and torch.equal(first_h, first_d.cpu())
-    if world > 1:  # the gathered mask holds this rank's flags at its place
-        assert torch.equal(gathered["valid_all"][rank * n:(rank + 1) * n], valid_d)
+    if world > 1:  # the gathered (packed) mask holds this rank's flags at its place
+        assert torch.equal(sh.unpack_mask(allbits_d, n, world)[rank * n:(rank + 1) * n], valid_d)
 
     # ---- N > 1: every rank validates its own shard of edges (Progressive), validity masks all-gathered ----
     edges_sharded = None
@@ -317,9 +320,9 @@ def run_b200(args):
             ws.validate_edges_ptr(pkg.METHOD_PROGRESSIVE, 1e-3, False, s1d.data_ptr(), s2d.data_ptr(), sLd.data_ptr(), ne,
                                   sv.data_ptr(), stf.data_ptr(), stl.data_ptr(), spr.data_ptr(), srs.data_ptr(), FLAGS_DEV)
             if world > 1:
-                gathered["sv_all"], _ = sh.all_gather_mask_packed(sv)
+                gathered["sv_bits"] = sh.all_gather_mask_packed(sv, unpack=False)[1]
         ms_s, _, _ = timed(shard_call, 3, 1)
-        sv_all = gathered.get("sv_all")
+        sv_all = sh.unpack_mask(gathered["sv_bits"], ne, world) if world > 1 else None
         edges_sharded = {"value": world * ne * 3 / (ms_s * 1e-3), "unit": "edges/s", "edges_per_gpu": ne, "param": 1e-3,
                          "method": "progressive", "ms_per_call": ms_s / 3,
                          "collective": "all_gather of bit-packed validity masks (NCCL, 1 bit per edge)" if world > 1 else "none",
@@ -369,9 +372,9 @@ def run_b200(args):
 
         def full_cfg():
             ws.validate_configs_ptr(qf.data_ptr(), nf, vf.data_ptr(), ff.data_ptr(), rf.data_ptr(), FLAGS_DEV)
-            gathered["vf_all"], _ = sh.all_gather_mask_packed(vf)
+            gathered["vf_bits"] = sh.all_gather_mask_packed(vf, unpack=False)[1]
         ms_fc, _, _ = timed(full_cfg, 3, 1)
-        vfrac = float(gathered["vf_all"].float().mean().item())
+        vfrac = float(sh.unpack_mask(gathered["vf_bits"], nf, world).float().mean().item())
         del qf, ff, rf
         cfge = pkg.uniform_configs(desc, 2 * nef, seed=SEED + 8, offset=rank * 2 * nef)
         f1 = torch.from_numpy(np.ascontiguousarray(cfge[0::2])).to(dev)
@@ -386,13 +389,13 @@ def run_b200(args):
         def full_edges():
             ws.validate_edges_ptr(pkg.METHOD_PROGRESSIVE, 1e-3, False, f1.data_ptr(), f2.data_ptr(), fL.data_ptr(), nef, fv.data_ptr(),
                                   ftf.data_ptr(), ftl.data_ptr(), fpr.data_ptr(), frs.data_ptr(), FLAGS_DEV)
-            gathered["fv_all"], _ = sh.all_gather_mask_packed(fv)
+            gathered["fv_bits"] = sh.all_gather_mask_packed(fv, unpack=False)[1]
         ms_fe, _, _ = timed(full_edges, 2, 1)
         full = {"configs": {"value": world * nf * 3 / (ms_fc * 1e-3), "unit": "configs/s", "configs_per_gpu_per_call": nf,
                             "total_configs": world * nf, "ms_per_call": ms_fc / 3, "valid_frac_all_ranks": vfrac},
                 "edges": {"value": world * nef * 2 / (ms_fe * 1e-3), "unit": "edges/s", "method": "progressive", "param": 1e-3,
                           "edges_per_gpu_per_call": nef, "total_edges": world * nef, "ms_per_call": ms_fe / 2,
-                          "valid_frac_all_ranks": float(gathered["fv_all"].float().mean().item())},
+                          "valid_frac_all_ranks": float(sh.unpack_mask(gathered["fv_bits"], nef, world).float().mean().item())},
                 "collective": "all_gather of bit-packed validity masks (NCCL)" if world > 1 else "none",
                 "note": "BASELINE configs[4]: 100 M configurations / 10 M edges over 8 GPUs; every rank validates its share in ONE call"}
         del f1, f2, fL, fv, ftf, ftl, fpr, frs, vf

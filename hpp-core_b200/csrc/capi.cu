@@ -425,16 +425,36 @@ int hppb200_validate_edge_chains(hppb200_workspace* wsp, int method, double para
   });
 }
 
+// The helpers below launch on a caller-provided stream: the launch needs the stream's device current, whatever the calling
+// thread's current device is (another library call may have changed it): take it from the data pointer, restore after.
+namespace {
+struct DeviceOfPointer {
+  int prev = -1;
+  explicit DeviceOfPointer(const void* p) {
+    cudaPointerAttributes a{};
+    HPPB200_CUDA_CHECK(cudaGetDevice(&prev));
+    HPPB200_CUDA_CHECK(cudaPointerGetAttributes(&a, p));
+    if (a.type != cudaMemoryTypeDevice && a.type != cudaMemoryTypeManaged) throw std::invalid_argument("device pointers expected");
+    if (a.device != prev) HPPB200_CUDA_CHECK(cudaSetDevice(a.device)); else prev = -1;
+  }
+  ~DeviceOfPointer() { if (prev >= 0) cudaSetDevice(prev); }
+};
+}  // namespace
+
 // ---- exchange helpers of the sharded form (device pointers, asynchronous on `cuda_stream`) ----
 int hppb200_pack_mask(void* cuda_stream, const uint8_t* valid, size_t n, uint32_t* bits) {
   return guarded([&] {
     if (n && (!valid || !bits)) throw std::invalid_argument("null argument");
+    if (!n) return;
+    DeviceOfPointer guard(valid);
     launchPackMask((cudaStream_t)cuda_stream, valid, n, bits);
   });
 }
 int hppb200_unpack_mask(void* cuda_stream, const uint32_t* bits, size_t n, uint8_t* valid) {
   return guarded([&] {
     if (n && (!valid || !bits)) throw std::invalid_argument("null argument");
+    if (!n) return;
+    DeviceOfPointer guard(valid);
     launchUnpackMask((cudaStream_t)cuda_stream, bits, n, valid);
   });
 }
@@ -442,6 +462,8 @@ int hppb200_knn_merge_shards(void* cuda_stream, const double* dist, const int64_
                              int64_t* out_idx, double* out_dist) {
   return guarded([&] {
     if (nqueries && (!dist || !idx || !out_idx || !out_dist)) throw std::invalid_argument("null argument");
+    if (!nqueries) return;
+    DeviceOfPointer guard(dist);
     launchKnnMergeShards((cudaStream_t)cuda_stream, dist, idx, nshards, nqueries, k, out_idx, out_dist);
   });
 }

@@ -117,6 +117,11 @@ int hppb200_multi_create(const hppb200_model* m, const int* devices, int ndevice
   if (count == 0) { hppb200::setLastError("no CUDA device visible: the engine has no CPU fallback"); return HPPB200_ERR_CUDA; }
   std::unique_ptr<hppb200_multi> h(new hppb200_multi);
   const int N = ndevices > 0 ? ndevices : count;  // ndevices == 0: every visible device
+  struct RestoreDevice {  // workspace creation makes its device current: leave the caller's as it was
+    int prev = 0;
+    RestoreDevice() { cudaGetDevice(&prev); }
+    ~RestoreDevice() { cudaSetDevice(prev); }
+  } restore;
   for (int r = 0; r < N; ++r) {
     std::unique_ptr<Worker> w(new Worker);
     w->device = ndevices > 0 ? devices[r] : r;

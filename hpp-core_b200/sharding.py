@@ -112,9 +112,11 @@ def merge_topk_device(gi, gd, k):
     return out_i, out_d
 
 
-def all_gather_mask_packed(valid, group=None):
-    """valid: CUDA uint8 tensor [n] (same n on every rank) -> uint8 [world * n] on every rank, moving n / 8 bytes per rank:
-    bit-pack (hppb200_pack_mask), all-gather of the words, unpack; all on torch's current stream."""
+def all_gather_mask_packed(valid, group=None, unpack=True, bits=None, allbits=None):
+    """valid: CUDA uint8 tensor [n] (same n on every rank).  Bit-packs it (hppb200_pack_mask), all-gathers the words
+    (n / 8 bytes per rank instead of n) and, if `unpack`, expands them to uint8 [world * n]; all on torch's current stream.
+    Returns (mask or None, allbits int32 [world * ceil(n / 32)]); rank r's words start at r * ceil(n / 32).
+    `bits` / `allbits`: optional preallocated int32 buffers (a timed loop should not allocate)."""
     import ctypes as C
     import torch
     import torch.distributed as dist
@@ -122,16 +124,30 @@ def all_gather_mask_packed(valid, group=None):
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     n = valid.shape[0]
     words = (n + 31) // 32
-    bits = torch.empty(words, dtype=torch.int32, device=valid.device)
+    if bits is None:
+        bits = torch.empty(words, dtype=torch.int32, device=valid.device)
     stream = torch.cuda.current_stream(valid.device).cuda_stream
     _check(lib().hppb200_pack_mask(C.c_void_p(stream), C.c_void_p(valid.data_ptr()), C.c_size_t(n), C.c_void_p(bits.data_ptr())))
     if world == 1:
         allbits = bits
     else:
-        allbits = torch.empty(world * words, dtype=torch.int32, device=valid.device)
+        if allbits is None:
+            allbits = torch.empty(world * words, dtype=torch.int32, device=valid.device)
         dist.all_gather_into_tensor(allbits, bits, group=group)
-    out = torch.empty(world * n, dtype=torch.uint8, device=valid.device)
+    if not unpack:
+        return None, allbits
+    return unpack_mask(allbits, n, world), allbits
+
+
+def unpack_mask(allbits, n, world):
+    """inverse of the packing above: uint8 [world * n]"""
+    import ctypes as C
+    import torch
+    from . import lib, _check
+    words = (n + 31) // 32
+    out = torch.empty(world * n, dtype=torch.uint8, device=allbits.device)
+    stream = torch.cuda.current_stream(allbits.device).cuda_stream
     for r in range(world):  # (n need not be a multiple of 32: every rank's words start at r * words)
         _check(lib().hppb200_unpack_mask(C.c_void_p(stream), C.c_void_p(allbits.data_ptr() + 4 * r * words), C.c_size_t(n),
                                          C.c_void_p(out.data_ptr() + r * n)))
-    return out, allbits
+    return out
