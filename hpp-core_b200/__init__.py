@@ -49,7 +49,8 @@ ABI_SYMBOLS = [
     "hppb200_model_get_body_pairs", "hppb200_model_num_body_geom_pairs", "hppb200_model_get_body_geom_pairs",
     "hppb200_model_num_coefficients", "hppb200_model_get_coefficients", "hppb200_model_get_body_radii",
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
-    "hppb200_validate_configs", "hppb200_validate_configs_noalloc", "hppb200_geometry_placements", "hppb200_pair_distances",
+    "hppb200_validate_configs", "hppb200_validate_configs_noalloc", "hppb200_geometry_placements", "hppb200_pair_distances", "hppb200_all_collisions", "hppb200_model_num_distance_pairs",
+    "hppb200_distance_between_objects",
     "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edge_chains", "hppb200_workspace_set_max_iterations",
     "hppb200_multi_create", "hppb200_multi_destroy", "hppb200_multi_num_devices", "hppb200_multi_workspace",
     "hppb200_multi_validate_configs", "hppb200_multi_validate_edges",
@@ -226,6 +227,26 @@ class Workspace:
         npairs = lib().hppb200_model_num_config_pairs(self.model.h)
         out = np.zeros((q.shape[0], npairs))
         _check(lib().hppb200_pair_distances(self.h, _p(q, _dp), C.c_size_t(q.shape[0]), C.c_uint32(0), _p(out, _dp)))
+        return out
+
+    def all_collisions(self, q):
+        """CollisionValidation with computeAllContacts: (valid, first, list of colliding pair indices per configuration)"""
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.model.nq)
+        n = q.shape[0]
+        npairs = lib().hppb200_model_num_config_pairs(self.model.h)
+        words = (npairs + 31) // 32
+        valid, first, count = np.zeros(n, np.uint8), np.full(n, -1, np.int32), np.zeros(n, np.int32)
+        mask = np.zeros((n, words), np.uint32)
+        _check(lib().hppb200_all_collisions(self.h, _p(q, _dp), C.c_size_t(n), C.c_uint32(0), _p(valid, _u8p), _p(first, _ip),
+                                            mask.ctypes.data_as(C.c_void_p), _p(count, _ip)))
+        bits = np.unpackbits(mask.view(np.uint8), axis=1, bitorder="little")[:, :npairs]
+        return valid, first, [np.nonzero(b)[0] for b in bits], count
+
+    def distance_between_objects(self, q):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.model.nq)
+        per = lib().hppb200_model_num_distance_pairs(self.model.h)
+        out = np.zeros((q.shape[0], per))
+        _check(lib().hppb200_distance_between_objects(self.h, _p(q, _dp), C.c_size_t(q.shape[0]), C.c_uint32(0), _p(out, _dp)))
         return out
 
     def straight_lengths(self, q1, q2):

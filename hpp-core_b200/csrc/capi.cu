@@ -290,6 +290,49 @@ int hppb200_pair_distances(hppb200_workspace* wsp, const double* q, size_t n, ui
   });
 }
 
+int hppb200_all_collisions(hppb200_workspace* wsp, const double* q, size_t n, uint32_t flags, uint8_t* valid, int32_t* first_pair,
+                           uint32_t* mask, int32_t* count) {
+  return guarded([&] {
+    if (!wsp || (n && (!q || !valid || !mask))) throw std::invalid_argument("null argument");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq, words = (ws->model->cPairs.size() + 31) / 32;
+    if (flags & HPPB200_DEVICE_POINTERS) {
+      launchAllCollisions(ws, q, n, valid, first_pair, mask, count);
+      HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+      return;
+    }
+    ws->d_q.reserve(n * nq); ws->d_valid.reserve(n); ws->d_pair.reserve(n); ws->d_mask.reserve(n * words); ws->d_ncoll.reserve(n);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchAllCollisions(ws, ws->d_q.p, n, ws->d_valid.p, ws->d_pair.p, ws->d_mask.p, ws->d_ncoll.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_valid.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    if (first_pair) HPPB200_CUDA_CHECK(cudaMemcpyAsync(first_pair, ws->d_pair.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(mask, ws->d_mask.p, n * words * sizeof(uint32_t), cudaMemcpyDeviceToHost, ws->stream));
+    if (count) HPPB200_CUDA_CHECK(cudaMemcpyAsync(count, ws->d_ncoll.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  });
+}
+
+int hppb200_model_num_distance_pairs(const hppb200_model* m) { return (int)m->impl.dboPairs.size(); }
+int hppb200_distance_between_objects(hppb200_workspace* wsp, const double* q, size_t n, uint32_t flags, double* dist) {
+  return guarded([&] {
+    if (!wsp || (n && (!q || !dist))) throw std::invalid_argument("null argument");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq, per = ws->model->dboPairs.size();
+    if (flags & HPPB200_DEVICE_POINTERS) {
+      launchDistanceBetweenObjects(ws, q, n, dist);
+      HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+      return;
+    }
+    ws->d_q.reserve(n * nq); ws->d_tfail.reserve(n * per + 1);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchDistanceBetweenObjects(ws, ws->d_q.p, n, ws->d_tfail.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(dist, ws->d_tfail.p, n * per * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  });
+}
+
 int hppb200_straight_lengths(hppb200_workspace* wsp, const double* q1, const double* q2, size_t n, uint32_t flags,
                              double* L) {
   return guarded([&] {

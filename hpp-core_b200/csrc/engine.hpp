@@ -95,6 +95,7 @@ struct Model {
   std::vector<DevPair> cPairs;        // first/second as in cPairs_ (NOT canonicalised); pPairs_ appended when checked
   std::vector<DevPair> pPairs, dPairs;  // parameterized / disabled pairs (ObstacleUser::filterCollisionPairs)
   int nParameterized = 0;             // trailing entries of cPairs that are pPairs_
+  std::vector<DevPair> dboPairs;      // DistanceBetweenObjects pairs (inner object, obstacle), canonical order, margin 0
   std::vector<BodyPairHost> bodyPairs;
   // device
   std::vector<unsigned char> blob;
@@ -166,6 +167,10 @@ struct Workspace {
   DeviceBuffer<unsigned long long> d_count;
   DeviceBuffer<int32_t> d_pair, d_pair_int, d_chain, d_cpair, d_cbad;
   DeviceBuffer<uint8_t> d_cvalid, d_creason;
+  DeviceBuffer<DevPair> d_dbo;
+  bool dboUploaded = false;
+  DeviceBuffer<uint32_t> d_mask;
+  DeviceBuffer<int32_t> d_ncoll;
   DeviceBuffer<double> d_ctfail, d_ctlast;
   DeviceBuffer<unsigned long long> d_jobs;
   unsigned long long last_jobs = 0;
@@ -189,6 +194,8 @@ void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, ui
                                   uint8_t* d_reason);
 void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint32_t flags, uint8_t* h_valid, int32_t* h_first,
                                uint8_t* h_reason);
+void launchAllCollisions(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint32_t* d_mask, int32_t* d_count);
+void launchDistanceBetweenObjects(Workspace* ws, const double* d_q, size_t n, double* d_out);
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg);
 void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_dist);
 void launchStraightLengths(Workspace* ws, const double* d_q1, const double* d_q2, size_t n, double* d_L);

@@ -634,6 +634,73 @@ void launchPairDistances(Workspace* ws, const double* d_q, size_t n, double* d_d
 }
 
 
+// ------------------------------------------------------------------------------------------------
+// CollisionValidation with computeAllContacts (reference src/collision-validation.cc:72-89): the report lists the first
+// colliding pair and every LATER colliding pair of the same table (cPairs_, or pPairs_ when the first hit is there).
+// One thread per configuration over the distances of MODE_DISTANCES (distance - margin of every pair in table order).
+__global__ void allCollisionsKernel(const double* __restrict__ dist, size_t n, int npairs, int nparam, uint8_t* valid, int32_t* first,
+                                    uint32_t* mask, int32_t* count) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int words = (npairs + 31) / 32, nc = npairs - nparam;
+  const double* d = dist + i * (size_t)npairs;
+  int f = -1;
+  for (int p = 0; p < npairs && f < 0; ++p)
+    if (d[p] <= HPPB200_COLLISION_THRESHOLD) f = p;
+  uint32_t* m = mask + i * (size_t)words;
+  for (int w = 0; w < words; ++w) m[w] = 0u;
+  int c = 0;
+  if (f >= 0) {
+    const int end = f < nc ? nc : npairs;  // the table the first hit is in
+    for (int p = f; p < end; ++p)
+      if (d[p] <= HPPB200_COLLISION_THRESHOLD) { m[p >> 5] |= 1u << (p & 31); ++c; }
+  }
+  valid[i] = f < 0 ? 1 : 0;
+  if (first) first[i] = f;
+  if (count) count[i] = c;
+}
+
+void launchAllCollisions(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint32_t* d_mask, int32_t* d_count) {
+  if (n == 0) return;
+  const int np = (int)ws->model->cPairs.size();
+  ws->d_scratch.reserve((size_t)np * n);
+  launchConfigKernel(ws, d_q, n, 0, MODE_DISTANCES, nullptr, nullptr, nullptr, ws->d_scratch.p);
+  allCollisionsKernel<<<(unsigned)((n + 127) / 128), 128, 0, ws->stream>>>(ws->d_scratch.p, n, np, ws->model->nParameterized, d_valid, d_first,
+                                                                          d_mask, d_count);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 1;
+}
+
+// DistanceBetweenObjects::computeDistances (reference src/distance-between-objects.cc:62-77): the distance (no security
+// margin) of every (inner object of a body, obstacle) pair, obstacle-major in addObstacle order (:41-53).
+// Thread per (configuration, pair) over the placements of MODE_PLACEMENTS.
+__global__ void distancePairsKernel(ModelView mv, const DevPair* __restrict__ pairs, int npairs, const double* __restrict__ oMg, size_t n,
+                                    double* __restrict__ out) {
+  const Tables T = makeTables(mv.blob, mv);
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= n * (size_t)npairs) return;
+  const size_t i = idx / (size_t)npairs;
+  const int p = (int)(idx - i * (size_t)npairs);
+  GjkCounters cnt = {0u, 0u, 0u};
+  out[idx] = pairLowerBound(T, pairs[p], oMg + i * (size_t)mv.ngeoms * 12, 1, mv.vertices, cnt);
+}
+
+void launchDistanceBetweenObjects(Workspace* ws, const double* d_q, size_t n, double* d_out) {
+  const std::vector<DevPair>& pairs = ws->model->dboPairs;
+  if (n == 0 || pairs.empty()) return;
+  if (!ws->dboUploaded) {
+    ws->d_dbo.reserve(pairs.size());
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_dbo.p, pairs.data(), pairs.size() * sizeof(DevPair), cudaMemcpyHostToDevice, ws->stream));
+    ws->dboUploaded = true;
+  }
+  ws->d_scratch.reserve((size_t)ws->view.ngeoms * 12 * n);
+  launchConfigKernel(ws, d_q, n, 0, MODE_PLACEMENTS, nullptr, nullptr, nullptr, ws->d_scratch.p);
+  const size_t total = n * pairs.size();
+  distancePairsKernel<<<(unsigned)((total + 127) / 128), 128, 0, ws->stream>>>(ws->view, ws->d_dbo.p, (int)pairs.size(), ws->d_scratch.p, n, d_out);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 1;
+}
+
 // FP64 FMA peak: 8 independent DFMA chains per thread, 4096 steps, enough CTAs to fill the chip.
 __global__ void __launch_bounds__(256) fp64PeakKernel(double* out, double a, double b, int iters) {
   double x0 = threadIdx.x, x1 = x0 + 1, x2 = x0 + 2, x3 = x0 + 3, x4 = x0 + 4, x5 = x0 + 5, x6 = x0 + 6, x7 = x0 + 7;

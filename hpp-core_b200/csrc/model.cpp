@@ -405,6 +405,12 @@ void Model::buildBlob() {
   std::vector<DevBodyPair> bps;
   std::vector<DevCoef> cf, rcf;
   for (const DevPair& p : cPairs) cp.push_back(canonical(p));
+  // DistanceBetweenObjects::addObstacle (src/distance-between-objects.cc:41-53): obstacle-major, joints in order, inner objects
+  dboPairs.clear();
+  for (int o = 0; o < (int)obstacles.size(); ++o)
+    for (int j = 1; j <= njoints; ++j)
+      for (int g = 0; g < (int)geoms.size(); ++g)
+        if (geoms[g].joint == j) dboPairs.push_back(canonical(DevPair{g, -(o + 1), 0, 0, 0.0, 0.0}));
   for (const BodyPairHost& b : bodyPairs) {
     DevBodyPair B{};
     B.joint_a = b.joint_a;

@@ -284,6 +284,23 @@ int hppb200_geometry_placements(hppb200_workspace* ws, const double* q, size_t n
 int hppb200_pair_distances(hppb200_workspace* ws, const double* q, size_t n,
                            uint32_t flags, double* dist);
 
+/* CollisionValidation with computeAllContacts (reference src/collision-validation.cc:72-89,
+   include/hpp/core/collision-validation.hh:63-65): what AllCollisionsValidationReport::collisionReports lists, per
+   configuration: mask [n][(npairs + 31) / 32], bit p set iff pair p of the configuration-pair table
+   (hppb200_model_get_config_pairs) collides AND lies in the table (cPairs_ / pPairs_) of the first colliding pair, at
+   or after it; count [n] = number of set bits; valid / first_pair as hppb200_validate_configs (collision only). */
+int hppb200_all_collisions(hppb200_workspace* ws, const double* q, size_t n, uint32_t flags,
+                           uint8_t* valid, int32_t* first_pair, uint32_t* mask, int32_t* count);
+
+/* DistanceBetweenObjects::computeDistances (reference src/distance-between-objects.cc:41-77): for every configuration the
+   distance, without security margin, between every inner object of every moving body and every obstacle:
+   dist [n][npairs], pairs obstacle-major in addObstacle order, then joints, then the joint's inner objects
+   (hppb200_model_num_distance_pairs of them).  Separated shapes: the exact separation (what
+   coal::DistanceResult::min_distance holds); overlapping shapes: core distance 0 minus the inflation radii (no EPA
+   penetration depth). */
+int hppb200_model_num_distance_pairs(const hppb200_model* m);
+int hppb200_distance_between_objects(hppb200_workspace* ws, const double* q, size_t n, uint32_t flags, double* dist);
+
 /* ---- edge (StraightPath) validation ------------------------------------ */
 /* L[i] = WeighedDistance(q1[i], q2[i]) (steeringMethod::Straight). */
 int hppb200_straight_lengths(hppb200_workspace* ws, const double* q1,

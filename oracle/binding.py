@@ -113,6 +113,24 @@ class Oracle:
         lib().oracle_pair_distances(self.h, _p(q, dp), C.c_size_t(q.shape[0]), _p(out, dp))
         return out
 
+    def all_collisions(self, q):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.nq)
+        n = q.shape[0]
+        npairs = lib().oracle_num_config_pairs(self.h)
+        words = (npairs + 31) // 32
+        valid, first, count = np.zeros(n, np.uint8), np.zeros(n, np.int32), np.zeros(n, np.int32)
+        mask = np.zeros((n, words), np.uint32)
+        lib().oracle_all_collisions(self.h, _p(q, dp), C.c_size_t(n), _p(valid, u8p), _p(first, ip), mask.ctypes.data_as(C.c_void_p), _p(count, ip))
+        bits = np.unpackbits(mask.view(np.uint8), axis=1, bitorder="little")[:, :npairs]
+        return valid, first, [np.nonzero(b)[0] for b in bits], count
+
+    def distance_between_objects(self, q):
+        q = np.ascontiguousarray(q, np.float64).reshape(-1, self.nq)
+        per = lib().oracle_num_distance_pairs(self.h)
+        out = np.zeros((q.shape[0], per))
+        lib().oracle_distance_between_objects(self.h, _p(q, dp), C.c_size_t(q.shape[0]), _p(out, dp))
+        return out
+
     def validate_configs(self, q, check_bounds=False, nthreads=0):
         q = np.ascontiguousarray(q, np.float64).reshape(-1, self.nq)
         n = q.shape[0]

@@ -114,6 +114,58 @@ void oracle_pair_distances(OracleHandle* h, const double* q, size_t n, double* d
       dist[i * cp.size() + p] = collidePair(d, data, cp[p], nullptr).distanceLowerBound;
   }
 }
+// CollisionValidation::validate with computeAllContacts_ (src/collision-validation.cc:72-89): the first colliding pair,
+// then every remaining pair of the same table that collides.  mask over the table cPairs ++ pPairs.
+void oracle_all_collisions(OracleHandle* h, const double* q, size_t n, uint8_t* valid, int32_t* first, uint32_t* mask, int32_t* count) {
+  const Device& d = *h->dev;
+  ObstacleUser ou(d);
+  const size_t np = ou.checkedPairs().size(), words = (np + 31) / 32;
+  DeviceData data;
+  for (size_t i = 0; i < n; ++i) {
+    d.forwardKinematics(q + i * d.nq, data);
+    for (size_t w = 0; w < words; ++w) mask[i * words + w] = 0u;
+    const std::vector<CollisionPair>* pairs = &ou.cPairs;
+    size_t base = 0, iPair = 0;
+    bool collide = ou.collide(ou.cPairs, data, iPair, nullptr);
+    if (!collide && d.checkParameterized) {
+      collide = ou.collide(ou.pPairs, data, iPair, nullptr);
+      pairs = &ou.pPairs;
+      base = ou.cPairs.size();
+    }
+    int c = 0;
+    if (collide) {
+      first[i] = (int32_t)(base + iPair);
+      mask[i * words + ((base + iPair) >> 5)] |= 1u << ((base + iPair) & 31);
+      ++c;
+      for (++iPair; iPair < pairs->size(); ++iPair)
+        if (collidePair(d, data, (*pairs)[iPair], nullptr).collision) { mask[i * words + ((base + iPair) >> 5)] |= 1u << ((base + iPair) & 31); ++c; }
+    } else first[i] = -1;
+    valid[i] = collide ? 0 : 1;
+    count[i] = c;
+  }
+}
+// DistanceBetweenObjects (src/distance-between-objects.cc:41-77): obstacle-major (inner object, obstacle) pairs, plain distance
+int oracle_num_distance_pairs(OracleHandle* h) {
+  const Device& d = *h->dev;
+  int c = 0;
+  for (size_t o = 0; o < d.obstacles.size(); ++o)
+    for (int j = 1; j <= d.njoints(); ++j)
+      for (size_t g = 0; g < d.geoms.size(); ++g) c += d.geoms[g].joint == j;
+  return c;
+}
+void oracle_distance_between_objects(OracleHandle* h, const double* q, size_t n, double* dist) {
+  const Device& d = *h->dev;
+  const size_t per = (size_t)oracle_num_distance_pairs(h);
+  DeviceData data;
+  for (size_t i = 0; i < n; ++i) {
+    d.forwardKinematics(q + i * d.nq, data);
+    size_t k = 0;
+    for (size_t o = 0; o < d.obstacles.size(); ++o)
+      for (int j = 1; j <= d.njoints(); ++j)
+        for (size_t g = 0; g < d.geoms.size(); ++g)
+          if (d.geoms[g].joint == j) dist[i * per + k++] = collidePair(d, data, CollisionPair{(int)g, -((int)o + 1), 0.0}, nullptr).distanceLowerBound;
+  }
+}
 // distance between two shapes given as (type, params[4], placement[12]); convex verts optional
 double oracle_shape_distance(int ta, const double* pa, const double* Ta, const double* va, int na, int tb,
                              const double* pb, const double* Tb, const double* vb, int nb) {

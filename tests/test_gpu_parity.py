@@ -815,3 +815,26 @@ def test_exchange_helpers_pack_mask_and_knn_shard_merge(pkg, eng, ur5):
         assert np.array_equal(oi.cpu().numpy(), ri) and np.array_equal(od.cpu().numpy(), rd)
         hi, hd = sh.merge_topk([x for x in gd.cpu().numpy()], [x for x in gi.cpu().numpy()], k)
         assert np.array_equal(hi, ri) and np.array_equal(hd, rd)
+
+
+@pytest.mark.parametrize("name,check_parameterized", [("ur5_boxes8.json", False), ("ur5_boxes32.json", False), ("edited", True)])
+def test_all_collisions_and_distance_between_objects(pkg, ob, name, check_parameterized):
+    """CollisionValidation with computeAllContacts (AllCollisionsValidationReport: the first colliding pair and
+    every later colliding pair of the same table, src/collision-validation.cc:72-89) and DistanceBetweenObjects
+    (src/distance-between-objects.cc:41-77), against the oracle, bit for bit."""
+    if name == "edited":
+        from test_abi import pair_op_model
+        desc = pair_op_model(pkg)
+        desc.check_parameterized = check_parameterized
+    else:
+        desc = pkg.ModelDescription.load(name)
+    o = ob.Oracle(desc)
+    ws = pkg.Workspace(pkg.Model(desc), 0)
+    q = pkg.uniform_configs(desc, 4000, seed=123)
+    gv, gf, gl, gc = ws.all_collisions(q)
+    ov, of, ol, oc = o.all_collisions(q)
+    assert np.array_equal(gv, ov) and np.array_equal(gf, of) and np.array_equal(gc, oc)
+    assert all(np.array_equal(a, b) for a, b in zip(gl, ol))
+    assert gc.max() > 1 and np.array_equal(gv, ws.validate_configs(q)[0])  # several contacts at once do occur; flags as validate
+    d, e = ws.distance_between_objects(q[:1500]), o.distance_between_objects(q[:1500])
+    assert d.shape[1] == desc.nobstacles * int((desc.geom_joint > 0).sum()) and np.array_equal(d, e)
