@@ -415,6 +415,7 @@ class NearestNeighbor:
         return [idx[i, :min(count[i], cap)].copy() for i in range(n)], count
 
 
-from .planners import BiRRTPlanner, EngineBackend, KPrmStar, Roadmap  # noqa: E402,F401
+from .planners import (BiRRTPlanner, DiffusingPlanner, EngineBackend, KPrmStar, RandomShortcut, Roadmap,  # noqa: E402,F401
+                       VisibilityPrmPlanner)  # noqa: E402,F401
 from .validators import (CollisionValidation, ConfigValidations, Dichotomy, Discretized,  # noqa: E402,F401
                          JointBoundValidation, Progressive, StraightPath, ValidationReport)

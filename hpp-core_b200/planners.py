@@ -470,3 +470,288 @@ class KPrmStar:
         rm.add_edges(np.stack([i_of[e_idx], j_of[e_idx]], axis=1))
         tm["roadmap edges + components (host)"] = time.perf_counter() - t0
         return self.solved()
+
+
+class _Stepper:
+    """Common pieces of the two planners below: shots, new components, valid parts."""
+
+    def __init__(self, backend, desc, q_init, q_goal, seed):
+        self.b, self.desc, self.seed = backend, desc, seed
+        self.roadmap = Roadmap(backend, desc.nq)
+        self.init = self.roadmap.add_node(np.asarray(q_init, np.float64), 0)
+        self.goal = self.roadmap.add_node(np.asarray(q_goal, np.float64), 1)
+        self.shots = 0
+        self.validations = 0  # path validations asked of the backend (batched forms validate speculatively: >= sequential)
+
+    def solved(self):
+        return self.roadmap.cc[self.init] == self.roadmap.cc[self.goal]
+
+    def shoot(self, n=1):
+        q = uniform_configs(self.desc, n, seed=self.seed, offset=self.shots)
+        self.shots += n
+        return q
+
+    def components(self):
+        """labels of the connected components in ascending order (the reference iterates a std::set of shared
+        pointers, i.e. in address order: any fixed order gives the same nodes and edges up to insertion order)"""
+        return sorted(set(self.roadmap.cc.tolist()))
+
+    def new_component_node(self, q):
+        """Roadmap::addNode(q): an existing node with this configuration, or a new node in a new component"""
+        rm = self.roadmap
+        n = rm.add_node(q, rm.next_cc)
+        if n == rm.n - 1 and rm.cc[n] == rm.next_cc:
+            rm.next_cc += 1
+        return n
+
+    def validate(self, q1, q2):
+        """(L, ok, t_last, end of the valid part) of the straight paths q1[i] -> q2[i], one batch"""
+        q1, q2 = np.asarray(q1, np.float64).reshape(-1, self.desc.nq), np.asarray(q2, np.float64).reshape(-1, self.desc.nq)
+        L = self.b.lengths(q1, q2)
+        ok, tl = self.b.validate(q1, q2, L, False)
+        self.validations += len(L)
+        ends = q2.copy()
+        bad = np.nonzero(~ok)[0]
+        if len(bad):
+            ends[bad] = self.b.path_eval(q1[bad], q2[bad], L[bad], tl[bad])
+        return L, ok, tl, ends
+
+
+class DiffusingPlanner(_Stepper):
+    """DiffusingPlanner::oneStep (reference src/diffusing-planner.cc:180-318, no constraints, default parameters
+    extensionStepLength = extensionStepRatio = -1): extend every connected component towards one random configuration,
+    then try to connect the new nodes with one another and with the nearest nodes of the other components.
+    `one_step` validates path by path in the reference's order; `one_step_batch` submits the extensions as one edge
+    batch and ALL connection attempts as a second one, then replays the reference's loop on the results (an attempt
+    the reference skips because an earlier one merged the two components is discarded): same roadmap."""
+
+    def _extend_phase(self, q_rand, batch):
+        rm = self.roadmap
+        ccs = self.components()
+        nears = [int(self.b.nearest(q_rand.reshape(1, -1), c)[0][0]) for c in ccs]  # Roadmap::nearestNode(q_rand, cc)
+        res = None
+        if batch:
+            res = self.validate(rm.nodes[nears], np.repeat(q_rand.reshape(1, -1), len(nears), axis=0))
+        new_nodes, delayed = [], []
+        for k, near in enumerate(nears):
+            L, ok, tl, end = (x[k] for x in res) if batch else (x[0] for x in self.validate(rm.nodes[near], q_rand))
+            t_final = L if ok else tl
+            if t_final == 0.0:  # validPath->timeRange().second == path->timeRange().first
+                continue
+            q_new = end
+            if (not ok) or not any(np.array_equal(rm.nodes[n], q_new) for n in new_nodes):  # belongs(q_new, newNodes)
+                new_nodes.append(rm.add_node_and_edge(near, q_new))
+            else:
+                delayed.append((near, q_new))
+        for near, q_new in delayed:
+            n = self.new_component_node(q_new)
+            rm.add_edge(near, n)
+        return new_nodes, nears
+
+    def _connect(self, a, q_b, node_b, res):
+        """one connection attempt of the reference's second phase, given its validation result"""
+        rm = self.roadmap
+        L, ok, tl, end = res
+        if ok:
+            rm.add_edge(a, node_b)
+        elif tl > 0:  # validPath && validPath->length() > 0
+            rm.add_node_and_edge(a, end)
+
+    def one_step(self, batch=False):
+        rm = self.roadmap
+        q_rand = self.shoot()[0]
+        new_nodes, nears = self._extend_phase(q_rand, batch)
+        # attempts in the reference's order: (n1, later new nodes...), then (n1, nearest neighbours of other components)
+        attempts = []
+        for i, n1 in enumerate(new_nodes):
+            attempts += [(n1, n2, False) for n2 in new_nodes[i + 1:]]
+            attempts += [(n1, n2, True) for n2 in nears]
+        results = None
+        if batch and attempts:
+            a = np.array([t[0] for t in attempts])
+            c = np.array([t[1] for t in attempts])
+            results = self.validate(rm.nodes[a].copy(), rm.nodes[c].copy())
+        for k, (n1, n2, check_cc) in enumerate(attempts):
+            if check_cc and rm.cc[n1] == rm.cc[n2]:
+                continue
+            if np.array_equal(rm.nodes[n1], rm.nodes[n2]):
+                continue  # (the reference asserts q1 != q2)
+            r = tuple(x[k] for x in results) if results is not None else tuple(x[0] for x in self.validate(rm.nodes[n1], rm.nodes[n2]))
+            self._connect(n1, rm.nodes[n2], n2, r)
+
+    def one_step_batch(self):
+        self.one_step(batch=True)
+
+    def solve(self, max_steps=1000, batch=False):
+        steps = 0
+        while not self.solved() and steps < max_steps:
+            self.one_step(batch)
+            steps += 1
+        return steps
+
+
+class VisibilityPrmPlanner(_Stepper):
+    """VisibilityPrmPlanner::oneStep / visibleFromCC (reference src/visibility-prm-planner.cc:73-186): a random valid
+    configuration is tested for visibility (a valid straight path) from the GUARD nodes of every connected component;
+    seen from none: it becomes a guard; seen from several: it becomes a connection node linked to the nearest visible
+    guard of each.  `one_step` validates guard by guard, component by component; `one_step_batch` validates the paths
+    to ALL guards of ALL components as one batch (visibleFromCC is 'one q against every guard of a component': a
+    ready-made batch).  Guards of a component are visited in node order; the shortest valid path wins (strict <)."""
+
+    def __init__(self, backend, desc, q_init, q_goal, seed=1):
+        super().__init__(backend, desc, q_init, q_goal, seed)
+        self.guard = {self.init: True, self.goal: True}  # nodeStatus_
+
+    def _valid_shot(self, batch):
+        """shoot until the configuration validations accept (the shots consumed are those of the sequential loop)"""
+        while True:
+            if not batch:
+                q = self.shoot()[0]
+                if self.b.config_valid(q.reshape(1, -1))[0]:
+                    return q
+                continue
+            block = uniform_configs(self.desc, 64, seed=self.seed, offset=self.shots)
+            ok = self.b.config_valid(block)
+            first = int(np.argmax(ok)) if ok.any() else -1
+            self.shots += 64 if first < 0 else first + 1
+            if first >= 0:
+                return block[first]
+
+    def one_step(self, batch=False):
+        rm = self.roadmap
+        q = self._valid_shot(batch)
+        guards = [n for n in range(rm.n) if self.guard.get(n, False)]
+        ccs = self.components()
+        by_cc = {c: [n for n in guards if rm.cc[n] == c] for c in ccs}
+        res = None
+        if batch and guards:
+            order = [n for c in ccs for n in by_cc[c]]
+            L, ok, _, _ = self.validate(np.repeat(q.reshape(1, -1), len(order), axis=0), rm.nodes[order])
+            res = {n: (L[k], ok[k]) for k, n in enumerate(order)}
+        delayed = []
+        for c in ccs:  # visibleFromCC
+            best, best_len = -1, np.inf
+            for n in by_cc[c]:
+                if res is not None:
+                    L, ok = res[n]
+                else:
+                    Lv, okv, _, _ = self.validate(q, rm.nodes[n])
+                    L, ok = Lv[0], okv[0]
+                if ok and L < best_len:
+                    best, best_len = n, L
+            if best >= 0:
+                delayed.append(best)
+        if len(delayed) == 0:
+            n = self.new_component_node(q)
+            self.guard[n] = True
+        if len(delayed) > 1:
+            for near in delayed:
+                n = self.new_component_node(q)
+                self.guard[n] = False
+                rm.add_edge(near, n)
+
+    def one_step_batch(self):
+        self.one_step(batch=True)
+
+    def solve(self, max_steps=1000, batch=False):
+        steps = 0
+        while not self.solved() and steps < max_steps:
+            self.one_step(batch)
+            steps += 1
+        return steps
+
+
+class RandomShortcut:
+    """pathOptimization::RandomShortcut::optimize (reference src/path-optimization/random-shortcut.cc:73-181) for a
+    PathVector of StraightPaths given by its waypoints, no constraints: two random parameters t1 < t2, the three
+    straight paths q0 -> q(t1) -> q(t2) -> q3 are validated, valid ones replace the corresponding parts, the result
+    is kept if it is shorter; stop after NumberOfLoops iterations without improvement or when the last NumberOfLoops
+    improvements gained less than 1e-4.
+    `optimize(batch=False)` validates path by path like the reference.  `optimize(batch=True)` is the speculative form
+    (SURVEY.md 8f-2): the loop ends after `projectionError` failures in a row, so that many iterations are drawn on the
+    CURRENT path at once -- 2 evaluations + 3 validations each, one `path_eval` and one edge batch for all of them -- and
+    replayed in order; the first improvement changes the path, the draws behind it are redone on the new path with the
+    same random numbers.  Same result, `projectionError` times fewer validation calls."""
+
+    def __init__(self, backend, desc, number_of_loops=5, seed=1):
+        self.b, self.desc, self.n, self.seed = backend, desc, int(number_of_loops), seed
+        self.draws = 0
+        self.validation_calls = 0
+
+    def _u(self, k):  # k-th pair of uniform numbers (the reference draws u2 first, then u1: shootTimes :183-195)
+        from .model_io import splitmix64
+        x = splitmix64(np.arange(2 * k, 2 * k + 2, dtype=np.uint64) + np.uint64(self.seed) * np.uint64(0x100000001B3))
+        u = (x >> np.uint64(11)).astype(np.float64) * (2.0 ** -53)
+        return u[0], u[1]
+
+    def _seglens(self, W):
+        return self.b.lengths(W[:-1], W[1:])
+
+    @staticmethod
+    def _rank(lens, t):
+        """PathVector::rankAtParam (src/path-vector.cc:40-69): segment and local parameter of t"""
+        r, local = 0, t
+        while r + 1 < len(lens) and local > lens[r]:
+            local -= lens[r]
+            r += 1
+        return r, min(local, lens[r])
+
+    def _extract(self, W, lens, ta, qa, tb, qb):
+        """waypoints of tmpPath->extract(ta, tb), ta <= tb: qa, the waypoints strictly inside, qb"""
+        ra, _ = self._rank(lens, ta)
+        rb, _ = self._rank(lens, tb)
+        cum = np.concatenate([[0.0], np.cumsum(lens)])
+        inner = [W[k] for k in range(ra + 1, rb + 1) if ta < cum[k] < tb]
+        return [qa] + inner + [qb]
+
+    def optimize(self, waypoints, batch=False):
+        W = np.asarray(waypoints, np.float64)
+        lens = self._seglens(W)
+        length = [np.inf] * (self.n - 1) + [float(lens.sum())]
+        perr, finished, result = self.n, False, None
+        while not finished and perr != 0:
+            depth = perr if batch else 1
+            T3 = float(lens.sum())
+            ts, idx = [], []
+            for k in range(depth):
+                u2, u1 = self._u(self.draws + k)
+                a, c = T3 * u2, T3 * u1
+                ts.append((min(a, c), max(a, c)))
+            # q(t1), q(t2) of every draw: one path_eval over the segments they fall in
+            seg, loc = [], []
+            for t1, t2 in ts:
+                for t in (t1, t2):
+                    r, l = self._rank(lens, t)
+                    seg.append(r)
+                    loc.append(l)
+            seg = np.array(seg)
+            qs = self.b.path_eval(W[seg], W[seg + 1], lens[seg], np.array(loc)).reshape(depth, 2, -1)
+            a = np.concatenate([np.stack([W[0], qs[k, 0], qs[k, 1]]) for k in range(depth)])
+            c = np.concatenate([np.stack([qs[k, 0], qs[k, 1], W[-1]]) for k in range(depth)])
+            L = self.b.lengths(a, c)
+            ok, _ = self.b.validate(a, c, L, False)
+            self.validation_calls += 1
+            improved = False
+            for k in range(depth):
+                self.draws += 1
+                t = [0.0, ts[k][0], ts[k][1], T3]
+                q = [W[0], qs[k, 0], qs[k, 1], W[-1]]
+                new = [q[0]]
+                for i in range(3):
+                    part = [q[i], q[i + 1]] if ok[3 * k + i] else self._extract(W, lens, t[i], q[i], t[i + 1], q[i + 1])
+                    new += part[1:]
+                newW = np.asarray(new)
+                newlens = self._seglens(newW)
+                newLength = float(newlens.sum())
+                if length[-1] <= newLength:
+                    perr -= 1
+                    if perr == 0:
+                        break
+                    continue
+                length = length[1:] + [newLength]
+                finished = (length[0] - length[-1]) <= 1e-4 * length[-1]
+                W, lens, result, perr, improved = newW, newlens, newW, self.n, True
+                break  # the draws behind this one were made on the old path: redo them on the new one
+            if not improved and not batch:
+                continue
+        return W if result is not None else np.asarray(waypoints, np.float64)

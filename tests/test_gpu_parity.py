@@ -838,3 +838,31 @@ def test_all_collisions_and_distance_between_objects(pkg, ob, name, check_parame
     assert gc.max() > 1 and np.array_equal(gv, ws.validate_configs(q)[0])  # several contacts at once do occur; flags as validate
     d, e = ws.distance_between_objects(q[:1500]), o.distance_between_objects(q[:1500])
     assert d.shape[1] == desc.nobstacles * int((desc.geom_joint > 0).sum()) and np.array_equal(d, e)
+
+
+def test_planner_front_ends_engine_equals_oracle(pkg, ob):
+    """SURVEY 8f-1/8f-2 on the engine: DiffusingPlanner and VisibilityPrmPlanner steps (batched inner loops) and the
+    speculative RandomShortcut build, on the GPU, exactly the roadmap / path they build on the CPU oracle."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from oracle_backend import OracleBackend
+    desc = pkg.ModelDescription.load("ur5_boxes8.json")
+    o = ob.Oracle(desc)
+    cand = pkg.uniform_configs(desc, 400, seed=5)
+    free = cand[o.validate_configs(cand, check_bounds=True)[0] == 1]
+    q0, q1 = free[0], free[1]
+    model = pkg.Model(desc)
+    for cls, steps in ((pkg.DiffusingPlanner, 30), (pkg.VisibilityPrmPlanner, 60)):
+        gpu = cls(pkg.EngineBackend(pkg, model, 0, 1, 1e-3), desc, q0, q1, seed=31)
+        cpu = cls(OracleBackend(ob.Oracle(desc), 1, 1e-3), desc, q0, q1, seed=31)
+        for _ in range(steps):
+            gpu.one_step_batch()
+            cpu.one_step_batch()
+        assert np.array_equal(gpu.roadmap.nodes, cpu.roadmap.nodes) and gpu.roadmap.n > 10
+        assert gpu.roadmap.edges == cpu.roadmap.edges and np.array_equal(gpu.roadmap.cc, cpu.roadmap.cc)
+    planner = pkg.BiRRTPlanner(pkg.EngineBackend(pkg, model, 0, 1, 1e-3), desc, q0, q1, seed=4)
+    planner.solve(max_steps=400)
+    way = planner.roadmap.nodes[planner.path()]
+    g = pkg.RandomShortcut(pkg.EngineBackend(pkg, model, 0, 1, 1e-3), desc, 8, seed=9).optimize(way, batch=True)
+    c = pkg.RandomShortcut(OracleBackend(ob.Oracle(desc), 1, 1e-3), desc, 8, seed=9).optimize(way, batch=True)
+    assert np.array_equal(g, c) and len(g) >= 2
