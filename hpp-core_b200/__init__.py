@@ -43,7 +43,7 @@ class hppb200_stats(C.Structure):
 
 # every symbol include/hppb200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
-    "hppb200_abi_version", "hppb200_last_error", "hppb200_device_count", "hppb200_measure_fp64_peak",
+    "hppb200_abi_version", "hppb200_last_error", "hppb200_device_count", "hppb200_measure_fp64_peak", "hppb200_measure_tmem_read_peak",
     "hppb200_model_create", "hppb200_model_destroy", "hppb200_model_nq", "hppb200_model_nv",
     "hppb200_model_num_config_pairs", "hppb200_model_get_config_pairs", "hppb200_model_num_parameterized_pairs", "hppb200_model_num_body_pairs",
     "hppb200_model_get_body_pairs", "hppb200_model_num_body_geom_pairs", "hppb200_model_get_body_geom_pairs",
@@ -108,6 +108,12 @@ def _is_torch(x):
 def measure_fp64_peak(device=0):
     v = C.c_double()
     _check(lib().hppb200_measure_fp64_peak(C.c_int(device), C.byref(v)))
+    return v.value
+
+
+def measure_tmem_read_peak(device=0):
+    v = C.c_double()
+    _check(lib().hppb200_measure_tmem_read_peak(C.c_int(device), C.byref(v)))
     return v.value
 
 

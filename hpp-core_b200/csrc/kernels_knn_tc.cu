@@ -186,6 +186,7 @@ struct TcFilterArgs {
   unsigned ntiles;       // node tiles of the prefix
   int nqt, kc, bstages, gstride, capc;  // capc: list capacity per (query, CTA) of this launch
   int swapOffsets;       // debug: exchange the leading/stride byte offsets of the descriptors
+  int ablate;            // timing experiments only (results are wrong): 1 tcgen05.ld without the sign test, 2 no tcgen05.ld either
 };
 
 // Persistent grid, one CTA per SM.  Warp TC_EPI_WARPS lane 0: bulk copies (query tiles once, node tiles through a ring);
@@ -301,6 +302,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
         };
         uint32_t ra[32], rb[32];
         __syncwarp();
+        if (A.ablate) {
+          if (A.ablate == 1) {
+            uint32_t acc = 0;
+#pragma unroll
+            for (int cb = 0; cb < TC_N / 32; cb += 2) {
+              tcLoad32(laneAddr + (uint32_t)cb * 32u, ra);
+              tcLoad32(laneAddr + (uint32_t)(cb + 1) * 32u, rb);
+              tcWaitLoad(ra);
+              tcWaitLoad(rb);
+              acc |= ra[0] | rb[31];
+            }
+            if (acc == 0x12345u) sCnt[q] = 1;
+          }
+          tcFenceBefore();
+          mbarArrive(bar(ACC_EMPTY + group));
+          continue;
+        }
         tcLoad32(laneAddr, ra);
 #pragma unroll
         for (int cb = 0; cb < TC_N / 32; cb += 2) {
@@ -627,6 +645,7 @@ static int tcLaunchFilter(hppb200_knn* nn, size_t prefixNodes, int nqtTotal, flo
     a.dump = qt0 == 0 ? dump : nullptr;
     a.ntiles = ntiles;
     a.swapOffsets = swapOffsets;
+    { const char* v = std::getenv("HPPB200_KNN_TC_ABLATE"); a.ablate = v ? std::atoi(v) : 0; }
     knnTcFilterKernel<<<grid, TC_THREADS, tcSmemBytes(a.nqt, kc, a.bstages), nn->stream>>>(a);
     HPPB200_CUDA_CHECK(cudaGetLastError());
   }
@@ -750,6 +769,79 @@ int hppb200_knn_tc_stats(hppb200_knn* nn, int64_t* out) {
     setLastError(e.what());
     return std::strncmp(e.what(), "CUDA", 4) == 0 ? HPPB200_ERR_CUDA : HPPB200_ERR_INVALID_ARGUMENT;
   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Measured TMEM -> register bandwidth: the roofline denominator of knnTcFilterKernel, whose output (one FP32 word per
+// (query, node) pair) has to leave tensor memory through tcgen05.ld.  One CTA per SM allocates the whole tensor memory
+// (512 columns); 16 warps (warp w reads TMEM lanes 32 (w % 4) .., columns 128 (w / 4) ..: every warp can only reach its own
+// lane quarter) stream it with the filter's own access shape (tcgen05.ld.32x32b.x32, two loads in flight per warp) and OR
+// the words so that nothing is optimised away.  Bytes = loads x 32 lanes x 32 columns x 4 B.
+__global__ void __launch_bounds__(512, 1) tmemReadPeakKernel(int iters, unsigned* sink) {
+  __shared__ uint32_t tmemPtr;
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smemAddr(&tmemPtr)), "r"(512u) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tcFenceBefore();
+  __syncthreads();
+  tcFenceAfter();
+  const uint32_t base = tmemPtr + ((uint32_t)(32 * (warp & 3)) << 16) + (uint32_t)(128 * (warp >> 2));
+  uint32_t a[32], b[32];
+  unsigned acc = 0;
+  for (int it = 0; it < iters; ++it) {
+#pragma unroll
+    for (int c = 0; c < 128; c += 64) {
+      tcLoad32(base + c, a);
+      tcLoad32(base + c + 32, b);
+      tcWaitLoad(a);
+      tcWaitLoad(b);
+#pragma unroll
+      for (int i = 0; i < 32; ++i) acc |= a[i] | b[i];
+    }
+  }
+  if (acc == 0x12345u) sink[0] = acc;  // (never true in practice: keeps the loads alive)
+  tcFenceBefore();
+  __syncthreads();
+  if (warp == 0) {
+    tcFenceAfter();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmemPtr), "r"(512u) : "memory");
+  }
+}
+
+int hppb200_measure_tmem_read_peak(int device, double* tb_per_s) {
+  try {
+    if (!tb_per_s) throw std::invalid_argument("null argument");
+    if (hppb200_device_count() == 0) throw std::runtime_error("no CUDA device visible: the engine has no CPU fallback");
+    HPPB200_CUDA_CHECK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    HPPB200_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    unsigned* sink = nullptr;
+    HPPB200_CUDA_CHECK(cudaMalloc((void**)&sink, sizeof(unsigned)));
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int iters = 4096;
+    double best = 0;
+    for (int rep = 0; rep < 5; ++rep) {
+      cudaEventRecord(e0);
+      tmemReadPeakKernel<<<prop.multiProcessorCount, 512>>>(iters, sink);
+      cudaEventRecord(e1);
+      HPPB200_CUDA_CHECK(cudaEventSynchronize(e1));
+      HPPB200_CUDA_CHECK(cudaGetLastError());
+      float ms = 0;
+      cudaEventElapsedTime(&ms, e0, e1);
+      const double bytes = (double)prop.multiProcessorCount * 16 /* warps */ * iters * 4 /* loads per turn */ * 32 * 32 * 4;
+      if (rep > 0) best = std::max(best, bytes / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    *tb_per_s = best;
+    return HPPB200_OK;
+  } catch (std::invalid_argument& e) { setLastError(e.what()); return HPPB200_ERR_INVALID_ARGUMENT; }
+  catch (std::exception& e) { setLastError(e.what()); return HPPB200_ERR_CUDA; }
 }
 
 int hppb200_knn_tc_filter_time(hppb200_knn* nn, double* ms, double* pairs) {

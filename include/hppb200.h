@@ -207,6 +207,11 @@ int hppb200_device_count(void);       /* 0 when no CUDA device is visible       
    the roofline denominator for the narrow-phase kernels. */
 int hppb200_measure_fp64_peak(int device, double* tflops);
 
+/* Measured TMEM -> register bandwidth of `device` in TB/s (tcgen05.ld.32x32b.x32 from 16 warps per SM over a resident
+   512-column allocation, CUDA events): the roofline denominator of the k-NN tensor-core filter pass, whose every
+   (query, node) accumulator word has to leave tensor memory that way. */
+int hppb200_measure_tmem_read_peak(int device, double* tb_per_s);
+
 /* ---- model ------------------------------------------------------------- */
 int hppb200_model_create(const hppb200_model_desc* desc, hppb200_model** out);
 void hppb200_model_destroy(hppb200_model* m);
