@@ -51,7 +51,7 @@ ABI_SYMBOLS = [
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
     "hppb200_validate_configs", "hppb200_validate_configs_noalloc", "hppb200_geometry_placements", "hppb200_pair_distances", "hppb200_all_collisions", "hppb200_model_num_distance_pairs",
     "hppb200_distance_between_objects",
-    "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edge_chains", "hppb200_workspace_set_max_iterations",
+    "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edges_indexed", "hppb200_validate_edge_chains", "hppb200_workspace_set_max_iterations",
     "hppb200_multi_create", "hppb200_multi_destroy", "hppb200_multi_num_devices", "hppb200_multi_workspace",
     "hppb200_multi_validate_configs", "hppb200_multi_validate_edges",
     "hppb200_pack_mask", "hppb200_unpack_mask", "hppb200_knn_merge_shards",
@@ -287,6 +287,19 @@ class Workspace:
         return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason)
 
 
+    def validate_edges_indexed(self, nn, method, param, node_a, node_b, reverse=False):
+        """edges between nodes of the device roadmap mirror `nn`, given by node index"""
+        a = np.ascontiguousarray(node_a, np.int64)
+        b = np.ascontiguousarray(node_b, np.int64)
+        n = a.shape[0]
+        valid, reason = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        t_fail, t_last, L = np.zeros(n), np.zeros(n), np.zeros(n)
+        pair = np.full(n, -1, np.int32)
+        _check(lib().hppb200_validate_edges_indexed(self.h, nn.h, C.c_int(method), C.c_double(param), C.c_int(1 if reverse else 0),
+                                                    _p(a, _i64p), _p(b, _i64p), C.c_size_t(n), C.c_uint32(0), _p(valid, _u8p),
+                                                    _p(t_fail, _dp), _p(t_last, _dp), _p(pair, _ip), _p(reason, _u8p), _p(L, _dp)))
+        return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, length=L)
+
     def validate_edge_chains(self, method, param, q1, q2, L, chain_begin, reverse=False):
         """PathVectors of StraightPaths (ContinuousValidation::validate recursion, src/continuous-validation.cc:153-192)."""
         q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.model.nq)
@@ -421,7 +434,7 @@ class NearestNeighbor:
         return [idx[i, :min(count[i], cap)].copy() for i in range(n)], count
 
 
-from .planners import (BiRRTPlanner, DiffusingPlanner, EngineBackend, KPrmStar, RandomShortcut, Roadmap,  # noqa: E402,F401
-                       VisibilityPrmPlanner)  # noqa: E402,F401
+from .planners import (BiRRTPlanner, DiffusingPlanner, EngineBackend, KPrmStar, PartialShortcut, RandomShortcut,  # noqa: E402,F401
+                       Roadmap, SimpleShortcut, VisibilityPrmPlanner)  # noqa: E402,F401
 from .validators import (CollisionValidation, ConfigValidations, Dichotomy, Discretized,  # noqa: E402,F401
                          JointBoundValidation, Progressive, StraightPath, ValidationReport)

@@ -7,6 +7,7 @@
 #include <cstring>
 
 #include "engine.hpp"
+#include "knn_state.hpp"
 
 namespace hppb200 {
 
@@ -46,6 +47,7 @@ Workspace::~Workspace() {
   if (own_stream && stream) cudaStreamDestroy(stream);
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
+  if (h_njobs) cudaFreeHost(h_njobs);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream3) cudaStreamDestroy(stream3);
   if (stream4) cudaStreamDestroy(stream4);
@@ -232,7 +234,8 @@ int hppb200_validate_configs(hppb200_workspace* wsp, const double* q, size_t n, 
     if (flags & HPPB200_DEVICE_POINTERS) {
       Timed tm(ws);
       launchValidateConfigs(ws, q, n, flags, valid, first_pair, reason);
-      tm.stop();
+      tm.stop();  // (synchronises)
+      finishValidateConfigs(ws, q, n, flags, valid, first_pair, reason);
       return;
     }
     (void)nq;
@@ -464,6 +467,50 @@ int hppb200_validate_edge_chains(hppb200_workspace* wsp, int method, double para
       if (reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(reason, ws->d_creason.p, n_chains, cudaMemcpyDeviceToHost, ws->stream));
       if (first_bad_edge) HPPB200_CUDA_CHECK(cudaMemcpyAsync(first_bad_edge, ws->d_cbad.p, n_chains * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
     }
+    tm.stop();
+  });
+}
+
+int hppb200_validate_edges_indexed(hppb200_workspace* wsp, hppb200_knn* nn, int method, double param, int reverse, const int64_t* node_a,
+                                   const int64_t* node_b, size_t n, uint32_t flags, uint8_t* valid, double* t_fail, double* t_last_valid,
+                                   int32_t* pair, uint8_t* reason, double* length) {
+  return guarded([&] {
+    if (!wsp || !nn || (n && (!node_a || !node_b || !valid))) throw std::invalid_argument("null argument");
+    if (flags & HPPB200_DEVICE_POINTERS) throw std::invalid_argument("hppb200_validate_edges_indexed takes host arrays");
+    if (method == HPPB200_METHOD_PROGRESSIVE && !(param > 0))
+      throw std::runtime_error("tolerance should be positive for progressive continuous validation.");
+    if (method == HPPB200_METHOD_DICHOTOMY && param != 0) throw std::runtime_error("Dichotomy path validation method does not support penetration.");
+    if (method == HPPB200_METHOD_DISCRETIZED && !(param > 0)) throw std::invalid_argument("step size must be positive");
+    if (method < HPPB200_METHOD_DISCRETIZED || method > HPPB200_METHOD_DICHOTOMY) throw std::invalid_argument("unknown method");
+    Workspace* ws = &wsp->impl;
+    if (nn->device != ws->device || nn->model->nq != ws->model->nq) throw std::invalid_argument("the roadmap mirror and the workspace must share device and robot");
+    if (n == 0) return;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));  // appended nodes are in place
+    const size_t nq = (size_t)ws->model->nq;
+    ws->d_ia.reserve(n); ws->d_ib.reserve(n); ws->d_q.reserve(n * nq); ws->d_q2.reserve(n * nq); ws->d_L.reserve(n);
+    ws->d_valid.reserve(n); ws->d_reason.reserve(n); ws->d_pair.reserve(n); ws->d_tfail.reserve(n); ws->d_tlast.reserve(n);
+    ws->d_count.reserve(2);
+    Timed tm(ws);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_ia.p, node_a, n * sizeof(int64_t), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_ib.p, node_b, n * sizeof(int64_t), cudaMemcpyHostToDevice, ws->stream));
+    unsigned* d_bad = (unsigned*)ws->d_count.p;
+    HPPB200_CUDA_CHECK(cudaMemsetAsync(d_bad, 0, sizeof(unsigned), ws->stream));
+    launchGatherEdgeEnds(ws->stream, nn->d_nodes, nn->n, (int)nq, (const int64_t*)ws->d_ia.p, (const int64_t*)ws->d_ib.p, n, ws->d_q.p, ws->d_q2.p, d_bad);
+    unsigned h_bad = 0;
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(&h_bad, d_bad, sizeof(unsigned), cudaMemcpyDeviceToHost, ws->stream));
+    launchStraightLengths(ws, ws->d_q.p, ws->d_q2.p, n, ws->d_L.p);  // steeringMethod::Straight: L = WeighedDistance(q1, q2)
+    HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    if (h_bad) throw std::invalid_argument("node index out of range of the roadmap mirror");
+    ws->stats.kernel_launches += 1;
+    launchValidateEdges(ws, method, param, reverse, ws->d_q.p, ws->d_q2.p, ws->d_L.p, n, flags, ws->d_valid.p, ws->d_tfail.p, ws->d_tlast.p,
+                        ws->d_pair.p, ws->d_reason.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_valid.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    if (t_fail) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_fail, ws->d_tfail.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    if (t_last_valid) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_last_valid, ws->d_tlast.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    if (pair) HPPB200_CUDA_CHECK(cudaMemcpyAsync(pair, ws->d_pair.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    if (reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(reason, ws->d_reason.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    if (length) HPPB200_CUDA_CHECK(cudaMemcpyAsync(length, ws->d_L.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
     tm.stop();
   });
 }

@@ -167,6 +167,7 @@ struct Workspace {
   DeviceBuffer<unsigned long long> d_count;
   DeviceBuffer<int32_t> d_pair, d_pair_int, d_chain, d_cpair, d_cbad;
   DeviceBuffer<uint8_t> d_cvalid, d_creason;
+  DeviceBuffer<long long> d_ia, d_ib;
   DeviceBuffer<DevPair> d_dbo;
   bool dboUploaded = false;
   DeviceBuffer<uint32_t> d_mask;
@@ -174,6 +175,7 @@ struct Workspace {
   DeviceBuffer<double> d_ctfail, d_ctlast;
   DeviceBuffer<unsigned long long> d_jobs;
   unsigned long long last_jobs = 0;
+  unsigned long long* h_njobs = nullptr;  // pinned: queue counter of the last configuration batch
   DeviceBuffer<unsigned char> d_state, d_tail, d_sort;
   bool wavefront_lpt = true;   // wavefront engines pull the edges longest first (kernels_sort.cu; HPPB200_WF_LPT=0: input order)
   bool use_tail = true;        // Dichotomy: CTA-per-edge pass for handed-over edges (HPPB200_TAIL=0: walker large-list pass only)
@@ -187,6 +189,8 @@ void setLastError(const std::string& s);
 double measureFp64Peak(int device);
 
 // kernel launchers (kernels_config.cu / kernels_edges.cu), all asynchronous on ws->stream
+void finishValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first,
+                           uint8_t* d_reason);
 void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
                            int32_t* d_first, uint8_t* d_reason);
 void noallocSetup(int device);  // resolves the static scratch array's device address (cudaGetSymbolAddress), once per device
@@ -229,6 +233,8 @@ bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d
 void launchChainReduce(Workspace* ws, const int32_t* d_chainBegin, size_t nChains, int reverse, const double* d_L, const uint8_t* eValid,
                        const double* eTfail, const double* eTlast, const int32_t* ePair, const uint8_t* eReason, uint8_t* valid,
                        double* tFail, double* tLast, int32_t* pair, uint8_t* reason, int32_t* firstBad);
+void launchGatherEdgeEnds(cudaStream_t stream, const double* nodes, size_t nNodes, int nq, const int64_t* a, const int64_t* b, size_t n,
+                          double* q1, double* q2, unsigned* bad);
 void launchPackMask(cudaStream_t stream, const uint8_t* valid, size_t n, uint32_t* bits);
 void launchUnpackMask(cudaStream_t stream, const uint32_t* bits, size_t n, uint8_t* valid);
 void launchKnnMergeShards(cudaStream_t stream, const double* dist, const int64_t* idx, int W, size_t Q, int k, int64_t* outIdx, double* outDist);

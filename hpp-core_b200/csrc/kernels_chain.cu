@@ -117,3 +117,29 @@ void launchKnnMergeShards(cudaStream_t stream, const double* dist, const int64_t
 }
 
 }  // namespace hppb200
+
+// ------------------------------------------------------------------------------------------------
+// Edges given as pairs of ROADMAP NODE indices (kPRM*-style linking, src/path-planner/k-prm-star.cc:134-193: every
+// candidate edge joins two nodes that already live in the device mirror of the roadmap): the end configurations are
+// gathered on the device instead of being gathered on the host and uploaded (96 B per UR5 edge down to 16 B).
+namespace hppb200 {
+__global__ void gatherEdgeEndsKernel(const double* __restrict__ nodes, size_t nNodes, int nq, const long long* __restrict__ a,
+                                     const long long* __restrict__ b, size_t n, double* __restrict__ q1, double* __restrict__ q2,
+                                     unsigned* __restrict__ bad) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * (size_t)nq) return;
+  const size_t e = i / (size_t)nq;
+  const int c = (int)(i - e * (size_t)nq);
+  const long long ia = a[e], ib = b[e];
+  if (ia < 0 || ib < 0 || (size_t)ia >= nNodes || (size_t)ib >= nNodes) { if (c == 0) atomicAdd(bad, 1u); q1[i] = 0; q2[i] = 0; return; }
+  q1[i] = nodes[(size_t)ia * nq + c];
+  q2[i] = nodes[(size_t)ib * nq + c];
+}
+void launchGatherEdgeEnds(cudaStream_t stream, const double* nodes, size_t nNodes, int nq, const int64_t* a, const int64_t* b, size_t n,
+                          double* q1, double* q2, unsigned* bad) {
+  if (!n) return;
+  const size_t total = n * (size_t)nq;
+  gatherEdgeEndsKernel<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(nodes, nNodes, nq, (const long long*)a, (const long long*)b, n, q1, q2, bad);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+}
+}  // namespace hppb200

@@ -431,18 +431,27 @@ static void launchConfigKernel(Workspace* ws, const double* d_q, size_t n, uint3
   if (mode == MODE_VALIDATE) ws->stats.configs += n;
 }
 
+// Asynchronous: the queue-overflow counter (more than ~2 surviving GJK pairs per configuration on average) is copied to
+// pinned host memory behind the kernels and looked at by finishValidateConfigs AFTER the caller's own synchronisation
+// (round 1 synchronised here on every call for a case that does not occur on the bench scenes).
 void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
                            int32_t* d_first, uint8_t* d_reason) {
   if (n == 0) return;
   launchValidateTwoKernel(ws, d_q, n, flags, d_valid, d_first, d_reason);
-  // queue overflow (more than ~2 surviving GJK pairs per configuration on average): fall back to the
-  // single fused kernel, which needs no queue.  Checked after the fact; costs one 8-byte read.
-  unsigned long long njobs = 0;
-  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&njobs, ws->d_jobs.p, sizeof(njobs), cudaMemcpyDeviceToHost, ws->stream));
-  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
-  ws->last_jobs = njobs;
-  if (njobs > 2 * n + 4096) launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
+  if (!ws->h_njobs) HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&ws->h_njobs, sizeof(unsigned long long), cudaHostAllocDefault));
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->h_njobs, ws->d_jobs.p, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ws->stream));
 }
+// After the stream has been synchronised: a batch whose queue overflowed is redone by the single fused kernel, which
+// needs no queue (still on the device; synchronises again).
+void finishValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first,
+                           uint8_t* d_reason) {
+  if (n == 0 || !ws->h_njobs) return;
+  ws->last_jobs = *ws->h_njobs;
+  if (ws->last_jobs <= 2 * n + 4096) return;
+  launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+}
+
 // ------------------------------------------------------------------------------------------------
 // hppb200_validate_configs_noalloc: the same two kernels (configPassKernel + gjkJobsKernel) with their scratch
 // (job counter, job queue, placement SoA) in a file-scope device array instead of the workspace's cudaMalloc'ed

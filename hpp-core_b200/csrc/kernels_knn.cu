@@ -8,10 +8,12 @@
 // selection passes, each keeping the best key strictly greater than the previous one.
 #include <algorithm>
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 
 #include "dev_model.cuh"
 #include "dev_knn.cuh"
+#include "knn_latency.hpp"
 
 namespace hppb200 {
 
@@ -330,7 +332,9 @@ int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out) {
       HPPB200_CUDA_CHECK(cudaFuncSetAttribute(nn->ff ? knnTileTopkKernel<true> : knnTileTopkKernel<false>,
                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes));
       // pinned staging for small calls (a planner's single queries): truly asynchronous copies, one sync per call
-      HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&nn->h_stage, KNN_STAGE_BYTES, cudaHostAllocDefault));
+      HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&nn->h_stage, KNN_STAGE_BYTES, cudaHostAllocMapped));
+      HPPB200_CUDA_CHECK(cudaHostGetDevicePointer((void**)&nn->d_stage_map, nn->h_stage, 0));  // the single-query kernel writes its result here
+      if (const char* v = std::getenv("HPPB200_KNN_LATENCY")) nn->lat_enabled = std::atoi(v) != 0;
     }
     knnTcInit(nn);
     *out = nn;
@@ -410,6 +414,16 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
       if (knnTcEligible(nn, nqueries, k, cc)) knnTcRun(nn, d_q, nqueries, k, cc, d_i, d_d);
       else knnExactRun(nn, d_q, nqueries, k, cc, nn->n, d_i, d_d);
     };
+    if (!(flags & HPPB200_DEVICE_POINTERS) && knnLatencyEligible(nn, nqueries, k)) {
+      // a planner's single query: one kernel (query in the parameter block, result written to mapped pinned memory by
+      // the last CTA), one synchronisation
+      nn->tc_last_used = false;
+      knnLatencyRun(nn, queries, k, cc, (long long*)nn->d_stage_map, (double*)(nn->d_stage_map + 32 * sizeof(long long)));
+      HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
+      std::memcpy(idx, nn->h_stage, (size_t)k * sizeof(int64_t));
+      std::memcpy(dist, nn->h_stage + 32 * sizeof(long long), (size_t)k * sizeof(double));
+      return;
+    }
     if (flags & HPPB200_DEVICE_POINTERS) {
       run(queries, (long long*)idx, dist);
       HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));

@@ -13,7 +13,7 @@
 // together; when the sign bit is set the GROUPS of 8 nodes holding a hit go to a list private to (query, CTA) (a
 // shared-memory counter, no global atomics) and the re-rank looks at all 8 exactly.  The threshold is an exact upper bound of the k-th distance: the k-th
 // exact distance over a PREFIX of the nodes (the first 512 by the re-rank kernel itself, then the candidates of a
-// <= 16x larger prefix, ...), inflated by the error bound eps = 2^-16 (na + max nb).  Every node whose exact distance
+// <= 16x larger prefix, ...), inflated by the error bound eps = 2^-15 (na + max nb) (2^-14 for models with more than 32 K slots).  Every node whose exact distance
 // is <= the k-th exact distance therefore survives, and the final result is the exact FP64 top-k of the survivors by
 // the same (distance, node index) key and the same operation order as the exact scan: identical indices and
 // distances, bit for bit.  A query one of whose lists overflows is redone by the exact scan.
@@ -32,7 +32,9 @@ constexpr int TC_N = 128;            // nodes per B tile (UMMA N)
 constexpr int TC_NBUF = 4;           // TMEM accumulators (TC_NBUF * TC_N = 512 columns: the whole tensor memory)
 constexpr int TC_CAPC = 16;          // candidates kept per (query, CTA) and stage when all SMs work (more per CTA otherwise)
 constexpr int TC_EPI_WARPS = 4 * TC_NBUF;  // one group of 4 warps per accumulator buffer
-constexpr int TC_THREADS = (TC_EPI_WARPS + 2) * 32;  // + bulk-copy producer warp + MMA issuer warp
+constexpr int TC_ISSUERS = 2;        // warps issuing tcgen05.mma (lane 0 each), tile pairs dealt round-robin: ONE thread's serial
+                                     // instruction stream was the pacing step of the kernel (profiles/r2b_knn_filter_ablation.txt)
+constexpr int TC_THREADS = (TC_EPI_WARPS + 1 + TC_ISSUERS) * 32;  // + bulk-copy producer warp + MMA issuer warps
 constexpr int TC_BSTAGES = 8;        // node-tile ring (at most; fewer when shared memory is short)
 constexpr int TC_MAX_KC = 6;
 constexpr int TC_MAX_QT = 8;
@@ -134,6 +136,12 @@ __device__ __forceinline__ void bulkCopy(uint32_t dst, const void* src, uint32_t
                "r"(bytes), "r"(bar)
                : "memory");
 }
+// one lane of the (converged) warp, the same one every time
+__device__ __forceinline__ bool electOne() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tcFenceBefore() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcFenceAfter() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tcCommit(uint32_t bar) {
@@ -146,6 +154,23 @@ __device__ __forceinline__ void tcMma(uint32_t tmem, uint64_t adesc, uint64_t bd
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem),
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// the same with the descriptors given as their low words (start address and leading byte offset fields; advancing the
+// start address by x bytes adds x >> 4) and the common high word: two moves instead of 64-bit shifts in the issuing thread
+__device__ __forceinline__ void tcMmaLo(uint32_t tmem, uint32_t aLo, uint32_t bLo, uint32_t hi, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "mov.b64 da, {%1, %3};\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t}" ::"r"(tmem),
+      "r"(aLo), "r"(bLo), "r"(hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+template <int KC>
+__device__ __forceinline__ void tcIssuePair(uint32_t tmem, uint32_t aLo, uint32_t bLo, uint32_t hi, uint32_t idesc) {
+#pragma unroll
+  for (int c = 0; c < KC; ++c) tcMmaLo(tmem, aLo + 16u * (uint32_t)c, bLo + 16u * (uint32_t)c, hi, idesc, c > 0 ? 1u : 0u);  // 256 B per K = 8 slot
 }
 // 32 consecutive accumulator columns of this thread's TMEM lane (= query row); valid after tcWaitLoad on the same array
 __device__ __forceinline__ void tcLoad32(uint32_t taddr, uint32_t (&r)[32]) {
@@ -186,13 +211,17 @@ struct TcFilterArgs {
   unsigned ntiles;       // node tiles of the prefix
   int nqt, kc, bstages, gstride, capc;  // capc: list capacity per (query, CTA) of this launch
   int swapOffsets;       // debug: exchange the leading/stride byte offsets of the descriptors
-  int ablate;            // timing experiments only (results are wrong): 1 tcgen05.ld without the sign test, 2 no tcgen05.ld either
+  long long* prof;       // timing experiments: [grid][8] cycles (MMA thread: wait B, wait accumulator, issue, total; epilogue warp 0:
+                         // wait accumulator, drain, total) or null
+  int ablate;            // timing experiments only (results are wrong): 1 tcgen05.ld without the sign test, 2 no tcgen05.ld either,
+                         // 3 = 2 + no tcgen05.mma (barrier protocol alone), 4 = 2 + one tcgen05.mma per tile pair
 };
 
 // Persistent grid, one CTA per SM.  Warp TC_EPI_WARPS lane 0: bulk copies (query tiles once, node tiles through a ring);
-// next warp lane 0: tcgen05.mma issue, kc K = 8 steps per (node tile, query tile) into one of TC_NBUF 128-column TMEM
-// accumulators; epilogue warps 4 g .. 4 g + 3 drain accumulator g (thread = TMEM lane = query row), two tcgen05.ld in
+// next TC_ISSUERS warps, lane 0 each: tcgen05.mma issue, kc K = 8 steps per (node tile, query tile) into one of TC_NBUF
+// 128-column TMEM accumulators; epilogue warps 4 g .. 4 g + 3 drain accumulator g (thread = TMEM lane = query row), two tcgen05.ld in
 // flight per warp.
+template <bool PROF>
 __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs A) {
   extern __shared__ __align__(128) unsigned char smem[];
   // barriers: 0 a_full, B_FULL.. b_full, B_EMPTY.. b_empty, ACC_FULL.. acc_full, ACC_EMPTY.. acc_empty
@@ -206,13 +235,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
   int* sCnt = (int*)(sB + (size_t)A.bstages * bBytes);  // candidates of this CTA per query row
   const uint32_t barBase = smemAddr(bars);
   auto bar = [&](int i) { return barBase + 8u * (uint32_t)i; };
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // (shuffles from lane 0: the compiler then keeps the warp index, and below the TMEM base, in uniform registers, which is
+  // where tcgen05.mma / commit / ld take their operands from; per-thread values cost an R2UR waterfall loop per instruction)
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
   const unsigned S = (unsigned)A.bstages;
 
   if (threadIdx.x == 0) {
     mbarInit(bar(0), 1);
-    for (int s = 0; s < TC_BSTAGES; ++s) { mbarInit(bar(B_FULL + s), 1); mbarInit(bar(B_EMPTY + s), 1); }
-    for (int b = 0; b < TC_NBUF; ++b) { mbarInit(bar(ACC_FULL + b), 1); mbarInit(bar(ACC_EMPTY + b), 128); }
+    for (int s = 0; s < TC_BSTAGES; ++s) { mbarInit(bar(B_FULL + s), 1); mbarInit(bar(B_EMPTY + s), TC_ISSUERS); }
+    for (int b = 0; b < TC_NBUF; ++b) { mbarInit(bar(ACC_FULL + b), 1); mbarInit(bar(ACC_EMPTY + b), 4); }  // one arrival per draining warp
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   }
@@ -224,7 +255,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
   tcFenceBefore();
   __syncthreads();
   tcFenceAfter();
-  const uint32_t tmemBase = *tmemPtr;
+  const uint32_t tmemBase = __shfl_sync(0xffffffffu, *tmemPtr, 0);
 
   if (warp == TC_EPI_WARPS) {
     if (lane == 0) {
@@ -239,53 +270,97 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
         bulkCopy(smemAddr(sB + (size_t)s * bBytes), A.btiles + (size_t)t * (bBytes / 4), bBytes, bar(B_FULL + s));
       }
     }
-  } else if (warp == TC_EPI_WARPS + 1) {
-    if (lane == 0) {
-      // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10), both
-      // K-major, N >> 3 at bit 17, M >> 4 at bit 24
-      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
-      const uint32_t lbo = A.swapOffsets ? (uint32_t)A.kc * 256u : 128u, sbo = A.swapOffsets ? 128u : (uint32_t)A.kc * 256u;
-      mbarWait(bar(0), 0);
-      unsigned it = 0, j = 0;
-      for (unsigned t = blockIdx.x; t < A.ntiles; t += gridDim.x, ++it) {
-        const unsigned s = it % S, ph = (it / S) & 1u;
-        mbarWait(bar(B_FULL + s), ph);
+  } else if (warp > TC_EPI_WARPS) {
+    // Issuing warp `me` of TC_ISSUERS takes the tile pairs j = me (mod TC_ISSUERS).  The WHOLE warp runs the loop on
+    // warp-uniform values and one elected lane issues: the loop body is then a few dozen uniform-datapath instructions
+    // (one thread's serial latency through this loop is what paces the tensor pipe at K = 8 kc).
+    const unsigned me = (unsigned)(warp - (TC_EPI_WARPS + 1));
+    // instruction descriptor (cute::UMMA::InstrDescriptor): D = F32 (1 << 4), A = B = TF32 (2 << 7, 2 << 10), both
+    // K-major, N >> 3 at bit 17, M >> 4 at bit 24
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+    const uint32_t lbo = A.swapOffsets ? (uint32_t)A.kc * 256u : 128u, sbo = A.swapOffsets ? 128u : (uint32_t)A.kc * 256u;
+    const uint64_t d0 = tcSmemDesc(0, lbo, sbo);
+    const uint32_t descHi = (uint32_t)(d0 >> 32), lboField = (uint32_t)d0;
+    const uint32_t aLo0 = ((smemAddr(sA) & 0x3FFFFu) >> 4) | lboField, bLo0 = ((smemAddr(sB) & 0x3FFFFu) >> 4) | lboField;
+    const uint32_t aStep = aBytes >> 4, bStep = bBytes >> 4;
+    const int kcUse = A.ablate == 3 ? 0 : A.ablate == 4 ? 1 : A.kc;  // (timing experiments)
+    mbarWait(bar(0), 0);
+    unsigned it = 0, j = 0;
+    long long pB = 0, pAcc = 0, pT0 = PROF ? clock64() : 0, c0 = 0;
+    for (unsigned t = blockIdx.x; t < A.ntiles; t += gridDim.x, ++it) {
+      const unsigned s = it % S, ph = (it / S) & 1u;
+      if (PROF) c0 = clock64();
+      mbarWait(bar(B_FULL + s), ph);
+      if (PROF) pB += clock64() - c0;
+      tcFenceAfter();
+      const uint32_t bLo = bLo0 + s * bStep;
+      uint32_t aLo = aLo0;
+      for (int qt = 0; qt < A.nqt; ++qt, ++j, aLo += aStep) {
+        if (j % TC_ISSUERS != me) continue;
+        const unsigned buf = j % TC_NBUF;
+        if (PROF) c0 = clock64();
+        mbarWait(bar(ACC_EMPTY + buf), ((j / TC_NBUF) & 1u) ^ 1u);
+        if (PROF) pAcc += clock64() - c0;
         tcFenceAfter();
-        const uint32_t bAddr = smemAddr(sB + (size_t)s * bBytes);
-        for (int qt = 0; qt < A.nqt; ++qt, ++j) {
-          const unsigned buf = j % TC_NBUF, aph = (j / TC_NBUF) & 1u;
-          mbarWait(bar(ACC_EMPTY + buf), aph ^ 1u);
-          tcFenceAfter();
-          const uint32_t aAddr = smemAddr(sA + (size_t)qt * aBytes);
-          for (int c = 0; c < A.kc; ++c)
-            tcMma(tmemBase + buf * (uint32_t)TC_N, tcSmemDesc(aAddr + (uint32_t)c * 256u, lbo, sbo),
-                  tcSmemDesc(bAddr + (uint32_t)c * 256u, lbo, sbo), idesc, c > 0 ? 1u : 0u);
+        const uint32_t acc = tmemBase + buf * (uint32_t)TC_N;
+        if (electOne()) {
+          switch (kcUse) {
+            case 1: tcIssuePair<1>(acc, aLo, bLo, descHi, idesc); break;
+            case 2: tcIssuePair<2>(acc, aLo, bLo, descHi, idesc); break;
+            case 3: tcIssuePair<3>(acc, aLo, bLo, descHi, idesc); break;
+            case 4: tcIssuePair<4>(acc, aLo, bLo, descHi, idesc); break;
+            case 5: tcIssuePair<5>(acc, aLo, bLo, descHi, idesc); break;
+            case 6: tcIssuePair<6>(acc, aLo, bLo, descHi, idesc); break;
+            default: break;
+          }
           tcCommit(bar(ACC_FULL + buf));
         }
-        tcCommit(bar(B_EMPTY + s));
+        __syncwarp();
       }
+      if (electOne()) tcCommit(bar(B_EMPTY + s));  // (TC_ISSUERS arrivals free the stage: a commit covers the committing thread's MMAs)
+      __syncwarp();
+    }
+    if (PROF && me == 0 && lane == 0) {
+      const long long tot = clock64() - pT0;
+      long long* P = A.prof + 8 * blockIdx.x;
+      P[0] = pB; P[1] = pAcc; P[2] = tot - pB - pAcc; P[3] = tot;
     }
   } else {
     const unsigned group = (unsigned)warp >> 2;               // accumulator buffer this warp drains
     const int row = (warp & 3) * 32 + lane;                    // TMEM lane = query row of the tile
     const uint32_t laneAddr = tmemBase + ((uint32_t)((warp & 3) * 32) << 16) + group * (uint32_t)TC_N;
-    unsigned j = 0, use = 0;
-    for (unsigned t = blockIdx.x; t < A.ntiles; t += gridDim.x) {
-      for (int qt = 0; qt < A.nqt; ++qt, ++j) {
-        if (j % TC_NBUF != group) continue;
+    unsigned use = 0;
+    const bool profMe = PROF && threadIdx.x == 0;
+    long long pW = 0, pT0 = profMe ? clock64() : 0, c0 = 0;
+    // this group's tile pairs only: j = group, group + TC_NBUF, ... in the issuers' order (t outer, qt inner); stepping
+    // through all pairs and skipping three of four cost the draining warps ~15 % of their issue slots
+    unsigned t = blockIdx.x;
+    int qt = (int)group;
+    for (;; qt += TC_NBUF) {
+      while (qt >= A.nqt) { qt -= A.nqt; t += gridDim.x; }
+      if (t >= A.ntiles) break;
+      {
+        if (profMe) c0 = clock64();
         mbarWait(bar(ACC_FULL + group), use & 1u);
+        if (profMe) pW += clock64() - c0;
         ++use;
         tcFenceAfter();
         const int q = qt * TC_M + row;
         // 32 columns: OR of the sign bits first; a set sign bit = approximate squared distance below the threshold
         auto process = [&](const uint32_t (&r)[32], int cb) {
-          uint32_t any = 0;
+          // (reduction trees of depth 3 + 1, not one chain of 32 dependent ORs: the chain's latency, 4 blocks per
+          // accumulator, was what the draining warps spent their time on)
+          uint32_t og[4];
 #pragma unroll
-          for (int i = 0; i < 32; ++i) any |= r[i];
+          for (int g = 0; g < 4; ++g) {
+            const uint32_t t1 = r[8 * g] | r[8 * g + 1] | r[8 * g + 2], t2 = r[8 * g + 3] | r[8 * g + 4] | r[8 * g + 5];
+            og[g] = (t1 | r[8 * g + 6]) | (t2 | r[8 * g + 7]);
+          }
+          const uint32_t any = (og[0] | og[1]) | (og[2] | og[3]);
           if ((int)any < 0) {  // rare: the groups of 8 nodes holding a hit go to the query's list of this CTA
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
-              const uint32_t o = r[8 * g] | r[8 * g + 1] | r[8 * g + 2] | r[8 * g + 3] | r[8 * g + 4] | r[8 * g + 5] | r[8 * g + 6] | r[8 * g + 7];
+              const uint32_t o = og[g];
               if ((int)o < 0) {
                 const int slot = atomicAdd(&sCnt[q], 1);
                 if (slot < A.capc)
@@ -316,22 +391,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
             if (acc == 0x12345u) sCnt[q] = 1;
           }
           tcFenceBefore();
-          mbarArrive(bar(ACC_EMPTY + group));
+          __syncwarp();
+          if (lane == 0) mbarArrive(bar(ACC_EMPTY + group));
           continue;
         }
+        // two loads in flight; the next pair is issued as soon as its registers are free, so that its latency runs
+        // under the sign tests of the current pair (tcgen05.wait::ld waits for ALL loads of the thread: one wait per pair)
         tcLoad32(laneAddr, ra);
+        tcLoad32(laneAddr + 32u, rb);
 #pragma unroll
         for (int cb = 0; cb < TC_N / 32; cb += 2) {
           tcWaitLoad(ra);
-          tcLoad32(laneAddr + (uint32_t)(cb + 1) * 32u, rb);
-          process(ra, cb);
           tcWaitLoad(rb);
+          process(ra, cb);
           if (cb + 2 < TC_N / 32) tcLoad32(laneAddr + (uint32_t)(cb + 2) * 32u, ra);
           process(rb, cb + 1);
+          if (cb + 3 < TC_N / 32) tcLoad32(laneAddr + (uint32_t)(cb + 3) * 32u, rb);
         }
+        // every lane's loads have landed (tcgen05.wait::ld above); one arrival per warp: 128 arrivals on one barrier word
+        // serialise in the shared-memory atomic unit and were the pacing step of the kernel (profiles/r2b_knn_filter_ablation.txt)
         tcFenceBefore();
-        mbarArrive(bar(ACC_EMPTY + group));
+        __syncwarp();
+        if (lane == 0) mbarArrive(bar(ACC_EMPTY + group));
       }
+    }
+    if (profMe) {
+      const long long tot = clock64() - pT0;
+      long long* P = A.prof + 8 * blockIdx.x;
+      P[4] = pW; P[5] = tot - pW; P[6] = tot; P[7] = (long long)use;
     }
   }
   tcFenceBefore();
@@ -348,7 +435,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) knnTcFilterKernel(TcFilterArgs 
 // by (distance, node index).  A candidate is a group of 8 consecutive nodes: the first `prefixNodes` nodes
 // (bootstrap, cnt == null) or the query's per-CTA lists of the last filter launch, compacted into shared memory by
 // warp 0; every warp then takes 4 groups per trip (lane = node), keeps its k best sorted across the lanes, and warp
-// 0 merges.  Not final: the new threshold thr = d_k^2 (1 + 1e-6) + eps, eps = 2^-16 (na + max nb), rounded up, if
+// 0 merges.  Not final: the new threshold thr = d_k^2 (1 + 1e-6) + eps, eps = 2^-15 .. 2^-14 (na + max nb), rounded up, if
 // it is tighter.  Final: write the result; a query with an overflowed list is flagged (idx[q][0] = -2, appended to
 // `flagged`) and redone by the exact scan.
 constexpr int TC_RR_WARPS = 4;
@@ -358,6 +445,12 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
                   int gused, int gstride, int capc, int prefixNodes, const unsigned* __restrict__ maxNorm, float* __restrict__ thr,
                   int finalStage, long long* __restrict__ idx, double* __restrict__ dist, unsigned* __restrict__ nflagged,
                   int* __restrict__ flagged, const int32_t* __restrict__ ccOf, int32_t ccFilter, int prefilter) {
+  // Error bound of the TF32 accumulator the thresholds are inflated by: eps = 2^epsExp (|a'|^2 + max |b'|^2).  The
+  // products are exact in FP32; what is left is the dropped al*bl term and the split residuals (~2^-20 of the norms)
+  // and the FP32 accumulation of K = 8 kc slots, whose order and rounding tcgen05 does not specify: at most
+  // ~(8 kc + 4) 2^-23 of the largest partial sum (norms + threshold <= 3 (na + nb)): 2^-15 covers kc <= 4 (K <= 32)
+  // with a factor > 2, wider models get 2^-14.  Measured on UR5 (kc = 3): 2^-22.
+  const int epsExp = (3 * mv.nq + 6 > 32) ? -14 : -15;
   extern __shared__ __align__(16) unsigned char rsm[];
   __shared__ Key lists[TC_RR_WARPS][32];
   __shared__ int sTotal, sKept;
@@ -472,7 +565,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
       if (keys[k - 1].i != LLONG_MAX) {
         double na = 0;
         for (int c = 0; c < mv.nq; ++c) { const double x = scale[c] * sq[c]; na = fma(x, x, na); }
-        const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), -16) + 1e-30;
+        const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), epsExp) + 1e-30;
         t = fminf(TC_THR_MAX, __double2float_ru(keys[k - 1].d * keys[k - 1].d * (1.0 + 1e-6) + eps));
       }
       if (cnt == nullptr || t < thr[q]) thr[q] = t;
@@ -521,7 +614,7 @@ knnTcRerankKernel(ModelView mv, const double* __restrict__ nodes, size_t n, cons
     if (ak.i != LLONG_MAX) {
       double na = 0;
       for (int c = 0; c < mv.nq; ++c) { const double x = scale[c] * sq[c]; na = fma(x, x, na); }
-      const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), -16) + 1e-30;
+      const double eps = ldexp(na + (double)__uint_as_float(*maxNorm), epsExp) + 1e-30;
       t = fminf(TC_THR_MAX, __double2float_ru(ak.d * ak.d * (1.0 + 1e-6) + eps));
     }
     if (cnt == nullptr || t < thr[q]) thr[q] = t;
@@ -580,7 +673,8 @@ void knnTcInit(hppb200_knn* nn) {
   HPPB200_CUDA_CHECK(cudaMemcpy(nn->d_tc_scale.p, scale.data(), (size_t)nq * sizeof(double), cudaMemcpyHostToDevice));
   nn->d_tc_misc.reserve(4);
   HPPB200_CUDA_CHECK(cudaMemset(nn->d_tc_misc.p, 0, 4 * sizeof(unsigned)));
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTcFilterKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTcFilterKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(knnTcFilterKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
   HPPB200_CUDA_CHECK(cudaEventCreate(&nn->tc_ev0));
   HPPB200_CUDA_CHECK(cudaEventCreate(&nn->tc_ev1));
 }
@@ -646,8 +740,23 @@ static int tcLaunchFilter(hppb200_knn* nn, size_t prefixNodes, int nqtTotal, flo
     a.ntiles = ntiles;
     a.swapOffsets = swapOffsets;
     { const char* v = std::getenv("HPPB200_KNN_TC_ABLATE"); a.ablate = v ? std::atoi(v) : 0; }
-    knnTcFilterKernel<<<grid, TC_THREADS, tcSmemBytes(a.nqt, kc, a.bstages), nn->stream>>>(a);
+    a.prof = nullptr;
+    static const bool wantProf = std::getenv("HPPB200_KNN_TC_PROF") != nullptr;  // timing experiments: per-CTA wait cycles to stderr
+    DeviceBuffer<long long> prof;
+    if (wantProf) { prof.reserve((size_t)grid * 8); a.prof = prof.p; }
+    if (wantProf) knnTcFilterKernel<true><<<grid, TC_THREADS, tcSmemBytes(a.nqt, kc, a.bstages), nn->stream>>>(a);
+    else knnTcFilterKernel<false><<<grid, TC_THREADS, tcSmemBytes(a.nqt, kc, a.bstages), nn->stream>>>(a);
     HPPB200_CUDA_CHECK(cudaGetLastError());
+    if (wantProf) {
+      std::vector<long long> h((size_t)grid * 8);
+      HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
+      HPPB200_CUDA_CHECK(cudaMemcpy(h.data(), prof.p, h.size() * sizeof(long long), cudaMemcpyDeviceToHost));
+      double m[8] = {0};
+      for (unsigned c = 0; c < grid; ++c) for (int i = 0; i < 8; ++i) m[i] += (double)h[(size_t)c * 8 + i] / grid;
+      std::fprintf(stderr, "knnTcFilter prof: tiles %u nqt %d kc %d stages %d | mma thread: wait B %.0f wait acc %.0f issue %.0f total %.0f | "
+                   "epilogue warp 0: wait acc %.0f drain %.0f total %.0f uses %.0f (cycles, mean over %u CTAs)\n",
+                   ntiles, a.nqt, kc, a.bstages, m[0], m[1], m[2], m[3], m[4], m[5], m[6], m[7], grid);
+    }
   }
   return (int)grid;
 }

@@ -1145,6 +1145,9 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     return !emit && !stop;
   };
 
+  // (explicit reconvergence points: the scans have data-dependent trip counts, and lanes that leave one early otherwise
+  //  run the rest of the kernel on their own, see wfProgControlKernel)
+  __syncwarp();
   if (active) {
     const bool complete = scan(pos, false);
     if (active && complete) {
@@ -1182,6 +1185,7 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     }
   }
 
+  __syncwarp();
   // ---- REFILL ---------------------------------------------------------------------------------------  @region refill
   {
     const bool want = !active && !retired;
@@ -1214,6 +1218,7 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     }
   }
 
+  __syncwarp();
   // ---- next sample: iteration cap, then the candidates of a sample without results -----------------  @region sample
   if (needSample) {
     if (iters >= A.max_iter) {
@@ -1230,6 +1235,7 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     }
   }
 
+  __syncwarp();
   // ---- EMIT ------------------------------------------------------------------------------------------  @region emit
   wfEmitJobs<W>(A, T, e, lane, active, cand, nEm, sCnt, ctl);
 

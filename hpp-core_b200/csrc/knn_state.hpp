@@ -15,7 +15,12 @@ struct hppb200_knn {
   hppb200::DeviceBuffer<long long> d_idx, d_count;
   hppb200::DeviceBuffer<unsigned char> d_keys;  // previous keys [Q] + per-tile partial keys [tiles][Q]
   int num_sms = 148;
-  unsigned char* h_stage = nullptr;  // pinned staging block for small query calls
+  unsigned char* h_stage = nullptr;  // pinned staging block for small query calls (mapped: d_stage_map is its device address)
+  unsigned char* d_stage_map = nullptr;
+  // single-query path (kernels_knn_latency.cu): ticket counter (first 256 B) + per-CTA candidate lists
+  hppb200::DeviceBuffer<unsigned char> d_lat;
+  bool lat_ticket_zeroed = false;
+  bool lat_enabled = true;  // HPPB200_KNN_LATENCY (0: single queries go through the tiled scan as before)
 
   // ---- tensor-core candidate pass (kernels_knn_tc.cu) ----
   bool ff = false;           // the model has free-flyer joints (no GEMM form of the distance)

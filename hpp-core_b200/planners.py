@@ -58,6 +58,12 @@ class EngineBackend:
     def path_eval(self, q1, q2, L, t):
         return self.ws.path_eval(q1, q2, L, t)
 
+    def validate_nodes(self, a, b):
+        """path validation of the straight paths between roadmap nodes a[i] -> b[i], end configurations gathered on the
+        device from the mirror (hppb200_validate_edges_indexed)"""
+        r = self.ws.validate_edges_indexed(self.nn, self.method, self.param, a, b)
+        return r["valid"].astype(bool)
+
 
 class Roadmap:
     """Nodes in insertion order, undirected edges, connected-component labels (src/roadmap.cc:74-142,209-255)."""
@@ -445,6 +451,8 @@ class KPrmStar:
             a, c = i_of[sel], j_of[sel]
             if len(a) == 0:
                 return np.zeros(0, bool)
+            if hasattr(b, "validate_nodes"):  # both ends live in the device mirror: send indices, not configurations
+                return np.asarray(b.validate_nodes(a, c), bool)
             qa, qc = rm.nodes[a], rm.nodes[c]
             return np.asarray(b.validate(qa, qc, b.lengths(qa, qc), False)[0], bool)
 
@@ -755,3 +763,139 @@ class RandomShortcut:
             if not improved and not batch:
                 continue
         return W if result is not None else np.asarray(waypoints, np.float64)
+
+
+class SimpleShortcut:
+    """pathOptimization::SimpleShortcut::optimize (reference src/path-optimization/simple-shortcut.cc:51-83) for a
+    PathVector of StraightPaths given by its waypoints: a roadmap of the waypoints with the path's own edges
+    (i -> i + 1), every pair (i, j >= i + 2) steered and validated, the valid ones added as edges i -> j, and the
+    solution extracted by A* (src/astar.hh:96-136) with edge cost = path length and heuristic = distance to the goal.
+    The N (N - 1) / 2 - (N - 1) validations are independent of each other: ONE edge batch (the reference validates them
+    one by one).  The A* replay keeps the reference's container semantics (open list re-sorted with a stable sort by
+    estimated cost every iteration, out-edges in insertion order), so that cost ties resolve the same way."""
+
+    def __init__(self, backend):
+        self.b = backend
+        self.validated = 0
+
+    def optimize(self, waypoints):
+        W = np.asarray(waypoints, np.float64)
+        n = len(W)
+        if n < 3:
+            return W
+        a, c = np.triu_indices(n, 2)
+        L = self.b.lengths(W[a], W[c])
+        ok, _ = self.b.validate(W[a], W[c], L, False)
+        self.validated += len(a)
+        own = self.b.lengths(W[:-1], W[1:])
+        h = self.b.lengths(W, np.repeat(W[-1:], n, axis=0))
+        out = [[(i + 1, float(own[i]))] if i + 1 < n else [] for i in range(n)]
+        for e in np.nonzero(ok)[0]:
+            out[int(a[e])].append((int(c[e]), float(L[e])))
+        return W[self._astar(out, h, n - 1)]
+
+    @staticmethod
+    def _astar(out, h, goal):
+        open_, closed, parent = [0], set(), {}
+        g, f = {0: 0.0}, {0: 0.0}  # (std::map::operator[]: the init node's entries are value-initialised)
+        while open_:
+            open_.sort(key=lambda x: f[x])  # std::list::sort is stable
+            cur = open_[0]
+            if cur == goal:
+                path = [cur]
+                while path[-1] in parent:
+                    path.append(parent[path[-1]])
+                return path[::-1]
+            open_.pop(0)
+            closed.add(cur)
+            for child, cost in out[cur]:
+                if child in closed:
+                    continue
+                tmp = g[cur] + cost
+                new = child not in open_
+                if new or tmp < g[child]:
+                    parent[child], g[child], f[child] = cur, tmp, tmp + float(h[child])
+                    if new:
+                        open_.append(child)
+        raise RuntimeError("A* failed to find a solution to the goal.")
+
+
+class PartialShortcut:
+    """pathOptimization::PartialShortcut::optimize with its default parameters (onlyFullShortcut = true; reference
+    src/path-optimization/partial-shortcut.cc:84-98, 100-151, 186-223) for a PathVector of StraightPaths given by its
+    waypoints, no constraints: joint after joint, the joint's configuration is replaced along the WHOLE path by its
+    interpolation between the path's first and last configurations (at the ratio of the arc length reached at each
+    waypoint), the resulting chain of straight paths is validated, and kept if valid.
+    `optimize(batch=False)` validates one chain per joint like the reference.  `optimize(batch=True)` is the speculative
+    form: the candidates of ALL remaining joints are built on the current path and validated as one
+    edge batch; the first valid one in joint order is adopted (the reference would have adopted exactly that one, the
+    failed ones before it are final), the candidates behind it are rebuilt on the new path.  Same result; the number
+    of validation calls drops from the number of joints to the number of adopted joints + 1.
+    (The random phase, optimizeRandom :225-330, runs only when onlyFullShortcut is switched off and draws from C
+    rand(); it is not restated.)"""
+
+    def __init__(self, backend, desc):
+        self.b, self.desc = backend, desc
+        self.validation_calls = 0
+        self.failed_joints = []
+        seg, r = [], 0
+        for t in desc.joint_type:
+            sz = 7 if int(t) == 6 else 1
+            seg.append((r, sz))
+            r += sz
+        self.segments = seg
+
+    @staticmethod
+    def _total(lens):  # PathVector::appendPath accumulates timeRange().second leaf by leaf
+        t = 0.0
+        for x in lens:
+            t += float(x)
+        return t
+
+    def _candidate(self, W, lens, seg):
+        """generatePath(opted, joint, 0, q0, t3, q3): waypoints of the new chain, or None (single leaf: rkAtP2 == rkAtP1)"""
+        n = len(W) - 1
+        if n < 2:
+            return None
+        t3, t, us = self._total(lens), 0.0, []
+        for i in range(n - 1):
+            t += float(lens[i])
+            us.append(t / (t3 - 0.0))
+        us = np.asarray(us)
+        # interpolate(q0, q3, u) of the whole configuration, of which the joint's segment is taken (the Lie-group
+        # interpolation is joint-wise): the straight path q0 -> q3 over the parameter range [0, 1] evaluated at u
+        m = len(us)
+        full = self.b.path_eval(np.repeat(W[:1], m, axis=0), np.repeat(W[-1:], m, axis=0), np.ones(m), us)
+        new = W.copy()
+        r, sz = seg
+        new[1:n, r:r + sz] = full[:, r:r + sz]
+        return new
+
+    def optimize(self, waypoints, batch=False):
+        W = np.asarray(waypoints, np.float64)
+        lens = self.b.lengths(W[:-1], W[1:])
+        self.failed_joints = []
+        j, J = 0, len(self.segments)
+        while j < J:
+            todo = range(j, J) if batch else range(j, j + 1)
+            cands = [self._candidate(W, lens, self.segments[x]) for x in todo]
+            if cands[0] is None:  # a single straight path: nothing to do for any joint
+                self.failed_joints += list(range(j, J))
+                break
+            a = np.concatenate([c[:-1] for c in cands])
+            c2 = np.concatenate([c[1:] for c in cands])
+            L = self.b.lengths(a, c2)
+            ok, _ = self.b.validate(a, c2, L, False)
+            self.validation_calls += 1
+            m = len(W) - 1
+            adopted = False
+            for x, cand in zip(todo, cands):
+                sl = slice((x - j) * m, (x - j + 1) * m)
+                if bool(np.all(ok[sl])):
+                    W, lens, adopted = cand, L[sl], True
+                    j = x + 1
+                    break
+                self.failed_joints.append(x)
+            if not adopted:
+                j = todo[-1] + 1
+        return W

@@ -365,6 +365,17 @@ int hppb200_multi_validate_edges(hppb200_multi* h, int method, double param, int
                                  uint32_t flags, uint8_t* valid, double* t_fail, double* t_last_valid,
                                  int32_t* pair, uint8_t* reason);
 
+/* Path validation of edges between ROADMAP NODES (kPRM*-style linking, reference src/path-planner/k-prm-star.cc:134-193:
+   (*sm)(q_i, q_j) then pathValidation()->validate for nodes i, j that are already in the roadmap): node_a / node_b [n] are
+   indices into the device mirror `nn` (insertion order, as hppb200_knn_query returns them); the end configurations are
+   gathered on the device and L = WeighedDistance(q_a, q_b) (steeringMethod::Straight) is computed there, so that a call
+   moves 16 B per edge to the device instead of 2 nq + 1 doubles.  Outputs as hppb200_validate_edges, plus length [n]
+   (may be NULL).  Host arrays only; `nn` and `ws` must share device and robot. */
+int hppb200_validate_edges_indexed(hppb200_workspace* ws, hppb200_knn* nn, int method, double param, int reverse,
+                                   const int64_t* node_a, const int64_t* node_b, size_t n, uint32_t flags,
+                                   uint8_t* valid, double* t_fail, double* t_last_valid, int32_t* pair,
+                                   uint8_t* reason, double* length);
+
 /* Exchange helpers of the one-process-per-GPU form (bench.py --gpus N, hpp-core_b200/sharding.py), where the path's only
    cross-GPU data are validity masks and k-NN candidates.  DEVICE pointers, asynchronous on
    `cuda_stream` (a cudaStream_t; the caller's NCCL collective goes on the same stream).

@@ -257,9 +257,54 @@ def test_knn_tensor_core_tile_error_bound(pkg, eng, ur5):
     ref = (((qs[:, None, :] - nodes[None, :256, :]) * w) ** 2).sum(-1)
     tile = nn.tc_debug_tile(qs)[:100]
     na, nb = ((qs * w) ** 2).sum(-1), ((nodes * w) ** 2).sum(-1).max()
-    eps = (na + nb) * 2.0 ** -16
-    assert np.all(np.abs(tile - ref) < 0.25 * eps[:, None])
+    eps = (na + nb) * 2.0 ** -15
+    assert np.all(np.abs(tile - ref) < 0.125 * eps[:, None])
     assert np.all(nn.tc_debug_tile(qs)[100:] > 1e29)  # padding rows never pass a threshold
+
+
+def _prismatic_chain(pkg, nj, lo, hi):
+    """a chain of nj prismatic joints with configuration values in [lo, hi]: norms far larger than distances"""
+    eye = [1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0.1]
+    return pkg.ModelDescription(dict(name="prismatic%d" % nj, joint_parent=list(range(nj)), joint_type=[3 + (k % 3) for k in range(nj)],
+                                     joint_placement=[eye] * nj, q_lower=[lo] * nj, q_upper=[hi] * nj, geom_joint=[nj],
+                                     geom_placement=[eye], geom_shape=[0], geom_params=[[0.05, 0, 0, 0]], self_pairs=[],
+                                     weights=[1.0 + 0.1 * k for k in range(nj)]))
+
+
+@pytest.mark.parametrize("nj,lo,hi", [(14, 90.0, 110.0), (10, -3.0, 3.0), (14, -1.0, 1.0)])
+def test_knn_tensor_core_error_bound_wide_models_far_from_origin(pkg, nj, lo, hi):
+    """the bound the thresholds carry must hold for the widest models the tensor-core pass takes (kc = 6: 48 K
+    slots at nq = 14) and for nodes far from the origin (norms >> distances), and a miss would drop a true neighbour
+    silently: raw accumulators against FP64 (|error| < eps / 2), then full queries against the exact scan, exact
+    duplicates (ties) included."""
+    desc = _prismatic_chain(pkg, nj, lo, hi)
+    m = pkg.Model(desc)
+    nn = pkg.NearestNeighbor(m, 0)
+    nodes = pkg.uniform_configs(desc, 40000, seed=191)
+    nodes[20000:20040] = nodes[100:140]  # exact duplicates: ties decided by node index
+    qs = pkg.uniform_configs(desc, 128, seed=192)
+    qs[:40] = nodes[100:140] + 1e-7
+    nn.append(nodes)
+    w = np.asarray(desc.weights)  # prismatic joints: translation part is unweighted in WeighedDistance
+    ref = ((qs[:, None, :] - nodes[None, :256, :]) ** 2).sum(-1)
+    tile = nn.tc_debug_tile(qs)
+    na, nb = (qs ** 2).sum(-1), (nodes ** 2).sum(-1).max()
+    eps = (na + nb) * 2.0 ** (-14 if 3 * nj + 6 > 32 else -15)
+    assert np.all(np.abs(tile[:128] - ref) < 0.5 * eps[:, None]), float((np.abs(tile[:128] - ref) / eps[:, None]).max())
+    import os
+    for k in (1, 10):
+        gi, gd = nn.query(qs, k)
+        assert nn.tc_stats()["used"]
+        os.environ["HPPB200_KNN_TC"] = "0"
+        try:
+            ex = pkg.NearestNeighbor(m, 0)
+        finally:
+            del os.environ["HPPB200_KNN_TC"]
+        ex.append(nodes)
+        ei, ed = ex.query(qs, k)
+        assert not ex.tc_stats()["used"]
+        assert np.array_equal(gi, ei) and np.array_equal(gd, ed)
+    assert np.array_equal(gi[:40, 0], np.arange(100, 140))  # the earlier of two identical nodes wins
 
 
 def test_knn_tensor_core_pass_matches_exact_scan_and_oracle(pkg, eng, ur5, ob, monkeypatch):
@@ -866,3 +911,75 @@ def test_planner_front_ends_engine_equals_oracle(pkg, ob):
     g = pkg.RandomShortcut(pkg.EngineBackend(pkg, model, 0, 1, 1e-3), desc, 8, seed=9).optimize(way, batch=True)
     c = pkg.RandomShortcut(OracleBackend(ob.Oracle(desc), 1, 1e-3), desc, 8, seed=9).optimize(way, batch=True)
     assert np.array_equal(g, c) and len(g) >= 2
+    # SimpleShortcut (all waypoint pairs in one edge batch + A*) and PartialShortcut (joint-wise straightening, speculative)
+    g = pkg.SimpleShortcut(pkg.EngineBackend(pkg, model, 0, 1, 1e-3)).optimize(way)
+    c = pkg.SimpleShortcut(OracleBackend(ob.Oracle(desc), 1, 1e-3)).optimize(way)
+    assert np.array_equal(g, c) and 2 <= len(g) <= len(way)
+    gp = pkg.PartialShortcut(pkg.EngineBackend(pkg, model, 0, 1, 1e-3), desc)
+    cp = pkg.PartialShortcut(OracleBackend(ob.Oracle(desc), 1, 1e-3), desc)
+    g, c = gp.optimize(way, batch=True), cp.optimize(way, batch=False)
+    assert np.array_equal(g, c) and gp.failed_joints == cp.failed_joints
+
+
+def test_validate_edges_indexed_over_the_roadmap_mirror(pkg, eng, ur5, ur5_oracle):
+    """hppb200_validate_edges_indexed: edges between nodes of the device mirror by index == the same edges given by their
+    end configurations (and the oracle); bad indices are rejected."""
+    m, ws = eng
+    nn = pkg.NearestNeighbor(m, 0)
+    nodes = pkg.uniform_configs(ur5, 5000, seed=141)
+    nn.append(nodes[:3000])
+    nn.append(nodes[3000:])
+    rng = np.random.default_rng(5)
+    a, b = rng.integers(0, 5000, 4000), rng.integers(0, 5000, 4000)
+    a[:5] = b[:5]  # zero-length edges too
+    for meth, par in ((1, 1e-3), (2, 0.0), (0, 0.05)):
+        r = ws.validate_edges_indexed(nn, meth, par, a, b)
+        L = ur5_oracle.straight_lengths(nodes[a], nodes[b])
+        e = ur5_oracle.validate_edges(meth, par, nodes[a], nodes[b], L)
+        assert np.array_equal(r["length"], L)
+        for k in ("valid", "reason", "pair", "t_last_valid"):
+            assert np.array_equal(r[k], e[k]), (meth, k)
+        assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+    with pytest.raises(ValueError):
+        ws.validate_edges_indexed(nn, 1, 1e-3, [0, 5000], [1, 2])
+    with pytest.raises(ValueError):
+        ws.validate_edges_indexed(nn, 1, 1e-3, [0, -1], [1, 2])
+
+
+def test_knn_single_query_latency_path(pkg, eng, ur5, ob):
+    """One query per call (BiRRT's nearestNode): the one-kernel path (query in the parameter block, last CTA merges and
+    writes the result to mapped pinned memory) == the oracle == the tiled scan it replaces, ties by node index, component
+    filter, fewer than k candidates, repeated calls (the ticket counter is reset by the kernel)."""
+    import os
+    humanoid = pkg.ModelDescription.load("humanoid_ff_obst6.json")
+    for desc, n in ((ur5, 70001), (humanoid, 9000)):  # revolute chain / free-flyer root (SO(3) distance)
+        m = pkg.Model(desc)
+        o = ob.Oracle(desc)
+        nn = pkg.NearestNeighbor(m, 0)
+        nodes = pkg.uniform_configs(desc, n, seed=301)
+        nodes[n - 1] = nodes[17]  # exact duplicate: the earlier node wins
+        cc = (np.arange(n) % 3).astype(np.int32)
+        nn.append(nodes, cc)
+        o.knn_append(nodes, cc)
+        os.environ["HPPB200_KNN_LATENCY"] = "0"
+        try:
+            tiled = pkg.NearestNeighbor(m, 0)
+        finally:
+            del os.environ["HPPB200_KNN_LATENCY"]
+        tiled.append(nodes, cc)
+        qs = pkg.uniform_configs(desc, 12, seed=302)
+        qs[0] = nodes[17]
+        for k, c in ((1, -1), (1, 1), (3, 2), (10, -1), (32, -1), (32, 0)):
+            for q in qs:
+                gi, gd = nn.query(q[None, :], k, c)
+                oi, od = o.knn_query(q[None, :], k, c)
+                srt = np.lexsort((oi, od), axis=1)
+                oi, od = np.take_along_axis(oi, srt, axis=1), np.take_along_axis(od, srt, axis=1)
+                ti, td = tiled.query(q[None, :], k, c)
+                assert np.array_equal(gi, oi) and np.array_equal(gd, od), (desc.name, k, c)
+                assert np.array_equal(gi, ti) and np.array_equal(gd, td)
+        assert nn.query(qs[:1], 1)[0][0, 0] == 17
+    small = pkg.NearestNeighbor(pkg.Model(ur5), 0)
+    small.append(pkg.uniform_configs(ur5, 3, seed=303))
+    gi, gd = small.query(pkg.uniform_configs(ur5, 1, seed=304), 10)
+    assert np.array_equal(gi[0, 3:], -np.ones(7, np.int64)) and np.all(np.isinf(gd[0, 3:])) and sorted(gi[0, :3]) == [0, 1, 2]

@@ -100,3 +100,81 @@ def test_random_shortcut_speculative_equals_sequential(pkg, ob, ur5, loops):
     L0, L1 = o.straight_lengths(way[:-1], way[1:]).sum(), o.straight_lengths(wb[:-1], wb[1:]).sum()
     assert L1 < L0 and np.array_equal(wb[0], way[0]) and np.array_equal(wb[-1], way[-1])
     assert o.validate_edges(1, 1e-3, wb[:-1], wb[1:], o.straight_lengths(wb[:-1], wb[1:]))["valid"].all()  # still collision free
+
+
+def _planned_path(pkg, ob, ur5, seed=4):
+    q0, q1 = _free_pair(pkg, ob, ur5)
+    planner = pkg.BiRRTPlanner(OracleBackend(ob.Oracle(ur5), 1, 1e-3), ur5, q0, q1, seed=seed)
+    planner.solve(max_steps=400)
+    assert planner.solved()
+    way = planner.roadmap.nodes[planner.path()]
+    assert len(way) > 3
+    return way
+
+
+def test_simple_shortcut_all_pairs_batch_and_astar(pkg, ob, ur5):
+    """SimpleShortcut::optimize (src/path-optimization/simple-shortcut.cc:51-83): every non-adjacent waypoint pair
+    validated in one batch, then the A* of src/astar.hh.  The result is checked against the definition: it is the
+    shortest path of the graph {own edges + valid shortcuts} (exhaustive dynamic programme over the DAG), its edges are
+    valid, and it starts / ends where the input does."""
+    way = _planned_path(pkg, ob, ur5)
+    o = ob.Oracle(ur5)
+    opt = pkg.SimpleShortcut(OracleBackend(o, 1, 1e-3))
+    res = opt.optimize(way)
+    n = len(way)
+    assert opt.validated == (n - 1) * (n - 2) // 2
+    assert np.array_equal(res[0], way[0]) and np.array_equal(res[-1], way[-1])
+    Lr = o.straight_lengths(res[:-1], res[1:])
+    assert o.validate_edges(1, 1e-3, res[:-1], res[1:], Lr)["valid"].all()
+    # brute force: best[j] = min over i < j with an edge i -> j
+    best, INF = [0.0] + [np.inf] * (n - 1), np.inf
+    for j in range(1, n):
+        for i in range(j):
+            L = o.straight_lengths(way[i:i + 1], way[j:j + 1])
+            ok = j == i + 1 or bool(o.validate_edges(1, 1e-3, way[i:i + 1], way[j:j + 1], L)["valid"][0])
+            if ok and best[i] + float(L[0]) < best[j]:
+                best[j] = best[i] + float(L[0])
+    assert abs(float(Lr.sum()) - best[-1]) <= 1e-12 * best[-1]
+    assert float(Lr.sum()) <= float(o.straight_lengths(way[:-1], way[1:]).sum())
+    # every waypoint of the result is one of the input waypoints, in order
+    idx = [int(np.nonzero((way == r).all(axis=1))[0][0]) for r in res]
+    assert idx == sorted(idx) and idx[0] == 0 and idx[-1] == n - 1
+    # two waypoints: nothing to do
+    assert np.array_equal(opt.optimize(way[:2]), way[:2])
+
+
+def test_simple_shortcut_astar_replay_tie_rule():
+    """the A* replay keeps the reference's containers: with two routes of equal cost the one found first stays
+    (strict '<' on the cost from start, src/astar.hh:121), and the open list is re-sorted stably"""
+    from hpp_core_b200.planners import SimpleShortcut
+    out = [[(1, 1.0), (2, 1.0)], [(3, 1.0)], [(3, 1.0)], []]
+    assert SimpleShortcut._astar(out, [0.0, 0.0, 0.0, 0.0], 3) == [0, 1, 3]
+    out = [[(1, 1.0), (2, 0.5)], [(3, 1.0)], [(3, 1.0)], []]
+    assert SimpleShortcut._astar(out, [0.0, 0.0, 0.0, 0.0], 3) == [0, 2, 3]
+
+
+def test_partial_shortcut_speculative_equals_sequential(pkg, ob, ur5):
+    """PartialShortcut::optimize, default parameters (src/path-optimization/partial-shortcut.cc:84-98,186-223): the
+    speculative batch form adopts the same joints in the same order as the joint-by-joint loop, with fewer calls;
+    an adopted joint moves linearly in arc length between the end configurations, the others keep their waypoints."""
+    way = _planned_path(pkg, ob, ur5, seed=6)
+    o = ob.Oracle(ur5)
+    seq = pkg.PartialShortcut(OracleBackend(ob.Oracle(ur5), 1, 1e-3), ur5)
+    bat = pkg.PartialShortcut(OracleBackend(ob.Oracle(ur5), 1, 1e-3), ur5)
+    ws, wb = seq.optimize(way), bat.optimize(way, batch=True)
+    assert np.array_equal(ws, wb) and seq.failed_joints == bat.failed_joints
+    assert seq.validation_calls == ur5.njoints and bat.validation_calls <= seq.validation_calls
+    assert ws.shape == way.shape and np.array_equal(ws[0], way[0]) and np.array_equal(ws[-1], way[-1])
+    L = o.straight_lengths(ws[:-1], ws[1:])
+    assert o.validate_edges(1, 1e-3, ws[:-1], ws[1:], L)["valid"].all()
+    for j in range(ur5.njoints):
+        if j in seq.failed_joints:
+            continue
+        d = np.diff(ws[:, j])
+        assert np.all(d >= -1e-12) or np.all(d <= 1e-12)  # monotone between the two ends
+    for j in seq.failed_joints:
+        assert np.array_equal(ws[:, j], way[:, j])
+    assert len(seq.failed_joints) < ur5.njoints  # the planned path is not already optimal
+    # a single straight path: generatePath returns null for every joint (rkAtP2 == rkAtP1)
+    one = pkg.PartialShortcut(OracleBackend(ob.Oracle(ur5), 1, 1e-3), ur5)
+    assert np.array_equal(one.optimize(way[:2]), way[:2]) and one.failed_joints == list(range(ur5.njoints))
