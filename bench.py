@@ -590,6 +590,27 @@ def run_b200(args):
                 ti, td = nn.query(qs, kk)
                 knn[label]["identical_to_tensor_core_path"] = bool(np.array_equal(ti, idx) and np.array_equal(td, dd))
         del nn_exact
+        # the single-query kernel alone (BiRRT's nearestNode): CUDA events on the mirror's stream around the one launch,
+        # against the HBM copy peak: the node stream (8 nq bytes per node) is all it reads
+        os.environ["HPPB200_KNN_TIMING"] = "1"
+        nn_t = pkg.NearestNeighbor(model, local_rank)
+        del os.environ["HPPB200_KNN_TIMING"]
+        nn_t.append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
+        q1 = pkg.uniform_configs(desc, 1, seed=SEED + 3)
+        for kk in (1, 10):
+            ms = []
+            for _ in range(30):
+                nn_t.query(q1, kk)
+                t_ms, nbytes = nn_t.latency_time()
+                if t_ms > 0:
+                    ms.append(t_ms)
+            if ms:
+                med = sorted(ms)[len(ms) // 2]
+                gbs = nbytes / (med * 1e-3) / 1e9
+                knn["q1_k%d" % kk]["kernel"] = {"ms": med, "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s",
+                                                                          "frac": gbs / hbm_peak, "bytes_per_node": 8 * nq,
+                                                                          "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}}
+        del nn_t
         if not args.no_cpu:
             orc.knn_append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
             qs = pkg.uniform_configs(desc, 64, seed=SEED + 3)

@@ -51,12 +51,12 @@ ABI_SYMBOLS = [
     "hppb200_workspace_create", "hppb200_workspace_destroy", "hppb200_get_stats", "hppb200_workspace_set_stream",
     "hppb200_validate_configs", "hppb200_validate_configs_noalloc", "hppb200_geometry_placements", "hppb200_pair_distances", "hppb200_all_collisions", "hppb200_model_num_distance_pairs",
     "hppb200_distance_between_objects",
-    "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edges_indexed", "hppb200_validate_edge_chains", "hppb200_workspace_set_max_iterations",
+    "hppb200_straight_lengths", "hppb200_path_eval", "hppb200_validate_edges", "hppb200_validate_edges_indexed", "hppb200_validate_edge_chains", "hppb200_validate_spline_edges", "hppb200_workspace_set_max_iterations",
     "hppb200_multi_create", "hppb200_multi_destroy", "hppb200_multi_num_devices", "hppb200_multi_workspace",
     "hppb200_multi_validate_configs", "hppb200_multi_validate_edges",
     "hppb200_pack_mask", "hppb200_unpack_mask", "hppb200_knn_merge_shards",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_set_labels", "hppb200_knn_size",
-    "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_tc_debug_tile",
+    "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_latency_time", "hppb200_knn_tc_debug_tile",
 ]
 
 _LIB = None
@@ -316,6 +316,34 @@ class Workspace:
                                                   _p(pair, _ip), _p(reason, _u8p), _p(bad, _ip)))
         return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, first_bad_edge=bad)
 
+    def validate_spline_edges(self, method, param, base, params, L, reverse=False, check_bounds=False):
+        """edges that are path::Spline<BernsteinBasis, 3> (tests/test-continuous-validation.cc:288-427):
+        base [n][nq], params [n][4][nv], L [n]; same outputs as validate_edges"""
+        nq = self.model.nq
+        base = np.ascontiguousarray(base, np.float64).reshape(-1, nq)
+        params = np.ascontiguousarray(params, np.float64).reshape(base.shape[0], 4, nq)
+        L = np.ascontiguousarray(L, np.float64)
+        n = base.shape[0]
+        valid, reason = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        t_fail, t_last = np.zeros(n), np.zeros(n)
+        pair = np.full(n, -1, np.int32)
+        _check(lib().hppb200_validate_spline_edges(self.h, C.c_int(method), C.c_double(param), C.c_int(1 if reverse else 0),
+                                                   _p(base, _dp), _p(params, _dp), _p(L, _dp), C.c_size_t(n),
+                                                   C.c_uint32(CHECK_JOINT_BOUNDS if check_bounds else 0), _p(valid, _u8p),
+                                                   _p(t_fail, _dp), _p(t_last, _dp), _p(pair, _ip), _p(reason, _u8p)))
+        return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason)
+
+
+def spline_steer(q1, v1, q2, v2, L):
+    """steeringMethod::Spline<BernsteinBasis, 3>::steer(q1, {1}, v1, q2, {1}, v2, L) (reference
+    src/steering-method/spline.cc:75-142) for vector-space configurations, in closed form: the cubic Bezier curve over
+    [0, L] from q1 to q2 with end velocities v1, v2 (base = q1; control points 0, L v1 / 3, (q2 - q1) - L v2 / 3, q2 - q1).
+    The reference solves the same 4 x 4 system with a Jacobi SVD: equal up to rounding.  Returns (base, params [.., 4, nv])."""
+    q1, v1, q2, v2 = (np.asarray(x, np.float64) for x in (q1, v1, q2, v2))
+    L = np.asarray(L, np.float64)[..., None]
+    d = q2 - q1
+    return q1.copy(), np.stack([np.zeros_like(d), L * v1 / 3.0, d - L * v2 / 3.0, d], axis=-2)
+
 
 class MultiGpu:
     """hppb200_multi_*: a device list, sharded internally (host arrays in, host arrays out)."""
@@ -417,6 +445,12 @@ class NearestNeighbor:
         _check(lib().hppb200_knn_tc_filter_time(self.h, C.byref(ms), C.byref(pairs)))
         return dict(used=bool(out[0]), stages=int(out[1]), redone=int(out[2]), candidates=int(out[3]),
                     filter_ms=ms.value, filter_pairs=pairs.value)
+
+    def latency_time(self):
+        """(ms, bytes scanned) of the single-query kernel of the last query (mirror created under HPPB200_KNN_TIMING=1)"""
+        ms, nbytes = C.c_double(0), C.c_double(0)
+        _check(lib().hppb200_knn_latency_time(self.h, C.byref(ms), C.byref(nbytes)))
+        return ms.value, nbytes.value
 
     def tc_debug_tile(self, queries, swap_offsets=0):
         queries = np.ascontiguousarray(queries, np.float64).reshape(-1, self.model.nq)

@@ -421,6 +421,51 @@ int hppb200_validate_edges(hppb200_workspace* wsp, int method, double param, int
   });
 }
 
+int hppb200_validate_spline_edges(hppb200_workspace* wsp, int method, double param, int reverse, const double* base,
+                                  const double* params, const double* L, size_t n, uint32_t flags, uint8_t* valid, double* t_fail,
+                                  double* t_last_valid, int32_t* pair, uint8_t* reason) {
+  return guarded([&] {
+    if (!wsp || (n && (!base || !params || !L || !valid))) throw std::invalid_argument("null argument");
+    if (method == HPPB200_METHOD_PROGRESSIVE && !(param > 0))
+      throw std::runtime_error("tolerance should be positive for progressive continuous validation.");  // progressive.cc:138-145
+    if (method == HPPB200_METHOD_DICHOTOMY && param != 0)
+      throw std::runtime_error("Dichotomy path validation method does not support penetration.");  // dichotomy.cc:139-148
+    if (method == HPPB200_METHOD_DISCRETIZED && !(param > 0)) throw std::invalid_argument("step size must be positive");
+    if (method < HPPB200_METHOD_DISCRETIZED || method > HPPB200_METHOD_DICHOTOMY) throw std::invalid_argument("unknown method");
+    Workspace* ws = &wsp->impl;
+    HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
+    const size_t nq = (size_t)ws->model->nq;
+    if (ws->model->nq != ws->model->nv)
+      throw std::invalid_argument("spline paths: vector-space configuration spaces only (no free-flyer joints)");
+    if (flags & HPPB200_DEVICE_POINTERS) {
+      Timed tm(ws);
+      launchValidateSplineEdges(ws, method, param, reverse, base, params, L, n, flags, valid, t_fail, t_last_valid, pair, reason);
+      tm.stop();
+      return;
+    }
+    ws->d_q.reserve(n * nq);
+    ws->d_q2.reserve(n * 4 * nq);
+    ws->d_L.reserve(n);
+    ws->d_valid.reserve(n);
+    ws->d_reason.reserve(n);
+    ws->d_pair.reserve(n);
+    ws->d_tfail.reserve(n);
+    ws->d_tlast.reserve(n);
+    Timed tm(ws);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, base, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q2.p, params, n * 4 * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_L.p, L, n * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    launchValidateSplineEdges(ws, method, param, reverse, ws->d_q.p, ws->d_q2.p, ws->d_L.p, n, flags, ws->d_valid.p, ws->d_tfail.p,
+                              ws->d_tlast.p, ws->d_pair.p, ws->d_reason.p);
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_valid.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    if (t_fail) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_fail, ws->d_tfail.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    if (t_last_valid) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_last_valid, ws->d_tlast.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+    if (pair) HPPB200_CUDA_CHECK(cudaMemcpyAsync(pair, ws->d_pair.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));
+    if (reason) HPPB200_CUDA_CHECK(cudaMemcpyAsync(reason, ws->d_reason.p, n, cudaMemcpyDeviceToHost, ws->stream));
+    tm.stop();
+  });
+}
+
 int hppb200_validate_edge_chains(hppb200_workspace* wsp, int method, double param, int reverse, const double* q1, const double* q2,
                                  const double* L, size_t n_edges, const int32_t* chain_begin, size_t n_chains, uint32_t flags,
                                  uint8_t* valid, double* t_fail, double* t_last_valid, int32_t* pair, uint8_t* reason,

@@ -233,6 +233,9 @@ bool launchDichotomyTail(Workspace* ws, double tol, int reverse, const double* d
 void launchChainReduce(Workspace* ws, const int32_t* d_chainBegin, size_t nChains, int reverse, const double* d_L, const uint8_t* eValid,
                        const double* eTfail, const double* eTlast, const int32_t* ePair, const uint8_t* eReason, uint8_t* valid,
                        double* tFail, double* tLast, int32_t* pair, uint8_t* reason, int32_t* firstBad);
+void launchValidateSplineEdges(Workspace* ws, int method, double param, int reverse, const double* d_base, const double* d_params,
+                               const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid, double* d_tfail, double* d_tlast,
+                               int32_t* d_pair, uint8_t* d_reason);
 void launchGatherEdgeEnds(cudaStream_t stream, const double* nodes, size_t nNodes, int nq, const int64_t* a, const int64_t* b, size_t n,
                           double* q1, double* q2, unsigned* bad);
 void launchPackMask(cudaStream_t stream, const uint8_t* valid, size_t n, uint32_t* bits);

@@ -28,6 +28,7 @@
 #include <cstdlib>
 
 #include "dev_model.cuh"
+#include "dev_spline.cuh"
 
 namespace hppb200 {
 
@@ -51,6 +52,7 @@ struct EdgeScratch {
 struct EdgeArgs {
   const double* q1;
   const double* q2;
+  const double* P;  // spline edges: parameters [n][4][nv] (q1 = base configurations, q2 unused)
   const double* L;
   size_t n;
   uint32_t flags;
@@ -119,7 +121,10 @@ __device__ __forceinline__ bool ivContains(const double* lo, const double* hi, s
   return false;
 }
 
-template <int METHOD, bool TREE>
+// SPLINE: the edges are path::Spline<BernsteinBasis, 3> (dev_spline.cuh) instead of StraightPaths: A.q1 holds the base
+// configurations, A.P the parameters; BodyPairCollision refines its velocity bound on sub-intervals (refine_ = true,
+// body-pair-collision.cc:119-173).  Everything else -- sampling loops, skip rules, interval sets -- is path-independent.
+template <int METHOD, bool TREE, bool SPLINE = false>
 __global__ void __launch_bounds__(EDGE_THREADS)
 edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -164,6 +169,8 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
   size_t e = 0;
   const double* q1 = nullptr;
   const double* q2 = nullptr;
+  const double* Pp = nullptr;  // SPLINE: this edge's parameters
+  SplineQ sq;                  // SPLINE: the current sample
   double L = 0, t = 0, lastValid = 0, u = 0;
   int qmode = 0;  // 0: initial config, 1: end config, 2: interpolate
   int finished = 0;
@@ -215,7 +222,8 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
           else {
             e = A.edge_list ? (size_t)A.edge_list[idx] : (size_t)idx;
             q1 = A.q1 + e * (size_t)mv.nq;
-            q2 = A.q2 + e * (size_t)mv.nq;
+            q2 = SPLINE ? nullptr : A.q2 + e * (size_t)mv.nq;
+            if (SPLINE) Pp = A.P + e * 4 * (size_t)mv.nq;
             L = A.L[e];
             if (!DISC && A.mode == 2) {
               // resume after the first sample
@@ -260,16 +268,20 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
       } else {
         ++iters;
         ++samples;
-        // Path::eval -> StraightPath::impl_compute: stored end points are returned bit-exactly
-        if (t == 0.0 || L == 0.0) qmode = 0;
-        else if (t == L) qmode = 1;
-        else { qmode = 2; u = (t - 0.0) / L; }
+        if (SPLINE) {
+          sq = splineQ(q1, Pp, mv.nq, t, L);  // Spline::impl_compute: u clamped to [0, 1], no end-point shortcut
+        } else {
+          // Path::eval -> StraightPath::impl_compute: stored end points are returned bit-exactly
+          if (t == 0.0 || L == 0.0) qmode = 0;
+          else if (t == L) qmode = 1;
+          else { qmode = 2; u = (t - 0.0) / L; }
+        }
         int bad = -1;
         if (DISC && (A.flags & HPPB200_CHECK_JOINT_BOUNDS)) {
           for (int k = 0; k < mv.nq && bad < 0; ++k) {
             const double lo = T.lower[k], hi = T.upper[k];
             if (lo > hi) continue;
-            const double v = EdgeQ{q1, q2, qmode, u}(k);
+            const double v = SPLINE ? sq(k) : EdgeQ{q1, q2, qmode, u}(k);
             if (v < lo || hi < v) bad = k;
           }
         }
@@ -277,7 +289,10 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
         else work = true;
       }
     }
-    if (work) forwardKinematics<TREE>(T, mv, EdgeQ{q1, q2, qmode, u}, store, NS);
+    if (work) {
+      if (SPLINE) forwardKinematics<TREE>(T, mv, sq, store, NS);
+      else forwardKinematics<TREE>(T, mv, EdgeQ{q1, q2, qmode, u}, store, NS);
+    }
 
     // ================= C. pairs ======================================================================
     if (DISC) {
@@ -408,8 +423,9 @@ edgeWalkerKernel(ModelView mv, EdgeArgs A, EdgeScratch S, DeviceStats* stats) {
               double hd, ht;
               if (dlb == INF) { hd = INF; ht = 0; }
               else {
-                const double Vm = maximalVelocity(B);
-                hd = dlb / Vm;
+                double Vm;
+                if (SPLINE) hd = splineCollisionFreeInterval(T, B, Pp, mv.nq, L, t, dlb, Vm);
+                else { Vm = maximalVelocity(B); hd = dlb / Vm; }
                 ht = (Vm != 0) ? 2 * A.param / Vm : INF;
               }
               const double a = t - (hd + ht), b = t + (hd + ht);
@@ -575,10 +591,10 @@ __global__ void collectOverflowKernel(const uint8_t* __restrict__ reason, size_t
   if (i < n && reason[i] == REASON_OVERFLOW_INTERNAL) list[atomicAdd(count, 1ull)] = (uint32_t)i;
 }
 
-template <int METHOD>
+template <int METHOD, bool SPLINE = false>
 static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS, size_t maxSlots) {
   const bool tree = modelIsTree(ws->model);
-  auto kern = tree ? edgeWalkerKernel<METHOD, true> : edgeWalkerKernel<METHOD, false>;
+  auto kern = tree ? edgeWalkerKernel<METHOD, true, SPLINE> : edgeWalkerKernel<METHOD, false, SPLINE>;
   const ModelView& mv = ws->view;
   size_t smemBytes = 16 + mv.blob_bytes;
   const size_t nbp0 = METHOD == HPPB200_METHOD_DISCRETIZED ? 0 : (size_t)mv.nbodypairs;
@@ -758,6 +774,50 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   const size_t slots2 = 2048;  // 255-entry lists: ~4 KB per body pair per slot
   if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE>(ws, A, 255, 1, slots2);
   else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY>(ws, A, 255, 2048, slots2);
+}
+
+// Edges that are path::Spline<BernsteinBasis, 3> (reference tests/test-continuous-validation.cc:288-427):
+// the lane-per-edge walker with the spline's eval / velocityBound and the two-round refinement of BodyPairCollision.
+void launchValidateSplineEdges(Workspace* ws, int method, double param, int reverse, const double* d_base, const double* d_params,
+                               const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid, double* d_tfail, double* d_tlast,
+                               int32_t* d_pair, uint8_t* d_reason) {
+  if (n == 0) return;
+  if (n > 0xffffffffull) throw std::invalid_argument("at most 2^32-1 edges per call");
+  if (ws->view.nbodypairs > 65535) throw std::runtime_error("too many body pairs");
+  if (ws->model->nq != ws->model->nv) throw std::invalid_argument("spline paths: vector-space configuration spaces only (no free-flyer joints)");
+  if (!d_reason) {
+    ws->d_reason_int.reserve(n);
+    d_reason = ws->d_reason_int.p;
+  }
+  EdgeArgs A{};
+  A.q1 = d_base; A.q2 = nullptr; A.P = d_params; A.L = d_L; A.n = n; A.flags = flags; A.reverse = reverse; A.param = param;
+  A.max_iter = ws->max_iterations;
+  A.valid = d_valid; A.t_fail = d_tfail; A.t_last = d_tlast; A.pair = d_pair; A.reason = d_reason;
+  A.overflow_reason = REASON_OVERFLOW_INTERNAL;
+  const size_t allSlots = ~size_t(0);
+  if (method == HPPB200_METHOD_DISCRETIZED) { launchEdgeWalker<HPPB200_METHOD_DISCRETIZED, true>(ws, A, 1, 1, allSlots); return; }
+  DeviceStats before, after;
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
+  // (Progressive keeps one connected validated interval per body pair whatever the path: the next sample lies inside
+  //  every pair's last interval.  Dichotomy: short lists, the edges that outgrow them are redone with long ones.)
+  if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE, true>(ws, A, 1, 1, allSlots);
+  else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY, true>(ws, A, 12, 96, allSlots);
+  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&after, ws->d_stats, sizeof(after), cudaMemcpyDeviceToHost, ws->stream));
+  HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+  const unsigned long long nover = after.overflow - before.overflow;
+  if (nover == 0) return;
+  ws->d_list.reserve(nover + 1);
+  ws->d_count.reserve(1);
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(ws->d_count.p, 0, sizeof(unsigned long long), ws->stream));
+  collectOverflowKernel<<<(unsigned)((n + 255) / 256), 256, 0, ws->stream>>>(d_reason, n, ws->d_list.p, ws->d_count.p);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+  ws->stats.kernel_launches += 1;
+  A.edge_list = ws->d_list.p;
+  A.n = (size_t)nover;
+  A.overflow_reason = HPPB200_REASON_ITER_CAP;
+  const size_t slots2 = 2048;
+  if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE, true>(ws, A, 255, 1, slots2);
+  else launchEdgeWalker<HPPB200_METHOD_DICHOTOMY, true>(ws, A, 255, 2048, slots2);
 }
 
 }  // namespace hppb200

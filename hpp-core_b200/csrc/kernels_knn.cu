@@ -335,6 +335,7 @@ int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out) {
       HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&nn->h_stage, KNN_STAGE_BYTES, cudaHostAllocMapped));
       HPPB200_CUDA_CHECK(cudaHostGetDevicePointer((void**)&nn->d_stage_map, nn->h_stage, 0));  // the single-query kernel writes its result here
       if (const char* v = std::getenv("HPPB200_KNN_LATENCY")) nn->lat_enabled = std::atoi(v) != 0;
+      if (const char* v = std::getenv("HPPB200_KNN_TIMING")) nn->lat_timing = std::atoi(v) != 0;
     }
     knnTcInit(nn);
     *out = nn;
@@ -346,6 +347,8 @@ void hppb200_knn_destroy(hppb200_knn* nn) {
   if (nn->d_nodes) cudaFree(nn->d_nodes);
   if (nn->d_cc) cudaFree(nn->d_cc);
   knnTcDestroy(nn);
+  if (nn->lat_ev0) cudaEventDestroy(nn->lat_ev0);
+  if (nn->lat_ev1) cudaEventDestroy(nn->lat_ev1);
   if (nn->h_stage) cudaFreeHost(nn->h_stage);
   if (nn->stream) cudaStreamDestroy(nn->stream);
   delete nn;
@@ -418,12 +421,14 @@ int hppb200_knn_query(hppb200_knn* nn, const double* queries, size_t nqueries, i
       // a planner's single query: one kernel (query in the parameter block, result written to mapped pinned memory by
       // the last CTA), one synchronisation
       nn->tc_last_used = false;
+      nn->lat_last_used = true;
       knnLatencyRun(nn, queries, k, cc, (long long*)nn->d_stage_map, (double*)(nn->d_stage_map + 32 * sizeof(long long)));
       HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));
       std::memcpy(idx, nn->h_stage, (size_t)k * sizeof(int64_t));
       std::memcpy(dist, nn->h_stage + 32 * sizeof(long long), (size_t)k * sizeof(double));
       return;
     }
+    nn->lat_last_used = false;
     if (flags & HPPB200_DEVICE_POINTERS) {
       run(queries, (long long*)idx, dist);
       HPPB200_CUDA_CHECK(cudaStreamSynchronize(nn->stream));

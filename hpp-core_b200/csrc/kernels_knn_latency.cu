@@ -18,6 +18,7 @@
 #include "knn_latency.hpp"
 
 namespace hppb200 {
+void setLastError(const std::string& s);
 
 constexpr int LAT_THREADS = 256;
 constexpr int LAT_WARPS = LAT_THREADS / 32;
@@ -158,8 +159,28 @@ void knnLatencyRun(hppb200_knn* nn, const double* h_query, int k, int32_t cc, lo
   unsigned* ticket = (unsigned*)nn->d_lat.p;
   Key* partial = (Key*)(nn->d_lat.p + 256);
   auto kern = nn->ff ? knnLatencyKernel<true> : knnLatencyKernel<false>;
+  if (nn->lat_timing) {
+    if (!nn->lat_ev0) { HPPB200_CUDA_CHECK(cudaEventCreate(&nn->lat_ev0)); HPPB200_CUDA_CHECK(cudaEventCreate(&nn->lat_ev1)); }
+    HPPB200_CUDA_CHECK(cudaEventRecord(nn->lat_ev0, nn->stream));
+  }
   kern<<<grid, LAT_THREADS, 0, nn->stream>>>(nn->view, nn->d_nodes, nn->d_cc, nn->n, Q, cc, k, partial, ticket, outIdx, outDist);
   HPPB200_CUDA_CHECK(cudaGetLastError());
+  if (nn->lat_timing) HPPB200_CUDA_CHECK(cudaEventRecord(nn->lat_ev1, nn->stream));
 }
 
 }  // namespace hppb200
+
+extern "C" int hppb200_knn_latency_time(hppb200_knn* nn, double* ms, double* bytes) {
+  if (!nn || !ms || !bytes) { hppb200::setLastError("null argument"); return HPPB200_ERR_INVALID_ARGUMENT; }
+  *ms = 0.0;
+  *bytes = 0.0;
+  if (!nn->lat_last_used || !nn->lat_timing || !nn->lat_ev0) return HPPB200_OK;
+  float f = 0;
+  if (cudaSetDevice(nn->device) != cudaSuccess || cudaEventElapsedTime(&f, nn->lat_ev0, nn->lat_ev1) != cudaSuccess) {
+    hppb200::setLastError("CUDA: event timing of the single-query kernel failed");
+    return HPPB200_ERR_CUDA;
+  }
+  *ms = (double)f;
+  *bytes = (double)nn->n * (double)nn->model->nq * sizeof(double);
+  return HPPB200_OK;
+}

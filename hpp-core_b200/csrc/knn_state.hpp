@@ -20,6 +20,9 @@ struct hppb200_knn {
   // single-query path (kernels_knn_latency.cu): ticket counter (first 256 B) + per-CTA candidate lists
   hppb200::DeviceBuffer<unsigned char> d_lat;
   bool lat_ticket_zeroed = false;
+  bool lat_timing = false;  // HPPB200_KNN_TIMING=1: events around the single-query kernel (hppb200_knn_latency_time)
+  bool lat_last_used = false;
+  cudaEvent_t lat_ev0 = nullptr, lat_ev1 = nullptr;
   bool lat_enabled = true;  // HPPB200_KNN_LATENCY (0: single queries go through the tiled scan as before)
 
   // ---- tensor-core candidate pass (kernels_knn_tc.cu) ----

@@ -328,6 +328,18 @@ int hppb200_validate_edges(hppb200_workspace* ws, int method, double param,
                            const double* L, size_t n, uint32_t flags,
                            uint8_t* valid, double* t_fail, double* t_last_valid,
                            int32_t* pair, uint8_t* reason);
+/* Edges that are path::Spline<BernsteinBasis, 3> (reference include/hpp/core/path/spline.hh, src/path/spline.cc; what
+   steeringMethod::Spline<BernsteinBasis, 3>::steer returns, src/steering-method/spline.cc:75-142, and the path type of
+   the reference's non-straight validation test, tests/test-continuous-validation.cc:288-427): spline i is
+   q(t) = base_i + sum_k b_k((t - 0) / L_i) params_i[k], t in [0, L_i], b_k the cubic Bernstein polynomials; base
+   [n][nq] = Spline::base(), params [n][4][nv] row-major = Spline::parameters(), L [n] = the time range.  Same methods,
+   outputs and error behaviour as hppb200_validate_edges.  The continuous methods use Spline::impl_velocityBound on
+   sub-intervals with the two-round refinement of BodyPairCollision::collisionFreeInterval (refine_ = true,
+   src/continuous-validation/body-pair-collision.cc:101-173).  Vector-space configuration spaces only (nq == nv: no
+   free-flyer joint), else HPPB200_ERR_INVALID_ARGUMENT. */
+int hppb200_validate_spline_edges(hppb200_workspace* ws, int method, double param, int reverse, const double* base,
+                                  const double* params, const double* L, size_t n, uint32_t flags, uint8_t* valid,
+                                  double* t_fail, double* t_last_valid, int32_t* pair, uint8_t* reason);
 /* A PathVector of StraightPaths per chain (what RandomShortcut and the other optimisers hand to the path validation):
    chain c = edges [chain_begin[c], chain_begin[c+1]) in path order; chain_begin has n_chains + 1 entries.  Replays the
    recursion of ContinuousValidation::validate (reference src/continuous-validation.cc:153-192) for Progressive and
@@ -418,6 +430,11 @@ int hppb200_knn_tc_stats(hppb200_knn* nn, int64_t* out /* [4] */);
 /* Device time (CUDA events on the mirror's stream) of the whole-roadmap tcgen05 filter pass of the last query and
    the (query, node) pairs it evaluated (padded to tiles): the kernel the k-NN roofline is reported on. */
 int hppb200_knn_tc_filter_time(hppb200_knn* nn, double* ms, double* pairs);
+/* Device time (CUDA events on the mirror's stream) of the single-query kernel of the last hppb200_knn_query call
+   that took the one-kernel path (one query in host memory, k <= 32; kernels_knn_latency.cu), and the bytes of the node
+   stream it scanned; 0 / 0 when the last call took another path.  The events are recorded only when the mirror was
+   created with HPPB200_KNN_TIMING=1 in the environment (two event records per call are not free at ~20 us). */
+int hppb200_knn_latency_time(hppb200_knn* nn, double* ms, double* bytes);
 /* Test hook: approximate squared distances (the TMEM accumulator) of up to 128 queries against the first 256
    nodes, out [128][256] row-major FP32; swap_offsets != 0 exchanges the descriptor byte offsets (bring-up). */
 int hppb200_knn_tc_debug_tile(hppb200_knn* nn, const double* queries, size_t nqueries, int swap_offsets,

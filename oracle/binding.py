@@ -181,6 +181,45 @@ class Oracle:
             raise RuntimeError(lib().oracle_last_error().decode())
         return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, samples=samples)
 
+    def _spline_args(self, base, params, L):
+        base = np.ascontiguousarray(base, np.float64).reshape(-1, self.nq)
+        params = np.ascontiguousarray(params, np.float64).reshape(base.shape[0], 4, self.nq)
+        return base, params, np.ascontiguousarray(L, np.float64)
+
+    def validate_spline_edges(self, method, param, base, params, L, reverse=False, check_bounds=False, max_iter=0, nthreads=0):
+        """edges that are path::Spline<BernsteinBasis, 3>: base [n][nq], params [n][4][nv], L [n]"""
+        base, params, L = self._spline_args(base, params, L)
+        n = base.shape[0]
+        valid, reason = np.zeros(n, np.uint8), np.zeros(n, np.uint8)
+        t_fail, t_last = np.zeros(n), np.zeros(n)
+        pair = np.zeros(n, np.int32)
+        samples = np.zeros(n, np.uint64)
+        rc = lib().oracle_validate_spline_edges(self.h, C.c_int(method), C.c_double(param), C.c_int(1 if reverse else 0),
+                                                _p(base, dp), _p(params, dp), _p(L, dp), C.c_size_t(n),
+                                                C.c_uint32(1 if check_bounds else 0), _p(valid, u8p), _p(t_fail, dp),
+                                                _p(t_last, dp), _p(pair, ip), _p(reason, u8p), _p(samples, u64p),
+                                                C.c_uint64(max_iter), C.c_int(nthreads))
+        if rc != 0:
+            raise RuntimeError(lib().oracle_last_error().decode())
+        return dict(valid=valid, t_fail=t_fail, t_last_valid=t_last, pair=pair, reason=reason, samples=samples)
+
+    def spline_eval(self, base, params, L, t):
+        base, params, L = self._spline_args(base, params, L)
+        t = np.ascontiguousarray(t, np.float64)
+        q = np.zeros_like(base)
+        if lib().oracle_spline_eval(self.h, _p(base, dp), _p(params, dp), _p(L, dp), _p(t, dp), C.c_size_t(base.shape[0]), _p(q, dp)) != 0:
+            raise RuntimeError(lib().oracle_last_error().decode())
+        return q
+
+    def spline_velocity_bound(self, base, params, L, ta, tb):
+        base, params, L = self._spline_args(base, params, L)
+        ta, tb = np.ascontiguousarray(ta, np.float64), np.ascontiguousarray(tb, np.float64)
+        vb = np.zeros_like(base)
+        if lib().oracle_spline_velocity_bound(self.h, _p(base, dp), _p(params, dp), _p(L, dp), _p(ta, dp), _p(tb, dp),
+                                              C.c_size_t(base.shape[0]), _p(vb, dp)) != 0:
+            raise RuntimeError(lib().oracle_last_error().decode())
+        return vb
+
     def validate_edge_chains(self, method, param, q1, q2, L, chain_begin, reverse=False, nthreads=0):
         q1 = np.ascontiguousarray(q1, np.float64).reshape(-1, self.nq)
         q2 = np.ascontiguousarray(q2, np.float64).reshape(-1, self.nq)

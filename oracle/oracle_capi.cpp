@@ -203,9 +203,13 @@ void oracle_straight_lengths(OracleHandle* h, const double* q1, const double* q2
   for (size_t i = 0; i < n; ++i) L[i] = weighedDistance(d, q1 + i * d.nq, q2 + i * d.nq);
 }
 
-int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse, const double* q1, const double* q2,
-                          const double* L, size_t n, uint32_t flags, uint8_t* valid, double* t_fail, double* t_last_valid,
-                          int32_t* pair, uint8_t* reason, uint64_t* samples, int order_mode, uint64_t max_iter, int nthreads) {
+}  // extern "C"
+
+// the edge loop of oracle_validate_edges, for any path type: makePath(i) builds edge i's path
+template <typename MakePath>
+static int validatePathsImpl(OracleHandle* h, int method, double param, int reverse, size_t n, uint32_t flags, uint8_t* valid, double* t_fail,
+                             double* t_last_valid, int32_t* pair, uint8_t* reason, uint64_t* samples, int order_mode, uint64_t max_iter,
+                             int nthreads, MakePath makePath) {
   const Device& d = *h->dev;
   if (nthreads <= 0) nthreads = omp_get_max_threads();
   if (order_mode == ORDER_PERSISTENT) nthreads = 1;  // history-dependent: sequential like one reference thread
@@ -223,7 +227,7 @@ int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse
       else { dich.reset(new Dichotomy(d, param)); dich->orderMode = order_mode; if (max_iter) dich->maxIterations = max_iter; }
 #pragma omp for schedule(dynamic, 16)
       for (long i = 0; i < (long)n; ++i) {
-        StraightPath path(d, q1 + (size_t)i * d.nq, q2 + (size_t)i * d.nq, L[i]);
+        const auto path = makePath((size_t)i);
         PathReport R;
         uint64_t ev = 0;
         if (disc) R = disc->validate(path, reverse != 0, &st);
@@ -246,6 +250,40 @@ int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse
   h->pairEvals += evals; h->samples += nsamples;
   h->stats.calls += calls; h->stats.iterations += iters; h->stats.closed += closed;
   return err;
+}
+
+extern "C" {
+
+int oracle_validate_edges(OracleHandle* h, int method, double param, int reverse, const double* q1, const double* q2,
+                          const double* L, size_t n, uint32_t flags, uint8_t* valid, double* t_fail, double* t_last_valid,
+                          int32_t* pair, uint8_t* reason, uint64_t* samples, int order_mode, uint64_t max_iter, int nthreads) {
+  const Device& d = *h->dev;
+  return validatePathsImpl(h, method, param, reverse, n, flags, valid, t_fail, t_last_valid, pair, reason, samples, order_mode, max_iter, nthreads,
+                           [&](size_t i) { return StraightPath(d, q1 + i * d.nq, q2 + i * d.nq, L[i]); });
+}
+
+// Spline<BernsteinBasis, 3> edges (tests/test-continuous-validation.cc:288-427): base [n][nq], params [n][4][nv], L [n]
+int oracle_validate_spline_edges(OracleHandle* h, int method, double param, int reverse, const double* base, const double* params,
+                                 const double* L, size_t n, uint32_t flags, uint8_t* valid, double* t_fail, double* t_last_valid,
+                                 int32_t* pair, uint8_t* reason, uint64_t* samples, uint64_t max_iter, int nthreads) {
+  const Device& d = *h->dev;
+  if (d.nq != d.nv) { g_err = "spline paths: vector-space configuration spaces only"; return 2; }
+  return validatePathsImpl(h, method, param, reverse, n, flags, valid, t_fail, t_last_valid, pair, reason, samples, ORDER_RESET_PER_EDGE, max_iter,
+                           nthreads, [&](size_t i) { return SplinePath(d, base + i * d.nq, params + i * 4 * (size_t)d.nv, L[i]); });
+}
+int oracle_spline_eval(OracleHandle* h, const double* base, const double* params, const double* L, const double* t, size_t n, double* q) {
+  const Device& d = *h->dev;
+  if (d.nq != d.nv) { g_err = "spline paths: vector-space configuration spaces only"; return 2; }
+  for (size_t i = 0; i < n; ++i) SplinePath(d, base + i * d.nq, params + i * 4 * (size_t)d.nv, L[i]).eval(q + i * d.nq, t[i]);
+  return 0;
+}
+// Path::velocityBound(t0, t1) of spline i: vb [n][nv]
+int oracle_spline_velocity_bound(OracleHandle* h, const double* base, const double* params, const double* L, const double* ta, const double* tb,
+                                 size_t n, double* vb) {
+  const Device& d = *h->dev;
+  if (d.nq != d.nv) { g_err = "spline paths: vector-space configuration spaces only"; return 2; }
+  for (size_t i = 0; i < n; ++i) SplinePath(d, base + i * d.nq, params + i * 4 * (size_t)d.nv, L[i]).velocityBound(vb + i * d.nv, ta[i], tb[i]);
+  return 0;
 }
 
 // ContinuousValidation::validate on a PathVector of StraightPaths (src/continuous-validation.cc:153-192), restated as the

@@ -71,6 +71,8 @@ struct SolidSolidCollision {
   Intervals validInterval_;  // boost::icl::interval_set of closed intervals
   double maximalVelocity_ = 0;
   interval_t timeRange;
+  const Path* path_ = nullptr;
+  bool refine_ = false;
 
   // solid-solid-collision.cc:162-198 — climb from the larger index
   std::vector<int> computeSequenceOfJoints() const {
@@ -128,17 +130,41 @@ struct SolidSolidCollision {
     return ab;
   }
   // body-pair-collision.cc:101-117 (StraightPath => refine_ = false)
-  void setPath(const StraightPath& path) {
+  void setPath(const Path& path) {
     valid_ = false;
     validInterval_.clear();
     timeRange = interval_t(path.t0, path.t1);
+    path_ = &path;
+    refine_ = !path.straight();
     if (path.t1 - path.t0 == 0) {
       maximalVelocity_ = kInf;
+      refine_ = false;
     } else {
       std::vector<double> Vb(dev->nv);
-      path.velocityBound(Vb.data());
+      path.velocityBound(Vb.data(), path.t0, path.t1);
       maximalVelocity_ = computeMaximalVelocity(Vb.data());
     }
+  }
+  // body-pair-collision.cc:119-173: two rounds of "velocity bound on the interval just found -> new interval"
+  double collisionFreeInterval(double t, double dlb, double& maxVelocity) const {
+    constexpr int Nrefine = 2;
+    double T[1 + 2 * Nrefine], Vm[1 + 2 * Nrefine];
+    Vm[0] = maxVelocity = maximalVelocity_;
+    T[0] = dlb / maxVelocity;
+    if (!refine_) return T[0];
+    double tm = t - T[0], tM = t + T[0];
+    const bool leftIsValid = tm < timeRange.first, rightIsValid = tM > timeRange.second;
+    if (leftIsValid && rightIsValid) return T[0];
+    std::vector<double> Vb(dev->nv);
+    for (int i = 0; i < 2 * Nrefine; ++i) {
+      tm = t - (leftIsValid ? 0 : T[i]);
+      tM = t + (rightIsValid ? 0 : T[i]);
+      path_->velocityBound(Vb.data(), tm, tM);
+      Vm[i + 1] = computeMaximalVelocity(Vb.data());
+      T[i + 1] = dlb / Vm[i + 1];
+    }
+    maxVelocity = Vm[2 * Nrefine];
+    return T[2 * Nrefine];
   }
   // body-pair-collision.cc:175-198
   bool computeDistanceLowerBound(double& dlb, const DeviceData& data, int& hit, GjkStats* st) const {
@@ -160,8 +186,8 @@ struct SolidSolidCollision {
     double halfLengthDist, halfLengthTol;
     if (dlb == kInf) { halfLengthDist = kInf; halfLengthTol = 0; }
     else {
-      double Vm = maximalVelocity_;
-      halfLengthDist = dlb / Vm;  // collisionFreeInterval :119-128, refine_ == false
+      double Vm;
+      halfLengthDist = collisionFreeInterval(t, dlb, Vm);  // (refine_ == false: dlb / maximalVelocity_, :119-128)
       halfLengthTol = (Vm != 0) ? 2 * tolerance / Vm : kInf;
     }
     interval.first = t - (halfLengthDist + halfLengthTol);
@@ -299,7 +325,7 @@ struct ContinuousValidation {
   }
 
   // src/continuous-validation.cc:193-205 (pool) + :216-222 (setPath)
-  std::vector<SolidSolidCollision>& acquire(const StraightPath& path) {
+  std::vector<SolidSolidCollision>& acquire(const Path& path) {
     if (orderMode == ORDER_RESET_PER_EDGE || pooled_.empty()) pooled_ = intervalValidations_;
     for (auto& b : pooled_) b.setPath(path);
     return pooled_;
@@ -311,7 +337,7 @@ struct Progressive : ContinuousValidation {
   Progressive(const Device& d, double tol) : ContinuousValidation(d, tol) {
     if (tol <= 0) throw std::runtime_error("tolerance should be positive for progressive continuous validation.");
   }
-  PathReport validate(const StraightPath& path, bool reverse, GjkStats* st = nullptr, uint64_t* evals = nullptr) {
+  PathReport validate(const Path& path, bool reverse, GjkStats* st = nullptr, uint64_t* evals = nullptr) {
     PathReport R;
     std::vector<SolidSolidCollision>& bpc = acquire(path);
     const interval_t tr(path.t0, path.t1);
@@ -349,7 +375,7 @@ struct Dichotomy : ContinuousValidation {
   Dichotomy(const Device& d, double tol) : ContinuousValidation(d, tol) {
     if (tol != 0) throw std::runtime_error("Dichotomy path validation method does not support penetration.");
   }
-  PathReport validate(const StraightPath& path, bool reverse, GjkStats* st = nullptr, uint64_t* evals = nullptr) {
+  PathReport validate(const Path& path, bool reverse, GjkStats* st = nullptr, uint64_t* evals = nullptr) {
     PathReport R;
     std::vector<SolidSolidCollision>& bpc = acquire(path);
     bool finished = false, valid = true;

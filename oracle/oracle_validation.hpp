@@ -222,16 +222,29 @@ inline double weighedDistance(const Device& dev, const double* q1, const double*
   return std::sqrt(res);
 }
 
-// src/straight-path.cc:91-158, src/steering-method/straight.cc:38-51
-struct StraightPath {
-  const Device* dev;
-  std::vector<double> initial, end;
+// include/hpp/core/path.hh: what the validation algorithms need of a path
+struct Path {
+  const Device* dev = nullptr;
   double t0 = 0, t1 = 0;  // paramRange == timeRange (no time parameterization)
-  StraightPath(const Device& d, const double* q1, const double* q2, double L)
-      : dev(&d), initial(q1, q1 + d.nq), end(q2, q2 + d.nq), t0(0), t1(L) {}
+  virtual ~Path() {}
+  virtual void eval(double* q, double param) const = 0;
+  // Path::velocityBound(result, t0, t1) on a sub-interval (impl_velocityBound)
+  virtual void velocityBound(double* vb, double ta, double tb) const = 0;
+  // BodyPairCollision::setupPath (body-pair-collision.cc:101-105): refine_ = path is not a StraightPath
+  virtual bool straight() const = 0;
   double length() const { return t1 - t0; }
+};
+
+// src/straight-path.cc:91-158, src/steering-method/straight.cc:38-51
+struct StraightPath : Path {
+  std::vector<double> initial, end;
+  StraightPath(const Device& d, const double* q1, const double* q2, double L) : initial(q1, q1 + d.nq), end(q2, q2 + d.nq) {
+    dev = &d; t0 = 0; t1 = L;
+  }
+  bool straight() const override { return true; }
+  void velocityBound(double* vb, double, double) const override { velocityBound(vb); }
   // impl_compute :91-110 — endpoints returned bit-exactly
-  void eval(double* q, double param) const {
+  void eval(double* q, double param) const override {
     const double L = t1 - t0;
     if (param == t0 || L == 0) { std::memcpy(q, initial.data(), sizeof(double) * dev->nq); return; }
     if (param == t1) { std::memcpy(q, end.data(), sizeof(double) * dev->nq); return; }
@@ -244,6 +257,77 @@ struct StraightPath {
     lieDifference(*dev, end.data(), initial.data(), vb);
     const double L = t1 - t0;
     for (int i = 0; i < dev->nv; ++i) vb[i] = std::fabs(vb[i]) / L;
+  }
+};
+
+// src/path/spline.cc, include/hpp/core/path/spline.hh: path::Spline<BernsteinBasis, 3>, the path type of the reference's
+// non-straight continuous-validation test (tests/test-continuous-validation.cc:288-427).  q(t) = base (+) P^T b(u),
+// u = (t - t0) / (t1 - t0) clamped to [0, 1], b the four cubic Bernstein polynomials, P [4][nv] the parameters
+// (tangent vectors at `base`).  Vector-space configuration spaces only (nq == nv: the (+) is a sum).
+struct SplinePath : Path {
+  std::vector<double> base, P;  // P row-major [4][nv]
+  SplinePath(const Device& d, const double* base_, const double* params, double L) : base(base_, base_ + d.nq), P(params, params + 4 * d.nv) {
+    if (d.nq != d.nv) throw std::runtime_error("spline paths: vector-space configuration spaces only");
+    dev = &d; t0 = 0; t1 = L;
+  }
+  bool straight() const override { return false; }
+  // spline_basis_function<BernsteinBasis, 3>::derivative (src/path/spline.cc:131-159), order k of the basis at t
+  static void basisDerivative(int k, double t, double res[4]) {
+    const int Degree = 3;
+    static const double factors[4] = {1, 1, 2, 6};
+    static const int binom[4][4] = {{1, 0, 0, 0}, {1, 1, 0, 0}, {1, 2, 1, 0}, {1, 3, 3, 1}};
+    for (int i = 0; i < 4; ++i) res[i] = 0;
+    if (k > Degree) return;
+    double pT[4], pO[4];
+    pT[0] = 1; pO[0] = 1;
+    const double oneMinusT = 1 - t;
+    for (int i = 1; i < 4; ++i) { pT[i] = pT[i - 1] * t; pO[i] = pO[i - 1] * oneMinusT; }
+    for (int i = 0; i < 4; ++i)
+      for (int p = std::max(0, k + i - Degree); p <= std::min(i, k); ++p) {
+        const int ip = i - p;
+        res[i] += double(((k - p) % 2 == 0 ? 1 : -1) * binom[k][p]) * pT[ip] * pO[Degree - k - ip] / double(factors[ip] * factors[Degree - k - ip]);
+      }
+    for (int i = 0; i < 4; ++i) res[i] *= factors[Degree];
+  }
+  // impl_compute :353-372 and value :455-470 (the matrix product accumulates the four terms in index order)
+  void eval(double* q, double s) const override {
+    double u = 0;
+    if (t1 - t0 != 0) {
+      u = (s - t0) / (t1 - t0);
+      if (u < 0.) u = 0.; else if (u > 1.) u = 1.;
+    }
+    double b[4];
+    basisDerivative(0, u, b);
+    const int nv = dev->nv;
+    for (int k = 0; k < nv; ++k) {
+      double v = 0;
+      for (int i = 0; i < 4; ++i) v += P[(size_t)i * nv + k] * b[i];
+      q[k] = base[k] + v;
+    }
+  }
+  // spline_basis_function<BernsteinBasis, 3>::bound (src/path/spline.cc:204-247), Degree = 3: b_up(1) = b_up(2) = 1
+  static void basisBound(double u0, double u1, double ub[4]) {
+    const int Degree = 3;
+    double b0[4], b1[4];
+    basisDerivative(1, u0, b0);
+    basisDerivative(1, u1, b1);
+    for (int i = 0; i < 4; ++i) ub[i] = std::max(std::fabs(b0[i]), std::fabs(b1[i]));
+    if (u0 * Degree < 2 && 2 < u1 * Degree) ub[1] = std::max(ub[1], 1.0);
+    if (u0 * Degree < Degree - 2 && Degree - 2 < u1 * Degree) ub[Degree - 1] = std::max(ub[Degree - 1], 1.0);
+  }
+  // impl_velocityBound :423-434
+  void velocityBound(double* vb, double ta, double tb) const override {
+    const double len = t1 - t0;
+    const double u0 = len == 0 ? 0 : (ta - t0) / len, u1 = len == 0 ? 0 : (tb - t0) / len;
+    double ub[4];
+    basisBound(u0, u1, ub);
+    for (int i = 0; i < 4; ++i) ub[i] /= len;
+    const int nv = dev->nv;
+    for (int k = 0; k < nv; ++k) {
+      double v = 0;
+      for (int i = 0; i < 4; ++i) v += std::fabs(P[(size_t)i * nv + k]) * ub[i];
+      vb[k] = v;
+    }
   }
 };
 
@@ -261,7 +345,7 @@ struct Discretized {
   ConfigValidations cfg;
   double stepSize;
   Discretized(const Device& d, double step, bool bounds) : cfg(d, bounds), stepSize(step) {}
-  PathReport validate(const StraightPath& path, bool reverse, GjkStats* st = nullptr) const {
+  PathReport validate(const Path& path, bool reverse, GjkStats* st = nullptr) const {
     PathReport R;
     const double tmin = path.t0, tmax = path.t1;
     unsigned finished = 0;

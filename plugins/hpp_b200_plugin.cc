@@ -30,6 +30,7 @@
 #include <hpp/core/joint-bound-validation.hh>
 #include <hpp/core/path-validation.hh>
 #include <hpp/core/path-vector.hh>
+#include <hpp/core/path/spline.hh>
 #include <hpp/core/plugin.hh>
 #include <hpp/core/problem-solver.hh>
 #include <hpp/core/problem.hh>
@@ -396,6 +397,12 @@ class B200PathValidation : public PathValidation, public ObstacleUserInterface {
       std::vector<StraightPathPtr_t> leaves;
       if (flatten(pv, leaves)) return validateChain(pv, leaves, reverse, validPart, report);
     }
+    // cubic Bezier splines (steeringMethod::Spline<BernsteinBasis, 3>, src/steering-method/spline.cc) on robots whose
+    // configuration space is a vector space: hppb200_validate_spline_edges
+    typedef path::Spline<path::BernsteinBasis, 3> Spline3_t;
+    shared_ptr<Spline3_t> spl = HPP_DYNAMIC_PTR_CAST(Spline3_t, path);
+    if (spl && !spl->constraints() && scene_->robot()->configSize() == scene_->robot()->numberDof())
+      return validateSpline(spl, reverse, validPart, report);
     return stock_->validate(path, reverse, validPart, report);
   }
   // batch extension: edges as (q1, q2, L) arrays; see hppb200_validate_edges in include/hppb200.h
@@ -461,6 +468,26 @@ class B200PathValidation : public PathValidation, public ObstacleUserInterface {
     if (reason == HPPB200_REASON_ITER_CAP)  // the engine's iteration cap (the reference has none): let the stock validator finish it
       return stock_->validate(sp, reverse, validPart, report);
     // ownership rule: validPart is set on every return (progressive.cc:121-127, discretized.cc:99-105)
+    validPart = reverse ? sp->extract(tr.first + tLast, tr.second) : sp->extract(tr.first, tr.first + tLast);
+    bool ok = true;
+    report = PathValidationReportPtr_t(new PathValidationReport(tr.first + tFail, configReport(reason, pair, sp->eval(tr.first + tFail, ok))));
+    return false;
+  }
+  // path::Spline<BernsteinBasis, 3>: base() [nq], parameters() [4][nv] (Eigen row-major matrix, rows = control points)
+  bool validateSpline(const shared_ptr<path::Spline<path::BernsteinBasis, 3> >& sp, bool reverse, PathPtr_t& validPart,
+                      PathValidationReportPtr_t& report) {
+    const interval_t tr = sp->timeRange();
+    const Configuration_t base = sp->base();
+    const Eigen::Matrix<value_type, Eigen::Dynamic, Eigen::Dynamic, Eigen::RowMajor> P = sp->parameters();
+    const double L = tr.second - tr.first;
+    uint8_t valid, reason; int32_t pair; double tFail, tLast;
+    {
+      Scene::Pool::Lease ws = scene_->workspace();
+      check(hppb200_validate_spline_edges(ws.get(), method_, param_, reverse ? 1 : 0, base.data(), P.data(), &L, 1, 0, &valid, &tFail, &tLast,
+                                          &pair, &reason));
+    }
+    if (valid) { validPart = sp; return true; }
+    if (reason == HPPB200_REASON_ITER_CAP) return stock_->validate(sp, reverse, validPart, report);
     validPart = reverse ? sp->extract(tr.first + tLast, tr.second) : sp->extract(tr.first, tr.first + tLast);
     bool ok = true;
     report = PathValidationReportPtr_t(new PathValidationReport(tr.first + tFail, configReport(reason, pair, sp->eval(tr.first + tFail, ok))));

@@ -983,3 +983,54 @@ def test_knn_single_query_latency_path(pkg, eng, ur5, ob):
     small.append(pkg.uniform_configs(ur5, 3, seed=303))
     gi, gd = small.query(pkg.uniform_configs(ur5, 1, seed=304), 10)
     assert np.array_equal(gi[0, 3:], -np.ones(7, np.int64)) and np.all(np.isinf(gd[0, 3:])) and sorted(gi[0, :3]) == [0, 1, 2]
+
+
+@pytest.mark.parametrize("name", ["ur5_boxes8.json", "humanoid_obst6.json"])
+def test_spline_edges_parity(pkg, ob, name):
+    """SURVEY 8f-3: path::Spline<BernsteinBasis, 3> edges (tests/test-continuous-validation.cc:288-427) through
+    hppb200_validate_spline_edges == the oracle (Spline eval, impl_velocityBound on sub-intervals, the two-round
+    refinement of BodyPairCollision::collisionFreeInterval), all three methods, forward and reverse, bit for bit;
+    zero-length splines, joint-bound failures of Discretized, the iteration cap."""
+    desc = pkg.ModelDescription.load(name)
+    assert desc.nq == sum(7 if int(t) == 6 else 1 for t in desc.joint_type)
+    o = ob.Oracle(desc)
+    m = pkg.Model(desc)
+    ws = pkg.Workspace(m, 0)
+    n = 3000 if name.startswith("ur5") else 600
+    cfg = pkg.uniform_configs(desc, 2 * n, seed=77)
+    q1, q2 = np.ascontiguousarray(cfg[0::2]), np.ascontiguousarray(cfg[1::2])
+    q2[:40] = q1[:40]  # zero-length: L = 0
+    rng = np.random.default_rng(78)
+    v1, v2 = rng.uniform(-1, 1, q1.shape), rng.uniform(-1, 1, q1.shape)
+    v1[:40] = 0
+    v2[:40] = 0
+    L = o.straight_lengths(q1, q2)
+    base, P = pkg.spline_steer(q1, v1, q2, v2, L)
+    for meth, par in ((1, 1e-2), (1, 1e-3), (2, 0.0), (0, 0.05)):
+        for rev in (False, True):
+            r = ws.validate_spline_edges(meth, par, base, P, L, reverse=rev)
+            e = o.validate_spline_edges(meth, par, base, P, L, reverse=rev)
+            for k in ("valid", "reason", "pair", "t_last_valid"):
+                assert np.array_equal(r[k], e[k]), (name, meth, par, rev, k, int((r[k] != e[k]).sum()))
+            assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True), (name, meth, par, rev)
+            assert 0.02 < r["valid"].mean() < 0.98
+    # Discretized with the joint-bound check: random end velocities push splines out of the joint range
+    r = ws.validate_spline_edges(0, 0.05, base, P, L, check_bounds=True)
+    e = o.validate_spline_edges(0, 0.05, base, P, L, check_bounds=True)
+    for k in ("valid", "reason", "pair", "t_last_valid"):
+        assert np.array_equal(r[k], e[k]), k
+    assert np.any(r["reason"] == pkg.REASON_JOINT_BOUND)
+    # iteration cap
+    ws.set_max_iterations(3)
+    try:
+        r = ws.validate_spline_edges(1, 1e-3, base[:500], P[:500], L[:500])
+        e = o.validate_spline_edges(1, 1e-3, base[:500], P[:500], L[:500], max_iter=3)
+        for k in ("valid", "reason", "t_last_valid"):
+            assert np.array_equal(r[k], e[k]), k
+    finally:
+        ws.set_max_iterations(1000000)
+    # free-flyer models are refused (vector-space configuration spaces only)
+    ff = pkg.ModelDescription.load("humanoid_ff_obst6.json")
+    wf = pkg.Workspace(pkg.Model(ff), 0)
+    with pytest.raises(ValueError):
+        wf.validate_spline_edges(1, 1e-3, np.zeros((1, ff.nq)), np.zeros((1, 4, ff.nq)), np.ones(1))

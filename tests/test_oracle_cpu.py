@@ -365,3 +365,78 @@ def test_freeflyer_humanoid_oracle_invariants(pkg, ob):
     cc = o.validate_edges(2, 0.0, q1, qb, L)["valid"]
     assert not np.any((dd == 0) & (cc == 1)) and np.mean((dd == 0) & (pp == 1)) < 0.01
     assert 0.05 < cc.mean() < 0.95
+
+
+def _random_splines(pkg, desc, n, seed):
+    """steeringMethod::Spline<BernsteinBasis, 3>::steer(q1, {1}, v1, q2, {1}, v2) with length = distance(q1, q2), as in
+    tests/test-continuous-validation.cc:288-345 (random end configurations and end velocities)"""
+    from oracle import binding as ob
+    cfg = pkg.uniform_configs(desc, 2 * n, seed=seed)
+    q1, q2 = np.ascontiguousarray(cfg[0::2]), np.ascontiguousarray(cfg[1::2])
+    rng = np.random.default_rng(seed)
+    v1, v2 = rng.uniform(-1, 1, q1.shape), rng.uniform(-1, 1, q1.shape)
+    L = ob.Oracle(desc).straight_lengths(q1, q2)
+    base, P = pkg.spline_steer(q1, v1, q2, v2, L)
+    return q1, v1, q2, v2, L, base, P
+
+
+def test_spline_path_eval_and_velocity_bound(pkg, ob, ur5):
+    """path::Spline<BernsteinBasis, 3> (src/path/spline.cc): end points and end velocities of the steered spline, the
+    Bernstein basis against its textbook form, and impl_velocityBound(t0, t1) really bounding |dq/dt| on [t0, t1]."""
+    o = ob.Oracle(ur5)
+    n = 200
+    q1, v1, q2, v2, L, base, P = _random_splines(pkg, ur5, n, 11)
+    assert np.array_equal(o.spline_eval(base, P, L, np.zeros(n)), q1)
+    assert np.allclose(o.spline_eval(base, P, L, L), q2, rtol=0, atol=1e-14)
+    h = 1e-6
+    assert np.allclose((o.spline_eval(base, P, L, np.full(n, h)) - q1) / h, v1, atol=2e-5)
+    assert np.allclose((q2 - o.spline_eval(base, P, L, L - h)) / h, v2, atol=2e-5)
+    rng = np.random.default_rng(3)
+    t = rng.uniform(0, 1, n) * L
+    u = (t / L)[:, None]
+    B = np.stack([(1 - u) ** 3, 3 * u * (1 - u) ** 2, 3 * u ** 2 * (1 - u), u ** 3], axis=1)  # [n, 4, 1]
+    assert np.allclose(o.spline_eval(base, P, L, t), base + (P * B).sum(axis=1), rtol=0, atol=1e-13)
+    # the bound on sub-intervals (what the refinement of BodyPairCollision::collisionFreeInterval calls)
+    a, b = np.sort(rng.uniform(0, 1, (2, n)), axis=0) * L
+    vb = o.spline_velocity_bound(base, P, L, a, b)
+    for s in np.linspace(0, 1, 33):
+        ts = a + s * (b - a)
+        num = (o.spline_eval(base, P, L, np.minimum(ts + h, L)) - o.spline_eval(base, P, L, np.maximum(ts - h, 0))) / (np.minimum(ts + h, L) - np.maximum(ts - h, 0))[:, None]
+        assert np.all(np.abs(num) <= vb * (1 + 1e-6) + 1e-6)
+    whole = o.spline_velocity_bound(base, P, L, np.zeros(n), L)
+    assert np.all(vb <= whole * (1 + 1e-12))  # a sub-interval never needs a larger bound than the whole path
+
+
+def test_spline_validation_consistency_like_the_reference_test(pkg, ob, ur5):
+    """tests/test-continuous-validation.cc:288-427 on the oracle: where Discretized (0.05) finds a collision on a random
+    spline, Progressive (0.01) must find one too, forward and reverse; a spline that IS a straight line (end velocities
+    = (q2 - q1) / L) validates like the straight path."""
+    o = ob.Oracle(ur5)
+    n = 600
+    q1, v1, q2, v2, L, base, P = _random_splines(pkg, ur5, n, 12)
+    for rev in (False, True):
+        d = o.validate_spline_edges(0, 0.05, base, P, L, reverse=rev)
+        p = o.validate_spline_edges(1, 0.01, base, P, L, reverse=rev)
+        start_free = o.validate_configs(q2 if rev else q1)[0] == 1
+        # (the tolerance lets Progressive accept penetrations of that order, e.g. an end configuration that barely
+        #  touches: a handful of such edges is what the tolerance means, many would be a wrong velocity bound)
+        assert np.sum(start_free & (d["valid"] == 0) & (p["valid"] == 1)) <= n // 100
+        assert 0.05 < p["valid"].mean() < 0.95
+        # Dichotomy has no tolerance: a path it accepts has no colliding sample at all, and it is at least as strict
+        # as Progressive
+        z = o.validate_spline_edges(2, 0.0, base, P, L, reverse=rev)
+        assert not np.any((z["valid"] == 1) & (d["valid"] == 0))
+        assert not np.any((z["valid"] == 1) & (p["valid"] == 0))
+        fine = o.validate_spline_edges(0, 0.002, base[:150], P[:150], L[:150], reverse=rev)
+        assert not np.any((z["valid"][:150] == 1) & (fine["valid"] == 0))
+    vs = (q2 - q1) / L[:, None]
+    sb, sp = pkg.spline_steer(q1, vs, q2, vs, L)
+    s = o.validate_spline_edges(1, 1e-3, sb, sp, L)
+    e = o.validate_edges(1, 1e-3, q1, q2, L)
+    assert (s["valid"] == e["valid"]).mean() > 0.99
+    both = (s["valid"] == 0) & (e["valid"] == 0)
+    assert np.allclose(s["t_fail"][both], e["t_fail"][both], atol=0.05)
+    # zero-length spline: one sample, the configuration decides
+    z = o.validate_spline_edges(1, 1e-3, q1[:50], np.zeros((50, 4, ur5.nq)), np.zeros(50))
+    assert np.array_equal(z["valid"], o.validate_configs(q1[:50])[0])
+    assert np.all(z["samples"] <= 2)
