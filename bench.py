@@ -541,7 +541,7 @@ def run_b200(args):
         nn.append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
         nn_exact.append(pkg.uniform_configs(desc, n_nodes, seed=SEED + 2))
         knn = {"nodes": n_nodes, "unit": "queries/s", "bytes_per_node": 8 * nq}
-        tmem_peak = pkg.measure_tmem_read_peak(local_rank) / 1e12  # TB/s
+        tmem_peak = pkg.measure_tmem_read_peak(local_rank)  # TB/s (the library reports TB/s)
         if "bf16_tflops" in peaks:
             tf32_peak = (peaks["bf16_tflops"] / 2.0, "MEASURED_PEAKS.json bf16_tflops (burst) / 2: kind::tf32 runs at half the bf16 rate")
         else:

@@ -170,7 +170,46 @@ struct ValidateArgs {
   unsigned long long* jobs;  // (config << 32 | pair)
   unsigned long long* njobs;
   unsigned long long jobs_cap;
+  // configPassKernel stages the blob WITHOUT the continuous-validation tables (body pairs, their geometry pairs,
+  // velocity coefficients): [0, blob_head) and [blob_tail_off, blob_tail_off + blob_tail_bytes) back to back; the
+  // kernel's ModelView has the offsets of the tables behind the gap moved down accordingly (configView below)
+  uint32_t blob_head, blob_tail_off, blob_tail_bytes;
+  int force_exact;         // SHADOW: every pair from the FP64 placements (HPPB200_CFG_SHADOW=2, tests)
+  double hmax, reach_max;  // SHADOW slack: largest capsule half-length of a robot geometry, largest cull reach of a pair
 };
+
+// Two TMA bulk copies on one mbarrier (see stageBlobTMA): the blob without the gap.
+__device__ __forceinline__ void stageBlobSplitTMA(unsigned char* sdst, const unsigned char* gsrc, uint32_t head, uint32_t tailOff,
+                                                  uint32_t tailBytes, uint64_t* bar) {
+  const uint32_t bar_s = (uint32_t)__cvta_generic_to_shared(bar);
+  const uint32_t dst_s = (uint32_t)__cvta_generic_to_shared(sdst);
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_s) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_s), "r"(head + tailBytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s), "l"(gsrc),
+                 "r"(head), "r"(bar_s)
+                 : "memory");
+    if (tailBytes)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_s + head),
+                   "l"(gsrc + tailOff), "r"(tailBytes), "r"(bar_s)
+                   : "memory");
+  }
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar_s), "r"(0u)
+        : "memory");
+  }
+}
 
 // Sparse pinocchio joint transform: liMi = P * M_joint(q), exploiting the zeros/ones of M.
 // Bit-identical to the dense product up to the sign of zeros.
@@ -203,25 +242,89 @@ __device__ __forceinline__ void pushJob(unsigned long long job, unsigned long lo
   if (g < A.jobs_cap) A.jobs[g] = job;
 }
 
-template <bool TREE>
-__global__ void __launch_bounds__(K1_THREADS)
+// SHADOW (the production form): the bounding cores of the robot geometries are kept in shared memory as the HIGH 32-bit
+// words of their FP64 coordinates (sign, exponent, 20 mantissa bits; rebuilt with a zero low word: no conversion
+// instruction), 24 instead of 48 bytes per geometry and thread, so that 5 CTAs instead of 3 fit an SM (the kernel is
+// latency-bound: 0.92 -> see DESIGN.md 3.1).  Decisions stay EXACT:
+//  * truncation moves a coordinate by < 2^-20 |x|, a core point (centre +- h axis) by < sqrt(3) 2^-20 (maxc + h), and
+//    core distances are 1-Lipschitz in their points, so |d~ - d| < 2 sqrt(3) 2^-20 (maxc + hmax) < 2^-18 (maxc + hmax);
+//    the point-segment form assumes a unit axis, |u~| is short by < 2^-19, which moves its foot point by < 2^-19 h.
+//    s = 2^-17 (maxc + hmax) + 1e-9 covers both twice over (maxc = largest |coordinate| of this configuration's cores);
+//  * closed forms: d~ - margin > threshold + s  => no collision;  <= threshold - s  => collision (the exact test says
+//    the same in both cases);  in between (|d - margin| < 2 s, ~1 pair in 10^4) the pair is evaluated again from the
+//    FP64 placements in the global scratch, with the operations of the FP64 path;
+//  * conservative culls only get the slack added (fewer culls, never a wrong one): core distance^2 > cull2 +
+//    s (2 reach_max + s), box-face bound > 1e-9 + s;
+//  * a configuration with NaN / infinite cores or maxc > 64 takes the exact path for every pair.
+#ifndef K1_MINB
+#define K1_MINB 6
+#endif
+__device__ __forceinline__ double hiWord(uint32_t h) { return __hiloint2double((int)h, 0); }
+
+// HOSTQ: A.q is PINNED HOST memory (zero-copy form of the host-pointer path): thread 0 pulls the CTA's 128 configurations
+// (one contiguous block) over PCIe with one TMA bulk copy into shared memory while the blob is staged; the copy engine, its
+// slice-sized latency and the device staging buffer drop out, and the transfer overlaps the FP64 work CTA by CTA.
+template <bool TREE, bool SHADOW, bool HOSTQ>
+__global__ void __launch_bounds__(K1_THREADS, SHADOW ? K1_MINB : 1)
 configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* bar = (uint64_t*)smem;
   int* scount = (int*)(smem + 8);
   unsigned char* sblob = smem + 16;
-  double* cstore = (double*)(sblob + mv.blob_bytes);                         // [ngeoms*6][K1_THREADS]
-  unsigned long long* sjobs = (unsigned long long*)(cstore + (size_t)mv.ngeoms * 6 * K1_THREADS);
+  double* cstore = (double*)(sblob + mv.blob_bytes);                         // [ngeoms*6][K1_THREADS] f64, or u32 (SHADOW)
+  uint32_t* cstore32 = (uint32_t*)cstore;
+  unsigned long long* sjobs = (unsigned long long*)((unsigned char*)cstore + (size_t)mv.ngeoms * 6 * K1_THREADS * (SHADOW ? 4 : 8));
   __shared__ unsigned long long sbase;
-  stageBlobTMA(sblob, mv.blob, mv.blob_bytes, bar);
-  const Tables T = makeTables(sblob, mv);
+  __shared__ __align__(8) uint64_t qbar;
   const int tid = threadIdx.x;
+  double* sq = (double*)sjobs;  // HOSTQ: [K1_THREADS][nq], in the job staging area (used only after phase 1)
+  bool qStaged = false;
+  if (HOSTQ) {
+    const size_t base = (size_t)blockIdx.x * K1_THREADS;
+    const size_t cnt = A.n - base < (size_t)K1_THREADS ? A.n - base : (size_t)K1_THREADS;
+    const uint32_t bytes = (uint32_t)(cnt * (size_t)mv.nq * sizeof(double));
+    // (a partial CTA with an odd number of doubles, or a misaligned block, reads its rows directly)
+    qStaged = (bytes & 15u) == 0u && ((uintptr_t)(A.q + base * (size_t)mv.nq) & 15u) == 0u;
+    if (qStaged && tid == 0) {
+      const uint32_t qb = (uint32_t)__cvta_generic_to_shared(&qbar);
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(qb) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(qb), "r"(bytes) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                       (uint32_t)__cvta_generic_to_shared(sq)),
+                   "l"(A.q + base * (size_t)mv.nq), "r"(bytes), "r"(qb)
+                   : "memory");
+    }
+  }
+  stageBlobSplitTMA(sblob, mv.blob, A.blob_head, A.blob_tail_off, A.blob_tail_bytes, bar);
+  const Tables T = makeTables(sblob, mv);
   if (tid == 0) *scount = 0;
   __syncthreads();
+  if (HOSTQ && qStaged) {
+    const uint32_t qb = (uint32_t)__cvta_generic_to_shared(&qbar);
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+          "selp.u32 %0, 1, 0, p;\n\t}"
+          : "=r"(done)
+          : "r"(qb), "r"(0u)
+          : "memory");
+    }
+  }
   const size_t i = (size_t)blockIdx.x * K1_THREADS + tid;
   unsigned tests = 0;
+  // phase 1: joint bounds + FK (the only reader of the configuration); phase 2: the pair loop.  HOSTQ separates them
+  // with a barrier because the staged rows share their shared memory with the job staging of phase 2.
+  bool live = false;
+  double* cs = cstore + tid;
+  uint32_t* cs32 = cstore32 + tid;
+  double maxc = 0.0;
+  bool exactAll = !SHADOW || A.force_exact != 0;
   if (i < A.n) {
-    const double* qc = A.q + i * (size_t)mv.nq;
+    const double* qc = (HOSTQ && qStaged) ? sq + (size_t)tid * mv.nq : A.q + i * (size_t)mv.nq;
     int bad = -1;
     if (A.flags & HPPB200_CHECK_JOINT_BOUNDS) {
       for (int k = 0; k < mv.nq && bad < 0; ++k) {
@@ -234,14 +337,26 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
       A.valid[i] = 0; A.first[i] = (uint32_t)bad; A.reason[i] = HPPB200_REASON_JOINT_BOUND;
     } else {
       // ---- FK: placements to global scratch, compact cores to shared memory ----
-      double* cs = cstore + tid;
+      live = true;
       auto emit = [&](int g, const T3& M) {
         store12s(A.oMg + (size_t)g * 12 * A.n + i, A.n, M);
         const DevGeom& G = T.geoms[g];
         V3 c = M.t;
         if (G.shape.type >= SH_BOX) c = rmul(M, mk(G.bound.bc[0], G.bound.bc[1], G.bound.bc[2])) + M.t;
-        cs[(g * 6 + 0) * K1_THREADS] = c.x; cs[(g * 6 + 1) * K1_THREADS] = c.y; cs[(g * 6 + 2) * K1_THREADS] = c.z;
-        cs[(g * 6 + 3) * K1_THREADS] = M.r[2]; cs[(g * 6 + 4) * K1_THREADS] = M.r[5]; cs[(g * 6 + 5) * K1_THREADS] = M.r[8];
+        if (SHADOW) {
+          cs32[(g * 6 + 0) * K1_THREADS] = (uint32_t)__double2hiint(c.x);
+          cs32[(g * 6 + 1) * K1_THREADS] = (uint32_t)__double2hiint(c.y);
+          cs32[(g * 6 + 2) * K1_THREADS] = (uint32_t)__double2hiint(c.z);
+          cs32[(g * 6 + 3) * K1_THREADS] = (uint32_t)__double2hiint(M.r[2]);
+          cs32[(g * 6 + 4) * K1_THREADS] = (uint32_t)__double2hiint(M.r[5]);
+          cs32[(g * 6 + 5) * K1_THREADS] = (uint32_t)__double2hiint(M.r[8]);
+          maxc = fmax(maxc, fmax(fabs(c.x), fmax(fabs(c.y), fabs(c.z))));
+          const double sum = ((c.x + c.y) + c.z) + ((M.r[2] + M.r[5]) + M.r[8]);
+          if (!(fabs(sum) < CUDART_INF)) exactAll = true;  // NaN or infinite somewhere
+        } else {
+          cs[(g * 6 + 0) * K1_THREADS] = c.x; cs[(g * 6 + 1) * K1_THREADS] = c.y; cs[(g * 6 + 2) * K1_THREADS] = c.z;
+          cs[(g * 6 + 3) * K1_THREADS] = M.r[2]; cs[(g * 6 + 4) * K1_THREADS] = M.r[5]; cs[(g * 6 + 5) * K1_THREADS] = M.r[8];
+        }
       };
       for (int g = 0; g < mv.ngeoms; ++g)
         if (T.geoms[g].joint == 0) emit(g, load12(T.geoms[g].P));
@@ -256,11 +371,35 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
         for (int g = 0; g < mv.ngeoms; ++g)
           if (T.geoms[g].joint == j) emit(g, compose(cur, load12(T.geoms[g].P)));
       }
+    }
+  }
+  if (HOSTQ) __syncthreads();
+  {
+    if (live) {
+      if (SHADOW && !(maxc <= 64.0)) exactAll = true;
+      const double slack = SHADOW ? fma(0x1p-17, maxc + A.hmax, 1e-9) : 0.0;
+      const double cullSlack = SHADOW ? slack * fma(2.0, A.reach_max, slack) * (1.0 + 1e-9) : 0.0;
       // ---- pair loop in reference order, early exit at the first definite hit ----
-      auto core = [&](int ref, V3& c, V3& u) {
+      auto core = [&](int ref, bool ex, V3& c, V3& u) {
         if (ref >= 0) {
-          c = mk(cs[(ref * 6 + 0) * K1_THREADS], cs[(ref * 6 + 1) * K1_THREADS], cs[(ref * 6 + 2) * K1_THREADS]);
-          u = mk(cs[(ref * 6 + 3) * K1_THREADS], cs[(ref * 6 + 4) * K1_THREADS], cs[(ref * 6 + 5) * K1_THREADS]);
+          if (!SHADOW) {
+            c = mk(cs[(ref * 6 + 0) * K1_THREADS], cs[(ref * 6 + 1) * K1_THREADS], cs[(ref * 6 + 2) * K1_THREADS]);
+            u = mk(cs[(ref * 6 + 3) * K1_THREADS], cs[(ref * 6 + 4) * K1_THREADS], cs[(ref * 6 + 5) * K1_THREADS]);
+          } else if (!ex) {
+            c = mk(hiWord(cs32[(ref * 6 + 0) * K1_THREADS]), hiWord(cs32[(ref * 6 + 1) * K1_THREADS]), hiWord(cs32[(ref * 6 + 2) * K1_THREADS]));
+            u = mk(hiWord(cs32[(ref * 6 + 3) * K1_THREADS]), hiWord(cs32[(ref * 6 + 4) * K1_THREADS]), hiWord(cs32[(ref * 6 + 5) * K1_THREADS]));
+          } else {  // the FP64 placement this thread wrote to the global scratch: the values the FP64 store would hold
+            const double* pm = A.oMg + (size_t)ref * 12 * A.n + i;
+            const DevGeom& G = T.geoms[ref];
+            if (G.shape.type >= SH_BOX) {
+              const T3 M = load12s(pm, A.n);
+              c = rmul(M, mk(G.bound.bc[0], G.bound.bc[1], G.bound.bc[2])) + M.t;
+              u = mk(M.r[2], M.r[5], M.r[8]);
+            } else {
+              c = mk(pm[9 * A.n], pm[10 * A.n], pm[11 * A.n]);
+              u = mk(pm[2 * A.n], pm[5 * A.n], pm[8 * A.n]);
+            }
+          }
         } else {
           const DevObstacle& O = T.obstacles[-(ref + 1)];
           c = mk(O.wc[0], O.wc[1], O.wc[2]);
@@ -268,13 +407,14 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
         }
       };
       int hit = -1;
-      for (int p = 0; p < mv.ncpairs; ++p) {
+      bool ex = exactAll;
+      for (int p = 0; p < mv.ncpairs;) {
         const DevPair pr = T.cpairs[p];
         const DevShape& sa = *(const DevShape*)(pr.a >= 0 ? &T.geoms[pr.a].shape : &T.obstacles[-(pr.a + 1)].shape);
         const DevShape& sb = *(const DevShape*)(pr.b >= 0 ? &T.geoms[pr.b].shape : &T.obstacles[-(pr.b + 1)].shape);
         V3 ca, ua, cb, ub;
-        core(pr.a, ca, ua);
-        core(pr.b, cb, ub);
+        core(pr.a, ex, ca, ua);
+        core(pr.b, ex, cb, ub);
         if (pr.kind <= PK_CAPSULE_CAPSULE) {
           double d;
           if (pr.kind == PK_SPHERE_SPHERE) { V3 dd = ca - cb; d = sqrt(dot(dd, dd)) - sa.p[0] - sb.p[0]; }
@@ -284,15 +424,25 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
             V3 p2 = axpy(-sb.p[1], ub, cb), q2 = axpy(sb.p[1], ub, cb);
             d = sqrt(segmentSegmentDist2(p1, q1, p2, q2)) - sa.p[0] - sb.p[0];
           }
+          const double dm = d - pr.margin;
+          if (SHADOW && !ex) {
+            if (dm > HPPB200_COLLISION_THRESHOLD + slack) { ++tests; ++p; continue; }
+            if (dm <= HPPB200_COLLISION_THRESHOLD - slack) { ++tests; hit = p; break; }
+            ex = true;  // within the slack of the threshold: the same pair again, from the FP64 placements
+            continue;
+          }
           ++tests;
-          if (d - pr.margin <= HPPB200_COLLISION_THRESHOLD) { hit = p; break; }
+          if (dm <= HPPB200_COLLISION_THRESHOLD) { hit = p; break; }
+          ex = exactAll;
+          ++p;
           continue;
         }
-        // GJK kinds: conservative cull on the bounding cores
+        // GJK kinds: conservative cull on the bounding cores (one-sided: the slack only keeps more pairs)
+        const double sl = (SHADOW && !ex) ? slack : 0.0, csl = (SHADOW && !ex) ? cullSlack : 0.0;
         double d2;
         if (pr.bound == 1) d2 = pointSegmentDist2(cb, ca, ua, sa.p[1]);
         else { V3 dd = ca - cb; d2 = dot(dd, dd); }
-        if (d2 > pr.cull2) continue;
+        if (d2 > pr.cull2 + csl) { ++p; continue; }
         if (pr.b < 0 && sb.type == SH_BOX) {
           // box-face separating axes: a lower bound of the distance to the obstacle box
           const DevObstacle& O = T.obstacles[-(pr.b + 1)];
@@ -303,9 +453,10 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
           const double sy = fmax(fmin(e0.y, e1.y) - sb.p[1], -fmax(e0.y, e1.y) - sb.p[1]);
           const double sz = fmax(fmin(e0.z, e1.z) - sb.p[2], -fmax(e0.z, e1.z) - sb.p[2]);
           const double ra = pr.a >= 0 ? T.geoms[pr.a].bound.br : T.obstacles[-(pr.a + 1)].bound.br;
-          if (fmax(sx, fmax(sy, sz)) - ra - pr.margin > 1e-9) continue;
+          if (fmax(sx, fmax(sy, sz)) - ra - pr.margin > 1e-9 + sl) { ++p; continue; }
         }
         pushJob(((unsigned long long)i << 32) | (unsigned)p, sjobs, scount, A);
+        ++p;
       }
       A.valid[i] = hit < 0 ? 1 : 0;
       A.first[i] = (uint32_t)hit;
@@ -323,7 +474,13 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
   if ((tid & 31) == 0 && stats && ts) atomicAdd(&stats->pair_tests, (unsigned long long)ts);
 }
 
-__global__ void __launch_bounds__(256)
+#ifndef K2_THREADS
+#define K2_THREADS 128  // 167 registers: 3 CTAs of 128 (12 warps per SM) instead of 1 CTA of 256 (8 warps)
+#endif
+#ifndef K2_GRID_PER_SM
+#define K2_GRID_PER_SM 12
+#endif
+__global__ void __launch_bounds__(K2_THREADS, 384 / K2_THREADS)
 gjkJobsKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* bar = (uint64_t*)smem;
@@ -359,12 +516,64 @@ gjkJobsKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
   }
 }
 
+
+// Launch set-up of configPassKernel: the blob view without the continuous-validation tables, the shadow slack inputs, the
+// shared-memory size and the kernel instance.  HPPB200_CFG_SHADOW=0 keeps FP64 cores in shared memory (3 CTAs per SM).
+namespace {
+typedef void (*ConfigPassFn)(ModelView, ValidateArgs, DeviceStats*);
+struct ConfigPassSetup {
+  ModelView cv;
+  uint32_t head, tailOff, tailBytes;
+  double hmax, reachMax;
+  int forceExact;
+  size_t smem;
+  ConfigPassFn fn;
+};
+ConfigPassSetup configPassSetup(Workspace* ws, bool hostq = false) {
+  const ModelView& mv = ws->view;
+  const Model* m = ws->model;
+  ConfigPassSetup S{};
+  const uint32_t gap = mv.off_lower - mv.off_bodypairs;
+  S.cv = mv;
+  S.cv.off_bodypairs = S.cv.off_bgpairs = S.cv.off_coefs = S.cv.off_rcoefs = 0;  // (not staged, not used by the kernel)
+  S.cv.off_lower -= gap; S.cv.off_upper -= gap; S.cv.off_weights -= gap; S.cv.off_cpairs -= gap;
+  S.cv.blob_bytes = mv.blob_bytes - gap;
+  S.head = mv.off_bodypairs;
+  S.tailOff = mv.off_lower;
+  S.tailBytes = mv.blob_bytes - mv.off_lower;
+  for (const DevGeom& G : m->geoms)
+    if (G.shape.type == HPPB200_SHAPE_CAPSULE) S.hmax = std::max(S.hmax, G.shape.p[1]);
+  const DevPair* cp = (const DevPair*)(m->blob.data() + mv.off_cpairs);
+  double c2 = 0;
+  for (int p = 0; p < mv.ncpairs; ++p) c2 = std::max(c2, cp[p].cull2);
+  S.reachMax = std::sqrt(c2) * (1.0 + 1e-12);
+  bool shadow = true;
+  if (const char* v = std::getenv("HPPB200_CFG_SHADOW")) { shadow = std::atoi(v) != 0; S.forceExact = std::atoi(v) == 2; }
+  if (hostq && !shadow) throw std::runtime_error("the zero-copy configuration pass exists in the shadow form only");
+  S.smem = 16 + S.cv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * (shadow ? sizeof(uint32_t) : sizeof(double)) +
+           std::max((size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long), hostq ? (size_t)K1_THREADS * mv.nq * sizeof(double) : (size_t)0);
+  if (S.smem > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
+  const bool tree = modelIsTree(m);
+  S.fn = hostq ? (tree ? configPassKernel<true, true, true> : configPassKernel<false, true, true>)
+         : shadow ? (tree ? configPassKernel<true, true, false> : configPassKernel<false, true, false>)
+                  : (tree ? configPassKernel<true, false, false> : configPassKernel<false, false, false>);
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(S.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
+  return S;
+}
+void launchConfigPass(const ConfigPassSetup& S, cudaStream_t stream, ValidateArgs A, DeviceStats* stats) {
+  A.blob_head = S.head; A.blob_tail_off = S.tailOff; A.blob_tail_bytes = S.tailBytes;
+  A.hmax = S.hmax; A.reach_max = S.reachMax; A.force_exact = S.forceExact;
+  S.fn<<<(unsigned)((A.n + K1_THREADS - 1) / K1_THREADS), K1_THREADS, S.smem, stream>>>(S.cv, A, stats);
+  HPPB200_CUDA_CHECK(cudaGetLastError());
+}
+}  // namespace
+
 // The two kernels on `stream`, scratch given by the caller: oMg [slots*12][n], njobs (one counter), jobs [cap].
 // streamJobs / evPass: when given, gjkJobsKernel runs on its own stream behind the event recorded after configPassKernel
 // (a latency-bound kernel: it overlaps the next slice's configPassKernel).
 static void launchTwoKernelsOn(Workspace* ws, cudaStream_t stream, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid,
                                int32_t* d_first, uint8_t* d_reason, double* oMg, unsigned long long* njobs, unsigned long long* jobs,
-                               size_t cap, cudaStream_t streamJobs = nullptr, cudaEvent_t evPass = nullptr) {
+                               size_t cap, cudaStream_t streamJobs = nullptr, cudaEvent_t evPass = nullptr, bool hostq = false) {
   const bool tree = modelIsTree(ws->model);
   const ModelView& mv = ws->view;
   ValidateArgs A{};
@@ -374,22 +583,16 @@ static void launchTwoKernelsOn(Workspace* ws, cudaStream_t stream, const double*
   A.jobs = jobs;
   A.jobs_cap = cap;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), stream));
-  const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
-                       (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
-  if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
-  auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-  k1<<<(unsigned)((n + K1_THREADS - 1) / K1_THREADS), K1_THREADS, smem1, stream>>>(mv, A, ws->d_stats);
-  HPPB200_CUDA_CHECK(cudaGetLastError());
+  launchConfigPass(configPassSetup(ws, hostq), stream, A, ws->d_stats);
   const size_t smem2 = 16 + mv.blob_bytes;
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  size_t grid2 = (size_t)ws->num_sms * 4;
+  size_t grid2 = (size_t)ws->num_sms * K2_GRID_PER_SM;
   if (streamJobs) {
     HPPB200_CUDA_CHECK(cudaEventRecord(evPass, stream));
     HPPB200_CUDA_CHECK(cudaStreamWaitEvent(streamJobs, evPass, 0));
     stream = streamJobs;
   }
-  gjkJobsKernel<<<(unsigned)grid2, 256, smem2, stream>>>(mv, A, ws->d_stats);
+  gjkJobsKernel<<<(unsigned)grid2, K2_THREADS, smem2, stream>>>(mv, A, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 2;
   ws->stats.configs += n;
@@ -506,16 +709,10 @@ void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, ui
   A.jobs_cap = cap;
   A.oMg = (double*)(base + offPlc);
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), ws->stream));  // the one thing that must start at zero
-  const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
-                       (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
-  if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
-  auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
-  k1<<<(unsigned)((n + K1_THREADS - 1) / K1_THREADS), K1_THREADS, smem1, ws->stream>>>(mv, A, ws->d_stats);
-  HPPB200_CUDA_CHECK(cudaGetLastError());
+  launchConfigPass(configPassSetup(ws), ws->stream, A, ws->d_stats);
   const size_t smem2 = 16 + mv.blob_bytes;
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  gjkJobsKernel<<<(unsigned)((size_t)ws->num_sms * 4), 256, smem2, ws->stream>>>(mv, A, ws->d_stats);
+  gjkJobsKernel<<<(unsigned)((size_t)ws->num_sms * K2_GRID_PER_SM), K2_THREADS, smem2, ws->stream>>>(mv, A, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 2;
   ws->stats.configs += n;
@@ -542,28 +739,56 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
   // slice sizes in whole WAVES of configPassKernel (resident CTAs x 128 configurations; a slice of 1.15 waves costs 2):
   // one wave first (the kernels start after its copy), then doubling up to `maxWaves`; the H2D stream runs ahead of the
   // compute stream (0.86 ns vs 1.09 ns per UR5 configuration), the D2H stream behind it
+  // Zero-copy form: h_q is pinned (cudaHostAlloc / cudaHostRegister) and 16-byte aligned, so configPassKernel can pull
+  // its rows over PCIe itself (HOSTQ); pageable memory keeps the staged copy.  HPPB200_CFG_ZEROCOPY=1 switches it on.
+  bool zeroCopy = false;
+  {
+    // Off by default: measured 1.38 ms per 1 M UR5 configurations against 1.37 ms for the staged slices (SM-initiated
+    // PCIe reads reach ~44 GB/s against ~50 GB/s for the copy engine, and the CTAs of one wave fetch, then compute, together).
+    bool want = false, shadow = true;
+    if (const char* v = std::getenv("HPPB200_CFG_ZEROCOPY")) want = std::atoi(v) != 0;
+    if (const char* v = std::getenv("HPPB200_CFG_SHADOW")) shadow = std::atoi(v) != 0;
+    if (want && shadow && ((uintptr_t)h_q & 15u) == 0) {
+      cudaPointerAttributes pa{};
+      if (cudaPointerGetAttributes(&pa, h_q) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer == (void*)h_q) zeroCopy = true;
+      else (void)cudaGetLastError();
+    }
+  }
   size_t wave;
   {
-    const size_t smem1 = 16 + mv.blob_bytes + (size_t)mv.ngeoms * 6 * K1_THREADS * sizeof(double) +
-                         (size_t)K1_JOBS_PER_BLOCK * sizeof(unsigned long long);
-    if (smem1 > 227u * 1024u) throw std::runtime_error("model too large for the configuration kernel");
-    auto k1 = tree ? configPassKernel<true> : configPassKernel<false>;
-    HPPB200_CUDA_CHECK(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    const ConfigPassSetup S = configPassSetup(ws, zeroCopy);
     int perSM = 0;
-    HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, k1, K1_THREADS, smem1));
+    HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, S.fn, K1_THREADS, S.smem));
     wave = (size_t)std::max(1, perSM) * (size_t)ws->num_sms * K1_THREADS;
   }
-  size_t maxWaves = 4;
+  size_t maxWaves = 2, tailWaves = 2;  // measured: 4/2 705, 2/2 762, 2/0 766, 1/2 747, 8/2 713 M configurations/s (1 M UR5, pinned)
   if (const char* v = std::getenv("HPPB200_CFG_SLICE_WAVES")) maxWaves = std::max<size_t>(1, (size_t)std::atoll(v));
+  if (const char* v = std::getenv("HPPB200_CFG_TAIL_WAVES")) tailWaves = (size_t)std::max(0ll, std::atoll(v));
+  // Slices in whole waves: 1, 2, 4, ... (the kernels start after the first, small copy), and `tailWaves` single-wave slices
+  // at the end: with the kernels as fast as the copy (0.90 vs 0.97 ms per 1 M UR5 configurations) the call ends one last
+  // slice of kernels + D2H after the last byte has arrived, so the last slice is the smallest efficient one.  The
+  // fractional wave of the batch rides in the second slice.
   std::vector<size_t> offs, lens;
-  for (size_t off = 0, w = 1; off < n; w = std::min(maxWaves, w * 2)) {
-    size_t m = std::min(w * wave, n - off);
-    if (n - off - m < wave / 2) m = n - off;  // no tiny last slice
-    offs.push_back(off); lens.push_back(m);
-    off += m;
+  {
+    const size_t full = n / wave, frac = n - full * wave;
+    std::vector<size_t> sz;
+    if (full < tailWaves + 2) sz.push_back(n);  // small batch: one slice (below ~4 waves slicing buys nothing)
+    else {
+      size_t body = full - tailWaves;
+      for (size_t w = zeroCopy ? maxWaves : 1; body > 0; w = std::min(maxWaves, w * 2)) {  // (zero-copy: no first copy to wait for)
+        const size_t m = std::min(w, body);
+        sz.push_back(m * wave);
+        body -= m;
+      }
+      sz[sz.size() > 1 ? 1 : 0] += frac / K1_THREADS * K1_THREADS;  // (slice offsets stay multiples of 128 configurations)
+      for (size_t k = 0; k < tailWaves; ++k) sz.push_back(wave);
+      sz.back() += frac % K1_THREADS;
+    }
+    size_t off = 0;
+    for (size_t m : sz) { offs.push_back(off); lens.push_back(m); off += m; }
   }
   const size_t ns = offs.size();
-  ws->d_q.reserve(n * nq);
+  if (!zeroCopy) ws->d_q.reserve(n * nq);
   ws->d_valid.reserve(n);
   ws->d_pair.reserve(n);
   ws->d_reason.reserve(n);
@@ -590,11 +815,12 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
   for (size_t k = 0; k < ns; ++k) {
     const size_t off = offs[k], m = lens[k];
     cudaEvent_t evIn = ws->evSlice[3 * k], evDone = ws->evSlice[3 * k + 1], evPass = ws->evSlice[3 * k + 2];
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p + off * nq, h_q + off * nq, m * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream2));
+    if (!zeroCopy) HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p + off * nq, h_q + off * nq, m * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream2));
     HPPB200_CUDA_CHECK(cudaEventRecord(evIn, ws->stream2));
     HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream, evIn, 0));
-    launchTwoKernelsOn(ws, ws->stream, ws->d_q.p + off * nq, m, flags, ws->d_valid.p + off, ws->d_pair.p + off, ws->d_reason.p + off,
-                       ws->d_scratch.p + slots * 12 * off, counters + k, queue + 2 * off + 4096 * k, 2 * m + 4096, ws->stream4, evPass);
+    launchTwoKernelsOn(ws, ws->stream, zeroCopy ? h_q + off * nq : ws->d_q.p + off * nq, m, flags, ws->d_valid.p + off, ws->d_pair.p + off,
+                       ws->d_reason.p + off, ws->d_scratch.p + slots * 12 * off, counters + k, queue + 2 * off + 4096 * k, 2 * m + 4096,
+                       ws->stream4, evPass, zeroCopy);
     HPPB200_CUDA_CHECK(cudaEventRecord(evDone, ws->stream4));
     HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream3, evDone, 0));
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_valid + off, ws->d_valid.p + off, m, cudaMemcpyDeviceToHost, ws->stream3));
@@ -626,6 +852,10 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
     ws->last_jobs += h_cnt[k];
     if (h_cnt[k] <= 2 * m + 4096) continue;
     // queue overflow in this slice: the fused single kernel needs no queue (same rule as launchValidateConfigs)
+    if (zeroCopy) {
+      ws->d_q.reserve(n * nq);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p + off * nq, h_q + off * nq, m * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
+    }
     launchConfigKernel(ws, ws->d_q.p + off * nq, m, flags, MODE_VALIDATE, ws->d_valid.p + off, ws->d_pair.p + off, ws->d_reason.p + off, nullptr);
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_valid + off, ws->d_valid.p + off, m, cudaMemcpyDeviceToHost, ws->stream));
     if (h_first) HPPB200_CUDA_CHECK(cudaMemcpyAsync(h_first + off, ws->d_pair.p + off, m * sizeof(int32_t), cudaMemcpyDeviceToHost, ws->stream));

@@ -60,6 +60,38 @@ def test_config_validation_joint_bounds_and_ragged(pkg, eng, ur5, ur5_oracle):
     assert v[0] == 1 and f[0] == -1
 
 
+@pytest.mark.parametrize("name", ["ur5_boxes8.json", "humanoid_obst16.json", "humanoid_ff_obst6.json"])
+def test_config_pass_shadow_cores_exact_and_zero_copy(pkg, ob, monkeypatch, name):
+    """configPassKernel keeps 32-bit shadows of the bounding cores: every form must give the oracle's
+    bits: shadow (default), FP64 cores (0), shadow kernel with every pair redone from the FP64 placements (2), and
+    the zero-copy host-pointer form reading a pinned buffer over PCIe.  Hostile rows (NaN, infinities, huge angles)
+    take the exact path."""
+    import torch
+    desc = pkg.ModelDescription.load(name)
+    model = pkg.Model(desc)
+    o = ob.Oracle(desc)
+    n = 60000 + 37
+    q = pkg.uniform_configs(desc, n, seed=77)
+    q[5, 0] = np.nan; q[6, :] = np.nan; q[7, 1] = np.inf; q[8, 2] = 9.9e4; q[9, 0] = -np.inf; q[10, -1] = 1e300
+    exp = o.validate_configs(q)
+    for mode in ("1", "0", "2"):
+        monkeypatch.setenv("HPPB200_CFG_SHADOW", mode)
+        ws = pkg.Workspace(model, 0)
+        for a, b in zip(ws.validate_configs(q), exp):
+            assert np.array_equal(a, b), mode
+    monkeypatch.setenv("HPPB200_CFG_SHADOW", "1")
+    monkeypatch.setenv("HPPB200_CFG_ZEROCOPY", "1")
+    ws = pkg.Workspace(model, 0)
+    qp = torch.from_numpy(q).pin_memory()
+    v = torch.empty(n, dtype=torch.uint8).pin_memory(); f = torch.empty(n, dtype=torch.int32).pin_memory()
+    r = torch.empty(n, dtype=torch.uint8).pin_memory()
+    for m in (n, 1000 + 37, 1):  # sliced, single slice with a ragged last block, one row
+        v.zero_(); f.zero_(); r.zero_()
+        ws.validate_configs_ptr(qp.data_ptr(), m, v.data_ptr(), f.data_ptr(), r.data_ptr(), 0)
+        for a, b in zip((v.numpy()[:m], f.numpy()[:m], r.numpy()[:m]), exp):
+            assert np.array_equal(a, b[:m]), m
+
+
 @pytest.mark.parametrize("name", ["ur5_boxes0.json", "ur5_boxes1.json", "ur5_boxes32.json"])
 def test_config_validation_other_scenes(pkg, ob, name):
     desc = pkg.ModelDescription.load(name)
