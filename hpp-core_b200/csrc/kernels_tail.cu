@@ -61,7 +61,7 @@ struct TailArgs {
 // dynamic shared memory of one CTA
 struct TailLayout {
   uint32_t off_plc, off_li, off_sv, off_vmax, off_cover, off_res, off_pcov, off_pres, off_sub, off_lists, off_order, off_cnt, off_state,
-      off_pflag, off_depth, off_visit, total;
+      off_pflag, off_depth, off_visit, off_gdist, off_sorted, off_bodyof, off_jobs, total;
 };
 // smemK: entries per body pair of the lists kept in shared memory (0: lists in global memory)
 __host__ __device__ inline TailLayout tailLayout(const ModelView& mv, int smemK) {
@@ -85,6 +85,12 @@ __host__ __device__ inline TailLayout tailLayout(const ModelView& mv, int smemK)
   Lo.off_depth = o; o += (uint32_t)mv.njoints;
   o = (o + 3u) & ~3u;
   Lo.off_visit = o; o += ((uint32_t)mv.nbodypairs + 31u) / 32u * 4u;  // positions the replay has to visit
+  // narrow phase by GEOMETRY pair: distance per geometry pair, the static cost order, the owner body pair, this stage's jobs
+  o = (o + 7u) & ~7u;
+  Lo.off_gdist = o; o += (uint32_t)mv.nbgpairs * 8u;
+  Lo.off_sorted = o; o += (uint32_t)mv.nbgpairs * 2u;
+  Lo.off_bodyof = o; o += (uint32_t)mv.nbgpairs * 2u;
+  Lo.off_jobs = o; o += (uint32_t)mv.nbgpairs * 2u;
   Lo.total = (o + 15u) & ~15u;
   return Lo;
 }
@@ -120,6 +126,11 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
   uint8_t* pflag = (uint8_t*)(smem + Lo.off_pflag);  // by position: PF_* in, decision out
   uint8_t* jdepth = (uint8_t*)(smem + Lo.off_depth);
   uint32_t* visit = (uint32_t*)(smem + Lo.off_visit);
+  double* gdist = (double*)(smem + Lo.off_gdist);
+  uint16_t* sortedGp = (uint16_t*)(smem + Lo.off_sorted);
+  uint16_t* bodyOf = (uint16_t*)(smem + Lo.off_bodyof);
+  uint16_t* jobs = (uint16_t*)(smem + Lo.off_jobs);
+  __shared__ int s_cls[4], s_njobs;
   __shared__ double s_t, s_ilo, s_ihi, s_last;
   __shared__ int s_run, s_pos, s_smallest, s_subCnt, s_overflow, s_has, s_stop, s_depth, s_finished;
   __shared__ uint32_t s_edge, s_iters, s_slot;
@@ -150,6 +161,31 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
     }
     s_depth = deepest;
   }
+  // Static cost order of the geometry pairs, once per CTA: GJK with two convex shapes, one, none, closed forms.  A stage's
+  // jobs keep this order, so a round of 128 jobs is as uniform in cost (and in code path) as the stage allows: the
+  // narrow phase takes sum over rounds of the SLOWEST job of the round (thread per body pair, in pair order, it was
+  // ~3 x a convex-convex GJK per sample on the 30-joint model).
+  const int NBG = mv.nbgpairs;
+  auto gpClass = [&](int gp) -> int {
+    const DevPair& pr = T.bgpairs[gp];
+    if (pr.kind != PK_GJK) return 3;
+    const DevShape& sa = *(const DevShape*)(pr.a >= 0 ? &T.geoms[pr.a].shape : &T.obstacles[-(pr.a + 1)].shape);
+    const DevShape& sb = *(const DevShape*)(pr.b >= 0 ? &T.geoms[pr.b].shape : &T.obstacles[-(pr.b + 1)].shape);
+    return 2 - (sa.type == SH_CONVEX ? 1 : 0) - (sb.type == SH_CONVEX ? 1 : 0);
+  };
+  if (tid < 4) s_cls[tid] = 0;
+  __syncthreads();
+  for (int gp = tid; gp < NBG; gp += DT_THREADS) atomicAdd(&s_cls[gpClass(gp)], 1);
+  for (int p = tid; p < NP; p += DT_THREADS)
+    for (int gp = T.bodypairs[p].pair_begin; gp < T.bodypairs[p].pair_end; ++gp) bodyOf[gp] = (uint16_t)p;
+  __syncthreads();
+  if (tid == 0) {
+    int acc = 0;
+    for (int c = 0; c < 4; ++c) { const int k = s_cls[c]; s_cls[c] = acc; acc += k; }
+  }
+  __syncthreads();
+  for (int gp = tid; gp < NBG; gp += DT_THREADS) sortedGp[atomicAdd(&s_cls[gpClass(gp)], 1)] = (uint16_t)gp;
+  __syncthreads();
   for (;;) {
     if (tid == 0) {
       const unsigned long long i = atomicAdd(A.counter, 1ull);
@@ -312,13 +348,42 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
       // ---- D / E: narrow phase of the flagged pairs, then the replay; a second stage when the replay meets a
       //      covered pair that the reference evaluates after all ----
       for (;;) {
+        // D1: this stage's jobs = the geometry pairs of the flagged body pairs, in the static cost order
+        if (tid == 0) s_njobs = 0;
+        __syncthreads();
+        for (int base = 0; base < NBG; base += DT_THREADS) {
+          const int i = base + tid;
+          int gp = 0;
+          bool want = false;
+          if (i < NBG) {
+            gp = sortedGp[i];
+            want = (state[bodyOf[gp]] & (ST_CAND | ST_DONE)) == ST_CAND;
+          }
+          const unsigned m = __ballot_sync(0xffffffffu, want);
+          int off = 0;
+          if ((tid & 31) == 0 && m) off = atomicAdd(&s_njobs, __popc(m));
+          off = __shfl_sync(0xffffffffu, off, 0);
+          if (want) jobs[off + __popc(m & ((1u << (tid & 31)) - 1u))] = (uint16_t)gp;
+        }
+        __syncthreads();
+        // D2: one distance per thread and round.  (The reference stops a body pair at its first colliding geometry pair;
+        // the later distances computed here are never read: D3 walks them in order.)
+        {
+          const int nj = s_njobs;
+          for (int j = tid; j < nj; j += DT_THREADS) {
+            const int gp = jobs[j];
+            gdist[gp] = pairLowerBound(T, T.bgpairs[gp], plc, 1, mv.vertices, cnt);
+          }
+        }
+        __syncthreads();
+        // D3: computeDistanceLowerBound per body pair (:175-198): geometry pairs in order, the first collision reports
         for (int p = tid; p < NP; p += DT_THREADS) {
           if ((state[p] & (ST_CAND | ST_DONE)) != ST_CAND) continue;
           const DevBodyPair& B = T.bodypairs[p];
-          double dlb = INF;  // computeDistanceLowerBound (:175-198): pairs in order, the first collision reports
+          double dlb = INF;
           int hit = -1;
           for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
-            const double d = pairLowerBound(T, T.bgpairs[gp], plc, 1, mv.vertices, cnt);
+            const double d = gdist[gp];
             ++tests;
             if (d <= HPPB200_COLLISION_THRESHOLD) { hit = gp; break; }
             if (d < dlb) dlb = d;
@@ -508,17 +573,31 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   auto kern = method == HPPB200_METHOD_PROGRESSIVE ? edgeTailKernel<HPPB200_METHOD_PROGRESSIVE> : edgeTailKernel<HPPB200_METHOD_DICHOTOMY>;
   if (n == 0) return true;
   if (mv.nbodypairs > 65535 || mv.nbodypairs == 0) return false;
+  if (mv.nbgpairs > 65535) return false;  // (16-bit job records)
   int K = DT_K;
   if (smemLists) {
     K = std::min<int>(DT_K, (int)(DT_SMEM_LISTS / (16u * (uint32_t)mv.nbodypairs)));
     if (K < 8) return false;
   }
-  const TailLayout Lo = tailLayout(mv, smemLists ? K : 0);
+  TailLayout Lo = tailLayout(mv, smemLists ? K : 0);
   if (Lo.total > 200u * 1024u) return false;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Lo.total));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
   int perSM = 0;
   HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, DT_THREADS, Lo.total));
   if (perSM < 1) return false;
+  // Many edges (a whole batch, not a handful of long ones): the kernel is latency-bound at 4 warps per CTA, so resident CTAs
+  // are worth more than list capacity.  Take the shortest lists (>= 8 entries) that let one more CTA onto the SM; an edge
+  // that outgrows them is reported with `overflow_reason` and redone by the next level, like any other overflow.
+  int tailOcc = 1;
+  if (const char* v = std::getenv("HPPB200_TAIL_OCC")) tailOcc = std::atoi(v);
+  if (tailOcc && smemLists && K > 8 && n >= (size_t)ws->num_sms * 8 && perSM < DT_MINB) {
+    for (int k2 = K - 1; k2 >= 8; --k2) {
+      const TailLayout L2 = tailLayout(mv, k2);
+      int p2 = 0;
+      HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2, kern, DT_THREADS, L2.total));
+      if (p2 > perSM) { K = k2; Lo = L2; perSM = p2; break; }
+    }
+  }
   const size_t grid = std::min<size_t>(n, (size_t)ws->num_sms * (size_t)perSM);
   const size_t listBytes = smemLists ? 0 : grid * (size_t)mv.nbodypairs * DT_K * sizeof(double2);
   ws->d_tail.reserve(listBytes + 128);
