@@ -108,15 +108,37 @@ __device__ __forceinline__ void gjkBegin(GjkState& s, const T3& rel) {
 
 // One iteration.  Returns true when the algorithm has terminated; `out` is then the distance between
 // the core shapes (0 when they intersect) and s.it the number of iterations minus one.
-__device__ __forceinline__ bool gjkStep(GjkState& s, const DevShape& A, const DevShape& B, const T3& rel,
+// `rel` is a T3 in registers, or a RelStrided view of 12 doubles kept elsewhere (shared memory: 24 registers less
+// across the simplex update, where the pressure peaks); the two give the same bits (same dot() order).
+template <int STRIDE>
+struct RelStrided {
+  const double* p;  // entry k (r[0..8], t.x, t.y, t.z) at p[k * STRIDE]
+};
+__device__ __forceinline__ V3 relRtmul(const T3& R, V3 v) { return rtmul(R, v); }
+__device__ __forceinline__ V3 relRmulT(const T3& R, V3 q) { return rmul(R, q) + R.t; }
+template <int STRIDE>
+__device__ __forceinline__ V3 relRtmul(const RelStrided<STRIDE>& R, V3 v) {
+  const double* p = R.p;
+  return mk(dot(mk(p[0 * STRIDE], p[3 * STRIDE], p[6 * STRIDE]), v), dot(mk(p[1 * STRIDE], p[4 * STRIDE], p[7 * STRIDE]), v),
+            dot(mk(p[2 * STRIDE], p[5 * STRIDE], p[8 * STRIDE]), v));
+}
+template <int STRIDE>
+__device__ __forceinline__ V3 relRmulT(const RelStrided<STRIDE>& R, V3 q) {
+  const double* p = R.p;
+  return mk(dot(mk(p[0 * STRIDE], p[1 * STRIDE], p[2 * STRIDE]), q), dot(mk(p[3 * STRIDE], p[4 * STRIDE], p[5 * STRIDE]), q),
+            dot(mk(p[6 * STRIDE], p[7 * STRIDE], p[8 * STRIDE]), q)) +
+         mk(p[9 * STRIDE], p[10 * STRIDE], p[11 * STRIDE]);
+}
+template <class REL>
+__device__ __forceinline__ bool gjkStep(GjkState& s, const DevShape& A, const DevShape& B, const REL& rel,
                                         const double* __restrict__ verts, double& out) {
   const V3 v = s.v;
   const double vv = s.vv;
   const int n = s.n;
   const V3 w0 = s.w0, w1 = s.w1, w2 = s.w2;
   V3 sa = supportLocal(A, verts, -v);
-  V3 sbl = supportLocal(B, verts, rtmul(rel, v));
-  V3 sb = rmul(rel, sbl) + rel.t;
+  V3 sbl = supportLocal(B, verts, relRtmul(rel, v));
+  V3 sb = relRmulT(rel, sbl);
   V3 w = sa - sb;
   double vw = dot(v, w);
   bool stop = (n > 0 && (vv - vw) <= HPPB200_GJK_EPS_REL * vv);

@@ -47,7 +47,10 @@ constexpr int WF_RB_BIG = 32;   // models with more than 64 body pairs: the firs
 constexpr int WF_RG_BIG = 48;
 constexpr int WF_CTHREADS = 128;
 constexpr int WF_NTHREADS = 128;
-constexpr int WF_CHUNK = 128;   // jobs a warp takes from the list per atomic
+#ifndef WF_CHUNK_JOBS
+#define WF_CHUNK_JOBS 32  // (128: 68.5 ms of narrow phase per 1 M UR5 edges, 64: 62.7, 32: 61.4: the last chunks of a round are the imbalance)
+#endif
+constexpr int WF_CHUNK = WF_CHUNK_JOBS;   // jobs a warp takes from the list per atomic
 
 struct WFRoundCtl {
   unsigned nG, nC, headG, headC;
@@ -786,14 +789,8 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
       ihi = (bb < ihi) ? bb : ihi;
     }
   };
-  // uniform pass over the non-valid_ positions >= from: Mo = those whose interval does not contain [xl, xh]
-  auto pass = [&](int from, double xl, double xh, u64 (&Mo)[W]) {
-    u64 need[W];
-#pragma unroll
-    for (int w = 0; w < W; ++w) {
-      const int lo = from - 64 * w;
-      need[w] = lo >= 64 ? 0ull : (lo > 0 ? nonv[w] & (~0ull << lo) : nonv[w]);
-    }
+  // uniform pass over the positions of `need`: Mo = those whose interval does not contain [xl, xh]
+  auto pass = [&](const u64 (&need)[W], double xl, double xh, u64 (&Mo)[W]) {
     for (int c0 = 0; c0 < NP; c0 += WP_CH) {
       const unsigned nb = chunkBitsN<W, WP_CH>(need, c0);
       double2 v[WP_CH];
@@ -806,6 +803,33 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
 #pragma unroll
       for (int k = 0; k < WP_CH; ++k) mb |= (!(v[k].x <= xl && xh <= v[k].y) ? 1u : 0u) << k;
       chunkOrN<W, WP_CH>(Mo, c0, mb & nb);
+    }
+  };
+  // the same with a second test in the same loads: Co = the positions whose interval does not contain [cl, ch]
+  auto pass2 = [&](const u64 (&need)[W], double xl, double xh, u64 (&Mo)[W], double cl, double ch, u64 (&Co)[W]) {
+    for (int c0 = 0; c0 < NP; c0 += WP_CH) {
+      const unsigned nb = chunkBitsN<W, WP_CH>(need, c0);
+      double2 v[WP_CH];
+#pragma unroll
+      for (int k = 0; k < WP_CH; ++k) {
+        v[k] = make_double2(-INF, INF);
+        if ((nb >> k) & 1u) v[k] = col[(size_t)(c0 + k) * E];
+      }
+      unsigned mb = 0u, cb = 0u;
+#pragma unroll
+      for (int k = 0; k < WP_CH; ++k) {
+        mb |= (!(v[k].x <= xl && xh <= v[k].y) ? 1u : 0u) << k;
+        cb |= (!(v[k].x <= cl && ch <= v[k].y) ? 1u : 0u) << k;
+      }
+      chunkOrN<W, WP_CH>(Mo, c0, mb & nb);
+      chunkOrN<W, WP_CH>(Co, c0, cb & nb);
+    }
+  };
+  auto fromMask = [&](int from, u64 (&need)[W]) {  // the non-valid_ positions >= from
+#pragma unroll
+    for (int w = 0; w < W; ++w) {
+      const int lo = from - 64 * w;
+      need[w] = lo >= 64 ? 0ull : (lo > 0 ? nonv[w] & (~0ull << lo) : nonv[w]);
     }
   };
 
@@ -821,8 +845,27 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
   }
   __syncwarp();
   // ---- phase 2: uniform pass against the running interval as it is now ------------------------------------
+  // The same loads also answer most of phase 4 (the candidates of the NEXT sample, window [tn - hn, tn + hn] with
+  // tn = the end of the FINAL intersection and hn = alpha |tn - t|): tn can only move from the current end towards t,
+  // so every such window lies inside the hull [cl, ch] computed here, and a position whose interval contains the hull
+  // contains the window.  Phase 4 then re-reads only the positions flagged here (C1), the positions the events rewrote
+  // and those before `from` (55 % of the kernel's sectors were the two full passes).
   const bool passed = scanning && !stop;
-  if (passed) pass(from, ilo, ihi, M);
+  u64 C1[W];
+#pragma unroll
+  for (int w = 0; w < W; ++w) C1[w] = 0ull;
+  double hullLo = INF, hullHi = -INF;  // (empty: no narrowed second pass)
+  if (passed) {
+    const double te = reverse ? ilo : ihi;            // the end the parameter moves to, as it is now
+    const double he = A.alpha * fabs(te - t);
+    // windows of every tn between t and te (piecewise linear in tn), and the running interval itself: a position the
+    // events rewrite (it does not contain the running interval) is then flagged in C1 as well
+    hullLo = fmin(fmin(te - he, t), ilo) - 1e-9;
+    hullHi = fmax(fmax(te + he, t), ihi) + 1e-9;
+    u64 need[W];
+    fromMask(from, need);
+    pass2(need, ilo, ihi, M, hullLo, hullHi, C1);
+  }
   __syncwarp();
   // ---- phase 3: the other events -------------------------------------------------------------------------
   if (passed) runEvents(M);
@@ -844,7 +887,19 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     const double hn = A.alpha * fabs(tn - t);
     wl = tn - hn; wh = tn + hn;
   }
-  if (complete || (emit && !passed)) pass(complete ? 0 : pos + 1, wl, wh, cand);
+  if (complete || (emit && !passed)) {
+    u64 need[W];
+    fromMask(complete ? 0 : pos + 1, need);
+    if (complete && hullLo <= wl && wh <= hullHi) {  // narrowed: flagged by the first pass (C1), or before `from`
+#pragma unroll
+      for (int w = 0; w < W; ++w) {
+        const int lo = from - 64 * w;
+        const u64 before = lo >= 64 ? ~0ull : (lo > 0 ? ((1ull << lo) - 1ull) : 0ull);
+        need[w] &= C1[w] | before;
+      }
+    }
+    pass(need, wl, wh, cand);
+  }
   __syncwarp();
   if (emit) {
     if (passed) {
@@ -1397,10 +1452,11 @@ wfNarrowKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     unsigned wcur = 0, wend = 0;
     bool exhausted = false, have = false;
     GjkState s;
-    T3 rel;
+    // per-thread job constants in shared memory, entry k at srel[k * WF_NTHREADS]: rel (12), the two inflations, the margin
+    double* srel = (double*)(sblob + ((mv.edge_blob_bytes + 15u) & ~15u)) + threadIdx.x;
+    const RelStrided<WF_NTHREADS> relv{srel};
     const DevShape* sa = nullptr;
     const DevShape* sb = nullptr;
-    double sub0 = 0, sub1 = 0, margin = 0;
     double* out = nullptr;
     for (;;) {
       const unsigned idle = __ballot_sync(FULL, !have);
@@ -1429,9 +1485,12 @@ wfNarrowKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
             else { const DevObstacle& O = T.obstacles[-(pr.a + 1)]; sa = (const DevShape*)&O.shape; TA = load12(O.P); }
             if (pr.b >= 0) { sb = (const DevShape*)&T.geoms[pr.b].shape; TB = load12(store + (size_t)pr.b * 12); }
             else { const DevObstacle& O = T.obstacles[-(pr.b + 1)]; sb = (const DevShape*)&O.shape; TB = load12(O.P); }
-            rel = composeInv(TA, TB);
+            const T3 rel = composeInv(TA, TB);
             gjkBegin(s, rel);
-            sub0 = inflation(*sa); sub1 = inflation(*sb); margin = pr.margin;
+#pragma unroll
+            for (int k = 0; k < 9; ++k) srel[k * WF_NTHREADS] = rel.r[k];
+            srel[9 * WF_NTHREADS] = rel.t.x; srel[10 * WF_NTHREADS] = rel.t.y; srel[11 * WF_NTHREADS] = rel.t.z;
+            srel[12 * WF_NTHREADS] = inflation(*sa); srel[13 * WF_NTHREADS] = inflation(*sb); srel[14 * WF_NTHREADS] = pr.margin;
             out = A.res + (size_t)ri * E + e;
             have = true;
             need = false;
@@ -1444,9 +1503,9 @@ wfNarrowKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
       if (!__any_sync(FULL, have)) break;  // nothing running and nothing left to fetch
       if (have) {
         double core;
-        if (gjkStep(s, *sa, *sb, rel, mv.vertices, core)) {
+        if (gjkStep(s, *sa, *sb, relv, mv.vertices, core)) {
           // shapeDistance (GJK kinds) - margin, same operation order as pairLowerBound
-          *out = ((core - sub0) - sub1) - margin;
+          *out = ((core - srel[12 * WF_NTHREADS]) - srel[13 * WF_NTHREADS]) - srel[14 * WF_NTHREADS];
           iterations += (unsigned)s.it + 1u;
           if (s.it == HPPB200_GJK_MAX_ITER) ++capHits;
           have = false;
@@ -1585,7 +1644,7 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
     if ((int)b.pairs.size() > WF_RG) return false;  // (a body pair must fit one round's job cap)
   if (NP > 256) return false;
   const int W = NP <= 64 ? 1 : 4;
-  const size_t smemC = 48 + WF_RING_BYTES + mv.edge_blob_bytes, smemN = 16 + mv.edge_blob_bytes;
+  const size_t smemC = 48 + WF_RING_BYTES + mv.edge_blob_bytes, smemN = 16 + ((mv.edge_blob_bytes + 15u) & ~15u) + 15u * WF_NTHREADS * sizeof(double);
   if (smemC > 200u * 1024u) return false;
   const bool tree = modelIsTree(m);
 
