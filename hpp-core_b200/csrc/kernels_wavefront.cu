@@ -101,6 +101,10 @@ struct WFArgs {
   double2* ivl;        // Dichotomy: [NP * WD_K][E] validated intervals by order position
   double2* sub;        // Dichotomy: [WD_KS][E] valid subset of the edge
   uint8_t* st_subCnt;  // Dichotomy: [E]
+  // control form 3 (Progressive): the emission record and the results slot-major, so that one thread pulls its slot's
+  // rows into shared memory with a few 16-byte cp.async at kernel start (one latency instead of one per use)
+  uint32_t* emA;       // [E][rb]: position | first result << 8 | pair id << 16 | geometry pairs << 24   (null: emPos / emRes below)
+  double* resA;        // [E][rg] (null: res below)
   uint16_t* emPos;     // [WF_RB][E] order position of the k-th emitted body pair
   uint8_t* emRes;      // [WF_RB][E] its first result slot
   double2* fold;       // [WF_RB][E] its folded result: validated interval (a, b), or (geometry pair, -inf)
@@ -236,8 +240,11 @@ __device__ __forceinline__ void wfEmitJobs(const WFArgs& A, const Tables& T, uin
         const DevBodyPair& B = T.bodypairs[id];
         const int ng = B.pair_end - B.pair_begin;
         if (nb >= A.rb || nr + ng > A.rg) { full = true; break; }
-        A.emPos[(size_t)nb * E + e] = (uint16_t)p;
-        A.emRes[(size_t)nb * E + e] = (uint8_t)nr;
+        if (A.emA) A.emA[(size_t)e * A.rb + nb] = (uint32_t)p | ((uint32_t)nr << 8) | ((uint32_t)id << 16) | ((uint32_t)ng << 24);
+        else {
+          A.emPos[(size_t)nb * E + e] = (uint16_t)p;
+          A.emRes[(size_t)nb * E + e] = (uint8_t)nr;
+        }
         for (int gp = B.pair_begin; gp < B.pair_end; ++gp) {
           const bool g = T.bgpairs[gp].kind == PK_GJK;
           jl[nr++] = (uint32_t)gp | (g ? 0x80000000u : 0u);
@@ -254,21 +261,17 @@ __device__ __forceinline__ void wfEmitJobs(const WFArgs& A, const Tables& T, uin
     const int g2 = __shfl_up_sync(FULL, gOff, o), c2 = __shfl_up_sync(FULL, cOff, o);
     if (lane >= o) { gOff += g2; cOff += c2; }
   }
+  // one global atomic per warp and list (a CTA-wide prefix cost two barriers that every warp of the CTA waited at:
+  // 12 % of the control kernel's stall samples)
   unsigned wG = 0, wC = 0;
   if (lane == 31) {
-    wG = gOff ? atomicAdd(&sCnt[0], (unsigned)gOff) : 0u;
-    wC = cOff ? atomicAdd(&sCnt[1], (unsigned)cOff) : 0u;
+    wG = gOff ? atomicAdd(&ctl->nG, (unsigned)gOff) : 0u;
+    wC = cOff ? atomicAdd(&ctl->nC, (unsigned)cOff) : 0u;
   }
   wG = __shfl_sync(FULL, wG, 31);
   wC = __shfl_sync(FULL, wC, 31);
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    sCnt[2] = sCnt[0] ? atomicAdd(&ctl->nG, sCnt[0]) : 0u;
-    sCnt[3] = sCnt[1] ? atomicAdd(&ctl->nC, sCnt[1]) : 0u;
-  }
-  __syncthreads();
-  size_t gi = (size_t)sCnt[2] + wG + (unsigned)(gOff - nGl);
-  size_t ci = (size_t)sCnt[3] + wC + (unsigned)(cOff - nCl);
+  size_t gi = (size_t)wG + (unsigned)(gOff - nGl);
+  size_t ci = (size_t)wC + (unsigned)(cOff - nCl);
   for (int i = 0; i < nr; ++i) {
     const uint32_t j = jl[i];
     const unsigned long long job =
@@ -623,18 +626,40 @@ __device__ __forceinline__ void chunkOrN(u64 (&m)[W], int c0, unsigned bits) {
   for (int k = 0; k < N; ++k) maskSet<W>(m, c0 + k, (bits >> k) & 1u);
 }
 constexpr int WP_CH = 8;  // positions per trip of the uniform pass
+constexpr int WF_RES_STAGED = 8;  // control form 3: results per slot staged in shared memory (8 keeps 8 CTAs per SM on UR5-class models)
 
 #ifndef WF_PC_MINB
 #define WF_PC_MINB 8
 #endif
-template <int W>
+// AOS (control form 3): the emission records and last round's distances of the slot come slot-major (WFArgs::emA, resA)
+// and are pulled into shared memory by the thread itself with 16-byte cp.async while the blob is staged; the fold of a
+// distance into a validated interval happens in the event that uses it (its only remaining load, vht, is issued next to
+// the event's interval load).  Why: the kernel is bound by the NUMBER of dependent global-load steps a warp goes through
+// (profiles/r2c_wfProgControl_ncu_full.txt), and the up-front fold loop alone was 4 steps x max(nEm) of them.
+template <int W, bool AOS>
 __global__ void __launch_bounds__(WF_CTHREADS, W == 1 ? WF_PC_MINB : 4)
 wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
-  // shared memory: [0,8) mbarrier | [16,48) block counters | model blob prefix
+  // shared memory: [0,8) mbarrier | [16,48) block counters | model blob prefix | AOS: staging rows, 16-byte chunk c of thread t at (c * 128 + t) * 16
   extern __shared__ __align__(16) unsigned char smem[];
   uint64_t* bar = (uint64_t*)smem;
   unsigned* sCnt = (unsigned*)(smem + 16);
   unsigned char* sblob = smem + 48;
+  unsigned char* stg = sblob + ((mv.edge_blob_bytes + 15u) & ~15u) + (size_t)threadIdx.x * 16;
+  const int NE = AOS ? (A.rb * 4 + 15) / 16 : 0;  // chunks of the emission row; the result row follows
+  if (AOS) {
+    const uint32_t e0 = blockIdx.x * WF_CTHREADS + threadIdx.x;
+    const int NR = WF_RES_STAGED / 2;  // the first WF_RES_STAGED results of the slot; later ones (rare) are read in place
+    const unsigned char* ge = (const unsigned char*)(A.emA + (size_t)e0 * A.rb);
+    const unsigned char* gr = (const unsigned char*)(A.resA + (size_t)e0 * A.rg);
+    for (int c = 0; c < NE; ++c) cpAsync16(stg + (size_t)c * WF_CTHREADS * 16, ge + c * 16);
+    for (int c = 0; c < NR; ++c) cpAsync16(stg + (size_t)(NE + c) * WF_CTHREADS * 16, gr + c * 16);
+    cpAsyncCommit();
+  }
+  auto emAt = [&](int k) -> uint32_t { return ((const uint32_t*)(stg + (size_t)(k >> 2) * WF_CTHREADS * 16))[k & 3]; };
+  auto resAt = [&](int r) -> double {
+    if (r >= WF_RES_STAGED) return A.resA[(size_t)(blockIdx.x * WF_CTHREADS + threadIdx.x) * A.rg + r];
+    return ((const double*)(stg + (size_t)(NE + (r >> 1)) * WF_CTHREADS * 16))[r & 1];
+  };
   if (threadIdx.x < 8) sCnt[threadIdx.x] = 0u;
   stageBlobTMA(sblob, mv.blob, mv.edge_blob_bytes, bar);
   const Tables T = makeTables(sblob, mv);
@@ -684,7 +709,7 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
   // of the nEm entries are independent; inside the event loop they were a chain of four dependent global loads each).
   // BodyPairCollision::validateConfiguration :65-89 up to the interval [t - (hd + ht), t + (hd + ht)]; a collision is
   // kept as (geometry pair, -inf).  Whether an interval is USED is decided by the replay below.
-  if (active) {
+  if (!AOS && active) {
     const uint16_t* od = A.ord + (size_t)e * A.ordStride;
     for (int k = 0; k < nEm; ++k) {
       const int p = A.emPos[(size_t)k * E + e];
@@ -714,6 +739,25 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
     }
   }
 
+  if (AOS) cpAsyncWait<0>();  // (every thread reads only the chunks it copied itself)
+  // AOS: BodyPairCollision::validateConfiguration :65-89 for the c-th emitted body pair, at the moment the replay uses it
+  auto foldAt = [&](int c, double2 vh) -> double2 {
+    const uint32_t em = emAt(c);
+    const int r0 = (int)((em >> 8) & 0xffu), ng = (int)(em >> 24);
+    double dlb = INF;  // computeDistanceLowerBound (:175-198): geometry pairs in order, first collision reports
+    int hit = -1;
+    for (int j = 0; j < ng; ++j) {
+      const double d = resAt(r0 + j);
+      if (d <= HPPB200_COLLISION_THRESHOLD) { hit = j; break; }
+      if (d < dlb) dlb = d;
+    }
+    if (hit >= 0) return make_double2((double)(T.bodypairs[(em >> 16) & 0xffu].pair_begin + hit), -INF);
+    double hd, ht;  // :72-85
+    if (dlb == INF) { hd = INF; ht = 0; }
+    else { hd = dlb / vh.x; ht = vh.y; }
+    return make_double2(t - (hd + ht), t + (hd + ht));
+  };
+  auto posAt = [&](int c) -> int { return AOS ? (int)(emAt(c) & 0xffu) : (int)A.emPos[(size_t)c * E + e]; };
   // The phases below are separated by __syncwarp(): the event loops have data-dependent trip counts, and without
   // an explicit reconvergence point the lanes that leave a loop early run the rest of the kernel on their own
   // (measured: 3.2 of 32 lanes in the completion code).
@@ -732,7 +776,7 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
   const bool scanning = active;  // slots that hold an edge at the start of the round
   bool vdone = false, stop = false, emit = false;
   int cursor = 0;
-  int nextP = (scanning && nEm > 0) ? (int)A.emPos[e] : -1;
+  int nextP = (scanning && nEm > 0) ? posAt(0) : -1;
 
   // events of the positions in Mk, in order (validateIntervals, continuous-validation.hh:267-298)
   auto runEvents = [&](u64 (&Mk)[W]) {
@@ -746,7 +790,29 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
         ihi = (L < ihi) ? L : ihi;
         vdone = true;
       }
-      const double2 lh = col[(size_t)p * E];
+      double2 lh, rr;
+      if (AOS) {
+        // results of pairs the replay skipped (the walk order is fixed: this does not depend on position p's interval)
+        while (nextP >= 0 && nextP < p) {
+          ++discarded;
+          ++cursor;
+          nextP = cursor < nEm ? posAt(cursor) : -1;
+        }
+        double2 vh = make_double2(1.0, 0.0);
+        if (nextP == p) vh = A.vht[(size_t)((emAt(cursor) >> 16) & 0xffu) * E + e];  // in flight next to the interval
+        lh = col[(size_t)p * E];
+        if (lh.x <= ilo && ihi <= lh.y) continue;  // validInterval_ contains the running interval (:56-63)
+        if (nextP != p) {  // the reference evaluates this pair now and its distance is not there yet
+          emit = true;
+          pos = p;
+          stop = true;
+          break;
+        }
+        rr = foldAt(cursor, vh);
+        ++cursor;
+        nextP = cursor < nEm ? posAt(cursor) : -1;
+      } else {
+      lh = col[(size_t)p * E];
       if (lh.x <= ilo && ihi <= lh.y) continue;  // validInterval_ contains the running interval (:56-63)
       while (nextP >= 0 && nextP < p) {  // results of pairs the replay skipped
         ++discarded;
@@ -759,9 +825,10 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
         stop = true;
         break;
       }
-      const double2 rr = A.fold[(size_t)cursor * E + e];
+      rr = A.fold[(size_t)cursor * E + e];
       ++cursor;
       nextP = cursor < nEm ? (int)A.emPos[(size_t)cursor * E + e] : -1;
+      }
       const double a = rr.x, bb = rr.y;
       if (bb == -INF) {  // collision: a carries the geometry pair
         finishEdge(false, HPPB200_REASON_COLLISION, t, lastValid, (int)a);
@@ -1491,7 +1558,7 @@ wfNarrowKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
             for (int k = 0; k < 9; ++k) srel[k * WF_NTHREADS] = rel.r[k];
             srel[9 * WF_NTHREADS] = rel.t.x; srel[10 * WF_NTHREADS] = rel.t.y; srel[11 * WF_NTHREADS] = rel.t.z;
             srel[12 * WF_NTHREADS] = inflation(*sa); srel[13 * WF_NTHREADS] = inflation(*sb); srel[14 * WF_NTHREADS] = pr.margin;
-            out = A.res + (size_t)ri * E + e;
+            out = A.resA ? A.resA + (size_t)e * A.rg + ri : A.res + (size_t)ri * E + e;
             have = true;
             need = false;
             ++tests;
@@ -1522,7 +1589,7 @@ wfNarrowKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
       const uint32_t e = (uint32_t)job;
       const int gp = (int)((job >> 32) & 0x00ffffffu), ri = (int)(job >> 56);
       const DevPair pr = T.bgpairs[gp];
-      A.res[(size_t)ri * E + e] = pairLowerBound(T, pr, A.plc + (size_t)e * slotStride, 1, mv.vertices, cnt);
+      *(A.resA ? A.resA + (size_t)e * A.rg + ri : A.res + (size_t)ri * E + e) = pairLowerBound(T, pr, A.plc + (size_t)e * slotStride, 1, mv.vertices, cnt);
       ++tests;
     }
     iterations += cnt.iterations;
@@ -1680,7 +1747,8 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   const size_t o_counter = c.take<unsigned long long>(1), o_ctl = c.take<WFRoundCtl>(2), o_alive = c.take<unsigned>(BATCH);
   const bool dich = method == HPPB200_METHOD_DICHOTOMY;
   const size_t o_lohi = c.take<double2>(dich ? 0 : (size_t)NP * E), o_ord = c.take<uint16_t>((size_t)((NP + 15) / 16 * 16) * E);
-  int controlForm = 2;  // Progressive: 2 = phase-convergent control kernel with the fold inside; 1 = first form + wfFoldKernel
+  int controlForm = 3;  // Progressive: 3 = form 2 with slot-major emission / result rows prefetched to shared memory and the fold inside the events;
+                        // 2 = phase-convergent control kernel with the fold up front; 1 = first form + wfFoldKernel
   if (const char* v = std::getenv("HPPB200_WF_CONTROL")) controlForm = std::atoi(v);
   const bool foldKernel = dich || controlForm == 1;
   const size_t o_vmax = c.take<double>(foldKernel ? (size_t)NP * E : 0), o_sv = c.take<double>((size_t)mv.nv * E);
@@ -1694,6 +1762,8 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   A.rb = NP > 64 ? WF_RB_BIG : WF_RB;
   A.rg = NP > 64 ? WF_RG_BIG : WF_RG;
   const size_t RB = (size_t)A.rb, RG = (size_t)A.rg;
+  const bool aos = !dich && controlForm == 3;
+  const size_t o_emA = c.take<uint32_t>(aos ? RB * E : 0), o_resA = c.take<double>(aos ? RG * E : 0);
   const size_t o_emPos = c.take<uint16_t>(RB * E), o_emRes = c.take<uint8_t>(RB * E);
   const size_t o_fold = c.take<double2>(RB * E);
   const size_t o_res = c.take<double>(RG * E), o_plc = c.take<double>(E * (size_t)A.fkSlots * 12);
@@ -1716,12 +1786,16 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
   A.st_subCnt = base + o_subCnt;
   A.emPos = (uint16_t*)(base + o_emPos); A.emRes = base + o_emRes; A.fold = (double2*)(base + o_fold);
   A.res = (double*)(base + o_res); A.plc = (double*)(base + o_plc);
+  A.emA = aos ? (uint32_t*)(base + o_emA) : nullptr;
+  A.resA = aos ? (double*)(base + o_resA) : nullptr;
   A.jobsG = (unsigned long long*)(base + o_jG); A.jobsC = (unsigned long long*)(base + o_jC);
 
-  const size_t smemCtl = (foldKernel && !dich) ? smemC : 48 + mv.edge_blob_bytes;
+  const size_t smemCtl = (foldKernel && !dich) ? smemC
+                         : 48 + ((mv.edge_blob_bytes + 15u) & ~15u) + (aos ? ((RB * 4 + 15) / 16 + WF_RES_STAGED / 2) * 16 * (size_t)WF_CTHREADS : 0);
   auto kc = dich ? (W == 1 ? wfDichControlKernel<1> : wfDichControlKernel<4>)
                  : (controlForm == 1 ? (W == 1 ? wfControlKernel<1> : wfControlKernel<4>)
-                                     : (W == 1 ? wfProgControlKernel<1> : wfProgControlKernel<4>));
+                    : controlForm == 2 ? (W == 1 ? wfProgControlKernel<1, false> : wfProgControlKernel<4, false>)
+                                       : (W == 1 ? wfProgControlKernel<1, true> : wfProgControlKernel<4, true>));
   auto kf = tree ? wfFkKernel<true> : wfFkKernel<false>;
   const size_t smemF = 16 + (WF_CTHREADS / 32) * WF_FK_TILE + mv.edge_blob_bytes;
   HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemF));
@@ -1750,7 +1824,8 @@ bool launchWavefront(Workspace* ws, int method, double tol, int reverse, const d
     addMove(A.st_cbits, 8, (size_t)4 * W, false); addMove(A.ivl, 16, (size_t)NP * WD_K, false);
     addMove(A.sub, 16, WD_KS, false); addMove(A.st_subCnt, 1, 1, false);
   }
-  addMove(A.emPos, 2, RB, false); addMove(A.emRes, 1, RB, false); addMove(A.res, 8, RG, false);
+  if (aos) { addMove(A.emA, 4, RB, true); addMove(A.resA, 8, RG, true); }
+  else { addMove(A.emPos, 2, RB, false); addMove(A.emRes, 1, RB, false); addMove(A.res, 8, RG, false); }
   addMove(A.plc, 8, (size_t)A.fkSlots * 12, true);
   uint32_t* d_src = (uint32_t*)(base + o_cmp);
   uint32_t* d_dst = d_src + E;
