@@ -55,6 +55,7 @@ ABI_SYMBOLS = [
     "hppb200_multi_create", "hppb200_multi_destroy", "hppb200_multi_num_devices", "hppb200_multi_workspace",
     "hppb200_multi_validate_configs", "hppb200_multi_validate_edges",
     "hppb200_pack_mask", "hppb200_unpack_mask", "hppb200_knn_merge_shards",
+    "hppb200_kprm_link_candidates", "hppb200_roadmap_merge_edges",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_set_labels", "hppb200_knn_size",
     "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_latency_time", "hppb200_knn_tc_debug_tile",
 ]
@@ -115,6 +116,28 @@ def measure_tmem_read_peak(device=0):
     v = C.c_double()
     _check(lib().hppb200_measure_tmem_read_peak(C.c_int(device), C.byref(v)))
     return v.value
+
+
+def kprm_link_candidates(nbrs, dist, symmetric_distance):
+    """hppb200_kprm_link_candidates: (kind [n][k] u8, mirror [n][k] i64) of the directed kPRM* candidates (host-side C++)."""
+    nbrs = np.ascontiguousarray(nbrs, np.int64)
+    n, k = nbrs.shape
+    dist = np.ascontiguousarray(dist, np.float64) if dist is not None else None
+    kind, mirror = np.zeros((n, k), np.uint8), np.zeros((n, k), np.int64)
+    _check(lib().hppb200_kprm_link_candidates(C.c_size_t(n), C.c_int(k), nbrs.ctypes.data_as(C.c_void_p),
+                                              dist.ctypes.data_as(C.c_void_p) if dist is not None else None,
+                                              C.c_int(1 if symmetric_distance else 0), kind.ctypes.data_as(C.c_void_p),
+                                              mirror.ctypes.data_as(C.c_void_p)))
+    return kind, mirror
+
+
+def roadmap_merge_edges(labels, pairs):
+    """hppb200_roadmap_merge_edges: the labels after adding `pairs` ([m][2]) in order (the second component joins the first)."""
+    labels = np.array(labels, np.int64, copy=True)
+    pairs = np.ascontiguousarray(pairs, np.int64).reshape(-1, 2)
+    _check(lib().hppb200_roadmap_merge_edges(C.c_size_t(len(labels)), labels.ctypes.data_as(C.c_void_p),
+                                             pairs.ctypes.data_as(C.c_void_p), C.c_size_t(len(pairs))))
+    return labels
 
 
 class Model:

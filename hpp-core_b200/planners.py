@@ -15,6 +15,13 @@ import numpy as np
 from .model_io import uniform_configs
 
 
+def _pkg():
+    """the package module (host-side C++ helpers of libhppb200.so: kprm_link_candidates, roadmap_merge_edges)"""
+    from . import kprm_link_candidates, roadmap_merge_edges  # noqa: F401
+    import sys
+    return sys.modules[__package__]
+
+
 class EngineBackend:
     """hpp-core's interfaces for one model, served by the engine (Workspace + NearestNeighbor)."""
 
@@ -164,43 +171,14 @@ class Roadmap:
         return out
 
     def add_edges(self, pairs):
-        """`add_edge` for many edges in the given order with the same final state: the component merges are those of
-        the first-come spanning forest (minimum spanning forest with the edge rank as weight), replayed in order; the
-        device mirror receives the final labels in one call."""
-        from scipy.sparse import coo_matrix
-        from scipy.sparse.csgraph import minimum_spanning_tree
+        """`add_edge` for many edges in the given order with the same final state (hppb200_roadmap_merge_edges: the
+        component of an edge's second node joins the first node's, edge by edge); the device mirror receives the final
+        labels in one call."""
         pairs = np.asarray(pairs, np.int64).reshape(-1, 2)
         if len(pairs) == 0:
             return
         self._blocks.append(pairs)
-        n = len(self.cc)
-        cc = np.asarray(self.cc, np.int64)
-        labels, rep = np.unique(cc, return_index=True)           # first node of every existing component
-        rep_of = rep[np.searchsorted(labels, cc)]
-        a, c = rep_of[pairs[:, 0]], rep_of[pairs[:, 1]]
-        keep = a != c
-        lo, hi = np.minimum(a, c), np.maximum(a, c)
-        _, firsts = np.unique((lo * n + hi)[keep], return_index=True)
-        ranks = np.nonzero(keep)[0][firsts]                      # first occurrence of every unordered component pair
-        g = coo_matrix((ranks + 1.0, (lo[ranks], hi[ranks])), shape=(n, n))
-        msf = minimum_spanning_tree(g.tocsr()).tocoo()
-        merge_ranks = np.sort(msf.data.astype(np.int64) - 1)
-        parent = np.arange(n)
-
-        def root(x):
-            while parent[x] != x:
-                parent[x] = parent[parent[x]]
-                x = parent[x]
-            return x
-
-        for r in merge_ranks:                                    # ConnectedComponent::merge: the second joins the first
-            ra, rc = root(a[r]), root(c[r])
-            if ra != rc:
-                parent[rc] = ra
-        final = np.arange(n)
-        for x in rep.tolist():
-            final[x] = root(x)
-        new_cc = cc[final[rep_of]]
+        new_cc = _pkg().roadmap_merge_edges(self.cc, pairs)      # union-find replay in insertion order (host C++)
         self.cc = new_cc
         self.b.set_labels(new_cc.astype(np.int32))
 
@@ -428,27 +406,16 @@ class KPrmStar:
         nbrs = np.asarray(nbrs, np.int64)
         tm["k-NN (one call)"] = time.perf_counter() - t0
         t0 = time.perf_counter()
-        i_of = np.repeat(np.arange(n, dtype=np.int64), nbrs.shape[1])
-        j_of = nbrs.ravel()
-        cand = (j_of >= 0) & (j_of != i_of)                      # directed candidates (i, j), j among i's neighbours
-        mirror = j_of * n + i_of
-        if getattr(self.desc, "has_freeflyer", False) or not self.symmetric_distance:
-            keys = np.sort((i_of * n + j_of)[cand])              # is i among j's neighbours?  by lookup
-            pos = np.minimum(np.searchsorted(keys, mirror), max(len(keys) - 1, 0))
-            mirrored = cand & (keys[pos] == mirror) if len(keys) else np.zeros_like(cand)
-        else:
-            # WeighedDistance on a vector space is symmetric bit for bit ((a - b)^2 == (b - a)^2, same summation order),
-            # and the k nearest are the k smallest (distance, index) keys: i is among j's neighbours iff its key is not
-            # above j's last one
-            jj = np.where(cand, j_of, 0)
-            d_ij = np.asarray(dist).ravel()
-            d_last, i_last = np.asarray(dist)[jj, -1], nbrs[jj, -1]
-            mirrored = cand & ((i_last < 0) | (d_ij < d_last) | ((d_ij == d_last) & (i_of <= i_last)))
-        second = cand & (j_of < i_of) & mirrored                 # tried by the reference only if j -> i was invalid
-        first = cand & ~second                                   # always tried
+        # directed candidates (i, j), j among i's neighbours: `first` = always tried, `second` = tried by the reference only
+        # if the mirrored edge j -> i (j < i, i among j's neighbours) was invalid; hppb200_kprm_link_candidates (host C++,
+        # csrc/planner_link.cpp) classifies all N k of them and returns, for a `second`, the slot of its mirror
+        kk = nbrs.shape[1]
+        symmetric = self.symmetric_distance and not getattr(self.desc, "has_freeflyer", False)
+        kind, mirror = _pkg().kprm_link_candidates(nbrs, dist if symmetric else None, symmetric)
+        kind, mirror, j_of = kind.ravel(), mirror.ravel(), nbrs.ravel()
 
         def validate(sel):
-            a, c = i_of[sel], j_of[sel]
+            a, c = sel // kk, j_of[sel]
             if len(a) == 0:
                 return np.zeros(0, bool)
             if hasattr(b, "validate_nodes"):  # both ends live in the device mirror: send indices, not configurations
@@ -456,26 +423,19 @@ class KPrmStar:
             qa, qc = rm.nodes[a], rm.nodes[c]
             return np.asarray(b.validate(qa, qc, b.lengths(qa, qc), False)[0], bool)
 
-        ok = np.zeros(len(i_of), bool)
-        f_idx = np.nonzero(first)[0]
+        ok = np.zeros(len(j_of), bool)
+        f_idx = np.nonzero(kind == 1)[0]
+        s_idx = np.nonzero(kind == 2)[0]
         tm["candidate pairs (host)"] = time.perf_counter() - t0
         t0 = time.perf_counter()
         ok[f_idx] = validate(f_idx)
-        # outcome of the mirrored edge (j, i) of every `second` candidate: it is a mirrored `first` candidate of node j
-        # (j < i); both sets hold every mirrored unordered pair once, so sorting by the pair key aligns them
-        fm_idx = np.nonzero(first & mirrored & (i_of < j_of))[0]
-        s_idx = np.nonzero(second)[0]
-        fm_idx = fm_idx[np.argsort((i_of * n + j_of)[fm_idx])]
-        s_idx = s_idx[np.argsort(mirror[s_idx])]
-        assert len(fm_idx) == len(s_idx)
-        m_ok = ok[fm_idx]
-        s_idx = s_idx[~m_ok]
+        s_idx = s_idx[~ok[mirror[s_idx]]]                        # the mirrored edge was found invalid
         ok[s_idx] = validate(s_idx)
         self.validated_edges = int(len(f_idx) + len(s_idx))
         tm["edge validation (two batches, host gathers included)"] = time.perf_counter() - t0
         t0 = time.perf_counter()
         e_idx = np.nonzero(ok)[0]                                # node by node, nearest neighbour first: the reference order
-        rm.add_edges(np.stack([i_of[e_idx], j_of[e_idx]], axis=1))
+        rm.add_edges(np.stack([e_idx // kk, j_of[e_idx]], axis=1))
         tm["roadmap edges + components (host)"] = time.perf_counter() - t0
         return self.solved()
 

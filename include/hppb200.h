@@ -401,6 +401,25 @@ int hppb200_unpack_mask(void* cuda_stream, const uint32_t* bits, size_t n, uint8
 int hppb200_knn_merge_shards(void* cuda_stream, const double* dist, const int64_t* idx, int nshards,
                              size_t nqueries, int k, int64_t* out_idx, double* out_dist);
 
+/* ---- batched planner front-end: host-side array passes (no device work) ---- */
+/* kPrmStar::linkNodes / connectNodeToClosestNeighbors (reference src/path-planner/k-prm-star.cc:134-193) over the neighbour
+   lists of ALL nodes at once.  nbrs / dist [n][k]: the k nearest nodes of every node, nearest first (-1 padded), as
+   hppb200_knn_query returns them with the nodes themselves as queries.  The reference walks node i's list and skips a
+   neighbour j that already has an edge j -> i; so a directed candidate (i, j) is
+     kind 1: validated whatever happens (j > i, or i is not among j's neighbours);
+     kind 2: validated only if the mirrored candidate (j, i) was found invalid; mirror[slot] = flat slot j * k + position
+             of i in j's list, where that outcome lives;
+     kind 0: no candidate (padding, the node itself).
+   symmetric_distance != 0: the distance is symmetric bit for bit (WeighedDistance on a vector space, reference
+   src/weighed-distance.cc:272-289) and the lists are sorted by (distance, index): membership by binary search on that key;
+   otherwise by scanning j's list. */
+int hppb200_kprm_link_candidates(size_t n, int k, const int64_t* nbrs, const double* dist, int symmetric_distance,
+                                 uint8_t* kind /* [n][k] */, int64_t* mirror /* [n][k] */);
+/* Roadmap::addEdges + ConnectedComponent::merge (reference src/roadmap.cc:209-255) for `nedges` edges (pairs [nedges][2],
+   node indices) in insertion order: the component of an edge's second node joins the component of its first node.
+   labels [n] in/out: connected-component label per node (nodes sharing a label on entry are one component). */
+int hppb200_roadmap_merge_edges(size_t n, int64_t* labels, const int64_t* pairs, size_t nedges);
+
 /* ---- nearest neighbour (WeighedDistance brute force) ------------------- */
 int hppb200_knn_create(const hppb200_model* m, int device, hppb200_knn** out);
 void hppb200_knn_destroy(hppb200_knn* nn);

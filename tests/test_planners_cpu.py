@@ -178,3 +178,41 @@ def test_partial_shortcut_speculative_equals_sequential(pkg, ob, ur5):
     # a single straight path: generatePath returns null for every joint (rkAtP2 == rkAtP1)
     one = pkg.PartialShortcut(OracleBackend(ob.Oracle(ur5), 1, 1e-3), ur5)
     assert np.array_equal(one.optimize(way[:2]), way[:2]) and one.failed_joints == list(range(ur5.njoints))
+
+
+def test_kprm_link_helpers_match_the_array_form(pkg):
+    """hppb200_kprm_link_candidates / hppb200_roadmap_merge_edges (host C++, csrc/planner_link.cpp) against the plain numpy
+    statement of the same rules: `second` = (i, j) with j < i and i among j's neighbours, its mirror the slot of (j, i);
+    edge merges = ConnectedComponent::merge edge by edge (the second component joins the first)."""
+    rng = np.random.default_rng(3)
+    n, k = 300, 9
+    pts = rng.normal(size=(n, 3))
+    pts[17] = pts[40]  # exact distance ties
+    d = ((pts[:, None, :] - pts[None, :, :]) ** 2).sum(-1)
+    order = np.lexsort((np.broadcast_to(np.arange(n), (n, n)), d), axis=1)  # by (distance, index); the node itself first
+    nbrs = order[:, :k].astype(np.int64)
+    dist = np.take_along_axis(d, nbrs, axis=1)
+    nbrs[5, -2:] = -1  # padding
+    for symmetric in (True, False):
+        kind, mirror = pkg.kprm_link_candidates(nbrs, dist if symmetric else None, symmetric)
+        for i in range(n):
+            for s in range(k):
+                j = nbrs[i, s]
+                if j < 0 or j == i:
+                    assert kind[i, s] == 0 and mirror[i, s] == -1
+                    continue
+                pos = np.nonzero(nbrs[j] == i)[0]
+                if j < i and len(pos):
+                    assert kind[i, s] == 2 and mirror[i, s] == j * k + pos[0], (i, s)
+                else:
+                    assert kind[i, s] == 1 and mirror[i, s] == -1, (i, s)
+    lab = np.arange(n, dtype=np.int64) + 1000
+    lab[7] = lab[3]; lab[250] = lab[3]
+    pairs = rng.integers(0, n, (400, 2))
+    cc = lab.copy()
+    for a, b in pairs:
+        ca, cb = cc[a], cc[b]
+        if ca != cb:
+            cc[cc == cb] = ca
+    assert np.array_equal(pkg.roadmap_merge_edges(lab, pairs), cc)
+    assert np.array_equal(pkg.roadmap_merge_edges(lab, np.zeros((0, 2), np.int64)), lab)
