@@ -130,7 +130,7 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
   uint16_t* sortedGp = (uint16_t*)(smem + Lo.off_sorted);
   uint16_t* bodyOf = (uint16_t*)(smem + Lo.off_bodyof);
   uint16_t* jobs = (uint16_t*)(smem + Lo.off_jobs);
-  __shared__ int s_cls[4], s_njobs;
+  __shared__ int s_cls[4], s_njobs, s_firstLimit;
   __shared__ double s_t, s_ilo, s_ihi, s_last;
   __shared__ int s_run, s_pos, s_smallest, s_subCnt, s_overflow, s_has, s_stop, s_depth, s_finished;
   __shared__ uint32_t s_edge, s_iters, s_slot;
@@ -185,6 +185,20 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
   }
   __syncthreads();
   for (int gp = tid; gp < NBG; gp += DT_THREADS) sortedGp[atomicAdd(&s_cls[gpClass(gp)], 1)] = (uint16_t)gp;
+  // First sample of a fresh edge: no pair has a validated interval, so every pair is a candidate, and the reference stops at
+  // the FIRST colliding pair of the construction order.  When the pairs make more jobs than one round of threads, the first
+  // stage takes only the leading pairs that fill one round; the replay then either meets a collision among them (most
+  // random configurations of a cluttered scene collide: the other two thirds of the distances are never needed) or asks
+  // for the rest through the second-stage protocol below.
+  if (tid == 0) {
+    int lim = NP;
+    if (NBG > DT_THREADS) {
+      lim = 0;
+      while (lim < NP && T.bodypairs[lim].pair_end <= DT_THREADS) ++lim;
+      if (lim == 0) lim = NP;
+    }
+    s_firstLimit = lim;
+  }
   __syncthreads();
   for (;;) {
     if (tid == 0) {
@@ -347,7 +361,9 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
 
       // ---- D / E: narrow phase of the flagged pairs, then the replay; a second stage when the replay meets a
       //      covered pair that the reference evaluates after all ----
-      for (;;) {
+      const bool freshFirst = s_iters == 1 && !(PROG && A.resume.slots) && s_firstLimit < NP;  // (order = construction order)
+      for (int stage = 0;; ++stage) {
+        const int plim = (freshFirst && stage == 0) ? s_firstLimit : NP;  // body pairs (= positions) this stage evaluates
         // D1: this stage's jobs = the geometry pairs of the flagged body pairs, in the static cost order
         if (tid == 0) s_njobs = 0;
         __syncthreads();
@@ -357,7 +373,7 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
           bool want = false;
           if (i < NBG) {
             gp = sortedGp[i];
-            want = (state[bodyOf[gp]] & (ST_CAND | ST_DONE)) == ST_CAND;
+            want = (int)bodyOf[gp] < plim && (state[bodyOf[gp]] & (ST_CAND | ST_DONE)) == ST_CAND;
           }
           const unsigned m = __ballot_sync(0xffffffffu, want);
           int off = 0;
@@ -377,7 +393,7 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
         }
         __syncthreads();
         // D3: computeDistanceLowerBound per body pair (:175-198): geometry pairs in order, the first collision reports
-        for (int p = tid; p < NP; p += DT_THREADS) {
+        for (int p = tid; p < plim; p += DT_THREADS) {
           if ((state[p] & (ST_CAND | ST_DONE)) != ST_CAND) continue;
           const DevBodyPair& B = T.bodypairs[p];
           double dlb = INF;
