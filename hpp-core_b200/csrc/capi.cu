@@ -51,6 +51,7 @@ Workspace::~Workspace() {
   if (stream2) cudaStreamDestroy(stream2);
   if (stream3) cudaStreamDestroy(stream3);
   if (stream4) cudaStreamDestroy(stream4);
+  if (stream5) cudaStreamDestroy(stream5);
   for (cudaEvent_t e : evSlice) cudaEventDestroy(e);
   if (evFork) cudaEventDestroy(evFork);
   if (evJoin) cudaEventDestroy(evJoin);

@@ -143,7 +143,7 @@ struct Workspace {
   cudaStream_t stream = nullptr;
   bool own_stream = true;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  cudaStream_t stream2 = nullptr, stream3 = nullptr, stream4 = nullptr;  // H2D / D2H streams of the sliced host-pointer path (created on first use)
+  cudaStream_t stream2 = nullptr, stream3 = nullptr, stream4 = nullptr, stream5 = nullptr;  // H2D / D2H streams of the sliced host-pointer path (created on first use)
   std::vector<cudaEvent_t> evSlice;
   cudaEvent_t evFork = nullptr, evJoin = nullptr;
   ModelView view;

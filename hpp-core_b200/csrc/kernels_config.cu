@@ -761,7 +761,9 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
     HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, S.fn, K1_THREADS, S.smem));
     wave = (size_t)std::max(1, perSM) * (size_t)ws->num_sms * K1_THREADS;
   }
-  size_t maxWaves = 2, tailWaves = 2;  // measured: 4/2 705, 2/2 762, 2/0 766, 1/2 747, 8/2 713 M configurations/s (1 M UR5, pinned)
+  // measured (1 M UR5, pinned), one stream for configPassKernel: 4/2 705, 2/2 762, 2/0 766, 1/2 747, 8/2 713 M configurations/s;
+  // two alternating streams: 2/2 797, 1/2 845, 4/2 711
+  size_t maxWaves = 1, tailWaves = 2;
   if (const char* v = std::getenv("HPPB200_CFG_SLICE_WAVES")) maxWaves = std::max<size_t>(1, (size_t)std::atoll(v));
   if (const char* v = std::getenv("HPPB200_CFG_TAIL_WAVES")) tailWaves = (size_t)std::max(0ll, std::atoll(v));
   // Slices in whole waves: 1, 2, 4, ... (the kernels start after the first, small copy), and `tailWaves` single-wave slices
@@ -800,6 +802,7 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
     HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->stream3, cudaStreamNonBlocking));
     // (a high-priority stream for gjkJobsKernel was measured slower: 655 vs 697 M configurations/s end to end)
     HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->stream4, cudaStreamNonBlocking));
+    HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->stream5, cudaStreamNonBlocking));
     HPPB200_CUDA_CHECK(cudaEventCreateWithFlags(&ws->evJoin, cudaEventDisableTiming));
     HPPB200_CUDA_CHECK(cudaEventCreateWithFlags(&ws->evFork, cudaEventDisableTiming));
   }
@@ -810,6 +813,11 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
   }
   HPPB200_CUDA_CHECK(cudaEventRecord(ws->evFork, ws->stream));  // (the staging buffers may still be read by earlier work)
   HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream2, ws->evFork, 0));
+  // configPassKernel of consecutive slices on two alternating streams: the next slice's CTAs fill the SMs the last wave of
+  // the previous one leaves idle (HPPB200_CFG_K1_STREAMS=1: one stream)
+  bool twoK1 = true;
+  if (const char* v = std::getenv("HPPB200_CFG_K1_STREAMS")) twoK1 = std::atoi(v) >= 2;
+  if (twoK1) HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream5, ws->evFork, 0));
   unsigned long long* counters = ws->d_jobs.p;       // [ns]
   unsigned long long* queue = ws->d_jobs.p + ns;     // slice k at 2 * off + 4096 * k
   for (size_t k = 0; k < ns; ++k) {
@@ -817,8 +825,9 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
     cudaEvent_t evIn = ws->evSlice[3 * k], evDone = ws->evSlice[3 * k + 1], evPass = ws->evSlice[3 * k + 2];
     if (!zeroCopy) HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p + off * nq, h_q + off * nq, m * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream2));
     HPPB200_CUDA_CHECK(cudaEventRecord(evIn, ws->stream2));
-    HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream, evIn, 0));
-    launchTwoKernelsOn(ws, ws->stream, zeroCopy ? h_q + off * nq : ws->d_q.p + off * nq, m, flags, ws->d_valid.p + off, ws->d_pair.p + off,
+    cudaStream_t k1s = (twoK1 && (k & 1)) ? ws->stream5 : ws->stream;
+    HPPB200_CUDA_CHECK(cudaStreamWaitEvent(k1s, evIn, 0));
+    launchTwoKernelsOn(ws, k1s, zeroCopy ? h_q + off * nq : ws->d_q.p + off * nq, m, flags, ws->d_valid.p + off, ws->d_pair.p + off,
                        ws->d_reason.p + off, ws->d_scratch.p + slots * 12 * off, counters + k, queue + 2 * off + 4096 * k, 2 * m + 4096,
                        ws->stream4, evPass, zeroCopy);
     HPPB200_CUDA_CHECK(cudaEventRecord(evDone, ws->stream4));
