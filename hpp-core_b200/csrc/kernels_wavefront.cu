@@ -1107,12 +1107,23 @@ wfProgControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
 //    WD_KS intervals per slot.
 //  * the next parameter is known only after the scan, so the candidates of the next sample come from a second,
 //    emit-only scan in the same round (window = alpha x the half-width just validated).
+// out-of-line copies for the Dichotomy control kernel (119 KB of SASS with everything inline: 6.4 'no instruction' stalls per issue)
+static __device__ __noinline__ bool wdUnionNI(double2* v, size_t stride, int* cnt, int cap, double a, double b) {
+  int c = *cnt;
+  const bool ok = wdUnion(v, stride, c, cap, a, b);
+  *cnt = c;
+  return ok;
+}
+static __device__ __noinline__ bool wdContainsNI(const double2* v, size_t stride, int cnt, double a, double b) { return wdContains(v, stride, cnt, a, b); }
 constexpr int WD_K = 12;
 constexpr int WD_KS = 16;
 constexpr int WD_CH = 8;  // first intervals of this many positions are loaded ahead of their use
 
+#ifndef WF_DC_MINB
+#define WF_DC_MINB 5
+#endif
 template <int W>
-__global__ void __launch_bounds__(WF_CTHREADS)
+__global__ void __launch_bounds__(WF_CTHREADS, W == 1 ? WF_DC_MINB : 1)
 wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
   extern __shared__ __align__(16) unsigned char smem[];  // @region setup
   uint64_t* bar = (uint64_t*)smem;
@@ -1241,14 +1252,14 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
             stop = true;
             continue;
           }
-          if (!wdUnion(lst, E, cnt, WD_K, a, bb)) {  // validInterval_.insert (:90) needs a longer list: walker
+          if (!wdUnionNI(lst, E, &cnt, WD_K, a, bb)) {  // validInterval_.insert (:90) needs a longer list: walker
             ++overflows;
             finishEdge(false, A.overflow_reason, t, dichLast(), -1);
             stop = true;
             continue;
           }
           setCnt(p, cnt);
-          if (wdContains(lst, E, cnt, 0.0, L)) maskSet<W>(vmask, p, true);  // valid_ (:92-96)
+          if (wdContainsNI(lst, E, cnt, 0.0, L)) maskSet<W>(vmask, p, true);  // valid_ (:92-96)
           if (ihi > bb) smallest = p;  // validateIntervals: fold into the running intersection
           ilo = (ilo < a) ? a : ilo;
           ihi = (bb < ihi) ? bb : ihi;
@@ -1292,10 +1303,10 @@ wfDichControlKernel(ModelView mv, WFArgs A, DeviceStats* stats) {
       }
       // dichotomy.cc:96-109
       hp = A.alpha * (0.5 * (ihi - ilo));
-      if (!wdUnion(sub, E, subCnt, WD_KS, ilo, ihi)) {
+      if (!wdUnionNI(sub, E, &subCnt, WD_KS, ilo, ihi)) {
         ++overflows;
         finishEdge(false, A.overflow_reason, t, dichLast(), -1);
-      } else if (wdContains(sub, E, subCnt, 0.0, L)) {
+      } else if (wdContainsNI(sub, E, subCnt, 0.0, L)) {
         finishEdge(true, HPPB200_REASON_VALID, CUDART_NAN, reverse ? 0.0 : L, -1);
       } else {
         double t0, t1;  // middle of the first non-validated gap
