@@ -168,7 +168,11 @@ __device__ __forceinline__ bool gjkStep(GjkState& s, const DevShape& A, const De
     double best = CUDART_INF;
     bool any = false;
     tn = 0; nv = v;
-#pragma unroll
+#ifndef HPPB200_GJK_FACE_UNROLL
+#define HPPB200_GJK_FACE_UNROLL 1  // 1: one copy of the face code (4: four closestTriangle bodies inline, ~4x the SASS of the tetrahedron case)
+#endif
+    constexpr int kFaceUnroll = HPPB200_GJK_FACE_UNROLL;
+#pragma unroll kFaceUnroll
     for (int f = 0; f < 4; ++f) {
       V3 a, b, c, d;
       if (f == 0) { a = w0; b = w1; c = w2; d = w; }
