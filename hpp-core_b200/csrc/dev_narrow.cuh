@@ -42,7 +42,20 @@ __device__ __forceinline__ V3 supportLocal(const DevShape& s, const double* __re
       int best = 0;
       double bv = -CUDART_INF;
       const double* vp = verts + 3 * (size_t)s.vbegin;
-      for (int i = 0; i < s.vcount; ++i) {
+      // four independent dot chains per trip (one job is a dependent FP64 chain; the scan is its longest stretch on convex
+      // shapes), compared in vertex order: the first maximal vertex, as before
+      int i = 0;
+      for (; i + 4 <= s.vcount; i += 4) {
+        const double h0 = dot(mk(vp[3 * i], vp[3 * i + 1], vp[3 * i + 2]), d);
+        const double h1 = dot(mk(vp[3 * i + 3], vp[3 * i + 4], vp[3 * i + 5]), d);
+        const double h2 = dot(mk(vp[3 * i + 6], vp[3 * i + 7], vp[3 * i + 8]), d);
+        const double h3 = dot(mk(vp[3 * i + 9], vp[3 * i + 10], vp[3 * i + 11]), d);
+        if (h0 > bv) { bv = h0; best = i; }
+        if (h1 > bv) { bv = h1; best = i + 1; }
+        if (h2 > bv) { bv = h2; best = i + 2; }
+        if (h3 > bv) { bv = h3; best = i + 3; }
+      }
+      for (; i < s.vcount; ++i) {
         double h = dot(mk(vp[3 * i], vp[3 * i + 1], vp[3 * i + 2]), d);
         if (h > bv) { bv = h; best = i; }
       }

@@ -1,18 +1,24 @@
 #!/usr/bin/env python3
-"""One launch of the CTA-per-edge Dichotomy kernel on n random UR5 edges (for ncu)."""
+"""ncu target: one Dichotomy call on the 30-joint tree model (BASELINE configs[3] shape: local edges), all of it in edgeTailKernel.
+   python tools/tail_prof.py [n]"""
 import sys, os
+import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-os.environ["HPPB200_WF_MIN"] = "1000000000"
-os.environ["HPPB200_TAIL_MAX"] = "1000000000"
-import numpy as np
+import torch
 import __graft_entry__ as ge
 pkg = ge.load()
-name = sys.argv[1] if len(sys.argv) > 1 else "ur5_boxes8.json"
-n = int(sys.argv[2]) if len(sys.argv) > 2 else 4000
-desc = pkg.ModelDescription.load(name)
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 131072
+desc = pkg.ModelDescription.load("humanoid_obst16.json")
 ws = pkg.Workspace(pkg.Model(desc), 0)
-q1, q2 = pkg.uniform_configs(desc, n, seed=101), pkg.uniform_configs(desc, n, seed=102)
+q1 = pkg.uniform_configs(desc, n, seed=101)
+d = np.random.default_rng(5).normal(size=q1.shape)
+q2 = pkg.normalize_quaternions(desc, np.clip(q1 + 0.2 * d / np.linalg.norm(d, axis=1, keepdims=True), desc.q_lower, desc.q_upper))
 L = ws.straight_lengths(q1, q2)
-r = ws.validate_edges(2, 0.0, q1, q2, L)
-print("valid", r["valid"].mean())
+dev = torch.device("cuda", 0)
+a, b, l = (torch.from_numpy(x).to(dev) for x in (q1, q2, L))
+v = torch.empty(n, dtype=torch.uint8, device=dev); tf = torch.empty(n, dtype=torch.float64, device=dev); tl = torch.empty(n, dtype=torch.float64, device=dev)
+pr = torch.empty(n, dtype=torch.int32, device=dev); rs = torch.empty(n, dtype=torch.uint8, device=dev)
+for _ in range(2):
+    ws.validate_edges_ptr(2, 0.0, False, a.data_ptr(), b.data_ptr(), l.data_ptr(), n, v.data_ptr(), tf.data_ptr(), tl.data_ptr(), pr.data_ptr(), rs.data_ptr(), pkg.DEVICE_POINTERS)
+print("done", ws.stats()["last_kernel_ms"], float(v.float().mean()))
