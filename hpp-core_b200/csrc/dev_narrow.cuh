@@ -259,13 +259,18 @@ __device__ __forceinline__ double segmentSegmentDist2(V3 p1, V3 q1, V3 p2, V3 q2
     double c = dot(d1, r);
     if (e <= EPS) { t = 0; s = clamp01(-c / a); }
     else {
+      // the general case without branches: two divisions on every lane, operands by select (same expressions as the branchy
+      // form in the oracle; a warp's lanes used to split three ways at the second one)
       double b = dot(d1, d2);
       double denom = fma(a, e, -(b * b));
-      if (denom > 0) s = clamp01(fma(b, f, -(c * e)) / denom); else s = 0;
+      const double s0 = clamp01(fma(b, f, -(c * e)) / denom);
+      s = denom > 0 ? s0 : 0;
       double tnom = fma(b, s, f);
-      if (tnom < 0) { t = 0; s = clamp01(-c / a); }
-      else if (tnom > e) { t = 1; s = clamp01((b - c) / a); }
-      else t = tnom / e;
+      const bool lo = tnom < 0, hi = !lo && tnom > e;
+      const double num = lo ? -c : (hi ? b - c : tnom), den = (lo || hi) ? a : e;
+      const double q = num / den;
+      t = lo ? 0.0 : (hi ? 1.0 : q);
+      s = (lo || hi) ? clamp01(q) : s;
     }
   }
   V3 c1 = axpy(s, d1, p1), c2 = axpy(t, d2, p2);
