@@ -406,6 +406,26 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
           u = mk(O.P[2], O.P[5], O.P[8]);
         }
       };
+      // box-face separating axes: a lower bound of the distance of geometry a's core to the obstacle box b (true: culled)
+      auto boxFaceCull = [&](int p, bool ex) -> bool {
+        const DevPair pr = T.cpairs[p];
+        const DevShape& sa = *(const DevShape*)(pr.a >= 0 ? &T.geoms[pr.a].shape : &T.obstacles[-(pr.a + 1)].shape);
+        const DevObstacle& O = T.obstacles[-(pr.b + 1)];
+        V3 ca, ua;
+        core(pr.a, ex, ca, ua);
+        const double sl = (SHADOW && !ex) ? slack : 0.0;
+        const T3 TB = load12(O.P);
+        const double h = pr.bound == 1 ? sa.p[1] : 0.0;
+        const V3 e0 = rtmul(TB, axpy(-h, ua, ca) - TB.t), e1 = rtmul(TB, axpy(h, ua, ca) - TB.t);
+        const double sx = fmax(fmin(e0.x, e1.x) - O.shape.p[0], -fmax(e0.x, e1.x) - O.shape.p[0]);
+        const double sy = fmax(fmin(e0.y, e1.y) - O.shape.p[1], -fmax(e0.y, e1.y) - O.shape.p[1]);
+        const double sz = fmax(fmin(e0.z, e1.z) - O.shape.p[2], -fmax(e0.z, e1.z) - O.shape.p[2]);
+        const double ra = pr.a >= 0 ? T.geoms[pr.a].bound.br : T.obstacles[-(pr.a + 1)].bound.br;
+        return fmax(sx, fmax(sy, sz)) - ra - pr.margin > 1e-9 + sl;
+      };
+      const bool deferSat = mv.ncpairs <= 256;
+      unsigned long long surv = 0;
+      int nsurv = 0;
       int hit = -1;
       bool ex = exactAll;
       for (int p = 0; p < mv.ncpairs;) {
@@ -444,19 +464,20 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
         else { V3 dd = ca - cb; d2 = dot(dd, dd); }
         if (d2 > pr.cull2 + csl) { ++p; continue; }
         if (pr.b < 0 && sb.type == SH_BOX) {
-          // box-face separating axes: a lower bound of the distance to the obstacle box
-          const DevObstacle& O = T.obstacles[-(pr.b + 1)];
-          const T3 TB = load12(O.P);
-          const double h = pr.bound == 1 ? sa.p[1] : 0.0;
-          const V3 e0 = rtmul(TB, axpy(-h, ua, ca) - TB.t), e1 = rtmul(TB, axpy(h, ua, ca) - TB.t);
-          const double sx = fmax(fmin(e0.x, e1.x) - sb.p[0], -fmax(e0.x, e1.x) - sb.p[0]);
-          const double sy = fmax(fmin(e0.y, e1.y) - sb.p[1], -fmax(e0.y, e1.y) - sb.p[1]);
-          const double sz = fmax(fmin(e0.z, e1.z) - sb.p[2], -fmax(e0.z, e1.z) - sb.p[2]);
-          const double ra = pr.a >= 0 ? T.geoms[pr.a].bound.br : T.obstacles[-(pr.a + 1)].bound.br;
-          if (fmax(sx, fmax(sy, sz)) - ra - pr.margin > 1e-9 + sl) { ++p; continue; }
+          // The box-face bound runs for the few pairs that pass the first cull, at a different pair per lane: inline it
+          // executed at 1.6 of 32 lanes (8 % of the kernel's instructions).  The survivors are noted (up to 8 pair indices of
+          // 8 bits) and tested after the loop, every lane walking its own list in step.
+          if (deferSat && nsurv < 8) { surv |= (unsigned long long)p << (8 * nsurv); ++nsurv; ++p; continue; }
+          if (!boxFaceCull(p, ex)) pushJob(((unsigned long long)i << 32) | (unsigned)p, sjobs, scount, A);
+          ++p;
+          continue;
         }
         pushJob(((unsigned long long)i << 32) | (unsigned)p, sjobs, scount, A);
         ++p;
+      }
+      for (int k = 0; k < nsurv; ++k) {
+        const int p = (int)((surv >> (8 * k)) & 0xffull);
+        if (!boxFaceCull(p, exactAll)) pushJob(((unsigned long long)i << 32) | (unsigned)p, sjobs, scount, A);
       }
       A.valid[i] = hit < 0 ? 1 : 0;
       A.first[i] = (uint32_t)hit;
