@@ -252,10 +252,33 @@ def run_b200(args):
     bits_d = torch.empty((n + 31) // 32, dtype=torch.int32, device=dev)
     allbits_d = torch.empty(world * ((n + 31) // 32), dtype=torch.int32, device=dev)
 
+    # N > 1: the mask gather as ONE kernel over NVLink peer memory (hppb200_exchange_mask: pack + stores into every rank's
+    # buffer + epoch flags); checked against the NCCL form once, which stays the fallback (HPPB200_BENCH_PEER=0 forces it)
+    px = None
+    if world > 1 and os.environ.get("HPPB200_BENCH_PEER", "1") != "0":
+        try:
+            px = sh.PeerMaskExchange.create(local_rank, n)
+        except Exception as exc:  # (every rank takes the same branch only if create() itself agreed: it does, see sharding.py)
+            sys.stderr.write("[bench] peer exchange unavailable: %s\n" % exc)
+            px = None
+        if px is not None:
+            ws.validate_configs_ptr(q_dev.data_ptr(), n, valid_d.data_ptr(), first_d.data_ptr(), reason_d.data_ptr(), FLAGS_DEV)
+            ref_bits = sh.all_gather_mask_packed(valid_d, unpack=False, bits=bits_d, allbits=allbits_d)[1]
+            peer_bits = px.gather(valid_d)
+            same = torch.tensor([1 if (not px.timed_out()) and torch.equal(peer_bits, ref_bits) else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(same, op=dist.ReduceOp.MIN)
+            if int(same.item()) == 0:
+                sys.stderr.write("[bench] peer exchange differs from the NCCL all-gather: NCCL form kept\n")
+                px.close()
+                px = None
+
     def step_device():
         ws.validate_configs_ptr(q_dev.data_ptr(), n, valid_d.data_ptr(), first_d.data_ptr(), reason_d.data_ptr(), FLAGS_DEV)
         if world > 1:  # the path's only exchange: gather of the validity masks, bit-packed (1 bit per configuration)
-            sh.all_gather_mask_packed(valid_d, unpack=False, bits=bits_d, allbits=allbits_d)
+            if px is not None:
+                gathered["cfg_bits"] = px.gather(valid_d)
+            else:
+                gathered["cfg_bits"] = sh.all_gather_mask_packed(valid_d, unpack=False, bits=bits_d, allbits=allbits_d)[1]
 
     def step_e2e():
         ws.validate_configs_ptr(q_host.data_ptr(), n, valid_h.data_ptr(), first_h.data_ptr(), reason_h.data_ptr(), 0)
@@ -300,7 +323,8 @@ def run_b200(args):
     # identical results on both paths
     assert torch.equal(valid_h, valid_d.cpu()) and torch.equal(first_h, first_d.cpu())
     if world > 1:  # the gathered (packed) mask holds this rank's flags at its place
-        assert torch.equal(sh.unpack_mask(allbits_d, n, world)[rank * n:(rank + 1) * n], valid_d)
+        assert torch.equal(sh.unpack_mask(gathered["cfg_bits"], n, world)[rank * n:(rank + 1) * n], valid_d)
+        assert px is None or not px.timed_out(), "a peer exchange inside the timed region timed out" 
 
     # ---- N > 1: every rank validates its own shard of edges (Progressive), validity masks all-gathered ----
     edges_sharded = None
@@ -685,7 +709,9 @@ def run_b200(args):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "model": MODEL, "configs_per_gpu_per_step": n, "seed": SEED, "pairs": int(len(model.config_pairs()[0])),
                    "l2": "flushed between timed steps (256 MiB memset, untimed)",
-                   "collective": "all_gather of bit-packed validity masks (NCCL, 1 bit per configuration)" if world > 1 else "none"},
+                   "collective": ("none" if world == 1 else
+                                  "bit-packed validity masks stored into every rank's buffer over NVLink peer memory by one kernel (hppb200_exchange_mask), 1 bit per configuration"
+                                  if px is not None else "all_gather of bit-packed validity masks (NCCL, 1 bit per configuration)")},
         "e2e": {"value": e2e_value, "unit": "configs/s", "h2d_bytes_per_step": n * nq * 8, "d2h_bytes_per_step": n * 6,
                 "ms_per_step": e2e_ms / args.steps},
         "gpu_launches": int(launches),

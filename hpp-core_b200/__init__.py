@@ -56,6 +56,7 @@ ABI_SYMBOLS = [
     "hppb200_multi_validate_configs", "hppb200_multi_validate_edges",
     "hppb200_pack_mask", "hppb200_unpack_mask", "hppb200_knn_merge_shards",
     "hppb200_kprm_link_candidates", "hppb200_roadmap_merge_edges",
+    "hppb200_exchange_create", "hppb200_exchange_open_peers", "hppb200_exchange_mask", "hppb200_exchange_status", "hppb200_exchange_destroy",
     "hppb200_knn_create", "hppb200_knn_destroy", "hppb200_knn_append", "hppb200_knn_relabel", "hppb200_knn_set_labels", "hppb200_knn_size",
     "hppb200_knn_query", "hppb200_knn_within_ball", "hppb200_knn_tc_stats", "hppb200_knn_tc_filter_time", "hppb200_knn_latency_time", "hppb200_knn_tc_debug_tile",
 ]

@@ -151,3 +151,70 @@ def unpack_mask(allbits, n, world):
         _check(lib().hppb200_unpack_mask(C.c_void_p(stream), C.c_void_p(allbits.data_ptr() + 4 * r * words), C.c_size_t(n),
                                          C.c_void_p(out.data_ptr() + r * n)))
     return out
+
+
+class PeerMaskExchange:
+    """hppb200_exchange_*: the mask gather as ONE kernel over NVLink peer memory (bit-pack + stores into every rank's buffer +
+    epoch flags) instead of hppb200_pack_mask + an NCCL all-gather.  Ranks of one node; the IPC handles travel through
+    torch.distributed.  `create` returns None on every rank when any rank cannot set it up (the caller keeps the NCCL form)."""
+
+    class _Raw:
+        def __init__(self, ptr, nwords):
+            self.__cuda_array_interface__ = {"shape": (int(nwords),), "typestr": "<i4", "data": (int(ptr), False), "version": 2}
+
+    def __init__(self, handle, rank, world):
+        self.h, self.rank, self.world = handle, rank, world
+
+    @classmethod
+    def create(cls, device_index, max_units, group=None):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        from . import lib
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        dev = torch.device("cuda", device_index)
+        h = C.c_void_p()
+        mine = (C.c_ubyte * 64)()
+        ok = lib().hppb200_exchange_create(C.c_int(device_index), C.c_int(rank), C.c_int(world), C.c_size_t(max_units), C.byref(h), mine) == 0
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 0:
+            if ok:
+                lib().hppb200_exchange_destroy(h)
+            return None
+        hs = torch.empty(world * 64, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(hs, torch.tensor(list(mine), dtype=torch.uint8, device=dev), group=group)
+        blob = bytes(hs.cpu().numpy().tobytes())
+        ok = lib().hppb200_exchange_open_peers(h, C.c_char_p(blob)) == 0
+        flag = torch.tensor([1 if ok else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 0:
+            lib().hppb200_exchange_destroy(h)
+            return None
+        return cls(h, rank, world)
+
+    def gather(self, valid):
+        """valid: CUDA uint8 [n] (same n on every rank), on torch's current stream.  Returns an int32 tensor VIEW of
+        world * ceil(n / 32) words in the exchange buffer (valid until the second next call)."""
+        import ctypes as C
+        import torch
+        from . import lib, _check
+        n = valid.shape[0]
+        out = C.c_void_p()
+        stream = torch.cuda.current_stream(valid.device).cuda_stream
+        _check(lib().hppb200_exchange_mask(self.h, C.c_void_p(stream), C.c_void_p(valid.data_ptr()), C.c_size_t(n), C.byref(out)))
+        return torch.as_tensor(self._Raw(out.value, self.world * ((n + 31) // 32)), device=valid.device)
+
+    def timed_out(self):
+        """synchronises; True when a wait gave up (a peer never delivered)"""
+        import ctypes as C
+        from . import lib, _check
+        t = C.c_int(0)
+        _check(lib().hppb200_exchange_status(self.h, C.byref(t)))
+        return t.value != 0
+
+    def close(self):
+        from . import lib
+        if self.h:
+            lib().hppb200_exchange_destroy(self.h)
+            self.h = None

@@ -401,6 +401,26 @@ int hppb200_unpack_mask(void* cuda_stream, const uint32_t* bits, size_t n, uint8
 int hppb200_knn_merge_shards(void* cuda_stream, const double* dist, const int64_t* idx, int nshards,
                              size_t nqueries, int k, int64_t* out_idx, double* out_dist);
 
+/* ---- fused exchange step over NVLink peer memory (processes of one node) ----
+   The sharded form's only exchange is the gather of the validity masks (the per-unit results of ConfigValidations /
+   PathValidation::validate over disjoint index ranges).  hppb200_exchange_mask does it in ONE kernel: the
+   rank's mask is bit-packed and stored straight into every rank's gather buffer (cudaIpc-mapped peer memory), the last
+   CTA publishes an epoch flag on every rank, and a one-warp kernel on the same stream waits for all ranks' flags.  No
+   counterpart in the reference (hpp-core is single-process); it replaces hppb200_pack_mask + an NCCL all-gather.
+   create: allocates this rank's buffer for masks of up to max_units units and returns its 64-byte IPC handle; the caller
+   exchanges the handles of all ranks (any transport) and passes them, rank-major, to open_peers (which blocks until the
+   mappings exist: every rank must have called create first).  exchange_mask: collective, same n on every rank, asynchronous
+   on cuda_stream; *gathered points to world * ceil(n / 32) words in THIS rank's memory, rank r's words at r * ceil(n / 32),
+   valid until the second next call (two slots by call parity). */
+typedef struct hppb200_exchange hppb200_exchange;
+int hppb200_exchange_create(int device, int rank, int world, size_t max_units, hppb200_exchange** out, unsigned char* handle64);
+int hppb200_exchange_open_peers(hppb200_exchange* ex, const unsigned char* handles /* [world][64] */);
+int hppb200_exchange_mask(hppb200_exchange* ex, void* cuda_stream, const uint8_t* valid, size_t n, const uint32_t** gathered);
+/* Synchronises the device; *timed_out != 0 when a wait of an earlier hppb200_exchange_mask gave up after ~2 s (a peer never
+   delivered): the gathered words of that call are not complete. */
+int hppb200_exchange_status(hppb200_exchange* ex, int* timed_out);
+void hppb200_exchange_destroy(hppb200_exchange* ex);
+
 /* ---- batched planner front-end: host-side array passes (no device work) ---- */
 /* kPrmStar::linkNodes / connectNodeToClosestNeighbors (reference src/path-planner/k-prm-star.cc:134-193) over the neighbour
    lists of ALL nodes at once.  nbrs / dist [n][k]: the k nearest nodes of every node, nearest first (-1 padded), as

@@ -1066,3 +1066,34 @@ def test_spline_edges_parity(pkg, ob, name):
     wf = pkg.Workspace(pkg.Model(ff), 0)
     with pytest.raises(ValueError):
         wf.validate_spline_edges(1, 1e-3, np.zeros((1, ff.nq)), np.zeros((1, 4, ff.nq)), np.ones(1))
+
+
+def test_peer_mask_exchange_single_rank_matches_pack_mask(pkg, eng, ur5):
+    """hppb200_exchange_mask with world = 1 (the fused pack + peer-store + flag kernel writing into its own buffer): the gathered
+    words equal hppb200_pack_mask's on three calls in a row (both slot parities, ragged n); the world > 1 form is checked against
+    the NCCL all-gather by bench.py on every multi-GPU run."""
+    import ctypes as C
+    import torch
+    _, ws = eng
+    lib = pkg.lib()
+    dev = torch.device("cuda", 0)
+    h = C.c_void_p()
+    handle = (C.c_ubyte * 64)()
+    assert lib.hppb200_exchange_create(C.c_int(0), C.c_int(0), C.c_int(1), C.c_size_t(100000), C.byref(h), handle) == 0
+    assert lib.hppb200_exchange_open_peers(h, C.c_char_p(bytes(handle))) == 0
+    try:
+        for n, seed in ((100000, 1), (99999, 2), (77, 3)):
+            valid = (torch.rand(n, device=dev, generator=torch.Generator(device=dev).manual_seed(seed)) < 0.4).to(torch.uint8)
+            bits = torch.zeros((n + 31) // 32, dtype=torch.int32, device=dev)
+            stream = torch.cuda.current_stream().cuda_stream
+            assert lib.hppb200_pack_mask(C.c_void_p(stream), C.c_void_p(valid.data_ptr()), C.c_size_t(n), C.c_void_p(bits.data_ptr())) == 0
+            out = C.c_void_p()
+            assert lib.hppb200_exchange_mask(h, C.c_void_p(stream), C.c_void_p(valid.data_ptr()), C.c_size_t(n), C.byref(out)) == 0
+            torch.cuda.synchronize()
+            from hpp_core_b200 import sharding as sh
+            got = torch.as_tensor(sh.PeerMaskExchange._Raw(out.value, bits.numel()), device=dev)
+            assert torch.equal(got, bits), n
+        out = C.c_void_p()
+        assert lib.hppb200_exchange_mask(h, C.c_void_p(0), C.c_void_p(valid.data_ptr()), C.c_size_t(1 << 22), C.byref(out)) != 0  # beyond max_units
+    finally:
+        lib.hppb200_exchange_destroy(h)
