@@ -48,6 +48,7 @@ Workspace::~Workspace() {
   if (ev0) cudaEventDestroy(ev0);
   if (ev1) cudaEventDestroy(ev1);
   if (h_njobs) cudaFreeHost(h_njobs);
+  if (h_small) cudaFreeHost(h_small);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream3) cudaStreamDestroy(stream3);
   if (stream4) cudaStreamDestroy(stream4);
@@ -239,8 +240,28 @@ int hppb200_validate_configs(hppb200_workspace* wsp, const double* q, size_t n, 
       finishValidateConfigs(ws, q, n, flags, valid, first_pair, reason);
       return;
     }
-    (void)nq;
     if (n == 0) return;
+    static const size_t smallMax = [] { const char* v = std::getenv("HPPB200_SMALL_CALL_MAX"); return v ? (size_t)std::atoll(v) : (size_t)32; }();
+    if (n <= smallMax && n * nq * sizeof(double) + 16 * n + 64 <= SMALL_STAGE_BYTES / 2) {
+      // A planner's one-item call (ConfigValidation::validate(q)): one pinned block up, the CTA-cooperative kernel (pairs spread
+      // over the warps: a lone configuration does not wait for one thread to walk all of them), one block down, one synchronisation.
+      if (!ws->h_small) HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&ws->h_small, SMALL_STAGE_BYTES, cudaHostAllocDefault));
+      ws->d_small.reserve(SMALL_STAGE_BYTES);
+      const size_t inBytes = n * nq * sizeof(double);
+      const size_t oFirst = 0, oValid = n * sizeof(int32_t), oReason = oValid + n, outBytes = oReason + n;
+      const size_t outOff = SMALL_STAGE_BYTES / 2;
+      std::memcpy(ws->h_small, q, inBytes);
+      Timed tm(ws);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_small.p, ws->h_small, inBytes, cudaMemcpyHostToDevice, ws->stream));
+      unsigned char* dout = ws->d_small.p + outOff;
+      launchValidateConfigsSmall(ws, (const double*)ws->d_small.p, n, flags, dout + oValid, (int32_t*)(dout + oFirst), dout + oReason);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->h_small + outOff, dout, outBytes, cudaMemcpyDeviceToHost, ws->stream));
+      tm.stop();
+      std::memcpy(valid, ws->h_small + outOff + oValid, n);
+      if (first_pair) std::memcpy(first_pair, ws->h_small + outOff + oFirst, n * sizeof(int32_t));
+      if (reason) std::memcpy(reason, ws->h_small + outOff + oReason, n);
+      return;
+    }
     // slices on two streams: copies overlap the kernels (kernels_config.cu, launchValidateConfigsHost)
     HPPB200_CUDA_CHECK(cudaEventRecord(ws->ev0, ws->stream));
     launchValidateConfigsHost(ws, q, n, flags, valid, first_pair, reason);  // records ev1, returns synchronised
@@ -344,6 +365,19 @@ int hppb200_straight_lengths(hppb200_workspace* wsp, const double* q1, const dou
     HPPB200_CUDA_CHECK(cudaSetDevice(ws->device));
     const size_t nq = (size_t)ws->model->nq;
     if (flags & HPPB200_DEVICE_POINTERS) { launchStraightLengths(ws, q1, q2, n, L); HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream)); return; }
+    if (n && n <= 32 && (2 * nq + 1) * n * sizeof(double) <= SMALL_STAGE_BYTES / 2) {  // one-item call: one block up, one down (see hppb200_validate_edges)
+      if (!ws->h_small) HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&ws->h_small, SMALL_STAGE_BYTES, cudaHostAllocDefault));
+      ws->d_small.reserve(SMALL_STAGE_BYTES);
+      const size_t qBytes = n * nq * sizeof(double), outOff = SMALL_STAGE_BYTES / 2;
+      std::memcpy(ws->h_small, q1, qBytes);
+      std::memcpy(ws->h_small + qBytes, q2, qBytes);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_small.p, ws->h_small, 2 * qBytes, cudaMemcpyHostToDevice, ws->stream));
+      launchStraightLengths(ws, (const double*)ws->d_small.p, (const double*)(ws->d_small.p + qBytes), n, (double*)(ws->d_small.p + outOff));
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->h_small + outOff, ws->d_small.p + outOff, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
+      HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+      std::memcpy(L, ws->h_small + outOff, n * sizeof(double));
+      return;
+    }
     ws->d_q.reserve(n * nq);
     ws->d_q2.reserve(n * nq);
     ws->d_L.reserve(n);
@@ -397,6 +431,34 @@ int hppb200_validate_edges(hppb200_workspace* wsp, int method, double param, int
       Timed tm(ws);
       launchValidateEdges(ws, method, param, reverse, q1, q2, L, n, flags, valid, t_fail, t_last_valid, pair, reason);
       tm.stop();
+      return;
+    }
+    static const size_t smallMax = [] { const char* v = std::getenv("HPPB200_SMALL_CALL_MAX"); return v ? (size_t)std::atoll(v) : (size_t)32; }();
+    if (n && n <= smallMax && (2 * nq + 1) * n * sizeof(double) + 32 * n + 64 <= SMALL_STAGE_BYTES / 2) {
+      // A planner's one-item call (PathValidation::validate(path)): the two ends and the length in one pinned block and one H2D,
+      // the five outputs in one device block and one D2H.
+      if (!ws->h_small) HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&ws->h_small, SMALL_STAGE_BYTES, cudaHostAllocDefault));
+      ws->d_small.reserve(SMALL_STAGE_BYTES);
+      const size_t qBytes = n * nq * sizeof(double), inBytes = 2 * qBytes + n * sizeof(double);
+      const size_t oTf = 0, oTl = n * sizeof(double), oPair = 2 * n * sizeof(double), oValid = oPair + n * sizeof(int32_t), oReason = oValid + n,
+                   outBytes = oReason + n, outOff = SMALL_STAGE_BYTES / 2;
+      std::memcpy(ws->h_small, q1, qBytes);
+      std::memcpy(ws->h_small + qBytes, q2, qBytes);
+      std::memcpy(ws->h_small + 2 * qBytes, L, n * sizeof(double));
+      Timed tm(ws);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_small.p, ws->h_small, inBytes, cudaMemcpyHostToDevice, ws->stream));
+      unsigned char* din = ws->d_small.p;
+      unsigned char* dout = ws->d_small.p + outOff;
+      launchValidateEdges(ws, method, param, reverse, (const double*)din, (const double*)(din + qBytes), (const double*)(din + 2 * qBytes), n, flags,
+                          dout + oValid, (double*)(dout + oTf), (double*)(dout + oTl), (int32_t*)(dout + oPair), dout + oReason);
+      HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->h_small + outOff, dout, outBytes, cudaMemcpyDeviceToHost, ws->stream));
+      tm.stop();
+      const unsigned char* ho = ws->h_small + outOff;
+      std::memcpy(valid, ho + oValid, n);
+      if (t_fail) std::memcpy(t_fail, ho + oTf, n * sizeof(double));
+      if (t_last_valid) std::memcpy(t_last_valid, ho + oTl, n * sizeof(double));
+      if (pair) std::memcpy(pair, ho + oPair, n * sizeof(int32_t));
+      if (reason) std::memcpy(reason, ho + oReason, n);
       return;
     }
     ws->d_q.reserve(n * nq);

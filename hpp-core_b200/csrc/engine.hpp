@@ -134,6 +134,7 @@ struct DeviceBuffer {
   ~DeviceBuffer() { if (p) cudaFree(p); }
 };
 
+constexpr size_t SMALL_STAGE_BYTES = 64 * 1024;
 struct Workspace {
   Workspace(const Model* m, int device);
   ~Workspace();
@@ -175,6 +176,12 @@ struct Workspace {
   DeviceBuffer<double> d_ctfail, d_ctlast;
   DeviceBuffer<unsigned long long> d_jobs;
   unsigned long long last_jobs = 0;
+  // one-item / small host-pointer calls (a planner's single-item virtuals): inputs packed in ONE pinned block and one H2D, outputs
+  // in one device block and one D2H (capi.cu)
+  unsigned char* h_small = nullptr;       // pinned, SMALL_STAGE_BYTES
+  DeviceBuffer<unsigned char> d_small;
+  bool overflow_known = false;            // DeviceStats::overflow as of the end of the last edge call, when that call read it last
+  unsigned long long overflow_cached = 0;
   unsigned long long* h_njobs = nullptr;  // pinned: queue counter of the last configuration batch
   DeviceBuffer<unsigned char> d_state, d_tail, d_sort;
   bool wavefront_lpt = true;   // wavefront engines pull the edges longest first (kernels_sort.cu; HPPB200_WF_LPT=0: input order)
@@ -196,6 +203,7 @@ void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t 
 void noallocSetup(int device);  // resolves the static scratch array's device address (cudaGetSymbolAddress), once per device
 void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first,
                                   uint8_t* d_reason);
+void launchValidateConfigsSmall(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason);
 void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint32_t flags, uint8_t* h_valid, int32_t* h_first,
                                uint8_t* h_reason);
 void launchAllCollisions(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint32_t* d_mask, int32_t* d_count);

@@ -895,6 +895,10 @@ void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint3
   }
 }
 
+// Few configurations (one-item calls): the CTA-cooperative kernel, whose warps share out the pairs of a configuration.
+void launchValidateConfigsSmall(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason) {
+  launchConfigKernel(ws, d_q, n, flags, MODE_VALIDATE, d_valid, d_first, d_reason, nullptr);
+}
 void launchGeometryPlacements(Workspace* ws, const double* d_q, size_t n, double* d_oMg) {
   launchConfigKernel(ws, d_q, n, 0, MODE_PLACEMENTS, nullptr, nullptr, nullptr, d_oMg);
 }

@@ -669,10 +669,14 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   // body pair; Dichotomy keeps short lists.  An edge whose lists overflow the
   // fast-path capacity is re-run ON THE DEVICE with large lists (second pass); if even that
   // overflows it is reported as HPPB200_REASON_ITER_CAP, never silently accepted.
-  DeviceStats before, after;
-  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
   const size_t allSlots = ~size_t(0);
-  if (method == HPPB200_METHOD_DISCRETIZED) { launchEdgeWalker<HPPB200_METHOD_DISCRETIZED>(ws, A, 1, 1, allSlots); return; }
+  if (method == HPPB200_METHOD_DISCRETIZED) { launchEdgeWalker<HPPB200_METHOD_DISCRETIZED>(ws, A, 1, 1, allSlots); return; }  // (no lists, no overflow)
+  DeviceStats before{}, after;
+  // (only the overflow counter is compared; it changes in edge calls only, and every edge call ends by reading it: a one-item
+  //  call does not pay a copy and a wait for a number the host already has)
+  if (ws->overflow_known) before.overflow = ws->overflow_cached;
+  else HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
+  ws->overflow_known = false;
   // Progressive on models whose per-edge state fits in shared memory: the control/narrow-phase
   // engine of kernels_continuous.cu.  Anything else: the generic walker below.
   bool engineDone = false;
@@ -738,7 +742,7 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
   const unsigned long long nover = after.overflow - before.overflow;
   if (std::getenv("HPPB200_WF_TRACE")) std::fprintf(stderr, "[edges] %llu of %zu edges go to the large-list walker pass\n", nover, n);
-  if (nover == 0) return;
+  if (nover == 0) { ws->overflow_known = true; ws->overflow_cached = after.overflow; return; }
   // second pass: gather the overflowed edges and walk them with large interval lists
   ws->d_list.reserve(nover + 1);
   ws->d_count.reserve(1);
@@ -796,8 +800,12 @@ void launchValidateSplineEdges(Workspace* ws, int method, double param, int reve
   A.overflow_reason = REASON_OVERFLOW_INTERNAL;
   const size_t allSlots = ~size_t(0);
   if (method == HPPB200_METHOD_DISCRETIZED) { launchEdgeWalker<HPPB200_METHOD_DISCRETIZED, true>(ws, A, 1, 1, allSlots); return; }
-  DeviceStats before, after;
-  HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
+  DeviceStats before{}, after;
+  // (only the overflow counter is compared; it changes in edge calls only, and every edge call ends by reading it: a one-item
+  //  call does not pay a copy and a wait for a number the host already has)
+  if (ws->overflow_known) before.overflow = ws->overflow_cached;
+  else HPPB200_CUDA_CHECK(cudaMemcpyAsync(&before, ws->d_stats, sizeof(before), cudaMemcpyDeviceToHost, ws->stream));
+  ws->overflow_known = false;
   // (Progressive keeps one connected validated interval per body pair whatever the path: the next sample lies inside
   //  every pair's last interval.  Dichotomy: short lists, the edges that outgrow them are redone with long ones.)
   if (method == HPPB200_METHOD_PROGRESSIVE) launchEdgeWalker<HPPB200_METHOD_PROGRESSIVE, true>(ws, A, 1, 1, allSlots);

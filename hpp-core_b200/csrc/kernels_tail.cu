@@ -25,6 +25,9 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <map>
+#include <mutex>
+#include <tuple>
 
 #include "dev_intervals.cuh"
 
@@ -597,9 +600,22 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   }
   TailLayout Lo = tailLayout(mv, smemLists ? K : 0);
   if (Lo.total > 200u * 1024u) return false;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  // (attribute and occupancy are host calls of several microseconds each: asked once per (device, method, shared-memory size);
+  //  the one-item calls of a planner come through here)
   int perSM = 0;
-  HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, DT_THREADS, Lo.total));
+  {
+    static std::mutex mu;
+    static std::map<std::tuple<int, int, uint32_t>, int> cache;
+    std::lock_guard<std::mutex> lock(mu);
+    const auto key = std::make_tuple(ws->device, method, Lo.total);
+    auto it = cache.find(key);
+    if (it == cache.end()) {
+      HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, DT_THREADS, Lo.total));
+      it = cache.emplace(key, perSM).first;
+    }
+    perSM = it->second;
+  }
   if (perSM < 1) return false;
   // Many edges (a whole batch, not a handful of long ones): the kernel is latency-bound at 4 warps per CTA, so resident CTAs
   // are worth more than list capacity.  Take the shortest lists (>= 8 entries) that let one more CTA onto the SM; an edge
