@@ -11,6 +11,7 @@
 // Keys and distance arithmetic are those of the exact scan (kernels_knn.cu, dev_knn.cuh): same bits, same tie rule
 // (equal distances: the earlier node, basic.cc:66,106).
 #include <algorithm>
+#include <cstdlib>
 #include <climits>
 
 #include "dev_model.cuh"
@@ -150,9 +151,10 @@ void knnLatencyRun(hppb200_knn* nn, const double* h_query, int k, int32_t cc, lo
   for (int x = 0; x < nq; ++x) Q.q[x] = h_query[x];
   // grid: a few CTAs per SM (enough loads in flight for the HBM stream), never more than one warp trip pair per CTA wants
   const size_t perCta = (size_t)LAT_WARPS * 64;
-  const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((size_t)nn->num_sms * 4, (nn->n + perCta - 1) / perCta));
+  static const size_t ctasPerSm = [] { const char* v = std::getenv("HPPB200_KNN_LAT_CTAS"); return v ? (size_t)std::max(1, std::atoi(v)) : (size_t)2; }();  // measured per SM: 1: 35 us, 2: 28.5, 4: 30.5, 8: 38, 16: 49 us (k = 1; the last CTA merges grid x k keys)
+  const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((size_t)nn->num_sms * ctasPerSm, (nn->n + perCta - 1) / perCta));
   if (!nn->lat_ticket_zeroed) {  // sized for the largest grid once: the ticket counter must survive from call to call
-    nn->d_lat.reserve((size_t)nn->num_sms * 4 * 32 * sizeof(Key) + 256);
+    nn->d_lat.reserve((size_t)nn->num_sms * ctasPerSm * 32 * sizeof(Key) + 256);
     HPPB200_CUDA_CHECK(cudaMemsetAsync(nn->d_lat.p, 0, 256, nn->stream));
     nn->lat_ticket_zeroed = true;
   }
