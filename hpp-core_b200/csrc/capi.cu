@@ -36,6 +36,8 @@ Workspace::Workspace(const Model* m, int dev) : model(m), device(dev) {
   if (const char* v = std::getenv("HPPB200_TAIL_SMEM")) tail_smem = std::atoi(v) != 0;
   if (const char* v = std::getenv("HPPB200_TAIL_MAX")) tail_max = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_PROG_TAIL_MAX")) prog_tail_max = (size_t)std::atoll(v);
+  if (const char* v = std::getenv("HPPB200_FIRST_SAMPLE_SCREEN")) first_sample_screen = std::atoi(v) != 0;
+  if (const char* v = std::getenv("HPPB200_FS_MIN")) first_sample_min = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_WF_SLOTS")) wavefront_slots = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_WF_LPT")) wavefront_lpt = std::atoi(v) != 0;
   if (const char* v = std::getenv("HPPB200_ENGINE_ALPHA")) engine_alpha = std::atof(v);
@@ -49,6 +51,7 @@ Workspace::~Workspace() {
   if (ev1) cudaEventDestroy(ev1);
   if (h_njobs) cudaFreeHost(h_njobs);
   if (h_small) cudaFreeHost(h_small);
+  if (h_fs) cudaFreeHost(h_fs);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream3) cudaStreamDestroy(stream3);
   if (stream4) cudaStreamDestroy(stream4);

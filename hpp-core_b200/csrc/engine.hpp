@@ -176,6 +176,16 @@ struct Workspace {
   DeviceBuffer<double> d_ctfail, d_ctlast;
   DeviceBuffer<unsigned long long> d_jobs;
   unsigned long long last_jobs = 0;
+  // first-sample screen of the edge path (kernels_edges.cu::launchValidateEdges)
+  bool first_sample_screen = true;     // HPPB200_FIRST_SAMPLE_SCREEN=0 switches it off
+  size_t first_sample_min = 2048;      // smallest batch that is screened (HPPB200_FS_MIN)
+  DeviceBuffer<double> d_fs_q, d_fs_q1, d_fs_q2, d_fs_L, d_fs_tfail, d_fs_tlast;
+  DeviceBuffer<uint8_t> d_fs_valid, d_fs_reason, d_fs_ovalid, d_fs_oreason;
+  DeviceBuffer<int32_t> d_fs_first, d_fs_opair;
+  DeviceBuffer<uint32_t> d_fs_list;
+  DeviceBuffer<unsigned long long> d_fs_cnt;
+  DeviceBuffer<unsigned char> d_fs_tmp;
+  unsigned long long* h_fs = nullptr;  // pinned: survivor count + the chunks' queue counters
   // one-item / small host-pointer calls (a planner's single-item virtuals): inputs packed in ONE pinned block and one H2D, outputs
   // in one device block and one D2H (capi.cu)
   unsigned char* h_small = nullptr;       // pinned, SMALL_STAGE_BYTES
@@ -203,6 +213,10 @@ void launchValidateConfigs(Workspace* ws, const double* d_q, size_t n, uint32_t 
 void noallocSetup(int device);  // resolves the static scratch array's device address (cudaGetSymbolAddress), once per device
 void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first,
                                   uint8_t* d_reason);
+size_t firstSampleChunk();
+size_t firstSampleQueueCap(size_t n);
+void launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
+                             unsigned long long* d_njobs);
 void launchValidateConfigsSmall(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason);
 void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint32_t flags, uint8_t* h_valid, int32_t* h_first,
                                uint8_t* h_reason);

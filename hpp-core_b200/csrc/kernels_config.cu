@@ -550,23 +550,28 @@ struct ConfigPassSetup {
   size_t smem;
   ConfigPassFn fn;
 };
-ConfigPassSetup configPassSetup(Workspace* ws, bool hostq = false) {
+// firstSample: the pair table is the continuous validation's (the body pairs' geometry pairs in body-pair order,
+// SolidSolidCollision's m.pairs flattened), staged with the bounds behind it; the configuration pair table stays out.
+ConfigPassSetup configPassSetup(Workspace* ws, bool hostq = false, bool firstSample = false) {
   const ModelView& mv = ws->view;
   const Model* m = ws->model;
   ConfigPassSetup S{};
-  const uint32_t gap = mv.off_lower - mv.off_bodypairs;
+  const uint32_t tail0 = firstSample ? mv.off_bgpairs : mv.off_lower;
+  const uint32_t tail1 = firstSample ? mv.off_cpairs : mv.blob_bytes;
+  const uint32_t gap = tail0 - mv.off_bodypairs;
   S.cv = mv;
   S.cv.off_bodypairs = S.cv.off_bgpairs = S.cv.off_coefs = S.cv.off_rcoefs = 0;  // (not staged, not used by the kernel)
   S.cv.off_lower -= gap; S.cv.off_upper -= gap; S.cv.off_weights -= gap; S.cv.off_cpairs -= gap;
-  S.cv.blob_bytes = mv.blob_bytes - gap;
+  if (firstSample) { S.cv.off_cpairs = mv.off_bgpairs - gap; S.cv.ncpairs = mv.nbgpairs; }
+  S.cv.blob_bytes = mv.off_bodypairs + (tail1 - tail0);
   S.head = mv.off_bodypairs;
-  S.tailOff = mv.off_lower;
-  S.tailBytes = mv.blob_bytes - mv.off_lower;
+  S.tailOff = tail0;
+  S.tailBytes = tail1 - tail0;
   for (const DevGeom& G : m->geoms)
     if (G.shape.type == HPPB200_SHAPE_CAPSULE) S.hmax = std::max(S.hmax, G.shape.p[1]);
-  const DevPair* cp = (const DevPair*)(m->blob.data() + mv.off_cpairs);
+  const DevPair* cp = (const DevPair*)(m->blob.data() + (firstSample ? mv.off_bgpairs : mv.off_cpairs));
   double c2 = 0;
-  for (int p = 0; p < mv.ncpairs; ++p) c2 = std::max(c2, cp[p].cull2);
+  for (int p = 0; p < S.cv.ncpairs; ++p) c2 = std::max(c2, cp[p].cull2);
   S.reachMax = std::sqrt(c2) * (1.0 + 1e-12);
   bool shadow = true;
   if (const char* v = std::getenv("HPPB200_CFG_SHADOW")) { shadow = std::atoi(v) != 0; S.forceExact = std::atoi(v) == 2; }
@@ -617,6 +622,47 @@ static void launchTwoKernelsOn(Workspace* ws, cudaStream_t stream, const double*
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 2;
   ws->stats.configs += n;
+}
+
+// First-sample screen of the edge path (kernels_edges.cu::launchValidateEdges): the configurations q(t0) of a batch of
+// edges against the CONTINUOUS validation's pair table: first[i] = index (into the body pairs' geometry pairs, reference
+// order) of the first colliding pair, which is what BodyPairCollision::computeDistanceLowerBound reports for the first
+// sample of an edge (body-pair-collision.cc:175-198: same predicate, same order, nothing validated yet).  In chunks, so
+// that the placement scratch stays bounded.  d_njobs [chunks] receives the queue counter of every chunk; the caller
+// compares them with firstSampleQueueCap(min(n, chunk)) after synchronising: an overflowed queue voids the screen.
+size_t firstSampleChunk() { return 262144; }
+size_t firstSampleQueueCap(size_t n) { return 16 * n + 4096; }
+void launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
+                             unsigned long long* d_njobs /* [chunks] */) {
+  const bool tree = modelIsTree(ws->model);
+  const ModelView& mv = ws->view;
+  ModelView mv2 = mv;
+  mv2.off_cpairs = mv.off_bgpairs;
+  mv2.ncpairs = mv.nbgpairs;
+  const ConfigPassSetup S = configPassSetup(ws, false, true);
+  const size_t chunk = std::min(n, firstSampleChunk());
+  const size_t slots = (size_t)mv.ngeoms + (tree ? mv.njoints : 0);
+  ws->d_scratch.reserve(slots * 12 * chunk);
+  const size_t cap = firstSampleQueueCap(chunk);
+  ws->d_jobs.reserve(cap + 1);
+  const size_t smem2 = 16 + mv.blob_bytes;
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  const size_t nq = (size_t)ws->model->nq;
+  HPPB200_CUDA_CHECK(cudaMemsetAsync(d_njobs, 0, ((n + chunk - 1) / chunk) * sizeof(unsigned long long), ws->stream));
+  size_t c = 0;
+  for (size_t off = 0; off < n; off += chunk, ++c) {
+    const size_t len = std::min(chunk, n - off);
+    ValidateArgs A{};
+    A.q = d_q + off * nq; A.n = len; A.flags = 0; A.valid = d_valid + off; A.first = (uint32_t*)(d_first + off); A.reason = d_reason + off;
+    A.oMg = ws->d_scratch.p;
+    A.njobs = d_njobs + c;
+    A.jobs = ws->d_jobs.p + 1;
+    A.jobs_cap = cap;
+    launchConfigPass(S, ws->stream, A, ws->d_stats);
+    gjkJobsKernel<<<(unsigned)((size_t)ws->num_sms * K2_GRID_PER_SM), K2_THREADS, smem2, ws->stream>>>(mv2, A, ws->d_stats);
+    HPPB200_CUDA_CHECK(cudaGetLastError());
+    ws->stats.kernel_launches += 2;
+  }
 }
 
 // Jobs that did not fit the queue (pathological scenes): detected on the host, which re-runs the

@@ -649,7 +649,7 @@ static void launchEdgeWalker(Workspace* ws, const EdgeArgs& A0, int K, int KS, s
   ws->stats.kernel_launches += 1;
 }
 
-void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1, const double* d_q2,
+void launchValidateEdgesCore(Workspace* ws, int method, double param, int reverse, const double* d_q1, const double* d_q2,
                          const double* d_L, size_t n, uint32_t flags, uint8_t* d_valid, double* d_tfail, double* d_tlast,
                          int32_t* d_pair, uint8_t* d_reason) {
   if (n == 0) return;

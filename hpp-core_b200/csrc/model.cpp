@@ -434,9 +434,11 @@ void Model::buildBlob() {
   view.off_geoms = append(geoms.data(), geoms.size() * sizeof(DevGeom));
   view.off_obstacles = append(obstacles.data(), obstacles.size() * sizeof(DevObstacle));
   view.off_bodypairs = append(bps.data(), bps.size() * sizeof(DevBodyPair));
-  view.off_bgpairs = append(bg.data(), bg.size() * sizeof(DevPair));
   view.off_coefs = append(cf.data(), cf.size() * sizeof(DevCoef));
   view.off_rcoefs = append(rcf.data(), rcf.size() * sizeof(DevCoef));
+  // (the body pairs' geometry pairs sit right in front of the bounds: the first-sample screen of the edge path stages
+  //  [0, off_bodypairs) + [off_bgpairs, off_cpairs) and reads them as ITS pair table, kernels_config.cu::configPassSetup)
+  view.off_bgpairs = append(bg.data(), bg.size() * sizeof(DevPair));
   view.off_lower = append(lower.data(), lower.size() * sizeof(double));
   view.off_upper = append(upper.data(), upper.size() * sizeof(double));
   view.off_weights = append(weights.data(), weights.size() * sizeof(double));

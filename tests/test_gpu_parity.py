@@ -563,6 +563,44 @@ def test_humanoid_tree_convex_parity(pkg, ob, monkeypatch, name):
             assert 0.02 < r["valid"].mean() < 0.98
 
 
+@pytest.mark.parametrize("name", ["ur5_boxes8.json", "humanoid_obst16.json", "humanoid_ff_obst6.json"])
+def test_first_sample_screen_same_results(pkg, ob, monkeypatch, name):
+    """First-sample screen of the edge path (kernels_screen.cu): q(t0) of every edge through the configuration kernels on
+    the continuous pair table, the edges that start in collision finished there, the rest gathered for the edge engines.
+    Same results as the unscreened engines and as the oracle: random edges (most start in collision on the humanoid),
+    edges that start at VALID configurations, zero-length edges, forward and reverse, a batch that is screened away
+    entirely and one nothing is removed from."""
+    desc = pkg.ModelDescription.load(name)
+    o = ob.Oracle(desc)
+    monkeypatch.setenv("HPPB200_FS_MIN", "1")
+    ws_on = pkg.Workspace(pkg.Model(desc), 0)
+    monkeypatch.setenv("HPPB200_FIRST_SAMPLE_SCREEN", "0")
+    ws_off = pkg.Workspace(pkg.Model(desc), 0)
+    a1, a2 = _local_edges(pkg, desc, 2500, 301, 0.4)
+    b1, b2, _ = _edges(pkg, desc, o, 1500, 302)
+    z = pkg.uniform_configs(desc, 64, seed=303)
+    q1, q2 = np.concatenate([a1, b1, z]), np.concatenate([a2, b2, z])
+    L = o.straight_lengths(q1, q2)
+    ok1 = o.validate_configs(q1)[0].astype(bool)
+    ok2 = o.validate_configs(q2)[0].astype(bool)
+    assert 0.02 < ok1.mean() < 0.98
+    subsets = {"all": np.arange(len(q1)), "valid start": np.flatnonzero(ok1 & ok2), "colliding start": np.flatnonzero(~ok1 & ~ok2)}
+    for method, param in ((1, 1e-3), (2, 0.0)):
+        for rev in (False, True):
+            for label, idx in subsets.items():
+                if len(idx) == 0:
+                    continue
+                r = ws_on.validate_edges(method, param, q1[idx], q2[idx], L[idx], reverse=rev)
+                u = ws_off.validate_edges(method, param, q1[idx], q2[idx], L[idx], reverse=rev)
+                e = o.validate_edges(method, param, q1[idx], q2[idx], L[idx], reverse=rev)
+                for k in ("valid", "reason", "pair", "t_last_valid"):
+                    assert np.array_equal(r[k], e[k]), (name, method, rev, label, k)
+                    assert np.array_equal(r[k], u[k]), (name, method, rev, label, k)
+                assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+                if label == "colliding start":
+                    assert not r["valid"].any()
+
+
 @pytest.mark.parametrize("path", ["cta", "walker"])
 @pytest.mark.parametrize("reverse", [False, True])
 def test_dichotomy_cta_per_edge_parity(pkg, eng, ur5, ur5_oracle, golden_configs, monkeypatch, path, reverse):
@@ -590,8 +628,9 @@ def test_dichotomy_cta_per_edge_parity(pkg, eng, ur5, ur5_oracle, golden_configs
         assert np.array_equal(r[k], e[k]), (path, reverse, k)
     assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
     assert s1["iter_cap_hits"] == s0["iter_cap_hits"]
-    if path == "cta":  # one launch for the batch (+ at most the second pass for lists beyond 64 entries)
-        assert s1["kernel_launches"] - s0["kernel_launches"] <= 3
+    if path == "cta":  # one launch for the batch (+ at most the second pass for lists beyond 64 entries), behind the
+        # first-sample screen (kernels_screen.cu: start configurations, 2 configuration kernels, 2 of the select, finish, gather, scatter)
+        assert s1["kernel_launches"] - s0["kernel_launches"] <= 3 + 8
     ws.set_max_iterations(7)
     r = ws.validate_edges(2, 0.0, q1[:2000], q2[:2000], L[:2000], reverse=reverse)
     e = o.validate_edges(2, 0.0, q1[:2000], q2[:2000], L[:2000], reverse=reverse, max_iter=7)

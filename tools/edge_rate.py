@@ -16,6 +16,10 @@ desc = pkg.ModelDescription.load(name)
 ws = pkg.Workspace(pkg.Model(desc), 0)
 o = ob.Oracle(desc)
 q1 = pkg.uniform_configs(desc, n, seed=101)
+if os.environ.get("EDGE_RATE_VALID_START"):  # edges that start at VALID configurations (what a planner extends from)
+    pool = pkg.uniform_configs(desc, 20 * n, seed=103)
+    ok = np.flatnonzero(ws.validate_configs(pool)[0])
+    q1 = np.ascontiguousarray(pool[ok[np.arange(n) % len(ok)]])
 if step > 0:
     d = np.random.default_rng(5).normal(size=q1.shape)
     q2 = pkg.normalize_quaternions(desc, np.clip(q1 + step * d / np.linalg.norm(d, axis=1, keepdims=True), desc.q_lower, desc.q_upper))
