@@ -689,7 +689,10 @@ void launchValidateEdgesCore(Workspace* ws, int method, double param, int revers
     engineDone = launchWavefront(ws, method, param, reverse, d_q1, d_q2, d_L, n, d_valid, d_tfail, d_tlast, d_pair,
                                             d_reason, REASON_OVERFLOW_INTERNAL);
   // Progressive, small batches: one CTA per edge (kernels_tail.cu), the latency of a sample instead of the CTA engine's ticks
-  if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_tail && n <= ws->prog_tail_max) {
+  // (models with many body pairs: the CTA-per-edge kernel also wins on mid-sized batches, e.g. what the first-sample screen leaves of
+  //  BASELINE configs[3]: 87 k edges of the 273-pair humanoid 59.9 ms against 64.2 ms through the CTA engine; 1 M edges 169 vs 163 ms)
+  const size_t progTailMax = ws->view.nbodypairs > 128 ? std::max<size_t>(ws->prog_tail_max, ws->prog_tail_max ? 131072 : 0) : ws->prog_tail_max;
+  if (!engineDone && method == HPPB200_METHOD_PROGRESSIVE && ws->use_tail && n <= progTailMax) {
     const int k = std::min(64, (int)(65536 / (16 * std::max(1, (int)ws->view.nbodypairs))));
     if (k >= 8)
       engineDone = launchEdgeTail(ws, method, param, reverse, d_q1, d_q2, d_L, nullptr, n, d_valid, d_tfail, d_tlast, d_pair, d_reason,

@@ -20,6 +20,7 @@
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 
@@ -160,8 +161,15 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   fsGatherKernel<<<(unsigned)((ns * (size_t)nq + 255) / 256), 256, 0, ws->stream>>>(ws->d_fs_list.p, ns, nq, d_q1, d_q2, d_L, ws->d_fs_q1.p,
                                                                                    ws->d_fs_q2.p, ws->d_fs_L.p);
   HPPB200_CUDA_CHECK(cudaGetLastError());
+  std::chrono::steady_clock::time_point c0;
+  if (trace) { cudaStreamSynchronize(ws->stream); c0 = std::chrono::steady_clock::now(); }
   launchValidateEdgesCore(ws, method, param, reverse, ws->d_fs_q1.p, ws->d_fs_q2.p, ws->d_fs_L.p, ns, flags, ws->d_fs_ovalid.p,
                           ws->d_fs_tfail.p, ws->d_fs_tlast.p, ws->d_fs_opair.p, ws->d_fs_oreason.p);
+  if (trace) {
+    cudaStreamSynchronize(ws->stream);
+    std::fprintf(stderr, "[edges] engines on the %zu screened edges: %.3f ms\n", ns,
+                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - c0).count());
+  }
   fsScatterKernel<<<(unsigned)((ns + 255) / 256), 256, 0, ws->stream>>>(ws->d_fs_list.p, ns, ws->d_fs_ovalid.p, ws->d_fs_tfail.p, ws->d_fs_tlast.p,
                                                                        ws->d_fs_opair.p, ws->d_fs_oreason.p, d_valid, d_tfail, d_tlast, d_pair,
                                                                        d_reason);

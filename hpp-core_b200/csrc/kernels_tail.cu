@@ -57,6 +57,7 @@ struct TailArgs {
   unsigned long long* counter;
   double2* lists;  // [grid][nbodypairs][K] in global memory, or null: the lists live in shared memory
   int K;           // validated intervals per body pair
+  double2* retry_lists;  // lists in shared memory with K < DT_K: [grid][nbodypairs][DT_K] in global memory for the edges that outgrow them
   unsigned long long* clk;  // optional [8]: cycles of thread 0 per phase (HPPB200_WF_TRACE)
   TailResume resume;        // Progressive: continue the edges of these wavefront slots (slots == null: start edges afresh)
 };
@@ -137,13 +138,15 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
   __shared__ double s_t, s_ilo, s_ihi, s_last;
   __shared__ int s_run, s_pos, s_smallest, s_subCnt, s_overflow, s_has, s_stop, s_depth, s_finished;
   __shared__ uint32_t s_edge, s_iters, s_slot;
+  __shared__ int s_redo;  // the current edge outgrew the shared-memory lists: the CTA validates it again with DT_K entries per pair in global memory
 
   const int tid = threadIdx.x;
   const int NP = mv.nbodypairs, NJ = mv.njoints, NG = mv.ngeoms;
   const double INF = CUDART_INF;
   const bool reverse = A.reverse != 0;
-  const int K = A.K;
-  double2* lists = A.lists ? A.lists + (size_t)blockIdx.x * NP * K : (double2*)(smem + Lo.off_lists);
+  int K = A.K;
+  double2* const baseLists = A.lists ? A.lists + (size_t)blockIdx.x * NP * A.K : (double2*)(smem + Lo.off_lists);
+  double2* lists = baseLists;
   double2* sub = (double2*)(smem + Lo.off_sub);
   __shared__ long long s_ck[8];
   long long c0 = 0;
@@ -201,19 +204,32 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
       if (lim == 0) lim = NP;
     }
     s_firstLimit = lim;
+    s_redo = 0;
   }
   __syncthreads();
   for (;;) {
     if (tid == 0) {
-      const unsigned long long i = atomicAdd(A.counter, 1ull);
-      s_has = i < A.n ? 1 : 0;
-      if (s_has) {
-        if (A.resume.slots) { s_slot = A.resume.slots[i]; s_edge = A.resume.st_edge[s_slot]; }
-        else s_edge = A.edge_list ? A.edge_list[i] : (uint32_t)i;
+      if (s_redo) s_has = 1;  // the same edge (and slot) once more, from its start
+      else {
+        const unsigned long long i = atomicAdd(A.counter, 1ull);
+        s_has = i < A.n ? 1 : 0;
+        if (s_has) {
+          if (A.resume.slots) { s_slot = A.resume.slots[i]; s_edge = A.resume.st_edge[s_slot]; }
+          else s_edge = A.edge_list ? A.edge_list[i] : (uint32_t)i;
+        }
       }
     }
     __syncthreads();
     if (!s_has) break;
+    {
+      // In-kernel second level: an edge that outgrows the K-entry lists in shared memory (K is cut to 8 on whole batches for a
+      // third resident CTA) is validated again at once by the CTA that found out, with DT_K entries per pair in global memory.
+      // (A second LAUNCH for those edges, 131 in a million on BASELINE configs[3], waited for the whole batch and then ran the
+      // serial chain of the longest of them alone: 23 ms behind 53 ms.)  s_redo is cleared behind the next barriers.
+      const bool redo = s_redo != 0;
+      K = redo ? DT_K : A.K;
+      lists = redo ? A.retry_lists + (size_t)blockIdx.x * NP * DT_K : baseLists;
+    }
     const uint32_t edge = s_edge;
     const double L = A.L[edge];
     const double* q1 = A.q1 + (size_t)edge * mv.nq;
@@ -262,6 +278,7 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
       s_run = RUN_SAMPLE;
       s_last = t;                                            // progressive.cc:93-100
       s_finished = (reverse ? t <= 0.0 : t >= L) ? 1 : 0;  // a zero-length path: one configuration to validate
+      s_redo = 0;
     }
     if (PROG && A.resume.slots) {
       // continue an edge of the wavefront engine (kernels_wavefront.cu) at a sample boundary: order, one validated
@@ -533,8 +550,11 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
           if (!PROG) over = !wdUnion(sub, 1, sc, DT_KS, ilo, ihi);  // dichotomy.cc:96-109
         }
         if (over) {
-          if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
-          finishEdge(false, A.overflow_reason, t, dichLast(), -1);
+          if (s_overflow != 0 && A.retry_lists && K != DT_K) s_redo = 1;  // (a pair list, not the valid subset)
+          else {
+            if (A.overflow_reason == HPPB200_REASON_ITER_CAP) ++caps; else ++overflows;
+            finishEdge(false, A.overflow_reason, t, dichLast(), -1);
+          }
           s_run = RUN_FINISHED;
         } else if (PROG) {  // progressive.cc:104-117
           double tn = reverse ? ilo : ihi;
@@ -597,6 +617,7 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   if (smemLists) {
     K = std::min<int>(DT_K, (int)(DT_SMEM_LISTS / (16u * (uint32_t)mv.nbodypairs)));
     if (K < 8) return false;
+    if (const char* v = std::getenv("HPPB200_TAIL_K")) K = std::max(2, std::min(K, std::atoi(v)));  // (tests: short lists, so that edges outgrow them)
   }
   TailLayout Lo = tailLayout(mv, smemLists ? K : 0);
   if (Lo.total > 200u * 1024u) return false;
@@ -631,7 +652,8 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
     }
   }
   const size_t grid = std::min<size_t>(n, (size_t)ws->num_sms * (size_t)perSM);
-  const size_t listBytes = smemLists ? 0 : grid * (size_t)mv.nbodypairs * DT_K * sizeof(double2);
+  const bool retry = smemLists && K < DT_K;
+  const size_t listBytes = smemLists && !retry ? 0 : grid * (size_t)mv.nbodypairs * DT_K * sizeof(double2);
   ws->d_tail.reserve(listBytes + 128);
   const bool trace = std::getenv("HPPB200_WF_TRACE") != nullptr;
   TailArgs A{};
@@ -639,18 +661,26 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   A.reverse = reverse; A.tol = tol; A.max_iter = ws->max_iterations; A.overflow_reason = overflow_reason;
   A.valid = d_valid; A.t_fail = d_tfail; A.t_last = d_tlast; A.pair = d_pair; A.reason = d_reason;
   A.lists = smemLists ? nullptr : (double2*)ws->d_tail.p;
+  A.retry_lists = retry ? (double2*)ws->d_tail.p : nullptr;
   A.K = K;
   if (resume) A.resume = *resume;
   A.counter = (unsigned long long*)(ws->d_tail.p + listBytes);
   A.clk = trace ? A.counter + 1 : nullptr;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.counter, 0, 9 * sizeof(unsigned long long), ws->stream));
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (trace) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, ws->stream); }
   kern<<<(unsigned)grid, DT_THREADS, Lo.total, ws->stream>>>(mv, A, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 1;
   if (trace) {
+    cudaEventRecord(e1, ws->stream);
     unsigned long long ck[8];
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(ck, A.clk, sizeof(ck), cudaMemcpyDeviceToHost, ws->stream));
     HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
+    float kms = 0;
+    cudaEventElapsedTime(&kms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    std::fprintf(stderr, "[tail] kernel %.3f ms\n", kms);
     std::fprintf(stderr, "[tail] n=%zu grid=%zu (%d per SM) K=%d %s smem=%u B; thread-0 Mcycles: A %.2f B %.2f C %.2f narrow %.2f replay %.2f insert %.2f next %.2f; second stages %llu\n",
                  n, grid, perSM, K, smemLists ? "shared" : "global", Lo.total, ck[0] * 1e-6, ck[1] * 1e-6, ck[2] * 1e-6, ck[3] * 1e-6, ck[4] * 1e-6,
                  ck[5] * 1e-6, ck[6] * 1e-6, ck[7]);

@@ -640,6 +640,34 @@ def test_dichotomy_cta_per_edge_parity(pkg, eng, ur5, ur5_oracle, golden_configs
     assert (r["reason"] == 3).any()
 
 
+@pytest.mark.parametrize("reverse", [False, True])
+def test_cta_per_edge_lists_outgrown_in_kernel_retry(pkg, eng, ur5, ur5_oracle, monkeypatch, reverse):
+    """CTA-per-edge kernel with SHORT shared-memory lists (HPPB200_TAIL_K=3; whole batches on large models run with 8 entries
+    per pair): an edge that outgrows them is validated again by the same CTA with 64-entry lists in global memory, inside the
+    launch.  Same results as the oracle, and no edge is left for a second pass."""
+    m, _ = eng
+    monkeypatch.setenv("HPPB200_WF_MIN", "100000000")
+    monkeypatch.setenv("HPPB200_TAIL_MAX", "100000")
+    monkeypatch.setenv("HPPB200_TAIL_K", "3")
+    monkeypatch.setenv("HPPB200_FIRST_SAMPLE_SCREEN", "0")
+    ws = pkg.Workspace(m, 0)
+    o = ur5_oracle
+    q1, q2, L = _edges(pkg, ur5, o, 3000, 47)
+    s0 = ws.stats()
+    r = ws.validate_edges(2, 0.0, q1, q2, L, reverse=reverse)
+    s1 = ws.stats()
+    e = o.validate_edges(2, 0.0, q1, q2, L, reverse=reverse)
+    for k in ("valid", "reason", "pair", "t_last_valid"):
+        assert np.array_equal(r[k], e[k]), (reverse, k)
+    assert np.array_equal(r["t_fail"], e["t_fail"], equal_nan=True)
+    assert s1["kernel_launches"] - s0["kernel_launches"] == 1
+    monkeypatch.delenv("HPPB200_TAIL_K")  # (read at every launch) 64-entry lists in shared memory: nothing is redone
+    u = ws.validate_edges(2, 0.0, q1, q2, L, reverse=reverse)
+    s2 = ws.stats()
+    assert np.array_equal(u["valid"], r["valid"]) and np.array_equal(u["t_fail"], r["t_fail"], equal_nan=True)
+    assert s1["edge_samples"] - s0["edge_samples"] > s2["edge_samples"] - s1["edge_samples"]  # the redone edges' first attempts
+
+
 @pytest.mark.parametrize("wf_min", ["1", "100000000"])
 def test_freeflyer_humanoid_parity(pkg, ob, monkeypatch, wf_min):
     """BASELINE configs[3] model WITH its free-flyer root (R^3 x SO(3), nq = 37, nv = 36): FK from the quaternion,
