@@ -38,6 +38,7 @@ Workspace::Workspace(const Model* m, int dev) : model(m), device(dev) {
   if (const char* v = std::getenv("HPPB200_PROG_TAIL_MAX")) prog_tail_max = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_FIRST_SAMPLE_SCREEN")) first_sample_screen = std::atoi(v) != 0;
   if (const char* v = std::getenv("HPPB200_FS_MIN")) first_sample_min = (size_t)std::atoll(v);
+  if (const char* v = std::getenv("HPPB200_FS_ORDER")) first_sample_order = std::atoi(v) != 0;
   if (const char* v = std::getenv("HPPB200_WF_SLOTS")) wavefront_slots = (size_t)std::atoll(v);
   if (const char* v = std::getenv("HPPB200_WF_LPT")) wavefront_lpt = std::atoi(v) != 0;
   if (const char* v = std::getenv("HPPB200_ENGINE_ALPHA")) engine_alpha = std::atof(v);

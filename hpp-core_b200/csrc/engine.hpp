@@ -179,11 +179,13 @@ struct Workspace {
   // first-sample screen of the edge path (kernels_edges.cu::launchValidateEdges)
   bool first_sample_screen = true;     // HPPB200_FIRST_SAMPLE_SCREEN=0 switches it off
   size_t first_sample_min = 2048;      // smallest batch that is screened (HPPB200_FS_MIN)
+  bool first_sample_order = true;      // the screened edges go to the engines closest-to-an-obstacle first (HPPB200_FS_ORDER=0: input order)
   DeviceBuffer<double> d_fs_q, d_fs_q1, d_fs_q2, d_fs_L, d_fs_tfail, d_fs_tlast;
   DeviceBuffer<uint8_t> d_fs_valid, d_fs_reason, d_fs_ovalid, d_fs_oreason;
   DeviceBuffer<int32_t> d_fs_first, d_fs_opair;
   DeviceBuffer<uint32_t> d_fs_list;
-  DeviceBuffer<unsigned long long> d_fs_cnt;
+  DeviceBuffer<unsigned long long> d_fs_cnt, d_fs_dmin, d_fs_keys, d_fs_keys2;
+  DeviceBuffer<uint32_t> d_fs_list2;
   DeviceBuffer<unsigned char> d_fs_tmp;
   unsigned long long* h_fs = nullptr;  // pinned: survivor count + the chunks' queue counters
   // one-item / small host-pointer calls (a planner's single-item virtuals): inputs packed in ONE pinned block and one H2D, outputs
@@ -215,8 +217,8 @@ void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, ui
                                   uint8_t* d_reason);
 size_t firstSampleChunk();
 size_t firstSampleQueueCap(size_t n);
-void launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
-                             unsigned long long* d_njobs);
+bool launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
+                             unsigned long long* d_njobs, unsigned long long* d_dmin);
 void launchValidateConfigsSmall(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason);
 void launchValidateConfigsHost(Workspace* ws, const double* h_q, size_t n, uint32_t flags, uint8_t* h_valid, int32_t* h_first,
                                uint8_t* h_reason);

@@ -176,6 +176,10 @@ struct ValidateArgs {
   uint32_t blob_head, blob_tail_off, blob_tail_bytes;
   int force_exact;         // SHADOW: every pair from the FP64 placements (HPPB200_CFG_SHADOW=2, tests)
   double hmax, reach_max;  // SHADOW slack: largest capsule half-length of a robot geometry, largest cull reach of a pair
+  // DMIN instances (first-sample screen of the edge path): [n] smallest distance among the pairs this configuration had EVALUATED
+  // (closed forms here, GJK jobs in gjkJobsKernel; culled pairs are far), as the bits of a non-negative double.  A scheduling
+  // hint only (edges that start close to an obstacle take the most samples and are started first); it reaches no result.
+  unsigned long long* dmin;
 };
 
 // Two TMA bulk copies on one mbarrier (see stageBlobTMA): the blob without the gap.
@@ -264,7 +268,7 @@ __device__ __forceinline__ double hiWord(uint32_t h) { return __hiloint2double((
 // HOSTQ: A.q is PINNED HOST memory (zero-copy form of the host-pointer path): thread 0 pulls the CTA's 128 configurations
 // (one contiguous block) over PCIe with one TMA bulk copy into shared memory while the blob is staged; the copy engine, its
 // slice-sized latency and the device staging buffer drop out, and the transfer overlaps the FP64 work CTA by CTA.
-template <bool TREE, bool SHADOW, bool HOSTQ>
+template <bool TREE, bool SHADOW, bool HOSTQ, bool DMIN = false>
 __global__ void __launch_bounds__(K1_THREADS, SHADOW ? K1_MINB : 1)
 configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -428,6 +432,7 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
       int nsurv = 0;
       int hit = -1;
       bool ex = exactAll;
+      double dminLocal = CUDART_INF;
       for (int p = 0; p < mv.ncpairs;) {
         const DevPair pr = T.cpairs[p];
         const DevShape& sa = *(const DevShape*)(pr.a >= 0 ? &T.geoms[pr.a].shape : &T.obstacles[-(pr.a + 1)].shape);
@@ -445,6 +450,7 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
             d = sqrt(segmentSegmentDist2(p1, q1, p2, q2)) - sa.p[0] - sb.p[0];
           }
           const double dm = d - pr.margin;
+          if (DMIN) dminLocal = fmin(dminLocal, dm);
           if (SHADOW && !ex) {
             if (dm > HPPB200_COLLISION_THRESHOLD + slack) { ++tests; ++p; continue; }
             if (dm <= HPPB200_COLLISION_THRESHOLD - slack) { ++tests; hit = p; break; }
@@ -482,6 +488,7 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
       A.valid[i] = hit < 0 ? 1 : 0;
       A.first[i] = (uint32_t)hit;
       A.reason[i] = hit < 0 ? HPPB200_REASON_VALID : HPPB200_REASON_COLLISION;
+      if (DMIN) A.dmin[i] = (unsigned long long)__double_as_longlong(fmax(dminLocal, 0.0));  // (gjkJobsKernel runs behind this kernel)
     }
   }
   // ---- flush this block's jobs with ONE global atomic ----
@@ -501,6 +508,7 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
 #ifndef K2_GRID_PER_SM
 #define K2_GRID_PER_SM 12
 #endif
+template <bool DMIN = false>
 __global__ void __launch_bounds__(K2_THREADS, 384 / K2_THREADS)
 gjkJobsKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
   extern __shared__ __align__(16) unsigned char smem[];
@@ -525,7 +533,7 @@ gjkJobsKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
       atomicMin(&A.first[i], p);
       A.valid[i] = 0;
       A.reason[i] = HPPB200_REASON_COLLISION;
-    }
+    } else if (DMIN) atomicMin(&A.dmin[i], (unsigned long long)__double_as_longlong(d));
   }
   const unsigned ts = __reduce_add_sync(0xffffffffu, tests);
   const unsigned gi = __reduce_add_sync(0xffffffffu, cnt.iterations);
@@ -611,14 +619,14 @@ static void launchTwoKernelsOn(Workspace* ws, cudaStream_t stream, const double*
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), stream));
   launchConfigPass(configPassSetup(ws, hostq), stream, A, ws->d_stats);
   const size_t smem2 = 16 + mv.blob_bytes;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
   size_t grid2 = (size_t)ws->num_sms * K2_GRID_PER_SM;
   if (streamJobs) {
     HPPB200_CUDA_CHECK(cudaEventRecord(evPass, stream));
     HPPB200_CUDA_CHECK(cudaStreamWaitEvent(streamJobs, evPass, 0));
     stream = streamJobs;
   }
-  gjkJobsKernel<<<(unsigned)grid2, K2_THREADS, smem2, stream>>>(mv, A, ws->d_stats);
+  gjkJobsKernel<false><<<(unsigned)grid2, K2_THREADS, smem2, stream>>>(mv, A, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 2;
   ws->stats.configs += n;
@@ -632,21 +640,29 @@ static void launchTwoKernelsOn(Workspace* ws, cudaStream_t stream, const double*
 // compares them with firstSampleQueueCap(min(n, chunk)) after synchronising: an overflowed queue voids the screen.
 size_t firstSampleChunk() { return 262144; }
 size_t firstSampleQueueCap(size_t n) { return 16 * n + 4096; }
-void launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
-                             unsigned long long* d_njobs /* [chunks] */) {
+// Returns whether d_dmin (the scheduling hint, see ValidateArgs::dmin) was filled.
+bool launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
+                             unsigned long long* d_njobs /* [chunks] */, unsigned long long* d_dmin /* [n] or null */) {
   const bool tree = modelIsTree(ws->model);
   const ModelView& mv = ws->view;
   ModelView mv2 = mv;
   mv2.off_cpairs = mv.off_bgpairs;
   mv2.ncpairs = mv.nbgpairs;
-  const ConfigPassSetup S = configPassSetup(ws, false, true);
+  ConfigPassSetup S = configPassSetup(ws, false, true);
+  if (d_dmin) {  // (the DMIN instances exist in the shadow form; HPPB200_CFG_SHADOW=0: no hint)
+    if (S.fn == configPassKernel<true, true, false>) S.fn = configPassKernel<true, true, false, true>;
+    else if (S.fn == configPassKernel<false, true, false>) S.fn = configPassKernel<false, true, false, true>;
+    else d_dmin = nullptr;
+    if (d_dmin) HPPB200_CUDA_CHECK(cudaFuncSetAttribute(S.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S.smem));
+  }
   const size_t chunk = std::min(n, firstSampleChunk());
   const size_t slots = (size_t)mv.ngeoms + (tree ? mv.njoints : 0);
   ws->d_scratch.reserve(slots * 12 * chunk);
   const size_t cap = firstSampleQueueCap(chunk);
   ws->d_jobs.reserve(cap + 1);
   const size_t smem2 = 16 + mv.blob_bytes;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
   const size_t nq = (size_t)ws->model->nq;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(d_njobs, 0, ((n + chunk - 1) / chunk) * sizeof(unsigned long long), ws->stream));
   size_t c = 0;
@@ -658,11 +674,14 @@ void launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t
     A.njobs = d_njobs + c;
     A.jobs = ws->d_jobs.p + 1;
     A.jobs_cap = cap;
+    A.dmin = d_dmin ? d_dmin + off : nullptr;
     launchConfigPass(S, ws->stream, A, ws->d_stats);
-    gjkJobsKernel<<<(unsigned)((size_t)ws->num_sms * K2_GRID_PER_SM), K2_THREADS, smem2, ws->stream>>>(mv2, A, ws->d_stats);
+    if (d_dmin) gjkJobsKernel<true><<<(unsigned)((size_t)ws->num_sms * K2_GRID_PER_SM), K2_THREADS, smem2, ws->stream>>>(mv2, A, ws->d_stats);
+    else gjkJobsKernel<false><<<(unsigned)((size_t)ws->num_sms * K2_GRID_PER_SM), K2_THREADS, smem2, ws->stream>>>(mv2, A, ws->d_stats);
     HPPB200_CUDA_CHECK(cudaGetLastError());
     ws->stats.kernel_launches += 2;
   }
+  return d_dmin != nullptr;
 }
 
 // Jobs that did not fit the queue (pathological scenes): detected on the host, which re-runs the
@@ -778,8 +797,8 @@ void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, ui
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.njobs, 0, sizeof(unsigned long long), ws->stream));  // the one thing that must start at zero
   launchConfigPass(configPassSetup(ws), ws->stream, A, ws->d_stats);
   const size_t smem2 = 16 + mv.blob_bytes;
-  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
-  gjkJobsKernel<<<(unsigned)((size_t)ws->num_sms * K2_GRID_PER_SM), K2_THREADS, smem2, ws->stream>>>(mv, A, ws->d_stats);
+  HPPB200_CUDA_CHECK(cudaFuncSetAttribute(gjkJobsKernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+  gjkJobsKernel<false><<<(unsigned)((size_t)ws->num_sms * K2_GRID_PER_SM), K2_THREADS, smem2, ws->stream>>>(mv, A, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 2;
   ws->stats.configs += n;

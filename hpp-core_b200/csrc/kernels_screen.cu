@@ -17,6 +17,7 @@
 // Batches whose start configurations are all valid (a planner extending from roadmap nodes) pay the screen (~1 % of a
 // Progressive batch) and run unscreened; batches of random edges lose the share that starts in collision (93 % on
 // BASELINE configs[3]).
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_select.cuh>
 #include <cub/iterator/counting_input_iterator.cuh>
 
@@ -59,6 +60,11 @@ __global__ void fsFinishKernel(const uint8_t* __restrict__ fsValid, const int32_
   }
   const unsigned b = __ballot_sync(0xffffffffu, hit);
   if ((threadIdx.x & 31) == 0 && b && stats) atomicAdd(&stats->edge_samples, (unsigned long long)__popc(b));
+}
+
+__global__ void fsKeysKernel(const uint32_t* __restrict__ list, size_t ns, const unsigned long long* __restrict__ dmin, unsigned long long* __restrict__ keys) {
+  const size_t j = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < ns) keys[j] = dmin[list[j]];
 }
 
 __global__ void fsGatherKernel(const uint32_t* __restrict__ list, size_t ns, int nq, const double* __restrict__ q1,
@@ -117,7 +123,10 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   ws->d_fs_list.reserve(n);
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (trace) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, ws->stream); }
-  launchFirstSampleScreen(ws, qStart, n, ws->d_fs_valid.p, ws->d_fs_first.p, ws->d_fs_reason.p, ws->d_fs_cnt.p + 1);
+  const bool order = ws->first_sample_order;
+  if (order) ws->d_fs_dmin.reserve(n);
+  const bool hint = launchFirstSampleScreen(ws, qStart, n, ws->d_fs_valid.p, ws->d_fs_first.p, ws->d_fs_reason.p, ws->d_fs_cnt.p + 1,
+                                            order ? ws->d_fs_dmin.p : nullptr);
   if (trace) cudaEventRecord(e1, ws->stream);
   // survivors, in input order
   size_t tmpBytes = 0;
@@ -158,7 +167,26 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   ws->d_fs_tlast.reserve(ns);
   ws->d_fs_opair.reserve(ns);
   ws->d_fs_oreason.reserve(ns);
-  fsGatherKernel<<<(unsigned)((ns * (size_t)nq + 255) / 256), 256, 0, ws->stream>>>(ws->d_fs_list.p, ns, nq, d_q1, d_q2, d_L, ws->d_fs_q1.p,
+  // The edges that go on, closest-to-an-obstacle first: an edge that starts (or, in reverse, ends) millimetres from an obstacle is
+  // the one that takes hundreds of dependent samples, and the CTA-per-edge kernel ends when the LAST such chain ends: started in
+  // input order, the longest chains of BASELINE configs[3] begin anywhere in the batch and stretch it by ~20 ms of 63.  The order
+  // decides only when an edge runs; the key is the smallest distance the screen happened to evaluate at q(t0).
+  const uint32_t* list = ws->d_fs_list.p;
+  if (hint) {
+    ws->d_fs_keys.reserve(ns);
+    ws->d_fs_keys2.reserve(ns);
+    ws->d_fs_list2.reserve(ns);
+    fsKeysKernel<<<(unsigned)((ns + 255) / 256), 256, 0, ws->stream>>>(ws->d_fs_list.p, ns, ws->d_fs_dmin.p, ws->d_fs_keys.p);
+    HPPB200_CUDA_CHECK(cudaGetLastError());
+    size_t sortBytes = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, sortBytes, ws->d_fs_keys.p, ws->d_fs_keys2.p, ws->d_fs_list.p, ws->d_fs_list2.p, (int)ns, 0, 64, ws->stream);
+    ws->d_fs_tmp.reserve(sortBytes + 256);
+    HPPB200_CUDA_CHECK(cub::DeviceRadixSort::SortPairs(ws->d_fs_tmp.p, sortBytes, ws->d_fs_keys.p, ws->d_fs_keys2.p, ws->d_fs_list.p, ws->d_fs_list2.p,
+                                                       (int)ns, 0, 64, ws->stream));
+    ws->stats.kernel_launches += 2;
+    list = ws->d_fs_list2.p;
+  }
+  fsGatherKernel<<<(unsigned)((ns * (size_t)nq + 255) / 256), 256, 0, ws->stream>>>(list, ns, nq, d_q1, d_q2, d_L, ws->d_fs_q1.p,
                                                                                    ws->d_fs_q2.p, ws->d_fs_L.p);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   std::chrono::steady_clock::time_point c0;
@@ -170,7 +198,7 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
     std::fprintf(stderr, "[edges] engines on the %zu screened edges: %.3f ms\n", ns,
                  std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - c0).count());
   }
-  fsScatterKernel<<<(unsigned)((ns + 255) / 256), 256, 0, ws->stream>>>(ws->d_fs_list.p, ns, ws->d_fs_ovalid.p, ws->d_fs_tfail.p, ws->d_fs_tlast.p,
+  fsScatterKernel<<<(unsigned)((ns + 255) / 256), 256, 0, ws->stream>>>(list, ns, ws->d_fs_ovalid.p, ws->d_fs_tfail.p, ws->d_fs_tlast.p,
                                                                        ws->d_fs_opair.p, ws->d_fs_oreason.p, d_valid, d_tfail, d_tlast, d_pair,
                                                                        d_reason);
   HPPB200_CUDA_CHECK(cudaGetLastError());

@@ -34,7 +34,10 @@
 namespace hppb200 {
 
 constexpr int DT_THREADS = 128;
-constexpr int DT_MINB = 3;   // CTAs per SM the register budget is held to
+#ifndef HPPB200_DT_MINB
+#define HPPB200_DT_MINB 3
+#endif
+constexpr int DT_MINB = HPPB200_DT_MINB;   // CTAs per SM the register budget is held to
 constexpr int DT_K = 64;     // validated intervals per body pair (lists in global memory)
 constexpr int DT_KS = 256;   // intervals of the edge's valid subset (shared memory)
 constexpr uint32_t DT_SMEM_LISTS = 64u * 1024u;  // shared-memory budget of the per-pair lists of the first pass
