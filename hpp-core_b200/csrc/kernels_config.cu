@@ -638,7 +638,10 @@ static void launchTwoKernelsOn(Workspace* ws, cudaStream_t stream, const double*
 // sample of an edge (body-pair-collision.cc:175-198: same predicate, same order, nothing validated yet).  In chunks, so
 // that the placement scratch stays bounded.  d_njobs [chunks] receives the queue counter of every chunk; the caller
 // compares them with firstSampleQueueCap(min(n, chunk)) after synchronising: an overflowed queue voids the screen.
-size_t firstSampleChunk() { return 262144; }
+size_t firstSampleChunk() {
+  if (const char* v = std::getenv("HPPB200_FS_CHUNK")) return (size_t)std::max(128ll, std::atoll(v));  // (tests: several chunks on a small batch)
+  return 262144;
+}
 size_t firstSampleQueueCap(size_t n) { return 16 * n + 4096; }
 // Returns whether d_dmin (the scheduling hint, see ValidateArgs::dmin) was filled.
 bool launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,

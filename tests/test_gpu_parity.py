@@ -573,6 +573,7 @@ def test_first_sample_screen_same_results(pkg, ob, monkeypatch, name):
     desc = pkg.ModelDescription.load(name)
     o = ob.Oracle(desc)
     monkeypatch.setenv("HPPB200_FS_MIN", "1")
+    monkeypatch.setenv("HPPB200_FS_CHUNK", "1000")  # (read at every call) the screen in several chunks, the last one partial
     ws_on = pkg.Workspace(pkg.Model(desc), 0)
     monkeypatch.setenv("HPPB200_FIRST_SAMPLE_SCREEN", "0")
     ws_off = pkg.Workspace(pkg.Model(desc), 0)
