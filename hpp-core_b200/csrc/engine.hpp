@@ -217,6 +217,7 @@ void launchValidateConfigsNoAlloc(Workspace* ws, const double* d_q, size_t n, ui
                                   uint8_t* d_reason);
 size_t firstSampleChunk();
 size_t firstSampleQueueCap(size_t n);
+bool firstSampleScreenAvailable(Workspace* ws);
 bool launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
                              unsigned long long* d_njobs, unsigned long long* d_dmin);
 void launchValidateConfigsSmall(Workspace* ws, const double* d_q, size_t n, uint32_t flags, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason);

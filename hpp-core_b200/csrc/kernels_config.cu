@@ -176,9 +176,11 @@ struct ValidateArgs {
   uint32_t blob_head, blob_tail_off, blob_tail_bytes;
   int force_exact;         // SHADOW: every pair from the FP64 placements (HPPB200_CFG_SHADOW=2, tests)
   double hmax, reach_max;  // SHADOW slack: largest capsule half-length of a robot geometry, largest cull reach of a pair
-  // DMIN instances (first-sample screen of the edge path): [n] smallest distance among the pairs this configuration had EVALUATED
-  // (closed forms here, GJK jobs in gjkJobsKernel; culled pairs are far), as the bits of a non-negative double.  A scheduling
-  // hint only (edges that start close to an obstacle take the most samples and are started first); it reaches no result.
+  // DMIN instances (first-sample screen of the edge path): [n] how close this configuration is to a collision: the smallest of the
+  // distances of the pairs that were evaluated (closed forms here, GJK jobs in gjkJobsKernel) and of the separation bounds of the
+  // pairs that were culled (a culled pair is provably apart, possibly by a fraction of a millimetre), as the bits of a non-negative
+  // double.  A scheduling hint only (edges that start close to an obstacle take the most samples and are started first); it
+  // reaches no result.
   unsigned long long* dmin;
 };
 
@@ -410,6 +412,7 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
           u = mk(O.P[2], O.P[5], O.P[8]);
         }
       };
+      double dminLocal = CUDART_INF;  // DMIN: smallest distance (evaluated pairs) or separation bound (culled pairs) of this configuration
       // box-face separating axes: a lower bound of the distance of geometry a's core to the obstacle box b (true: culled)
       auto boxFaceCull = [&](int p, bool ex) -> bool {
         const DevPair pr = T.cpairs[p];
@@ -425,14 +428,15 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
         const double sy = fmax(fmin(e0.y, e1.y) - O.shape.p[1], -fmax(e0.y, e1.y) - O.shape.p[1]);
         const double sz = fmax(fmin(e0.z, e1.z) - O.shape.p[2], -fmax(e0.z, e1.z) - O.shape.p[2]);
         const double ra = pr.a >= 0 ? T.geoms[pr.a].bound.br : T.obstacles[-(pr.a + 1)].bound.br;
-        return fmax(sx, fmax(sy, sz)) - ra - pr.margin > 1e-9 + sl;
+        const double gap = fmax(sx, fmax(sy, sz)) - ra - pr.margin;
+        if (DMIN && gap > 1e-9 + sl) dminLocal = fmin(dminLocal, gap);  // culled = provably apart, not far: the bound is the hint
+        return gap > 1e-9 + sl;
       };
       const bool deferSat = mv.ncpairs <= 256;
       unsigned long long surv = 0;
       int nsurv = 0;
       int hit = -1;
       bool ex = exactAll;
-      double dminLocal = CUDART_INF;
       for (int p = 0; p < mv.ncpairs;) {
         const DevPair pr = T.cpairs[p];
         const DevShape& sa = *(const DevShape*)(pr.a >= 0 ? &T.geoms[pr.a].shape : &T.obstacles[-(pr.a + 1)].shape);
@@ -468,7 +472,13 @@ configPassKernel(ModelView mv, ValidateArgs A, DeviceStats* stats) {
         double d2;
         if (pr.bound == 1) d2 = pointSegmentDist2(cb, ca, ua, sa.p[1]);
         else { V3 dd = ca - cb; d2 = dot(dd, dd); }
-        if (d2 > pr.cull2 + csl) { ++p; continue; }
+        if (d2 > pr.cull2 + csl) {
+          // (DMIN: cores farther apart than the reach, by this much at least; only looked at within 1.1 x the reach: the chains
+          //  that matter start millimetres from an obstacle)
+          if (DMIN && d2 < 1.21 * pr.cull2) dminLocal = fmin(dminLocal, sqrt(d2) - sqrt(pr.cull2));
+          ++p;
+          continue;
+        }
         if (pr.b < 0 && sb.type == SH_BOX) {
           // The box-face bound runs for the few pairs that pass the first cull, at a different pair per lane: inline it
           // executed at 1.6 of 32 lanes (8 % of the kernel's instructions).  The survivors are noted (up to 8 pair indices of
@@ -643,6 +653,15 @@ size_t firstSampleChunk() {
   return 262144;
 }
 size_t firstSampleQueueCap(size_t n) { return 16 * n + 4096; }
+// (a model whose tables do not fit the configuration kernel's shared memory is validated without the screen)
+bool firstSampleScreenAvailable(Workspace* ws) {
+  try {
+    (void)configPassSetup(ws, false, true);
+    return true;
+  } catch (const std::runtime_error&) {
+    return false;
+  }
+}
 // Returns whether d_dmin (the scheduling hint, see ValidateArgs::dmin) was filled.
 bool launchFirstSampleScreen(Workspace* ws, const double* d_q, size_t n, uint8_t* d_valid, int32_t* d_first, uint8_t* d_reason,
                              unsigned long long* d_njobs /* [chunks] */, unsigned long long* d_dmin /* [n] or null */) {

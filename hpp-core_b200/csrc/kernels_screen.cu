@@ -98,7 +98,7 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
                          size_t n, uint32_t flags, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason) {
   if (n == 0) return;
   const bool screen = ws->first_sample_screen && method != HPPB200_METHOD_DISCRETIZED && n >= ws->first_sample_min && n <= 0x7fffffffull &&
-                      ws->max_iterations >= 1 && ws->view.nbgpairs > 0;
+                      ws->max_iterations >= 1 && ws->view.nbgpairs > 0 && firstSampleScreenAvailable(ws);
   if (!screen) {
     launchValidateEdgesCore(ws, method, param, reverse, d_q1, d_q2, d_L, n, flags, d_valid, d_tfail, d_tlast, d_pair, d_reason);
     return;

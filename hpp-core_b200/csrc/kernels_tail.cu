@@ -26,6 +26,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <map>
+#include <vector>
 #include <mutex>
 #include <tuple>
 
@@ -33,7 +34,10 @@
 
 namespace hppb200 {
 
-constexpr int DT_THREADS = 128;
+#ifndef HPPB200_DT_THREADS
+#define HPPB200_DT_THREADS 128
+#endif
+constexpr int DT_THREADS = HPPB200_DT_THREADS;
 #ifndef HPPB200_DT_MINB
 #define HPPB200_DT_MINB 3
 #endif
@@ -62,6 +66,7 @@ struct TailArgs {
   int K;           // validated intervals per body pair
   double2* retry_lists;  // lists in shared memory with K < DT_K: [grid][nbodypairs][DT_K] in global memory for the edges that outgrow them
   unsigned long long* clk;  // optional [8]: cycles of thread 0 per phase (HPPB200_WF_TRACE)
+  unsigned long long* cta_log;  // optional [grid][4] (HPPB200_WF_TRACE): exit time, start / duration / samples of the CTA's longest edge (globaltimer ns)
   TailResume resume;        // Progressive: continue the edges of these wavefront slots (slots == null: start edges afresh)
 };
 
@@ -154,6 +159,7 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
   __shared__ long long s_ck[8];
   long long c0 = 0;
   const bool timing = A.clk != nullptr && tid == 0;
+  unsigned long long logStart = 0, logDur = 0, logIters = 0;
   if (timing)
     for (int i = 0; i < 8; ++i) s_ck[i] = 0;
 #define DT_TICK(i) do { if (timing) { const long long c1 = clock64(); s_ck[i] += c1 - c0; c0 = c1; } } while (0)
@@ -234,6 +240,8 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
       lists = redo ? A.retry_lists + (size_t)blockIdx.x * NP * DT_K : baseLists;
     }
     const uint32_t edge = s_edge;
+    unsigned long long tEdge0 = 0;
+    if (timing && A.cta_log) asm volatile("mov.u64 %0, %globaltimer;" : "=l"(tEdge0));
     const double L = A.L[edge];
     const double* q1 = A.q1 + (size_t)edge * mv.nq;
     const double* q2 = A.q2 + (size_t)edge * mv.nq;
@@ -588,7 +596,18 @@ edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
       DT_TICK(6);
       if (s_run == RUN_FINISHED) break;
     }
+    if (timing && A.cta_log) {
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+      if (t1 - tEdge0 > logDur) { logDur = t1 - tEdge0; logStart = tEdge0; logIters = s_iters; }
+    }
     __syncthreads();  // the edge's shared state is dead from here
+  }
+  if (timing && A.cta_log) {
+    unsigned long long t1;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t1));
+    unsigned long long* o = A.cta_log + 4 * (size_t)blockIdx.x;
+    o[0] = t1; o[1] = logStart; o[2] = logDur; o[3] = logIters;
   }
 
   if (timing)
@@ -655,10 +674,11 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
     }
   }
   const size_t grid = std::min<size_t>(n, (size_t)ws->num_sms * (size_t)perSM);
+  const bool trace0 = std::getenv("HPPB200_WF_TRACE") != nullptr;
   const bool retry = smemLists && K < DT_K;
   const size_t listBytes = smemLists && !retry ? 0 : grid * (size_t)mv.nbodypairs * DT_K * sizeof(double2);
-  ws->d_tail.reserve(listBytes + 128);
-  const bool trace = std::getenv("HPPB200_WF_TRACE") != nullptr;
+  ws->d_tail.reserve(listBytes + 128 + (trace0 ? grid * 32 : 0));
+  const bool trace = trace0;
   TailArgs A{};
   A.q1 = d_q1; A.q2 = d_q2; A.L = d_L; A.edge_list = d_list; A.n = n;
   A.reverse = reverse; A.tol = tol; A.max_iter = ws->max_iterations; A.overflow_reason = overflow_reason;
@@ -669,6 +689,7 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   if (resume) A.resume = *resume;
   A.counter = (unsigned long long*)(ws->d_tail.p + listBytes);
   A.clk = trace ? A.counter + 1 : nullptr;
+  A.cta_log = trace ? A.counter + 16 : nullptr;
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.counter, 0, 9 * sizeof(unsigned long long), ws->stream));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (trace) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, ws->stream); }
@@ -684,6 +705,26 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
     cudaEventElapsedTime(&kms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     std::fprintf(stderr, "[tail] kernel %.3f ms\n", kms);
+    if (grid > 1) {
+      std::vector<unsigned long long> lg(4 * grid);
+      HPPB200_CUDA_CHECK(cudaMemcpy(lg.data(), A.cta_log, lg.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+      unsigned long long t0 = ~0ull, tEnd = 0;
+      for (size_t b = 0; b < grid; ++b) { if (lg[4 * b + 1]) t0 = std::min(t0, lg[4 * b + 1]); tEnd = std::max(tEnd, lg[4 * b]); }
+      std::vector<double> ends;
+      for (size_t b = 0; b < grid; ++b) ends.push_back((double)(lg[4 * b] - t0) * 1e-6);
+      std::vector<size_t> idx(grid);
+      for (size_t b = 0; b < grid; ++b) idx[b] = b;
+      std::sort(idx.begin(), idx.end(), [&](size_t a, size_t b) { return ends[a] > ends[b]; });
+      std::vector<double> se = ends;
+      std::sort(se.begin(), se.end());
+      std::fprintf(stderr, "[tail] CTA exit times (ms after the first edge started): median %.2f, p90 %.2f, p99 %.2f, max %.2f; the last CTAs:\n", se[grid / 2],
+                   se[grid * 9 / 10], se[grid * 99 / 100], se[grid - 1]);
+      for (size_t k = 0; k < std::min<size_t>(6, grid); ++k) {
+        const size_t b = idx[k];
+        std::fprintf(stderr, "[tail]   CTA %zu exits at %.2f ms; its longest edge: started %.2f ms, took %.2f ms, %llu samples\n", b, ends[b],
+                     (double)(lg[4 * b + 1] - t0) * 1e-6, (double)lg[4 * b + 2] * 1e-6, lg[4 * b + 3]);
+      }
+    }
     std::fprintf(stderr, "[tail] n=%zu grid=%zu (%d per SM) K=%d %s smem=%u B; thread-0 Mcycles: A %.2f B %.2f C %.2f narrow %.2f replay %.2f insert %.2f next %.2f; second stages %llu\n",
                  n, grid, perSM, K, smemLists ? "shared" : "global", Lo.total, ck[0] * 1e-6, ck[1] * 1e-6, ck[2] * 1e-6, ck[3] * 1e-6, ck[4] * 1e-6,
                  ck[5] * 1e-6, ck[6] * 1e-6, ck[7]);
