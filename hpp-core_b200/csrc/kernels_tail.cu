@@ -670,7 +670,13 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
       const TailLayout L2 = tailLayout(mv, k2);
       int p2 = 0;
       HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2, kern, DT_THREADS, L2.total));
-      if (p2 > perSM) { K = k2; Lo = L2; perSM = p2; break; }
+      if (p2 > perSM) {
+        // ... and two entries less than that: what the lists give up goes to the L1 the three CTAs share (the tables are read
+        // from global memory; BASELINE configs[3]: 8 entries 51.0 ms, 6 entries 48.5 ms, 4 entries 50.2 ms with more edges redone)
+        K = std::max(6, k2 - 2); Lo = tailLayout(mv, K);
+        HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, DT_THREADS, Lo.total));
+        break;
+      }
     }
   }
   const size_t grid = std::min<size_t>(n, (size_t)ws->num_sms * (size_t)perSM);
