@@ -639,6 +639,9 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   if (smemLists) {
     K = std::min<int>(DT_K, (int)(DT_SMEM_LISTS / (16u * (uint32_t)mv.nbodypairs)));
     if (K < 8) return false;
+    // Progressive keeps ONE connected validated interval per body pair: two entries, the rest of the shared memory
+    // goes to the L1 (an edge that ever needed more would be redone with DT_K entries like any other overflow)
+    if (method == HPPB200_METHOD_PROGRESSIVE) K = std::min(K, 2);
     if (const char* v = std::getenv("HPPB200_TAIL_K")) K = std::max(2, std::min(K, std::atoi(v)));  // (tests: short lists, so that edges outgrow them)
   }
   TailLayout Lo = tailLayout(mv, smemLists ? K : 0);
