@@ -117,9 +117,13 @@ __device__ __forceinline__ void store12(double* p, const T3& X) {
   p[9] = X.t.x; p[10] = X.t.y; p[11] = X.t.z;
 }
 
-template <int METHOD>
-__global__ void __launch_bounds__(DT_THREADS, DT_MINB)
+template <int METHOD, int THREADS = 128>
+__global__ void __launch_bounds__(THREADS, THREADS == 96 ? 4 : hppb200::DT_MINB)
 edgeTailKernel(ModelView mv, TailArgs A, DeviceStats* stats) {
+  // THREADS = 96 (three warps, four CTAs per SM at the same 168 registers): Progressive on models with many body pairs, whose
+  // two-entry lists leave the shared memory for a fourth CTA (63.6 -> 52.6 ms on 87 k edges of the 273-pair humanoid; Dichotomy
+  // does not gain: its lists would have to shrink to 4 entries)
+  constexpr int DT_THREADS = THREADS;
   constexpr bool PROG = METHOD == HPPB200_METHOD_PROGRESSIVE;
   extern __shared__ __align__(16) unsigned char smem[];
   const Tables T = makeTables(mv.blob, mv);  // global copy (read-only, L1 resident)
@@ -631,7 +635,13 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
                     const uint32_t* d_list, size_t n, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair,
                     uint8_t* d_reason, int overflow_reason, bool smemLists, const TailResume* resume) {
   const ModelView& mv = ws->view;
-  auto kern = method == HPPB200_METHOD_PROGRESSIVE ? edgeTailKernel<HPPB200_METHOD_PROGRESSIVE> : edgeTailKernel<HPPB200_METHOD_DICHOTOMY>;
+  // (see the THREADS note at the kernel; HPPB200_TAIL_THREADS=128 keeps four warps everywhere)
+  bool narrowCta = method == HPPB200_METHOD_PROGRESSIVE && smemLists && mv.nbodypairs > 128 && n >= (size_t)ws->num_sms * 8;
+  if (const char* v = std::getenv("HPPB200_TAIL_THREADS")) narrowCta = narrowCta && std::atoi(v) == 96;
+  const int threads = narrowCta ? 96 : DT_THREADS, minb = narrowCta ? 4 : DT_MINB;
+  auto kern = method == HPPB200_METHOD_PROGRESSIVE
+                  ? (narrowCta ? edgeTailKernel<HPPB200_METHOD_PROGRESSIVE, 96> : edgeTailKernel<HPPB200_METHOD_PROGRESSIVE, 128>)
+                  : edgeTailKernel<HPPB200_METHOD_DICHOTOMY, 128>;
   if (n == 0) return true;
   if (mv.nbodypairs > 65535 || mv.nbodypairs == 0) return false;
   if (mv.nbgpairs > 65535) return false;  // (16-bit job records)
@@ -651,13 +661,13 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   int perSM = 0;
   {
     static std::mutex mu;
-    static std::map<std::tuple<int, int, uint32_t>, int> cache;
+    static std::map<std::tuple<int, int, int, uint32_t>, int> cache;
     std::lock_guard<std::mutex> lock(mu);
-    const auto key = std::make_tuple(ws->device, method, Lo.total);
+    const auto key = std::make_tuple(ws->device, method, threads, Lo.total);
     auto it = cache.find(key);
     if (it == cache.end()) {
       HPPB200_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, DT_THREADS, Lo.total));
+      HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, threads, Lo.total));
       it = cache.emplace(key, perSM).first;
     }
     perSM = it->second;
@@ -668,16 +678,16 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   // that outgrows them is reported with `overflow_reason` and redone by the next level, like any other overflow.
   int tailOcc = 1;
   if (const char* v = std::getenv("HPPB200_TAIL_OCC")) tailOcc = std::atoi(v);
-  if (tailOcc && smemLists && K > 8 && n >= (size_t)ws->num_sms * 8 && perSM < DT_MINB) {
+  if (tailOcc && smemLists && K > 8 && n >= (size_t)ws->num_sms * 8 && perSM < minb) {
     for (int k2 = K - 1; k2 >= 8; --k2) {
       const TailLayout L2 = tailLayout(mv, k2);
       int p2 = 0;
-      HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2, kern, DT_THREADS, L2.total));
+      HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&p2, kern, threads, L2.total));
       if (p2 > perSM) {
         // ... and two entries less than that: what the lists give up goes to the L1 the three CTAs share (the tables are read
         // from global memory; BASELINE configs[3]: 8 entries 51.0 ms, 6 entries 48.5 ms, 4 entries 50.2 ms with more edges redone)
         K = std::max(6, k2 - 2); Lo = tailLayout(mv, K);
-        HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, DT_THREADS, Lo.total));
+        HPPB200_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSM, kern, threads, Lo.total));
         break;
       }
     }
@@ -702,7 +712,7 @@ bool launchEdgeTail(Workspace* ws, int method, double tol, int reverse, const do
   HPPB200_CUDA_CHECK(cudaMemsetAsync(A.counter, 0, 9 * sizeof(unsigned long long), ws->stream));
   cudaEvent_t e0 = nullptr, e1 = nullptr;
   if (trace) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, ws->stream); }
-  kern<<<(unsigned)grid, DT_THREADS, Lo.total, ws->stream>>>(mv, A, ws->d_stats);
+  kern<<<(unsigned)grid, threads, Lo.total, ws->stream>>>(mv, A, ws->d_stats);
   HPPB200_CUDA_CHECK(cudaGetLastError());
   ws->stats.kernel_launches += 1;
   if (trace) {
