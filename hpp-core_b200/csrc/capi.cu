@@ -53,6 +53,9 @@ Workspace::~Workspace() {
   if (h_njobs) cudaFreeHost(h_njobs);
   if (h_small) cudaFreeHost(h_small);
   if (h_fs) cudaFreeHost(h_fs);
+  if (edge_copy_stream) cudaStreamDestroy(edge_copy_stream);
+  if (ev_edge_in) cudaEventDestroy(ev_edge_in);
+  if (ev_edge_q1) cudaEventDestroy(ev_edge_q1);
   if (stream2) cudaStreamDestroy(stream2);
   if (stream3) cudaStreamDestroy(stream3);
   if (stream4) cudaStreamDestroy(stream4);
@@ -475,10 +478,40 @@ int hppb200_validate_edges(hppb200_workspace* wsp, int method, double param, int
     ws->d_tlast.reserve(n);
     Timed tm(ws);
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q.p, q1, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q2.p, q2, n * nq * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
-    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_L.p, L, n * sizeof(double), cudaMemcpyHostToDevice, ws->stream));
-    launchValidateEdges(ws, method, param, reverse, ws->d_q.p, ws->d_q2.p, ws->d_L.p, n, flags, ws->d_valid.p,
-                        ws->d_tfail.p, ws->d_tlast.p, ws->d_pair.p, ws->d_reason.p);
+    // A batch the first-sample screen will look at (forward: it needs q1 only): q2 and L on their own stream, under the screen
+    // (the 30-joint model of BASELINE configs[3]: 240 MB of the 511 MB a 1 M-edge call brings in)
+    const bool split = ws->first_sample_screen && method != HPPB200_METHOD_DISCRETIZED && !reverse && n >= ws->first_sample_min;
+    cudaStream_t s2 = ws->stream;
+    if (split) {
+      if (!ws->edge_copy_stream) {
+        HPPB200_CUDA_CHECK(cudaStreamCreateWithFlags(&ws->edge_copy_stream, cudaStreamNonBlocking));
+        HPPB200_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_edge_in, cudaEventDisableTiming));
+        HPPB200_CUDA_CHECK(cudaEventCreateWithFlags(&ws->ev_edge_q1, cudaEventDisableTiming));
+      }
+      s2 = ws->edge_copy_stream;  // (nothing of an earlier call is in flight: every call returns synchronised)
+      // behind q1, not beside it: two H2D copies in flight share the link and q1 would arrive with q2
+      HPPB200_CUDA_CHECK(cudaEventRecord(ws->ev_edge_q1, ws->stream));
+      HPPB200_CUDA_CHECK(cudaStreamWaitEvent(s2, ws->ev_edge_q1, 0));
+    }
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_q2.p, q2, n * nq * sizeof(double), cudaMemcpyHostToDevice, s2));
+    HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->d_L.p, L, n * sizeof(double), cudaMemcpyHostToDevice, s2));
+    ws->edge_inputs_ready = nullptr;
+    if (split) {
+      HPPB200_CUDA_CHECK(cudaEventRecord(ws->ev_edge_in, s2));
+      ws->edge_inputs_ready = ws->ev_edge_in;
+    }
+    try {
+      launchValidateEdges(ws, method, param, reverse, ws->d_q.p, ws->d_q2.p, ws->d_L.p, n, flags, ws->d_valid.p,
+                          ws->d_tfail.p, ws->d_tlast.p, ws->d_pair.p, ws->d_reason.p);
+    } catch (...) {
+      ws->edge_inputs_ready = nullptr;
+      if (split) cudaStreamSynchronize(s2);
+      throw;
+    }
+    if (ws->edge_inputs_ready) {  // (not consumed: cannot happen, kept for safety)
+      HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream, ws->edge_inputs_ready, 0));
+      ws->edge_inputs_ready = nullptr;
+    }
     HPPB200_CUDA_CHECK(cudaMemcpyAsync(valid, ws->d_valid.p, n, cudaMemcpyDeviceToHost, ws->stream));
     if (t_fail) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_fail, ws->d_tfail.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));
     if (t_last_valid) HPPB200_CUDA_CHECK(cudaMemcpyAsync(t_last_valid, ws->d_tlast.p, n * sizeof(double), cudaMemcpyDeviceToHost, ws->stream));

@@ -188,6 +188,11 @@ struct Workspace {
   DeviceBuffer<uint32_t> d_fs_list2;
   DeviceBuffer<unsigned char> d_fs_tmp;
   unsigned long long* h_fs = nullptr;  // pinned: survivor count + the chunks' queue counters
+  // host-pointer edge calls (capi.cu): q2 and L arrive on their own stream while the screen runs on q1; launchValidateEdges waits for
+  // this event (recorded behind those copies) before it first touches q2 / L, and clears it
+  cudaStream_t edge_copy_stream = nullptr;
+  cudaEvent_t ev_edge_in = nullptr, ev_edge_q1 = nullptr;
+  cudaEvent_t edge_inputs_ready = nullptr;  // non-owning: ev_edge_in for the duration of a call, else null
   // one-item / small host-pointer calls (a planner's single-item virtuals): inputs packed in ONE pinned block and one H2D, outputs
   // in one device block and one D2H (capi.cu)
   unsigned char* h_small = nullptr;       // pinned, SMALL_STAGE_BYTES

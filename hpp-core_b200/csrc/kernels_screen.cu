@@ -97,9 +97,18 @@ __global__ void fsScatterKernel(const uint32_t* __restrict__ list, size_t ns, co
 void launchValidateEdges(Workspace* ws, int method, double param, int reverse, const double* d_q1, const double* d_q2, const double* d_L,
                          size_t n, uint32_t flags, uint8_t* d_valid, double* d_tfail, double* d_tlast, int32_t* d_pair, uint8_t* d_reason) {
   if (n == 0) return;
+  // host-pointer calls: q2 / L may still be on their way (capi.cu); waited for right before they are first read
+  cudaEvent_t inputsReady = ws->edge_inputs_ready;
+  ws->edge_inputs_ready = nullptr;
+  auto waitInputs = [&]() {
+    if (!inputsReady) return;
+    HPPB200_CUDA_CHECK(cudaStreamWaitEvent(ws->stream, inputsReady, 0));
+    inputsReady = nullptr;
+  };
   const bool screen = ws->first_sample_screen && method != HPPB200_METHOD_DISCRETIZED && n >= ws->first_sample_min && n <= 0x7fffffffull &&
                       ws->max_iterations >= 1 && ws->view.nbgpairs > 0 && firstSampleScreenAvailable(ws);
   if (!screen) {
+    waitInputs();
     launchValidateEdgesCore(ws, method, param, reverse, d_q1, d_q2, d_L, n, flags, d_valid, d_tfail, d_tlast, d_pair, d_reason);
     return;
   }
@@ -110,6 +119,7 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   if (!ws->h_fs) HPPB200_CUDA_CHECK(cudaHostAlloc((void**)&ws->h_fs, (1 + kMaxChunks) * sizeof(unsigned long long), cudaHostAllocDefault));
   const double* qStart = d_q1;
   if (reverse) {
+    waitInputs();
     ws->d_fs_q.reserve(n * (size_t)nq);
     fsStartConfigKernel<<<(unsigned)((n * (size_t)nq + 255) / 256), 256, 0, ws->stream>>>(d_q1, d_q2, d_L, n, nq, ws->d_fs_q.p);
     HPPB200_CUDA_CHECK(cudaGetLastError());
@@ -136,6 +146,7 @@ void launchValidateEdges(Workspace* ws, int method, double param, int reverse, c
   HPPB200_CUDA_CHECK(cub::DeviceSelect::Flagged(ws->d_fs_tmp.p, tmpBytes, iota, ws->d_fs_valid.p, ws->d_fs_list.p, ws->d_fs_cnt.p, (int)n, ws->stream));
   ws->stats.kernel_launches += 2;
   HPPB200_CUDA_CHECK(cudaMemcpyAsync(ws->h_fs, ws->d_fs_cnt.p, (1 + chunks) * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ws->stream));
+  waitInputs();  // (everything below reads q2 / L; the synchronisation that follows covers their copies as well)
   HPPB200_CUDA_CHECK(cudaStreamSynchronize(ws->stream));
   const size_t ns = (size_t)ws->h_fs[0];
   bool overflow = false;
